@@ -1,0 +1,89 @@
+"""ctypes binding of libdctr.so (include/dctr.h).  There is NO fallback: if the CUDA library is missing
+or a call fails, this raises."""
+import ctypes
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdctr.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+OK, EINVAL, EWORKSPACE, ECUDA = 0, -1, -2, -3
+ACT = {"none": 0, None: 0, "tanh": 1, "relu": 2, "sigmoid": 3}
+CROSS = {"none": 0, None: 0, "ip": 1, "op": 2}
+SCATTER_SUM, SCATTER_SEQ_DECAY = 0, 1
+GEMM_NN, GEMM_NT, GEMM_TN = 0, 1, 2
+EPI_NONE, EPI_FWD, EPI_DGRAD = 0, 1, 2
+LONG_SEG, SEG_CHUNK = 64, 128
+
+_p, _i, _l, _f, _z = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float, ctypes.c_size_t
+
+# name -> (restype, argtypes); must list every symbol include/dctr.h declares (tests/test_abi.py checks)
+SIGNATURES = {
+    "dctr_version": (_i, []),
+    "dctr_last_error": (ctypes.c_char_p, []),
+    "dctr_launch_count": (ctypes.c_longlong, []),
+    "dctr_gather_concat_fwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
+    "dctr_cross_bwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
+    "dctr_fm_fwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _p, _p, _f, _p, _p, _p, _p, _p, _i, _p]),
+    "dctr_sort_rows_workspace": (_z, [_l]),
+    "dctr_sort_rows": (_i, [_p, _l, _l, _p, _p, _p, _z, _p]),
+    "dctr_scatter_workspace": (_z, [_l, _i]),
+    "dctr_scatter_sgd": (_i, [_i, _p, _p, _l, _i, _i, _p, _l, _i, _p, _f, _f, _p, _l, _i, _p, _z, _p]),
+    "dctr_scatter_sgd_fm": (_i, [_p, _p, _l, _i, _i, _p, _p, _i, _p, _f, _f, _p, _l, _i, _p, _z, _p]),
+    "dctr_decay_sweep": (_i, [_p, _l, _i, _f, _p, _l, _p]),
+    "dctr_gemm": (_i, [_i, _i, _i, _i, _p, _i, _p, _i, _p, _i, _i, _i, _p, _p, _i, _p, _i, _i, _p]),
+    "dctr_splitk_reduce": (_i, [_p, _i, _i, _i, _i, _p, _i, _p]),
+    "dctr_gemm_tc": (_i, [_i, _i, _i, _i, _p, _i, _p, _i, _p, _i, _i, _i, _p, _p, _i, _p, _i, _p]),
+    "dctr_out_xent_fwd": (_i, [_p, _i, _i, _i, _p, _p, _p, _f, _p, _p, _p, _p, _p]),
+    "dctr_out_bwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
+    "dctr_col_wsum_workspace": (_z, [_i, _i]),
+    "dctr_col_wsum": (_i, [_p, _i, _i, _i, _p, _p, _p, _z, _p]),
+    "dctr_vec_sum": (_i, [_p, _i, _f, _p, _p]),
+    "dctr_dense_sgd": (_i, [_p, _p, _l, _f, _f, _p]),
+}
+
+_lib = None
+
+
+def build(force=False):
+    """Compile libdctr.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    if force:
+        subprocess.run(["make", "-C", CSRC, "clean"], check=True, capture_output=True)
+    r = subprocess.run(["make", "-C", CSRC, "-j8"], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("building libdctr.so failed:\n" + r.stdout[-4000:] + r.stderr[-4000:])
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "libdctr.so is missing (%s): run `python -c 'import __graft_entry__ as g; g.build()'` or "
+                "`make -C deep-ctr_b200/csrc`.  There is no CPU fallback." % LIB_PATH)
+        h = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(h, name)
+            fn.restype, fn.argtypes = res, args
+        if h.dctr_version() != 1:
+            raise RuntimeError("libdctr.so version mismatch")
+        _lib = h
+    return _lib
+
+
+def call(name, *args):
+    """Invoke an int-returning entry point; raise RuntimeError with dctr_last_error() on failure."""
+    rc = getattr(lib(), name)(*args)
+    if rc != 0:
+        raise RuntimeError("%s failed (%d): %s" % (name, rc, lib().dctr_last_error().decode()))
+
+
+def launch_count():
+    return int(lib().dctr_launch_count())
+
+
+def ptr(t):
+    """device pointer of a torch tensor (or None)."""
+    return None if t is None else t.data_ptr()

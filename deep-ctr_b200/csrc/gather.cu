@@ -1,0 +1,215 @@
+// K1 / K2 / K3: per-field embedding gather + concat with the inner- / outer-product layer fused in,
+// and the backward of that layer into a per-(sample, field) gradient buffer.
+//
+// One warp owns one sample.  The F rows of the sample ("field block") are fetched with 128-bit loads
+// (row stride ld is a multiple of 4 floats, so a row is ld/4 LDG.128), scaled by the field weight and
+// staged in shared memory; the concat / IP / OP outputs are then produced from the staged block and
+// written with warp-coalesced stores.  HBM-bound: no tensor cores here by design.
+#include "common.cuh"
+
+namespace dctr {
+
+constexpr int kGatherWarps = 8;
+
+// stage e[f][0:ld) = w_f * table[id_f][0:ld) for one sample into this warp's smem block
+__device__ __forceinline__ void stage_field_block(const int32_t* __restrict__ ids, const float* __restrict__ wts,
+                                                  const float* __restrict__ table, int ld, int F, int64_t n,
+                                                  int lane, float* e) {
+    const int Q = ld >> 2;
+    const int T = F * Q;
+    for (int t = lane; t < T; t += 32) {
+        const int f = t / Q;
+        const int q = t - f * Q;
+        const int64_t p = n * F + f;
+        const int64_t id = ids[p];
+        const float w = wts ? wts[p] : 1.f;
+        float4 v = ldg_f4(table + id * ld + q * 4);
+        v.x *= w; v.y *= w; v.z *= w; v.w *= w;
+        *reinterpret_cast<float4*>(e + f * ld + q * 4) = v;
+    }
+    __syncwarp();
+}
+
+template <int CROSS>
+__global__ void __launch_bounds__(kGatherWarps * 32)
+gather_concat_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
+                     const float* __restrict__ table, int ld, int N, int F, int d, int bias_first,
+                     const float* __restrict__ bias, int act0, float* __restrict__ out, int ldz) {
+    extern __shared__ __align__(16) float smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float* e = smem + warp * F * ld;
+    const int Fd = F * d;
+    const int P = F * (F - 1) / 2;
+    const int crossw = CROSS == DCTR_CROSS_IP ? P : (CROSS == DCTR_CROSS_OP ? d * d : 0);
+    const int D0 = Fd + crossw + 1;
+    // pair table (i<<8 | j), i-outer / j-inner: the order of FNN_IP_L3.py:91-94
+    unsigned short* pairs = reinterpret_cast<unsigned short*>(smem + kGatherWarps * F * ld);
+    if (CROSS == DCTR_CROSS_IP) {
+        for (int i = threadIdx.x; i < F - 1; i += blockDim.x) {
+            int base = i * F - i * (i + 1) / 2 - i - 1;
+            for (int j = i + 1; j < F; ++j) pairs[base + j] = (unsigned short)((i << 8) | j);
+        }
+        __syncthreads();
+    }
+    const float bval = act_fwd(act0, bias ? __ldg(bias) : 0.f);
+
+    for (int64_t n = (int64_t)blockIdx.x * kGatherWarps + warp; n < N; n += (int64_t)gridDim.x * kGatherWarps) {
+        stage_field_block(ids, wts, table, ld, F, n, lane, e);
+        float* row = out + n * (int64_t)ldz;
+        const int eoff = bias_first ? 1 : 0;
+        for (int t = lane; t < Fd; t += 32) {
+            const int f = t / d;
+            const int c = t - f * d;
+            row[eoff + t] = act_fwd(act0, e[f * ld + c]);
+        }
+        if (CROSS == DCTR_CROSS_IP) {
+            for (int t = lane; t < P; t += 32) {
+                const int ij = pairs[t];
+                const float* ei = e + (ij >> 8) * ld;
+                const float* ej = e + (ij & 255) * ld;
+                float acc = 0.f;
+                for (int c = 0; c < d; ++c) acc = fmaf(ei[c], ej[c], acc);
+                row[Fd + t] = act_fwd(act0, acc);
+            }
+        } else if (CROSS == DCTR_CROSS_OP) {
+            // q[a,b] = sum_j prefix_{<j}[a] * e_j[b]   (== sum_{i<j} e_i[a] e_j[b], FNN_OP_L3.py:93-97)
+            for (int t = lane; t < crossw; t += 32) {
+                const int a = t / d, b = t - a * d;
+                float acc = 0.f, pre = 0.f;
+                for (int j = 0; j < F; ++j) {
+                    acc = fmaf(pre, e[j * ld + b], acc);
+                    pre += e[j * ld + a];
+                }
+                row[Fd + t] = act_fwd(act0, acc);
+            }
+        }
+        if (lane == 0) row[bias_first ? 0 : Fd + crossw] = bval;
+        for (int c = D0 + lane; c < ldz; c += 32) row[c] = 0.f;
+        __syncwarp();
+    }
+}
+
+template <int CROSS>
+__global__ void __launch_bounds__(kGatherWarps * 32)
+cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts, const float* __restrict__ table,
+                 int ld, int N, int F, int d, const float* __restrict__ dz, int ldz,
+                 float* __restrict__ ge, int ldg) {
+    extern __shared__ __align__(16) float smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int Fd = F * d;
+    const int P = F * (F - 1) / 2;
+    const int crossw = CROSS == DCTR_CROSS_IP ? P : (CROSS == DCTR_CROSS_OP ? d * d : 0);
+    const int per_warp = F * ld * (CROSS == DCTR_CROSS_OP ? 2 : 1) + crossw + (CROSS == DCTR_CROSS_OP ? d : 0);
+    float* e = smem + warp * per_warp;
+    float* pre = e + F * ld;                                        // OP only: prefix_{<f}[a]
+    float* dc = e + F * ld * (CROSS == DCTR_CROSS_OP ? 2 : 1);      // dL/dcross
+    float* tot = dc + crossw;                                       // OP only: sum_f e_f
+
+    for (int64_t n = (int64_t)blockIdx.x * kGatherWarps + warp; n < N; n += (int64_t)gridDim.x * kGatherWarps) {
+        const float* dzr = dz + n * (int64_t)ldz;
+        if (CROSS != DCTR_CROSS_NONE) {
+            for (int t = lane; t < crossw; t += 32) dc[t] = dzr[Fd + t];
+            stage_field_block(ids, wts, table, ld, F, n, lane, e);   // ends with __syncwarp
+        }
+        if (CROSS == DCTR_CROSS_OP) {
+            for (int c = lane; c < d; c += 32) {
+                float run = 0.f;
+                for (int j = 0; j < F; ++j) { pre[j * ld + c] = run; run += e[j * ld + c]; }
+                tot[c] = run;
+            }
+            __syncwarp();
+        }
+        for (int t = lane; t < Fd; t += 32) {
+            const int f = t / d;
+            const int c = t - f * d;
+            float acc = dzr[t];
+            if (CROSS == DCTR_CROSS_IP) {
+                // d e_f[c] += sum_{j != f} dp[pi(min,max)] * e_j[c]
+                for (int j = 0; j < f; ++j) acc = fmaf(dc[j * F - j * (j + 1) / 2 + f - j - 1], e[j * ld + c], acc);
+                const int base = f * F - f * (f + 1) / 2 - f - 1;
+                for (int j = f + 1; j < F; ++j) acc = fmaf(dc[base + j], e[j * ld + c], acc);
+            } else if (CROSS == DCTR_CROSS_OP) {
+                // as the j of a pair: sum_a dq[a,c] * prefix_{<f}[a]; as the i: sum_b dq[c,b] * suffix_{>f}[b]
+                for (int a = 0; a < d; ++a) {
+                    const float suf = tot[a] - pre[f * ld + a] - e[f * ld + a];
+                    acc = fmaf(dc[a * d + c], pre[f * ld + a], acc);
+                    acc = fmaf(dc[c * d + a], suf, acc);
+                }
+            }
+            const float w = wts ? wts[n * F + f] : 1.f;
+            ge[(n * F + f) * (int64_t)ldg + c] = w * acc;
+        }
+        if (ldg > d) {
+            const int padw = ldg - d;
+            for (int t = lane; t < F * padw; t += 32) {
+                const int f = t / padw;
+                ge[(n * F + f) * (int64_t)ldg + d + (t - f * padw)] = 0.f;
+            }
+        }
+        __syncwarp();
+    }
+}
+
+static int gather_grid(int N) {
+    int blocks = ceil_div(N, kGatherWarps);
+    int cap = kNumSMs * 8;  // 8 resident CTAs of 8 warps = 64 warps / SM
+    return blocks < cap ? (blocks > 0 ? blocks : 1) : cap;
+}
+
+}  // namespace dctr
+
+using namespace dctr;
+
+extern "C" int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
+                                      int N, int F, int d, int cross, int bias_first, const float* bias, int act0,
+                                      float* out, int ldz, void* stream) {
+    DCTR_REQUIRE(ids && table && out, "gather_concat_fwd: null pointer");
+    DCTR_REQUIRE(N >= 0 && F > 0 && F < 256 && d > 0 && d <= ld && (ld & 3) == 0, "gather_concat_fwd: bad shape N=%d F=%d d=%d ld=%d", N, F, d, ld);
+    DCTR_REQUIRE(cross >= 0 && cross <= 2 && !(cross && bias_first), "gather_concat_fwd: bad cross/bias_first");
+    const int crossw = cross == DCTR_CROSS_IP ? F * (F - 1) / 2 : (cross == DCTR_CROSS_OP ? d * d : 0);
+    DCTR_REQUIRE(ldz >= F * d + crossw + 1, "gather_concat_fwd: ldz=%d < D0=%d", ldz, F * d + crossw + 1);
+    DCTR_REQUIRE(X > 0 && X * (int64_t)ld < ((int64_t)1 << 40), "gather_concat_fwd: bad X");
+    if (N == 0) return DCTR_OK;
+    size_t smem = (size_t)kGatherWarps * F * ld * sizeof(float) + (cross == DCTR_CROSS_IP ? (size_t)crossw * 2 + 16 : 0);
+    DCTR_REQUIRE(smem <= 200 * 1024, "gather_concat_fwd: field block too large for shared memory");
+    dim3 grid(gather_grid(N)), block(kGatherWarps * 32);
+    cudaStream_t st = as_stream(stream);
+#define LAUNCH_G(C)                                                                                          \
+    do {                                                                                                     \
+        if (smem > 48 * 1024)                                                                                \
+            cudaFuncSetAttribute(gather_concat_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        gather_concat_kernel<C><<<grid, block, smem, st>>>(ids, wts, table, ld, N, F, d, bias_first, bias,   \
+                                                           act0, out, ldz);                                  \
+    } while (0)
+    if (cross == DCTR_CROSS_IP) LAUNCH_G(DCTR_CROSS_IP);
+    else if (cross == DCTR_CROSS_OP) LAUNCH_G(DCTR_CROSS_OP);
+    else LAUNCH_G(DCTR_CROSS_NONE);
+#undef LAUNCH_G
+    return check_launch("gather_concat_kernel");
+}
+
+extern "C" int dctr_cross_bwd(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
+                              int N, int F, int d, int cross, const float* dz, int ldz,
+                              float* ge, int ldg, void* stream) {
+    DCTR_REQUIRE(ids && table && dz && ge, "cross_bwd: null pointer");
+    DCTR_REQUIRE(N >= 0 && F > 0 && F < 256 && d > 0 && d <= ld && (ld & 3) == 0 && ldg >= d, "cross_bwd: bad shape");
+    DCTR_REQUIRE(cross >= 0 && cross <= 2 && X > 0, "cross_bwd: bad cross");
+    if (N == 0) return DCTR_OK;
+    const int crossw = cross == DCTR_CROSS_IP ? F * (F - 1) / 2 : (cross == DCTR_CROSS_OP ? d * d : 0);
+    const int per_warp = F * ld * (cross == DCTR_CROSS_OP ? 2 : 1) + crossw + (cross == DCTR_CROSS_OP ? d : 0);
+    size_t smem = (size_t)kGatherWarps * per_warp * sizeof(float);
+    DCTR_REQUIRE(smem <= 200 * 1024, "cross_bwd: field block too large for shared memory");
+    dim3 grid(gather_grid(N)), block(kGatherWarps * 32);
+    cudaStream_t st = as_stream(stream);
+#define LAUNCH_B(C)                                                                                          \
+    do {                                                                                                     \
+        if (smem > 48 * 1024)                                                                                \
+            cudaFuncSetAttribute(cross_bwd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        cross_bwd_kernel<C><<<grid, block, smem, st>>>(ids, wts, table, ld, N, F, d, dz, ldz, ge, ldg);      \
+    } while (0)
+    if (cross == DCTR_CROSS_IP) LAUNCH_B(DCTR_CROSS_IP);
+    else if (cross == DCTR_CROSS_OP) LAUNCH_B(DCTR_CROSS_OP);
+    else LAUNCH_B(DCTR_CROSS_NONE);
+#undef LAUNCH_B
+    return check_launch("cross_bwd_kernel");
+}

@@ -1,0 +1,319 @@
+"""Device-side step engine: owns the HBM-resident state (embedding table, flat MLP parameters, activation
+and workspace buffers) for one static batch size and issues the libdctr kernels of one train / predict step
+on the current CUDA stream.  torch is used for device memory, streams and CUDA-graph capture only.
+
+Layout in HBM
+  table   float32 [X, ld]      row = [w | v_1..v_r | 0 pad], ld = round_up(d, 4): a row is ld/4 128-bit loads
+  params  float32 flat         [W_0 (K_0 x ldw_0) | b_0 | ... | w_out (K) | b_out | bias(w_0 / fm b)], 16 B aligned
+  grads   float32 flat         same layout (one all-reduce buffer, one dense-SGD launch)
+  ins[l]  float32 [N, ld_l]    input of layer l (ins[0] = act0(z)), ld_l = round_up(width, 4), pad columns 0
+"""
+import torch
+
+from . import _lib as L
+
+
+def _r4(n):
+    return (n + 3) // 4 * 4
+
+
+class StepEngine:
+    def __init__(self, X, F, rank, hidden, batch_size, cross="none", bias_first=False, act0="none", act="tanh",
+                 scatter_mode="sum", device="cuda", ld=None):
+        L.lib()  # fail loudly when libdctr.so is missing
+        self.dev = torch.device(device)
+        self.X, self.F, self.d, self.N = int(X), int(F), int(rank) + 1, int(batch_size)
+        self.ld = ld or _r4(self.d)
+        self.cross, self.bias_first, self.act0, self.act = cross, bool(bias_first), act0, act
+        self.scatter_mode = L.SCATTER_SEQ_DECAY if scatter_mode == "seq_decay" else L.SCATTER_SUM
+        F_, d_ = self.F, self.d
+        self.crossw = {"none": 0, "ip": F_ * (F_ - 1) // 2, "op": d_ * d_}[cross]
+        self.D0 = F_ * d_ + self.crossw + 1
+        self.widths = [self.D0] + list(hidden)          # inputs of layers 0..L-1; the last layer maps to 1
+        self.nl = len(self.widths)
+        assert self.nl >= 2, "need at least one hidden layer"
+        f32 = dict(dtype=torch.float32, device=self.dev)
+        i32 = dict(dtype=torch.int32, device=self.dev)
+        N = self.N
+        self.table = torch.zeros(self.X, self.ld, **f32)
+        # ---- flat parameter / gradient buffers ----
+        self.w_off, self.b_off, self.ldw = [], [], []
+        off = 0
+        for l in range(self.nl):
+            K = self.widths[l]
+            Hout = self.widths[l + 1] if l + 1 < self.nl else 1
+            ldw = _r4(Hout) if l + 1 < self.nl else 1
+            self.ldw.append(ldw)
+            self.w_off.append(off)
+            off += _r4(K * ldw)
+            self.b_off.append(off)
+            off += _r4(Hout)
+        self.bias_off = off
+        off += 4
+        self.n_params = off
+        self.params = torch.zeros(off, **f32)
+        self.grads = torch.zeros(off, **f32)
+        # ---- activations / scratch ----
+        self.ldi = [_r4(w) for w in self.widths]
+        self.ins = [torch.zeros(N, self.ldi[l], **f32) for l in range(self.nl)]
+        maxw = max(self.ldi)
+        self.dbuf = [torch.zeros(N, maxw, **f32) for _ in range(2)]
+        self.ids = torch.zeros(N, F_, **i32)
+        self.wts = torch.ones(N, F_, **f32)
+        self.y = torch.zeros(N, **f32)
+        self.logit = torch.zeros(N, **f32)
+        self.pred = torch.zeros(N, **f32)
+        self.loss_n = torch.zeros(N, **f32)
+        self.dlogit = torch.zeros(N, **f32)
+        self.loss = torch.zeros(1, **f32)
+        self.masks = [None] * self.nl                   # mask on ins[l]; tensors [N, ldi] or [1, ldi]
+        M = N * F_
+        self.M = M
+        self.sorted_rows = torch.zeros(M, **i32)
+        self.sorted_pos = torch.zeros(M, **i32)
+        self.sort_ws = torch.zeros(L.lib().dctr_sort_rows_workspace(M), dtype=torch.uint8, device=self.dev)
+        self.scat_ws = torch.zeros(L.lib().dctr_scatter_workspace(M, self.ld), dtype=torch.uint8, device=self.dev)
+        self.ldg = self.ld
+        self.ge = torch.zeros(N, F_, self.ldg, **f32) if cross != "none" else None
+        # split-K plan for the weight gradients: aim at ~2 waves of 64x64 tiles
+        self.splits = []
+        ws_elems = 4
+        for l in range(self.nl - 1):
+            K, H = self.widths[l], self.widths[l + 1]
+            tiles = -(-K // 64) * -(-H // 64)
+            s = max(1, min(max(1, N // 256), -(-2 * 148 // tiles)))
+            self.splits.append(s)
+            ws_elems = max(ws_elems, s * K * self.ldw[l])
+        self.splitk_ws = torch.zeros(ws_elems, **f32)
+        self.col_ws = torch.zeros(max(16, L.lib().dctr_col_wsum_workspace(N, maxw)), dtype=torch.uint8, device=self.dev)
+        self.side = torch.cuda.Stream(device=self.dev)
+        self.wts_are_ones = True
+
+    # ---- parameter views -------------------------------------------------------------------------
+    def W(self, l, buf=None):
+        buf = self.params if buf is None else buf
+        K = self.widths[l]
+        return buf[self.w_off[l]:self.w_off[l] + K * self.ldw[l]].view(K, self.ldw[l])
+
+    def b(self, l, buf=None):
+        buf = self.params if buf is None else buf
+        Hout = self.widths[l + 1] if l + 1 < self.nl else 1
+        return buf[self.b_off[l]:self.b_off[l] + Hout]
+
+    def bias(self, buf=None):
+        buf = self.params if buf is None else buf
+        return buf[self.bias_off:self.bias_off + 1]
+
+    def set_layer(self, l, W, b):
+        """W: [K, Hout] array-like, b: [Hout]."""
+        W = torch.as_tensor(W, dtype=torch.float32).reshape(self.widths[l], -1)
+        self.W(l)[:, :W.shape[1]] = W.to(self.dev)
+        self.b(l).copy_(torch.as_tensor(b, dtype=torch.float32).reshape(-1))
+
+    def get_layer(self, l):
+        Hout = self.widths[l + 1] if l + 1 < self.nl else 1
+        return self.W(l)[:, :Hout].cpu().numpy(), self.b(l).cpu().numpy()
+
+    def set_table(self, table):
+        t = torch.as_tensor(table, dtype=torch.float32)
+        self.table.zero_()
+        self.table[:, :t.shape[1]] = t.to(self.dev)
+
+    def get_table(self):
+        return self.table[:, :self.d].cpu().numpy()
+
+    # ---- kernels ---------------------------------------------------------------------------------
+    def _st(self):
+        return torch.cuda.current_stream(self.dev).cuda_stream
+
+    def _mask(self, l):
+        m = self.masks[l]
+        if m is None:
+            return None, 0
+        return m.data_ptr(), (0 if m.shape[0] == 1 else m.stride(0))
+
+    def forward(self, with_loss, gscale=1.0):
+        st = self._st()
+        N, F, d, p = self.N, self.F, self.d, L.ptr
+        wts = None if self.wts_are_ones else self.wts
+        L.call("dctr_gather_concat_fwd", p(self.ids), p(wts), p(self.table), self.X, self.ld, N, F, d,
+               L.CROSS[self.cross], int(self.bias_first), p(self.bias()), L.ACT[self.act0],
+               p(self.ins[0]), self.ldi[0], st)
+        if self.masks[0] is not None:
+            self.ins[0].mul_(self.masks[0])     # input dropout (tf.nn.dropout on act(z1), FNN.py:87): torch elementwise
+        for l in range(self.nl - 1):
+            mp, mld = self._mask(l + 1)
+            L.call("dctr_gemm", L.GEMM_NN, N, self.widths[l + 1], self.widths[l], p(self.ins[l]), self.ldi[l],
+                   p(self.W(l)), self.ldw[l], p(self.ins[l + 1]), self.ldi[l + 1], L.EPI_FWD, L.ACT[self.act],
+                   p(self.b(l)), None, 0, mp, mld, 1, st)
+        last = self.nl - 1
+        L.call("dctr_out_xent_fwd", p(self.ins[last]), self.ldi[last], N, self.widths[last], p(self.W(last)),
+               p(self.b(last)), p(self.y) if with_loss else None, float(gscale), p(self.logit), p(self.pred),
+               p(self.loss_n), p(self.dlogit), st)
+        if with_loss:
+            L.call("dctr_vec_sum", p(self.loss_n), N, float(gscale), p(self.loss), st)
+
+    def backward(self):
+        """Fills self.grads (dense) and leaves d loss / d z in self.dbuf[k]; returns that buffer."""
+        st = self._st()
+        N, p = self.N, L.ptr
+        last = self.nl - 1
+        H = self.widths[last]
+        cw, cwb = p(self.col_ws), self.col_ws.numel()
+        L.call("dctr_col_wsum", p(self.ins[last]), self.ldi[last], N, H, p(self.dlogit), p(self.W(last, self.grads)), cw, cwb, st)
+        L.call("dctr_vec_sum", p(self.dlogit), N, 1.0, p(self.b(last, self.grads)), st)
+        cur = 0
+        mp, mld = self._mask(last)
+        ldd = self.dbuf[0].stride(0)
+        L.call("dctr_out_bwd", p(self.dlogit), p(self.W(last)), p(self.ins[last]), self.ldi[last], N, H,
+               L.ACT[self.act], mp, mld, p(self.dbuf[cur]), ldd, st)
+        for l in range(last - 1, -1, -1):
+            K, Hl = self.widths[l], self.widths[l + 1]
+            dpre = self.dbuf[cur]
+            s = self.splits[l]
+            gW = self.W(l, self.grads)
+            if s > 1:
+                L.call("dctr_gemm", L.GEMM_TN, K, Hl, N, p(self.ins[l]), self.ldi[l], p(dpre), ldd, p(self.splitk_ws),
+                       self.ldw[l], L.EPI_NONE, 0, None, None, 0, None, 0, s, st)
+                L.call("dctr_splitk_reduce", p(self.splitk_ws), s, K, Hl, self.ldw[l], p(gW), self.ldw[l], st)
+            else:
+                L.call("dctr_gemm", L.GEMM_TN, K, Hl, N, p(self.ins[l]), self.ldi[l], p(dpre), ldd, p(gW),
+                       self.ldw[l], L.EPI_NONE, 0, None, None, 0, None, 0, 1, st)
+            L.call("dctr_col_wsum", p(dpre), ldd, N, Hl, None, p(self.b(l, self.grads)), cw, cwb, st)
+            mp, mld = self._mask(l)
+            act = self.act if l > 0 else self.act0
+            L.call("dctr_gemm", L.GEMM_NT, N, K, Hl, p(dpre), ldd, p(self.W(l)), self.ldw[l], p(self.dbuf[cur ^ 1]), ldd,
+                   L.EPI_DGRAD, L.ACT[act], None, p(self.ins[l]), self.ldi[l], mp, mld, 1, st)
+            cur ^= 1
+        return self.dbuf[cur]
+
+    def sort_ids(self, ids=None, M=None, rows=None, pos=None, ws=None):
+        ids = self.ids if ids is None else ids
+        M = self.M if M is None else M
+        ws = self.sort_ws if ws is None else ws
+        L.call("dctr_sort_rows", L.ptr(ids), M, self.X, L.ptr(self.sorted_rows if rows is None else rows),
+               L.ptr(self.sorted_pos if pos is None else pos), L.ptr(ws), ws.numel(), self._st())
+
+    def embedding_update(self, dz, lr, decay=1.0, train_bias=True):
+        """dz: [N, ldd] gradient w.r.t. z.  Requires sort_ids() to have run on this stream (or joined)."""
+        st = self._st()
+        N, F, d, p = self.N, self.F, self.d, L.ptr
+        ldd = dz.stride(0)
+        wts = None if self.wts_are_ones else self.wts
+        if train_bias:
+            col = 0 if self.bias_first else F * d + self.crossw
+            L.call("dctr_col_wsum", dz.data_ptr() + 4 * col, ldd, N, 1, None, p(self.bias(self.grads)),
+                   p(self.col_ws), self.col_ws.numel(), st)
+        if self.cross != "none":
+            L.call("dctr_cross_bwd", p(self.ids), p(wts), p(self.table), self.X, self.ld, N, F, d, L.CROSS[self.cross],
+                   p(dz), ldd, p(self.ge), self.ldg, st)
+            g, g_ld_n, g_ld_f, w = self.ge.data_ptr(), F * self.ldg, self.ldg, None
+        else:
+            g, g_ld_n, g_ld_f, w = dz.data_ptr() + (4 if self.bias_first else 0), ldd, d, p(wts)
+        L.call("dctr_scatter_sgd", self.scatter_mode, p(self.sorted_rows), p(self.sorted_pos), self.M, F, d,
+               g, g_ld_n, g_ld_f, w, float(lr), float(decay), p(self.table), self.X, self.ld,
+               p(self.scat_ws), self.scat_ws.numel(), st)
+
+    def dense_update(self, lr, last_decay=1.0):
+        st = self._st()
+        if last_decay == 1.0:
+            L.call("dctr_dense_sgd", L.ptr(self.params), L.ptr(self.grads), self.n_params, float(lr), 1.0, st)
+        else:   # Theano: cost += lambda1*(|w3|^2 + b3^2) touches the output unit only (FNN_wnzh.py:173)
+            lo = self.w_off[self.nl - 1]
+            hi = self.bias_off
+            pp, gg = self.params.data_ptr(), self.grads.data_ptr()
+            L.call("dctr_dense_sgd", pp, gg, lo, float(lr), 1.0, st)
+            L.call("dctr_dense_sgd", pp + 4 * lo, gg + 4 * lo, hi - lo, float(lr), float(last_decay), st)
+            L.call("dctr_dense_sgd", pp + 4 * hi, gg + 4 * hi, self.n_params - hi, float(lr), 1.0, st)
+
+    def train_step(self, lr, decay=1.0, gscale=1.0, train_bias=True, last_decay=1.0):
+        """One full step on device buffers ids/wts/y (+ masks).  The row sort only depends on the ids, so it
+        runs on a side stream concurrently with the MLP forward/backward."""
+        cur = torch.cuda.current_stream(self.dev)
+        self.side.wait_stream(cur)
+        with torch.cuda.stream(self.side):
+            self.sort_ids()
+        self.forward(True, gscale)
+        dz = self.backward()
+        cur.wait_stream(self.side)
+        self.embedding_update(dz, lr, decay, train_bias)
+        self.dense_update(lr, last_decay)
+
+
+class FMEngine:
+    """FM (and LR with rank 0): fm_fwd -> [sort on a side stream] -> scatter_sgd_fm -> bias SGD (+ L2 sweep)."""
+
+    def __init__(self, X, F, rank, batch_size, device="cuda", ld=None):
+        L.lib()
+        self.dev = torch.device(device)
+        self.X, self.F, self.d, self.N = int(X), int(F), int(rank) + 1, int(batch_size)
+        self.ld = ld or _r4(self.d)
+        self.lds = _r4(self.d)
+        f32 = dict(dtype=torch.float32, device=self.dev)
+        i32 = dict(dtype=torch.int32, device=self.dev)
+        N, M = self.N, self.N * self.F
+        self.M = M
+        self.table = torch.zeros(self.X, self.ld, **f32)
+        self.params = torch.zeros(4, **f32)     # [b, -, -, -]
+        self.grads = torch.zeros(4, **f32)
+        self.ids = torch.zeros(N, self.F, **i32)
+        self.wts = torch.ones(N, self.F, **f32)
+        self.y = torch.zeros(N, **f32)
+        self.logit = torch.zeros(N, **f32)
+        self.pred = torch.zeros(N, **f32)
+        self.loss_n = torch.zeros(N, **f32)
+        self.g = torch.zeros(N, **f32)
+        self.s = torch.zeros(N, self.lds, **f32)
+        self.loss = torch.zeros(1, **f32)
+        self.sorted_rows = torch.zeros(M, **i32)
+        self.sorted_pos = torch.zeros(M, **i32)
+        self.sort_ws = torch.zeros(L.lib().dctr_sort_rows_workspace(M), dtype=torch.uint8, device=self.dev)
+        self.scat_ws = torch.zeros(L.lib().dctr_scatter_workspace(M, self.ld), dtype=torch.uint8, device=self.dev)
+        self.side = torch.cuda.Stream(device=self.dev)
+        self.wts_are_ones = False
+
+    def bias(self, buf=None):
+        return (self.params if buf is None else buf)[0:1]
+
+    def set_table(self, table):
+        t = torch.as_tensor(table, dtype=torch.float32)
+        self.table.zero_()
+        self.table[:, :t.shape[1]] = t.to(self.dev)
+
+    def get_table(self):
+        return self.table[:, :self.d].cpu().numpy()
+
+    def _st(self):
+        return torch.cuda.current_stream(self.dev).cuda_stream
+
+    def forward(self, with_loss, gscale=1.0):
+        p = L.ptr
+        wts = None if self.wts_are_ones else self.wts
+        L.call("dctr_fm_fwd", p(self.ids), p(wts), p(self.table), self.X, self.ld, self.N, self.F, self.d,
+               p(self.bias()), p(self.y) if with_loss else None, float(gscale), p(self.logit), p(self.pred),
+               p(self.loss_n), p(self.g), p(self.s) if with_loss else None, self.lds, self._st())
+        if with_loss:
+            L.call("dctr_vec_sum", p(self.loss_n), self.N, float(gscale), p(self.loss), self._st())
+
+    def sort_ids(self):
+        L.call("dctr_sort_rows", L.ptr(self.ids), self.M, self.X, L.ptr(self.sorted_rows), L.ptr(self.sorted_pos),
+               L.ptr(self.sort_ws), self.sort_ws.numel(), self._st())
+
+    def train_step(self, lr, lam=0.0, gscale=1.0, dense_l2=True):
+        cur = torch.cuda.current_stream(self.dev)
+        self.side.wait_stream(cur)
+        with torch.cuda.stream(self.side):
+            self.sort_ids()
+        self.forward(True, gscale)
+        st = self._st()
+        p = L.ptr
+        decay = 1.0 - lr * lam
+        L.call("dctr_vec_sum", p(self.g), self.N, 1.0, p(self.grads), st)           # d loss / d b = sum_n g_n
+        cur.wait_stream(self.side)
+        wts = None if self.wts_are_ones else self.wts
+        L.call("dctr_scatter_sgd_fm", p(self.sorted_rows), p(self.sorted_pos), self.M, self.F, self.d, p(self.g),
+               p(self.s), self.lds, p(wts), float(lr), float(decay), p(self.table), self.X, self.ld,
+               p(self.scat_ws), self.scat_ws.numel(), st)
+        if lam != 0.0 and dense_l2:   # FM.py:39: the L2 term reaches every row, touched or not
+            L.call("dctr_decay_sweep", p(self.table), self.X, self.ld, float(decay), p(self.sorted_rows), self.M, st)
+        L.call("dctr_dense_sgd", p(self.params), p(self.grads), 1, float(lr), float(decay), st)

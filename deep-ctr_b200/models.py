@@ -1,0 +1,400 @@
+"""Host-side mirror of the reference's model interface (the drop-in surface).
+
+The reference classes build a TensorFlow graph and are driven through `sess.run([ptmzr, loss, train_preds],
+feed_dict)` / `model.eval_preds.eval(feed_dict)` (baseline.py:351,362-366,421).  The classes here keep the
+constructor signatures, attribute names, feed keys and checkpoint format, and route every step to the
+sm_100a kernels of libdctr.so through engine.py.  numpy in, numpy out; the host<->device copies happen
+inside (pinned staging buffers), so a call is an end-to-end step.
+
+Deviations, all forced by the environment or by reference defects:
+  * random init uses numpy Generator(PCG64(seed)) per variable instead of TF's Philox stream (Q11);
+    parity runs always inject weights through the pickle path of `_init_argv[-1]` (tf_util.py:41-49);
+  * only plain SGD ('sgd') is on the fast path; 'adam' / 'ftrl' (tf_util.py:17-25) raise NotImplementedError;
+  * FNN_OP_L3 sizes h1_w from the forward's true width F*d + d*d + 1 (Q2).
+"""
+import pickle
+
+import numpy as np
+import torch
+
+from .engine import FMEngine, StepEngine
+
+
+class Placeholder(object):
+    """Stands in for a tf.placeholder: only used as a feed_dict key."""
+
+    def __init__(self, name):
+        self.name = name
+
+    def __repr__(self):
+        return "<placeholder %s>" % self.name
+
+
+class Fetch(object):
+    """Stands in for a fetchable tensor: `fetch.eval(feed_dict=...)` like tf.Tensor.eval (baseline.py:366)."""
+
+    def __init__(self, model, kind):
+        self.model, self.kind = model, kind
+
+    def eval(self, feed_dict=None):
+        return self.model._fetch(self.kind, feed_dict or {})
+
+
+class Session(object):
+    """Minimal tf.Session look-alike so the reference loop body reads the same (baseline.py:328-351)."""
+
+    def __init__(self, model):
+        self.model = model
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+    def run(self, fetches, feed_dict=None):
+        single = not isinstance(fetches, (list, tuple))
+        fl = [fetches] if single else list(fetches)
+        m = self.model
+        out = {}
+        if any(f is m.ptmzr for f in fl):
+            loss, preds = m.train_step(feed_dict)
+            out = {"ptmzr": None, "loss": loss, "train_preds": preds}
+        res = [out[f.kind] if f.kind in out else f.eval(feed_dict) for f in fl]
+        return res[0] if single else res
+
+
+def init_var_map(_init_argv, variables):
+    """tf_util.py:41-82: load `{name: ndarray}` from the pickle named by _init_argv[-1]; every missing key is
+    drawn ('random': uniform[a,b) or normal(mean, std), one seed per random variable, in declaration order)
+    or zero-filled."""
+    path = _init_argv[-1]
+    if path:
+        with open(path, "rb") as f:
+            var_map = pickle.load(f, encoding="latin1")
+        log = "init model from: %s, " % path
+    else:
+        var_map, log = {}, "random init, "
+    method = _init_argv[0]
+    a, b, seeds = _init_argv[1:-1]
+    if method == "normal":
+        log += "init method: %s(mean=%g, stddev=%g), seeds: %s\n" % (method, a, b, str(seeds))
+    else:
+        log += "init method: %s(minval=%g, maxval=%g), seeds: %s\n" % (method, a, b, str(seeds))
+    j = 0
+    for key, shape, action in variables:
+        if key in var_map:
+            var_map[key] = np.asarray(var_map[key], dtype=np.float32).reshape(shape)
+            continue
+        if action == "random":
+            rng = np.random.Generator(np.random.PCG64(seeds[j]))
+            j += 1
+            if method == "normal":
+                var_map[key] = rng.normal(a, b, size=shape).astype(np.float32)
+            else:
+                var_map[key] = rng.uniform(a, b, size=shape).astype(np.float32)
+        else:
+            var_map[key] = np.zeros(shape, dtype=np.float32)
+    return var_map, log
+
+
+def _optimizer(_ptmzr_argv):
+    """tf_util.py:15-29.  Returns (lr, log)."""
+    name = _ptmzr_argv[0]
+    if name in ("adam", "ftrl"):
+        raise NotImplementedError("optimizer %r is not on the B200 fast path yet (SGD only; SURVEY.md 8(f) f1)" % name)
+    lr = _ptmzr_argv[1]
+    return float(lr), "optimizer: %s, learning rate: %g" % (name, lr)
+
+
+class _Pinned(object):
+    """Pinned host staging for one static batch: ids int32 [N,F], wts fp32 [N,F], y fp32 [N]."""
+
+    def __init__(self, N, F):
+        self.ids = torch.empty(N, F, dtype=torch.int32).pin_memory()
+        self.wts = torch.empty(N, F, dtype=torch.float32).pin_memory()
+        self.y = torch.empty(N, dtype=torch.float32).pin_memory()
+        self.pred = torch.empty(N, dtype=torch.float32).pin_memory()
+        self.loss = torch.empty(1, dtype=torch.float32).pin_memory()
+        self.ids_np, self.wts_np, self.y_np = self.ids.numpy(), self.wts.numpy(), self.y.numpy()
+
+
+class _Base(object):
+    """Shared host logic: staging, CUDA-graph replay of the step, chunked inference."""
+
+    use_graph = True
+
+    def _setup_host(self, engine, batch_size, F):
+        self.engine = engine
+        self.N, self.F = batch_size, F
+        self._pin = _Pinned(batch_size, F)
+        self._graph = None
+        self._warm = 0
+        self.h2d_bytes = batch_size * F * 8 + batch_size * 4
+        self.d2h_bytes = batch_size * 4 + 4
+
+    def session(self):
+        return Session(self)
+
+    # -- subclasses: _device_step() issues the kernels of one train step on the current stream
+    def _run_step(self):
+        if not self.use_graph:
+            self._device_step()
+            return
+        if self._graph is None:
+            if self._warm < 2:          # eager warm-up steps before capture (attribute setup, allocator)
+                self._device_step()
+                self._warm += 1
+                return
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._device_step()
+            self._graph = g
+            # capture does not execute: fall through to the first replay
+        self._graph.replay()
+
+    def _stage_and_step(self, ids, wts, y):
+        e, pin = self.engine, self._pin
+        np.copyto(pin.ids_np, ids, casting="unsafe")
+        np.copyto(pin.wts_np, wts, casting="unsafe")
+        np.copyto(pin.y_np, y, casting="unsafe")
+        e.ids.copy_(pin.ids, non_blocking=True)
+        e.wts.copy_(pin.wts, non_blocking=True)
+        e.y.copy_(pin.y, non_blocking=True)
+        self._pre_step()
+        self._run_step()
+        pin.pred.copy_(e.pred, non_blocking=True)
+        pin.loss.copy_(e.loss, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(pin.loss[0]), pin.pred.numpy().copy()
+
+    def _pre_step(self):
+        pass
+
+    def _predict_chunks(self, ids, wts):
+        """Inference over E rows in chunks of the static batch (last chunk padded with row 0 / weight 0)."""
+        e, pin = self.engine, self._pin
+        E = ids.shape[0]
+        out = np.empty(E, dtype=np.float32)
+        saved = self._swap_masks(None)
+        for s in range(0, E, self.N):
+            k = min(self.N, E - s)
+            pin.ids_np[:k] = ids[s:s + k]
+            pin.wts_np[:k] = wts[s:s + k]
+            if k < self.N:
+                pin.ids_np[k:] = 0
+                pin.wts_np[k:] = 0
+            e.ids.copy_(pin.ids, non_blocking=True)
+            e.wts.copy_(pin.wts, non_blocking=True)
+            e.forward(False)
+            pin.pred.copy_(e.pred, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            out[s:s + k] = pin.pred.numpy()[:k]
+        self._swap_masks(saved)
+        return out
+
+    def _swap_masks(self, masks):
+        return None
+
+
+# ==================================================================================================
+# FM  (FM.py)
+# ==================================================================================================
+class FM(_Base):
+    """FM(batch_size, [X_dim, X_feas, rank], _init_argv, _ptmzr_argv, [lambda], mode, eval_size) -- FM.py:5."""
+
+    def __init__(self, batch_size, _rch_argv, _init_argv, _ptmzr_argv, _reg_argv, mode, eval_size, device="cuda"):
+        X_dim, X_feas, rank = _rch_argv
+        self.X_dim, self.X_feas, self.rank, self.mode = X_dim, X_feas, rank, mode
+        self.log = "input dim: %d, features: %d, rank: %d, " % (X_dim, X_feas, rank)
+        var_map, log = init_var_map(_init_argv, [("W", [X_dim, 1], "random"), ("V", [X_dim, rank], "random"),
+                                                 ("b", [1], "zero")])
+        self.log += log
+        eng = FMEngine(X_dim, X_feas, rank, batch_size, device=device)
+        eng.set_table(np.concatenate([var_map["W"], var_map["V"]], axis=1))
+        eng.bias().copy_(torch.as_tensor(var_map["b"], dtype=torch.float32))
+        self._setup_host(eng, batch_size, X_feas)
+        self.sp_id_hldr, self.sp_wt_hldr, self.lbl_hldr = Placeholder("sp_id"), Placeholder("sp_wt"), Placeholder("lbl")
+        if mode == "train":
+            self._lambda = float(_reg_argv[0])
+            self._reduce = _ptmzr_argv[-1]
+            self.lr, log = _optimizer(_ptmzr_argv)
+            self.log += "%s, lambda(l2): %g, reduce by: %s" % (log, self._lambda, self._reduce)
+            self.eval_size = eval_size
+            self.eval_id_hldr, self.eval_wts_hldr = Placeholder("eval_id"), Placeholder("eval_wts")
+            self.eval_wt_hldr = self.eval_wts_hldr      # ipinyou.py:192 uses this spelling
+            self.ptmzr, self.loss, self.train_preds = Fetch(self, "ptmzr"), Fetch(self, "loss"), Fetch(self, "train_preds")
+            self.eval_preds = Fetch(self, "eval_preds")
+        else:
+            self.test_preds = Fetch(self, "test_preds")
+
+    def _device_step(self):
+        gs = 1.0 if self._reduce == "sum" else 1.0 / self.N
+        self.engine.train_step(self.lr, self._lambda, gs)
+
+    def train_step(self, feed):
+        ids = np.asarray(feed[self.sp_id_hldr]).reshape(self.N, self.F)
+        wts = np.asarray(feed[self.sp_wt_hldr]).reshape(self.N, self.F)
+        y = np.asarray(feed[self.lbl_hldr]).reshape(self.N)
+        return self._stage_and_step(ids, wts, y)
+
+    def _fetch(self, kind, feed):
+        if kind == "eval_preds":
+            ids, wts = feed[self.eval_id_hldr], feed[self.eval_wts_hldr]
+        elif kind == "test_preds":
+            ids, wts = feed[self.sp_id_hldr], feed[self.sp_wt_hldr]
+        else:
+            raise ValueError("fetch %r needs Session.run with model.ptmzr" % kind)
+        ids = np.asarray(ids).reshape(-1, self.F)
+        return self._predict_chunks(ids, np.asarray(wts).reshape(-1, self.F))
+
+    def dump(self, model_path):
+        """FM.py:66-69: pickle {'W','V','b'}."""
+        t = self.engine.get_table()
+        var_map = {"W": t[:, :1].copy(), "V": t[:, 1:].copy(), "b": self.engine.bias().cpu().numpy()}
+        with open(model_path, "wb") as f:
+            pickle.dump(var_map, f)
+        print("model dumped at %s" % model_path)
+
+
+# ==================================================================================================
+# FNN family  (FNN.py, FNN_IP_L3/L5/L7.py, FNN_OP_L3.py)
+# ==================================================================================================
+class _FNNBase(_Base):
+    cross = "none"
+    n_hidden = 2
+
+    def __init__(self, cat_sizes, offsets, batch_size, _rch_argv, _init_argv, _ptmzr_argv, _reg_argv, mode,
+                 eval_size, device="cuda"):
+        X_dim, X_feas, rank = _rch_argv[:3]
+        hidden = list(_rch_argv[3:3 + self.n_hidden])
+        act_func = _rch_argv[3 + self.n_hidden]
+        self.X_dim, self.X_feas, self.rank, self.mode = X_dim, X_feas, rank, mode
+        self.offsets = np.asarray(offsets, dtype=np.int64)
+        self.n_num = X_feas - len(cat_sizes)        # 13 numeric fields for Criteo (FNN.py:41-43)
+        d = rank + 1
+        crossw = {"none": 0, "ip": X_feas * (X_feas - 1) // 2, "op": d * d}[self.cross]
+        mbd_dim = X_feas * d + crossw + 1
+        self.log = "input dim: %d, features: %d, rank: %d, embedding: %d, " % (X_dim, X_feas, rank, mbd_dim)
+        self.log += ", ".join("h%d: %d" % (i + 1, h) for i, h in enumerate(hidden)) + ", activate: %s" % act_func
+        dims = [mbd_dim] + hidden + [1]
+        variables = [("W", [X_dim, 1], "random"), ("V", [X_dim, rank], "random"), ("b", [1], "zero")]
+        for i in range(len(dims) - 1):
+            variables += [("h%d_w" % (i + 1), [dims[i], dims[i + 1]], "random"), ("h%d_b" % (i + 1), [dims[i + 1]], "zero")]
+        var_map, log = init_var_map(_init_argv, variables)
+        self.log += log
+        act = act_func if act_func in ("tanh", "relu") else "sigmoid"     # tf_util.py:32-38
+        eng = StepEngine(X_dim, X_feas, rank, hidden, batch_size, cross=self.cross, bias_first=False,
+                         act0=act, act=act, scatter_mode="sum", device=device)
+        eng.set_table(np.concatenate([var_map["W"], var_map["V"]], axis=1))
+        eng.bias().copy_(torch.as_tensor(var_map["b"], dtype=torch.float32))
+        for i in range(len(dims) - 1):
+            eng.set_layer(i, var_map["h%d_w" % (i + 1)], var_map["h%d_b" % (i + 1)])
+        eng.wts_are_ones = False
+        self._setup_host(eng, batch_size, X_feas)
+        self.v_wt_hldr, self.c_id_hldr, self.c_wt_hldr = Placeholder("v_wt"), Placeholder("c_id"), Placeholder("c_wt")
+        self.lbl_hldr = Placeholder("lbl")
+        self._num_ids = np.arange(self.n_num, dtype=np.int64)[None, :]
+        self._masks = None
+        if mode == "train":
+            self._keep_prob = float(_reg_argv[0])
+            self._reduce = _ptmzr_argv[-1]
+            self.lr, log = _optimizer(_ptmzr_argv)
+            self.log += "%s, reduce by: %s, keep_prob(drop_out): %g" % (log, self._reduce, self._keep_prob)
+            self.eval_size = eval_size
+            self.eval_id_hldr, self.eval_wts_hldr = Placeholder("eval_id"), Placeholder("eval_wts")
+            self.ptmzr, self.loss, self.train_preds = Fetch(self, "ptmzr"), Fetch(self, "loss"), Fetch(self, "train_preds")
+            self.eval_preds = Fetch(self, "eval_preds")
+            if self._keep_prob < 1.0:
+                # tf.nn.dropout on every layer input incl. act(z1) (FNN.py:87-89): Bernoulli(keep)/keep
+                self._masks = [torch.ones(batch_size, eng.ldi[l], device=eng.dev) for l in range(eng.nl)]
+                eng.masks = list(self._masks)
+                self._gen = torch.Generator(device=eng.dev)
+                self._gen.manual_seed(0x5EED)
+        else:
+            self.test_preds = Fetch(self, "test_preds")
+
+    def set_dropout_masks(self, masks):
+        """Inject explicit masks (list over layers, [N, width] arrays or None) -- parity runs."""
+        eng = self.engine
+        self._masks = None
+        eng.masks = [None] * eng.nl
+        for l, m in enumerate(masks):
+            if m is not None:
+                t = torch.zeros(self.N, eng.ldi[l], device=eng.dev)
+                t[:, :eng.widths[l]] = torch.as_tensor(np.asarray(m), dtype=torch.float32).to(eng.dev)
+                eng.masks[l] = t
+        self._graph = None
+
+    def _swap_masks(self, masks):
+        old = self.engine.masks
+        self.engine.masks = masks if masks is not None else [None] * self.engine.nl
+        return old
+
+    def _pre_step(self):
+        if self._masks is not None:
+            for m in self._masks:
+                m.copy_((torch.rand(m.shape, device=m.device, generator=self._gen) < self._keep_prob).float() / self._keep_prob)
+
+    def _device_step(self):
+        gs = 1.0 if self._reduce == "sum" else 1.0 / self.N
+        self.engine.train_step(self.lr, 1.0, gs, train_bias=True)
+
+    def _global(self, v_wts, c_ids, c_wts):
+        n = len(c_ids)
+        ids = np.concatenate([np.broadcast_to(self._num_ids, (n, self.n_num)), np.asarray(c_ids) + self.offsets], axis=1)
+        wts = np.concatenate([np.asarray(v_wts).reshape(n, self.n_num), np.asarray(c_wts)], axis=1)
+        return ids, wts
+
+    def train_step(self, feed):
+        ids, wts = self._global(feed[self.v_wt_hldr], feed[self.c_id_hldr], feed[self.c_wt_hldr])
+        return self._stage_and_step(ids, wts, np.asarray(feed[self.lbl_hldr]).reshape(self.N))
+
+    def _fetch(self, kind, feed):
+        if kind == "eval_preds":       # global ids [E, X_feas]; the graph subtracts offsets itself (FNN.py:65-69)
+            ids, wts = np.asarray(feed[self.eval_id_hldr]), np.asarray(feed[self.eval_wts_hldr])
+        elif kind == "test_preds":
+            ids, wts = self._global(feed[self.v_wt_hldr], feed[self.c_id_hldr], feed[self.c_wt_hldr])
+        else:
+            raise ValueError("fetch %r needs Session.run with model.ptmzr" % kind)
+        return self._predict_chunks(ids, wts)
+
+    def var_map(self):
+        t = self.engine.get_table()
+        vm = {"W": t[:, :1].copy(), "V": t[:, 1:].copy(), "b": self.engine.bias().cpu().numpy()}
+        for i in range(self.engine.nl):
+            w, b = self.engine.get_layer(i)
+            vm["h%d_w" % (i + 1)], vm["h%d_b" % (i + 1)] = w, b
+        return vm
+
+    def dump(self, model_path):
+        """FNN.py:96-101: pickle {'W','V','b','h{i}_w','h{i}_b'}."""
+        with open(model_path, "wb") as f:
+            pickle.dump(self.var_map(), f)
+        print("model dumped at %s" % model_path)
+
+
+class FNN(_FNNBase):
+    """FNN.py:4 -- _rch_argv = [X_dim, X_feas, rank, h1, h2, act]."""
+    cross, n_hidden = "none", 2
+
+
+class FNN_IP_L3(_FNNBase):
+    """FNN_IP_L3.py:4 -- _rch_argv = [X_dim, X_feas, rank, h1, h2, h3, act]."""
+    cross, n_hidden = "ip", 3
+
+
+class FNN_IP_L5(_FNNBase):
+    """FNN_IP_L5.py:4 -- five hidden layers."""
+    cross, n_hidden = "ip", 5
+
+
+class FNN_IP_L7(_FNNBase):
+    """FNN_IP_L7.py:4 -- seven hidden layers."""
+    cross, n_hidden = "ip", 7
+
+
+class FNN_OP_L3(_FNNBase):
+    """FNN_OP_L3.py:4 -- outer-product layer; h1_w sized from the true forward width."""
+    cross, n_hidden = "op", 3

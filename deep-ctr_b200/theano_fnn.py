@@ -1,0 +1,131 @@
+"""Theano-generation FNN (python/FNN_wnzh.py) on the B200 hot path.
+
+The reference script compiles `train(x, y) -> [gx, w1, w2, w3, b1, b2, b3]` and `predict(x) -> p`
+(FNN_wnzh.py:177-183), gathers x on the host from a Python dict (:87-96) and applies the touched-row SGD
+in a Python triple loop (:300-306).  Here the gather, the MLP, the loss and the sequential decayed scatter
+all run on the GPU, so `train` takes FEATURE IDS instead of the dense x and returns (loss, p_drop).
+"""
+import numpy as np
+import torch
+
+from .engine import StepEngine
+from .models import _Base
+
+NAME_FIELD = {'weekday': 0, 'hour': 1, 'useragent': 2, 'IP': 3, 'region': 4, 'city': 5, 'adexchange': 6, 'domain': 7,
+              'slotid': 8, 'slotwidth': 9, 'slotheight': 10, 'slotvisibility': 11, 'slotformat': 12, 'creative': 13,
+              'advertiser': 14, 'slotprice': 15}   # FNN_wnzh.py:51-53
+
+
+def init_mlp(xdim, hidden1, hidden2, acti_type="tanh", seed=1234):
+    """FNN_wnzh.py:16-17,106-130: numpy legacy global RNG seeded 1234; U(+-sqrt(6/(fan_in+fan_out))), x4 for tanh;
+    w3 = 0, biases 0."""
+    rng = np.random.RandomState(seed)
+    lim1 = np.sqrt(6.0 / (xdim + hidden1))
+    w = rng.uniform(low=-lim1, high=lim1, size=(xdim, hidden1))
+    ww1 = w if acti_type == "sigmoid" else (w * 4 if acti_type == "tanh" else rng.uniform(-1, 1, size=(xdim, hidden1)))
+    lim2 = np.sqrt(6.0 / (hidden1 + hidden2))
+    v = rng.uniform(low=-lim2, high=lim2, size=(hidden1, hidden2))
+    ww2 = v if acti_type == "sigmoid" else (v * 4 if acti_type == "tanh" else rng.uniform(-1, 1, size=(hidden1, hidden2)))
+    return [ww1, ww2, np.zeros((hidden2, 1))], [np.zeros(hidden1), np.zeros(hidden2), np.zeros(1)]
+
+
+class MaskStreams(object):
+    """Dropout masks r1, r2 = srng.binomial(size=(1,H), n=1, p=dropout) (FNN_wnzh.py:154,166) from
+    RandomStreams(seed=234) (:15).  Theano seeds each op's numpy RandomState from
+    RandomState(234).randint(2**30) in creation order r0, r1, r2 (recollection, cannot be checked
+    without Theano) -- parity tests inject masks instead of relying on this."""
+
+    def __init__(self, hidden1, hidden2, p, seed=234):
+        g = np.random.RandomState(seed)
+        seeds = [int(g.randint(2 ** 30)) for _ in range(3)]
+        self.r1 = np.random.RandomState(seeds[1])
+        self.r2 = np.random.RandomState(seeds[2])
+        self.h1, self.h2, self.p = hidden1, hidden2, p
+
+    def draw(self):
+        return (self.r1.binomial(n=1, p=self.p, size=(1, self.h1)).astype(np.float32),
+                self.r2.binomial(n=1, p=self.p, size=(1, self.h2)).astype(np.float32))
+
+
+class FNN_wnzh(_Base):
+    def __init__(self, fm_model, batch_size=100, lr=0.001, dropout=0.5, hidden1=300, hidden2=100, lambda1=0.0,
+                 lambda_fm=0.1, acti_type="tanh", n_fields=16, device="cuda", weights=None):
+        """fm_model: dict(w_0=float, table=[X, k+1] float array indexed by feature id, feat_field=[X] int)
+        as loaded by data.load_fm_model (FNN_wnzh.py:62-84).  Hyper-parameters default to the advertiser-2997
+        branch (:43-49), the only one that defines them all."""
+        table = np.asarray(fm_model["table"], dtype=np.float32)
+        X, d = table.shape
+        self.k = d
+        self.xdim = 1 + n_fields * d                                  # :78
+        self.feat_field = np.asarray(fm_model["feat_field"], dtype=np.int64)
+        self.lr, self.dropout, self.lambda1, self.lambda_fm = lr, dropout, lambda1, lambda_fm
+        act = {"tanh": "tanh", "sigmoid": "sigmoid", "linear": "none"}[acti_type]
+        # one extra all-zero row X: the slot of a field that a sample does not have (x stays 0 there, :91-95)
+        eng = StepEngine(X + 1, n_fields, d - 1, [hidden1, hidden2], batch_size, cross="none", bias_first=True,
+                         act0="none", act=act, scatter_mode="seq_decay", device=device)
+        eng.set_table(np.concatenate([table, np.zeros((1, d), np.float32)], axis=0))
+        eng.bias().fill_(float(fm_model["w_0"]))
+        Ws, bs = weights if weights is not None else init_mlp(self.xdim, hidden1, hidden2, acti_type)
+        for l in range(3):
+            eng.set_layer(l, Ws[l], bs[l])
+        eng.wts_are_ones = False
+        self.pad_row = X
+        self._setup_host(eng, batch_size, n_fields)
+        self.mask_streams = MaskStreams(hidden1, hidden2, dropout) if dropout < 1.0 else None
+        if self.mask_streams is not None:
+            eng.masks = [None, torch.ones(1, eng.ldi[1], device=eng.dev), torch.ones(1, eng.ldi[2], device=eng.dev)]
+        self._next_masks = None
+
+    # ---- host side of feats_to_layer_one_array: slot of a feature = its field (FNN_wnzh.py:87-96) ----
+    def arrange(self, feats):
+        feats = np.asarray(feats, dtype=np.int64)
+        n = feats.shape[0]
+        ids = np.full((n, self.F), self.pad_row, dtype=np.int64)
+        wts = np.zeros((n, self.F), dtype=np.float32)
+        valid = feats >= 0
+        rows = np.broadcast_to(np.arange(n)[:, None], feats.shape)[valid]
+        slot = self.feat_field[feats[valid]]
+        ids[rows, slot] = feats[valid]            # a later feature of the same field overwrites (:94-95)
+        wts[rows, slot] = 1.0
+        return ids, wts
+
+    def set_masks(self, r1, r2):
+        """Inject the dropout masks of the NEXT train() call ([1,H] or [H] arrays of 0/1)."""
+        self._next_masks = (np.asarray(r1, np.float32).reshape(1, -1), np.asarray(r2, np.float32).reshape(1, -1))
+
+    def _pre_step(self):
+        if self.mask_streams is None:
+            return
+        r1, r2 = self._next_masks if self._next_masks is not None else self.mask_streams.draw()
+        self._next_masks = None
+        e = self.engine
+        e.masks[1][:, :r1.shape[1]].copy_(torch.from_numpy(r1))
+        e.masks[2][:, :r2.shape[1]].copy_(torch.from_numpy(r2))
+
+    def _device_step(self):
+        decay = 1.0 - 2.0 * self.lambda_fm * self.lr / self.N        # FNN_wnzh.py:305
+        self.engine.train_step(self.lr, decay, 1.0, train_bias=False, last_decay=1.0 - 2.0 * self.lr * self.lambda1)
+
+    def train(self, feats, y):
+        """One step of the loop body FNN_wnzh.py:296-306.  feats: [N, <=16] feature ids (-1 = absent)."""
+        ids, wts = self.arrange(feats)
+        return self._stage_and_step(ids, wts, np.asarray(y, dtype=np.float32).reshape(self.N))
+
+    def _swap_masks(self, masks):
+        old = self.engine.masks
+        self.engine.masks = masks if masks is not None else [None] * self.engine.nl
+        return old
+
+    def predict(self, feats):
+        """predict(x) -> p_1: the no-dropout branch, no rescaling (FNN_wnzh.py:157-170,183)."""
+        ids, wts = self.arrange(feats)
+        return self._predict_chunks(ids, wts)
+
+    def get_weights(self):
+        """(w1, w2, w3, b1, b2, b3) like the tail of train()'s outputs -- POST-update here."""
+        e = self.engine
+        (w1, b1), (w2, b2), (w3, b3) = e.get_layer(0), e.get_layer(1), e.get_layer(2)
+        return w1, w2, w3.reshape(-1), b1, b2, float(b3[0])
+
+    def get_table(self):
+        return self.engine.get_table()[:self.pad_row]

@@ -1,0 +1,150 @@
+/*
+ * dctr.h -- C-ABI of the B200-native deep-ctr hot path (libdctr.so, sm_100a).
+ *
+ * The reference (Atomu2014/deep-ctr) is pure Python on top of Theano / TensorFlow 0.x and has NO
+ * FFI of its own; every entry point below therefore names the reference
+ * ENGINE CALL (file:line under /root/reference) it replaces.  INTEGRATION.md shows the ctypes stub
+ * a maintainer would add on the reference side.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer borrowed for the call unless the name ends in `_host`;
+ *     nothing is allocated, freed or synchronised inside (stream-ordered, CUDA-graph capturable);
+ *   - `stream` is a cudaStream_t passed as void*;
+ *   - return 0 on success, a negative DCTR_E* code otherwise; the message is kept per thread and
+ *     read back with dctr_last_error(); no C++ exception crosses the boundary;
+ *   - embedding table: float32 [X, ld], ld % 4 == 0, row = [w | v_1..v_r | zero pad], d = r + 1;
+ *   - ids: int32 GLOBAL row ids [N, F] (row-major, sample x field); wts: float32 [N, F] or NULL (=1);
+ *   - all reductions run in a fixed order: two runs on the same inputs are bit-identical.
+ */
+#ifndef DCTR_H_
+#define DCTR_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DCTR_VERSION 1
+
+enum { DCTR_OK = 0, DCTR_EINVAL = -1, DCTR_EWORKSPACE = -2, DCTR_ECUDA = -3 };
+enum { DCTR_ACT_NONE = 0, DCTR_ACT_TANH = 1, DCTR_ACT_RELU = 2, DCTR_ACT_SIGMOID = 3 };
+enum { DCTR_CROSS_NONE = 0, DCTR_CROSS_IP = 1, DCTR_CROSS_OP = 2 };
+/* duplicate-row semantics of the sparse update */
+enum { DCTR_SCATTER_SUM = 0,      /* TF: row -= lr * sum of its gradients (FNN.py:46-49 densified grad) */
+       DCTR_SCATTER_SEQ_DECAY = 1 /* Theano: per occurrence, in sample order, row = row*c - lr*g (FNN_wnzh.py:300-306) */ };
+/* GEMM operand layouts / epilogues */
+enum { DCTR_GEMM_NN = 0, DCTR_GEMM_NT = 1, DCTR_GEMM_TN = 2 };
+enum { DCTR_EPI_NONE = 0, DCTR_EPI_FWD = 1, DCTR_EPI_DGRAD = 2 };
+
+int dctr_version(void);
+const char* dctr_last_error(void);
+/* number of kernels this library has launched from the calling process (bench.py's gpu_launches) */
+long long dctr_launch_count(void);
+
+/* ---- K1: per-field embedding gather + concat (+ fused inner/outer product layer) -------------
+ * replaces feats_to_layer_one_array (FNN_wnzh.py:87-96, data_fm.py:46-54), the 13 rank-1 matmuls +
+ * 26 embedding_lookup_sparse + concat of FNN.forward (FNN.py:76-85), the N*P scalar matmuls of
+ * FNN_IP_L3.forward (FNN_IP_L3.py:91-97) and the outer-product sum of FNN_OP_L3.forward
+ * (FNN_OP_L3.py:93-100).
+ *   e[n,f,:] = wts[n,f] * table[ids[n,f], 0:d]
+ *   bias_first=1 (Theano): z[n,:] = [ bias | e[n,0,:] .. e[n,F-1,:] ]
+ *   bias_first=0 (TF):     z[n,:] = [ e[n,0,:] .. e[n,F-1,:] | cross | bias ]
+ *   cross IP: p[pi(i,j)] = <e_i,e_j>, i<j, pi = i*F - i(i+1)/2 + j-i-1;  OP: q[a*d+b] = sum_{i<j} e_i[a] e_j[b]
+ *   out[n,c] = act0(z[n,c]) for c < D0; columns D0..ldz-1 are written as 0.
+ * bias: device pointer to ONE float (w_0 / b). */
+int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
+                           int N, int F, int d, int cross, int bias_first, const float* bias, int act0,
+                           float* out, int ldz, void* stream);
+
+/* backward of the cross layer into a per-(sample,field) embedding-gradient buffer
+ *   ge[n,f,c] = wts[n,f] * ( dz[n, f*d+c] + d(cross)/d(e_f[c]) ),  ge: float32 [N, F, ldg], ldg%4==0
+ * dz is dL/dz (the activation derivative already applied), TF layout (bias last).
+ * cross = NONE just copies/scales the embedding block.  Reads the PRE-update table. */
+int dctr_cross_bwd(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
+                   int N, int F, int d, int cross, const float* dz, int ldz,
+                   float* ge, int ldg, void* stream);
+
+/* ---- K1fm: fused gather + FM forward + sigmoid cross-entropy (FM.py:55-64, 33-38) -------------
+ *   s[n,c] = sum_f x_f*row_f[c];  logit = s[n,0] + b + 0.5*sum_{c>=1}( s[n,c]^2 - sum_f x_f^2 row_f[c]^2 )
+ *   pred = sigmoid(logit); loss_n = max(z,0) - z*y + log1p(exp(-|z|)); g[n] = (pred - y)*gscale
+ * y == NULL: inference only (loss_n, g untouched).  s: float32 [N, lds] (lds%4==0) or NULL. */
+int dctr_fm_fwd(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
+                int N, int F, int d, const float* bias, const float* y, float gscale,
+                float* logit, float* pred, float* loss_n, float* g, float* s, int lds, void* stream);
+
+/* ---- K6a: stable LSD radix sort of the (row, position) list ----------------------------------
+ * keys = ids[0..M), payload = position p = n*F+f.  Stable, so equal rows keep sample order: this is
+ * what makes the duplicate-row fold deterministic and lets SEQ_DECAY follow FNN_wnzh.py:300-306. */
+size_t dctr_sort_rows_workspace(int64_t M);
+int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t* sorted_rows, int32_t* sorted_pos,
+                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- K6b: segmented fold + SGD into the touched rows only -------------------------------------
+ * dense source (FNN*, Theano FNN):  grad(p=n*F+f, c) = (wts? wts[p] : 1) * g[n*g_ld_n + f*g_ld_f + c]
+ *   SUM:        row -= lr * sum_p grad(p,:)
+ *   SEQ_DECAY:  for p in segment order: row = row*decay - lr*grad(p,:)
+ * workspace: dctr_scatter_workspace(M, ld) bytes (long-segment list + chunk partials). */
+#define DCTR_LONG_SEG 64    /* segments longer than this are folded by chunks of DCTR_SEG_CHUNK */
+#define DCTR_SEG_CHUNK 128
+size_t dctr_scatter_workspace(int64_t M, int ld);
+int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
+                     const float* g, int64_t g_ld_n, int g_ld_f, const float* wts,
+                     float lr, float decay, float* table, int64_t X, int ld,
+                     void* workspace, size_t workspace_bytes, void* stream);
+/* FM source (FM.py:55-64 differentiated):
+ *   grad(p,0) = g[n]*x_p ; grad(p,c>=1) = g[n]*( x_p*s[n,c] - x_p^2*row_old[c] ) ; row = row*decay - lr*sum grad
+ *   (decay = 1 - lr*lambda realises the L2 term of FM.py:39 on the touched rows). */
+int dctr_scatter_sgd_fm(const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
+                        const float* g, const float* s, int lds, const float* wts,
+                        float lr, float decay, float* table, int64_t X, int ld,
+                        void* workspace, size_t workspace_bytes, void* stream);
+/* dense L2 sweep for FM.py:39 on the rows the batch did NOT touch: table[r,:] *= decay unless r is in
+ * sorted_rows (binary search).  Pure streaming read-modify-write over X*ld floats. */
+int dctr_decay_sweep(float* table, int64_t X, int ld, float decay,
+                     const int32_t* sorted_rows, int64_t M, void* stream);
+
+/* ---- K4: fp32 GEMM with fused MLP epilogues ---------------------------------------------------
+ * replaces tf.matmul + bias + activate + dropout (FNN.py:86-94) and T.dot/T.tanh (FNN_wnzh.py:147-170)
+ * and their autodiff.  C[M,N] = op(A)*op(B):
+ *   NN: A[M,K] (lda), B[K,N] (ldb)      forward
+ *   NT: A[M,K] (lda), B[N,K] (ldb)      dgrad  (dY * W^T)
+ *   TN: A[K,M] (lda), B[K,N] (ldb)      wgrad  (act^T * dY), split-K over `splits` slabs
+ * epilogues (aux: [M,N] with ldaux, mask: [M,N] with ldmask, ldmask==0 broadcasts one row, NULL = 1):
+ *   FWD:   C = act(acc + bias[n]) * mask
+ *   DGRAD: C = acc * mask * act'(aux/mask)      (aux = the stored forward output of that layer)
+ * TN writes `splits` partial slabs into C (slab stride M*ldc) when splits > 1; fold them with
+ * dctr_splitk_reduce (fixed order). */
+int dctr_gemm(int layout, int M, int N, int K, const float* A, int lda, const float* B, int ldb,
+              float* C, int ldc, int epilogue, int act, const float* bias,
+              const float* aux, int ldaux, const float* mask, int ldmask, int splits, void* stream);
+int dctr_splitk_reduce(const float* partials, int splits, int M, int N, int ldc, float* out, int ldo, void* stream);
+/* 3xTF32 error-compensated tensor-core variant (tcgen05.mma kind::tf32, TMEM accumulators); same
+ * contract as dctr_gemm NN/FWD; returns DCTR_EINVAL for shapes it does not cover. */
+int dctr_gemm_tc(int layout, int M, int N, int K, const float* A, int lda, const float* B, int ldb,
+                 float* C, int ldc, int epilogue, int act, const float* bias,
+                 const float* aux, int ldaux, const float* mask, int ldmask, void* stream);
+
+/* ---- K5: output unit + loss (FNN.py:54-63, FNN_wnzh.py:169-173) --------------------------------
+ *   logit[n] = <a[n,0:H], w> + b ; pred = sigmoid ; loss_n = stable xent ; dlogit[n] = (pred-y)*gscale */
+int dctr_out_xent_fwd(const float* a, int lda, int N, int H, const float* w, const float* b, const float* y,
+                      float gscale, float* logit, float* pred, float* loss_n, float* dlogit, void* stream);
+/*   da[n,h] = dlogit[n]*w[h] * mask * act'(a/mask)   (backward through the last hidden activation) */
+int dctr_out_bwd(const float* dlogit, const float* w, const float* a, int lda, int N, int H, int act,
+                 const float* mask, int ldmask, float* da, int ldda, void* stream);
+/*   out[h] = sum_n (wv? wv[n]:1) * A[n,h]   two-stage fixed-order column reduction (bias / last-layer grads);
+ *   partial: float32 workspace of dctr_col_wsum_workspace(N,H) bytes */
+size_t dctr_col_wsum_workspace(int N, int H);
+int dctr_col_wsum(const float* A, int lda, int N, int H, const float* wv, float* out,
+                  void* partial, size_t partial_bytes, void* stream);
+/*   out[0] = sum_n v[n]  (fixed order, one CTA) -- loss = reduce_sum(log_loss) (FM.py:36) */
+int dctr_vec_sum(const float* v, int N, float scale, float* out, void* stream);
+
+/* ---- K7: dense SGD over a flat parameter buffer (tf_util.py:27 / FNN_wnzh.py:180-182) ---------- */
+int dctr_dense_sgd(float* param, const float* grad, int64_t n, float lr, float decay, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DCTR_H_ */

@@ -1,0 +1,328 @@
+"""CPU oracle for the deep-ctr hot path -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+A numpy (float64 by default) restatement of the reference algorithm for the path of BASELINE.json's
+north_star.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg may
+import this file; the product package (deep-ctr_b200/) never does.
+
+PARITY UNPINNED: the reference (Python 2 + Theano / TensorFlow 0.x) cannot run in this image and ships no
+tests, golden vectors or fixtures.  This restatement is therefore pinned only by
+(a) line-by-line citation of the reference, (b) central finite differences of every hand-derived backward
+(tests/test_oracle.py) and (c) algebraic identities (FM pairwise identity, OP prefix form, IP index formula).
+
+Reference citations are file:line under /root/reference/python.
+"""
+import numpy as np
+
+ACTS = ("none", "tanh", "relu", "sigmoid")
+
+
+def activate(act, x):
+    """tf_util.py:32-38 (tanh / relu / else sigmoid); 'none' is the Theano input layer (FNN_wnzh.py:147)."""
+    if act == "none":
+        return x
+    if act == "tanh":
+        return np.tanh(x)
+    if act == "relu":
+        return np.maximum(x, 0)
+    return 1.0 / (1.0 + np.exp(-x))
+
+
+def activate_grad_from_out(act, t):
+    if act == "none":
+        return np.ones_like(t)
+    if act == "tanh":
+        return 1 - t * t
+    if act == "relu":
+        return (t > 0).astype(t.dtype)
+    return t * (1 - t)
+
+
+def sigmoid(z):
+    return 1.0 / (1.0 + np.exp(-z))
+
+
+def xent_with_logits(z, y):
+    """tf.nn.sigmoid_cross_entropy_with_logits (FM.py:34, FNN.py:54): max(z,0) - z*y + log1p(exp(-|z|)).
+    Equal to the naive Theano form -y log p - (1-y) log(1-p) (FNN_wnzh.py:172) wherever that is finite."""
+    return np.maximum(z, 0) - z * y + np.log1p(np.exp(-np.abs(z)))
+
+
+def pair_index(i, j, F):
+    """Position of pair (i<j) in the i-outer / j-inner enumeration of FNN_IP_L3.py:91-94."""
+    return i * F - i * (i + 1) // 2 + (j - i - 1)
+
+
+# --------------------------------------------------------------------------------------------------
+# embedding layer: gather + concat (+ IP / OP)
+# --------------------------------------------------------------------------------------------------
+def gather_fields(table, ids, wts):
+    """e[n,f,:] = wts[n,f] * table[ids[n,f], :].
+    Theano: FNN_wnzh.py:91-96 (weights ignored = 1).  TF: numeric field i is value * row i (FNN.py:77),
+    categorical field j is embedding_lookup_sparse with weight c_wts (FNN.py:78-82); with global ids
+    `range(13) + offsets+local` (baseline.py:190-198) both are this one expression."""
+    e = table[ids]
+    if wts is not None:
+        e = e * wts[..., None]
+    return e
+
+
+def cross_ip(e):
+    """p[n, pi(i,j)] = <e_i, e_j>, i<j (FNN_IP_L3.py:91-94)."""
+    N, F, d = e.shape
+    iu, ju = np.triu_indices(F, 1)   # row-major upper triangle == i-outer / j-inner
+    return np.einsum("npd,npd->np", e[:, iu, :], e[:, ju, :])
+
+
+def cross_op(e):
+    """q[n, a*d+b] = sum_{i<j} e_i[a] e_j[b] (FNN_OP_L3.py:93-97: outer(mbd_i, mbd_j) flattened row-major,
+    summed over pairs)."""
+    N, F, d = e.shape
+    q = np.zeros((N, d, d), dtype=e.dtype)
+    for i in range(F - 1):
+        for j in range(i + 1, F):
+            q += e[:, i, :, None] * e[:, j, None, :]
+    return q.reshape(N, d * d)
+
+
+def build_z(e, cross, bias, bias_first):
+    """Theano: x = [w_0 | e...] (FNN_wnzh.py:92-95).  TF: z1 = [mbd | p_mbd | b_mbd] (FNN.py:83-85,
+    FNN_IP_L3.py:95-97).  The OP width is the forward's true d*d, not the declared P."""
+    N, F, d = e.shape
+    parts = [e.reshape(N, F * d)]
+    if cross == "ip":
+        parts.append(cross_ip(e))
+    elif cross == "op":
+        parts.append(cross_op(e))
+    b = np.full((N, 1), bias, dtype=e.dtype)
+    parts = [b] + parts if bias_first else parts + [b]
+    return np.concatenate(parts, axis=1)
+
+
+def cross_backward(e, cross, dz_cross):
+    """d loss / d e from the cross block (hand-derived; finite-difference checked in tests/test_oracle.py)."""
+    N, F, d = e.shape
+    de = np.zeros_like(e)
+    if cross == "ip":
+        iu, ju = np.triu_indices(F, 1)
+        for t in range(len(iu)):
+            i, j = iu[t], ju[t]
+            de[:, i, :] += dz_cross[:, t, None] * e[:, j, :]
+            de[:, j, :] += dz_cross[:, t, None] * e[:, i, :]
+    elif cross == "op":
+        dq = dz_cross.reshape(N, d, d)
+        for i in range(F - 1):
+            for j in range(i + 1, F):
+                de[:, i, :] += np.einsum("nab,nb->na", dq, e[:, j, :])
+                de[:, j, :] += np.einsum("nab,na->nb", dq, e[:, i, :])
+    return de
+
+
+# --------------------------------------------------------------------------------------------------
+# the network: embedding layer + MLP
+# --------------------------------------------------------------------------------------------------
+class OracleNet:
+    """in_1 = act0(z); pre_l = in_l W_l + b_l; in_{l+1} = mask_l * act(pre_l); logit = pre_L.
+    TF (FNN.py:86-94): act0 = act, masks are tf.nn.dropout masks (0 or 1/keep) applied to EVERY layer input
+    including act(z1); Theano (FNN_wnzh.py:147-170): act0 = none, masks r1, r2 in {0,1} broadcast over the
+    batch, no rescale."""
+
+    def __init__(self, table, bias, Ws, bs, F, d, cross="none", bias_first=False, act0="none", act="tanh",
+                 dtype=np.float64):
+        self.dtype = dtype
+        self.table = np.array(table, dtype=dtype)      # [X, d]
+        self.bias = dtype(bias)
+        self.Ws = [np.array(w, dtype=dtype) for w in Ws]
+        self.bs = [np.array(b, dtype=dtype).reshape(-1) for b in bs]
+        self.F, self.d, self.cross, self.bias_first, self.act0, self.act = F, d, cross, bias_first, act0, act
+
+    # masks: list of length L (mask on in_1 .. in_L) or None; each None or array broadcastable to the layer input
+    def forward(self, ids, wts=None, masks=None):
+        dt = self.dtype
+        wts = None if wts is None else np.asarray(wts, dtype=dt)
+        e = gather_fields(self.table, ids, wts)
+        z = build_z(e, self.cross, self.bias, self.bias_first)
+        L = len(self.Ws)
+        masks = masks or [None] * L
+        ins = []
+        a = activate(self.act0, z)
+        if masks[0] is not None:
+            a = a * masks[0]
+        ins.append(a)
+        for l in range(L - 1):
+            pre = ins[l] @ self.Ws[l] + self.bs[l]
+            a = activate(self.act, pre)
+            if masks[l + 1] is not None:
+                a = a * masks[l + 1]
+            ins.append(a)
+        logit = (ins[L - 1] @ self.Ws[L - 1] + self.bs[L - 1]).reshape(-1)
+        return logit, dict(e=e, z=z, ins=ins, masks=masks, ids=ids, wts=wts)
+
+    def predict(self, ids, wts=None):
+        return sigmoid(self.forward(ids, wts)[0])
+
+    def backward(self, cache, dlogit):
+        """Returns dWs, dbs, dbias, ge[N,F,d] (gradient w.r.t. the gathered table rows, weight applied) and
+        gz (gradient w.r.t. z -- Theano's gx, FNN_wnzh.py:174)."""
+        L = len(self.Ws)
+        ins, masks = cache["ins"], cache["masks"]
+        dWs, dbs = [None] * L, [None] * L
+        dpre = dlogit.reshape(-1, 1)
+        for l in range(L - 1, -1, -1):
+            dWs[l] = ins[l].T @ dpre
+            dbs[l] = dpre.sum(axis=0)
+            din = dpre @ self.Ws[l].T
+            act = self.act if l > 0 else self.act0
+            m = masks[l]
+            if m is not None:
+                safe = np.where(m != 0, m, 1.0)
+                t = np.where(m != 0, ins[l] / safe, 0.0)
+                dpre = din * m * activate_grad_from_out(act, t)
+            else:
+                dpre = din * activate_grad_from_out(act, ins[l])
+        gz = dpre                                   # d loss / d z  [N, D0]
+        N = gz.shape[0]
+        F, d = self.F, self.d
+        off = 1 if self.bias_first else 0
+        de = gz[:, off:off + F * d].reshape(N, F, d).copy()
+        if self.cross != "none":
+            cw = F * (F - 1) // 2 if self.cross == "ip" else d * d
+            de += cross_backward(cache["e"], self.cross, gz[:, F * d:F * d + cw])
+        dbias = gz[:, 0].sum() if self.bias_first else gz[:, -1].sum()
+        ge = de if cache["wts"] is None else de * cache["wts"][..., None]
+        return dWs, dbs, dbias, ge, gz
+
+    # ---- TF semantics: loss = reduce(xent), plain SGD on every variable (tf_util.py:26-28) ------------
+    def train_step_tf(self, ids, wts, y, lr, masks=None, reduce="sum"):
+        y = np.asarray(y, dtype=self.dtype)
+        logit, cache = self.forward(ids, wts, masks)
+        N = len(y)
+        scale = 1.0 if reduce == "sum" else 1.0 / N
+        loss = xent_with_logits(logit, y).sum() * scale
+        dlogit = (sigmoid(logit) - y) * scale
+        dWs, dbs, dbias, ge, _ = self.backward(cache, dlogit)
+        # embedding rows: the gradient of tf.slice/concat + embedding_lookup_sparse is the SUM over duplicates
+        # (FNN.py:46-49); only touched rows have a non-zero gradient, so SGD moves only them.
+        np.add.at(self.table, ids.reshape(-1), -lr * ge.reshape(-1, self.d))
+        self.bias = self.bias - lr * dbias          # fm_b is a trained variable (FNN.py:30)
+        for l in range(len(self.Ws)):
+            self.Ws[l] -= lr * dWs[l]
+            self.bs[l] -= lr * dbs[l]
+        return loss, sigmoid(logit)
+
+    # ---- Theano semantics (FNN_wnzh.py:172-182, 298-306) --------------------------------------------
+    def train_step_theano(self, ids, y, lr, lambda_fm, masks=None, lambda1=0.0, faithful=False):
+        y = np.asarray(y, dtype=self.dtype)
+        logit, cache = self.forward(ids, None, masks)
+        p = sigmoid(logit)
+        # cost = xent.sum() + lambda1*(|w3|^2 + b3^2)   (FNN_wnzh.py:172-173)
+        loss = xent_with_logits(logit, y).sum() + lambda1 * ((self.Ws[-1] ** 2).sum() + (self.bs[-1] ** 2).sum())
+        dWs, dbs, _, ge, gz = self.backward(cache, p - y)
+        dWs[-1] = dWs[-1] + 2 * lambda1 * self.Ws[-1]
+        dbs[-1] = dbs[-1] + 2 * lambda1 * self.bs[-1]
+        N, F = ids.shape
+        decay = 1 - 2.0 * lambda_fm * lr / N
+        if faithful:
+            # the literal triple loop of FNN_wnzh.py:300-306 (sample-major, duplicates applied one after another)
+            off = 1
+            for t in range(N):
+                for f in range(F):
+                    feat = ids[t, f]
+                    for l in range(self.d):
+                        self.table[feat, l] = self.table[feat, l] * decay - lr * gz[t, off + f * self.d + l]
+        else:
+            seq_decay_scatter(self.table, ids, ge, lr, decay)
+        for l in range(len(self.Ws)):               # w_0 (the bias column) is never updated (FNN_wnzh.py:93,300-306)
+            self.Ws[l] -= lr * dWs[l]
+            self.bs[l] -= lr * dbs[l]
+        return loss, p
+
+
+def seq_decay_scatter(table, ids, ge, lr, decay):
+    """Vectorised equivalent of FNN_wnzh.py:300-306: per row, occurrences in (sample, field) order,
+    w <- w*decay - lr*g.  Rounds of 'k-th occurrence of each row' keep the per-row order exact."""
+    flat = ids.reshape(-1)
+    g = ge.reshape(len(flat), -1)
+    order = np.argsort(flat, kind="stable")
+    srow = flat[order]
+    first = np.r_[True, srow[1:] != srow[:-1]]
+    start = np.maximum.accumulate(np.where(first, np.arange(len(srow)), 0))
+    occ = np.arange(len(srow)) - start            # occurrence number within its segment
+    for k in range(int(occ.max()) + 1 if len(occ) else 0):
+        sel = order[occ == k]
+        rows = flat[sel]
+        table[rows] = table[rows] * decay - lr * g[sel]
+
+
+# --------------------------------------------------------------------------------------------------
+# FM (FM.py)
+# --------------------------------------------------------------------------------------------------
+class OracleFM:
+    """table[:,0] = W, table[:,1:] = V (FM.py:15-20); b scalar."""
+
+    def __init__(self, table, b, dtype=np.float64):
+        self.dtype = dtype
+        self.table = np.array(table, dtype=dtype)
+        self.b = dtype(b)
+
+    def logits(self, ids, wts):
+        """FM.factorization, FM.py:55-64."""
+        x = np.asarray(wts, dtype=self.dtype)
+        rows = self.table[ids]                                  # [N,F,d]
+        W, V = rows[..., 0], rows[..., 1:]
+        yhat = (W * x).sum(1) + self.b                          # :57
+        vx = (V * x[..., None]).sum(1)                          # :59
+        v2x2 = ((V ** 2) * (x ** 2)[..., None]).sum(1)          # :61
+        return yhat + 0.5 * ((vx ** 2).sum(1) - v2x2.sum(1)), vx   # :63
+
+    def predict(self, ids, wts):
+        return sigmoid(self.logits(ids, wts)[0])
+
+    def train_step(self, ids, wts, y, lr, lam=0.0, reduce="sum", dense_l2=True):
+        """loss = reduce(xent) + lam*(l2_loss(W)+l2_loss(V)+l2_loss(b)), l2_loss = sum(t^2)/2 (FM.py:33-39);
+        plain SGD (tf_util.py:26-28).  dense_l2=False restricts the decay to the touched rows."""
+        x = np.asarray(wts, dtype=self.dtype)
+        y = np.asarray(y, dtype=self.dtype)
+        N, F = ids.shape
+        z, vx = self.logits(ids, x)
+        scale = 1.0 if reduce == "sum" else 1.0 / N
+        loss = xent_with_logits(z, y).sum() * scale
+        if lam:
+            loss += lam * 0.5 * ((self.table ** 2).sum() + self.b ** 2)
+        g = (sigmoid(z) - y) * scale
+        rows = self.table[ids]
+        grad = np.empty_like(rows)
+        grad[..., 0] = g[:, None] * x
+        grad[..., 1:] = g[:, None, None] * (x[..., None] * vx[:, None, :] - (x ** 2)[..., None] * rows[..., 1:])
+        dense = np.zeros_like(self.table)
+        np.add.at(dense, ids.reshape(-1), grad.reshape(N * F, -1))
+        if lam:
+            if dense_l2:
+                dense += lam * self.table
+            else:
+                touched = np.unique(ids)
+                dense[touched] += lam * self.table[touched]
+        self.table -= lr * dense
+        self.b = self.b - lr * (g.sum() + lam * self.b)
+        return loss, sigmoid(z)
+
+
+# --------------------------------------------------------------------------------------------------
+# initialisation (FNN_wnzh.py:15-17,106-130) -- reproducible with numpy's legacy RandomState alone
+# --------------------------------------------------------------------------------------------------
+def theano_fnn_init(xdim, hidden1, hidden2, acti_type="tanh", seed=1234):
+    rng = np.random.RandomState(seed)
+    w = rng.uniform(low=-np.sqrt(6.0 / (xdim + hidden1)), high=np.sqrt(6.0 / (xdim + hidden1)), size=(xdim, hidden1))
+    if acti_type == "sigmoid":
+        ww1 = w
+    elif acti_type == "tanh":
+        ww1 = w * 4
+    else:
+        ww1 = rng.uniform(-1, 1, size=(xdim, hidden1))
+    v = rng.uniform(low=-np.sqrt(6.0 / (hidden1 + hidden2)), high=np.sqrt(6.0 / (hidden1 + hidden2)), size=(hidden1, hidden2))
+    if acti_type == "sigmoid":
+        ww2 = v
+    elif acti_type == "tanh":
+        ww2 = v * 4
+    else:
+        ww2 = rng.uniform(-1, 1, size=(hidden1, hidden2))
+    return [ww1, ww2, np.zeros((hidden2, 1))], [np.zeros(hidden1), np.zeros(hidden2), np.zeros(1)]

@@ -1,0 +1,57 @@
+"""CPU-side checks of the drop-in boundary: libdctr.so builds, loads and exports every symbol that
+include/dctr.h declares, and argument validation fails loudly without touching a GPU."""
+import ctypes
+import os
+import re
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "dctr.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(dctr_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_symbols_exported(built_lib):
+    from deepctr_b200 import _lib
+    syms = declared_symbols()
+    assert len(syms) >= 20
+    raw = ctypes.CDLL(_lib.LIB_PATH)
+    for s in syms:
+        assert hasattr(raw, s), "libdctr.so does not export %s" % s
+        assert s in _lib.SIGNATURES, "no ctypes signature for %s" % s
+    assert set(_lib.SIGNATURES) == set(syms)
+
+
+def test_version_and_error_slot(built_lib):
+    from deepctr_b200 import _lib
+    assert built_lib.dctr_version() == 1
+    # bad arguments are rejected before any CUDA call: ld not a multiple of 4
+    rc = built_lib.dctr_gather_concat_fwd(1, None, 1, 10, 3, 1, 2, 3, 0, 0, None, 0, 1, 16, None)
+    assert rc == _lib.EINVAL
+    assert b"gather_concat_fwd" in built_lib.dctr_last_error()
+    try:
+        _lib.call("dctr_gemm", 7, 1, 1, 1, 16, 4, 16, 4, 16, 4, 0, 0, None, None, 0, None, 0, 1, None)
+    except RuntimeError as e:
+        assert "bad layout" in str(e)
+    else:
+        raise AssertionError("expected RuntimeError")
+
+
+def test_workspace_queries(built_lib):
+    assert built_lib.dctr_sort_rows_workspace(65536) >= 2 * 65536 * 4
+    assert built_lib.dctr_scatter_workspace(65536, 12) > 0
+    assert built_lib.dctr_col_wsum_workspace(4096, 300) >= 300 * 4
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    from deepctr_b200 import _lib
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "nope.so"))
+    try:
+        _lib.lib()
+    except RuntimeError as e:
+        assert "no CPU fallback" in str(e)
+    else:
+        raise AssertionError("expected RuntimeError")

@@ -1,0 +1,341 @@
+"""GPU parity tests, kernel by kernel, through the C-ABI (ctypes) against the numpy oracle.
+Integer / index work (sort order, segment structure) is checked BIT-EXACT; fp32 kernels against the fp64
+oracle at rtol 1e-5 (+ a small absolute floor), the tolerance BASELINE.json's north_star states."""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+RTOL, ATOL = 1e-5, 1e-6
+
+
+@pytest.fixture(scope="module")
+def L():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from deepctr_b200 import _lib
+    _lib.lib()
+    return _lib
+
+
+def dev(a, dtype=None):
+    t = torch.as_tensor(np.ascontiguousarray(a))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.cuda()
+
+
+def padded_table(table, ld):
+    X, d = table.shape
+    t = np.zeros((X, ld), np.float32)
+    t[:, :d] = table
+    return dev(t)
+
+
+def r4(n):
+    return (n + 3) // 4 * 4
+
+
+def close(a, b, rtol=RTOL, atol=ATOL):
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    np.testing.assert_allclose(a, b, rtol=rtol, atol=atol)
+
+
+@pytest.mark.parametrize("cross,bias_first,act0,F,d,N", [
+    ("none", True, "none", 16, 11, 100), ("none", False, "tanh", 39, 11, 33), ("ip", False, "relu", 16, 11, 65),
+    ("ip", False, "tanh", 39, 11, 17), ("op", False, "sigmoid", 16, 11, 40), ("op", False, "tanh", 7, 3, 9),
+    ("ip", False, "tanh", 5, 40, 12), ("none", True, "none", 1, 1, 3)])
+def test_gather_concat_fwd(L, cross, bias_first, act0, F, d, N):
+    import deepctr_oracle as O
+    rng = np.random.default_rng(7)
+    X, ld = 1000, r4(d)
+    table = rng.normal(0, 0.3, (X, d)).astype(np.float32)
+    ids = rng.integers(0, X, (N, F))
+    ids[N // 2] = ids[0]
+    wts = rng.uniform(0, 1.5, (N, F)).astype(np.float32)
+    e = O.gather_fields(table.astype(np.float64), ids, wts.astype(np.float64))
+    z = O.activate(act0, O.build_z(e, cross, 0.37, bias_first))
+    D0 = z.shape[1]
+    ldz = r4(D0) + 4
+    out = torch.full((N, ldz), 7.0, device="cuda")
+    bias = dev(np.array([0.37], np.float32))
+    L.call("dctr_gather_concat_fwd", dev(ids, torch.int32).data_ptr(), dev(wts).data_ptr(), padded_table(table, ld).data_ptr(),
+           X, ld, N, F, d, L.CROSS[cross], int(bias_first), bias.data_ptr(), L.ACT[act0], out.data_ptr(), ldz, None)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    close(got[:, :D0], z)
+    assert (got[:, D0:] == 0).all()
+
+
+@pytest.mark.parametrize("cross,F,d,N", [("none", 16, 11, 50), ("ip", 16, 11, 41), ("ip", 39, 11, 9), ("op", 16, 11, 23), ("op", 6, 5, 8)])
+def test_cross_bwd(L, cross, F, d, N):
+    import deepctr_oracle as O
+    rng = np.random.default_rng(11)
+    X, ld = 500, r4(d)
+    table = rng.normal(0, 0.3, (X, d)).astype(np.float32)
+    ids = rng.integers(0, X, (N, F))
+    wts = rng.uniform(0.2, 1.5, (N, F)).astype(np.float32)
+    cw = {"none": 0, "ip": F * (F - 1) // 2, "op": d * d}[cross]
+    D0 = F * d + cw + 1
+    ldz = r4(D0)
+    dz = rng.normal(0, 1, (N, ldz)).astype(np.float32)
+    e = O.gather_fields(table.astype(np.float64), ids, wts.astype(np.float64))
+    de = dz[:, :F * d].astype(np.float64).reshape(N, F, d) + O.cross_backward(e, cross, dz[:, F * d:F * d + cw].astype(np.float64))
+    want = de * wts[..., None]
+    ge = torch.full((N, F, ld), 5.0, device="cuda")
+    L.call("dctr_cross_bwd", dev(ids, torch.int32).data_ptr(), dev(wts).data_ptr(), padded_table(table, ld).data_ptr(), X, ld,
+           N, F, d, L.CROSS[cross], dev(dz).data_ptr(), ldz, ge.data_ptr(), ld, None)
+    torch.cuda.synchronize()
+    got = ge.cpu().numpy()
+    close(got[..., :d], want, atol=1e-5)
+    assert (got[..., d:] == 0).all()
+
+
+@pytest.mark.parametrize("F,d,N", [(16, 11, 100), (39, 3, 7), (16, 1, 33), (4, 51, 19)])
+def test_fm_fwd(L, F, d, N):
+    import deepctr_oracle as O
+    rng = np.random.default_rng(3)
+    X, ld = 800, r4(d)
+    table = rng.normal(0, 0.2, (X, d)).astype(np.float32)
+    ids = rng.integers(0, X, (N, F))
+    ids[:, -1] = X - 1
+    wts = rng.uniform(0, 1.5, (N, F)).astype(np.float32)
+    wts[:, -1] = 0            # padded slot (ipinyou.py:58-59)
+    y = rng.integers(0, 2, N).astype(np.float32)
+    fm = O.OracleFM(table, 0.05)
+    z, vx = fm.logits(ids, wts)
+    f = lambda: torch.zeros(N, device="cuda")
+    logit, pred, loss_n, g = f(), f(), f(), f()
+    s = torch.full((N, ld), 3.0, device="cuda")
+    L.call("dctr_fm_fwd", dev(ids, torch.int32).data_ptr(), dev(wts).data_ptr(), padded_table(table, ld).data_ptr(), X, ld, N, F, d,
+           dev(np.array([0.05], np.float32)).data_ptr(), dev(y).data_ptr(), 0.5, logit.data_ptr(), pred.data_ptr(),
+           loss_n.data_ptr(), g.data_ptr(), s.data_ptr(), ld, None)
+    torch.cuda.synchronize()
+    close(logit.cpu(), z)
+    close(pred.cpu(), O.sigmoid(z))
+    close(loss_n.cpu(), O.xent_with_logits(z, y))
+    close(g.cpu(), (O.sigmoid(z) - y) * 0.5)
+    close(s.cpu().numpy()[:, 1:d], vx)
+    assert (s.cpu().numpy()[:, d:] == 0).all()
+
+
+@pytest.mark.parametrize("M,X", [(1, 5), (31, 3), (2048, 1000), (2049, 70000), (65536, 1000001), (300000, 2 ** 27), (5000, 1)])
+def test_sort_rows_bit_exact(L, M, X):
+    rng = np.random.default_rng(M)
+    ids = np.minimum((rng.pareto(1.1, M) * 3).astype(np.int64), X - 1) if X > 1 else np.zeros(M, np.int64)
+    ids = (ids * 2654435761) % X
+    order = np.argsort(ids, kind="stable")
+    rows = torch.zeros(M, dtype=torch.int32, device="cuda")
+    pos = torch.zeros(M, dtype=torch.int32, device="cuda")
+    ws = torch.zeros(L.lib().dctr_sort_rows_workspace(M), dtype=torch.uint8, device="cuda")
+    L.call("dctr_sort_rows", dev(ids, torch.int32).data_ptr(), M, X, rows.data_ptr(), pos.data_ptr(), ws.data_ptr(), ws.numel(), None)
+    torch.cuda.synchronize()
+    assert np.array_equal(rows.cpu().numpy(), ids[order])
+    assert np.array_equal(pos.cpu().numpy(), order)        # stability: equal rows keep (sample, field) order
+
+
+def _sorted(L, ids, X):
+    M = ids.size
+    rows = torch.zeros(M, dtype=torch.int32, device="cuda")
+    pos = torch.zeros(M, dtype=torch.int32, device="cuda")
+    ws = torch.zeros(L.lib().dctr_sort_rows_workspace(M), dtype=torch.uint8, device="cuda")
+    L.call("dctr_sort_rows", dev(ids.reshape(-1), torch.int32).data_ptr(), M, X, rows.data_ptr(), pos.data_ptr(), ws.data_ptr(), ws.numel(), None)
+    return rows, pos
+
+
+@pytest.mark.parametrize("mode", ["sum", "seq"])
+@pytest.mark.parametrize("N,F,d,X,hot", [(100, 16, 11, 300, False), (700, 16, 11, 50, True), (64, 39, 11, 2000, True), (33, 3, 20, 10, False)])
+def test_scatter_sgd(L, mode, N, F, d, X, hot):
+    import deepctr_oracle as O
+    rng = np.random.default_rng(5)
+    ld = r4(d)
+    table = rng.normal(0, 0.5, (X, d)).astype(np.float32)
+    ids = rng.integers(0, X, (N, F))
+    if hot:
+        ids[:, 0] = 1          # one row shared by every sample (Criteo numeric rows): long-segment path
+        ids[: N // 2, 1] = 2
+    wts = rng.uniform(0.2, 1.5, (N, F)).astype(np.float32)
+    ldz = r4(1 + F * d)
+    dz = rng.normal(0, 1, (N, ldz)).astype(np.float32)
+    ge = dz[:, 1:1 + F * d].astype(np.float64).reshape(N, F, d) * wts[..., None]
+    lr, decay = 0.01, 0.999
+    want = table.astype(np.float64)
+    if mode == "seq":
+        O.seq_decay_scatter(want, ids, ge, lr, decay)
+    else:
+        upd = np.zeros_like(want)
+        np.add.at(upd, ids.reshape(-1), ge.reshape(-1, d))
+        touched = np.unique(ids)
+        want[touched] = want[touched] * decay - lr * upd[touched]
+    rows, pos = _sorted(L, ids, X)
+    t = padded_table(table, ld)
+    ws = torch.zeros(L.lib().dctr_scatter_workspace(N * F, ld), dtype=torch.uint8, device="cuda")
+    dzd = dev(dz)
+    L.call("dctr_scatter_sgd", L.SCATTER_SEQ_DECAY if mode == "seq" else L.SCATTER_SUM, rows.data_ptr(), pos.data_ptr(), N * F, F, d,
+           dzd.data_ptr() + 4, ldz, d, dev(wts).data_ptr(), lr, decay, t.data_ptr(), X, ld, ws.data_ptr(), ws.numel(), None)
+    torch.cuda.synchronize()
+    got = t.cpu().numpy()
+    close(got[:, :d], want, atol=2e-6)
+    assert (got[:, d:] == 0).all()
+    untouched = np.setdiff1d(np.arange(X), ids)
+    assert np.array_equal(got[untouched, :d], table[untouched])     # touched-row set is exact
+
+
+def test_scatter_deterministic(L):
+    rng = np.random.default_rng(9)
+    N, F, d, X, ld = 2000, 16, 11, 100, 12
+    ids = rng.integers(0, X, (N, F))
+    dz = dev(rng.normal(0, 1, (N, F * d + 3)).astype(np.float32))
+    table = rng.normal(0, 0.5, (X, ld)).astype(np.float32)
+    outs = []
+    for _ in range(2):
+        rows, pos = _sorted(L, ids, X)
+        t = dev(table)
+        ws = torch.zeros(L.lib().dctr_scatter_workspace(N * F, ld), dtype=torch.uint8, device="cuda")
+        L.call("dctr_scatter_sgd", L.SCATTER_SUM, rows.data_ptr(), pos.data_ptr(), N * F, F, d, dz.data_ptr(), F * d + 3, d, None,
+               0.1, 1.0, t.data_ptr(), X, ld, ws.data_ptr(), ws.numel(), None)
+        torch.cuda.synchronize()
+        outs.append(t.cpu().numpy())
+    assert np.array_equal(outs[0], outs[1])
+
+
+@pytest.mark.parametrize("lam", [0.0, 0.01])
+def test_fm_scatter_and_sweep(L, lam):
+    import deepctr_oracle as O
+    rng = np.random.default_rng(13)
+    N, F, d, X = 300, 16, 11, 400
+    ld = r4(d)
+    table = rng.normal(0, 0.2, (X, d)).astype(np.float32)
+    ids = rng.integers(0, X - 100, (N, F))
+    ids[:, 0] = 7
+    wts = rng.uniform(0, 1.5, (N, F)).astype(np.float32)
+    y = rng.integers(0, 2, N).astype(np.float32)
+    lr = 0.05
+    fm = O.OracleFM(table, 0.0)
+    fm.train_step(ids, wts, y, lr, lam)
+    t = padded_table(table, ld)
+    idsd, wtsd = dev(ids, torch.int32), dev(wts)
+    g, s = torch.zeros(N, device="cuda"), torch.zeros(N, ld, device="cuda")
+    L.call("dctr_fm_fwd", idsd.data_ptr(), wtsd.data_ptr(), t.data_ptr(), X, ld, N, F, d, None, dev(y).data_ptr(), 1.0,
+           None, None, None, g.data_ptr(), s.data_ptr(), ld, None)
+    rows, pos = _sorted(L, ids, X)
+    ws = torch.zeros(L.lib().dctr_scatter_workspace(N * F, ld), dtype=torch.uint8, device="cuda")
+    decay = 1 - lr * lam
+    L.call("dctr_scatter_sgd_fm", rows.data_ptr(), pos.data_ptr(), N * F, F, d, g.data_ptr(), s.data_ptr(), ld, wtsd.data_ptr(),
+           lr, decay, t.data_ptr(), X, ld, ws.data_ptr(), ws.numel(), None)
+    if lam:
+        L.call("dctr_decay_sweep", t.data_ptr(), X, ld, decay, rows.data_ptr(), N * F, None)
+    torch.cuda.synchronize()
+    close(t.cpu().numpy()[:, :d], fm.table, atol=2e-6)
+
+
+@pytest.mark.parametrize("layout", ["nn", "nt", "tn"])
+@pytest.mark.parametrize("M,N,K", [(100, 300, 177), (4096, 100, 300), (33, 7, 5), (257, 129, 1171), (64, 64, 16), (1, 1, 1)])
+def test_gemm_layouts(L, layout, M, N, K):
+    rng = np.random.default_rng(17)
+    A = rng.normal(0, 1, (M, K)).astype(np.float32)
+    B = rng.normal(0, 1, (K, N)).astype(np.float32)
+    want = A.astype(np.float64) @ B.astype(np.float64)
+
+    def pad(a):
+        r, c = a.shape
+        o = np.zeros((r, r4(c) + 4), np.float32)
+        o[:, :c] = a
+        return dev(o)
+
+    Ad = pad(A if layout != "tn" else A.T.copy())
+    Bd = pad(B if layout != "nt" else B.T.copy())
+    ldc = r4(N) + 4
+    splits = 3 if layout == "tn" else 1
+    C = torch.full((splits, M, ldc), 9.0, device="cuda")
+    lay = {"nn": L.GEMM_NN, "nt": L.GEMM_NT, "tn": L.GEMM_TN}[layout]
+    L.call("dctr_gemm", lay, M, N, K, Ad.data_ptr(), Ad.stride(0), Bd.data_ptr(), Bd.stride(0), C.data_ptr(), ldc,
+           L.EPI_NONE, 0, None, None, 0, None, 0, splits, None)
+    if splits > 1:
+        out = torch.zeros(M, ldc, device="cuda")
+        L.call("dctr_splitk_reduce", C.data_ptr(), splits, M, N, ldc, out.data_ptr(), ldc, None)
+    else:
+        out = C[0]
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()[:, :N]
+    scale = np.sqrt(K)
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=2e-6 * scale)
+
+
+@pytest.mark.parametrize("act", ["tanh", "relu", "sigmoid", "none"])
+@pytest.mark.parametrize("bcast", [False, True])
+def test_gemm_epilogues(L, act, bcast):
+    import deepctr_oracle as O
+    rng = np.random.default_rng(19)
+    M, N, K = 130, 70, 45
+    A = rng.normal(0, 0.5, (M, r4(K))).astype(np.float32); A[:, K:] = 0
+    B = rng.normal(0, 0.5, (K, r4(N))).astype(np.float32); B[:, N:] = 0
+    bias = rng.normal(0, 0.5, N).astype(np.float32)
+    mrows = 1 if bcast else M
+    mask = ((rng.random((mrows, r4(N))) < 0.6) / (1.0 if bcast else 0.6)).astype(np.float32)
+    pre = A[:, :K].astype(np.float64) @ B[:, :N].astype(np.float64) + bias
+    want = O.activate(act, pre) * mask[:, :N]
+    C = torch.zeros(M, r4(N), device="cuda")
+    md = dev(mask)
+    L.call("dctr_gemm", L.GEMM_NN, M, N, K, dev(A).data_ptr(), r4(K), dev(B).data_ptr(), r4(N), C.data_ptr(), r4(N),
+           L.EPI_FWD, L.ACT[act], dev(bias).data_ptr(), None, 0, md.data_ptr(), 0 if bcast else r4(N), 1, None)
+    torch.cuda.synchronize()
+    close(C.cpu().numpy()[:, :N], want, atol=3e-6)
+    # DGRAD: dA = (dY @ W^T) * mask * act'(stored/mask); stored = the forward output `want`-like tensor
+    dY = rng.normal(0, 1, (M, r4(K))).astype(np.float32); dY[:, K:] = 0          # [M, K] plays dY, W = B^T-shaped [N, K]
+    W = rng.normal(0, 0.5, (N, r4(K))).astype(np.float32); W[:, K:] = 0
+    stored = np.zeros((M, r4(N)), np.float32); stored[:, :N] = want
+    din = dY[:, :K].astype(np.float64) @ W[:, :K].astype(np.float64).T
+    mk = np.broadcast_to(mask[:, :N], (M, N)).astype(np.float64)
+    t = np.where(mk != 0, stored[:, :N] / np.where(mk != 0, mk, 1), 0)
+    want_d = din * mk * O.activate_grad_from_out(act, t)
+    D = torch.zeros(M, r4(N), device="cuda")
+    L.call("dctr_gemm", L.GEMM_NT, M, N, K, dev(dY).data_ptr(), r4(K), dev(W).data_ptr(), r4(K), D.data_ptr(), r4(N),
+           L.EPI_DGRAD, L.ACT[act], None, dev(stored).data_ptr(), r4(N), md.data_ptr(), 0 if bcast else r4(N), 1, None)
+    torch.cuda.synchronize()
+    close(D.cpu().numpy()[:, :N], want_d, atol=1e-5)
+
+
+def test_output_unit_and_reductions(L):
+    import deepctr_oracle as O
+    rng = np.random.default_rng(23)
+    N, H = 1000, 100
+    a = rng.normal(0, 1, (N, r4(H))).astype(np.float32)
+    w = rng.normal(0, 0.3, H).astype(np.float32)
+    y = rng.integers(0, 2, N).astype(np.float32)
+    z = a[:, :H].astype(np.float64) @ w + 0.2
+    f = lambda: torch.zeros(N, device="cuda")
+    logit, pred, loss_n, dl = f(), f(), f(), f()
+    ad, wd = dev(a), dev(w)
+    L.call("dctr_out_xent_fwd", ad.data_ptr(), r4(H), N, H, wd.data_ptr(), dev(np.array([0.2], np.float32)).data_ptr(),
+           dev(y).data_ptr(), 1.0, logit.data_ptr(), pred.data_ptr(), loss_n.data_ptr(), dl.data_ptr(), None)
+    close(logit.cpu(), z, atol=1e-5)
+    close(loss_n.cpu(), O.xent_with_logits(z, y), atol=1e-5)
+    close(dl.cpu(), O.sigmoid(z) - y, atol=1e-5)
+    out = torch.zeros(1, device="cuda")
+    L.call("dctr_vec_sum", loss_n.data_ptr(), N, 0.5, out.data_ptr(), None)
+    close(out.cpu(), [0.5 * loss_n.cpu().numpy().astype(np.float64).sum()])
+    ws = torch.zeros(L.lib().dctr_col_wsum_workspace(N, H), dtype=torch.uint8, device="cuda")
+    gw = torch.zeros(H, device="cuda")
+    L.call("dctr_col_wsum", ad.data_ptr(), r4(H), N, H, dl.data_ptr(), gw.data_ptr(), ws.data_ptr(), ws.numel(), None)
+    close(gw.cpu(), (dl.cpu().numpy().astype(np.float64)[:, None] * a[:, :H]).sum(0), atol=1e-4)
+    da = torch.zeros(N, r4(H), device="cuda")
+    L.call("dctr_out_bwd", dl.data_ptr(), wd.data_ptr(), ad.data_ptr(), r4(H), N, H, L.ACT["tanh"], None, 0, da.data_ptr(), r4(H), None)
+    tt = np.tanh(rng.normal(0, 1, 1))  # unused; keeps rng advancing identical across runs
+    close(da.cpu().numpy()[:, :H], dl.cpu().numpy().astype(np.float64)[:, None] * w * (1 - a[:, :H].astype(np.float64) ** 2), atol=1e-5)
+    p = dev(rng.normal(0, 1, 1001).astype(np.float32)); g = dev(rng.normal(0, 1, 1001).astype(np.float32))
+    want = p.cpu().numpy().astype(np.float64) * 0.99 - 0.1 * g.cpu().numpy()
+    L.call("dctr_dense_sgd", p.data_ptr(), g.data_ptr(), 1001, 0.1, 0.99, None)
+    torch.cuda.synchronize()
+    close(p.cpu(), want)
+
+
+def test_empty_inputs(L):
+    # N = 0 / M = 0 are accepted and launch nothing
+    before = L.launch_count()
+    L.call("dctr_gather_concat_fwd", 16, None, 16, 10, 12, 0, 16, 11, 0, 1, None, 0, 16, 180, None)
+    L.call("dctr_sort_rows", None, 0, 10, None, None, None, 0, None)
+    L.call("dctr_gemm", L.GEMM_NN, 0, 4, 4, 16, 4, 16, 4, 16, 4, 0, 0, None, None, 0, None, 0, 1, None)
+    assert L.launch_count() == before
