@@ -73,9 +73,21 @@ def lib():
     return _lib
 
 
+PROFILE = None   # bench.py sets this to a list; every call then appends (name, args, start_event, end_event)
+
+
 def call(name, *args):
     """Invoke an int-returning entry point; raise RuntimeError with dctr_last_error() on failure."""
-    rc = getattr(lib(), name)(*args)
+    if PROFILE is not None:
+        import torch
+        st = torch.cuda.current_stream()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        rc = getattr(lib(), name)(*args)
+        e1.record(st)
+        PROFILE.append((name, args, e0, e1))
+    else:
+        rc = getattr(lib(), name)(*args)
     if rc != 0:
         raise RuntimeError("%s failed (%d): %s" % (name, rc, lib().dctr_last_error().decode()))
 

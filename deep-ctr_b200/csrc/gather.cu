@@ -99,7 +99,7 @@ cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
     const int Fd = F * d;
     const int P = F * (F - 1) / 2;
     const int crossw = CROSS == DCTR_CROSS_IP ? P : (CROSS == DCTR_CROSS_OP ? d * d : 0);
-    const int per_warp = F * ld * (CROSS == DCTR_CROSS_OP ? 2 : 1) + crossw + (CROSS == DCTR_CROSS_OP ? d : 0);
+    const int per_warp = (F * ld * (CROSS == DCTR_CROSS_OP ? 2 : 1) + crossw + (CROSS == DCTR_CROSS_OP ? d : 0) + 3) & ~3;  // keep float4 alignment
     float* e = smem + warp * per_warp;
     float* pre = e + F * ld;                                        // OP only: prefix_{<f}[a]
     float* dc = e + F * ld * (CROSS == DCTR_CROSS_OP ? 2 : 1);      // dL/dcross
@@ -196,7 +196,7 @@ extern "C" int dctr_cross_bwd(const int32_t* ids, const float* wts, const float*
     DCTR_REQUIRE(cross >= 0 && cross <= 2 && X > 0, "cross_bwd: bad cross");
     if (N == 0) return DCTR_OK;
     const int crossw = cross == DCTR_CROSS_IP ? F * (F - 1) / 2 : (cross == DCTR_CROSS_OP ? d * d : 0);
-    const int per_warp = F * ld * (cross == DCTR_CROSS_OP ? 2 : 1) + crossw + (cross == DCTR_CROSS_OP ? d : 0);
+    const int per_warp = (F * ld * (cross == DCTR_CROSS_OP ? 2 : 1) + crossw + (cross == DCTR_CROSS_OP ? d : 0) + 3) & ~3;
     size_t smem = (size_t)kGatherWarps * per_warp * sizeof(float);
     DCTR_REQUIRE(smem <= 200 * 1024, "cross_bwd: field block too large for shared memory");
     dim3 grid(gather_grid(N)), block(kGatherWarps * 32);

@@ -19,11 +19,24 @@ def L():
     return _lib
 
 
+_KEEP = []   # device tensors stay referenced until the test ends: kernels are asynchronous and the caching
+             # allocator would hand a dropped temporary's block to the next allocation
+
+
+@pytest.fixture(autouse=True)
+def _release():
+    yield
+    torch.cuda.synchronize()
+    del _KEEP[:]
+
+
 def dev(a, dtype=None):
     t = torch.as_tensor(np.ascontiguousarray(a))
     if dtype is not None:
         t = t.to(dtype)
-    return t.cuda()
+    t = t.cuda()
+    _KEEP.append(t)
+    return t
 
 
 def padded_table(table, ld):
