@@ -1,0 +1,418 @@
+#!/usr/bin/env python
+"""bench.py -- one JSON line per run (see the driver contract in DESIGN.md section "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload fnn_ipinyou] [--impl reference]
+
+A "step" is one full train step of the hot path (gather -> MLP fwd/bwd -> sorted segmented scatter-SGD ->
+dense SGD) over one synthetic batch.  `value` is device-timed with the batch already resident in HBM;
+`e2e` goes through the reference-facing model class with HOST numpy buffers (H2D + D2H inside).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (form, F, X, rank, hidden, cross, batch per GPU)
+    "fnn_ipinyou": ("theano", 16, 1_000_000, 10, [300, 100], "none", 4096),
+    "fm_ipinyou": ("fm", 16, 1_000_000, 10, [], "none", 4096),
+    "fnn_ip_l3_ipinyou": ("tf", 16, 1_000_000, 10, [400, 400, 200], "ip", 4096),
+    "fnn_op_l3_ipinyou": ("tf", 16, 1_000_000, 10, [800, 400, 200], "op", 4096),
+    "fnn_ip_l7_ipinyou": ("tf", 16, 1_000_000, 10, [1000, 800, 600, 400, 200, 100, 50], "ip", 65536),
+    "fnn_criteo": ("tf", 39, 1_636_608, 10, [400, 400], "none", 65536),
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tensor=d.get("bf16_tflops_sustained", d["bf16_tflops"]), src="measured")
+    return dict(hbm=6650.0, tensor=1400.0, src="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons every 200 ms while the timed region runs."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        self.stop_flag = True
+        self.join(timeout=6)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons, "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# synthetic workload (seeded; iPinYou-shaped: 16 fields, field cardinalities summing to X, Zipf(1.1) ids)
+# ---------------------------------------------------------------------------------------------------
+def make_pool(form, F, X, N, n_batches, seed):
+    from deepctr_b200 import data
+    rng = np.random.default_rng(seed)
+    if F == 39:
+        sizes = data.scaled_criteo_cat_sizes(X) if X != 13 + int(data.CRITEO_CAT_SIZES.sum()) else data.CRITEO_CAT_SIZES
+        pool = []
+        for _ in range(n_batches):
+            ids, wts = data.make_criteo_batch(rng, N, sizes)
+            pool.append((ids, wts, (rng.random(N) < 0.05).astype(np.float32)))
+        return pool, sizes
+    sizes = data.ipinyou_field_sizes(X)
+    pool = []
+    for _ in range(n_batches):
+        ids = data.make_field_batch(rng, N, sizes, 1.1)
+        pool.append((ids, np.ones((N, F), np.float32), (rng.random(N) < 0.05).astype(np.float32)))
+    return pool, sizes
+
+
+def build_model(wl, N, seed=1234):
+    """Returns (model, train_fn(host ids, wts, y) -> (loss, preds)) through the reference-facing classes."""
+    form, F, X, rank, hidden, cross, _ = WORKLOADS[wl]
+    rng = np.random.default_rng(seed)
+    d = rank + 1
+    if form == "theano":
+        from deepctr_b200.theano_fnn import FNN_wnzh
+        from deepctr_b200 import data
+        sizes = data.ipinyou_field_sizes(X)
+        feat_field = np.repeat(np.arange(F), sizes)
+        table = rng.uniform(-0.01, 0.01, (X, d)).astype(np.float32)
+        m = FNN_wnzh(dict(w_0=0.0, table=table, feat_field=feat_field), batch_size=N, lr=0.001, dropout=0.5,
+                     hidden1=hidden[0], hidden2=hidden[1], lambda1=0.0, lambda_fm=0.1)
+        m.engine.W(2).uniform_(-0.05, 0.05)      # w3 = 0 (FNN_wnzh.py:130) would make step-1 gradients trivially 0
+        return m, lambda ids, wts, y: m.train(ids, y)
+    if form == "fm":
+        from deepctr_b200.models import FM
+        m = FM(N, [X, F, rank], ["uniform", -0.01, 0.01, [0x3210, 0x7654], None], ["sgd", 1e-3, "sum"], [0.0], "train", N)
+        return m, lambda ids, wts, y: m.train_step({m.sp_id_hldr: ids.reshape(-1), m.sp_wt_hldr: wts.reshape(-1), m.lbl_hldr: y})
+    import deepctr_b200.models as M
+    from deepctr_b200 import data
+    cls = {("none", 2): M.FNN, ("ip", 3): M.FNN_IP_L3, ("op", 3): M.FNN_OP_L3, ("ip", 5): M.FNN_IP_L5, ("ip", 7): M.FNN_IP_L7}[(cross, len(hidden))]
+    if F == 39:
+        cat_sizes = data.CRITEO_CAT_SIZES if X == 13 + int(data.CRITEO_CAT_SIZES.sum()) else data.scaled_criteo_cat_sizes(X)
+        n_num = 13
+    else:
+        cat_sizes, n_num = data.ipinyou_field_sizes(X), 0
+    offsets = data.offsets_of(cat_sizes, n_num)
+    m = cls(cat_sizes, offsets, N, [X, F, rank] + hidden + ["tanh"], ["uniform", -0.01, 0.01, list(range(1, 20)), None],
+            ["sgd", 1e-3, "sum"], [1.0], "train", N)
+    for l in range(m.engine.nl):     # +-0.01 weights make every activation ~0: use fan-in scaling for a realistic step
+        m.engine.W(l).uniform_(-1, 1).mul_(1.0 / np.sqrt(m.engine.widths[l]))
+
+    def train(ids, wts, y):
+        return m.train_step({m.v_wt_hldr: wts[:, :n_num], m.c_id_hldr: ids[:, n_num:] - offsets, m.c_wt_hldr: wts[:, n_num:], m.lbl_hldr: y})
+    return m, train
+
+
+# algorithmic bytes / flops per call; args are the ctypes arguments of the call
+def call_cost(name, a):
+    if name == "dctr_gemm":
+        return "flop", 2.0 * a[1] * a[2] * a[3]
+    if name == "dctr_gather_concat_fwd":
+        N, F, d, ldz = a[5], a[6], a[7], a[13]
+        cross = a[8]
+        D0 = F * d + (F * (F - 1) // 2 if cross == 1 else d * d if cross == 2 else 0) + 1
+        return "byte", N * (F * 8 + F * 4 * d + 4 * D0)
+    if name == "dctr_fm_fwd":
+        N, F, d = a[5], a[6], a[7]
+        return "byte", N * (F * 8 + 4 + F * 4 * d + 4 + 4 * d)
+    if name in ("dctr_scatter_sgd", "dctr_scatter_sgd_fm"):
+        M, d = (a[3], a[5]) if name == "dctr_scatter_sgd" else (a[2], a[4])
+        return "byte", M * (4 + 4 * d + 2 * 4 * d)
+    if name == "dctr_cross_bwd":
+        N, F, d, ldz = a[5], a[6], a[7], a[10]
+        return "byte", N * (F * 8 + F * 4 * d + 4 * ldz + F * 4 * d)
+    if name == "dctr_sort_rows":
+        M, X = a[1], a[2]
+        passes = max(1, (max(1, int(X - 1).bit_length()) + 7) // 8)
+        return "byte", passes * M * (8 + 16)       # histogram read + scatter read/write of (key, pos)
+    if name == "dctr_splitk_reduce":
+        return "byte", (a[1] + 1) * a[2] * a[3] * 4
+    if name == "dctr_dense_sgd":
+        return "byte", a[2] * 12
+    if name == "dctr_out_bwd":
+        return "byte", a[4] * a[5] * 8
+    if name == "dctr_col_wsum":
+        return "byte", a[2] * a[3] * 4
+    if name == "dctr_out_xent_fwd":
+        return "byte", a[2] * a[3] * 4
+    return "byte", 0.0
+
+
+def run_b200(args, rank, world):
+    import torch
+    import deepctr_b200
+    from deepctr_b200 import _lib
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    wl = args.workload
+    form, F, X, rank_k, hidden, cross, N = WORKLOADS[wl]
+    N = args.batch or N
+    model, train = build_model(wl, N)
+    if world > 1:
+        from deepctr_b200 import dist as ddist
+        ddist.attach(model, dist)
+    eng = model.engine
+    pool, _ = make_pool(form, F, X, N, 8, seed=1234 + rank)
+    if form == "theano":
+        pool = [(model.arrange(ids)[0], w, y) for ids, w, y in pool]
+    dpool = [(torch.as_tensor(i.astype(np.int32)).cuda(), torch.as_tensor(w).cuda(), torch.as_tensor(y).cuda()) for i, w, y in pool]
+    flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device="cuda")     # > 126 MB L2
+    K, W = args.steps, max(3, args.warmup)
+
+    def device_step(i):
+        ids, wts, y = dpool[i % len(dpool)]
+        eng.ids.copy_(ids)
+        eng.wts.copy_(wts)
+        eng.y.copy_(y)
+        model._pre_step()
+        model._run_step()
+
+    for i in range(W):
+        device_step(i)
+    torch.cuda.synchronize()
+    assert model._graph is not None or not model.use_graph
+    l0 = _lib.launch_count()
+    model.use_graph, g = False, model._graph
+    device_step(0)                       # one eager step just to count this library's launches per step
+    per_step_launches = _lib.launch_count() - l0
+    model.use_graph, model._graph = True, g
+    if dist:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    evs = []
+    for i in range(K):
+        flush.zero_()                    # evict table / weights / activations from L2 (not timed)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        device_step(W + i)
+        e1.record()
+        evs.append((e0, e1))
+    torch.cuda.synchronize()
+    if dist:
+        dist.barrier()
+    total_ms = sum(a.elapsed_time(b) for a, b in evs)
+    # warm-L2 variant (no flush, back to back): reported next to the cold number
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(K):
+        device_step(W + i)
+    e1.record()
+    torch.cuda.synchronize()
+    warm_ms = e0.elapsed_time(e1)
+    clocks = sampler.summary()
+    if dist:
+        t = torch.tensor([total_ms, warm_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, warm_ms = float(t[0]), float(t[1])
+
+    # ---- end to end: host numpy in, loss / preds out, through the model class ----
+    hp = pool
+    for i in range(3):
+        train(*hp[i % len(hp)])
+    torch.cuda.synchronize()
+    if dist:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for i in range(K):
+        loss, preds = train(*hp[i % len(hp)])
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if dist:
+        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t[0])
+    assert np.isfinite(loss) and np.isfinite(preds).all()
+
+    # ---- per-kernel timing (CUDA events on the launching stream; eager; launches queued behind a sleep) ----
+    kernels, roof = [], None
+    if not args.no_profile:
+        model.use_graph = False
+        agg = {}
+        P = 5
+        for i in range(P):
+            flush.zero_()
+            torch.cuda._sleep(2_000_000)           # ~1 ms: lets the host enqueue the whole step ahead of the GPU
+            _lib.PROFILE = []
+            device_step(i)
+            torch.cuda.synchronize()
+            for name, a, s, e in _lib.PROFILE:
+                key = name if name != "dctr_gemm" else "dctr_gemm[%s %dx%dx%d]" % (["NN", "NT", "TN"][a[0]], a[1], a[2], a[3])
+                unit, cost = call_cost(name, a)
+                r = agg.setdefault(key, dict(ms=0.0, cost=0.0, unit=unit, calls=0))
+                r["ms"] += s.elapsed_time(e)
+                r["cost"] += cost
+                r["calls"] += 1
+            _lib.PROFILE = None
+        model.use_graph = True
+        pk = peaks()
+        tot = sum(r["ms"] for r in agg.values())
+        for key, r in sorted(agg.items(), key=lambda kv: -kv[1]["ms"]):
+            ach = r["cost"] / (r["ms"] * 1e-3) / (1e12 if r["unit"] == "flop" else 1e9) if r["ms"] > 0 else 0.0
+            peak = pk["tensor"] if r["unit"] == "flop" else pk["hbm"]
+            kernels.append({"kernel": key, "us_per_step": round(r["ms"] / P * 1e3, 2), "share": round(r["ms"] / tot, 3),
+                            "achieved": round(ach, 2), "unit": "TFLOP/s" if r["unit"] == "flop" else "GB/s",
+                            "frac": round(ach / peak, 4), "calls_per_step": r["calls"] // P})
+        top = kernels[0]
+        roof = {"kernel": top["kernel"], "bound": "tensor" if top["unit"] == "TFLOP/s" else "hbm", "achieved": top["achieved"],
+                "peak": pk["tensor"] if top["unit"] == "TFLOP/s" else pk["hbm"], "unit": top["unit"], "frac": top["frac"],
+                "traffic": None, "peak_source": pk["src"] + (" (bf16 sustained)" if top["unit"] == "TFLOP/s" else " (copy)"),
+                "share_of_step": top["share"]}
+        if top["unit"] == "TFLOP/s":
+            roof["note"] = "fp32 FFMA parity path; fp32 SIMT peak is 74.4 TFLOP/s -> frac_of_fp32_peak"
+            roof["frac_of_fp32_peak"] = round(top["achieved"] / 74.4, 4)
+
+    out = {
+        "metric": "FNN train samples/s", "value": N * world * K / (total_ms * 1e-3), "unit": "samples/s", "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl, "form": form, "fields": F, "rows": X, "rank": rank_k, "hidden": hidden, "cross": cross,
+                   "batch_per_gpu": N, "global_batch": N * world, "l2": "flushed (512 MB write) before every timed step",
+                   "parallelism": "dp%d" % world if world > 1 else "single", "cuda_graph": True},
+        "warm_l2": {"ms_per_step": warm_ms / K, "value": N * world * K / (warm_ms * 1e-3)},
+        "e2e": {"value": N * world * K / e2e_s, "unit": "samples/s", "h2d_bytes_per_step": model.h2d_bytes,
+                "d2h_bytes_per_step": model.d2h_bytes, "ms_per_step": e2e_s / K * 1e3},
+        "gpu_launches": int(per_step_launches * K), "launches_per_step": int(per_step_launches),
+        "clocks": clocks,
+    }
+    if roof:
+        out["roofline"] = roof
+        out["kernels"] = kernels
+    if rank == 0 and world == 1 and not args.no_cpu:
+        out["cpu_baseline"] = cpu_baseline(wl, N, budget_s=12.0)
+    if rank == 0:
+        print(json.dumps(out))
+    if dist:
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arm: the oracle restatement of the reference step (numpy float64 + OpenBLAS, all host cores)
+# ---------------------------------------------------------------------------------------------------
+def oracle_stepper(wl, N, seed=1234):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import deepctr_oracle as O
+    form, F, X, rank, hidden, cross, _ = WORKLOADS[wl]
+    rng = np.random.default_rng(seed)
+    d = rank + 1
+    table = rng.uniform(-0.01, 0.01, (X, d))
+    if form == "fm":
+        fm = O.OracleFM(table, 0.0)
+        return lambda ids, wts, y: fm.train_step(ids, wts, y, 1e-3, 0.0, dense_l2=False)
+    cw = {"none": 0, "ip": F * (F - 1) // 2, "op": d * d}[cross]
+    dims = [F * d + cw + 1] + hidden + [1]
+    Ws = [rng.uniform(-1, 1, (dims[i], dims[i + 1])) / np.sqrt(dims[i]) for i in range(len(dims) - 1)]
+    bs = [np.zeros(dims[i + 1]) for i in range(len(dims) - 1)]
+    if form == "theano":
+        net = O.OracleNet(table, 0.0, Ws, bs, F, d, "none", True, "none", "tanh")
+        mrng = np.random.RandomState(234)
+
+        def step(ids, wts, y):
+            masks = [None, mrng.binomial(1, 0.5, (1, hidden[0])).astype(np.float64), mrng.binomial(1, 0.5, (1, hidden[1])).astype(np.float64)]
+            return net.train_step_theano(ids, y, 1e-3, 0.1, masks=masks, closed_form=True)
+        return step
+    net = O.OracleNet(table, 0.0, Ws, bs, F, d, cross, False, "tanh", "tanh")
+    return lambda ids, wts, y: net.train_step_tf(ids, wts, y, 1e-3)
+
+
+def cpu_baseline(wl, N, budget_s=12.0, steps=None):
+    form, F, X, *_ = WORKLOADS[wl]
+    step = oracle_stepper(wl, N)
+    pool, _ = make_pool(form, F, X, N, 4, seed=99)
+    step(*pool[0])                                  # warm-up (BLAS threads, page faults)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        step(*pool[n % len(pool)])
+        n += 1
+        el = time.perf_counter() - t0
+        if (steps and n >= steps) or (not steps and el > budget_s):
+            break
+    return {"value": n * N / el, "unit": "samples/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": "%d steps of batch %d of workload %s (vectorised numpy float64 restatement, OpenBLAS threads = all cores)" % (n, N, wl),
+            "ms_per_step": el / n * 1e3}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU path (oracle port; the Py2/Theano/TF original cannot run here)."""
+    if rank != 0:
+        return
+    wl = args.workload
+    N = args.batch or WORKLOADS[wl][6]
+    K, W = args.steps, max(1, args.warmup)
+    step = oracle_stepper(wl, N)
+    form, F, X, *_ = WORKLOADS[wl]
+    pool, _ = make_pool(form, F, X, N, 4, seed=99)
+    for i in range(min(W, 3)):
+        step(*pool[i % 4])
+    K = min(K, 200)
+    t0 = time.perf_counter()
+    done = 0
+    for i in range(K):
+        step(*pool[i % 4])
+        done += 1
+        if time.perf_counter() - t0 > 120:        # bounded sample
+            break
+    el = time.perf_counter() - t0
+    v = done * N / el
+    print(json.dumps({
+        "impl": "reference", "metric": "FNN train samples/s", "value": v, "unit": "samples/s", "n_gpus": world, "steps": done,
+        "warmup": W, "ms_per_step": el / done * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": wl, "batch_per_gpu": N, "note": "CPU oracle port of the reference step on rank 0's host cores"},
+        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": os.cpu_count(), "kind": "port",
+                         "sample": "%d steps of batch %d (numpy float64 + OpenBLAS)" % (done, N)},
+        "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="fnn_ipinyou", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_b200(args, rank, world)
+
+
+if __name__ == "__main__":
+    main()
