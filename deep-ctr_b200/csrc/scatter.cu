@@ -48,7 +48,8 @@ __device__ __forceinline__ int64_t segment_end(const int32_t* __restrict__ rows,
 template <bool SEQ, class Src>
 __global__ void __launch_bounds__(kFoldThreads)
 fold_short_kernel(Src src, const int32_t* __restrict__ rows, const int32_t* __restrict__ pos, int64_t M, int F, int d,
-                  float lr, float decay, float* __restrict__ table, int ld, int32_t* __restrict__ hdr, LongSeg* __restrict__ longs) {
+                  float lr, float decay, float* __restrict__ table, int ld, int32_t* __restrict__ hdr, LongSeg* __restrict__ longs,
+                  int32_t* __restrict__ chunk_seg) {
     const int64_t i = ((int64_t)blockIdx.x * kFoldThreads + threadIdx.x) / kGroup;
     const int gl = threadIdx.x & (kGroup - 1);
     if (i >= M) return;
@@ -57,12 +58,18 @@ fold_short_kernel(Src src, const int32_t* __restrict__ rows, const int32_t* __re
     const int64_t end = segment_end(rows, i, M, row);
     const int len = (int)(end - i);
     if (len > DCTR_LONG_SEG) {
+        const int nchunks = (len + DCTR_SEG_CHUNK - 1) / DCTR_SEG_CHUNK;
+        int slot = 0, coff = 0;
         if (gl == 0) {
-            const int slot = atomicAdd(&hdr[0], 1);
-            const int nchunks = (len + DCTR_SEG_CHUNK - 1) / DCTR_SEG_CHUNK;
-            LongSeg ls; ls.start = (int32_t)i; ls.len = len; ls.chunk_off = atomicAdd(&hdr[1], nchunks); ls.pad = 0;
+            slot = atomicAdd(&hdr[0], 1);
+            coff = atomicAdd(&hdr[1], nchunks);
+            LongSeg ls; ls.start = (int32_t)i; ls.len = len; ls.chunk_off = coff; ls.pad = 0;
             longs[slot] = ls;   // slot order is arbitrary; every segment is folded independently
         }
+        const unsigned gmask = 0xffffu << (threadIdx.x & 16);
+        slot = __shfl_sync(gmask, slot, 0, kGroup);
+        coff = __shfl_sync(gmask, coff, 0, kGroup);
+        for (int j = gl; j < nchunks; j += kGroup) chunk_seg[coff + j] = slot;   // chunk -> owning long segment
         return;
     }
     float* trow = table + (int64_t)row * ld;
@@ -80,37 +87,35 @@ fold_short_kernel(Src src, const int32_t* __restrict__ rows, const int32_t* __re
     }
 }
 
-// one 16-lane group per (long segment, chunk): partial[chunk][c] = B, partial[chunk][ld + c] = A
+// one 16-lane group per chunk of a long segment: partial[chunk][c] = B, partial[chunk][ld + c] = A
 template <bool SEQ, class Src>
 __global__ void __launch_bounds__(kFoldThreads)
 fold_chunk_kernel(Src src, const int32_t* __restrict__ pos, int F, int d, float lr, float decay,
                   const float* __restrict__ table, const int32_t* __restrict__ rows, int ld,
-                  const int32_t* __restrict__ hdr, const LongSeg* __restrict__ longs, float* __restrict__ partial) {
-    const int nlong = hdr[0];
+                  const int32_t* __restrict__ hdr, const LongSeg* __restrict__ longs,
+                  const int32_t* __restrict__ chunk_seg, float* __restrict__ partial) {
+    const int total_chunks = hdr[1];
     const int gl = threadIdx.x & (kGroup - 1);
-    const int group = threadIdx.x / kGroup;
     const int groups_total = gridDim.x * (kFoldThreads / kGroup);
-    for (int sidx = 0; sidx < nlong; ++sidx) {
-        const LongSeg ls = longs[sidx];
-        const int nchunks = (ls.len + DCTR_SEG_CHUNK - 1) / DCTR_SEG_CHUNK;
+    for (int g = blockIdx.x * (kFoldThreads / kGroup) + threadIdx.x / kGroup; g < total_chunks; g += groups_total) {
+        const LongSeg ls = longs[chunk_seg[g]];
+        const int j = g - ls.chunk_off;
         const float* trow = table + (int64_t)rows[ls.start] * ld;
-        for (int j = blockIdx.x * (kFoldThreads / kGroup) + group; j < nchunks; j += groups_total) {
-            const int64_t k0 = (int64_t)ls.start + (int64_t)j * DCTR_SEG_CHUNK;
-            const int64_t k1 = (k0 + DCTR_SEG_CHUNK < (int64_t)ls.start + ls.len) ? k0 + DCTR_SEG_CHUNK : (int64_t)ls.start + ls.len;
-            float* out = partial + (int64_t)(ls.chunk_off + j) * 2 * ld;
-            for (int c = gl; c < d; c += kGroup) {
-                const float old = trow[c];
-                float a = 1.f, b = 0.f;
+        const int64_t k0 = (int64_t)ls.start + (int64_t)j * DCTR_SEG_CHUNK;
+        const int64_t k1 = (k0 + DCTR_SEG_CHUNK < (int64_t)ls.start + ls.len) ? k0 + DCTR_SEG_CHUNK : (int64_t)ls.start + ls.len;
+        float* out = partial + (int64_t)g * 2 * ld;
+        for (int c = gl; c < d; c += kGroup) {
+            const float old = trow[c];
+            float a = 1.f, b = 0.f;
 #pragma unroll 4
-                for (int64_t k = k0; k < k1; ++k) {
-                    const int p = pos[k];
-                    const int n = p / F;
-                    const float gk = src(p, n, p - n * F, c, old);
-                    if (SEQ) { b = fmaf(b, decay, -lr * gk); a *= decay; } else { b += gk; }
-                }
-                out[c] = b;
-                out[ld + c] = a;
+            for (int64_t k = k0; k < k1; ++k) {
+                const int p = pos[k];
+                const int n = p / F;
+                const float gk = src(p, n, p - n * F, c, old);
+                if (SEQ) { b = fmaf(b, decay, -lr * gk); a *= decay; } else { b += gk; }
             }
+            out[c] = b;
+            out[ld + c] = a;
         }
     }
 }
@@ -166,18 +171,19 @@ static int run_fold(int mode, Src src, const int32_t* rows, const int32_t* pos, 
     }
     int32_t* hdr = static_cast<int32_t*>(workspace);
     LongSeg* longs = reinterpret_cast<LongSeg*>(hdr + 4);
-    float* partial = reinterpret_cast<float*>(longs + longs_capacity(M));
+    int32_t* chunk_seg = reinterpret_cast<int32_t*>(longs + longs_capacity(M));
+    float* partial = reinterpret_cast<float*>(chunk_seg + ((chunks_capacity(M) + 3) & ~(size_t)3));
     cudaMemsetAsync(hdr, 0, 16, st);
     const int blocks = ceil_div(M * kGroup, kFoldThreads);
     const int pgrid = kNumSMs * 4;
     const bool seq = mode == DCTR_SCATTER_SEQ_DECAY;
     int rc;
-    if (seq) fold_short_kernel<true, Src><<<blocks, kFoldThreads, 0, st>>>(src, rows, pos, M, F, d, lr, decay, table, ld, hdr, longs);
-    else fold_short_kernel<false, Src><<<blocks, kFoldThreads, 0, st>>>(src, rows, pos, M, F, d, lr, decay, table, ld, hdr, longs);
+    if (seq) fold_short_kernel<true, Src><<<blocks, kFoldThreads, 0, st>>>(src, rows, pos, M, F, d, lr, decay, table, ld, hdr, longs, chunk_seg);
+    else fold_short_kernel<false, Src><<<blocks, kFoldThreads, 0, st>>>(src, rows, pos, M, F, d, lr, decay, table, ld, hdr, longs, chunk_seg);
     if ((rc = check_launch("fold_short_kernel"))) return rc;
     if (M > DCTR_LONG_SEG) {
-        if (seq) fold_chunk_kernel<true, Src><<<pgrid, kFoldThreads, 0, st>>>(src, pos, F, d, lr, decay, table, rows, ld, hdr, longs, partial);
-        else fold_chunk_kernel<false, Src><<<pgrid, kFoldThreads, 0, st>>>(src, pos, F, d, lr, decay, table, rows, ld, hdr, longs, partial);
+        if (seq) fold_chunk_kernel<true, Src><<<pgrid, kFoldThreads, 0, st>>>(src, pos, F, d, lr, decay, table, rows, ld, hdr, longs, chunk_seg, partial);
+        else fold_chunk_kernel<false, Src><<<pgrid, kFoldThreads, 0, st>>>(src, pos, F, d, lr, decay, table, rows, ld, hdr, longs, chunk_seg, partial);
         if ((rc = check_launch("fold_chunk_kernel"))) return rc;
         if (seq) fold_combine_kernel<true><<<kNumSMs, kFoldThreads, 0, st>>>(d, lr, decay, table, rows, ld, hdr, longs, partial);
         else fold_combine_kernel<false><<<kNumSMs, kFoldThreads, 0, st>>>(d, lr, decay, table, rows, ld, hdr, longs, partial);
@@ -192,7 +198,8 @@ using namespace dctr;
 
 extern "C" size_t dctr_scatter_workspace(int64_t M, int ld) {
     if (M < 0) M = 0;
-    return 16 + longs_capacity(M) * sizeof(LongSeg) + chunks_capacity(M) * 2 * (size_t)ld * sizeof(float);
+    return 16 + longs_capacity(M) * sizeof(LongSeg) + ((chunks_capacity(M) + 3) & ~(size_t)3) * sizeof(int32_t) +
+           chunks_capacity(M) * 2 * (size_t)ld * sizeof(float);
 }
 
 extern "C" int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F,

@@ -86,8 +86,8 @@ int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t* sorted_row
  *   SUM:        row -= lr * sum_p grad(p,:)
  *   SEQ_DECAY:  for p in segment order: row = row*decay - lr*grad(p,:)
  * workspace: dctr_scatter_workspace(M, ld) bytes (long-segment list + chunk partials). */
-#define DCTR_LONG_SEG 64    /* segments longer than this are folded by chunks of DCTR_SEG_CHUNK */
-#define DCTR_SEG_CHUNK 128
+#define DCTR_LONG_SEG 32    /* segments longer than this are folded by chunks of DCTR_SEG_CHUNK */
+#define DCTR_SEG_CHUNK 32
 size_t dctr_scatter_workspace(int64_t M, int ld);
 int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
                      const float* g, int64_t g_ld_n, int g_ld_f, const float* wts,
