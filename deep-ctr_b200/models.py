@@ -230,7 +230,7 @@ class FM(_Base):
             self.test_preds = Fetch(self, "test_preds")
 
     def _device_step(self):
-        gs = 1.0 if self._reduce == "sum" else 1.0 / self.N
+        gs = 1.0 if self._reduce == "sum" else 1.0 / getattr(self, "global_N", self.N)
         self.engine.train_step(self.lr, self._lambda, gs)
 
     def train_step(self, feed):
@@ -338,7 +338,7 @@ class _FNNBase(_Base):
                 m.copy_((torch.rand(m.shape, device=m.device, generator=self._gen) < self._keep_prob).float() / self._keep_prob)
 
     def _device_step(self):
-        gs = 1.0 if self._reduce == "sum" else 1.0 / self.N
+        gs = 1.0 if self._reduce == "sum" else 1.0 / getattr(self, "global_N", self.N)
         self.engine.train_step(self.lr, 1.0, gs, train_bias=True)
 
     def _global(self, v_wts, c_ids, c_wts):

@@ -103,7 +103,7 @@ class FNN_wnzh(_Base):
         e.masks[2][:, :r2.shape[1]].copy_(torch.from_numpy(r2))
 
     def _device_step(self):
-        decay = 1.0 - 2.0 * self.lambda_fm * self.lr / self.N        # FNN_wnzh.py:305
+        decay = 1.0 - 2.0 * self.lambda_fm * self.lr / getattr(self, "global_N", self.N)   # FNN_wnzh.py:305 (b_size)
         self.engine.train_step(self.lr, decay, 1.0, train_bias=False, last_decay=1.0 - 2.0 * self.lr * self.lambda1)
 
     def train(self, feats, y):
