@@ -202,10 +202,11 @@ def run_b200(args, rank, world):
     torch.cuda.synchronize()
     assert model._graph is not None or not model.use_graph
     l0 = _lib.launch_count()
-    model.use_graph, g = False, model._graph
+    was_graph, g = model.use_graph, model._graph
+    model.use_graph = False
     device_step(0)                       # one eager step just to count this library's launches per step
     per_step_launches = _lib.launch_count() - l0
-    model.use_graph, model._graph = True, g
+    model.use_graph, model._graph = was_graph, g
     if dist:
         dist.barrier()
     torch.cuda.synchronize()
@@ -259,6 +260,7 @@ def run_b200(args, rank, world):
     # ---- per-kernel timing (CUDA events on the launching stream; eager; launches queued behind a sleep) ----
     kernels, roof = [], None
     if not args.no_profile:
+        was_graph = model.use_graph
         model.use_graph = False
         agg = {}
         P = 5
@@ -276,7 +278,7 @@ def run_b200(args, rank, world):
                 r["cost"] += cost
                 r["calls"] += 1
             _lib.PROFILE = None
-        model.use_graph = True
+        model.use_graph = was_graph
         pk = peaks()
         tot = sum(r["ms"] for r in agg.values())
         for key, r in sorted(agg.items(), key=lambda kv: -kv[1]["ms"]):
@@ -300,7 +302,7 @@ def run_b200(args, rank, world):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl, "form": form, "fields": F, "rows": X, "rank": rank_k, "hidden": hidden, "cross": cross,
                    "batch_per_gpu": N, "global_batch": N * world, "l2": "flushed (512 MB write) before every timed step",
-                   "parallelism": "dp%d" % world if world > 1 else "single", "cuda_graph": True},
+                   "parallelism": "dp%d" % world if world > 1 else "single", "cuda_graph": bool(model.use_graph)},
         "warm_l2": {"ms_per_step": warm_ms / K, "value": N * world * K / (warm_ms * 1e-3)},
         "e2e": {"value": N * world * K / e2e_s, "unit": "samples/s", "h2d_bytes_per_step": model.h2d_bytes,
                 "d2h_bytes_per_step": model.d2h_bytes, "ms_per_step": e2e_s / K * 1e3},
