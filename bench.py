@@ -164,6 +164,59 @@ def call_cost(name, a):
     return "byte", 0.0
 
 
+def emb_roofline(N=1 << 20, F=16, rank=10, X=20_000_000, reps=5):
+    """The HBM-bound kernels alone at a size where they ARE bandwidth-bound (table 0.96 GB >> 126 MB L2,
+    N = 2^20 samples per launch): achieved algorithmic GB/s vs the measured copy peak."""
+    import torch
+    from deepctr_b200 import _lib as L, data
+    d = rank + 1
+    ld = (d + 3) // 4 * 4
+    rng = np.random.default_rng(7)
+    sizes = data.ipinyou_field_sizes(X)
+    ids_h = data.make_field_batch(rng, N, sizes, 1.1).astype(np.int32)
+    dev = "cuda"
+    ids = torch.as_tensor(ids_h).to(dev)
+    wts = torch.ones(N, F, device=dev)
+    table = torch.empty(X, ld, device=dev).uniform_(-0.01, 0.01)
+    D0 = 1 + F * d
+    ldz = (D0 + 3) // 4 * 4
+    z = torch.empty(N, ldz, device=dev)
+    dz = torch.empty(N, ldz, device=dev).uniform_(-1, 1)
+    y = (torch.rand(N, device=dev) < 0.05).float()
+    bias = torch.zeros(1, device=dev)
+    M = N * F
+    rows, pos = torch.empty(M, dtype=torch.int32, device=dev), torch.empty(M, dtype=torch.int32, device=dev)
+    sws = torch.empty(L.lib().dctr_sort_rows_workspace(M), dtype=torch.uint8, device=dev)
+    fws = torch.empty(L.lib().dctr_scatter_workspace(M, ld), dtype=torch.uint8, device=dev)
+    logit, pred, lossn, g = (torch.empty(N, device=dev) for _ in range(4))
+    s = torch.empty(N, ld, device=dev)
+    p = lambda t: t.data_ptr()
+    calls = {
+        "gather_concat_fwd": ("dctr_gather_concat_fwd", (p(ids), p(wts), p(table), X, ld, N, F, d, 0, 1, p(bias), 0, p(z), ldz, None)),
+        "fm_fwd": ("dctr_fm_fwd", (p(ids), p(wts), p(table), X, ld, N, F, d, p(bias), p(y), 1.0, p(logit), p(pred), p(lossn), p(g), p(s), ld, None)),
+        "sort_rows": ("dctr_sort_rows", (p(ids), M, X, p(rows), p(pos), p(sws), sws.numel(), None)),
+        "scatter_sgd[seq_decay]": ("dctr_scatter_sgd", (1, p(rows), p(pos), M, F, d, p(dz) + 4, ldz, d, p(wts), 1e-3, 0.9999, p(table), X, ld, p(fws), fws.numel(), None)),
+        "scatter_sgd[sum]": ("dctr_scatter_sgd", (0, p(rows), p(pos), M, F, d, p(dz) + 4, ldz, d, p(wts), 1e-3, 1.0, p(table), X, ld, p(fws), fws.numel(), None)),
+        "scatter_sgd_fm": ("dctr_scatter_sgd_fm", (p(rows), p(pos), M, F, d, p(g), p(s), ld, p(wts), 1e-3, 1.0, p(table), X, ld, p(fws), fws.numel(), None)),
+    }
+    pk = peaks()
+    out = {"N": N, "F": F, "d": d, "rows": X, "table_GB": round(X * ld * 4 / 1e9, 2), "peak_GBs": pk["hbm"], "kernels": {}}
+    for key, (name, a) in calls.items():
+        L.call(name, *a)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            L.call(name, *a)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        _, cost = call_cost(name, a)
+        gbs = cost / (ms * 1e-3) / 1e9
+        out["kernels"][key] = {"ms": round(ms, 4), "algorithmic_MB": round(cost / 1e6, 1), "GBs": round(gbs, 1), "frac": round(gbs / pk["hbm"], 4)}
+    return out
+
+
 def run_b200(args, rank, world):
     import torch
     import deepctr_b200
@@ -312,6 +365,10 @@ def run_b200(args, rank, world):
     if roof:
         out["roofline"] = roof
         out["kernels"] = kernels
+    if rank == 0 and world == 1 and not args.no_profile:
+        del flush, dpool
+        torch.cuda.empty_cache()
+        out["emb_roofline"] = emb_roofline()
     if rank == 0 and world == 1 and not args.no_cpu:
         out["cpu_baseline"] = cpu_baseline(wl, N, budget_s=12.0)
     if rank == 0:
@@ -408,9 +465,14 @@ def main():
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--emb-only", action="store_true", help="only run the embedding-kernel roofline sweep")
+    ap.add_argument("--emb-n", type=int, default=1 << 20)
+    ap.add_argument("--emb-reps", type=int, default=5)
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
-    if args.impl == "reference":
+    if args.emb_only:
+        print(json.dumps({"emb_roofline": emb_roofline(N=args.emb_n, reps=args.emb_reps)}))
+    elif args.impl == "reference":
         run_reference(args, rank, world)
     else:
         run_b200(args, rank, world)

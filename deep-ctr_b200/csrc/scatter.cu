@@ -32,6 +32,11 @@ struct FmSrc {
 
 // header of the workspace: [0] = number of long segments, [1] = number of chunk partials reserved
 struct LongSeg { int32_t start, len, chunk_off, pad; };
+// chunk length grows with the segment so that a segment never has more than 256 partials to compose
+__device__ __forceinline__ int chunk_len_of(int len) {
+    const int c = (len + 255) >> 8;
+    return c < DCTR_SEG_CHUNK ? DCTR_SEG_CHUNK : c;
+}
 
 __device__ __forceinline__ int64_t segment_end(const int32_t* __restrict__ rows, int64_t i, int64_t M, int32_t row) {
     // gallop then bisect: first index > i whose row differs
@@ -58,7 +63,7 @@ fold_short_kernel(Src src, const int32_t* __restrict__ rows, const int32_t* __re
     const int64_t end = segment_end(rows, i, M, row);
     const int len = (int)(end - i);
     if (len > DCTR_LONG_SEG) {
-        const int nchunks = (len + DCTR_SEG_CHUNK - 1) / DCTR_SEG_CHUNK;
+        const int nchunks = (len + chunk_len_of(len) - 1) / chunk_len_of(len);
         int slot = 0, coff = 0;
         if (gl == 0) {
             slot = atomicAdd(&hdr[0], 1);
@@ -101,8 +106,9 @@ fold_chunk_kernel(Src src, const int32_t* __restrict__ pos, int F, int d, float 
         const LongSeg ls = longs[chunk_seg[g]];
         const int j = g - ls.chunk_off;
         const float* trow = table + (int64_t)rows[ls.start] * ld;
-        const int64_t k0 = (int64_t)ls.start + (int64_t)j * DCTR_SEG_CHUNK;
-        const int64_t k1 = (k0 + DCTR_SEG_CHUNK < (int64_t)ls.start + ls.len) ? k0 + DCTR_SEG_CHUNK : (int64_t)ls.start + ls.len;
+        const int cl = chunk_len_of(ls.len);
+        const int64_t k0 = (int64_t)ls.start + (int64_t)j * cl;
+        const int64_t k1 = (k0 + cl < (int64_t)ls.start + ls.len) ? k0 + cl : (int64_t)ls.start + ls.len;
         float* out = partial + (int64_t)g * 2 * ld;
         for (int c = gl; c < d; c += kGroup) {
             const float old = trow[c];
@@ -130,11 +136,12 @@ fold_combine_kernel(int d, float lr, float decay, float* __restrict__ table, con
     const int groups_total = gridDim.x * (kFoldThreads / kGroup);
     for (int sidx = blockIdx.x * (kFoldThreads / kGroup) + threadIdx.x / kGroup; sidx < nlong; sidx += groups_total) {
         const LongSeg ls = longs[sidx];
-        const int nchunks = (ls.len + DCTR_SEG_CHUNK - 1) / DCTR_SEG_CHUNK;
+        const int nchunks = (ls.len + chunk_len_of(ls.len) - 1) / chunk_len_of(ls.len);
         float* trow = table + (int64_t)rows[ls.start] * ld;
         for (int c = gl; c < d; c += kGroup) {
             const float old = trow[c];
             float w = SEQ ? old : 0.f;
+#pragma unroll 8
             for (int j = 0; j < nchunks; ++j) {
                 const float* pj = partial + (int64_t)(ls.chunk_off + j) * 2 * ld;
                 w = SEQ ? fmaf(w, pj[ld + c], pj[c]) : w + pj[c];

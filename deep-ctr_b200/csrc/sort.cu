@@ -31,54 +31,70 @@ sort_hist_kernel(const int32_t* __restrict__ keys, int64_t M, int shift, int num
     hist[(int64_t)threadIdx.x * num_tiles + blockIdx.x] = h[threadIdx.x];
 }
 
-// exclusive scan of `total` int32 entries in place, one CTA of 1024 threads, fixed order
-__global__ void __launch_bounds__(1024) sort_scan_kernel(int32_t* __restrict__ data, int64_t total) {
+// one CTA per digit: exclusive scan of that digit's per-tile counts (in place, tile order) + the digit total.
+// The scatter kernel turns the 256 totals into digit base offsets itself, so the scan is parallel over digits.
+__global__ void __launch_bounds__(1024) sort_scan_kernel(int32_t* __restrict__ hist, int num_tiles, int32_t* __restrict__ totals) {
     __shared__ int32_t warp_tot[32];
-    const int tid = threadIdx.x;
-    const int64_t per = (total + 1023) / 1024;
-    const int64_t lo = tid * per;
-    const int64_t hi = lo + per < total ? lo + per : total;
-    int32_t sum = 0;
-    for (int64_t i = lo; i < hi; ++i) sum += data[i];
-    // block exclusive scan of `sum`
-    int32_t incl = sum;
-    const int lane = tid & 31, warp = tid >> 5;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        int32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
-    }
-    if (lane == 31) warp_tot[warp] = incl;
+    __shared__ int32_t carry_s;
+    int32_t* row = hist + (int64_t)blockIdx.x * num_tiles;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry_s = 0;
     __syncthreads();
-    if (warp == 0) {
-        int32_t w = warp_tot[lane];
-        int32_t wi = w;
+    for (int base = 0; base < num_tiles; base += 1024) {
+        const int i = base + tid;
+        const int32_t v = i < num_tiles ? row[i] : 0;
+        int32_t incl = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            int32_t v = __shfl_up_sync(0xffffffffu, wi, o);
-            if (lane >= o) wi += v;
+            const int32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += u;
         }
-        warp_tot[lane] = wi - w;
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            const int32_t w = warp_tot[lane];
+            int32_t wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int32_t u = __shfl_up_sync(0xffffffffu, wi, o);
+                if (lane >= o) wi += u;
+            }
+            warp_tot[lane] = wi - w;
+        }
+        __syncthreads();
+        const int32_t carry = carry_s;
+        if (i < num_tiles) row[i] = carry + warp_tot[warp] + incl - v;
+        __syncthreads();
+        if (tid == 1023) carry_s = carry + warp_tot[31] + incl;
+        __syncthreads();
     }
-    __syncthreads();
-    int32_t run = warp_tot[warp] + incl - sum;
-    for (int64_t i = lo; i < hi; ++i) {
-        const int32_t v = data[i];
-        data[i] = run;
-        run += v;
-    }
+    if (tid == 0) totals[blockIdx.x] = carry_s;
 }
 
 // pos_in == nullptr: payload is the element index itself (first pass)
 __global__ void __launch_bounds__(kSortThreads)
 sort_scatter_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict__ pos_in, int64_t M, int shift,
-                    int num_tiles, const int32_t* __restrict__ hist_scanned, int32_t* __restrict__ keys_out,
-                    int32_t* __restrict__ pos_out) {
+                    int num_tiles, const int32_t* __restrict__ hist_scanned, const int32_t* __restrict__ totals,
+                    int32_t* __restrict__ keys_out, int32_t* __restrict__ pos_out) {
     __shared__ unsigned short cnt[kSortChunks][kRadix];  // 32 KB: per-chunk digit counts -> exclusive prefix
     __shared__ int32_t gbase[kRadix];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < kSortChunks * kRadix / 2; i += kSortThreads) reinterpret_cast<uint32_t*>(&cnt[0][0])[i] = 0u;
-    gbase[tid] = hist_scanned[(int64_t)tid * num_tiles + blockIdx.x];
+    {   // digit base = exclusive scan of the 256 digit totals (one value per thread)
+        __shared__ int32_t wsum[8];
+        const int32_t t = totals[tid];
+        int32_t incl = t;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += u;
+        }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        int32_t off = 0;
+        for (int w = 0; w < warp; ++w) off += wsum[w];
+        gbase[tid] = off + incl - t + hist_scanned[(int64_t)tid * num_tiles + blockIdx.x];
+    }
     __syncthreads();
 
     const int64_t base = (int64_t)blockIdx.x * kSortTile;
@@ -133,7 +149,7 @@ extern "C" size_t dctr_sort_rows_workspace(int64_t M) {
     if (M <= 0) return 16;
     const int64_t tiles = (M + kSortTile - 1) / kSortTile;
     const int64_t m4 = (M + 3) / 4 * 4;
-    return (size_t)(2 * m4 + (int64_t)kRadix * tiles) * sizeof(int32_t);
+    return (size_t)(2 * m4 + (int64_t)kRadix * tiles + kRadix) * sizeof(int32_t);
 }
 
 extern "C" int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t* sorted_rows, int32_t* sorted_pos,
@@ -150,6 +166,7 @@ extern "C" int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t*
     int32_t* alt_keys = static_cast<int32_t*>(workspace);
     int32_t* alt_pos = alt_keys + m4;
     int32_t* hist = alt_pos + m4;
+    int32_t* totals = hist + (int64_t)kRadix * tiles;
     cudaStream_t st = as_stream(stream);
     const int passes = num_passes(X);
     const int32_t* kin = ids;
@@ -162,10 +179,10 @@ extern "C" int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t*
         sort_hist_kernel<<<tiles, kSortThreads, 0, st>>>(kin, M, shift, tiles, hist);
         int rc = check_launch("sort_hist_kernel");
         if (rc) return rc;
-        sort_scan_kernel<<<1, 1024, 0, st>>>(hist, (int64_t)kRadix * tiles);
+        sort_scan_kernel<<<kRadix, 1024, 0, st>>>(hist, tiles, totals);
         rc = check_launch("sort_scan_kernel");
         if (rc) return rc;
-        sort_scatter_kernel<<<tiles, kSortThreads, 0, st>>>(kin, pin, M, shift, tiles, hist, kout, pout);
+        sort_scatter_kernel<<<tiles, kSortThreads, 0, st>>>(kin, pin, M, shift, tiles, hist, totals, kout, pout);
         rc = check_launch("sort_scatter_kernel");
         if (rc) return rc;
         kin = kout;
