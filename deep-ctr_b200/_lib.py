@@ -14,7 +14,7 @@ CROSS = {"none": 0, None: 0, "ip": 1, "op": 2}
 SCATTER_SUM, SCATTER_SEQ_DECAY = 0, 1
 GEMM_NN, GEMM_NT, GEMM_TN = 0, 1, 2
 EPI_NONE, EPI_FWD, EPI_DGRAD = 0, 1, 2
-LONG_SEG, SEG_CHUNK = 32, 32
+FOLD_CHUNK, FOLD_TILE = 8, 512
 
 _p, _i, _l, _f, _z = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float, ctypes.c_size_t
 

@@ -56,6 +56,59 @@ __device__ __forceinline__ float xent_logits(float z, float y) {
 }
 
 __device__ __forceinline__ float4 ldg_f4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+// "Issue" loads: volatile asm keeps them in program order relative to each other.  ptxas otherwise sinks every
+// load to its first use and serialises a batch of independent gathers; callers issue a batch of these and then
+// consume the LAST-issued value first, which forces the whole batch to be in flight before any use.
+__device__ __forceinline__ float4 ldg_f4_issue(const float* p) {
+    float4 v;
+    asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+
+// ids / weights of 8 consecutive fields [f0, f0+8) of one sample (row-major [N, F] arrays, pbase = n*F); slots past F
+// get id 0 / weight 0.  `vec`: F % 4 == 0 and 16-byte aligned arrays, so the 8 values are two 128-bit loads.
+__device__ __forceinline__ void load_fields8(const int32_t* __restrict__ ids, const float* __restrict__ wts, int64_t pbase,
+                                             int f0, int F, bool vec, int (&id)[8], float (&w)[8]) {
+    if (vec && f0 + 8 <= F) {
+        const int4 a = __ldg(reinterpret_cast<const int4*>(ids + pbase + f0)), b = __ldg(reinterpret_cast<const int4*>(ids + pbase + f0) + 1);
+        id[0] = a.x; id[1] = a.y; id[2] = a.z; id[3] = a.w; id[4] = b.x; id[5] = b.y; id[6] = b.z; id[7] = b.w;
+        if (wts) {
+            const float4 c = __ldg(reinterpret_cast<const float4*>(wts + pbase + f0)), e = __ldg(reinterpret_cast<const float4*>(wts + pbase + f0) + 1);
+            w[0] = c.x; w[1] = c.y; w[2] = c.z; w[3] = c.w; w[4] = e.x; w[5] = e.y; w[6] = e.z; w[7] = e.w;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) w[k] = 1.f;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const bool ok = f0 + k < F;
+            id[k] = ok ? __ldg(ids + pbase + f0 + k) : 0;
+            w[k] = ok ? (wts ? __ldg(wts + pbase + f0 + k) : 1.f) : 0.f;
+        }
+    }
+}
+
+__device__ __forceinline__ float4 ld_f4_issue(const float* p, bool pred) {      // plain (coherent) load, predicated
+    float4 v;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %5, 0;\n\tmov.f32 %0, 0f00000000;\n\tmov.f32 %1, 0f00000000;\n\t"
+                 "mov.f32 %2, 0f00000000;\n\tmov.f32 %3, 0f00000000;\n\t@p ld.global.v4.f32 {%0,%1,%2,%3}, [%4];\n\t}"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p), "r"((int)pred));
+    return v;
+}
+__device__ __forceinline__ float4 ldg_f4_issue(const float* p, bool pred) {
+    float4 v;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %5, 0;\n\tmov.f32 %0, 0f00000000;\n\tmov.f32 %1, 0f00000000;\n\t"
+                 "mov.f32 %2, 0f00000000;\n\tmov.f32 %3, 0f00000000;\n\t@p ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];\n\t}"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p), "r"((int)pred));
+    return v;
+}
+__device__ __forceinline__ float ldg_f_issue(const float* p, bool pred) {
+    float v;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %2, 0;\n\tmov.f32 %0, 0f00000000;\n\t@p ld.global.nc.f32 %0, [%1];\n\t}"
+                 : "=f"(v) : "l"(p), "r"((int)pred));
+    return v;
+}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

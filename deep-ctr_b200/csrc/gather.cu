@@ -1,10 +1,9 @@
 // K1 / K2 / K3: per-field embedding gather + concat with the inner- / outer-product layer fused in,
 // and the backward of that layer into a per-(sample, field) gradient buffer.
 //
-// One warp owns one sample.  The F rows of the sample ("field block") are fetched with 128-bit loads
-// (row stride ld is a multiple of 4 floats, so a row is ld/4 LDG.128), scaled by the field weight and
-// staged in shared memory; the concat / IP / OP outputs are then produced from the staged block and
-// written with warp-coalesced stores.  HBM-bound: no tensor cores here by design.
+// Rows are fetched with 128-bit loads (row stride ld is a multiple of 4 floats, so a row is ld/4 LDG.128), scaled
+// by the field weight and staged in shared memory; the concat / IP / OP outputs are produced from the staged
+// block and written with warp-coalesced 128-bit stores.  HBM-bound: no tensor cores here by design.
 #include "common.cuh"
 
 namespace dctr {
@@ -30,20 +29,30 @@ __device__ __forceinline__ void stage_field_block(const int32_t* __restrict__ id
     __syncwarp();
 }
 
+// Forward: a warp owns 8 consecutive samples at a time.  A 4-lane group gathers one sample -- lane q reads float4
+// q of each of the F rows (F independent 128-bit loads in flight per lane) -- and scatters the scaled values
+// into the warp's shared-memory image of the 8 output rows, already in concat order.  The inner- / outer-product
+// columns are then formed from that image by all 32 lanes, and the image (8 * ldz contiguous floats, also
+// contiguous in global memory) leaves with coalesced 128-bit stores, the input activation applied on the way.
+constexpr int kSamplesPerWarp = 8;
+
 template <int CROSS>
 __global__ void __launch_bounds__(kGatherWarps * 32)
 gather_concat_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
                      const float* __restrict__ table, int ld, int N, int F, int d, int bias_first,
-                     const float* __restrict__ bias, int act0, float* __restrict__ out, int ldz) {
+                     const float* __restrict__ bias, int act0, float* __restrict__ out, int ldz, int warps, int vec) {
     extern __shared__ __align__(16) float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float* e = smem + warp * F * ld;
+    const int q = lane & 3, g = lane >> 2;
     const int Fd = F * d;
     const int P = F * (F - 1) / 2;
     const int crossw = CROSS == DCTR_CROSS_IP ? P : (CROSS == DCTR_CROSS_OP ? d * d : 0);
     const int D0 = Fd + crossw + 1;
+    const int eoff = bias_first ? 1 : 0;
+    const int Q = ld >> 2, ldz4 = ldz >> 2;
+    float* zs = smem + (size_t)warp * kSamplesPerWarp * ldz;
     // pair table (i<<8 | j), i-outer / j-inner: the order of FNN_IP_L3.py:91-94
-    unsigned short* pairs = reinterpret_cast<unsigned short*>(smem + kGatherWarps * F * ld);
+    unsigned short* pairs = reinterpret_cast<unsigned short*>(smem + (size_t)warps * kSamplesPerWarp * ldz);
     if (CROSS == DCTR_CROSS_IP) {
         for (int i = threadIdx.x; i < F - 1; i += blockDim.x) {
             int base = i * F - i * (i + 1) / 2 - i - 1;
@@ -51,40 +60,89 @@ gather_concat_kernel(const int32_t* __restrict__ ids, const float* __restrict__ 
         }
         __syncthreads();
     }
-    const float bval = act_fwd(act0, bias ? __ldg(bias) : 0.f);
+    const float bval = bias ? __ldg(bias) : 0.f;
 
-    for (int64_t n = (int64_t)blockIdx.x * kGatherWarps + warp; n < N; n += (int64_t)gridDim.x * kGatherWarps) {
-        stage_field_block(ids, wts, table, ld, F, n, lane, e);
-        float* row = out + n * (int64_t)ldz;
-        const int eoff = bias_first ? 1 : 0;
-        for (int t = lane; t < Fd; t += 32) {
-            const int f = t / d;
-            const int c = t - f * d;
-            row[eoff + t] = act_fwd(act0, e[f * ld + c]);
-        }
-        if (CROSS == DCTR_CROSS_IP) {
-            for (int t = lane; t < P; t += 32) {
-                const int ij = pairs[t];
-                const float* ei = e + (ij >> 8) * ld;
-                const float* ej = e + (ij & 255) * ld;
-                float acc = 0.f;
-                for (int c = 0; c < d; ++c) acc = fmaf(ei[c], ej[c], acc);
-                row[Fd + t] = act_fwd(act0, acc);
+    for (int64_t n0 = ((int64_t)blockIdx.x * warps + warp) * kSamplesPerWarp; n0 < N;
+         n0 += (int64_t)gridDim.x * warps * kSamplesPerWarp) {
+        const int cnt = (int)min((int64_t)kSamplesPerWarp, (int64_t)N - n0);
+        float* zr = zs + g * ldz;
+        if (g < cnt) {
+            const int64_t pbase = (n0 + g) * F;
+            for (int qq = q; qq < Q; qq += 4) {
+                const int c0 = qq * 4;
+                for (int f0 = 0; f0 < F; f0 += 8) {
+                    int id[8]; float w[8]; float4 v[8];
+                    load_fields8(ids, wts, pbase, f0, F, vec, id, w);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) v[k] = ldg_f4_issue(table + (int64_t)id[k] * ld + c0);
+#pragma unroll
+                    for (int k = 7; k >= 0; --k) {         // last-issued load first (common.cuh)
+                        if (f0 + k < F) {
+                            float* dst = zr + eoff + (f0 + k) * d + c0;
+                            if (c0 < d) dst[0] = v[k].x * w[k];
+                            if (c0 + 1 < d) dst[1] = v[k].y * w[k];
+                            if (c0 + 2 < d) dst[2] = v[k].z * w[k];
+                            if (c0 + 3 < d) dst[3] = v[k].w * w[k];
+                        }
+                    }
+                }
             }
+            if (q == 3) {
+                zr[bias_first ? 0 : Fd + crossw] = bval;
+                for (int c = D0; c < ldz; ++c) zr[c] = 0.f;
+            }
+        }
+        __syncwarp();
+        if (CROSS == DCTR_CROSS_IP) {
+            for (int s = 0; s < cnt; ++s) {
+                const float* e = zs + s * ldz;
+                for (int t = lane; t < P; t += 32) {
+                    const int ij = pairs[t];
+                    const float* ei = e + (ij >> 8) * d;
+                    const float* ej = e + (ij & 255) * d;
+                    float acc = 0.f;
+                    for (int c = 0; c < d; ++c) acc = fmaf(ei[c], ej[c], acc);
+                    zs[s * ldz + Fd + t] = acc;
+                }
+            }
+            __syncwarp();
         } else if (CROSS == DCTR_CROSS_OP) {
             // q[a,b] = sum_j prefix_{<j}[a] * e_j[b]   (== sum_{i<j} e_i[a] e_j[b], FNN_OP_L3.py:93-97)
-            for (int t = lane; t < crossw; t += 32) {
-                const int a = t / d, b = t - a * d;
-                float acc = 0.f, pre = 0.f;
-                for (int j = 0; j < F; ++j) {
-                    acc = fmaf(pre, e[j * ld + b], acc);
-                    pre += e[j * ld + a];
+            for (int s = 0; s < cnt; ++s) {
+                const float* e = zs + s * ldz;
+                for (int t = lane; t < crossw; t += 32) {
+                    const int a = t / d, b = t - a * d;
+                    float acc = 0.f, pre = 0.f;
+                    for (int j = 0; j < F; ++j) {
+                        acc = fmaf(pre, e[j * d + b], acc);
+                        pre += e[j * d + a];
+                    }
+                    zs[s * ldz + Fd + t] = acc;
                 }
-                row[Fd + t] = act_fwd(act0, acc);
+            }
+            __syncwarp();
+        }
+        // the image is cnt * ldz contiguous floats both here and in global memory
+        float4* dst = reinterpret_cast<float4*>(out + n0 * (int64_t)ldz);
+        const float4* src = reinterpret_cast<const float4*>(zs);
+        const int total4 = cnt * ldz4;
+        if (act0 == DCTR_ACT_NONE) {
+            for (int i = lane; i < total4; i += 32) dst[i] = src[i];
+        } else {
+            int col4 = lane;                   // float4 column inside the row, tracked incrementally
+            while (col4 >= ldz4) col4 -= ldz4;
+            for (int i = lane; i < total4; i += 32) {
+                float4 v = src[i];
+                const int c = col4 * 4;
+                v.x = c < D0 ? act_fwd(act0, v.x) : 0.f;
+                v.y = c + 1 < D0 ? act_fwd(act0, v.y) : 0.f;
+                v.z = c + 2 < D0 ? act_fwd(act0, v.z) : 0.f;
+                v.w = c + 3 < D0 ? act_fwd(act0, v.w) : 0.f;
+                dst[i] = v;
+                col4 += 32;
+                while (col4 >= ldz4) col4 -= ldz4;
             }
         }
-        if (lane == 0) row[bias_first ? 0 : Fd + crossw] = bval;
-        for (int c = D0 + lane; c < ldz; c += 32) row[c] = 0.f;
         __syncwarp();
     }
 }
@@ -170,16 +228,27 @@ extern "C" int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, cons
     DCTR_REQUIRE(ldz >= F * d + crossw + 1, "gather_concat_fwd: ldz=%d < D0=%d", ldz, F * d + crossw + 1);
     DCTR_REQUIRE(X > 0 && X * (int64_t)ld < ((int64_t)1 << 40), "gather_concat_fwd: bad X");
     if (N == 0) return DCTR_OK;
-    size_t smem = (size_t)kGatherWarps * F * ld * sizeof(float) + (cross == DCTR_CROSS_IP ? (size_t)crossw * 2 + 16 : 0);
-    DCTR_REQUIRE(smem <= 200 * 1024, "gather_concat_fwd: field block too large for shared memory");
-    dim3 grid(gather_grid(N)), block(kGatherWarps * 32);
+    DCTR_REQUIRE((ldz & 3) == 0 && ((uintptr_t)out & 15) == 0 && ((uintptr_t)table & 15) == 0,
+                 "gather_concat_fwd: out / table must be 16-byte aligned and ldz a multiple of 4");
+    // shared memory: one image of 8 output rows per warp; fewer warps per CTA when the rows are wide
+    const size_t per_warp = (size_t)kSamplesPerWarp * ldz * sizeof(float);
+    const size_t extra = cross == DCTR_CROSS_IP ? (size_t)crossw * 2 + 16 : 0;
+    int warps = kGatherWarps;
+    while (warps > 1 && warps * per_warp + extra > 96 * 1024) warps >>= 1;
+    const size_t smem = warps * per_warp + extra;
+    DCTR_REQUIRE(smem <= 200 * 1024, "gather_concat_fwd: output row too wide for shared memory (ldz=%d)", ldz);
+    int blocks = ceil_div(N, warps * kSamplesPerWarp);
+    const int cap = kNumSMs * (smem > 48 * 1024 ? 2 : 4);
+    if (blocks > cap) blocks = cap;
+    dim3 grid(blocks), block(warps * 32);
     cudaStream_t st = as_stream(stream);
+    const int vec = (F & 3) == 0 && ((uintptr_t)ids & 15) == 0 && (!wts || ((uintptr_t)wts & 15) == 0);
 #define LAUNCH_G(C)                                                                                          \
     do {                                                                                                     \
         if (smem > 48 * 1024)                                                                                \
             cudaFuncSetAttribute(gather_concat_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         gather_concat_kernel<C><<<grid, block, smem, st>>>(ids, wts, table, ld, N, F, d, bias_first, bias,   \
-                                                           act0, out, ldz);                                  \
+                                                           act0, out, ldz, warps, vec);                      \
     } while (0)
     if (cross == DCTR_CROSS_IP) LAUNCH_G(DCTR_CROSS_IP);
     else if (cross == DCTR_CROSS_OP) LAUNCH_G(DCTR_CROSS_OP);

@@ -1,154 +1,292 @@
 // K6b: deterministic segmented fold + SGD into the touched embedding rows only.
-// Input is the row-sorted (row, position) list from sort.cu.  Equal rows form a segment whose elements
-// are in (sample, field) order.  A 16-lane group owns one sorted index; the group at a segment head folds
-// the segment, lane c owning component c, so a row is read and written exactly once and the summation
-// order is fixed.  Segments longer than DCTR_LONG_SEG (hot rows: Zipf heads, the 13 Criteo numeric rows
-// that every sample touches) are cut into chunks of DCTR_SEG_CHUNK, folded chunk-parallel into affine
-// partials (A, B) and then composed in chunk order -- still deterministic.
-//   SUM (TF semantics, FNN.py:46-49):          row = row*decay - lr * sum_k grad_k
-//   SEQ_DECAY (Theano, FNN_wnzh.py:300-306):   for k in order: row = row*decay - lr*grad_k
+//
+// Input is the row-sorted (row, position) list from sort.cu: equal rows form a segment whose elements are in
+// (sample, field) order.  The fold is FLAT over the sorted list -- the work per launch does not depend on how
+// the list splits into segments (Zipf heads and the Criteo numeric rows that every sample touches cost the
+// same per element as singletons):
+//
+//   level 0  a 4-lane group owns DCTR_FOLD_CHUNK = 8 consecutive sorted elements; lane q owns one float4 of the
+//            row.  All 8 gradient gathers (random 44-48 B reads) and the old rows of the segments that END in
+//            the chunk are issued up front (16 independent 128-bit loads per lane), then the chunk is folded
+//            serially in list order.  A segment that starts and ends inside the chunk is written straight to
+//            the table (one read-modify-write per touched row).
+//   level 1  pieces that cross chunk borders are parked in shared memory as partials (P, Q) and composed in
+//            group order by the group that holds the segment head (CTA tile = 64 groups = 512 elements).
+//   level 2  pieces that cross tile borders leave the CTA as one carry-in and one carry-out partial per tile;
+//            fold_stitch_kernel walks them in tile order and writes the row.
+//
+// Every composition happens in list order with a fixed association, so two runs are bit-identical and no float
+// atomics are used.  Partials are per-mode:
+//   SUM  (TF, FNN.py:46-49 densified gradient + SGD)      Q = sum g                    row = row*decay - lr*Q
+//   SEQ  (Theano, FNN_wnzh.py:300-306, per occurrence)    w -> w*decay - lr*g composed as w -> P*w + Q
+//   FM   (FM.py:55-64 differentiated)          Q = sum gn*x*s, P = sum gn*x^2  row = row*decay - lr*(Q - P*row)
 #include "common.cuh"
 
 namespace dctr {
 
-constexpr int kGroup = 16;          // lanes per sorted element
-constexpr int kFoldThreads = 256;   // 16 groups per CTA
+constexpr int kC = DCTR_FOLD_CHUNK;            // sorted elements per group
+constexpr int kG = 4;                          // lanes per group
+constexpr int kFoldThreads = 256;
+constexpr int kGroups = kFoldThreads / kG;     // 64 groups per CTA
+constexpr int kTile = kGroups * kC;            // 512 sorted elements per CTA
+constexpr int kSlab = 4 * kG;                  // 16 table columns per launch
+static_assert(kTile == DCTR_FOLD_TILE, "dctr.h out of sync");
 
-struct DenseSrc {
-    const float* g; int64_t ld_n; int ld_f; const float* wts;
-    __device__ __forceinline__ float operator()(int p, int n, int f, int c, float) const {
-        const float v = g[n * ld_n + (int64_t)f * ld_f + c];
-        return wts ? wts[p] * v : v;
-    }
+enum { kSum = 0, kSeq = 1, kFm = 2 };
+enum { kHasF = 1, kFClosed = 2, kHasL = 4 };
+enum { kInValid = 1, kInClosed = 2 };
+
+struct FoldArgs {
+    const int32_t* rows; const int32_t* pos; int64_t M;
+    int F; uint64_t fmul;          // n = p / F  ==  (p * fmul) >> 40 when fmul != 0 (F < 512, p < 2^31)
+    int d, ld, col0;
+    float lr, decay;
+    float* table;
+    // gradient source: dense g[n*ld_n + f*ld_f + c] (* wts[p]); FM: g[n], s[n*ld_f + c], x = wts[p]
+    const float* g; const float* s; int64_t ld_n; int ld_f; const float* wts;
+    // per-tile carries
+    float* in_q; float* out_q; float* in_p; float* out_p; int32_t* in_flag; int32_t* out_row;
 };
-struct FmSrc {
-    const float* g; const float* s; int lds; const float* wts;
-    __device__ __forceinline__ float operator()(int p, int n, int, int c, float old) const {
-        const float x = wts ? wts[p] : 1.f;
-        const float gn = g[n];
-        return c == 0 ? gn * x : gn * (x * s[(int64_t)n * lds + c] - x * x * old);
-    }
-};
 
-// header of the workspace: [0] = number of long segments, [1] = number of chunk partials reserved
-struct LongSeg { int32_t start, len, chunk_off, pad; };
-// chunk length grows with the segment so that a segment never has more than 256 partials to compose
-__device__ __forceinline__ int chunk_len_of(int len) {
-    const int c = (len + 255) >> 8;
-    return c < DCTR_SEG_CHUNK ? DCTR_SEG_CHUNK : c;
+template <int MODE> __device__ __forceinline__ float p_identity() { return MODE == kSeq ? 1.f : 0.f; }
+
+template <int MODE>
+__device__ __forceinline__ void fold_elem(float& P, float4& Q, const float4& e, float v, float lr, float decay) {
+    if (MODE == kSeq) {
+        P *= decay;
+        Q.x = fmaf(Q.x, decay, -lr * e.x); Q.y = fmaf(Q.y, decay, -lr * e.y);
+        Q.z = fmaf(Q.z, decay, -lr * e.z); Q.w = fmaf(Q.w, decay, -lr * e.w);
+    } else {
+        if (MODE == kFm) P += v;
+        Q.x += e.x; Q.y += e.y; Q.z += e.z; Q.w += e.w;
+    }
+}
+// (P, Q) followed in list order by (P2, Q2)
+template <int MODE>
+__device__ __forceinline__ void fold_combine(float& P, float4& Q, float P2, const float4& Q2) {
+    if (MODE == kSeq) {
+        Q.x = fmaf(Q.x, P2, Q2.x); Q.y = fmaf(Q.y, P2, Q2.y); Q.z = fmaf(Q.z, P2, Q2.z); Q.w = fmaf(Q.w, P2, Q2.w);
+        P *= P2;
+    } else {
+        if (MODE == kFm) P += P2;
+        Q.x += Q2.x; Q.y += Q2.y; Q.z += Q2.z; Q.w += Q2.w;
+    }
+}
+template <int MODE>
+__device__ __forceinline__ float4 fold_final(const float4& old, float P, const float4& Q, int c0, float lr, float decay) {
+    float4 r;
+    if (MODE == kSeq) {
+        r.x = fmaf(P, old.x, Q.x); r.y = fmaf(P, old.y, Q.y); r.z = fmaf(P, old.z, Q.z); r.w = fmaf(P, old.w, Q.w);
+    } else if (MODE == kFm) {
+        const float gx = c0 == 0 ? Q.x : fmaf(-P, old.x, Q.x);     // component 0 is the linear weight: grad = gn*x
+        r.x = fmaf(old.x, decay, -lr * gx);
+        r.y = fmaf(old.y, decay, -lr * fmaf(-P, old.y, Q.y));
+        r.z = fmaf(old.z, decay, -lr * fmaf(-P, old.z, Q.z));
+        r.w = fmaf(old.w, decay, -lr * fmaf(-P, old.w, Q.w));
+    } else {
+        r.x = fmaf(old.x, decay, -lr * Q.x); r.y = fmaf(old.y, decay, -lr * Q.y);
+        r.z = fmaf(old.z, decay, -lr * Q.z); r.w = fmaf(old.w, decay, -lr * Q.w);
+    }
+    return r;
 }
 
-__device__ __forceinline__ int64_t segment_end(const int32_t* __restrict__ rows, int64_t i, int64_t M, int32_t row) {
-    // gallop then bisect: first index > i whose row differs
-    int64_t step = 1;
-    while (i + step < M && rows[i + step] == row) step <<= 1;
-    int64_t lo = i + (step >> 1), hi = (i + step < M) ? i + step : M;   // rows[lo]==row, rows[hi]!=row or hi==M
-    while (hi - lo > 1) {
-        const int64_t mid = (lo + hi) >> 1;
-        if (rows[mid] == row) lo = mid; else hi = mid;
+__device__ __forceinline__ float4 mask_cols(float4 v, int c0, int d) {
+    if (c0 + 3 >= d) {
+        if (c0 >= d) v.x = 0.f;
+        if (c0 + 1 >= d) v.y = 0.f;
+        if (c0 + 2 >= d) v.z = 0.f;
+        v.w = 0.f;
     }
-    return hi;
+    return v;
 }
 
-template <bool SEQ, class Src>
-__global__ void __launch_bounds__(kFoldThreads)
-fold_short_kernel(Src src, const int32_t* __restrict__ rows, const int32_t* __restrict__ pos, int64_t M, int F, int d,
-                  float lr, float decay, float* __restrict__ table, int ld, int32_t* __restrict__ hdr, LongSeg* __restrict__ longs,
-                  int32_t* __restrict__ chunk_seg) {
-    const int64_t i = ((int64_t)blockIdx.x * kFoldThreads + threadIdx.x) / kGroup;
-    const int gl = threadIdx.x & (kGroup - 1);
-    if (i >= M) return;
-    const int32_t row = rows[i];
-    if (i > 0 && rows[i - 1] == row) return;   // not a segment head
-    const int64_t end = segment_end(rows, i, M, row);
-    const int len = (int)(end - i);
-    if (len > DCTR_LONG_SEG) {
-        const int nchunks = (len + chunk_len_of(len) - 1) / chunk_len_of(len);
-        int slot = 0, coff = 0;
-        if (gl == 0) {
-            slot = atomicAdd(&hdr[0], 1);
-            coff = atomicAdd(&hdr[1], nchunks);
-            LongSeg ls; ls.start = (int32_t)i; ls.len = len; ls.chunk_off = coff; ls.pad = 0;
-            longs[slot] = ls;   // slot order is arbitrary; every segment is folded independently
+template <int MODE, bool ALIGNED>
+__global__ void __launch_bounds__(kFoldThreads, 2)
+fold_tile_kernel(const FoldArgs a) {
+    __shared__ float4 sQF[kFoldThreads], sQL[kFoldThreads];
+    __shared__ float sPF[kFoldThreads], sPL[kFoldThreads];
+    __shared__ int sFlag[kGroups];
+    const int tid = threadIdx.x, q = tid & (kG - 1), grp = tid >> 2;
+    const int c0 = a.col0 + 4 * q;
+    const bool lane_on = c0 < a.ld;
+    const int64_t tile = blockIdx.x;
+    const int64_t k0 = (tile * kGroups + grp) * kC;
+
+    // ---- the chunk's (row, position) pairs and its two neighbours ----
+    int r[kC], p[kC];
+    if (k0 + kC <= a.M) {
+        const int4 r0 = __ldg(reinterpret_cast<const int4*>(a.rows + k0)), r1 = __ldg(reinterpret_cast<const int4*>(a.rows + k0) + 1);
+        const int4 p0 = __ldg(reinterpret_cast<const int4*>(a.pos + k0)), p1 = __ldg(reinterpret_cast<const int4*>(a.pos + k0) + 1);
+        r[0] = r0.x; r[1] = r0.y; r[2] = r0.z; r[3] = r0.w; r[4] = r1.x; r[5] = r1.y; r[6] = r1.z; r[7] = r1.w;
+        p[0] = p0.x; p[1] = p0.y; p[2] = p0.z; p[3] = p0.w; p[4] = p1.x; p[5] = p1.y; p[6] = p1.z; p[7] = p1.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < kC; ++j) {
+            const bool ok = k0 + j < a.M;
+            r[j] = ok ? __ldg(a.rows + k0 + j) : -1;
+            p[j] = ok ? __ldg(a.pos + k0 + j) : 0;
         }
-        const unsigned gmask = 0xffffu << (threadIdx.x & 16);
-        slot = __shfl_sync(gmask, slot, 0, kGroup);
-        coff = __shfl_sync(gmask, coff, 0, kGroup);
-        for (int j = gl; j < nchunks; j += kGroup) chunk_seg[coff + j] = slot;   // chunk -> owning long segment
-        return;
     }
-    float* trow = table + (int64_t)row * ld;
-    for (int c = gl; c < d; c += kGroup) {
-        const float old = trow[c];
-        float w = SEQ ? old : 0.f;
-#pragma unroll 4
-        for (int64_t k = i; k < end; ++k) {
-            const int p = pos[k];
-            const int n = p / F;
-            const float gk = src(p, n, p - n * F, c, old);
-            w = SEQ ? fmaf(w, decay, -lr * gk) : w + gk;
-        }
-        trow[c] = SEQ ? w : fmaf(old, decay, -lr * w);
+    const int prev = (k0 > 0 && k0 <= a.M) ? __ldg(a.rows + k0 - 1) : -1;
+    const int next = (k0 + kC < a.M) ? __ldg(a.rows + k0 + kC) : -1;
+    unsigned head = 0, tail = 0, valid = 0;
+#pragma unroll
+    for (int j = 0; j < kC; ++j) {
+        const bool ok = r[j] >= 0;
+        valid |= (unsigned)ok << j;
+        head |= (unsigned)(ok && r[j] != (j ? r[j - 1] : prev)) << j;
+        tail |= (unsigned)(ok && r[j] != (j < kC - 1 ? r[j + 1] : next)) << j;
     }
-}
 
-// one 16-lane group per chunk of a long segment: partial[chunk][c] = B, partial[chunk][ld + c] = A
-template <bool SEQ, class Src>
-__global__ void __launch_bounds__(kFoldThreads)
-fold_chunk_kernel(Src src, const int32_t* __restrict__ pos, int F, int d, float lr, float decay,
-                  const float* __restrict__ table, const int32_t* __restrict__ rows, int ld,
-                  const int32_t* __restrict__ hdr, const LongSeg* __restrict__ longs,
-                  const int32_t* __restrict__ chunk_seg, float* __restrict__ partial) {
-    const int total_chunks = hdr[1];
-    const int gl = threadIdx.x & (kGroup - 1);
-    const int groups_total = gridDim.x * (kFoldThreads / kGroup);
-    for (int g = blockIdx.x * (kFoldThreads / kGroup) + threadIdx.x / kGroup; g < total_chunks; g += groups_total) {
-        const LongSeg ls = longs[chunk_seg[g]];
-        const int j = g - ls.chunk_off;
-        const float* trow = table + (int64_t)rows[ls.start] * ld;
-        const int cl = chunk_len_of(ls.len);
-        const int64_t k0 = (int64_t)ls.start + (int64_t)j * cl;
-        const int64_t k1 = (k0 + cl < (int64_t)ls.start + ls.len) ? k0 + cl : (int64_t)ls.start + ls.len;
-        float* out = partial + (int64_t)g * 2 * ld;
-        for (int c = gl; c < d; c += kGroup) {
-            const float old = trow[c];
-            float a = 1.f, b = 0.f;
-#pragma unroll 4
-            for (int64_t k = k0; k < k1; ++k) {
-                const int p = pos[k];
-                const int n = p / F;
-                const float gk = src(p, n, p - n * F, c, old);
-                if (SEQ) { b = fmaf(b, decay, -lr * gk); a *= decay; } else { b += gk; }
+    // ---- issue every gather of the chunk before folding: 8 gradient reads + the old rows of the closing segments ----
+    // (issued in reverse list order with "issue" loads, so the fold -- which starts with element 0, the last one
+    // issued -- cannot begin before all 16 gathers are in flight; see common.cuh)
+    float4 e[kC], old[kC];
+    float v[kC], w[kC], gn[kC];
+#pragma unroll
+    for (int j = kC - 1; j >= 0; --j)
+        old[j] = ld_f4_issue(a.table + (int64_t)(r[j] < 0 ? 0 : r[j]) * a.ld + c0,
+                             lane_on && ((tail >> j & 1) || (j == kC - 1 && (valid >> j & 1))));
+#pragma unroll
+    for (int j = kC - 1; j >= 0; --j) {
+        const bool on = lane_on && (valid >> j & 1);
+        const uint32_t pj = (uint32_t)p[j];
+        const uint32_t n = a.fmul ? (uint32_t)(((uint64_t)pj * a.fmul) >> 40) : pj / (uint32_t)a.F;
+        w[j] = a.wts ? ldg_f_issue(a.wts + pj, on) : 1.f;
+        if (MODE == kFm) {
+            gn[j] = ldg_f_issue(a.g + n, on);
+            e[j] = ldg_f4_issue(a.s + (int64_t)n * a.ld_f + c0, on);
+        } else {
+            const uint32_t f = pj - n * (uint32_t)a.F;
+            const float* src = a.g + (int64_t)n * a.ld_n + (int64_t)f * a.ld_f + c0;
+            if (ALIGNED) {
+                e[j] = ldg_f4_issue(src, on);
+            } else {
+                e[j].w = ldg_f_issue(src + 3, on && c0 + 3 < a.d);
+                e[j].z = ldg_f_issue(src + 2, on && c0 + 2 < a.d);
+                e[j].y = ldg_f_issue(src + 1, on && c0 + 1 < a.d);
+                e[j].x = ldg_f_issue(src, on && c0 < a.d);
             }
-            out[c] = b;
-            out[ld + c] = a;
         }
+    }
+#pragma unroll
+    for (int j = 0; j < kC; ++j) {
+        if (MODE == kFm) {
+            const float gx = gn[j] * w[j];
+            float4 s4 = e[j];
+            if (c0 == 0) s4.x = 1.f;
+            e[j] = mask_cols(make_float4(gx * s4.x, gx * s4.y, gx * s4.z, gx * s4.w), c0, a.d);
+            v[j] = gx * w[j];
+        } else {
+            const float4 g4 = mask_cols(e[j], c0, a.d);
+            e[j] = make_float4(g4.x * w[j], g4.y * w[j], g4.z * w[j], g4.w * w[j]);
+            v[j] = 0.f;
+        }
+    }
+
+    // ---- serial fold of the chunk in list order ----
+    float P = p_identity<MODE>(), PF = 0.f, PL = 0.f;
+    float4 Q = make_float4(0.f, 0.f, 0.f, 0.f), QF = Q, QL = Q, oldL = Q;
+    bool open_left = (valid & 1) && !(head & 1);
+    int flag = 0, rowL = -1;
+#pragma unroll
+    for (int j = 0; j < kC; ++j) {
+        if (valid >> j & 1) {
+            if (head >> j & 1) { P = p_identity<MODE>(); Q = make_float4(0.f, 0.f, 0.f, 0.f); open_left = false; }
+            fold_elem<MODE>(P, Q, e[j], v[j], a.lr, a.decay);
+            if (tail >> j & 1) {
+                if (!open_left) {
+                    if (lane_on)
+                        *reinterpret_cast<float4*>(a.table + (int64_t)r[j] * a.ld + c0) = fold_final<MODE>(old[j], P, Q, c0, a.lr, a.decay);
+                } else {
+                    PF = P; QF = Q; flag |= kHasF | kFClosed;
+                }
+            } else if (j == kC - 1) {
+                if (open_left) { PF = P; QF = Q; flag |= kHasF; }
+                else { PL = P; QL = Q; flag |= kHasL; oldL = old[j]; rowL = r[j]; }
+            }
+        }
+    }
+    sPF[tid] = PF; sQF[tid] = QF; sPL[tid] = PL; sQL[tid] = QL;
+    if (q == 0) sFlag[grp] = flag;
+    const int tile_has_head = __syncthreads_or(head != 0);
+
+    // ---- level 1: compose the pieces that cross chunk borders, in group order ----
+    if (flag & kHasL) {
+        P = PL; Q = QL;
+        bool closed = false;
+        for (int h = grp + 1; h < kGroups; ++h) {
+            const int fh = sFlag[h];
+            fold_combine<MODE>(P, Q, sPF[h * kG + q], sQF[h * kG + q]);
+            if (fh & kFClosed) { closed = true; break; }
+        }
+        if (closed) {
+            if (lane_on)
+                *reinterpret_cast<float4*>(a.table + (int64_t)rowL * a.ld + c0) = fold_final<MODE>(oldL, P, Q, c0, a.lr, a.decay);
+        } else {      // the segment runs past this tile: carry-out
+            reinterpret_cast<float4*>(a.out_q)[tile * kG + q] = Q;
+            if (q == 0) { a.out_p[tile] = P; a.out_row[tile] = rowL; }
+        }
+    }
+    if (grp == 0) {   // carry-in: the tile's first piece if it continues a segment of an earlier tile
+        int fl = 0;
+        if (flag & kHasF) {
+            P = PF; Q = QF;
+            bool closed = flag & kFClosed;
+            for (int h = 1; h < kGroups && !closed; ++h) {
+                const int fh = sFlag[h];
+                if (!(fh & kHasF)) break;     // only past the end of the list
+                fold_combine<MODE>(P, Q, sPF[h * kG + q], sQF[h * kG + q]);
+                closed = fh & kFClosed;
+            }
+            reinterpret_cast<float4*>(a.in_q)[tile * kG + q] = Q;
+            if (q == 0) a.in_p[tile] = P;
+            fl = kInValid | (closed ? kInClosed : 0);
+        }
+        if (q == 0) a.in_flag[tile] = fl;
+    }
+    if (grp == kGroups - 1 && q == 0) {
+        // a carry-out exists iff the tile's last element does not close its segment and the segment's head is in this tile
+        const bool right_open = (flag & kHasL) || ((flag & kHasF) && !(flag & kFClosed));
+        if (!(right_open && tile_has_head)) a.out_row[tile] = -1;
     }
 }
 
-// one group per long segment: compose the chunk partials in chunk order and write the row
-template <bool SEQ>
+// level 2: one group per tile with a carry-out; walks the carry-ins of the following tiles in order
+template <int MODE>
 __global__ void __launch_bounds__(kFoldThreads)
-fold_combine_kernel(int d, float lr, float decay, float* __restrict__ table, const int32_t* __restrict__ rows, int ld,
-                    const int32_t* __restrict__ hdr, const LongSeg* __restrict__ longs, const float* __restrict__ partial) {
-    const int nlong = hdr[0];
-    const int gl = threadIdx.x & (kGroup - 1);
-    const int groups_total = gridDim.x * (kFoldThreads / kGroup);
-    for (int sidx = blockIdx.x * (kFoldThreads / kGroup) + threadIdx.x / kGroup; sidx < nlong; sidx += groups_total) {
-        const LongSeg ls = longs[sidx];
-        const int nchunks = (ls.len + chunk_len_of(ls.len) - 1) / chunk_len_of(ls.len);
-        float* trow = table + (int64_t)rows[ls.start] * ld;
-        for (int c = gl; c < d; c += kGroup) {
-            const float old = trow[c];
-            float w = SEQ ? old : 0.f;
-#pragma unroll 8
-            for (int j = 0; j < nchunks; ++j) {
-                const float* pj = partial + (int64_t)(ls.chunk_off + j) * 2 * ld;
-                w = SEQ ? fmaf(w, pj[ld + c], pj[c]) : w + pj[c];
-            }
-            trow[c] = SEQ ? w : fmaf(old, decay, -lr * w);
+fold_stitch_kernel(const FoldArgs a, int tiles) {
+    const int64_t t = ((int64_t)blockIdx.x * kFoldThreads + threadIdx.x) >> 2;
+    const int q = threadIdx.x & (kG - 1);
+    if (t >= tiles) return;
+    const int row = a.out_row[t];
+    if (row < 0) return;
+    const int c0 = a.col0 + 4 * q;
+    const bool lane_on = c0 < a.ld;
+    float4 old = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (lane_on) old = *reinterpret_cast<const float4*>(a.table + (int64_t)row * a.ld + c0);
+    float P = a.out_p[t];
+    float4 Q = reinterpret_cast<const float4*>(a.out_q)[t * kG + q];
+    int64_t u = t + 1;
+    bool closed = false;
+    while (!closed && u < tiles) {
+        // four carry-ins per round trip: the addresses are known, only the stop condition is data dependent
+        int fl[4]; float pp[4]; float4 qq[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int64_t w = u + i < tiles ? u + i : tiles - 1;
+            fl[i] = a.in_flag[w]; pp[i] = a.in_p[w]; qq[i] = reinterpret_cast<const float4*>(a.in_q)[w * kG + q];
         }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (!closed && u + i < tiles) {
+                fold_combine<MODE>(P, Q, pp[i], qq[i]);
+                closed = fl[i] & kInClosed;
+            }
+        }
+        u += 4;
     }
+    if (lane_on) *reinterpret_cast<float4*>(a.table + (int64_t)row * a.ld + c0) = fold_final<MODE>(old, P, Q, c0, a.lr, a.decay);
 }
 
 __global__ void decay_sweep_kernel(float4* __restrict__ table, int64_t X, int q, float decay,
@@ -166,37 +304,42 @@ __global__ void decay_sweep_kernel(float4* __restrict__ table, int64_t X, int q,
     }
 }
 
-static size_t longs_capacity(int64_t M) { return (size_t)(M / DCTR_LONG_SEG + 2); }
-static size_t chunks_capacity(int64_t M) { return (size_t)(M / DCTR_SEG_CHUNK + M / DCTR_LONG_SEG + 4); }
+static int64_t num_tiles(int64_t M) { return (M + kTile - 1) / kTile; }
 
-template <class Src>
-static int run_fold(int mode, Src src, const int32_t* rows, const int32_t* pos, int64_t M, int F, int d, float lr,
-                    float decay, float* table, int ld, void* workspace, size_t workspace_bytes, cudaStream_t st) {
-    if (workspace_bytes < dctr_scatter_workspace(M, ld)) {
-        set_error("scatter_sgd: workspace %zu < %zu bytes", workspace_bytes, dctr_scatter_workspace(M, ld));
-        return DCTR_EWORKSPACE;
-    }
-    int32_t* hdr = static_cast<int32_t*>(workspace);
-    LongSeg* longs = reinterpret_cast<LongSeg*>(hdr + 4);
-    int32_t* chunk_seg = reinterpret_cast<int32_t*>(longs + longs_capacity(M));
-    float* partial = reinterpret_cast<float*>(chunk_seg + ((chunks_capacity(M) + 3) & ~(size_t)3));
-    cudaMemsetAsync(hdr, 0, 16, st);
-    const int blocks = ceil_div(M * kGroup, kFoldThreads);
-    const int pgrid = kNumSMs * 4;
-    const bool seq = mode == DCTR_SCATTER_SEQ_DECAY;
-    int rc;
-    if (seq) fold_short_kernel<true, Src><<<blocks, kFoldThreads, 0, st>>>(src, rows, pos, M, F, d, lr, decay, table, ld, hdr, longs, chunk_seg);
-    else fold_short_kernel<false, Src><<<blocks, kFoldThreads, 0, st>>>(src, rows, pos, M, F, d, lr, decay, table, ld, hdr, longs, chunk_seg);
-    if ((rc = check_launch("fold_short_kernel"))) return rc;
-    if (M > DCTR_LONG_SEG) {
-        if (seq) fold_chunk_kernel<true, Src><<<pgrid, kFoldThreads, 0, st>>>(src, pos, F, d, lr, decay, table, rows, ld, hdr, longs, chunk_seg, partial);
-        else fold_chunk_kernel<false, Src><<<pgrid, kFoldThreads, 0, st>>>(src, pos, F, d, lr, decay, table, rows, ld, hdr, longs, chunk_seg, partial);
-        if ((rc = check_launch("fold_chunk_kernel"))) return rc;
-        if (seq) fold_combine_kernel<true><<<kNumSMs, kFoldThreads, 0, st>>>(d, lr, decay, table, rows, ld, hdr, longs, partial);
-        else fold_combine_kernel<false><<<kNumSMs, kFoldThreads, 0, st>>>(d, lr, decay, table, rows, ld, hdr, longs, partial);
-        if ((rc = check_launch("fold_combine_kernel"))) return rc;
+template <int MODE>
+static int launch_fold(FoldArgs a, bool aligned, cudaStream_t st) {
+    const int tiles = (int)num_tiles(a.M);
+    for (int col0 = 0; col0 < a.ld; col0 += kSlab) {
+        a.col0 = col0;
+        if (aligned) fold_tile_kernel<MODE, true><<<tiles, kFoldThreads, 0, st>>>(a);
+        else fold_tile_kernel<MODE, false><<<tiles, kFoldThreads, 0, st>>>(a);
+        int rc = check_launch("fold_tile_kernel");
+        if (rc) return rc;
+        if (tiles > 1) {
+            fold_stitch_kernel<MODE><<<ceil_div((int64_t)tiles * kG, kFoldThreads), kFoldThreads, 0, st>>>(a, tiles);
+            if ((rc = check_launch("fold_stitch_kernel"))) return rc;
+        }
     }
     return DCTR_OK;
+}
+
+static int run_fold(int mode, FoldArgs a, bool aligned, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+    if (workspace_bytes < dctr_scatter_workspace(a.M, a.ld)) {
+        set_error("scatter_sgd: workspace %zu < %zu bytes", workspace_bytes, dctr_scatter_workspace(a.M, a.ld));
+        return DCTR_EWORKSPACE;
+    }
+    const int64_t tiles = num_tiles(a.M);
+    float* w = static_cast<float*>(workspace);
+    a.in_q = w;
+    a.out_q = w + tiles * kSlab;
+    a.in_p = w + 2 * tiles * kSlab;
+    a.out_p = a.in_p + tiles;
+    a.in_flag = reinterpret_cast<int32_t*>(a.out_p + tiles);
+    a.out_row = a.in_flag + tiles;
+    a.fmul = (a.F < 512) ? (((uint64_t)1 << 40) / (uint64_t)a.F + 1) : 0;
+    if (mode == kSeq) return launch_fold<kSeq>(a, aligned, st);
+    if (mode == kFm) return launch_fold<kFm>(a, aligned, st);
+    return launch_fold<kSum>(a, aligned, st);
 }
 
 }  // namespace dctr
@@ -204,32 +347,45 @@ static int run_fold(int mode, Src src, const int32_t* rows, const int32_t* pos, 
 using namespace dctr;
 
 extern "C" size_t dctr_scatter_workspace(int64_t M, int ld) {
+    (void)ld;
     if (M < 0) M = 0;
-    return 16 + longs_capacity(M) * sizeof(LongSeg) + ((chunks_capacity(M) + 3) & ~(size_t)3) * sizeof(int32_t) +
-           chunks_capacity(M) * 2 * (size_t)ld * sizeof(float);
+    const int64_t tiles = num_tiles(M) + 1;
+    return (size_t)tiles * (2 * kSlab + 4) * sizeof(float) + 64;
 }
+
+static bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 
 extern "C" int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F,
                                 int d, const float* g, int64_t g_ld_n, int g_ld_f, const float* wts, float lr,
                                 float decay, float* table, int64_t X, int ld, void* workspace,
                                 size_t workspace_bytes, void* stream) {
     DCTR_REQUIRE(mode == DCTR_SCATTER_SUM || mode == DCTR_SCATTER_SEQ_DECAY, "scatter_sgd: bad mode %d", mode);
-    DCTR_REQUIRE(M >= 0 && F > 0 && d > 0 && d <= ld && (ld & 3) == 0 && X > 0, "scatter_sgd: bad shape");
+    DCTR_REQUIRE(M >= 0 && M < ((int64_t)1 << 31) && F > 0 && d > 0 && d <= ld && (ld & 3) == 0 && X > 0, "scatter_sgd: bad shape");
     if (M == 0) return DCTR_OK;
     DCTR_REQUIRE(sorted_rows && sorted_pos && g && table && workspace, "scatter_sgd: null pointer");
-    DenseSrc src{g, g_ld_n, g_ld_f, wts};
-    return run_fold(mode, src, sorted_rows, sorted_pos, M, F, d, lr, decay, table, ld, workspace, workspace_bytes, as_stream(stream));
+    DCTR_REQUIRE(aligned16(sorted_rows) && aligned16(sorted_pos) && aligned16(table) && aligned16(workspace),
+                 "scatter_sgd: rows / pos / table / workspace must be 16-byte aligned");
+    FoldArgs a{};
+    a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table;
+    a.g = g; a.s = nullptr; a.ld_n = g_ld_n; a.ld_f = g_ld_f; a.wts = wts;
+    const bool aligned = aligned16(g) && (g_ld_n & 3) == 0 && (g_ld_f & 3) == 0 && g_ld_f >= ld;
+    return run_fold(mode == DCTR_SCATTER_SEQ_DECAY ? kSeq : kSum, a, aligned, workspace, workspace_bytes, as_stream(stream));
 }
 
 extern "C" int dctr_scatter_sgd_fm(const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
                                    const float* g, const float* s, int lds, const float* wts, float lr, float decay,
                                    float* table, int64_t X, int ld, void* workspace, size_t workspace_bytes,
                                    void* stream) {
-    DCTR_REQUIRE(M >= 0 && F > 0 && d > 0 && d <= ld && (ld & 3) == 0 && X > 0 && lds >= d, "scatter_sgd_fm: bad shape");
+    DCTR_REQUIRE(M >= 0 && M < ((int64_t)1 << 31) && F > 0 && d > 0 && d <= ld && (ld & 3) == 0 && X > 0 && lds >= ld && (lds & 3) == 0,
+                 "scatter_sgd_fm: bad shape (lds must be a multiple of 4 and >= ld)");
     if (M == 0) return DCTR_OK;
     DCTR_REQUIRE(sorted_rows && sorted_pos && g && s && table && workspace, "scatter_sgd_fm: null pointer");
-    FmSrc src{g, s, lds, wts};
-    return run_fold(DCTR_SCATTER_SUM, src, sorted_rows, sorted_pos, M, F, d, lr, decay, table, ld, workspace, workspace_bytes, as_stream(stream));
+    DCTR_REQUIRE(aligned16(sorted_rows) && aligned16(sorted_pos) && aligned16(table) && aligned16(workspace) && aligned16(s),
+                 "scatter_sgd_fm: rows / pos / table / s / workspace must be 16-byte aligned");
+    FoldArgs a{};
+    a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table;
+    a.g = g; a.s = s; a.ld_n = 0; a.ld_f = lds; a.wts = wts;
+    return run_fold(kFm, a, true, workspace, workspace_bytes, as_stream(stream));
 }
 
 extern "C" int dctr_decay_sweep(float* table, int64_t X, int ld, float decay, const int32_t* sorted_rows, int64_t M,

@@ -85,9 +85,12 @@ int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t* sorted_row
  * dense source (FNN*, Theano FNN):  grad(p=n*F+f, c) = (wts? wts[p] : 1) * g[n*g_ld_n + f*g_ld_f + c]
  *   SUM:        row -= lr * sum_p grad(p,:)
  *   SEQ_DECAY:  for p in segment order: row = row*decay - lr*grad(p,:)
- * workspace: dctr_scatter_workspace(M, ld) bytes (long-segment list + chunk partials). */
-#define DCTR_LONG_SEG 32    /* segments longer than this are folded by chunks of DCTR_SEG_CHUNK */
-#define DCTR_SEG_CHUNK 32
+ * The fold is flat over the sorted list: 4-lane groups fold DCTR_FOLD_CHUNK consecutive elements, pieces that
+ * cross chunk / tile borders are composed in list order (fixed association => bit-reproducible).
+ * rows / pos / table / workspace must be 16-byte aligned.
+ * workspace: dctr_scatter_workspace(M, ld) bytes (one carry-in and one carry-out partial per tile). */
+#define DCTR_FOLD_CHUNK 8    /* sorted elements folded serially by one 4-lane group */
+#define DCTR_FOLD_TILE 512   /* sorted elements per CTA */
 size_t dctr_scatter_workspace(int64_t M, int ld);
 int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
                      const float* g, int64_t g_ld_n, int g_ld_f, const float* wts,
