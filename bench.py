@@ -169,6 +169,16 @@ def emb_roofline(N=1 << 20, F=16, rank=10, X=20_000_000, reps=5):
     N = 2^20 samples per launch): achieved algorithmic GB/s vs the measured copy peak."""
     import torch
     from deepctr_b200 import _lib as L, data
+    if os.environ.get("DCTR_L2_FETCH"):       # experiment knob: cudaLimitMaxL2FetchGranularity (enum value 5)
+        import ctypes
+        rt = ctypes.CDLL("libcudart.so")
+        torch.zeros(1, device="cuda")
+        val = ctypes.c_size_t(0)
+        rt.cudaDeviceGetLimit(ctypes.byref(val), 5)
+        rc = rt.cudaDeviceSetLimit(5, ctypes.c_size_t(int(os.environ["DCTR_L2_FETCH"])))
+        val2 = ctypes.c_size_t(0)
+        rt.cudaDeviceGetLimit(ctypes.byref(val2), 5)
+        print("L2 fetch granularity: was %d, set rc=%d, now %d" % (val.value, rc, val2.value), file=sys.stderr)
     d = rank + 1
     ld = (d + 3) // 4 * 4
     rng = np.random.default_rng(7)
