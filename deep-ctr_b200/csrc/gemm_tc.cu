@@ -1,10 +1,347 @@
-// Tensor-core GEMM entry point (tcgen05.mma kind::tf32 with 3xTF32 error compensation).
-// Round-1 state: the kernel is not written yet; the entry point reports the shape as "not covered" so
-// callers stay on the fp32 SIMT path of gemm.cu.  No silent fallback happens inside this library.
+// K4-tc: tensor-core GEMM for the MLP -- tcgen05.mma kind::tf32 with 3xTF32 error compensation, TMEM accumulators.
+// Same contract as dctr_gemm (gemm.cu): NN forward / NT dgrad / TN wgrad (split-K slabs) with the fused epilogues.
+//
+//   C = A*B with A = A_hi + A_lo, B = B_hi + B_lo (hi = rna-tf32(x), lo = rna-tf32(x - hi)):
+//       acc += A_lo*B_hi + A_hi*B_lo + A_hi*B_hi        (fp32 accumulate in TMEM; the dropped A_lo*B_lo term is ~2^-22)
+//
+//   CTA = 5 warps, one 128 x BN output tile, BK = 32 fp32 (one 128-byte swizzle row):
+//     warps 0-3  producers: global -> registers (128-bit loads, zero-filled edges) -> hi/lo split -> shared memory in
+//                the canonical K-major SWIZZLE_128B UMMA layout, whatever the global major-ness (a transposed operand
+//                is transposed on its way into shared memory, so one descriptor form serves NN / NT / TN);
+//                then the epilogue: tcgen05.ld (lane = output row) -> bias / act / mask or dgrad -> 128-bit stores
+//     warp 4     allocates TMEM, one elected lane issues 4 k-steps x 3 tcgen05.mma per stage, tcgen05.commit frees the
+//                stage (mbarrier) and finally signals the epilogue.
 #include "common.cuh"
 
-extern "C" int dctr_gemm_tc(int, int, int, int, const float*, int, const float*, int, float*, int, int, int,
-                            const float*, const float*, int, const float*, int, void*) {
-    dctr::set_error("gemm_tc: no shape is covered by the tcgen05 path yet");
-    return DCTR_EINVAL;
+namespace dctr {
+namespace tc {
+
+constexpr int kBM = 128;
+constexpr int kBKf = 32;                 // fp32 per k-block = 128 bytes
+constexpr int kProducers = 128;
+constexpr int kThreads = 160;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc], fp32 operands read as tf32
+__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// arrives on the mbarrier once every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(v);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major SWIZZLE_128B shared-memory descriptor (cute::UMMA::SmemDescriptor): start address >> 4 in bits [0,14),
+// stride byte offset (8 rows x 128 B = 1024 B) >> 4 in bits [32,46), version 1 in bits [46,48), layout type 2
+// (SWIZZLE_128B) in bits [61,64); the tile base is 1024-byte aligned so base_offset = 0.
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+// byte offset of element (row, k) of a [rows x 32 fp32] tile in that layout (16-byte chunk index XOR row%8)
+__device__ __forceinline__ uint32_t swz(int row, int k) {
+    return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((((k >> 2) ^ (row & 7)) << 4)) + (k & 3) * 4);
+}
+__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
+    uint32_t h, l;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(x));
+    hi = __uint_as_float(h);
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l) : "f"(x - hi));
+    lo = __uint_as_float(l);
+}
+
+
+struct TcParams {
+    int M, N, K;
+    const float* A; int lda;
+    const float* B; int ldb;
+    float* C; int ldc;
+    int epilogue, act;
+    const float* bias;
+    const float* aux; int ldaux;
+    const float* mask; int ldmask;
+    int k_per_split;   // multiple of kBKf
+};
+
+// One operand tile [ROWS x 32] of the k-block starting at k0: global -> registers -> (hi, lo) -> swizzled shared memory.
+// KCONTIG: element (r, k) at base[r*ld + k]; otherwise at base[k*ld + r] (transposed on the way in).
+template <int ROWS, bool KCONTIG>
+__device__ __forceinline__ void produce_tile(const float* __restrict__ base, int ld, int r0, int rmax, int k0, int kend,
+                                             uint8_t* s_hi, uint8_t* s_lo, int t) {
+    constexpr int NV = ROWS / 16;            // float4 per producer thread
+    float4 x[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const int idx = t + i * kProducers;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (KCONTIG) {
+            const int row = idx >> 3, k = k0 + (idx & 7) * 4, gr = r0 + row;
+            if (gr < rmax) {
+                const float* src = base + (int64_t)gr * ld + k;
+                if (k + 3 < kend) v = __ldg(reinterpret_cast<const float4*>(src));
+                else {
+                    if (k < kend) v.x = __ldg(src);
+                    if (k + 1 < kend) v.y = __ldg(src + 1);
+                    if (k + 2 < kend) v.z = __ldg(src + 2);
+                }
+            }
+        } else {
+            const int kk = idx & 7, r4 = (idx >> 3) % (ROWS / 4), kb8 = idx / (8 * (ROWS / 4));
+            const int k = k0 + kb8 * 8 + kk, gr = r0 + r4 * 4;
+            if (k < kend) {
+                const float* src = base + (int64_t)k * ld + gr;
+                if (gr + 3 < rmax) v = __ldg(reinterpret_cast<const float4*>(src));
+                else {
+                    if (gr < rmax) v.x = __ldg(src);
+                    if (gr + 1 < rmax) v.y = __ldg(src + 1);
+                    if (gr + 2 < rmax) v.z = __ldg(src + 2);
+                }
+            }
+        }
+        x[i] = v;
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const int idx = t + i * kProducers;
+        float4 h, l;
+        split_tf32(x[i].x, h.x, l.x); split_tf32(x[i].y, h.y, l.y);
+        split_tf32(x[i].z, h.z, l.z); split_tf32(x[i].w, h.w, l.w);
+        if (KCONTIG) {
+            const uint32_t off = swz(idx >> 3, (idx & 7) * 4);
+            *reinterpret_cast<float4*>(s_hi + off) = h;
+            *reinterpret_cast<float4*>(s_lo + off) = l;
+        } else {
+            const int kk = idx & 7, r4 = (idx >> 3) % (ROWS / 4), kb8 = idx / (8 * (ROWS / 4));
+            const int kl = kb8 * 8 + kk, r = r4 * 4;
+            *reinterpret_cast<float*>(s_hi + swz(r, kl)) = h.x; *reinterpret_cast<float*>(s_lo + swz(r, kl)) = l.x;
+            *reinterpret_cast<float*>(s_hi + swz(r + 1, kl)) = h.y; *reinterpret_cast<float*>(s_lo + swz(r + 1, kl)) = l.y;
+            *reinterpret_cast<float*>(s_hi + swz(r + 2, kl)) = h.z; *reinterpret_cast<float*>(s_lo + swz(r + 2, kl)) = l.z;
+            *reinterpret_cast<float*>(s_hi + swz(r + 3, kl)) = h.w; *reinterpret_cast<float*>(s_lo + swz(r + 3, kl)) = l.w;
+        }
+    }
+}
+
+__device__ __forceinline__ float tc_epilogue(const TcParams& p, int m, int n, float acc) {
+    if (p.epilogue == DCTR_EPI_FWD) {
+        float v = act_fwd(p.act, acc + (p.bias ? __ldg(p.bias + n) : 0.f));
+        if (p.mask) v *= __ldg(p.mask + (int64_t)m * p.ldmask + n);
+        return v;
+    } else if (p.epilogue == DCTR_EPI_DGRAD) {
+        const float mk = p.mask ? __ldg(p.mask + (int64_t)m * p.ldmask + n) : 1.f;
+        if (mk == 0.f) return 0.f;
+        const float t = __ldg(p.aux + (int64_t)m * p.ldaux + n) / mk;
+        return acc * mk * act_bwd_from_out(p.act, t);
+    }
+    return acc;
+}
+
+
+template <int BN, int NS>
+struct TcSmem {
+    static constexpr int kA = kBM * 128;           // bytes of one [128 x 32] fp32 tile
+    static constexpr int kB = BN * 128;
+    static constexpr int kStage = 2 * kA + 2 * kB;  // A_hi | A_lo | B_hi | B_lo
+    static constexpr int kBytes = NS * kStage + 1024 /* alignment slack */ + 256 /* barriers */;
+};
+
+template <int BN, int NS, bool AK, bool BK>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tc_kernel(const TcParams p) {
+    using S = TcSmem<BN, NS>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + NS * S::kStage);
+    uint64_t* empty = full + NS;
+    uint64_t* accum_full = empty + NS;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_full + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int m0 = blockIdx.y * kBM, n0 = blockIdx.x * BN;
+    const int kbeg = blockIdx.z * p.k_per_split;
+    const int kend = min(p.K, kbeg + p.k_per_split);
+    const int nkb = kend > kbeg ? (kend - kbeg + kBKf - 1) / kBKf : 0;
+    float* C = p.C + (int64_t)blockIdx.z * p.M * p.ldc;
+
+    if (tid == 0) {
+        for (int s = 0; s < NS; ++s) { mbar_init(full + s, kProducers); mbar_init(empty + s, 1); }
+        mbar_init(accum_full, 1);
+        fence_mbar_init();
+    }
+    if (warp == 4) tmem_alloc(tmem_slot, BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp < 4) {
+        // ===== producers =====
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % NS;
+            const uint32_t ph = (kb / NS) & 1;
+            mbar_wait(empty + s, ph ^ 1);
+            uint8_t* st = smem + s * S::kStage;
+            const int k0 = kbeg + kb * kBKf;
+            produce_tile<kBM, AK>(p.A, p.lda, m0, p.M, k0, kend, st, st + S::kA, tid);
+            produce_tile<BN, BK>(p.B, p.ldb, n0, p.N, k0, kend, st + 2 * S::kA, st + 2 * S::kA + S::kB, tid);
+            fence_proxy_async();          // generic-proxy stores -> visible to the tensor core's async proxy
+            mbar_arrive(full + s);
+        }
+        // ===== epilogue: TMEM lane = output row =====
+        if (nkb > 0) {
+            mbar_wait(accum_full, 0);
+            tc_fence_after();
+        }
+        const int m = m0 + warp * 32 + lane;
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+            if (n0 + c >= p.N) break;                   // uniform across the CTA
+            float v[32];
+            if (nkb > 0) tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c, v);
+            else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = 0.f;
+            }
+            if (m < p.M) {
+                float* dst = C + (int64_t)m * p.ldc + n0 + c;
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    const int n = n0 + c + j;
+                    if (n + 3 < p.N) {
+                        float4 o;
+                        o.x = tc_epilogue(p, m, n, v[j]); o.y = tc_epilogue(p, m, n + 1, v[j + 1]);
+                        o.z = tc_epilogue(p, m, n + 2, v[j + 2]); o.w = tc_epilogue(p, m, n + 3, v[j + 3]);
+                        *reinterpret_cast<float4*>(dst + j) = o;
+                    } else {
+#pragma unroll
+                        for (int jj = 0; jj < 4; ++jj)
+                            if (n + jj < p.N) dst[j + jj] = tc_epilogue(p, m, n + jj, v[j + jj]);
+                    }
+                }
+            }
+        }
+    } else if (lane == 0) {
+        // ===== MMA issuer =====
+        // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (1 << 4), A = B = TF32 (2 << 7, 2 << 10),
+        // both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+        constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % NS;
+            const uint32_t ph = (kb / NS) & 1;
+            mbar_wait(full + s, ph);
+            tc_fence_after();
+            const uint32_t sa = smem_u32(smem + s * S::kStage);
+            const uint64_t a_hi = make_desc(sa), a_lo = make_desc(sa + S::kA);
+            const uint64_t b_hi = make_desc(sa + 2 * S::kA), b_lo = make_desc(sa + 2 * S::kA + S::kB);
+#pragma unroll
+            for (int k4 = 0; k4 < kBKf / 8; ++k4) {           // UMMA_K = 8 tf32 = 32 bytes = 2 descriptor units
+                const uint64_t adv = (uint64_t)(2 * k4);
+                mma_tf32(tmem_base, a_lo + adv, b_hi + adv, idesc, (kb | k4) != 0);
+                mma_tf32(tmem_base, a_hi + adv, b_lo + adv, idesc, 1);
+                mma_tf32(tmem_base, a_hi + adv, b_hi + adv, idesc, 1);
+            }
+            mma_commit(empty + s);        // frees the stage when these MMAs have read it
+        }
+        if (nkb > 0) mma_commit(accum_full);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) tmem_dealloc(tmem_base, BN);
+}
+
+template <int BN, int NS>
+static int launch_tc(int layout, const TcParams& p, dim3 grid, cudaStream_t st) {
+    constexpr int bytes = TcSmem<BN, NS>::kBytes;
+    cudaError_t e = cudaSuccess;
+#define DCTR_TC_LAUNCH(AKV, BKV)                                                                                      \
+    do {                                                                                                              \
+        e = cudaFuncSetAttribute(gemm_tc_kernel<BN, NS, AKV, BKV>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes); \
+        if (e == cudaSuccess) gemm_tc_kernel<BN, NS, AKV, BKV><<<grid, kThreads, bytes, st>>>(p);                      \
+    } while (0)
+    if (layout == DCTR_GEMM_NN) DCTR_TC_LAUNCH(true, false);
+    else if (layout == DCTR_GEMM_NT) DCTR_TC_LAUNCH(true, true);
+    else DCTR_TC_LAUNCH(false, false);
+#undef DCTR_TC_LAUNCH
+    if (e != cudaSuccess) {
+        set_error("gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        return DCTR_ECUDA;
+    }
+    return check_launch("gemm_tc_kernel");
+}
+
+}  // namespace tc
+}  // namespace dctr
+
+using namespace dctr;
+
+extern "C" int dctr_gemm_tc(int layout, int M, int N, int K, const float* A, int lda, const float* B, int ldb,
+                            float* C, int ldc, int epilogue, int act, const float* bias, const float* aux, int ldaux,
+                            const float* mask, int ldmask, int splits, void* stream) {
+    DCTR_REQUIRE(layout >= 0 && layout <= 2, "gemm_tc: bad layout %d", layout);
+    DCTR_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm_tc: negative shape");
+    if (M == 0 || N == 0) return DCTR_OK;
+    DCTR_REQUIRE(A && B && C, "gemm_tc: null pointer");
+    DCTR_REQUIRE((lda & 3) == 0 && (ldb & 3) == 0 && (ldc & 3) == 0, "gemm_tc: leading dimensions must be multiples of 4");
+    DCTR_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0 && ((uintptr_t)C & 15) == 0, "gemm_tc: operands must be 16-byte aligned");
+    DCTR_REQUIRE(epilogue >= 0 && epilogue <= 2 && (epilogue != DCTR_EPI_DGRAD || aux), "gemm_tc: bad epilogue");
+    if (splits < 1) splits = 1;
+    DCTR_REQUIRE(splits == 1 || epilogue == DCTR_EPI_NONE, "gemm_tc: split-K needs EPI_NONE");
+    tc::TcParams p{M, N, K, A, lda, B, ldb, C, ldc, epilogue, act, bias, aux, ldaux, mask, ldmask, 0};
+    int kper = (K + splits - 1) / splits;
+    kper = (kper + tc::kBKf - 1) / tc::kBKf * tc::kBKf;
+    if (kper == 0) kper = tc::kBKf;
+    p.k_per_split = kper;
+    cudaStream_t st = as_stream(stream);
+    const int mt = ceil_div(M, tc::kBM);
+    DCTR_REQUIRE(mt < 65536, "gemm_tc: M too large");
+    // narrow N tiles when a 128-wide tiling would leave most SMs idle
+    if (N <= 64 || mt * ceil_div(N, 128) * splits < kNumSMs / 2) {
+        dim3 grid(ceil_div(N, 64), mt, splits);
+        return tc::launch_tc<64, 4>(layout, p, grid, st);
+    }
+    dim3 grid(ceil_div(N, 128), mt, splits);
+    return tc::launch_tc<128, 3>(layout, p, grid, st);
 }

@@ -123,11 +123,12 @@ int dctr_gemm(int layout, int M, int N, int K, const float* A, int lda, const fl
               float* C, int ldc, int epilogue, int act, const float* bias,
               const float* aux, int ldaux, const float* mask, int ldmask, int splits, void* stream);
 int dctr_splitk_reduce(const float* partials, int splits, int M, int N, int ldc, float* out, int ldo, void* stream);
-/* 3xTF32 error-compensated tensor-core variant (tcgen05.mma kind::tf32, TMEM accumulators); same
- * contract as dctr_gemm NN/FWD; returns DCTR_EINVAL for shapes it does not cover. */
+/* 3xTF32 error-compensated tensor-core variant (tcgen05.mma kind::tf32, TMEM accumulators, operands split into
+ * tf32 hi + lo parts on their way into shared memory: acc += A_lo*B_hi + A_hi*B_lo + A_hi*B_hi).  Same contract,
+ * layouts, epilogues and split-K slab convention as dctr_gemm; results agree with it to ~1e-6 relative. */
 int dctr_gemm_tc(int layout, int M, int N, int K, const float* A, int lda, const float* B, int ldb,
                  float* C, int ldc, int epilogue, int act, const float* bias,
-                 const float* aux, int ldaux, const float* mask, int ldmask, void* stream);
+                 const float* aux, int ldaux, const float* mask, int ldmask, int splits, void* stream);
 
 /* ---- K5: output unit + loss (FNN.py:54-63, FNN_wnzh.py:169-173) --------------------------------
  *   logit[n] = <a[n,0:H], w> + b ; pred = sigmoid ; loss_n = stable xent ; dlogit[n] = (pred-y)*gscale */
