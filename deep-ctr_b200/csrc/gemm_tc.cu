@@ -1,16 +1,20 @@
-// K4-tc: tensor-core GEMM for the MLP -- tcgen05.mma kind::tf32 with 3xTF32 error compensation, TMEM accumulators.
-// Same contract as dctr_gemm (gemm.cu): NN forward / NT dgrad / TN wgrad (split-K slabs) with the fused epilogues.
+// K4-tc: tensor-core GEMM for the MLP -- tcgen05.mma kind::tf32 with 3xTF32 error compensation, TMA-staged operands,
+// TMEM accumulators.  Same contract as dctr_gemm (gemm.cu): NN forward / NT dgrad / TN wgrad (split-K slabs), fused epilogues.
 //
 //   C = A*B with A = A_hi + A_lo, B = B_hi + B_lo (hi = rna-tf32(x), lo = rna-tf32(x - hi)):
 //       acc += A_lo*B_hi + A_hi*B_lo + A_hi*B_hi        (fp32 accumulate in TMEM; the dropped A_lo*B_lo term is ~2^-22)
 //
-//   CTA = 5 warps, one 128 x BN output tile, BK = 32 fp32 (one 128-byte swizzle row):
-//     warps 0-3  producers: global -> registers (128-bit loads, zero-filled edges) -> hi/lo split -> shared memory in
-//                the canonical K-major SWIZZLE_128B UMMA layout, whatever the global major-ness (a transposed operand
-//                is transposed on its way into shared memory, so one descriptor form serves NN / NT / TN);
-//                then the epilogue: tcgen05.ld (lane = output row) -> bias / act / mask or dgrad -> 128-bit stores
-//     warp 4     allocates TMEM, one elected lane issues 4 k-steps x 3 tcgen05.mma per stage, tcgen05.commit frees the
-//                stage (mbarrier) and finally signals the epilogue.
+//   CTA = 6 warps, one 128 x BN output tile, BK = 32 fp32 (one 128-byte swizzle row), NS-stage mbarrier pipeline:
+//     warp 5     one lane issues the TMA loads (cp.async.bulk.tensor, SWIZZLE_128B, out-of-bounds zero fill) of the raw
+//                fp32 operand boxes: a K-contiguous operand as one [rows x 32] box (canonical K-major UMMA layout), an
+//                MN-contiguous operand as rows/32 boxes of [32 k x 32 mn] (SWIZZLE_128B_ATOM_32B, the MN-major fp32 UMMA layout) -- no
+//                transposes anywhere, the instruction descriptor carries the major-ness;
+//     warps 0-3  split every landed stage in place: raw -> hi (same bytes) and lo (second buffer, same layout), then
+//                fence.proxy.async + mbarrier arrive; after the last k-block they run the epilogue: tcgen05.ld (lane =
+//                output row) -> bias / act / mask or dgrad -> 128-bit stores;
+//     warp 4     allocates TMEM; one lane issues 4 k-steps x 3 tcgen05.mma per stage; tcgen05.commit frees the stage
+//                for the TMA lane and finally signals the epilogue.
+#include <cuda.h>
 #include "common.cuh"
 
 namespace dctr {
@@ -18,8 +22,8 @@ namespace tc {
 
 constexpr int kBM = 128;
 constexpr int kBKf = 32;                 // fp32 per k-block = 128 bytes
-constexpr int kProducers = 128;
-constexpr int kThreads = 160;
+constexpr int kConverters = 128;
+constexpr int kThreads = 192;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -37,6 +41,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "@p bra DONE_%=;\n\t"
         "bra WAIT_%=;\n\t"
         "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// 2-D tiled TMA load global -> shared, completion counted in bytes on the mbarrier
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
@@ -82,6 +94,12 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 __device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
     return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
 }
+// MN-major fp32 operands have exactly one legal layout, SWIZZLE_128B_BASE32B (layout type 1; TMA's
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B): atoms of [4 k x 32 mn] (512 B, 32-byte chunks XOR k%4).  The next 4 k-rows follow
+// at +512 B (stride byte offset), the next 32 mn at +4096 B (leading byte offset = one [32 k x 32 mn] TMA box).
+__device__ __forceinline__ uint64_t make_desc_mn(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(4096 >> 4) << 16) | ((uint64_t)(512 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)1 << 61);
+}
 // byte offset of element (row, k) of a [rows x 32 fp32] tile in that layout (16-byte chunk index XOR row%8)
 __device__ __forceinline__ uint32_t swz(int row, int k) {
     return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((((k >> 2) ^ (row & 7)) << 4)) + (k & 3) * 4);
@@ -107,64 +125,6 @@ struct TcParams {
     int k_per_split;   // multiple of kBKf
 };
 
-// One operand tile [ROWS x 32] of the k-block starting at k0: global -> registers -> (hi, lo) -> swizzled shared memory.
-// KCONTIG: element (r, k) at base[r*ld + k]; otherwise at base[k*ld + r] (transposed on the way in).
-template <int ROWS, bool KCONTIG>
-__device__ __forceinline__ void produce_tile(const float* __restrict__ base, int ld, int r0, int rmax, int k0, int kend,
-                                             uint8_t* s_hi, uint8_t* s_lo, int t) {
-    constexpr int NV = ROWS / 16;            // float4 per producer thread
-    float4 x[NV];
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-        const int idx = t + i * kProducers;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (KCONTIG) {
-            const int row = idx >> 3, k = k0 + (idx & 7) * 4, gr = r0 + row;
-            if (gr < rmax) {
-                const float* src = base + (int64_t)gr * ld + k;
-                if (k + 3 < kend) v = __ldg(reinterpret_cast<const float4*>(src));
-                else {
-                    if (k < kend) v.x = __ldg(src);
-                    if (k + 1 < kend) v.y = __ldg(src + 1);
-                    if (k + 2 < kend) v.z = __ldg(src + 2);
-                }
-            }
-        } else {
-            const int kk = idx & 7, r4 = (idx >> 3) % (ROWS / 4), kb8 = idx / (8 * (ROWS / 4));
-            const int k = k0 + kb8 * 8 + kk, gr = r0 + r4 * 4;
-            if (k < kend) {
-                const float* src = base + (int64_t)k * ld + gr;
-                if (gr + 3 < rmax) v = __ldg(reinterpret_cast<const float4*>(src));
-                else {
-                    if (gr < rmax) v.x = __ldg(src);
-                    if (gr + 1 < rmax) v.y = __ldg(src + 1);
-                    if (gr + 2 < rmax) v.z = __ldg(src + 2);
-                }
-            }
-        }
-        x[i] = v;
-    }
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-        const int idx = t + i * kProducers;
-        float4 h, l;
-        split_tf32(x[i].x, h.x, l.x); split_tf32(x[i].y, h.y, l.y);
-        split_tf32(x[i].z, h.z, l.z); split_tf32(x[i].w, h.w, l.w);
-        if (KCONTIG) {
-            const uint32_t off = swz(idx >> 3, (idx & 7) * 4);
-            *reinterpret_cast<float4*>(s_hi + off) = h;
-            *reinterpret_cast<float4*>(s_lo + off) = l;
-        } else {
-            const int kk = idx & 7, r4 = (idx >> 3) % (ROWS / 4), kb8 = idx / (8 * (ROWS / 4));
-            const int kl = kb8 * 8 + kk, r = r4 * 4;
-            *reinterpret_cast<float*>(s_hi + swz(r, kl)) = h.x; *reinterpret_cast<float*>(s_lo + swz(r, kl)) = l.x;
-            *reinterpret_cast<float*>(s_hi + swz(r + 1, kl)) = h.y; *reinterpret_cast<float*>(s_lo + swz(r + 1, kl)) = l.y;
-            *reinterpret_cast<float*>(s_hi + swz(r + 2, kl)) = h.z; *reinterpret_cast<float*>(s_lo + swz(r + 2, kl)) = l.z;
-            *reinterpret_cast<float*>(s_hi + swz(r + 3, kl)) = h.w; *reinterpret_cast<float*>(s_lo + swz(r + 3, kl)) = l.w;
-        }
-    }
-}
-
 __device__ __forceinline__ float tc_epilogue(const TcParams& p, int m, int n, float acc) {
     if (p.epilogue == DCTR_EPI_FWD) {
         float v = act_fwd(p.act, acc + (p.bias ? __ldg(p.bias + n) : 0.f));
@@ -184,18 +144,36 @@ template <int BN, int NS>
 struct TcSmem {
     static constexpr int kA = kBM * 128;           // bytes of one [128 x 32] fp32 tile
     static constexpr int kB = BN * 128;
-    static constexpr int kStage = 2 * kA + 2 * kB;  // A_hi | A_lo | B_hi | B_lo
+    static constexpr int kStage = 2 * kA + 2 * kB;  // A raw->hi | A lo | B raw->hi | B lo
     static constexpr int kBytes = NS * kStage + 1024 /* alignment slack */ + 256 /* barriers */;
 };
 
+// raw fp32 -> hi in place, lo into the twin buffer (same swizzled layout): 16-byte vectors, conflict-free
+template <int BYTES>
+__device__ __forceinline__ void split_in_place(uint8_t* hi, uint8_t* lo, int t) {
+    constexpr int NV = BYTES / 16 / kConverters;
+    float4 x[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) x[i] = *reinterpret_cast<const float4*>(hi + (t + i * kConverters) * 16);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        float4 h, l;
+        split_tf32(x[i].x, h.x, l.x); split_tf32(x[i].y, h.y, l.y);
+        split_tf32(x[i].z, h.z, l.z); split_tf32(x[i].w, h.w, l.w);
+        *reinterpret_cast<float4*>(hi + (t + i * kConverters) * 16) = h;
+        *reinterpret_cast<float4*>(lo + (t + i * kConverters) * 16) = l;
+    }
+}
+
 template <int BN, int NS, bool AK, bool BK>
 __global__ void __launch_bounds__(kThreads, 1)
-gemm_tc_kernel(const TcParams p) {
+gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB) {
     using S = TcSmem<BN, NS>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + NS * S::kStage);
-    uint64_t* empty = full + NS;
+    uint64_t* raw_full = reinterpret_cast<uint64_t*>(smem + NS * S::kStage);
+    uint64_t* conv_full = raw_full + NS;
+    uint64_t* empty = conv_full + NS;
     uint64_t* accum_full = empty + NS;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_full + 1);
 
@@ -207,7 +185,7 @@ gemm_tc_kernel(const TcParams p) {
     float* C = p.C + (int64_t)blockIdx.z * p.M * p.ldc;
 
     if (tid == 0) {
-        for (int s = 0; s < NS; ++s) { mbar_init(full + s, kProducers); mbar_init(empty + s, 1); }
+        for (int s = 0; s < NS; ++s) { mbar_init(raw_full + s, 1); mbar_init(conv_full + s, kConverters); mbar_init(empty + s, 1); }
         mbar_init(accum_full, 1);
         fence_mbar_init();
     }
@@ -218,17 +196,15 @@ gemm_tc_kernel(const TcParams p) {
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp < 4) {
-        // ===== producers =====
+        // ===== converters =====
         for (int kb = 0; kb < nkb; ++kb) {
             const int s = kb % NS;
-            const uint32_t ph = (kb / NS) & 1;
-            mbar_wait(empty + s, ph ^ 1);
+            mbar_wait(raw_full + s, (kb / NS) & 1);
             uint8_t* st = smem + s * S::kStage;
-            const int k0 = kbeg + kb * kBKf;
-            produce_tile<kBM, AK>(p.A, p.lda, m0, p.M, k0, kend, st, st + S::kA, tid);
-            produce_tile<BN, BK>(p.B, p.ldb, n0, p.N, k0, kend, st + 2 * S::kA, st + 2 * S::kA + S::kB, tid);
+            split_in_place<S::kA>(st, st + S::kA, tid);
+            split_in_place<S::kB>(st + 2 * S::kA, st + 2 * S::kA + S::kB, tid);
             fence_proxy_async();          // generic-proxy stores -> visible to the tensor core's async proxy
-            mbar_arrive(full + s);
+            mbar_arrive(conv_full + s);
         }
         // ===== epilogue: TMEM lane = output row =====
         if (nkb > 0) {
@@ -263,25 +239,46 @@ gemm_tc_kernel(const TcParams p) {
                 }
             }
         }
-    } else if (lane == 0) {
-        // ===== MMA issuer =====
-        // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (1 << 4), A = B = TF32 (2 << 7, 2 << 10),
-        // both K-major, N >> 3 at bit 17, M >> 4 at bit 24
-        constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+    } else if (warp == 5 && lane == 0) {
+        // ===== TMA producer =====
         for (int kb = 0; kb < nkb; ++kb) {
             const int s = kb % NS;
-            const uint32_t ph = (kb / NS) & 1;
-            mbar_wait(full + s, ph);
-            tc_fence_after();
-            const uint32_t sa = smem_u32(smem + s * S::kStage);
-            const uint64_t a_hi = make_desc(sa), a_lo = make_desc(sa + S::kA);
-            const uint64_t b_hi = make_desc(sa + 2 * S::kA), b_lo = make_desc(sa + 2 * S::kA + S::kB);
+            mbar_wait(empty + s, ((kb / NS) & 1) ^ 1);
+            uint8_t* st = smem + s * S::kStage;
+            const int k0 = kbeg + kb * kBKf;
+            mbar_expect_tx(raw_full + s, S::kA + S::kB);
+            if (AK) tma_load_2d(st, &mapA, k0, m0, raw_full + s);
+            else {
 #pragma unroll
-            for (int k4 = 0; k4 < kBKf / 8; ++k4) {           // UMMA_K = 8 tf32 = 32 bytes = 2 descriptor units
-                const uint64_t adv = (uint64_t)(2 * k4);
-                mma_tf32(tmem_base, a_lo + adv, b_hi + adv, idesc, (kb | k4) != 0);
-                mma_tf32(tmem_base, a_hi + adv, b_lo + adv, idesc, 1);
-                mma_tf32(tmem_base, a_hi + adv, b_hi + adv, idesc, 1);
+                for (int i = 0; i < kBM / 32; ++i) tma_load_2d(st + i * 4096, &mapA, m0 + 32 * i, k0, raw_full + s);
+            }
+            uint8_t* sb = st + 2 * S::kA;
+            if (BK) tma_load_2d(sb, &mapB, k0, n0, raw_full + s);
+            else {
+#pragma unroll
+                for (int i = 0; i < BN / 32; ++i) tma_load_2d(sb + i * 4096, &mapB, n0 + 32 * i, k0, raw_full + s);
+            }
+        }
+    } else if (warp == 4 && lane == 0) {
+        // ===== MMA issuer =====
+        // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (1 << 4), A = B = TF32 (2 << 7, 2 << 10),
+        // a_major bit 15 / b_major bit 16 (0 = K-major, 1 = MN-major), N >> 3 at bit 17, M >> 4 at bit 24
+        constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((AK ? 0u : 1u) << 15) | ((BK ? 0u : 1u) << 16) |
+                                   ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % NS;
+            mbar_wait(conv_full + s, (kb / NS) & 1);
+            tc_fence_after();
+            const uint32_t sa = smem_u32(smem + s * S::kStage), sb = sa + 2 * S::kA;
+#pragma unroll
+            for (int k4 = 0; k4 < kBKf / 8; ++k4) {           // UMMA_K = 8 tf32: +32 B inside a K-major row, +1024 B (8 k-rows = 2 atoms) MN-major
+                const uint64_t a_hi = AK ? make_desc(sa) + 2 * k4 : make_desc_mn(sa + k4 * 1024);
+                const uint64_t a_lo = AK ? make_desc(sa + S::kA) + 2 * k4 : make_desc_mn(sa + S::kA + k4 * 1024);
+                const uint64_t b_hi = BK ? make_desc(sb) + 2 * k4 : make_desc_mn(sb + k4 * 1024);
+                const uint64_t b_lo = BK ? make_desc(sb + S::kB) + 2 * k4 : make_desc_mn(sb + S::kB + k4 * 1024);
+                mma_tf32(tmem_base, a_lo, b_hi, idesc, (kb | k4) != 0);
+                mma_tf32(tmem_base, a_hi, b_lo, idesc, 1);
+                mma_tf32(tmem_base, a_hi, b_hi, idesc, 1);
             }
             mma_commit(empty + s);        // frees the stage when these MMAs have read it
         }
@@ -292,14 +289,53 @@ gemm_tc_kernel(const TcParams p) {
     if (warp == 4) tmem_dealloc(tmem_base, BN);
 }
 
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    }
+    return fn;
+}
+
+// Tensor map of one GEMM operand, an fp32 matrix with `rows` logical MN rows and `K` logical k columns.
+//   kcontig: element (r, k) at base[r*ld + k] -> dims {K, rows}, box {32 k, box_rows}      (K-major UMMA tile)
+//   else:    element (r, k) at base[k*ld + r] -> dims {rows, K}, box {32 mn, 32 k}         (MN-major UMMA atoms)
+// Out-of-range parts of a box are zero-filled by the TMA unit, which is what pads the M / N / K edges.
+static int make_map(CUtensorMap* map, const float* base, int ld, int rows, int K, bool kcontig, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) { set_error("gemm_tc: cuTensorMapEncodeTiled is not available from this driver"); return DCTR_ECUDA; }
+    cuuint64_t dims[2] = {(cuuint64_t)(kcontig ? K : rows), (cuuint64_t)(kcontig ? rows : K)};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
+    cuuint32_t box[2] = {32u, (cuuint32_t)(kcontig ? box_rows : 32)};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, kcontig ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("gemm_tc: cuTensorMapEncodeTiled failed (%d) rows=%d K=%d ld=%d", (int)r, rows, K, ld); return DCTR_ECUDA; }
+    return DCTR_OK;
+}
+
 template <int BN, int NS>
 static int launch_tc(int layout, const TcParams& p, dim3 grid, cudaStream_t st) {
     constexpr int bytes = TcSmem<BN, NS>::kBytes;
+    const bool ak = layout != DCTR_GEMM_TN, bk = layout == DCTR_GEMM_NT;
+    CUtensorMap mapA, mapB;
+    int rc = make_map(&mapA, p.A, p.lda, p.M, p.K, ak, kBM);
+    if (rc) return rc;
+    if ((rc = make_map(&mapB, p.B, p.ldb, p.N, p.K, bk, BN))) return rc;
     cudaError_t e = cudaSuccess;
 #define DCTR_TC_LAUNCH(AKV, BKV)                                                                                      \
     do {                                                                                                              \
         e = cudaFuncSetAttribute(gemm_tc_kernel<BN, NS, AKV, BKV>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes); \
-        if (e == cudaSuccess) gemm_tc_kernel<BN, NS, AKV, BKV><<<grid, kThreads, bytes, st>>>(p);                      \
+        if (e == cudaSuccess) gemm_tc_kernel<BN, NS, AKV, BKV><<<grid, kThreads, bytes, st>>>(p, mapA, mapB);          \
     } while (0)
     if (layout == DCTR_GEMM_NN) DCTR_TC_LAUNCH(true, false);
     else if (layout == DCTR_GEMM_NT) DCTR_TC_LAUNCH(true, true);
@@ -337,6 +373,7 @@ extern "C" int dctr_gemm_tc(int layout, int M, int N, int K, const float* A, int
     cudaStream_t st = as_stream(stream);
     const int mt = ceil_div(M, tc::kBM);
     DCTR_REQUIRE(mt < 65536, "gemm_tc: M too large");
+    if (K == 0) { p.K = 0; }
     // narrow N tiles when a 128-wide tiling would leave most SMs idle
     if (N <= 64 || mt * ceil_div(N, 128) * splits < kNumSMs / 2) {
         dim3 grid(ceil_div(N, 64), mt, splits);
