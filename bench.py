@@ -131,7 +131,7 @@ def build_model(wl, N, seed=1234):
 
 # algorithmic bytes / flops per call; args are the ctypes arguments of the call
 def call_cost(name, a):
-    if name == "dctr_gemm":
+    if name in ("dctr_gemm", "dctr_gemm_tc"):
         return "flop", 2.0 * a[1] * a[2] * a[3]
     if name == "dctr_gather_concat_fwd":
         N, F, d, ldz = a[5], a[6], a[7], a[13]
@@ -334,7 +334,7 @@ def run_b200(args, rank, world):
             device_step(i)
             torch.cuda.synchronize()
             for name, a, s, e in _lib.PROFILE:
-                key = name if name != "dctr_gemm" else "dctr_gemm[%s %dx%dx%d]" % (["NN", "NT", "TN"][a[0]], a[1], a[2], a[3])
+                key = name if not name.startswith("dctr_gemm") else "%s[%s %dx%dx%d]" % (name, ["NN", "NT", "TN"][a[0]], a[1], a[2], a[3])
                 unit, cost = call_cost(name, a)
                 r = agg.setdefault(key, dict(ms=0.0, cost=0.0, unit=unit, calls=0))
                 r["ms"] += s.elapsed_time(e)

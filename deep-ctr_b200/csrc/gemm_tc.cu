@@ -189,7 +189,9 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
         mbar_init(accum_full, 1);
         fence_mbar_init();
     }
-    if (warp == 4) tmem_alloc(tmem_slot, BN);
+    constexpr int kHiAcc = BN <= 64 ? 3 : 3;                  // hi*hi accumulators (+1 for the cross terms)
+    constexpr uint32_t kTmemCols = BN <= 64 ? 256 : 512;      // (kHiAcc + 1) * BN fp32 columns, power of two
+    if (warp == 4) tmem_alloc(tmem_slot, kTmemCols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -216,8 +218,17 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
         for (int c = 0; c < BN; c += 32) {
             if (n0 + c >= p.N) break;                   // uniform across the CTA
             float v[32];
-            if (nkb > 0) tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c, v);
-            else {
+            if (nkb > 0) {
+                const uint32_t ta = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c;
+                tmem_ld32(ta, v);
+#pragma unroll
+                for (int a = 1; a <= kHiAcc; ++a) {
+                    float u[32];
+                    tmem_ld32(ta + a * BN, u);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] += u[j];
+                }
+            } else {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = 0.f;
             }
@@ -241,6 +252,8 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
         }
     } else if (warp == 5 && lane == 0) {
         // ===== TMA producer =====
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapB)) : "memory");
         for (int kb = 0; kb < nkb; ++kb) {
             const int s = kb % NS;
             mbar_wait(empty + s, ((kb / NS) & 1) ^ 1);
@@ -276,9 +289,13 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
                 const uint64_t a_lo = AK ? make_desc(sa + S::kA) + 2 * k4 : make_desc_mn(sa + S::kA + k4 * 1024);
                 const uint64_t b_hi = BK ? make_desc(sb) + 2 * k4 : make_desc_mn(sb + k4 * 1024);
                 const uint64_t b_lo = BK ? make_desc(sb + S::kB) + 2 * k4 : make_desc_mn(sb + S::kB + k4 * 1024);
-                mma_tf32(tmem_base, a_lo, b_hi, idesc, (kb | k4) != 0);
-                mma_tf32(tmem_base, a_hi, b_lo, idesc, 1);
-                mma_tf32(tmem_base, a_hi, b_hi, idesc, 1);
+                // Several accumulators shorten every addition chain (the tensor core truncates when it accumulates): the
+                // hi*hi products of k-step t go to accumulator t % kHiAcc, the two small cross terms to the last one;
+                // the epilogue adds them up in fp32.
+                const int t = kb * (kBKf / 8) + k4;
+                mma_tf32(tmem_base + kHiAcc * BN, a_lo, b_hi, idesc, t != 0);
+                mma_tf32(tmem_base + kHiAcc * BN, a_hi, b_lo, idesc, 1);
+                mma_tf32(tmem_base + (t % kHiAcc) * BN, a_hi, b_hi, idesc, t >= kHiAcc);
             }
             mma_commit(empty + s);        // frees the stage when these MMAs have read it
         }
@@ -286,7 +303,7 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) tmem_dealloc(tmem_base, BN);
+    if (warp == 4) tmem_dealloc(tmem_base, kTmemCols);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,

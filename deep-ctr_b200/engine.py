@@ -8,6 +8,8 @@ Layout in HBM
   grads   float32 flat         same layout (one all-reduce buffer, one dense-SGD launch)
   ins[l]  float32 [N, ld_l]    input of layer l (ins[0] = act0(z)), ld_l = round_up(width, 4), pad columns 0
 """
+import os
+
 import torch
 
 from . import _lib as L
@@ -19,8 +21,13 @@ def _r4(n):
 
 class StepEngine:
     def __init__(self, X, F, rank, hidden, batch_size, cross="none", bias_first=False, act0="none", act="tanh",
-                 scatter_mode="sum", device="cuda", ld=None):
+                 scatter_mode="sum", device="cuda", ld=None, gemm=None):
         L.lib()  # fail loudly when libdctr.so is missing
+        # MLP GEMM path: "tc" = tcgen05 3xTF32 (gemm_tc.cu), "simt" = fp32 FFMA (gemm.cu); "auto" keeps the SIMT kernel
+        # for batches too small to fill one 128-row tensor-core tile per SM wave
+        gemm = gemm or os.environ.get("DCTR_GEMM", "auto")
+        assert gemm in ("auto", "tc", "simt"), gemm
+        self.gemm_fn = "dctr_gemm_tc" if (gemm == "tc" or (gemm == "auto" and int(batch_size) >= 1024)) else "dctr_gemm"
         self.dev = torch.device(device)
         self.X, self.F, self.d, self.N = int(X), int(F), int(rank) + 1, int(batch_size)
         self.ld = ld or _r4(self.d)
@@ -143,7 +150,7 @@ class StepEngine:
             self.ins[0].mul_(self.masks[0])     # input dropout (tf.nn.dropout on act(z1), FNN.py:87): torch elementwise
         for l in range(self.nl - 1):
             mp, mld = self._mask(l + 1)
-            L.call("dctr_gemm", L.GEMM_NN, N, self.widths[l + 1], self.widths[l], p(self.ins[l]), self.ldi[l],
+            L.call(self.gemm_fn, L.GEMM_NN, N, self.widths[l + 1], self.widths[l], p(self.ins[l]), self.ldi[l],
                    p(self.W(l)), self.ldw[l], p(self.ins[l + 1]), self.ldi[l + 1], L.EPI_FWD, L.ACT[self.act],
                    p(self.b(l)), None, 0, mp, mld, 1, st)
         last = self.nl - 1
@@ -173,16 +180,16 @@ class StepEngine:
             s = self.splits[l]
             gW = self.W(l, self.grads)
             if s > 1:
-                L.call("dctr_gemm", L.GEMM_TN, K, Hl, N, p(self.ins[l]), self.ldi[l], p(dpre), ldd, p(self.splitk_ws),
+                L.call(self.gemm_fn, L.GEMM_TN, K, Hl, N, p(self.ins[l]), self.ldi[l], p(dpre), ldd, p(self.splitk_ws),
                        self.ldw[l], L.EPI_NONE, 0, None, None, 0, None, 0, s, st)
                 L.call("dctr_splitk_reduce", p(self.splitk_ws), s, K, Hl, self.ldw[l], p(gW), self.ldw[l], st)
             else:
-                L.call("dctr_gemm", L.GEMM_TN, K, Hl, N, p(self.ins[l]), self.ldi[l], p(dpre), ldd, p(gW),
+                L.call(self.gemm_fn, L.GEMM_TN, K, Hl, N, p(self.ins[l]), self.ldi[l], p(dpre), ldd, p(gW),
                        self.ldw[l], L.EPI_NONE, 0, None, None, 0, None, 0, 1, st)
             L.call("dctr_col_wsum", p(dpre), ldd, N, Hl, None, p(self.b(l, self.grads)), cw, cwb, st)
             mp, mld = self._mask(l)
             act = self.act if l > 0 else self.act0
-            L.call("dctr_gemm", L.GEMM_NT, N, K, Hl, p(dpre), ldd, p(self.W(l)), self.ldw[l], p(self.dbuf[cur ^ 1]), ldd,
+            L.call(self.gemm_fn, L.GEMM_NT, N, K, Hl, p(dpre), ldd, p(self.W(l)), self.ldw[l], p(self.dbuf[cur ^ 1]), ldd,
                    L.EPI_DGRAD, L.ACT[act], None, p(self.ins[l]), self.ldi[l], mp, mld, 1, st)
             cur ^= 1
         return self.dbuf[cur]

@@ -18,6 +18,13 @@ def _need_cuda():
         pytest.skip("no CUDA device")
 
 
+@pytest.fixture(autouse=True, params=["simt", "tc"])
+def gemm_path(request, monkeypatch):
+    """Every model-level parity test runs on both MLP GEMM paths (fp32 FFMA and tcgen05 3xTF32)."""
+    monkeypatch.setenv("DCTR_GEMM", request.param)
+    return request.param
+
+
 def close(a, b, rtol=RTOL, atol=1e-6):
     np.testing.assert_allclose(np.asarray(a, np.float64), np.asarray(b, np.float64), rtol=rtol, atol=atol)
 
