@@ -246,18 +246,21 @@ def run_b200(args, rank, world):
         ddist.attach(model, dist)
     eng = model.engine
     pool, _ = make_pool(form, F, X, N, 8, seed=1234 + rank)
-    if form == "theano":
-        pool = [(model.arrange(ids)[0], w, y) for ids, w, y in pool]
     dpool = [(torch.as_tensor(i.astype(np.int32)).cuda(), torch.as_tensor(w).cuda(), torch.as_tensor(y).cuda()) for i, w, y in pool]
     flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device="cuda")     # > 126 MB L2
     K, W = args.steps, max(3, args.warmup)
 
     def device_step(i):
         ids, wts, y = dpool[i % len(dpool)]
-        eng.ids.copy_(ids)
-        eng.wts.copy_(wts)
+        if form == "theano":
+            model.feats.copy_(ids)      # raw feature lists; the slot-per-field arrangement is part of the device step
+        else:
+            eng.ids.copy_(ids)
+            eng.wts.copy_(wts)
         eng.y.copy_(y)
         model._pre_step()
+        if form == "theano":
+            model._upload_masks()
         model._run_step()
 
     for i in range(W):

@@ -208,6 +208,26 @@ cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
     }
 }
 
+// K0: slot of a feature = its field (feats_to_layer_one_array, FNN_wnzh.py:91-95).  One thread per sample walks its
+// feature list in order, so a later feature of the same field overwrites an earlier one exactly like the reference.
+__global__ void __launch_bounds__(256)
+arrange_fields_kernel(const int32_t* __restrict__ feats, const int32_t* __restrict__ feat_field, int N, int J, int F,
+                      int32_t pad_row, int32_t* __restrict__ ids, float* __restrict__ wts) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    int32_t* irow = ids + (int64_t)n * F;
+    float* wrow = wts + (int64_t)n * F;
+    for (int f = 0; f < F; ++f) { irow[f] = pad_row; wrow[f] = 0.f; }
+    const int32_t* frow = feats + (int64_t)n * J;
+    for (int j = 0; j < J; ++j) {
+        const int32_t feat = frow[j];
+        if (feat >= 0) {
+            const int slot = __ldg(feat_field + feat);
+            if (slot >= 0 && slot < F) { irow[slot] = feat; wrow[slot] = 1.f; }
+        }
+    }
+}
+
 static int gather_grid(int N) {
     int blocks = ceil_div(N, kGatherWarps);
     int cap = kNumSMs * 8;  // 8 resident CTAs of 8 warps = 64 warps / SM
@@ -281,4 +301,13 @@ extern "C" int dctr_cross_bwd(const int32_t* ids, const float* wts, const float*
     else LAUNCH_B(DCTR_CROSS_NONE);
 #undef LAUNCH_B
     return check_launch("cross_bwd_kernel");
+}
+
+extern "C" int dctr_arrange_fields(const int32_t* feats, const int32_t* feat_field, int N, int J, int F, int32_t pad_row,
+                                   int32_t* ids, float* wts, void* stream) {
+    DCTR_REQUIRE(N >= 0 && J > 0 && F > 0, "arrange_fields: bad shape N=%d J=%d F=%d", N, J, F);
+    if (N == 0) return DCTR_OK;
+    DCTR_REQUIRE(feats && feat_field && ids && wts, "arrange_fields: null pointer");
+    arrange_fields_kernel<<<ceil_div(N, 256), 256, 0, as_stream(stream)>>>(feats, feat_field, N, J, F, pad_row, ids, wts);
+    return check_launch("arrange_fields_kernel");
 }

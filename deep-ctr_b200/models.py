@@ -107,16 +107,27 @@ def _optimizer(_ptmzr_argv):
     return float(lr), "optimizer: %s, learning rate: %g" % (name, lr)
 
 
-class _Pinned(object):
-    """Pinned host staging for one static batch: ids int32 [N,F], wts fp32 [N,F], y fp32 [N]."""
+class _Staging(object):
+    """One pinned host buffer and one device buffer holding every per-step input block back to back (16-byte aligned),
+    so a step costs ONE host->device copy; `host[name]` are numpy views, `dev[name]` torch views of the same layout."""
 
-    def __init__(self, N, F):
-        self.ids = torch.empty(N, F, dtype=torch.int32).pin_memory()
-        self.wts = torch.empty(N, F, dtype=torch.float32).pin_memory()
-        self.y = torch.empty(N, dtype=torch.float32).pin_memory()
-        self.pred = torch.empty(N, dtype=torch.float32).pin_memory()
-        self.loss = torch.empty(1, dtype=torch.float32).pin_memory()
-        self.ids_np, self.wts_np, self.y_np = self.ids.numpy(), self.wts.numpy(), self.y.numpy()
+    def __init__(self, blocks, device):
+        offs, total = {}, 0
+        for name, dtype, shape in blocks:
+            nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+            offs[name] = (total, nbytes, dtype, tuple(shape))
+            total += (nbytes + 15) // 16 * 16
+        self.nbytes = total
+        self.pinned = torch.zeros(total, dtype=torch.uint8).pin_memory()
+        self.device = torch.zeros(total, dtype=torch.uint8, device=device)
+        tdt = {np.int32: torch.int32, np.float32: torch.float32}
+        self.host, self.dev = {}, {}
+        for name, (o, nb, dtype, shape) in offs.items():
+            self.host[name] = self.pinned[o:o + nb].numpy().view(dtype).reshape(shape)
+            self.dev[name] = self.device[o:o + nb].view(tdt[dtype]).view(*shape)
+
+    def upload(self):
+        self.device.copy_(self.pinned, non_blocking=True)
 
 
 class _Base(object):
@@ -124,14 +135,24 @@ class _Base(object):
 
     use_graph = True
 
-    def _setup_host(self, engine, batch_size, F):
+    def _setup_host(self, engine, batch_size, F, extra_blocks=(), with_ids=True):
         self.engine = engine
         self.N, self.F = batch_size, F
-        self._pin = _Pinned(batch_size, F)
+        N = batch_size
+        blocks = ([("ids", np.int32, (N, F)), ("wts", np.float32, (N, F))] if with_ids else []) + [("y", np.float32, (N,))]
+        self._stage = _Staging(blocks + list(extra_blocks), engine.dev)
+        # the engine reads its inputs straight from the staging buffer and writes pred | loss into one output buffer
+        if with_ids:
+            engine.ids, engine.wts = self._stage.dev["ids"], self._stage.dev["wts"]
+        engine.y = self._stage.dev["y"]
+        engine.out = torch.zeros(N + 4, dtype=torch.float32, device=engine.dev)
+        engine.pred, engine.loss = engine.out[:N], engine.out[N:N + 1]
+        self._out_pinned = torch.zeros(N + 4, dtype=torch.float32).pin_memory()
+        self._out_np = self._out_pinned.numpy()
         self._graph = None
         self._warm = 0
-        self.h2d_bytes = batch_size * F * 8 + batch_size * 4
-        self.d2h_bytes = batch_size * 4 + 4
+        self.h2d_bytes = self._stage.nbytes
+        self.d2h_bytes = (N + 4) * 4
 
     def session(self):
         return Session(self)
@@ -154,45 +175,45 @@ class _Base(object):
             # capture does not execute: fall through to the first replay
         self._graph.replay()
 
-    def _stage_and_step(self, ids, wts, y):
-        e, pin = self.engine, self._pin
-        np.copyto(pin.ids_np, ids, casting="unsafe")
-        np.copyto(pin.wts_np, wts, casting="unsafe")
-        np.copyto(pin.y_np, y, casting="unsafe")
-        e.ids.copy_(pin.ids, non_blocking=True)
-        e.wts.copy_(pin.wts, non_blocking=True)
-        e.y.copy_(pin.y, non_blocking=True)
-        self._pre_step()
+    def _finish_step(self):
+        """upload the staged inputs (one copy), run the step, fetch pred | loss (one copy)."""
+        self._stage.upload()
         self._run_step()
-        pin.pred.copy_(e.pred, non_blocking=True)
-        pin.loss.copy_(e.loss, non_blocking=True)
+        self._out_pinned.copy_(self.engine.out, non_blocking=True)
         torch.cuda.current_stream().synchronize()
-        return float(pin.loss[0]), pin.pred.numpy().copy()
+        return float(self._out_np[self.N]), self._out_np[:self.N].copy()
 
-    def _pre_step(self):
-        pass
+    def _stage_and_step(self, ids, wts, y):
+        h = self._stage.host
+        np.copyto(h["ids"], ids, casting="unsafe")
+        np.copyto(h["wts"], wts, casting="unsafe")
+        np.copyto(h["y"], y, casting="unsafe")
+        self._pre_step()
+        return self._finish_step()
 
     def _predict_chunks(self, ids, wts):
         """Inference over E rows in chunks of the static batch (last chunk padded with row 0 / weight 0)."""
-        e, pin = self.engine, self._pin
+        e, h = self.engine, self._stage.host
         E = ids.shape[0]
         out = np.empty(E, dtype=np.float32)
         saved = self._swap_masks(None)
         for s in range(0, E, self.N):
             k = min(self.N, E - s)
-            pin.ids_np[:k] = ids[s:s + k]
-            pin.wts_np[:k] = wts[s:s + k]
+            h["ids"][:k] = ids[s:s + k]
+            h["wts"][:k] = wts[s:s + k]
             if k < self.N:
-                pin.ids_np[k:] = 0
-                pin.wts_np[k:] = 0
-            e.ids.copy_(pin.ids, non_blocking=True)
-            e.wts.copy_(pin.wts, non_blocking=True)
+                h["ids"][k:] = 0
+                h["wts"][k:] = 0
+            self._stage.upload()
             e.forward(False)
-            pin.pred.copy_(e.pred, non_blocking=True)
+            self._out_pinned.copy_(e.out, non_blocking=True)
             torch.cuda.current_stream().synchronize()
-            out[s:s + k] = pin.pred.numpy()[:k]
+            out[s:s + k] = self._out_np[:k]
         self._swap_masks(saved)
         return out
+
+    def _pre_step(self):
+        pass
 
     def _swap_masks(self, masks):
         return None

@@ -8,6 +8,7 @@ all run on the GPU, so `train` takes FEATURE IDS instead of the dense x and retu
 import numpy as np
 import torch
 
+from . import _lib as L
 from .engine import StepEngine
 from .models import _Base
 
@@ -70,10 +71,18 @@ class FNN_wnzh(_Base):
             eng.set_layer(l, Ws[l], bs[l])
         eng.wts_are_ones = False
         self.pad_row = X
-        self._setup_host(eng, batch_size, n_fields)
+        N = batch_size
+        extra = [("feats", np.int32, (N, n_fields))]
         self.mask_streams = MaskStreams(hidden1, hidden2, dropout) if dropout < 1.0 else None
         if self.mask_streams is not None:
-            eng.masks = [None, torch.ones(1, eng.ldi[1], device=eng.dev), torch.ones(1, eng.ldi[2], device=eng.dev)]
+            extra += [("mask1", np.float32, (1, eng.ldi[1])), ("mask2", np.float32, (1, eng.ldi[2]))]
+        # feature ids, labels and the two broadcast dropout masks travel in ONE host->device copy; the slot-per-field
+        # arrangement (FNN_wnzh.py:91-95) happens on the device (dctr_arrange_fields)
+        self._setup_host(eng, batch_size, n_fields, extra_blocks=extra, with_ids=False)
+        self.feats = self._stage.dev["feats"]
+        self.feat_field_dev = torch.as_tensor(self.feat_field.astype(np.int32)).to(eng.dev)
+        if self.mask_streams is not None:
+            eng.masks = [None, self._stage.dev["mask1"], self._stage.dev["mask2"]]
         self._next_masks = None
 
     # ---- host side of feats_to_layer_one_array: slot of a feature = its field (FNN_wnzh.py:87-96) ----
@@ -94,22 +103,47 @@ class FNN_wnzh(_Base):
         self._next_masks = (np.asarray(r1, np.float32).reshape(1, -1), np.asarray(r2, np.float32).reshape(1, -1))
 
     def _pre_step(self):
+        """draw (or take the injected) masks of this step into the pinned staging block."""
         if self.mask_streams is None:
             return
         r1, r2 = self._next_masks if self._next_masks is not None else self.mask_streams.draw()
         self._next_masks = None
-        e = self.engine
-        e.masks[1][:, :r1.shape[1]].copy_(torch.from_numpy(r1))
-        e.masks[2][:, :r2.shape[1]].copy_(torch.from_numpy(r2))
+        h = self._stage.host
+        h["mask1"][:, :r1.shape[1]] = r1
+        h["mask2"][:, :r2.shape[1]] = r2
+
+    def _upload_masks(self):
+        """masks only (bench.py's device-resident loop keeps feats / labels on the device)."""
+        if self.mask_streams is not None:
+            st = self._stage
+            for k in ("mask1", "mask2"):
+                st.dev[k].copy_(torch.from_numpy(st.host[k]), non_blocking=True)
+
+    def _arrange_on_device(self):
+        L.call("dctr_arrange_fields", L.ptr(self.feats), L.ptr(self.feat_field_dev), self.N, self.F, self.F, self.pad_row,
+               L.ptr(self.engine.ids), L.ptr(self.engine.wts), torch.cuda.current_stream(self.engine.dev).cuda_stream)
 
     def _device_step(self):
         decay = 1.0 - 2.0 * self.lambda_fm * self.lr / getattr(self, "global_N", self.N)   # FNN_wnzh.py:305 (b_size)
+        self._arrange_on_device()
         self.engine.train_step(self.lr, decay, 1.0, train_bias=False, last_decay=1.0 - 2.0 * self.lr * self.lambda1)
+
+    def _stage_feats(self, feats, rows=None):
+        h = self._stage.host["feats"]
+        feats = np.asarray(feats)
+        k, j = feats.shape
+        h[:k, :j] = feats
+        if j < self.F:
+            h[:k, j:] = -1
+        if k < self.N:
+            h[k:] = -1
 
     def train(self, feats, y):
         """One step of the loop body FNN_wnzh.py:296-306.  feats: [N, <=16] feature ids (-1 = absent)."""
-        ids, wts = self.arrange(feats)
-        return self._stage_and_step(ids, wts, np.asarray(y, dtype=np.float32).reshape(self.N))
+        self._stage_feats(feats)
+        np.copyto(self._stage.host["y"], np.asarray(y).reshape(self.N), casting="unsafe")
+        self._pre_step()
+        return self._finish_step()
 
     def _swap_masks(self, masks):
         old = self.engine.masks
@@ -118,8 +152,21 @@ class FNN_wnzh(_Base):
 
     def predict(self, feats):
         """predict(x) -> p_1: the no-dropout branch, no rescaling (FNN_wnzh.py:157-170,183)."""
-        ids, wts = self.arrange(feats)
-        return self._predict_chunks(ids, wts)
+        feats = np.asarray(feats)
+        E = feats.shape[0]
+        out = np.empty(E, dtype=np.float32)
+        saved = self._swap_masks(None)
+        for s in range(0, E, self.N):
+            k = min(self.N, E - s)
+            self._stage_feats(feats[s:s + k])
+            self._stage.upload()
+            self._arrange_on_device()
+            self.engine.forward(False)
+            self._out_pinned.copy_(self.engine.out, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            out[s:s + k] = self._out_np[:k]
+        self._swap_masks(saved)
+        return out
 
     def get_weights(self):
         """(w1, w2, w3, b1, b2, b3) like the tail of train()'s outputs -- POST-update here."""

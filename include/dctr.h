@@ -58,6 +58,13 @@ int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, const float* ta
                            int N, int F, int d, int cross, int bias_first, const float* bias, int act0,
                            float* out, int ldz, void* stream);
 
+/* ---- K0: feature list -> one slot per field (the slot logic of feats_to_layer_one_array, FNN_wnzh.py:91-95) ----
+ * feats: int32 [N, J] feature ids, negative = absent; feat_field: int32 [X] field of every feature (fm.model.txt,
+ * FNN_wnzh.py:82-84).  ids[n, field(feat)] = feat, wts = 1; fields a sample does not have get (pad_row, 0); a later
+ * feature of the same field overwrites an earlier one, as in the reference loop. */
+int dctr_arrange_fields(const int32_t* feats, const int32_t* feat_field, int N, int J, int F, int32_t pad_row,
+                        int32_t* ids, float* wts, void* stream);
+
 /* backward of the cross layer into a per-(sample,field) embedding-gradient buffer
  *   ge[n,f,c] = wts[n,f] * ( dz[n, f*d+c] + d(cross)/d(e_f[c]) ),  ge: float32 [N, F, ldg], ldg%4==0
  * dz is dL/dz (the activation derivative already applied), TF layout (bias last).

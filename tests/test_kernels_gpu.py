@@ -82,6 +82,29 @@ def test_gather_concat_fwd(L, cross, bias_first, act0, F, d, N):
     assert (got[:, D0:] == 0).all()
 
 
+def test_arrange_fields_bit_exact(L):
+    """slot of a feature = its field; later feature of the same field overwrites; absent fields -> (pad_row, 0)
+    (FNN_wnzh.py:91-95).  Index work: checked bit-exact against the host restatement."""
+    rng = np.random.default_rng(31)
+    N, J, F, X = 257, 16, 16, 5000
+    feat_field = rng.integers(0, F, X).astype(np.int32)
+    feats = rng.integers(0, X, (N, J)).astype(np.int32)
+    feats[rng.random((N, J)) < 0.2] = -1
+    want_ids = np.full((N, F), X, np.int32)
+    want_wts = np.zeros((N, F), np.float32)
+    for n in range(N):
+        for j in range(J):
+            if feats[n, j] >= 0:
+                want_ids[n, feat_field[feats[n, j]]] = feats[n, j]
+                want_wts[n, feat_field[feats[n, j]]] = 1.0
+    ids = torch.zeros(N, F, dtype=torch.int32, device="cuda")
+    wts = torch.full((N, F), 9.0, device="cuda")
+    L.call("dctr_arrange_fields", dev(feats).data_ptr(), dev(feat_field).data_ptr(), N, J, F, X, ids.data_ptr(), wts.data_ptr(), None)
+    torch.cuda.synchronize()
+    assert np.array_equal(ids.cpu().numpy(), want_ids)
+    assert np.array_equal(wts.cpu().numpy(), want_wts)
+
+
 @pytest.mark.parametrize("cross,F,d,N", [("none", 16, 11, 50), ("ip", 16, 11, 41), ("ip", 39, 11, 9), ("op", 16, 11, 23), ("op", 6, 5, 8)])
 def test_cross_bwd(L, cross, F, d, N):
     import deepctr_oracle as O
