@@ -4,15 +4,15 @@
 //   C = A*B with A = A_hi + A_lo, B = B_hi + B_lo (hi = rna-tf32(x), lo = rna-tf32(x - hi)):
 //       acc += A_lo*B_hi + A_hi*B_lo + A_hi*B_hi        (fp32 accumulate in TMEM; the dropped A_lo*B_lo term is ~2^-22)
 //
-//   CTA = 6 warps, one 128 x BN output tile, BK = 32 fp32 (one 128-byte swizzle row), NS-stage mbarrier pipeline:
-//     warp 5     one lane issues the TMA loads (cp.async.bulk.tensor, SWIZZLE_128B, out-of-bounds zero fill) of the raw
+//   CTA = 10 warps, one 128 x BN output tile, BK = 32 fp32 (one 128-byte swizzle row), NS-stage mbarrier pipeline:
+//     warp 9     one lane issues the TMA loads (cp.async.bulk.tensor, SWIZZLE_128B, out-of-bounds zero fill) of the raw
 //                fp32 operand boxes: a K-contiguous operand as one [rows x 32] box (canonical K-major UMMA layout), an
 //                MN-contiguous operand as rows/32 boxes of [32 k x 32 mn] (SWIZZLE_128B_ATOM_32B, the MN-major fp32 UMMA layout) -- no
 //                transposes anywhere, the instruction descriptor carries the major-ness;
-//     warps 0-3  split every landed stage in place: raw -> hi (same bytes) and lo (second buffer, same layout), then
+//     warps 0-7  split every landed stage in place: raw -> hi (same bytes) and lo (second buffer, same layout), then
 //                fence.proxy.async + mbarrier arrive; after the last k-block they run the epilogue: tcgen05.ld (lane =
 //                output row) -> bias / act / mask or dgrad -> 128-bit stores;
-//     warp 4     allocates TMEM; one lane issues 4 k-steps x 3 tcgen05.mma per stage; tcgen05.commit frees the stage
+//     warp 8     allocates TMEM; one lane issues 4 k-steps x 3 tcgen05.mma per stage; tcgen05.commit frees the stage
 //                for the TMA lane and finally signals the epilogue.
 #include <cuda.h>
 #include "common.cuh"
@@ -22,8 +22,9 @@ namespace tc {
 
 constexpr int kBM = 128;
 constexpr int kBKf = 32;                 // fp32 per k-block = 128 bytes
-constexpr int kConverters = 128;
-constexpr int kThreads = 192;
+constexpr int kConverters = 256;
+constexpr int kThreads = 320;
+constexpr int kMmaWarp = kConverters / 32, kTmaWarp = kMmaWarp + 1;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -104,12 +105,12 @@ __device__ __forceinline__ uint64_t make_desc_mn(uint32_t saddr) {
 __device__ __forceinline__ uint32_t swz(int row, int k) {
     return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((((k >> 2) ^ (row & 7)) << 4)) + (k & 3) * 4);
 }
+// round-to-nearest (ties away, like cvt.rna.tf32.f32) by integer arithmetic on the bit pattern: the conversion unit
+// runs cvt at 1/8 rate and was the bottleneck of the split (measured with %globaltimer: ~1 us per k-block)
+__device__ __forceinline__ float rna_tf32(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u); }
 __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
-    uint32_t h, l;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(x));
-    hi = __uint_as_float(h);
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l) : "f"(x - hi));
-    lo = __uint_as_float(l);
+    hi = rna_tf32(x);
+    lo = rna_tf32(x - hi);
 }
 
 
@@ -125,20 +126,56 @@ struct TcParams {
     int k_per_split;   // multiple of kBKf
 };
 
-__device__ __forceinline__ float tc_epilogue(const TcParams& p, int m, int n, float acc) {
-    if (p.epilogue == DCTR_EPI_FWD) {
-        float v = act_fwd(p.act, acc + (p.bias ? __ldg(p.bias + n) : 0.f));
+// Epilogue of one 32-column chunk of one output row, specialised at compile time on (epilogue, activation): the
+// runtime dispatch happens once per chunk, not once per element (a per-element switch inlined 128 times made the
+// kernel 41k instructions long and the epilogue instruction-cache bound: 14 us -> measured with %globaltimer).
+template <int EPI, int ACT>
+__device__ __forceinline__ float tc_epi1(const TcParams& p, int m, int n, float acc) {
+    if (EPI == DCTR_EPI_FWD) {
+        float v = act_fwd(ACT, acc + (p.bias ? __ldg(p.bias + n) : 0.f));
         if (p.mask) v *= __ldg(p.mask + (int64_t)m * p.ldmask + n);
         return v;
-    } else if (p.epilogue == DCTR_EPI_DGRAD) {
-        const float mk = p.mask ? __ldg(p.mask + (int64_t)m * p.ldmask + n) : 1.f;
-        if (mk == 0.f) return 0.f;
-        const float t = __ldg(p.aux + (int64_t)m * p.ldaux + n) / mk;
-        return acc * mk * act_bwd_from_out(p.act, t);
+    } else if (EPI == DCTR_EPI_DGRAD) {
+        float mk = 1.f, t = __ldg(p.aux + (int64_t)m * p.ldaux + n);
+        if (p.mask) {
+            mk = __ldg(p.mask + (int64_t)m * p.ldmask + n);
+            if (mk == 0.f) return 0.f;
+            t *= __frcp_rn(mk);
+        }
+        return acc * mk * act_bwd_from_out(ACT, t);
     }
     return acc;
 }
-
+template <int EPI, int ACT>
+__device__ __forceinline__ void tc_store_chunk(const TcParams& p, float* __restrict__ dst, int m, int nbase, const float (&v)[32]) {
+    const int nlast = p.N - 1;
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+        const int n = nbase + j;
+        float4 o;      // columns past N reuse the last column's bias / mask / aux (loads stay in range) and are not stored
+        o.x = tc_epi1<EPI, ACT>(p, m, min(n, nlast), v[j]); o.y = tc_epi1<EPI, ACT>(p, m, min(n + 1, nlast), v[j + 1]);
+        o.z = tc_epi1<EPI, ACT>(p, m, min(n + 2, nlast), v[j + 2]); o.w = tc_epi1<EPI, ACT>(p, m, min(n + 3, nlast), v[j + 3]);
+        if (n + 3 < p.N) *reinterpret_cast<float4*>(dst + j) = o;
+        else {
+            if (n < p.N) dst[j] = o.x;
+            if (n + 1 < p.N) dst[j + 1] = o.y;
+            if (n + 2 < p.N) dst[j + 2] = o.z;
+        }
+    }
+}
+__device__ __forceinline__ void tc_store_dispatch(const TcParams& p, float* dst, int m, int nbase, const float (&v)[32]) {
+    switch (p.epilogue == DCTR_EPI_NONE ? 0 : p.epilogue * 4 + p.act) {
+        case DCTR_EPI_FWD * 4 + DCTR_ACT_NONE: tc_store_chunk<DCTR_EPI_FWD, DCTR_ACT_NONE>(p, dst, m, nbase, v); break;
+        case DCTR_EPI_FWD * 4 + DCTR_ACT_TANH: tc_store_chunk<DCTR_EPI_FWD, DCTR_ACT_TANH>(p, dst, m, nbase, v); break;
+        case DCTR_EPI_FWD * 4 + DCTR_ACT_RELU: tc_store_chunk<DCTR_EPI_FWD, DCTR_ACT_RELU>(p, dst, m, nbase, v); break;
+        case DCTR_EPI_FWD * 4 + DCTR_ACT_SIGMOID: tc_store_chunk<DCTR_EPI_FWD, DCTR_ACT_SIGMOID>(p, dst, m, nbase, v); break;
+        case DCTR_EPI_DGRAD * 4 + DCTR_ACT_NONE: tc_store_chunk<DCTR_EPI_DGRAD, DCTR_ACT_NONE>(p, dst, m, nbase, v); break;
+        case DCTR_EPI_DGRAD * 4 + DCTR_ACT_TANH: tc_store_chunk<DCTR_EPI_DGRAD, DCTR_ACT_TANH>(p, dst, m, nbase, v); break;
+        case DCTR_EPI_DGRAD * 4 + DCTR_ACT_RELU: tc_store_chunk<DCTR_EPI_DGRAD, DCTR_ACT_RELU>(p, dst, m, nbase, v); break;
+        case DCTR_EPI_DGRAD * 4 + DCTR_ACT_SIGMOID: tc_store_chunk<DCTR_EPI_DGRAD, DCTR_ACT_SIGMOID>(p, dst, m, nbase, v); break;
+        default: tc_store_chunk<DCTR_EPI_NONE, DCTR_ACT_NONE>(p, dst, m, nbase, v); break;
+    }
+}
 
 template <int BN, int NS>
 struct TcSmem {
@@ -191,13 +228,13 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
     }
     constexpr int kHiAcc = BN <= 64 ? 3 : 3;                  // hi*hi accumulators (+1 for the cross terms)
     constexpr uint32_t kTmemCols = BN <= 64 ? 256 : 512;      // (kHiAcc + 1) * BN fp32 columns, power of two
-    if (warp == 4) tmem_alloc(tmem_slot, kTmemCols);
+    if (warp == kMmaWarp) tmem_alloc(tmem_slot, kTmemCols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp < 4) {
+    if (warp < kMmaWarp) {
         // ===== converters =====
         for (int kb = 0; kb < nkb; ++kb) {
             const int s = kb % NS;
@@ -213,13 +250,15 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
             mbar_wait(accum_full, 0);
             tc_fence_after();
         }
-        const int m = m0 + warp * 32 + lane;
+        // a warp reaches the TMEM lanes 32*(warp%4)..+31 only: warps w and w+4 share a row quadrant and split the columns
+        const int quad = warp & 3;
+        const int m = m0 + quad * 32 + lane;
 #pragma unroll 1
-        for (int c = 0; c < BN; c += 32) {
-            if (n0 + c >= p.N) break;                   // uniform across the CTA
+        for (int c = (warp >> 2) * 32; c < BN; c += 64) {
+            if (n0 + c >= p.N) break;                   // uniform across the warp
             float v[32];
             if (nkb > 0) {
-                const uint32_t ta = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c;
+                const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c;
                 tmem_ld32(ta, v);
 #pragma unroll
                 for (int a = 1; a <= kHiAcc; ++a) {
@@ -232,25 +271,9 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = 0.f;
             }
-            if (m < p.M) {
-                float* dst = C + (int64_t)m * p.ldc + n0 + c;
-#pragma unroll
-                for (int j = 0; j < 32; j += 4) {
-                    const int n = n0 + c + j;
-                    if (n + 3 < p.N) {
-                        float4 o;
-                        o.x = tc_epilogue(p, m, n, v[j]); o.y = tc_epilogue(p, m, n + 1, v[j + 1]);
-                        o.z = tc_epilogue(p, m, n + 2, v[j + 2]); o.w = tc_epilogue(p, m, n + 3, v[j + 3]);
-                        *reinterpret_cast<float4*>(dst + j) = o;
-                    } else {
-#pragma unroll
-                        for (int jj = 0; jj < 4; ++jj)
-                            if (n + jj < p.N) dst[j + jj] = tc_epilogue(p, m, n + jj, v[j + jj]);
-                    }
-                }
-            }
+            if (m < p.M) tc_store_dispatch(p, C + (int64_t)m * p.ldc + n0 + c, m, n0 + c, v);
         }
-    } else if (warp == 5 && lane == 0) {
+    } else if (warp == kTmaWarp && lane == 0) {
         // ===== TMA producer =====
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapB)) : "memory");
@@ -272,7 +295,7 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
                 for (int i = 0; i < BN / 32; ++i) tma_load_2d(sb + i * 4096, &mapB, n0 + 32 * i, k0, raw_full + s);
             }
         }
-    } else if (warp == 4 && lane == 0) {
+    } else if (warp == kMmaWarp && lane == 0) {
         // ===== MMA issuer =====
         // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (1 << 4), A = B = TF32 (2 << 7, 2 << 10),
         // a_major bit 15 / b_major bit 16 (0 = K-major, 1 = MN-major), N >> 3 at bit 17, M >> 4 at bit 24
@@ -303,7 +326,7 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) tmem_dealloc(tmem_base, kTmemCols);
+    if (warp == kMmaWarp) tmem_dealloc(tmem_base, kTmemCols);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,

@@ -24,10 +24,10 @@ class StepEngine:
                  scatter_mode="sum", device="cuda", ld=None, gemm=None):
         L.lib()  # fail loudly when libdctr.so is missing
         # MLP GEMM path: "tc" = tcgen05 3xTF32 (gemm_tc.cu), "simt" = fp32 FFMA (gemm.cu); "auto" keeps the SIMT kernel
-        # below 8192 samples, where the step is launch-latency bound and the tensor-core pipeline cannot fill (measured: profiles/)
+        # below 1024 samples (fewer than 8 tensor-core row tiles)
         gemm = gemm or os.environ.get("DCTR_GEMM", "auto")
         assert gemm in ("auto", "tc", "simt"), gemm
-        self.gemm_fn = "dctr_gemm_tc" if (gemm == "tc" or (gemm == "auto" and int(batch_size) >= 8192)) else "dctr_gemm"
+        self.gemm_fn = "dctr_gemm_tc" if (gemm == "tc" or (gemm == "auto" and int(batch_size) >= 1024)) else "dctr_gemm"
         self.dev = torch.device(device)
         self.X, self.F, self.d, self.N = int(X), int(F), int(rank) + 1, int(batch_size)
         self.ld = ld or _r4(self.d)
