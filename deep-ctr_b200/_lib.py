@@ -36,7 +36,9 @@ SIGNATURES = {
     "dctr_gemm": (_i, [_i, _i, _i, _i, _p, _i, _p, _i, _p, _i, _i, _i, _p, _p, _i, _p, _i, _i, _p]),
     "dctr_splitk_reduce": (_i, [_p, _i, _i, _i, _i, _p, _i, _p]),
     "dctr_gemm_tc": (_i, [_i, _i, _i, _i, _p, _i, _p, _i, _p, _i, _i, _i, _p, _p, _i, _p, _i, _i, _p]),
-    "dctr_out_xent_fwd": (_i, [_p, _i, _i, _i, _p, _p, _p, _f, _p, _p, _p, _p, _p]),
+    "dctr_reduce_workspace": (_z, [_i, _i]),
+    "dctr_out_xent_fwd": (_i, [_p, _i, _i, _i, _p, _p, _p, _f, _p, _p, _p, _p, _f, _p, _p, _z, _p]),
+    "dctr_out_bwd_fused": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i, _p, _p, _p, _z, _p]),
     "dctr_out_bwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
     "dctr_col_wsum_workspace": (_z, [_i, _i]),
     "dctr_col_wsum": (_i, [_p, _i, _i, _i, _p, _p, _p, _z, _p]),

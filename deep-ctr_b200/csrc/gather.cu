@@ -208,23 +208,29 @@ cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
     }
 }
 
-// K0: slot of a feature = its field (feats_to_layer_one_array, FNN_wnzh.py:91-95).  One thread per sample walks its
-// feature list in order, so a later feature of the same field overwrites an earlier one exactly like the reference.
+// K0: slot of a feature = its field (feats_to_layer_one_array, FNN_wnzh.py:91-95).  One warp per sample: lanes fill the
+// row with (pad_row, 0), then lane j places feature j; when several features of one sample share a field the highest j
+// wins (__match_any_sync picks it), which is the reference loop's "later feature overwrites".
 __global__ void __launch_bounds__(256)
 arrange_fields_kernel(const int32_t* __restrict__ feats, const int32_t* __restrict__ feat_field, int N, int J, int F,
                       int32_t pad_row, int32_t* __restrict__ ids, float* __restrict__ wts) {
-    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (n >= N) return;
     int32_t* irow = ids + (int64_t)n * F;
     float* wrow = wts + (int64_t)n * F;
-    for (int f = 0; f < F; ++f) { irow[f] = pad_row; wrow[f] = 0.f; }
+    for (int f = lane; f < F; f += 32) { irow[f] = pad_row; wrow[f] = 0.f; }
     const int32_t* frow = feats + (int64_t)n * J;
-    for (int j = 0; j < J; ++j) {
-        const int32_t feat = frow[j];
+    for (int j0 = 0; j0 < J; j0 += 32) {          // chunks in list order, so a later chunk overwrites an earlier one
+        __syncwarp();
+        const int j = j0 + lane;
+        const int32_t feat = j < J ? frow[j] : -1;
+        int slot = -1 - lane;                     // invalid lanes: private keys
         if (feat >= 0) {
-            const int slot = __ldg(feat_field + feat);
-            if (slot >= 0 && slot < F) { irow[slot] = feat; wrow[slot] = 1.f; }
+            const int s = __ldg(feat_field + feat);
+            if (s >= 0 && s < F) slot = s;
         }
+        const unsigned peers = __match_any_sync(0xffffffffu, slot);
+        if (slot >= 0 && (31 - __clz(peers)) == lane) { irow[slot] = feat; wrow[slot] = 1.f; }
     }
 }
 
@@ -308,6 +314,6 @@ extern "C" int dctr_arrange_fields(const int32_t* feats, const int32_t* feat_fie
     DCTR_REQUIRE(N >= 0 && J > 0 && F > 0, "arrange_fields: bad shape N=%d J=%d F=%d", N, J, F);
     if (N == 0) return DCTR_OK;
     DCTR_REQUIRE(feats && feat_field && ids && wts, "arrange_fields: null pointer");
-    arrange_fields_kernel<<<ceil_div(N, 256), 256, 0, as_stream(stream)>>>(feats, feat_field, N, J, F, pad_row, ids, wts);
+    arrange_fields_kernel<<<ceil_div((int64_t)N * 32, 256), 256, 0, as_stream(stream)>>>(feats, feat_field, N, J, F, pad_row, ids, wts);
     return check_launch("arrange_fields_kernel");
 }

@@ -4,12 +4,70 @@
 
 namespace dctr {
 
+// ---- single-launch fixed-order reductions ------------------------------------------------------------------
+// Every CTA owns a block of rows and writes one partial row; the CTA that takes the last ticket adds the partial rows in
+// block order (fixed order => bit-reproducible, no float atomics) and resets the ticket, so the workspace stays
+// reusable across launches and CUDA-graph replays.  The workspace must be zero-filled once before first use.
+constexpr int kRedThreads = 256;
+constexpr int kRedMaxBlocks = kNumSMs;
+
+__device__ __forceinline__ bool take_last_ticket(unsigned* ticket, unsigned nblocks) {
+    __shared__ unsigned s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned t = atomicAdd(ticket, 1u);
+        s_last = (t == nblocks - 1) ? 1u : 0u;
+        if (s_last) *ticket = 0u;
+    }
+    __syncthreads();
+    if (s_last) __threadfence();
+    return s_last != 0;
+}
+
+// Last-CTA fold of partial[S][W] columns [0, Hn): column h is summed over the S partial rows in a fixed order -- by up to
+// 32 k-slices in parallel (each slice in row order, the slices then in slice order), so narrow reductions (a loss, a bias
+// column) do not serialise hundreds of dependent L2 round trips on one thread.  Called by every thread of the CTA.
+template <class Dst>
+__device__ __forceinline__ void ordered_reduce(const float* __restrict__ partial, int S, int W, int Hn, Dst dst) {
+    __shared__ float s_part[kRedThreads];
+    int KS = 1;
+    while (KS < 32 && KS * 2 * Hn <= kRedThreads) KS *= 2;
+    if (KS == 1) {
+        for (int h = threadIdx.x; h < Hn; h += kRedThreads) {
+            float s = 0.f;
+#pragma unroll 16
+            for (int k = 0; k < S; ++k) s += __ldcg(partial + (int64_t)k * W + h);
+            dst(h, s);
+        }
+        return;
+    }
+    const int slice = (S + KS - 1) / KS;
+    const int h = threadIdx.x % Hn, ks = threadIdx.x / Hn;
+    float s = 0.f;
+    if (ks < KS) {
+        const int k1 = min(S, (ks + 1) * slice);
+#pragma unroll 16
+        for (int k = ks * slice; k < k1; ++k) s += __ldcg(partial + (int64_t)k * W + h);
+    }
+    s_part[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x < Hn) {
+        float t = 0.f;
+        for (int q = 0; q < KS; ++q) t += s_part[q * Hn + threadIdx.x];
+        dst(threadIdx.x, t);
+    }
+}
+
 // one warp per sample: logit = <a[n,:], w> + b
 __global__ void __launch_bounds__(256)
 out_xent_fwd_kernel(const float* __restrict__ a, int lda, int N, int H, const float* __restrict__ w,
                     const float* __restrict__ b, const float* __restrict__ y, float gscale,
                     float* __restrict__ logit, float* __restrict__ pred, float* __restrict__ loss_n,
-                    float* __restrict__ dlogit) {
+                    float* __restrict__ dlogit, float loss_scale, float* __restrict__ loss_sum,
+                    float* __restrict__ partial, unsigned* __restrict__ ticket) {
+    __shared__ float s_loss[8];
+    float my_loss = 0.f;
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -25,11 +83,24 @@ out_xent_fwd_kernel(const float* __restrict__ a, int lda, int N, int H, const fl
             if (pred) pred[n] = p;
             if (y) {
                 const float yn = y[n];
-                if (loss_n) loss_n[n] = xent_logits(z, yn);
+                const float ln = xent_logits(z, yn);
+                my_loss += ln;
+                if (loss_n) loss_n[n] = ln;
                 if (dlogit) dlogit[n] = (p - yn) * gscale;
             }
         }
     }
+    if (!loss_sum) return;
+    // loss = scale * sum_n loss_n (FM.py:36 / FNN.py:57): warp partials in warp order, CTA partials in CTA order
+    if (lane == 0) s_loss[threadIdx.x >> 5] = my_loss;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float s = 0.f;
+        for (int k = 0; k < 8; ++k) s += s_loss[k];
+        partial[blockIdx.x] = s;
+    }
+    if (!take_last_ticket(ticket, gridDim.x)) return;
+    ordered_reduce(partial, (int)gridDim.x, 1, 1, [&](int, float s) { loss_sum[0] = s * loss_scale; });
 }
 
 __global__ void __launch_bounds__(256)
@@ -48,33 +119,49 @@ out_bwd_kernel(const float* __restrict__ dlogit, const float* __restrict__ w, co
     }
 }
 
-// stage 1: CTA (bx, by) reduces rows [by*rows_per, ...) of columns [bx*32, +32) -> partial[by][h]
-__global__ void __launch_bounds__(256)
-col_wsum_stage1(const float* __restrict__ A, int lda, int N, int H, const float* __restrict__ wv, int rows_per,
-                float* __restrict__ partial) {
-    __shared__ float sm[8][33];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int h = blockIdx.x * 32 + lane;
-    const int r0 = blockIdx.y * rows_per;
-    const int r1 = min(N, r0 + rows_per);
-    float acc = 0.f;
-    if (h < H)
-        for (int n = r0 + warp; n < r1; n += 8) acc = fmaf(wv ? __ldg(wv + n) : 1.f, A[(int64_t)n * lda + h], acc);
-    sm[warp][lane] = acc;
-    __syncthreads();
-    if (warp == 0 && h < H) {
-        float s = 0.f;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) s += sm[k][lane];
-        partial[(int64_t)blockIdx.y * H + h] = s;
+// out[h] = sum_n (wv ? wv[n] : 1) * A[n,h]
+__global__ void __launch_bounds__(kRedThreads)
+col_wsum_kernel(const float* __restrict__ A, int lda, int N, int H, const float* __restrict__ wv, int rows_per,
+                float* __restrict__ partial, unsigned* __restrict__ ticket, float* __restrict__ out) {
+    const int r0 = blockIdx.x * rows_per, r1 = min(N, r0 + rows_per);
+    for (int h = threadIdx.x; h < H; h += kRedThreads) {
+        float acc = 0.f;
+#pragma unroll 8
+        for (int n = r0; n < r1; ++n) acc = fmaf(wv ? __ldg(wv + n) : 1.f, A[(int64_t)n * lda + h], acc);
+        partial[(int64_t)blockIdx.x * H + h] = acc;
     }
+    if (!take_last_ticket(ticket, gridDim.x)) return;
+    ordered_reduce(partial, (int)gridDim.x, H, H, [&](int h, float s) { out[h] = s; });
 }
-__global__ void col_wsum_stage2(const float* __restrict__ partial, int S, int H, float* __restrict__ out) {
-    const int h = blockIdx.x * blockDim.x + threadIdx.x;
-    if (h >= H) return;
-    float s = 0.f;
-    for (int k = 0; k < S; ++k) s += partial[(int64_t)k * H + h];
-    out[h] = s;
+
+// backward of the output unit in one launch (FNN.py:54-63 / FNN_wnzh.py:169-174 differentiated):
+//   da[n,h] = dlogit[n]*w[h] * mask * act'(a/mask);  gw[h] = sum_n dlogit[n]*a[n,h];  gb = sum_n dlogit[n]
+__global__ void __launch_bounds__(kRedThreads)
+out_bwd_fused_kernel(const float* __restrict__ dlogit, const float* __restrict__ w, const float* __restrict__ a, int lda,
+                     int N, int H, int act, const float* __restrict__ mask, int ldmask, float* __restrict__ da, int ldda,
+                     int rows_per, float* __restrict__ partial, unsigned* __restrict__ ticket,
+                     float* __restrict__ gw, float* __restrict__ gb) {
+    const int r0 = blockIdx.x * rows_per, r1 = min(N, r0 + rows_per);
+    const int HP = H + 1;
+    for (int h = threadIdx.x; h < H; h += kRedThreads) {
+        const float wh = __ldg(w + h);
+        float acc = 0.f;
+#pragma unroll 8
+        for (int n = r0; n < r1; ++n) {
+            const float dl = __ldg(dlogit + n), av = a[(int64_t)n * lda + h];
+            acc = fmaf(dl, av, acc);
+            const float mk = mask ? __ldg(mask + (int64_t)n * ldmask + h) : 1.f;
+            da[(int64_t)n * ldda + h] = mk != 0.f ? dl * wh * mk * act_bwd_from_out(act, mask ? av / mk : av) : 0.f;
+        }
+        partial[(int64_t)blockIdx.x * HP + h] = acc;
+    }
+    if (threadIdx.x == 0) {
+        float s = 0.f;
+        for (int n = r0; n < r1; ++n) s += __ldg(dlogit + n);
+        partial[(int64_t)blockIdx.x * HP + H] = s;
+    }
+    if (!take_last_ticket(ticket, gridDim.x)) return;
+    ordered_reduce(partial, (int)gridDim.x, HP, HP, [&](int h, float s) { if (h < H) gw[h] = s; else gb[0] = s; });
 }
 
 __global__ void __launch_bounds__(1024) vec_sum_kernel(const float* __restrict__ v, int N, float scale, float* __restrict__ out) {
@@ -95,9 +182,10 @@ __global__ void dense_sgd_kernel(float* __restrict__ p, const float* __restrict_
         p[i] = fmaf(p[i], decay, -lr * g[i]);
 }
 
-static int col_chunks(int N, int* rows_per) {
-    int rp = (N + 127) / 128;
-    if (rp < 256) rp = 256;
+// row blocks of the single-launch reductions: at most kRedMaxBlocks CTAs, at least 32 rows each
+static int red_blocks(int N, int* rows_per) {
+    int rp = (N + kRedMaxBlocks - 1) / kRedMaxBlocks;
+    if (rp < 32) rp = 32;
     *rows_per = rp;
     return (N + rp - 1) / rp;
 }
@@ -106,15 +194,46 @@ static int col_chunks(int N, int* rows_per) {
 
 using namespace dctr;
 
+extern "C" size_t dctr_reduce_workspace(int N, int H) {
+    if (N < 1) N = 1;
+    if (H < 1) H = 1;
+    int rp;
+    const int S = red_blocks(N, &rp);
+    const size_t rows = (size_t)(S > kNumSMs * 8 ? S : kNumSMs * 8);     // also covers out_xent_fwd's CTA partials
+    return 16 + rows * (size_t)(H + 1) * sizeof(float);
+}
+
 extern "C" int dctr_out_xent_fwd(const float* a, int lda, int N, int H, const float* w, const float* b,
                                  const float* y, float gscale, float* logit, float* pred, float* loss_n,
-                                 float* dlogit, void* stream) {
+                                 float* dlogit, float loss_scale, float* loss_sum, void* workspace,
+                                 size_t workspace_bytes, void* stream) {
     DCTR_REQUIRE(a && w && N >= 0 && H > 0 && lda >= H, "out_xent_fwd: bad arguments");
+    DCTR_REQUIRE(!loss_sum || (y && workspace && workspace_bytes >= dctr_reduce_workspace(N, 1)),
+                 "out_xent_fwd: the loss sum needs labels and a dctr_reduce_workspace(N, 1) workspace");
     if (N == 0) return DCTR_OK;
     int blocks = ceil_div(N, 8);
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    out_xent_fwd_kernel<<<blocks, 256, 0, as_stream(stream)>>>(a, lda, N, H, w, b, y, gscale, logit, pred, loss_n, dlogit);
+    unsigned* ticket = static_cast<unsigned*>(workspace);
+    float* partial = workspace ? reinterpret_cast<float*>(ticket + 4) : nullptr;
+    out_xent_fwd_kernel<<<blocks, 256, 0, as_stream(stream)>>>(a, lda, N, H, w, b, y, gscale, logit, pred, loss_n, dlogit,
+                                                                loss_scale, loss_sum, partial, ticket);
     return check_launch("out_xent_fwd_kernel");
+}
+
+extern "C" int dctr_out_bwd_fused(const float* dlogit, const float* w, const float* a, int lda, int N, int H, int act,
+                                  const float* mask, int ldmask, float* da, int ldda, float* gw, float* gb,
+                                  void* workspace, size_t workspace_bytes, void* stream) {
+    DCTR_REQUIRE(dlogit && w && a && da && gw && gb && workspace && N > 0 && H > 0, "out_bwd_fused: bad arguments");
+    if (workspace_bytes < dctr_reduce_workspace(N, H)) {
+        set_error("out_bwd_fused: workspace %zu < %zu", workspace_bytes, dctr_reduce_workspace(N, H));
+        return DCTR_EWORKSPACE;
+    }
+    int rp;
+    const int S = red_blocks(N, &rp);
+    unsigned* ticket = static_cast<unsigned*>(workspace);
+    out_bwd_fused_kernel<<<S, kRedThreads, 0, as_stream(stream)>>>(dlogit, w, a, lda, N, H, act, mask, ldmask, da, ldda, rp,
+                                                                  reinterpret_cast<float*>(ticket + 4), ticket, gw, gb);
+    return check_launch("out_bwd_fused_kernel");
 }
 
 extern "C" int dctr_out_bwd(const float* dlogit, const float* w, const float* a, int lda, int N, int H, int act,
@@ -127,27 +246,20 @@ extern "C" int dctr_out_bwd(const float* dlogit, const float* w, const float* a,
     return check_launch("out_bwd_kernel");
 }
 
-extern "C" size_t dctr_col_wsum_workspace(int N, int H) {
-    int rp;
-    const int S = col_chunks(N > 0 ? N : 1, &rp);
-    return (size_t)S * (size_t)(H > 0 ? H : 1) * sizeof(float);
-}
+extern "C" size_t dctr_col_wsum_workspace(int N, int H) { return dctr_reduce_workspace(N, H); }
 
-extern "C" int dctr_col_wsum(const float* A, int lda, int N, int H, const float* wv, float* out, void* partial,
-                             size_t partial_bytes, void* stream) {
-    DCTR_REQUIRE(A && out && partial && N > 0 && H > 0, "col_wsum: bad arguments");
-    if (partial_bytes < dctr_col_wsum_workspace(N, H)) {
-        set_error("col_wsum: workspace %zu < %zu", partial_bytes, dctr_col_wsum_workspace(N, H));
+extern "C" int dctr_col_wsum(const float* A, int lda, int N, int H, const float* wv, float* out, void* workspace,
+                             size_t workspace_bytes, void* stream) {
+    DCTR_REQUIRE(A && out && workspace && N > 0 && H > 0, "col_wsum: bad arguments");
+    if (workspace_bytes < dctr_reduce_workspace(N, H)) {
+        set_error("col_wsum: workspace %zu < %zu", workspace_bytes, dctr_reduce_workspace(N, H));
         return DCTR_EWORKSPACE;
     }
     int rp;
-    const int S = col_chunks(N, &rp);
-    dim3 grid(ceil_div(H, 32), S);
-    col_wsum_stage1<<<grid, 256, 0, as_stream(stream)>>>(A, lda, N, H, wv, rp, static_cast<float*>(partial));
-    int rc = check_launch("col_wsum_stage1");
-    if (rc) return rc;
-    col_wsum_stage2<<<ceil_div(H, 128), 128, 0, as_stream(stream)>>>(static_cast<const float*>(partial), S, H, out);
-    return check_launch("col_wsum_stage2");
+    const int S = red_blocks(N, &rp);
+    unsigned* ticket = static_cast<unsigned*>(workspace);
+    col_wsum_kernel<<<S, kRedThreads, 0, as_stream(stream)>>>(A, lda, N, H, wv, rp, reinterpret_cast<float*>(ticket + 4), ticket, out);
+    return check_launch("col_wsum_kernel");
 }
 
 extern "C" int dctr_vec_sum(const float* v, int N, float scale, float* out, void* stream) {

@@ -92,7 +92,8 @@ class StepEngine:
             self.splits.append(s)
             ws_elems = max(ws_elems, s * K * self.ldw[l])
         self.splitk_ws = torch.zeros(ws_elems, **f32)
-        self.col_ws = torch.zeros(max(16, L.lib().dctr_col_wsum_workspace(N, maxw)), dtype=torch.uint8, device=self.dev)
+        # workspace of the single-launch reductions (ticket + CTA partials): zero-filled once, left zeroed by the kernels
+        self.col_ws = torch.zeros(L.lib().dctr_reduce_workspace(N, maxw), dtype=torch.uint8, device=self.dev)
         self.side = torch.cuda.Stream(device=self.dev)
         self.wts_are_ones = True
 
@@ -154,11 +155,11 @@ class StepEngine:
                    p(self.W(l)), self.ldw[l], p(self.ins[l + 1]), self.ldi[l + 1], L.EPI_FWD, L.ACT[self.act],
                    p(self.b(l)), None, 0, mp, mld, 1, st)
         last = self.nl - 1
+        # logit / pred / per-sample loss / dlogit and the reduced loss in one launch
         L.call("dctr_out_xent_fwd", p(self.ins[last]), self.ldi[last], N, self.widths[last], p(self.W(last)),
                p(self.b(last)), p(self.y) if with_loss else None, float(gscale), p(self.logit), p(self.pred),
-               p(self.loss_n), p(self.dlogit), st)
-        if with_loss:
-            L.call("dctr_vec_sum", p(self.loss_n), N, float(gscale), p(self.loss), st)
+               p(self.loss_n), p(self.dlogit), float(gscale), p(self.loss) if with_loss else None,
+               p(self.col_ws), self.col_ws.numel(), st)
 
     def backward(self):
         """Fills self.grads (dense) and leaves d loss / d z in self.dbuf[k]; returns that buffer."""
@@ -167,13 +168,13 @@ class StepEngine:
         last = self.nl - 1
         H = self.widths[last]
         cw, cwb = p(self.col_ws), self.col_ws.numel()
-        L.call("dctr_col_wsum", p(self.ins[last]), self.ldi[last], N, H, p(self.dlogit), p(self.W(last, self.grads)), cw, cwb, st)
-        L.call("dctr_vec_sum", p(self.dlogit), N, 1.0, p(self.b(last, self.grads)), st)
         cur = 0
         mp, mld = self._mask(last)
         ldd = self.dbuf[0].stride(0)
-        L.call("dctr_out_bwd", p(self.dlogit), p(self.W(last)), p(self.ins[last]), self.ldi[last], N, H,
-               L.ACT[self.act], mp, mld, p(self.dbuf[cur]), ldd, st)
+        # d(last hidden), d w_out and d b_out in one launch
+        L.call("dctr_out_bwd_fused", p(self.dlogit), p(self.W(last)), p(self.ins[last]), self.ldi[last], N, H,
+               L.ACT[self.act], mp, mld, p(self.dbuf[cur]), ldd, p(self.W(last, self.grads)), p(self.b(last, self.grads)),
+               cw, cwb, st)
         for l in range(last - 1, -1, -1):
             K, Hl = self.widths[l], self.widths[l + 1]
             dpre = self.dbuf[cur]

@@ -139,16 +139,26 @@ int dctr_gemm_tc(int layout, int M, int N, int K, const float* A, int lda, const
 
 /* ---- K5: output unit + loss (FNN.py:54-63, FNN_wnzh.py:169-173) --------------------------------
  *   logit[n] = <a[n,0:H], w> + b ; pred = sigmoid ; loss_n = stable xent ; dlogit[n] = (pred-y)*gscale */
+/* loss_sum != NULL additionally writes loss_scale * sum_n loss_n in the same launch (CTA partials folded in CTA order by
+ * the CTA that takes the last ticket).  workspace: dctr_reduce_workspace(N, 1) bytes, ZERO-FILLED ONCE before first use;
+ * the kernels leave it ready for the next launch (CUDA-graph replayable). */
+size_t dctr_reduce_workspace(int N, int H);
 int dctr_out_xent_fwd(const float* a, int lda, int N, int H, const float* w, const float* b, const float* y,
-                      float gscale, float* logit, float* pred, float* loss_n, float* dlogit, void* stream);
+                      float gscale, float* logit, float* pred, float* loss_n, float* dlogit,
+                      float loss_scale, float* loss_sum, void* workspace, size_t workspace_bytes, void* stream);
 /*   da[n,h] = dlogit[n]*w[h] * mask * act'(a/mask)   (backward through the last hidden activation) */
 int dctr_out_bwd(const float* dlogit, const float* w, const float* a, int lda, int N, int H, int act,
                  const float* mask, int ldmask, float* da, int ldda, void* stream);
-/*   out[h] = sum_n (wv? wv[n]:1) * A[n,h]   two-stage fixed-order column reduction (bias / last-layer grads);
- *   partial: float32 workspace of dctr_col_wsum_workspace(N,H) bytes */
+/*   the same plus the output unit's own gradients in ONE launch: gw[h] = sum_n dlogit[n]*a[n,h], gb = sum_n dlogit[n]
+ *   (fixed-order two-level sum).  workspace: dctr_reduce_workspace(N, H) bytes, zero-filled once. */
+int dctr_out_bwd_fused(const float* dlogit, const float* w, const float* a, int lda, int N, int H, int act,
+                       const float* mask, int ldmask, float* da, int ldda, float* gw, float* gb,
+                       void* workspace, size_t workspace_bytes, void* stream);
+/*   out[h] = sum_n (wv? wv[n]:1) * A[n,h]   single-launch fixed-order column reduction (bias / last-layer grads);
+ *   workspace: dctr_col_wsum_workspace(N,H) bytes, zero-filled once */
 size_t dctr_col_wsum_workspace(int N, int H);
 int dctr_col_wsum(const float* A, int lda, int N, int H, const float* wv, float* out,
-                  void* partial, size_t partial_bytes, void* stream);
+                  void* workspace, size_t workspace_bytes, void* stream);
 /*   out[0] = sum_n v[n]  (fixed order, one CTA) -- loss = reduce_sum(log_loss) (FM.py:36) */
 int dctr_vec_sum(const float* v, int N, float scale, float* out, void* stream);
 

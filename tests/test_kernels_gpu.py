@@ -352,22 +352,40 @@ def test_output_unit_and_reductions(L):
     f = lambda: torch.zeros(N, device="cuda")
     logit, pred, loss_n, dl = f(), f(), f(), f()
     ad, wd = dev(a), dev(w)
-    L.call("dctr_out_xent_fwd", ad.data_ptr(), r4(H), N, H, wd.data_ptr(), dev(np.array([0.2], np.float32)).data_ptr(),
-           dev(y).data_ptr(), 1.0, logit.data_ptr(), pred.data_ptr(), loss_n.data_ptr(), dl.data_ptr(), None)
-    close(logit.cpu(), z, atol=1e-5)
-    close(loss_n.cpu(), O.xent_with_logits(z, y), atol=1e-5)
-    close(dl.cpu(), O.sigmoid(z) - y, atol=1e-5)
+    ws = torch.zeros(L.lib().dctr_reduce_workspace(N, H), dtype=torch.uint8, device="cuda")
+    lsum = torch.zeros(1, device="cuda")
+    for rep in range(2):        # twice: the ticket workspace must come back ready for the next launch
+        L.call("dctr_out_xent_fwd", ad.data_ptr(), r4(H), N, H, wd.data_ptr(), dev(np.array([0.2], np.float32)).data_ptr(),
+               dev(y).data_ptr(), 1.0, logit.data_ptr(), pred.data_ptr(), loss_n.data_ptr(), dl.data_ptr(), 0.5, lsum.data_ptr(),
+               ws.data_ptr(), ws.numel(), None)
+        close(logit.cpu(), z, atol=1e-5)
+        close(loss_n.cpu(), O.xent_with_logits(z, y), atol=1e-5)
+        close(dl.cpu(), O.sigmoid(z) - y, atol=1e-5)
+        close(lsum.cpu(), [0.5 * O.xent_with_logits(z, y).sum()], atol=1e-4)
     out = torch.zeros(1, device="cuda")
     L.call("dctr_vec_sum", loss_n.data_ptr(), N, 0.5, out.data_ptr(), None)
     close(out.cpu(), [0.5 * loss_n.cpu().numpy().astype(np.float64).sum()])
-    ws = torch.zeros(L.lib().dctr_col_wsum_workspace(N, H), dtype=torch.uint8, device="cuda")
     gw = torch.zeros(H, device="cuda")
-    L.call("dctr_col_wsum", ad.data_ptr(), r4(H), N, H, dl.data_ptr(), gw.data_ptr(), ws.data_ptr(), ws.numel(), None)
-    close(gw.cpu(), (dl.cpu().numpy().astype(np.float64)[:, None] * a[:, :H]).sum(0), atol=1e-4)
+    want_gw = (dl.cpu().numpy().astype(np.float64)[:, None] * a[:, :H]).sum(0)
+    for rep in range(2):
+        L.call("dctr_col_wsum", ad.data_ptr(), r4(H), N, H, dl.data_ptr(), gw.data_ptr(), ws.data_ptr(), ws.numel(), None)
+        close(gw.cpu(), want_gw, atol=1e-4)
     da = torch.zeros(N, r4(H), device="cuda")
     L.call("dctr_out_bwd", dl.data_ptr(), wd.data_ptr(), ad.data_ptr(), r4(H), N, H, L.ACT["tanh"], None, 0, da.data_ptr(), r4(H), None)
-    tt = np.tanh(rng.normal(0, 1, 1))  # unused; keeps rng advancing identical across runs
-    close(da.cpu().numpy()[:, :H], dl.cpu().numpy().astype(np.float64)[:, None] * w * (1 - a[:, :H].astype(np.float64) ** 2), atol=1e-5)
+    want_da = dl.cpu().numpy().astype(np.float64)[:, None] * w * (1 - a[:, :H].astype(np.float64) ** 2)
+    close(da.cpu().numpy()[:, :H], want_da, atol=1e-5)
+    # fused: da + gw + gb in one launch, with a dropout-style mask
+    mask = ((rng.random((N, r4(H))) < 0.7) / 0.7).astype(np.float32)
+    am = (a * mask).astype(np.float32)                      # stored forward output = act * mask
+    amd, md = dev(am), dev(mask)
+    da2, gw2, gb2 = torch.zeros(N, r4(H), device="cuda"), torch.zeros(H, device="cuda"), torch.zeros(1, device="cuda")
+    for rep in range(2):
+        L.call("dctr_out_bwd_fused", dl.data_ptr(), wd.data_ptr(), amd.data_ptr(), r4(H), N, H, L.ACT["tanh"], md.data_ptr(), r4(H),
+               da2.data_ptr(), r4(H), gw2.data_ptr(), gb2.data_ptr(), ws.data_ptr(), ws.numel(), None)
+        dl64 = dl.cpu().numpy().astype(np.float64)
+        close(gw2.cpu(), (dl64[:, None] * am[:, :H]).sum(0), atol=1e-4)
+        close(gb2.cpu(), [dl64.sum()], atol=1e-4)
+        close(da2.cpu().numpy()[:, :H], dl64[:, None] * w * mask[:, :H] * (1 - a[:, :H].astype(np.float64) ** 2) * (mask[:, :H] != 0), atol=1e-5)
     p = dev(rng.normal(0, 1, 1001).astype(np.float32)); g = dev(rng.normal(0, 1, 1001).astype(np.float32))
     want = p.cpu().numpy().astype(np.float64) * 0.99 - 0.1 * g.cpu().numpy()
     L.call("dctr_dense_sgd", p.data_ptr(), g.data_ptr(), 1001, 0.1, 0.99, None)
