@@ -1,8 +1,9 @@
 // K6a: stable LSD radix sort of (row id, position) pairs -- the deterministic ordering step of the
-// sparse update.  Hand-written (no CUB): per pass  histogram -> exclusive scan -> stable scatter.
-// Stability inside a tile comes from ranking 32-element chunks with __match_any_sync and scanning the
-// per-chunk digit counts in chunk order, so equal rows keep their (sample, field) order: that is what
-// lets SEQ_DECAY reproduce the sample-major loop of FNN_wnzh.py:300-306 and makes SUM bit-reproducible.
+// sparse update.  Hand-written (no CUB): one histogram kernel for all digits, then ONE kernel per 8-bit digit
+// (tile ranking + decoupled look-back + scatter).  Stability inside a tile comes from ranking 32-key rows with
+// __match_any_sync on top of per-warp running digit counters, across tiles from the look-back running in tile
+// order, so equal rows keep their (sample, field) order: that is what lets SEQ_DECAY reproduce the sample-major
+// loop of FNN_wnzh.py:300-306 and makes SUM bit-reproducible.
 #include "common.cuh"
 
 namespace dctr {
@@ -10,127 +11,144 @@ namespace dctr {
 constexpr int kSortThreads = 256;
 constexpr int kSortItems = 8;                       // chunks per warp
 constexpr int kSortTile = kSortThreads * kSortItems;  // 2048 elements per CTA
-constexpr int kSortChunks = kSortTile / 32;         // 64
 constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
 
 __device__ __forceinline__ int digit_of(int32_t key, int shift) { return (key >> shift) & (kRadix - 1); }
 
+constexpr int kMaxPasses = 4;
+enum : unsigned { kFlagAgg = 1u, kFlagPrefix = 2u };       // tile status = (count << 2) | flag
+
+// digit histograms of ALL passes in one read of the keys (they do not depend on the order of the list)
 __global__ void __launch_bounds__(kSortThreads)
-sort_hist_kernel(const int32_t* __restrict__ keys, int64_t M, int shift, int num_tiles, int32_t* __restrict__ hist) {
-    __shared__ int32_t h[kRadix];
-    h[threadIdx.x] = 0;
+sort_hist_kernel(const int32_t* __restrict__ keys, int64_t M, int passes, unsigned* __restrict__ ghist) {
+    __shared__ unsigned h[kMaxPasses][kRadix];
+    for (int p = 0; p < passes; ++p) h[p][threadIdx.x] = 0;
     __syncthreads();
     const int64_t base = (int64_t)blockIdx.x * kSortTile;
 #pragma unroll
     for (int j = 0; j < kSortItems; ++j) {
         const int64_t i = base + j * kSortThreads + threadIdx.x;
-        if (i < M) atomicAdd(&h[digit_of(keys[i], shift)], 1);
+        if (i < M) {
+            const int32_t k = keys[i];
+            for (int p = 0; p < passes; ++p) atomicAdd(&h[p][digit_of(k, p * kRadixBits)], 1u);
+        }
     }
     __syncthreads();
-    hist[(int64_t)threadIdx.x * num_tiles + blockIdx.x] = h[threadIdx.x];
-}
-
-// one CTA per digit: exclusive scan of that digit's per-tile counts (in place, tile order) + the digit total.
-// The scatter kernel turns the 256 totals into digit base offsets itself, so the scan is parallel over digits.
-__global__ void __launch_bounds__(1024) sort_scan_kernel(int32_t* __restrict__ hist, int num_tiles, int32_t* __restrict__ totals) {
-    __shared__ int32_t warp_tot[32];
-    __shared__ int32_t carry_s;
-    int32_t* row = hist + (int64_t)blockIdx.x * num_tiles;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) carry_s = 0;
-    __syncthreads();
-    for (int base = 0; base < num_tiles; base += 1024) {
-        const int i = base + tid;
-        const int32_t v = i < num_tiles ? row[i] : 0;
-        int32_t incl = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int32_t u = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += u;
-        }
-        if (lane == 31) warp_tot[warp] = incl;
-        __syncthreads();
-        if (warp == 0) {
-            const int32_t w = warp_tot[lane];
-            int32_t wi = w;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int32_t u = __shfl_up_sync(0xffffffffu, wi, o);
-                if (lane >= o) wi += u;
-            }
-            warp_tot[lane] = wi - w;
-        }
-        __syncthreads();
-        const int32_t carry = carry_s;
-        if (i < num_tiles) row[i] = carry + warp_tot[warp] + incl - v;
-        __syncthreads();
-        if (tid == 1023) carry_s = carry + warp_tot[31] + incl;
-        __syncthreads();
+    for (int p = 0; p < passes; ++p) {
+        const unsigned v = h[p][threadIdx.x];
+        if (v) atomicAdd(&ghist[p * kRadix + threadIdx.x], v);      // integer atomics: the totals are order-independent
     }
-    if (tid == 0) totals[blockIdx.x] = carry_s;
 }
 
+// One pass of the LSD sort in ONE kernel ("onesweep"): a CTA takes the next tile (ticket), ranks its 2048 keys stably,
+// publishes its per-digit counts, obtains the counts of all earlier tiles by decoupled look-back (thread d walks digit
+// d back to the nearest tile whose inclusive prefix is published), and scatters.  Tiles are handed out in ticket order,
+// so a CTA only ever waits on tiles that are already running: no deadlock, and the output does not depend on timing.
 // pos_in == nullptr: payload is the element index itself (first pass)
 __global__ void __launch_bounds__(kSortThreads)
-sort_scatter_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict__ pos_in, int64_t M, int shift,
-                    int num_tiles, const int32_t* __restrict__ hist_scanned, const int32_t* __restrict__ totals,
-                    int32_t* __restrict__ keys_out, int32_t* __restrict__ pos_out) {
-    __shared__ unsigned short cnt[kSortChunks][kRadix];  // 32 KB: per-chunk digit counts -> exclusive prefix
-    __shared__ int32_t gbase[kRadix];
+sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict__ pos_in, int64_t M, int shift,
+                 const unsigned* __restrict__ ghist, unsigned* __restrict__ ticket, volatile unsigned* __restrict__ status,
+                 int32_t* __restrict__ keys_out, int32_t* __restrict__ pos_out) {
+    __shared__ unsigned cnt[kSortThreads / 32][kRadix];   // per-warp digit counts -> exclusive prefix over the warps
+    __shared__ unsigned gbase[kRadix];
+    __shared__ unsigned lbase[kRadix];
+    __shared__ unsigned wsum[kSortThreads / 32], lsum[kSortThreads / 32];
+    __shared__ int32_t skey[kSortTile], spos[kSortTile];
+    __shared__ unsigned s_tile;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < kSortChunks * kRadix / 2; i += kSortThreads) reinterpret_cast<uint32_t*>(&cnt[0][0])[i] = 0u;
-    {   // digit base = exclusive scan of the 256 digit totals (one value per thread)
-        __shared__ int32_t wsum[8];
-        const int32_t t = totals[tid];
-        int32_t incl = t;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int32_t u = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += u;
+    for (int w = 0; w < kSortThreads / 32; ++w) cnt[w][tid] = 0;
+    __syncthreads();
+    const unsigned tile = s_tile;
+    const int64_t base = (int64_t)tile * kSortTile;
+
+    // ---- stable ranks inside the tile: warp w owns rows w*8 .. w*8+7 of 32 consecutive keys ----
+    int32_t key[kSortItems];
+    unsigned rank[kSortItems];
+#pragma unroll
+    for (int j = 0; j < kSortItems; ++j) {
+        const int64_t i = base + (warp * kSortItems + j) * 32 + lane;
+        const bool valid = i < M;
+        key[j] = valid ? keys_in[i] : 0;
+        const int dg = digit_of(key[j], shift);
+        // lanes holding the same digit: eight ballots (one per digit bit) instead of __match_any_sync, whose cost grows
+        // with the number of distinct values in the warp
+        unsigned peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int bit = 0; bit < kRadixBits; ++bit) {
+            const unsigned m = __ballot_sync(0xffffffffu, (dg >> bit) & 1);
+            peers &= ((dg >> bit) & 1) ? m : ~m;
         }
-        if (lane == 31) wsum[warp] = incl;
-        __syncthreads();
-        int32_t off = 0;
-        for (int w = 0; w < warp; ++w) off += wsum[w];
-        gbase[tid] = off + incl - t + hist_scanned[(int64_t)tid * num_tiles + blockIdx.x];
+        const int leader = __ffs(peers) - 1;
+        unsigned before = 0;
+        if (valid && lane == leader) { before = cnt[warp][dg]; cnt[warp][dg] = before + __popc(peers); }
+        before = __shfl_sync(0xffffffffu, before, valid ? leader : lane);
+        rank[j] = before + __popc(peers & ((1u << lane) - 1u));
+        __syncwarp();
     }
     __syncthreads();
 
-    const int64_t base = (int64_t)blockIdx.x * kSortTile;
-    int32_t key[kSortItems];
-    int rank[kSortItems];
+    // ---- thread d owns digit d: prefix over the warps, publish, look back ----
+    unsigned total = 0;
 #pragma unroll
-    for (int j = 0; j < kSortItems; ++j) {
-        const int chunk = warp * kSortItems + j;
-        const int64_t i = base + chunk * 32 + lane;
-        const bool valid = i < M;
-        key[j] = valid ? keys_in[i] : 0;
-        const int dg = valid ? digit_of(key[j], shift) : kRadix + lane;  // invalid lanes: private groups
-        const unsigned peers = __match_any_sync(0xffffffffu, dg);
-        rank[j] = __popc(peers & ((1u << lane) - 1u));
-        if (valid && rank[j] == 0) cnt[chunk][dg] = (unsigned short)__popc(peers);
+    for (int w = 0; w < kSortThreads / 32; ++w) { const unsigned v = cnt[w][tid]; cnt[w][tid] = total; total += v; }
+    volatile unsigned* mine = status + (int64_t)tile * kRadix + tid;
+    unsigned excl = 0;
+    if (tile == 0) {
+        *mine = (total << 2) | kFlagPrefix;
+    } else {
+        *mine = (total << 2) | kFlagAgg;
+        for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
+            unsigned v;
+            do { v = status[t * kRadix + tid]; } while ((v & 3u) == 0u);
+            excl += v >> 2;
+            if (v & kFlagPrefix) break;
+        }
+        *mine = ((excl + total) << 2) | kFlagPrefix;
+    }
+    // ---- exclusive scans over the 256 digits: of the global totals (digit base) and of this tile's totals (local base) ----
+    unsigned lbase_d;
+    {
+        const unsigned t = ghist[tid];
+        unsigned incl = t, lincl = total;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned u = __shfl_up_sync(0xffffffffu, incl, o), lu = __shfl_up_sync(0xffffffffu, lincl, o);
+            if (lane >= o) { incl += u; lincl += lu; }
+        }
+        if (lane == 31) { wsum[warp] = incl; lsum[warp] = lincl; }
+        __syncthreads();
+        unsigned off = 0, loff = 0;
+        for (int w = 0; w < warp; ++w) { off += wsum[w]; loff += lsum[w]; }
+        lbase_d = loff + lincl - total;
+        lbase[tid] = lbase_d;
+        // destination of the tile's digit-d run, minus its offset inside the tile: dst = gbase[d] + (index in sorted tile)
+        gbase[tid] = off + incl - t + excl - lbase_d;
     }
     __syncthreads();
-    {   // thread `tid` owns digit `tid`: exclusive scan over the chunks, in chunk order
-        unsigned run = 0;
-#pragma unroll 8
-        for (int c = 0; c < kSortChunks; ++c) {
-            const unsigned v = cnt[c][tid];
-            cnt[c][tid] = (unsigned short)run;
-            run += v;
+    // ---- reorder the tile in shared memory (stable), then write out runs: consecutive threads -> consecutive addresses ----
+#pragma unroll
+    for (int j = 0; j < kSortItems; ++j) {
+        const int64_t i = base + (warp * kSortItems + j) * 32 + lane;
+        if (i < M) {
+            const int dg = digit_of(key[j], shift);
+            const unsigned lp = lbase[dg] + cnt[warp][dg] + rank[j];
+            skey[lp] = key[j];
+            spos[lp] = pos_in ? pos_in[i] : (int32_t)i;
         }
     }
     __syncthreads();
+    const int nvalid = (int)min((int64_t)kSortTile, M - base);
 #pragma unroll
     for (int j = 0; j < kSortItems; ++j) {
-        const int chunk = warp * kSortItems + j;
-        const int64_t i = base + chunk * 32 + lane;
-        if (i < M) {
-            const int dg = digit_of(key[j], shift);
-            const int64_t dst = (int64_t)gbase[dg] + cnt[chunk][dg] + rank[j];
-            keys_out[dst] = key[j];
-            pos_out[dst] = pos_in ? pos_in[i] : (int32_t)i;
+        const int t = j * kSortThreads + tid;
+        if (t < nvalid) {
+            const int32_t k = skey[t];
+            const unsigned dst = gbase[digit_of(k, shift)] + (unsigned)t;      // modulo 2^32: gbase may have wrapped below 0
+            keys_out[dst] = k;
+            pos_out[dst] = spos[t];
         }
     }
 }
@@ -145,16 +163,18 @@ static int num_passes(int64_t X) {
 
 using namespace dctr;
 
+static size_t sort_header_words(int64_t tiles) { return (size_t)kMaxPasses * kRadix + 16 + (size_t)kMaxPasses * tiles * kRadix; }
+
 extern "C" size_t dctr_sort_rows_workspace(int64_t M) {
     if (M <= 0) return 16;
     const int64_t tiles = (M + kSortTile - 1) / kSortTile;
     const int64_t m4 = (M + 3) / 4 * 4;
-    return (size_t)(2 * m4 + (int64_t)kRadix * tiles + kRadix) * sizeof(int32_t);
+    return (size_t)(2 * m4) * sizeof(int32_t) + sort_header_words(tiles) * sizeof(unsigned);
 }
 
 extern "C" int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t* sorted_rows, int32_t* sorted_pos,
                               void* workspace, size_t workspace_bytes, void* stream) {
-    DCTR_REQUIRE(M >= 0 && M < ((int64_t)1 << 31) && X > 0 && X <= ((int64_t)1 << 31), "sort_rows: bad M/X");
+    DCTR_REQUIRE(M >= 0 && M < ((int64_t)1 << 30) && X > 0 && X <= ((int64_t)1 << 31), "sort_rows: bad M/X");
     if (M == 0) return DCTR_OK;
     DCTR_REQUIRE(ids && sorted_rows && sorted_pos && workspace, "sort_rows: null pointer");
     if (workspace_bytes < dctr_sort_rows_workspace(M)) {
@@ -165,26 +185,24 @@ extern "C" int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t*
     const int64_t m4 = (M + 3) / 4 * 4;
     int32_t* alt_keys = static_cast<int32_t*>(workspace);
     int32_t* alt_pos = alt_keys + m4;
-    int32_t* hist = alt_pos + m4;
-    int32_t* totals = hist + (int64_t)kRadix * tiles;
+    unsigned* ghist = reinterpret_cast<unsigned*>(alt_pos + m4);       // [passes][256] digit totals
+    unsigned* tickets = ghist + kMaxPasses * kRadix;                    // [passes] tile tickets (padded to 16 words)
+    unsigned* status = tickets + 16;                                    // [passes][tiles][256] look-back state
     cudaStream_t st = as_stream(stream);
     const int passes = num_passes(X);
+    cudaMemsetAsync(ghist, 0, (size_t)(kMaxPasses * kRadix + 16 + (size_t)passes * tiles * kRadix) * sizeof(unsigned), st);
+    sort_hist_kernel<<<tiles, kSortThreads, 0, st>>>(ids, M, passes, ghist);
+    int rc = check_launch("sort_hist_kernel");
+    if (rc) return rc;
     const int32_t* kin = ids;
     const int32_t* pin = nullptr;
     for (int p = 0; p < passes; ++p) {
         const bool to_out = ((passes - p) & 1) == 1;
         int32_t* kout = to_out ? sorted_rows : alt_keys;
         int32_t* pout = to_out ? sorted_pos : alt_pos;
-        const int shift = p * kRadixBits;
-        sort_hist_kernel<<<tiles, kSortThreads, 0, st>>>(kin, M, shift, tiles, hist);
-        int rc = check_launch("sort_hist_kernel");
-        if (rc) return rc;
-        sort_scan_kernel<<<kRadix, 1024, 0, st>>>(hist, tiles, totals);
-        rc = check_launch("sort_scan_kernel");
-        if (rc) return rc;
-        sort_scatter_kernel<<<tiles, kSortThreads, 0, st>>>(kin, pin, M, shift, tiles, hist, totals, kout, pout);
-        rc = check_launch("sort_scatter_kernel");
-        if (rc) return rc;
+        sort_pass_kernel<<<tiles, kSortThreads, 0, st>>>(kin, pin, M, p * kRadixBits, ghist + p * kRadix, tickets + p,
+                                                         status + (size_t)p * tiles * kRadix, kout, pout);
+        if ((rc = check_launch("sort_pass_kernel"))) return rc;
         kin = kout;
         pin = pout;
     }
