@@ -28,6 +28,8 @@ WORKLOADS = {
     "fnn_op_l3_ipinyou": ("tf", 16, 1_000_000, 10, [800, 400, 200], "op", 4096),
     "fnn_ip_l7_ipinyou": ("tf", 16, 1_000_000, 10, [1000, 800, 600, 400, 200, 100, 50], "ip", 65536),
     "fnn_criteo": ("tf", 39, 1_636_608, 10, [400, 400], "none", 65536),
+    # BASELINE config 5: 26 categorical fields over a 10^8-row table, rows sharded over the ranks (row % world)
+    "fnn_criteo_sharded": ("tf", 26, 100_000_000, 10, [400, 400], "none", 65536),
 }
 
 
@@ -83,15 +85,15 @@ def make_pool(form, F, X, N, n_batches, seed):
             ids, wts = data.make_criteo_batch(rng, N, sizes)
             pool.append((ids, wts, (rng.random(N) < 0.05).astype(np.float32)))
         return pool, sizes
-    sizes = data.ipinyou_field_sizes(X)
+    sizes = data.scaled_criteo_cat_sizes(X + 13) if F == 26 else data.ipinyou_field_sizes(X)
     pool = []
     for _ in range(n_batches):
-        ids = data.make_field_batch(rng, N, sizes, 1.1)
+        ids = data.make_field_batch(rng, N, sizes, 1.05 if F == 26 else 1.1)
         pool.append((ids, np.ones((N, F), np.float32), (rng.random(N) < 0.05).astype(np.float32)))
     return pool, sizes
 
 
-def build_model(wl, N, seed=1234):
+def build_model(wl, N, seed=1234, shard=None):
     """Returns (model, train_fn(host ids, wts, y) -> (loss, preds)) through the reference-facing classes."""
     form, F, X, rank, hidden, cross, _ = WORKLOADS[wl]
     rng = np.random.default_rng(seed)
@@ -117,10 +119,10 @@ def build_model(wl, N, seed=1234):
         cat_sizes = data.CRITEO_CAT_SIZES if X == 13 + int(data.CRITEO_CAT_SIZES.sum()) else data.scaled_criteo_cat_sizes(X)
         n_num = 13
     else:
-        cat_sizes, n_num = data.ipinyou_field_sizes(X), 0
+        cat_sizes, n_num = data.scaled_criteo_cat_sizes(X + 13) if F == 26 else data.ipinyou_field_sizes(X), 0
     offsets = data.offsets_of(cat_sizes, n_num)
     m = cls(cat_sizes, offsets, N, [X, F, rank] + hidden + ["tanh"], ["uniform", -0.01, 0.01, list(range(1, 20)), None],
-            ["sgd", 1e-3, "sum"], [1.0], "train", N)
+            ["sgd", 1e-3, "sum"], [1.0], "train", N, shard=shard)
     for l in range(m.engine.nl):     # +-0.01 weights make every activation ~0: use fan-in scaling for a realistic step
         m.engine.W(l).uniform_(-1, 1).mul_(1.0 / np.sqrt(m.engine.widths[l]))
 
@@ -240,10 +242,14 @@ def run_b200(args, rank, world):
     wl = args.workload
     form, F, X, rank_k, hidden, cross, N = WORKLOADS[wl]
     N = args.batch or N
-    model, train = build_model(wl, N)
+    sharded = wl.endswith("_sharded")
+    model, train = build_model(wl, N, shard=(rank, world) if sharded else None)
     if world > 1:
         from deepctr_b200 import dist as ddist
-        ddist.attach(model, dist)
+        if sharded:
+            ddist.attach_sharded(model, dist, X)
+        else:
+            ddist.attach(model, dist)
     eng = model.engine
     pool, _ = make_pool(form, F, X, N, 8, seed=1234 + rank)
     dpool = [(torch.as_tensor(i.astype(np.int32)).cuda(), torch.as_tensor(w).cuda(), torch.as_tensor(y).cuda()) for i, w, y in pool]
@@ -368,7 +374,7 @@ def run_b200(args, rank, world):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl, "form": form, "fields": F, "rows": X, "rank": rank_k, "hidden": hidden, "cross": cross,
                    "batch_per_gpu": N, "global_batch": N * world, "l2": "flushed (512 MB write) before every timed step",
-                   "parallelism": "dp%d" % world if world > 1 else "single", "cuda_graph": bool(model.use_graph)},
+                   "parallelism": ("rowshard%d" if sharded else "dp%d") % world if world > 1 else "single", "cuda_graph": bool(model.use_graph)},
         "warm_l2": {"ms_per_step": warm_ms / K, "value": N * world * K / (warm_ms * 1e-3)},
         "e2e": {"value": N * world * K / e2e_s, "unit": "samples/s", "h2d_bytes_per_step": model.h2d_bytes,
                 "d2h_bytes_per_step": model.d2h_bytes, "ms_per_step": e2e_s / K * 1e3},

@@ -234,6 +234,18 @@ arrange_fields_kernel(const int32_t* __restrict__ feats, const int32_t* __restri
     }
 }
 
+// Row gather out[i, :] = table[ids[i], :] -- the owner-side lookup of the row-sharded table and the
+// permutation of gradient rows into exchange order.  One thread per 128-bit piece of a row.
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const int32_t* __restrict__ ids, const float4* __restrict__ table, int q, int64_t M, float4* __restrict__ out) {
+    const int64_t total = M * q;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = t / q;
+        const int c = (int)(t - i * q);
+        out[t] = __ldg(table + (int64_t)__ldg(ids + i) * q + c);
+    }
+}
+
 static int gather_grid(int N) {
     int blocks = ceil_div(N, kGatherWarps);
     int cap = kNumSMs * 8;  // 8 resident CTAs of 8 warps = 64 warps / SM
@@ -316,4 +328,15 @@ extern "C" int dctr_arrange_fields(const int32_t* feats, const int32_t* feat_fie
     DCTR_REQUIRE(feats && feat_field && ids && wts, "arrange_fields: null pointer");
     arrange_fields_kernel<<<ceil_div((int64_t)N * 32, 256), 256, 0, as_stream(stream)>>>(feats, feat_field, N, J, F, pad_row, ids, wts);
     return check_launch("arrange_fields_kernel");
+}
+
+extern "C" int dctr_gather_rows(const int32_t* ids, const float* table, int64_t X, int ld, int64_t M, float* out, void* stream) {
+    DCTR_REQUIRE(M >= 0 && X > 0 && ld > 0 && (ld & 3) == 0, "gather_rows: bad shape M=%lld ld=%d", (long long)M, ld);
+    if (M == 0) return DCTR_OK;
+    DCTR_REQUIRE(ids && table && out && ((uintptr_t)table & 15) == 0 && ((uintptr_t)out & 15) == 0, "gather_rows: null or unaligned pointer");
+    int blocks = ceil_div(M * (ld / 4), 256);
+    if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+    gather_rows_kernel<<<blocks, 256, 0, as_stream(stream)>>>(ids, reinterpret_cast<const float4*>(table), ld / 4, M,
+                                                              reinterpret_cast<float4*>(out));
+    return check_launch("gather_rows_kernel");
 }

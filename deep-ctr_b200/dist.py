@@ -7,7 +7,10 @@ concatenated (rank-major) global batch:
   sparse  all-gather of (ids, wts, per-sample embedding gradient); every rank then sorts the GLOBAL
           (row, position) list and folds it -- so replicated tables stay bit-identical across ranks and the
           sequential-decay semantics (FNN_wnzh.py:300-306) see the global sample order.
-The row-sharded table with id / embedding / gradient all-to-all (10^8 rows) is the next row of 8(e).
+For vocabularies too large to replicate (10^8 rows, BASELINE config 5) the table is ROW-SHARDED instead
+(ShardedStep): row g lives on rank g % world as local row g // world, and a step exchanges ids, embedding rows and
+gradient rows with three all-to-alls; the owner folds the received gradients in (source rank, sample, field) order,
+which is the global sample order, so the result equals the single-GPU step on the concatenated batch.
 The collectives below run on CPU tensors with gloo too, which is how tests/test_dist_cpu.py covers them.
 """
 import torch
@@ -108,6 +111,143 @@ class DataParallelStep(object):
             L.call("dctr_decay_sweep", L.ptr(e.table), e.X, e.ld, float(decay), self.g_rows.data_ptr(), self.GM, st)
         L.call("dctr_dense_sgd", L.ptr(e.params), L.ptr(e.grads), 1, float(lr), float(decay), st)
         self._keep = (gids, gwts, gg, gs)
+
+
+# ======================================================================================================
+# row-sharded embedding table (third row)
+# ======================================================================================================
+def plan_exchange(flat_ids, world, stable_argsort):
+    """Bucket the (sample, field) slots of one rank by owner.  flat_ids: [M] global row ids.
+    Returns perm [M] (slots ordered by owner rank, original order kept inside a bucket -- `stable_argsort(keys)` must
+    be stable), counts [world] (slots per owner) and send_rows [M] (owner-local row ids, in perm order)."""
+    owner = flat_ids % world
+    perm = stable_argsort(owner)
+    counts = torch.bincount(owner.long(), minlength=world)
+    send_rows = torch.div(flat_ids, world, rounding_mode="floor")[perm.long()]
+    return perm, counts, send_rows
+
+
+def all_to_all_rows(dist, send, send_counts, recv_counts, group=None):
+    """Variable-split all-to-all of the leading dimension; counts are Python ints per rank."""
+    out = torch.empty((int(sum(recv_counts)),) + tuple(send.shape[1:]), dtype=send.dtype, device=send.device)
+    dist.all_to_all_single(out, send.contiguous(), output_split_sizes=list(recv_counts), input_split_sizes=list(send_counts), group=group)
+    return out
+
+
+def exchange_counts(dist, counts, group=None):
+    """counts[r] = slots this rank sends to rank r  ->  recv[r] = slots rank r sends to this rank."""
+    recv = torch.empty_like(counts)
+    dist.all_to_all_single(recv, counts, group=group)
+    return recv
+
+
+class ShardedStep(object):
+    """Train / predict step over a row-sharded embedding table.  The engine's `table` holds only this rank's rows
+    (global row g = local row g // world on rank g % world); `engine.ids` carries GLOBAL row ids.
+
+      1  bucket the N*F slots by owner (stable: dctr_sort_rows on the owner key), all-to-all the counts and the ids
+      2  owners gather the requested rows (dctr_gather_rows), all-to-all them back
+      3  gather_concat / MLP forward + backward on the local samples, reading the exchanged row buffer
+      4  dense gradients + loss: all-reduce;  per-slot embedding gradients (dctr_cross_bwd): all-to-all to the owners
+      5  owners sort the received local rows and fold (dctr_scatter_sgd) -- received order is (source rank, sample,
+         field) = global sample order, so SUM and SEQ_DECAY both match the single-GPU step on the concatenated batch
+    """
+
+    def __init__(self, engine, dist, X_global, group=None):
+        self.e, self.dist, self.group = engine, dist, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.X_global = int(X_global)
+        e = engine
+        assert not e.bias_first, "row-sharded mode covers the TF-form models (bias column last)"
+        assert e.X >= (self.X_global + self.world - 1) // self.world, "engine table must hold ceil(X / world) local rows"
+        i32 = dict(dtype=torch.int32, device=e.dev)
+        self.owner_sorted = torch.zeros(e.M, **i32)
+        self.perm = torch.zeros(e.M, **i32)
+        self.inv = torch.zeros(e.N, e.F, **i32)
+        self.arange = torch.arange(e.M, **i32)
+        self.plan_ws = torch.zeros(L.lib().dctr_sort_rows_workspace(e.M), dtype=torch.uint8, device=e.dev)
+        self.ge = e.ge if e.ge is not None else torch.zeros(e.N, e.F, e.ldg, dtype=torch.float32, device=e.dev)
+        self.last = None
+
+    def _st(self):
+        return torch.cuda.current_stream(self.e.dev).cuda_stream
+
+    def _stable_argsort(self, owner):
+        e = self.e
+        L.call("dctr_sort_rows", L.ptr(owner.contiguous()), e.M, self.world, L.ptr(self.owner_sorted), L.ptr(self.perm),
+               L.ptr(self.plan_ws), self.plan_ws.numel(), self._st())
+        return self.perm
+
+    def lookup(self):
+        """steps 1-2: returns (inv ids [N,F], exchanged rows [M, ld]) and remembers the plan for the backward."""
+        e, dist = self.e, self.dist
+        perm, counts, send_rows = plan_exchange(e.ids.view(-1), self.world, self._stable_argsort)
+        recv_counts = exchange_counts(dist, counts, self.group)
+        sc, rc = counts.tolist(), recv_counts.tolist()                    # host sync: the split sizes
+        recv_rows = all_to_all_rows(dist, send_rows.to(torch.int32), sc, rc, self.group)
+        R = recv_rows.shape[0]
+        rows = torch.empty(max(R, 1), e.ld, dtype=torch.float32, device=e.dev)
+        L.call("dctr_gather_rows", L.ptr(recv_rows), L.ptr(e.table), e.X, e.ld, R, L.ptr(rows), self._st())
+        back = all_to_all_rows(dist, rows[:R], rc, sc, self.group)        # [M, ld], in perm order
+        self.inv.view(-1)[perm.long()] = self.arange                      # slot -> its row in `back`
+        self.last = (sc, rc, recv_rows, back)
+        return self.inv, back
+
+    def forward(self, with_loss, gscale=1.0):
+        """collective inference / forward: every rank must call it together (the lookups are all-to-alls)."""
+        inv, back = self.lookup()
+        self.e.forward(with_loss, gscale, lookup=(inv, back, max(back.shape[0], 1)))
+
+    def train_step(self, lr, decay=1.0, gscale=1.0, train_bias=True, last_decay=1.0):
+        e, dist = self.e, self.dist
+        self.forward(True, gscale)
+        sc, rc, recv_rows, back = self.last
+        dz = e.backward()
+        st = self._st()
+        N, F, d = e.N, e.F, e.d
+        ldd = dz.stride(0)
+        if train_bias:
+            L.call("dctr_col_wsum", dz.data_ptr() + 4 * (F * d + e.crossw), ldd, N, 1, None, L.ptr(e.bias(e.grads)),
+                   L.ptr(e.col_ws), e.col_ws.numel(), st)
+        allreduce_dense(dist, e.grads, self.group)
+        allreduce_dense(dist, e.loss, self.group)
+        # per-slot embedding gradient (weights applied), against the exchanged pre-update rows
+        wts = None if e.wts_are_ones else e.wts
+        L.call("dctr_cross_bwd", L.ptr(self.inv), L.ptr(wts), L.ptr(back), max(back.shape[0], 1), e.ld, N, F, d,
+               L.CROSS[e.cross], L.ptr(dz), ldd, L.ptr(self.ge), e.ldg, st)
+        send_g = torch.empty(e.M, e.ldg, dtype=torch.float32, device=e.dev)
+        L.call("dctr_gather_rows", L.ptr(self.perm), L.ptr(self.ge), e.M, e.ldg, e.M, L.ptr(send_g), st)
+        recv_g = all_to_all_rows(dist, send_g, sc, rc, self.group)       # aligned with recv_rows
+        R = recv_rows.shape[0]
+        if R > 0:
+            i32 = dict(dtype=torch.int32, device=e.dev)
+            rows, pos = torch.empty(R, **i32), torch.empty(R, **i32)
+            sws = torch.empty(L.lib().dctr_sort_rows_workspace(R), dtype=torch.uint8, device=e.dev)
+            fws = torch.empty(L.lib().dctr_scatter_workspace(R, e.ld), dtype=torch.uint8, device=e.dev)
+            L.call("dctr_sort_rows", L.ptr(recv_rows), R, e.X, L.ptr(rows), L.ptr(pos), L.ptr(sws), sws.numel(), st)
+            # one "field" per received slot: position p indexes recv_g directly
+            L.call("dctr_scatter_sgd", e.scatter_mode, L.ptr(rows), L.ptr(pos), R, 1, d, L.ptr(recv_g), e.ldg, e.ldg, None,
+                   float(lr), float(decay), L.ptr(e.table), e.X, e.ld, L.ptr(fws), fws.numel(), st)
+            self._keep = (rows, pos, sws, fws, recv_g, send_g, recv_rows, back)
+        e.dense_update(lr, last_decay)
+
+
+def attach_sharded(model, dist, X_global, group=None):
+    """Switch a TF-form model built with `shard=(rank, world)` (its engine table holds the local rows only) to the
+    row-sharded step.  'mean' reduce sees the GLOBAL batch; forward / predict become collective calls."""
+    sh = ShardedStep(model.engine, dist, X_global, group)
+    model.sharded = sh
+    model.use_graph = False           # the split sizes of the all-to-alls are read on the host every step
+    model.global_N = model.N * sh.world
+    model.engine.train_step = sh.train_step
+    eng_forward = model.engine.forward
+
+    def forward(with_loss, gscale=1.0, lookup=None):
+        if lookup is not None:
+            return eng_forward(with_loss, gscale, lookup)
+        return sh.forward(with_loss, gscale)
+    model.engine.forward = forward
+    return sh
 
 
 def attach(model, dist, group=None):

@@ -125,7 +125,7 @@ class StepEngine:
     def set_table(self, table):
         t = torch.as_tensor(table, dtype=torch.float32)
         self.table.zero_()
-        self.table[:, :t.shape[1]] = t.to(self.dev)
+        self.table[:t.shape[0], :t.shape[1]] = t.to(self.dev)      # a row shard may be one row short of the allocation
 
     def get_table(self):
         return self.table[:, :self.d].cpu().numpy()
@@ -140,11 +140,14 @@ class StepEngine:
             return None, 0
         return m.data_ptr(), (0 if m.shape[0] == 1 else m.stride(0))
 
-    def forward(self, with_loss, gscale=1.0):
+    def forward(self, with_loss, gscale=1.0, lookup=None):
+        """lookup = (ids, rows, n_rows): gather from an already exchanged row buffer instead of the local table
+        (row-sharded mode, dist.ShardedStep)."""
         st = self._st()
         N, F, d, p = self.N, self.F, self.d, L.ptr
         wts = None if self.wts_are_ones else self.wts
-        L.call("dctr_gather_concat_fwd", p(self.ids), p(wts), p(self.table), self.X, self.ld, N, F, d,
+        ids, table, X = (self.ids, self.table, self.X) if lookup is None else lookup
+        L.call("dctr_gather_concat_fwd", p(ids), p(wts), p(table), X, self.ld, N, F, d,
                L.CROSS[self.cross], int(self.bias_first), p(self.bias()), L.ACT[self.act0],
                p(self.ins[0]), self.ldi[0], st)
         if self.masks[0] is not None:

@@ -287,7 +287,9 @@ class _FNNBase(_Base):
     n_hidden = 2
 
     def __init__(self, cat_sizes, offsets, batch_size, _rch_argv, _init_argv, _ptmzr_argv, _reg_argv, mode,
-                 eval_size, device="cuda"):
+                 eval_size, device="cuda", shard=None):
+        """shard=(rank, world): row-sharded table (dist.attach_sharded) -- the engine then holds only the rows
+        g with g % world == rank; without a checkpoint they are drawn on the device (one stream per shard)."""
         X_dim, X_feas, rank = _rch_argv[:3]
         hidden = list(_rch_argv[3:3 + self.n_hidden])
         act_func = _rch_argv[3 + self.n_hidden]
@@ -300,15 +302,28 @@ class _FNNBase(_Base):
         self.log = "input dim: %d, features: %d, rank: %d, embedding: %d, " % (X_dim, X_feas, rank, mbd_dim)
         self.log += ", ".join("h%d: %d" % (i + 1, h) for i, h in enumerate(hidden)) + ", activate: %s" % act_func
         dims = [mbd_dim] + hidden + [1]
-        variables = [("W", [X_dim, 1], "random"), ("V", [X_dim, rank], "random"), ("b", [1], "zero")]
+        device_table = shard is not None and not _init_argv[-1]
+        variables = ([] if device_table else [("W", [X_dim, 1], "random"), ("V", [X_dim, rank], "random")]) + [("b", [1], "zero")]
         for i in range(len(dims) - 1):
             variables += [("h%d_w" % (i + 1), [dims[i], dims[i + 1]], "random"), ("h%d_b" % (i + 1), [dims[i + 1]], "zero")]
         var_map, log = init_var_map(_init_argv, variables)
         self.log += log
         act = act_func if act_func in ("tanh", "relu") else "sigmoid"     # tf_util.py:32-38
-        eng = StepEngine(X_dim, X_feas, rank, hidden, batch_size, cross=self.cross, bias_first=False,
+        self.shard = shard
+        X_rows = X_dim if shard is None else (X_dim + shard[1] - 1) // shard[1]
+        eng = StepEngine(X_rows, X_feas, rank, hidden, batch_size, cross=self.cross, bias_first=False,
                          act0=act, act=act, scatter_mode="sum", device=device)
-        eng.set_table(np.concatenate([var_map["W"], var_map["V"]], axis=1))
+        if device_table:
+            gen = torch.Generator(device=eng.dev)
+            gen.manual_seed(int(_init_argv[3][0]) * 1000003 + shard[0])
+            a, b = float(_init_argv[1]), float(_init_argv[2])
+            if _init_argv[0] == "normal":
+                eng.table[:, :d].normal_(a, b, generator=gen)
+            else:
+                eng.table[:, :d].uniform_(a, b, generator=gen)
+        else:
+            full = np.concatenate([var_map["W"], var_map["V"]], axis=1)
+            eng.set_table(full if shard is None else np.ascontiguousarray(full[shard[0]::shard[1]]))
         eng.bias().copy_(torch.as_tensor(var_map["b"], dtype=torch.float32))
         for i in range(len(dims) - 1):
             eng.set_layer(i, var_map["h%d_w" % (i + 1)], var_map["h%d_b" % (i + 1)])

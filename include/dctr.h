@@ -65,6 +65,10 @@ int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, const float* ta
 int dctr_arrange_fields(const int32_t* feats, const int32_t* feat_field, int N, int J, int F, int32_t pad_row,
                         int32_t* ids, float* wts, void* stream);
 
+/* row gather: out[i, 0:ld) = table[ids[i], 0:ld), i < M.  The owner-side lookup of the row-sharded table (SURVEY 8(e):
+ * rows live on rank row % world) and the permutation of per-slot gradient rows into all-to-all order. */
+int dctr_gather_rows(const int32_t* ids, const float* table, int64_t X, int ld, int64_t M, float* out, void* stream);
+
 /* backward of the cross layer into a per-(sample,field) embedding-gradient buffer
  *   ge[n,f,c] = wts[n,f] * ( dz[n, f*d+c] + d(cross)/d(e_f[c]) ),  ge: float32 [N, F, ldg], ldg%4==0
  * dz is dL/dz (the activation derivative already applied), TF layout (bias last).

@@ -105,6 +105,18 @@ def test_arrange_fields_bit_exact(L):
     assert np.array_equal(wts.cpu().numpy(), want_wts)
 
 
+@pytest.mark.parametrize("M,X,ld", [(1, 3, 4), (1000, 37, 12), (70001, 5000, 12), (513, 9, 52), (64, 64, 8)])
+def test_gather_rows_bit_exact(L, M, X, ld):
+    """the owner-side lookup of the row-sharded table and the gradient permutation: a pure row copy (bit-exact)"""
+    rng = np.random.default_rng(M)
+    table = rng.normal(0, 1, (X, ld)).astype(np.float32)
+    ids = rng.integers(0, X, M).astype(np.int32)
+    out = torch.empty(M, ld, dtype=torch.float32, device="cuda")
+    L.call("dctr_gather_rows", L.ptr(dev(ids)), L.ptr(dev(table)), X, ld, M, L.ptr(out), 0)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), table[ids])
+
+
 @pytest.mark.parametrize("cross,F,d,N", [("none", 16, 11, 50), ("ip", 16, 11, 41), ("ip", 39, 11, 9), ("op", 16, 11, 23), ("op", 6, 5, 8)])
 def test_cross_bwd(L, cross, F, d, N):
     import deepctr_oracle as O
