@@ -31,6 +31,7 @@ __device__ __forceinline__ bool take_last_ticket(unsigned* ticket, unsigned nblo
 template <class Dst>
 __device__ __forceinline__ void ordered_reduce(const float* __restrict__ partial, int S, int W, int Hn, Dst dst) {
     __shared__ float s_part[kRedThreads];
+    __syncthreads();                                        // s_part may still be read by a previous call
     int KS = 1;
     while (KS < 32 && KS * 2 * Hn <= kRedThreads) KS *= 2;
     if (KS == 1) {
@@ -119,49 +120,144 @@ out_bwd_kernel(const float* __restrict__ dlogit, const float* __restrict__ w, co
     }
 }
 
-// out[h] = sum_n (wv ? wv[n] : 1) * A[n,h]
-__global__ void __launch_bounds__(kRedThreads)
-col_wsum_kernel(const float* __restrict__ A, int lda, int N, int H, const float* __restrict__ wv, int rows_per,
-                float* __restrict__ partial, unsigned* __restrict__ ticket, float* __restrict__ out) {
-    const int r0 = blockIdx.x * rows_per, r1 = min(N, r0 + rows_per);
-    for (int h = threadIdx.x; h < H; h += kRedThreads) {
-        float acc = 0.f;
-#pragma unroll 8
-        for (int n = r0; n < r1; ++n) acc = fmaf(wv ? __ldg(wv + n) : 1.f, A[(int64_t)n * lda + h], acc);
-        partial[(int64_t)blockIdx.x * H + h] = acc;
+// ---- column reductions over an [N, H] row-major matrix ------------------------------------------------------
+// Grid = (column tiles, row chunks).  A CTA is TX column groups (V consecutive columns each: one LDG.128 when V = 4) by
+// TY = 256 / TX row lanes; every thread walks its chunk's rows with stride TY, four independent loads in flight, the
+// row lanes are then folded by a fixed shared-memory tree and the chunk's partial row goes to the workspace.  The last
+// CTA of each COLUMN TILE (one ticket per tile) adds the chunk partials in chunk order: fixed order, no float atomics.
+struct RedShape {
+    int TX, V, col_tiles, chunks, rows_per;
+};
+
+template <int V>
+__device__ __forceinline__ void ld_cols(const float* p, bool ok, float (&v)[V]) {
+    if constexpr (V == 4) {
+        const float4 t = ok ? *reinterpret_cast<const float4*>(p) : make_float4(0.f, 0.f, 0.f, 0.f);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else {
+        v[0] = ok ? *p : 0.f;
     }
-    if (!take_last_ticket(ticket, gridDim.x)) return;
-    ordered_reduce(partial, (int)gridDim.x, H, H, [&](int h, float s) { out[h] = s; });
+}
+
+// fold acc[V] over the TY row lanes (fixed tree); the result is valid in the ty == 0 threads
+template <int V>
+__device__ __forceinline__ void fold_row_lanes(float (&acc)[V], int TX, float* s_acc) {
+    const int TY = kRedThreads / TX, ty = threadIdx.x / TX;
+#pragma unroll
+    for (int c = 0; c < V; ++c) s_acc[c * kRedThreads + threadIdx.x] = acc[c];
+    __syncthreads();
+    for (int o = TY >> 1; o > 0; o >>= 1) {
+        if (ty < o) {
+#pragma unroll
+            for (int c = 0; c < V; ++c) s_acc[c * kRedThreads + threadIdx.x] += s_acc[c * kRedThreads + threadIdx.x + o * TX];
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int c = 0; c < V; ++c) acc[c] = s_acc[c * kRedThreads + threadIdx.x];
+}
+
+// out[h] = sum_n (wv ? wv[n] : 1) * A[n,h]
+template <int V>
+__global__ void __launch_bounds__(kRedThreads)
+col_wsum_kernel(const float* __restrict__ A, int lda, int N, int H, const float* __restrict__ wv, RedShape sh,
+                float* __restrict__ partial, unsigned* __restrict__ tickets, float* __restrict__ out) {
+    __shared__ float s_acc[V * kRedThreads];
+    const int TX = sh.TX, TY = kRedThreads / TX, tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const int c0 = blockIdx.x * TX * V, h0 = c0 + tx * V;
+    const int r0 = blockIdx.y * sh.rows_per, r1 = min(N, r0 + sh.rows_per);
+    const bool col_ok = h0 < H;
+    float acc[V] = {};
+    for (int n = r0 + ty; n < r1; n += 4 * TY) {
+        float v[4][V], w[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int nn = n + u * TY;
+            const bool ok = col_ok && nn < r1;
+            ld_cols<V>(A + (int64_t)nn * lda + h0, ok, v[u]);
+            w[u] = (wv && ok) ? __ldg(wv + nn) : 1.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+            for (int c = 0; c < V; ++c) acc[c] = fmaf(w[u], v[u][c], acc[c]);
+    }
+    fold_row_lanes<V>(acc, TX, s_acc);
+    if (ty == 0 && col_ok) {
+#pragma unroll
+        for (int c = 0; c < V; ++c)
+            if (h0 + c < H) partial[(int64_t)blockIdx.y * H + h0 + c] = acc[c];
+    }
+    if (!take_last_ticket(tickets + blockIdx.x, gridDim.y)) return;
+    ordered_reduce(partial + c0, (int)gridDim.y, H, min(TX * V, H - c0), [&](int h, float s) { out[c0 + h] = s; });
 }
 
 // backward of the output unit in one launch (FNN.py:54-63 / FNN_wnzh.py:169-174 differentiated):
 //   da[n,h] = dlogit[n]*w[h] * mask * act'(a/mask);  gw[h] = sum_n dlogit[n]*a[n,h];  gb = sum_n dlogit[n]
+template <int V>
 __global__ void __launch_bounds__(kRedThreads)
 out_bwd_fused_kernel(const float* __restrict__ dlogit, const float* __restrict__ w, const float* __restrict__ a, int lda,
                      int N, int H, int act, const float* __restrict__ mask, int ldmask, float* __restrict__ da, int ldda,
-                     int rows_per, float* __restrict__ partial, unsigned* __restrict__ ticket,
+                     RedShape sh, float* __restrict__ partial, unsigned* __restrict__ tickets,
                      float* __restrict__ gw, float* __restrict__ gb) {
-    const int r0 = blockIdx.x * rows_per, r1 = min(N, r0 + rows_per);
+    __shared__ float s_acc[V * kRedThreads];
+    const int TX = sh.TX, TY = kRedThreads / TX, tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+    const int c0 = blockIdx.x * TX * V, h0 = c0 + tx * V;
+    const int r0 = blockIdx.y * sh.rows_per, r1 = min(N, r0 + sh.rows_per);
     const int HP = H + 1;
-    for (int h = threadIdx.x; h < H; h += kRedThreads) {
-        const float wh = __ldg(w + h);
-        float acc = 0.f;
-#pragma unroll 8
-        for (int n = r0; n < r1; ++n) {
-            const float dl = __ldg(dlogit + n), av = a[(int64_t)n * lda + h];
-            acc = fmaf(dl, av, acc);
-            const float mk = mask ? __ldg(mask + (int64_t)n * ldmask + h) : 1.f;
-            da[(int64_t)n * ldda + h] = mk != 0.f ? dl * wh * mk * act_bwd_from_out(act, mask ? av / mk : av) : 0.f;
+    const bool col_ok = h0 < H;
+    float wh[V];
+#pragma unroll
+    for (int c = 0; c < V; ++c) wh[c] = (h0 + c < H) ? __ldg(w + h0 + c) : 0.f;
+    float acc[V] = {};
+    float dsum = 0.f;                                       // sum of dlogit over this thread's rows (used by tx == 0 of tile 0)
+    for (int n = r0 + ty; n < r1; n += 4 * TY) {
+        float av[4][V], mk[4][V], dl[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int nn = n + u * TY;
+            const bool ok = col_ok && nn < r1;
+            ld_cols<V>(a + (int64_t)nn * lda + h0, ok, av[u]);
+            if (mask) ld_cols<V>(mask + (int64_t)nn * ldmask + h0, ok, mk[u]);
+            dl[u] = ok ? __ldg(dlogit + nn) : 0.f;
         }
-        partial[(int64_t)blockIdx.x * HP + h] = acc;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int nn = n + u * TY;
+            if (!(col_ok && nn < r1)) continue;
+            dsum += dl[u];
+            float o[V];
+#pragma unroll
+            for (int c = 0; c < V; ++c) {
+                acc[c] = fmaf(dl[u], av[u][c], acc[c]);
+                const float m = mask ? mk[u][c] : 1.f;
+                o[c] = m != 0.f ? dl[u] * wh[c] * m * act_bwd_from_out(act, mask ? av[u][c] / m : av[u][c]) : 0.f;
+            }
+            float* dst = da + (int64_t)nn * ldda + h0;
+            if (V == 4 && h0 + 3 < H) {
+                *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+            } else {
+#pragma unroll
+                for (int c = 0; c < V; ++c)
+                    if (h0 + c < H) dst[c] = o[c];
+            }
+        }
     }
-    if (threadIdx.x == 0) {
-        float s = 0.f;
-        for (int n = r0; n < r1; ++n) s += __ldg(dlogit + n);
-        partial[(int64_t)blockIdx.x * HP + H] = s;
+    fold_row_lanes<V>(acc, TX, s_acc);
+    if (ty == 0 && col_ok) {
+#pragma unroll
+        for (int c = 0; c < V; ++c)
+            if (h0 + c < H) partial[(int64_t)blockIdx.y * HP + h0 + c] = acc[c];
     }
-    if (!take_last_ticket(ticket, gridDim.x)) return;
-    ordered_reduce(partial, (int)gridDim.x, HP, HP, [&](int h, float s) { if (h < H) gw[h] = s; else gb[0] = s; });
+    if (blockIdx.x == 0) {                                  // bias gradient: the dlogit column, folded the same way
+        __syncthreads();
+        float d1[1] = {tx == 0 ? dsum : 0.f};
+        fold_row_lanes<1>(d1, TX, s_acc);
+        if (threadIdx.x == 0) partial[(int64_t)blockIdx.y * HP + H] = d1[0];
+    }
+    if (!take_last_ticket(tickets + blockIdx.x, gridDim.y)) return;
+    ordered_reduce(partial + c0, (int)gridDim.y, HP, min(TX * V, H - c0), [&](int h, float s) { gw[c0 + h] = s; });
+    if (blockIdx.x == 0) ordered_reduce(partial + H, (int)gridDim.y, HP, 1, [&](int, float s) { gb[0] = s; });
 }
 
 __global__ void __launch_bounds__(1024) vec_sum_kernel(const float* __restrict__ v, int N, float scale, float* __restrict__ out) {
@@ -182,13 +278,29 @@ __global__ void dense_sgd_kernel(float* __restrict__ p, const float* __restrict_
         p[i] = fmaf(p[i], decay, -lr * g[i]);
 }
 
-// row blocks of the single-launch reductions: at most kRedMaxBlocks CTAs, at least 32 rows each
-static int red_blocks(int N, int* rows_per) {
-    int rp = (N + kRedMaxBlocks - 1) / kRedMaxBlocks;
-    if (rp < 32) rp = 32;
-    *rows_per = rp;
-    return (N + rp - 1) / rp;
+// Shape of a column reduction: V = 4 when every row start is 16-byte aligned, TX = the narrowest power of two covering
+// the columns (<= 32), enough row chunks for ~4 CTAs per SM but at least 4 rows per row lane and chunk.
+constexpr int kRedHeader = 1024;                       // bytes: one ticket per column tile
+constexpr int kRedMaxChunks = kNumSMs * 4;
+
+static RedShape red_shape(int N, int H, bool vec) {
+    RedShape s;
+    s.V = vec ? 4 : 1;
+    const int groups = (H + s.V - 1) / s.V;
+    s.TX = 1;
+    while (s.TX < 32 && s.TX < groups) s.TX *= 2;
+    s.col_tiles = (groups + s.TX - 1) / s.TX;
+    const int TY = kRedThreads / s.TX;
+    int chunks = (kRedMaxChunks + s.col_tiles - 1) / s.col_tiles;
+    const int max_chunks = (N + 4 * TY - 1) / (4 * TY);
+    if (chunks > max_chunks) chunks = max_chunks;
+    if (chunks < 1) chunks = 1;
+    s.rows_per = ((N + chunks - 1) / chunks + TY - 1) / TY * TY;
+    s.chunks = (N + s.rows_per - 1) / s.rows_per;
+    return s;
 }
+
+static bool vec_ok(const void* p, int ld) { return (((uintptr_t)p & 15) == 0) && (ld & 3) == 0; }
 
 }  // namespace dctr
 
@@ -197,10 +309,9 @@ using namespace dctr;
 extern "C" size_t dctr_reduce_workspace(int N, int H) {
     if (N < 1) N = 1;
     if (H < 1) H = 1;
-    int rp;
-    const int S = red_blocks(N, &rp);
-    const size_t rows = (size_t)(S > kNumSMs * 8 ? S : kNumSMs * 8);     // also covers out_xent_fwd's CTA partials
-    return 16 + rows * (size_t)(H + 1) * sizeof(float);
+    (void)N;
+    const size_t rows = (size_t)(kRedMaxChunks > kNumSMs * 8 ? kRedMaxChunks : kNumSMs * 8);   // also out_xent_fwd's CTA partials
+    return kRedHeader + rows * (size_t)(H + 1) * sizeof(float);
 }
 
 extern "C" int dctr_out_xent_fwd(const float* a, int lda, int N, int H, const float* w, const float* b,
@@ -214,7 +325,7 @@ extern "C" int dctr_out_xent_fwd(const float* a, int lda, int N, int H, const fl
     int blocks = ceil_div(N, 8);
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
     unsigned* ticket = static_cast<unsigned*>(workspace);
-    float* partial = workspace ? reinterpret_cast<float*>(ticket + 4) : nullptr;
+    float* partial = workspace ? reinterpret_cast<float*>(static_cast<char*>(workspace) + kRedHeader) : nullptr;
     out_xent_fwd_kernel<<<blocks, 256, 0, as_stream(stream)>>>(a, lda, N, H, w, b, y, gscale, logit, pred, loss_n, dlogit,
                                                                 loss_scale, loss_sum, partial, ticket);
     return check_launch("out_xent_fwd_kernel");
@@ -228,11 +339,18 @@ extern "C" int dctr_out_bwd_fused(const float* dlogit, const float* w, const flo
         set_error("out_bwd_fused: workspace %zu < %zu", workspace_bytes, dctr_reduce_workspace(N, H));
         return DCTR_EWORKSPACE;
     }
-    int rp;
-    const int S = red_blocks(N, &rp);
-    unsigned* ticket = static_cast<unsigned*>(workspace);
-    out_bwd_fused_kernel<<<S, kRedThreads, 0, as_stream(stream)>>>(dlogit, w, a, lda, N, H, act, mask, ldmask, da, ldda, rp,
-                                                                  reinterpret_cast<float*>(ticket + 4), ticket, gw, gb);
+    const bool vec = vec_ok(a, lda) && vec_ok(da, ldda) && (!mask || vec_ok(mask, ldmask));
+    const RedShape sh = red_shape(N, H, vec);
+    DCTR_REQUIRE(sh.col_tiles * 4 <= kRedHeader, "out_bwd_fused: H=%d too wide", H);
+    unsigned* tickets = static_cast<unsigned*>(workspace);
+    float* partial = reinterpret_cast<float*>(static_cast<char*>(workspace) + kRedHeader);
+    const dim3 grid(sh.col_tiles, sh.chunks);
+    if (vec)
+        out_bwd_fused_kernel<4><<<grid, kRedThreads, 0, as_stream(stream)>>>(dlogit, w, a, lda, N, H, act, mask, ldmask, da, ldda,
+                                                                            sh, partial, tickets, gw, gb);
+    else
+        out_bwd_fused_kernel<1><<<grid, kRedThreads, 0, as_stream(stream)>>>(dlogit, w, a, lda, N, H, act, mask, ldmask, da, ldda,
+                                                                            sh, partial, tickets, gw, gb);
     return check_launch("out_bwd_fused_kernel");
 }
 
@@ -255,10 +373,16 @@ extern "C" int dctr_col_wsum(const float* A, int lda, int N, int H, const float*
         set_error("col_wsum: workspace %zu < %zu", workspace_bytes, dctr_reduce_workspace(N, H));
         return DCTR_EWORKSPACE;
     }
-    int rp;
-    const int S = red_blocks(N, &rp);
-    unsigned* ticket = static_cast<unsigned*>(workspace);
-    col_wsum_kernel<<<S, kRedThreads, 0, as_stream(stream)>>>(A, lda, N, H, wv, rp, reinterpret_cast<float*>(ticket + 4), ticket, out);
+    const bool vec = vec_ok(A, lda);
+    const RedShape sh = red_shape(N, H, vec);
+    DCTR_REQUIRE(sh.col_tiles * 4 <= kRedHeader, "col_wsum: H=%d too wide", H);
+    unsigned* tickets = static_cast<unsigned*>(workspace);
+    float* partial = reinterpret_cast<float*>(static_cast<char*>(workspace) + kRedHeader);
+    const dim3 grid(sh.col_tiles, sh.chunks);
+    if (vec)
+        col_wsum_kernel<4><<<grid, kRedThreads, 0, as_stream(stream)>>>(A, lda, N, H, wv, sh, partial, tickets, out);
+    else
+        col_wsum_kernel<1><<<grid, kRedThreads, 0, as_stream(stream)>>>(A, lda, N, H, wv, sh, partial, tickets, out);
     return check_launch("col_wsum_kernel");
 }
 

@@ -95,6 +95,7 @@ class StepEngine:
         # workspace of the single-launch reductions (ticket + CTA partials): zero-filled once, left zeroed by the kernels
         self.col_ws = torch.zeros(L.lib().dctr_reduce_workspace(N, maxw), dtype=torch.uint8, device=self.dev)
         self.side = torch.cuda.Stream(device=self.dev)
+        self.overlap_sort = True
         self.wts_are_ones = True
 
     # ---- parameter views -------------------------------------------------------------------------
@@ -241,12 +242,16 @@ class StepEngine:
         """One full step on device buffers ids/wts/y (+ masks).  The row sort only depends on the ids, so it
         runs on a side stream concurrently with the MLP forward/backward."""
         cur = torch.cuda.current_stream(self.dev)
-        self.side.wait_stream(cur)
-        with torch.cuda.stream(self.side):
+        if self.overlap_sort:
+            self.side.wait_stream(cur)
+            with torch.cuda.stream(self.side):
+                self.sort_ids()
+        else:                                    # per-kernel timing (bench.py): everything on one stream
             self.sort_ids()
         self.forward(True, gscale)
         dz = self.backward()
-        cur.wait_stream(self.side)
+        if self.overlap_sort:
+            cur.wait_stream(self.side)
         self.embedding_update(dz, lr, decay, train_bias)
         self.dense_update(lr, last_decay)
 
@@ -281,6 +286,7 @@ class FMEngine:
         self.sort_ws = torch.zeros(L.lib().dctr_sort_rows_workspace(M), dtype=torch.uint8, device=self.dev)
         self.scat_ws = torch.zeros(L.lib().dctr_scatter_workspace(M, self.ld), dtype=torch.uint8, device=self.dev)
         self.side = torch.cuda.Stream(device=self.dev)
+        self.overlap_sort = True
         self.wts_are_ones = False
 
     def bias(self, buf=None):
@@ -312,15 +318,19 @@ class FMEngine:
 
     def train_step(self, lr, lam=0.0, gscale=1.0, dense_l2=True):
         cur = torch.cuda.current_stream(self.dev)
-        self.side.wait_stream(cur)
-        with torch.cuda.stream(self.side):
+        if self.overlap_sort:
+            self.side.wait_stream(cur)
+            with torch.cuda.stream(self.side):
+                self.sort_ids()
+        else:                                    # per-kernel timing (bench.py): everything on one stream
             self.sort_ids()
         self.forward(True, gscale)
         st = self._st()
         p = L.ptr
         decay = 1.0 - lr * lam
         L.call("dctr_vec_sum", p(self.g), self.N, 1.0, p(self.grads), st)           # d loss / d b = sum_n g_n
-        cur.wait_stream(self.side)
+        if self.overlap_sort:
+            cur.wait_stream(self.side)
         wts = None if self.wts_are_ones else self.wts
         L.call("dctr_scatter_sgd_fm", p(self.sorted_rows), p(self.sorted_pos), self.M, self.F, self.d, p(self.g),
                p(self.s), self.lds, p(wts), float(lr), float(decay), p(self.table), self.X, self.ld,

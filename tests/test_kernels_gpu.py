@@ -405,6 +405,51 @@ def test_output_unit_and_reductions(L):
     close(p.cpu(), want)
 
 
+@pytest.mark.parametrize("N,H,off,pad", [(1, 1, 0, 0), (37, 50, 0, 2), (4096, 300, 0, 0), (5000, 1, 177, 3), (70000, 400, 0, 0),
+                                          (3000, 129, 1, 4), (9000, 1000, 0, 0), (260, 7, 0, 0)])
+def test_column_reductions_shapes(L, N, H, off, pad):
+    """dctr_col_wsum / dctr_out_bwd_fused over the shapes the engine uses: wide and narrow, 16-byte aligned and not (a
+    single column inside a wider matrix), N far above and below one row chunk; run twice (ticket reset) and identical
+    both times (fixed-order reduction)."""
+    rng = np.random.default_rng(N + H)
+    lda = r4(H + off) + 4 * (pad // 2) if off == 0 else H + off + pad
+    A = rng.normal(0, 1, (N, lda)).astype(np.float32)
+    wv = rng.normal(0, 1, N).astype(np.float32)
+    Ad, wd = dev(A), dev(wv)
+    ws = torch.zeros(L.lib().dctr_reduce_workspace(N, H), dtype=torch.uint8, device="cuda")
+    out = torch.zeros(H, device="cuda")
+    want = (wv.astype(np.float64)[:, None] * A[:, off:off + H]).sum(0)
+    tol = 2e-6 * np.sqrt(N) * 4
+    res = []
+    for rep in range(2):
+        L.call("dctr_col_wsum", Ad.data_ptr() + 4 * off, lda, N, H, wd.data_ptr(), out.data_ptr(), ws.data_ptr(), ws.numel(), None)
+        res.append(out.cpu().numpy().copy())
+        close(res[-1], want, atol=tol)
+    assert np.array_equal(res[0], res[1])
+    L.call("dctr_col_wsum", Ad.data_ptr() + 4 * off, lda, N, H, None, out.data_ptr(), ws.data_ptr(), ws.numel(), None)
+    close(out.cpu(), A[:, off:off + H].astype(np.float64).sum(0), atol=tol)
+    # fused output-unit backward; row-broadcast mask (ldmask = 0, the FNN_wnzh dropout form) and none
+    w = rng.normal(0, 0.3, H).astype(np.float32)
+    act_out = np.tanh(A[:, off:off + H].astype(np.float64))
+    for use_mask in (False, True):
+        mask = ((rng.random(r4(H)) < 0.6) * 2.0).astype(np.float32) if use_mask else None
+        stored = np.zeros((N, lda), np.float32)
+        stored[:, off:off + H] = act_out * (mask[:H] if use_mask else 1.0)
+        sd = dev(stored)
+        da = torch.full((N, lda), 7.0, device="cuda")
+        gw, gb = torch.zeros(H, device="cuda"), torch.zeros(1, device="cuda")
+        L.call("dctr_out_bwd_fused", wd.data_ptr(), dev(w).data_ptr(), sd.data_ptr() + 4 * off, lda, N, H, L.ACT["tanh"],
+               dev(mask).data_ptr() if use_mask else None, 0, da.data_ptr() + 4 * off, lda, gw.data_ptr(), gb.data_ptr(),
+               ws.data_ptr(), ws.numel(), None)
+        wv64 = wv.astype(np.float64)
+        close(gw.cpu(), (wv64[:, None] * stored[:, off:off + H]).sum(0), atol=tol)
+        close(gb.cpu(), [wv64.sum()], atol=tol)
+        m = mask[:H].astype(np.float64) if use_mask else np.ones(H)
+        dan = da.cpu().numpy()
+        close(dan[:, off:off + H], wv64[:, None] * w * m * (1 - act_out ** 2), atol=1e-5)
+        assert np.all(dan[:, :off] == 7.0) and np.all(dan[:, off + H:] == 7.0)       # nothing written outside the H columns
+
+
 def test_empty_inputs(L):
     # N = 0 / M = 0 are accepted and launch nothing
     before = L.launch_count()
