@@ -42,16 +42,38 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons every 200 ms while the timed region runs."""
+    """SM clock + throttle reasons sampled while the timed region runs (NVML, else nvidia-smi every 200 ms)."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self.stop_flag = index, [], False
+        self.index, self.rows, self.stop_flag, self.first = index, [], False, 0
+
+    def begin(self):
+        """the timed region starts here: earlier samples (NVML start-up, warm-up) are not reported"""
+        self.first = max(0, len(self.rows) - 1)
+
+    def _nvml_loop(self):
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(self.index)
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        bits = [0x8, 0x40, 0x20, 0x4]        # hw_slowdown, hw_thermal_slowdown, sw_thermal_slowdown, sw_power_cap
+        while not self.stop_flag:
+            r = get_reasons(h)
+            self.rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(mx)] +
+                             ["Active" if r & b else "Not Active" for b in bits])
+            time.sleep(0.01)
 
     def run(self):
-        while not self.stop_flag:
+        try:
+            self._nvml_loop()              # NVML in-process: a sample every 10 ms
+            return
+        except Exception:
+            pass
+        while not self.stop_flag:          # fallback: the nvidia-smi query of the profiling recipe
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
                                      capture_output=True, text=True, timeout=5).stdout.strip()
@@ -64,6 +86,7 @@ class ClockSampler(threading.Thread):
     def summary(self):
         self.stop_flag = True
         self.join(timeout=6)
+        self.rows = self.rows[self.first:]
         if not self.rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
         sm = sorted(float(r[0]) for r in self.rows)
@@ -269,6 +292,8 @@ def run_b200(args, rank, world):
             model._upload_masks()
         model._run_step()
 
+    sampler = ClockSampler(local)
+    sampler.start()
     for i in range(W):
         device_step(i)
     torch.cuda.synchronize()
@@ -282,8 +307,7 @@ def run_b200(args, rank, world):
     if dist:
         dist.barrier()
     torch.cuda.synchronize()
-    sampler = ClockSampler(local)
-    sampler.start()
+    sampler.begin()
     evs = []
     for i in range(K):
         flush.zero_()                    # evict table / weights / activations from L2 (not timed)
@@ -334,6 +358,7 @@ def run_b200(args, rank, world):
     if not args.no_profile:
         was_graph = model.use_graph
         model.use_graph = False
+        eng.overlap_wgrad = False
         eng.overlap_sort = False           # the row sort normally overlaps the MLP on a side stream: serialise it to time it alone
         agg = {}
         P = 5
@@ -353,6 +378,7 @@ def run_b200(args, rank, world):
             _lib.PROFILE = None
         model.use_graph = was_graph
         eng.overlap_sort = True
+        eng.overlap_wgrad = True
         pk = peaks()
         tot = sum(r["ms"] for r in agg.values())
         for key, r in sorted(agg.items(), key=lambda kv: -kv[1]["ms"]):
@@ -479,7 +505,7 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="fnn_ipinyou", choices=sorted(WORKLOADS))

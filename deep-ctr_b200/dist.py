@@ -72,6 +72,7 @@ class DataParallelStep(object):
         if train_bias:
             col = 0 if e.bias_first else F * d + e.crossw
             L.call("dctr_col_wsum", dz.data_ptr() + 4 * col, ldd, N, 1, None, L.ptr(e.bias(e.grads)), L.ptr(e.col_ws), e.col_ws.numel(), st)
+        e.join_wgrad()
         allreduce_dense(dist, e.grads, self.group)
         allreduce_dense(dist, e.loss, self.group)
         if e.cross != "none":
@@ -209,6 +210,7 @@ class ShardedStep(object):
         if train_bias:
             L.call("dctr_col_wsum", dz.data_ptr() + 4 * (F * d + e.crossw), ldd, N, 1, None, L.ptr(e.bias(e.grads)),
                    L.ptr(e.col_ws), e.col_ws.numel(), st)
+        e.join_wgrad()
         allreduce_dense(dist, e.grads, self.group)
         allreduce_dense(dist, e.loss, self.group)
         # per-slot embedding gradient (weights applied), against the exchanged pre-update rows

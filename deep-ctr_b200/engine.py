@@ -64,7 +64,7 @@ class StepEngine:
         self.ldi = [_r4(w) for w in self.widths]
         self.ins = [torch.zeros(N, self.ldi[l], **f32) for l in range(self.nl)]
         maxw = max(self.ldi)
-        self.dbuf = [torch.zeros(N, maxw, **f32) for _ in range(2)]
+        self.dbuf = [torch.zeros(N, maxw, **f32) for _ in range(3)]
         self.ids = torch.zeros(N, F_, **i32)
         self.wts = torch.ones(N, F_, **f32)
         self.y = torch.zeros(N, **f32)
@@ -94,7 +94,11 @@ class StepEngine:
         self.splitk_ws = torch.zeros(ws_elems, **f32)
         # workspace of the single-launch reductions (ticket + CTA partials): zero-filled once, left zeroed by the kernels
         self.col_ws = torch.zeros(L.lib().dctr_reduce_workspace(N, maxw), dtype=torch.uint8, device=self.dev)
+        self.col_ws2 = torch.zeros_like(self.col_ws)           # reductions issued from the weight-gradient stream
         self.side = torch.cuda.Stream(device=self.dev)
+        self.side2 = torch.cuda.Stream(device=self.dev)
+        self.overlap_wgrad = True
+        self._wgrad_pending = False
         self.overlap_sort = True
         self.wts_are_ones = True
 
@@ -179,24 +183,41 @@ class StepEngine:
         L.call("dctr_out_bwd_fused", p(self.dlogit), p(self.W(last)), p(self.ins[last]), self.ldi[last], N, H,
                L.ACT[self.act], mp, mld, p(self.dbuf[cur]), ldd, p(self.W(last, self.grads)), p(self.b(last, self.grads)),
                cw, cwb, st)
+        # Per layer, the weight/bias gradients (TN GEMM [+ split-K fold], column sum) only need dz_l, as does the data
+        # gradient that continues the chain: they run on a second stream next to it (three rotating dz buffers, so the
+        # chain is two layers ahead before it overwrites what a weight-gradient GEMM still reads).
+        ov = self.overlap_wgrad
+        main = torch.cuda.current_stream(self.dev)
+        readers = [None, None, None]
         for l in range(last - 1, -1, -1):
             K, Hl = self.widths[l], self.widths[l + 1]
             dpre = self.dbuf[cur]
             s = self.splits[l]
             gW = self.W(l, self.grads)
-            if s > 1:
-                L.call(self.gemm_fn, L.GEMM_TN, K, Hl, N, p(self.ins[l]), self.ldi[l], p(dpre), ldd, p(self.splitk_ws),
-                       self.ldw[l], L.EPI_NONE, 0, None, None, 0, None, 0, s, st)
-                L.call("dctr_splitk_reduce", p(self.splitk_ws), s, K, Hl, self.ldw[l], p(gW), self.ldw[l], st)
-            else:
-                L.call(self.gemm_fn, L.GEMM_TN, K, Hl, N, p(self.ins[l]), self.ldi[l], p(dpre), ldd, p(gW),
-                       self.ldw[l], L.EPI_NONE, 0, None, None, 0, None, 0, 1, st)
-            L.call("dctr_col_wsum", p(dpre), ldd, N, Hl, None, p(self.b(l, self.grads)), cw, cwb, st)
+            if ov:
+                self.side2.wait_stream(main)
+            with torch.cuda.stream(self.side2 if ov else main):
+                st2 = self._st()
+                cw2, cwb2 = (p(self.col_ws2), self.col_ws2.numel()) if ov else (cw, cwb)
+                if s > 1:
+                    L.call(self.gemm_fn, L.GEMM_TN, K, Hl, N, p(self.ins[l]), self.ldi[l], p(dpre), ldd, p(self.splitk_ws),
+                           self.ldw[l], L.EPI_NONE, 0, None, None, 0, None, 0, s, st2)
+                    L.call("dctr_splitk_reduce", p(self.splitk_ws), s, K, Hl, self.ldw[l], p(gW), self.ldw[l], st2)
+                else:
+                    L.call(self.gemm_fn, L.GEMM_TN, K, Hl, N, p(self.ins[l]), self.ldi[l], p(dpre), ldd, p(gW),
+                           self.ldw[l], L.EPI_NONE, 0, None, None, 0, None, 0, 1, st2)
+                L.call("dctr_col_wsum", p(dpre), ldd, N, Hl, None, p(self.b(l, self.grads)), cw2, cwb2, st2)
+                if ov:
+                    readers[cur] = self.side2.record_event()
+                    self._wgrad_pending = True
             mp, mld = self._mask(l)
             act = self.act if l > 0 else self.act0
-            L.call(self.gemm_fn, L.GEMM_NT, N, K, Hl, p(dpre), ldd, p(self.W(l)), self.ldw[l], p(self.dbuf[cur ^ 1]), ldd,
+            nxt = (cur + 1) % 3
+            if readers[nxt] is not None:
+                main.wait_event(readers[nxt])
+            L.call(self.gemm_fn, L.GEMM_NT, N, K, Hl, p(dpre), ldd, p(self.W(l)), self.ldw[l], p(self.dbuf[nxt]), ldd,
                    L.EPI_DGRAD, L.ACT[act], None, p(self.ins[l]), self.ldi[l], mp, mld, 1, st)
-            cur ^= 1
+            cur = nxt
         return self.dbuf[cur]
 
     def sort_ids(self, ids=None, M=None, rows=None, pos=None, ws=None):
@@ -226,7 +247,14 @@ class StepEngine:
                g, g_ld_n, g_ld_f, w, float(lr), float(decay), p(self.table), self.X, self.ld,
                p(self.scat_ws), self.scat_ws.numel(), st)
 
+    def join_wgrad(self):
+        """self.grads is complete on the current stream after this (weight gradients run on a side stream)."""
+        if self._wgrad_pending:
+            torch.cuda.current_stream(self.dev).wait_stream(self.side2)
+            self._wgrad_pending = False
+
     def dense_update(self, lr, last_decay=1.0):
+        self.join_wgrad()
         st = self._st()
         if last_decay == 1.0:
             L.call("dctr_dense_sgd", L.ptr(self.params), L.ptr(self.grads), self.n_params, float(lr), 1.0, st)
