@@ -151,6 +151,11 @@ def build_model(wl, N, seed=1234, shard=None):
 
     def train(ids, wts, y):
         return m.train_step({m.v_wt_hldr: wts[:, :n_num], m.c_id_hldr: ids[:, n_num:] - offsets, m.c_wt_hldr: wts[:, n_num:], m.lbl_hldr: y})
+
+    def feed_of(ids, wts, y):        # the reference's feed: numeric weights, per-field LOCAL categorical ids, weights, labels
+        return {m.v_wt_hldr: np.ascontiguousarray(wts[:, :n_num]), m.c_id_hldr: np.ascontiguousarray(ids[:, n_num:] - offsets),
+                m.c_wt_hldr: np.ascontiguousarray(wts[:, n_num:]), m.lbl_hldr: y}
+    train.feed_of, train.step = feed_of, m.train_step
     return m, train
 
 
@@ -336,7 +341,11 @@ def run_b200(args, rank, world):
         total_ms, warm_ms = float(t[0]), float(t[1])
 
     # ---- end to end: host numpy in, loss / preds out, through the model class ----
-    hp = pool
+    if hasattr(train, "feed_of"):      # batches in the form the reference's input pipeline hands to Session.run
+        hp = [(train.feed_of(*b),) for b in pool]
+        train = train.step
+    else:
+        hp = pool
     for i in range(3):
         train(*hp[i % len(hp)])
     torch.cuda.synchronize()
@@ -419,9 +428,10 @@ def run_b200(args, rank, world):
     if rank == 0 and world == 1 and not args.no_cpu:
         out["cpu_baseline"] = cpu_baseline(wl, N, budget_s=12.0)
     if rank == 0:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
     if dist:
-        dist.destroy_process_group()
+        from deepctr_b200 import dist as ddist
+        ddist.shutdown(dist, [model])
 
 
 # ---------------------------------------------------------------------------------------------------

@@ -26,6 +26,7 @@ SIGNATURES = {
     "dctr_gather_concat_fwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
     "dctr_arrange_fields": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
     "dctr_gather_rows": (_i, [_p, _p, _l, _i, _l, _p, _p]),
+    "dctr_host_pack_fields": (_i, [_p, _i, _p, _p, _p, _l, _i, _i, _p, _p, _i]),
     "dctr_cross_bwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
     "dctr_fm_fwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _p, _p, _f, _p, _p, _p, _p, _p, _i, _p]),
     "dctr_sort_rows_workspace": (_z, [_l]),

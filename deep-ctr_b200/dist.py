@@ -13,6 +13,8 @@ gradient rows with three all-to-alls; the owner folds the received gradients in 
 which is the global sample order, so the result equals the single-GPU step on the concatenated batch.
 The collectives below run on CPU tensors with gloo too, which is how tests/test_dist_cpu.py covers them.
 """
+import os
+
 import torch
 
 from . import _lib as L
@@ -37,30 +39,55 @@ def allreduce_dense(dist, flat, group=None):
 
 
 class DataParallelStep(object):
-    """Replaces StepEngine.train_step / FMEngine.train_step with the data-parallel step."""
+    """Replaces StepEngine.train_step / FMEngine.train_step with the data-parallel step.  Every exchanged buffer is
+    allocated once, so the whole step -- kernels and NCCL collectives -- is captured into one CUDA graph by the model."""
 
     def __init__(self, engine, dist, group=None):
         self.e, self.dist, self.group = engine, dist, group
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         e = engine
-        self.GM = e.M * self.world
+        W = self.world
+        self.GM = e.M * W
         i32 = dict(dtype=torch.int32, device=e.dev)
+        f32 = dict(dtype=torch.float32, device=e.dev)
         self.g_rows = torch.zeros(self.GM, **i32)
         self.g_pos = torch.zeros(self.GM, **i32)
         self.sort_ws = torch.zeros(L.lib().dctr_sort_rows_workspace(self.GM), dtype=torch.uint8, device=e.dev)
         self.scat_ws = torch.zeros(L.lib().dctr_scatter_workspace(self.GM, e.ld), dtype=torch.uint8, device=e.dev)
         self.is_fm = not hasattr(e, "widths")
+        self.gids = torch.zeros(W * e.N, e.F, **i32)
+        self.gwts = torch.zeros(W * e.N, e.F, **f32)
+        self.loss_slot = e.grads[e.n_params:e.n_params + 1]
+        if self.is_fm:
+            self.gg, self.gs = torch.zeros(W * e.N, **f32), torch.zeros(W * e.N, e.lds, **f32)
+        elif e.cross != "none":
+            if e.ge is None:
+                e.ge = torch.zeros(e.N, e.F, e.ldg, **f32)
+            self.gg = torch.zeros(W * e.N, e.F, e.ldg, **f32)
+        else:
+            self.gg = torch.zeros(W * e.N, e.dbuf[0].stride(0), **f32)
+
+    def _gather(self, out, t):
+        self.dist.all_gather_into_tensor(out, t.contiguous(), group=self.group)
+        return out
 
     def _sort_global(self, gids):
         e = self.e
         L.call("dctr_sort_rows", gids.data_ptr(), self.GM, e.X, self.g_rows.data_ptr(), self.g_pos.data_ptr(),
                self.sort_ws.data_ptr(), self.sort_ws.numel(), torch.cuda.current_stream(e.dev).cuda_stream)
 
+    def _reduce_dense(self):
+        """ONE all-reduce for the dense gradients and the loss (the loss rides in the tail of the gradient buffer)."""
+        e = self.e
+        self.loss_slot.copy_(e.loss)
+        allreduce_dense(self.dist, e.grads, self.group)
+        e.loss.copy_(self.loss_slot)
+
     def train_step(self, lr, decay=1.0, gscale=1.0, train_bias=True, last_decay=1.0):
-        e, dist = self.e, self.dist
+        e = self.e
         cur = torch.cuda.current_stream(e.dev)
-        gids = all_gather_cat(dist, e.ids, self.group)
-        gwts = None if e.wts_are_ones else all_gather_cat(dist, e.wts, self.group)
+        gids = self._gather(self.gids, e.ids)
+        gwts = None if e.wts_are_ones else self._gather(self.gwts, e.wts)
         e.side.wait_stream(cur)
         with torch.cuda.stream(e.side):
             self._sort_global(gids)
@@ -72,38 +99,35 @@ class DataParallelStep(object):
         if train_bias:
             col = 0 if e.bias_first else F * d + e.crossw
             L.call("dctr_col_wsum", dz.data_ptr() + 4 * col, ldd, N, 1, None, L.ptr(e.bias(e.grads)), L.ptr(e.col_ws), e.col_ws.numel(), st)
-        e.join_wgrad()
-        allreduce_dense(dist, e.grads, self.group)
-        allreduce_dense(dist, e.loss, self.group)
         if e.cross != "none":
             wts = None if e.wts_are_ones else e.wts
             L.call("dctr_cross_bwd", L.ptr(e.ids), L.ptr(wts), L.ptr(e.table), e.X, e.ld, N, F, d, L.CROSS[e.cross],
                    L.ptr(dz), ldd, L.ptr(e.ge), e.ldg, st)
-            gg = all_gather_cat(dist, e.ge, self.group)
+            gg = self._gather(self.gg, e.ge)
             g, g_ld_n, g_ld_f, w = gg.data_ptr(), F * e.ldg, e.ldg, None
         else:
-            gg = all_gather_cat(dist, dz, self.group)
+            gg = self._gather(self.gg, dz)
             g, g_ld_n, g_ld_f, w = gg.data_ptr() + (4 if e.bias_first else 0), ldd, d, L.ptr(gwts)
+        e.join_wgrad()
+        self._reduce_dense()
         cur.wait_stream(e.side)
         L.call("dctr_scatter_sgd", e.scatter_mode, self.g_rows.data_ptr(), self.g_pos.data_ptr(), self.GM, F, d, g, g_ld_n, g_ld_f, w,
                float(lr), float(decay), L.ptr(e.table), e.X, e.ld, self.scat_ws.data_ptr(), self.scat_ws.numel(), st)
         e.dense_update(lr, last_decay)
-        self._keep = (gids, gwts, gg)       # keep the gathered buffers alive until the stream has consumed them
 
     def train_step_fm(self, lr, lam=0.0, gscale=1.0, dense_l2=True):
-        e, dist = self.e, self.dist
+        e = self.e
         cur = torch.cuda.current_stream(e.dev)
-        gids = all_gather_cat(dist, e.ids, self.group)
-        gwts = None if e.wts_are_ones else all_gather_cat(dist, e.wts, self.group)
+        gids = self._gather(self.gids, e.ids)
+        gwts = None if e.wts_are_ones else self._gather(self.gwts, e.wts)
         e.side.wait_stream(cur)
         with torch.cuda.stream(e.side):
             self._sort_global(gids)
         e.forward(True, gscale)
         st = cur.cuda_stream
         L.call("dctr_vec_sum", L.ptr(e.g), e.N, 1.0, L.ptr(e.grads), st)
-        allreduce_dense(dist, e.grads, self.group)
-        allreduce_dense(dist, e.loss, self.group)
-        gg, gs = all_gather_cat(dist, e.g, self.group), all_gather_cat(dist, e.s, self.group)
+        self._reduce_dense()
+        gg, gs = self._gather(self.gg, e.g), self._gather(self.gs, e.s)
         cur.wait_stream(e.side)
         decay = 1.0 - lr * lam
         L.call("dctr_scatter_sgd_fm", self.g_rows.data_ptr(), self.g_pos.data_ptr(), self.GM, e.F, e.d, gg.data_ptr(), gs.data_ptr(),
@@ -111,7 +135,6 @@ class DataParallelStep(object):
         if lam != 0.0 and dense_l2:
             L.call("dctr_decay_sweep", L.ptr(e.table), e.X, e.ld, float(decay), self.g_rows.data_ptr(), self.GM, st)
         L.call("dctr_dense_sgd", L.ptr(e.params), L.ptr(e.grads), 1, float(lr), float(decay), st)
-        self._keep = (gids, gwts, gg, gs)
 
 
 # ======================================================================================================
@@ -257,10 +280,32 @@ def attach(model, dist, group=None):
     batch-size-dependent constants see the GLOBAL batch: 'mean' reduce and the decay 1-2*lambda*lr/b_size."""
     dp = DataParallelStep(model.engine, dist, group)
     model.dp = dp
-    model.use_graph = False           # NCCL collectives are issued eagerly between the kernel groups
+    # kernels AND collectives of a step replay as one CUDA graph (NCCL is capturable); DCTR_DP_GRAPH=0 issues them eagerly
+    model.use_graph = os.environ.get("DCTR_DP_GRAPH", "1") != "0"
+    model._graph, model._warm = None, 0
     model.global_N = model.N * dp.world
     if dp.is_fm:
         model.engine.train_step = dp.train_step_fm
     else:
         model.engine.train_step = dp.train_step
     return dp
+
+
+def shutdown(dist, models=()):
+    """Tear the process group down.  Captured data-parallel steps hold NCCL work: drop the graphs first, drain the
+    device, meet at a barrier -- and do not let a stuck communicator teardown keep a finished job alive."""
+    import gc
+    import sys
+    import threading
+    for m in models:
+        m._graph = None
+    gc.collect()
+    torch.cuda.synchronize()
+    dist.barrier()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    timer = threading.Timer(20.0, lambda: os._exit(0))
+    timer.daemon = True
+    timer.start()
+    dist.destroy_process_group()
+    timer.cancel()

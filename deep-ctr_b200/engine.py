@@ -59,7 +59,7 @@ class StepEngine:
         off += 4
         self.n_params = off
         self.params = torch.zeros(off, **f32)
-        self.grads = torch.zeros(off, **f32)
+        self.grads = torch.zeros(off + 4, **f32)          # + a 4-float tail: the loss rides along in the data-parallel all-reduce
         # ---- activations / scratch ----
         self.ldi = [_r4(w) for w in self.widths]
         self.ins = [torch.zeros(N, self.ldi[l], **f32) for l in range(self.nl)]
@@ -299,7 +299,8 @@ class FMEngine:
         self.M = M
         self.table = torch.zeros(self.X, self.ld, **f32)
         self.params = torch.zeros(4, **f32)     # [b, -, -, -]
-        self.grads = torch.zeros(4, **f32)
+        self.grads = torch.zeros(8, **f32)          # [gb, -, -, -, loss slot of the data-parallel all-reduce, ...]
+        self.n_params = 4
         self.ids = torch.zeros(N, self.F, **i32)
         self.wts = torch.ones(N, self.F, **f32)
         self.y = torch.zeros(N, **f32)

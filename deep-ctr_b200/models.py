@@ -12,11 +12,13 @@ Deviations, all forced by the environment or by reference defects (SURVEY.md sec
   * only plain SGD ('sgd') is on the fast path; 'adam' / 'ftrl' (tf_util.py:17-25) raise NotImplementedError;
   * FNN_OP_L3 sizes h1_w from the forward's true width F*d + d*d + 1 (Q2).
 """
+import os
 import pickle
 
 import numpy as np
 import torch
 
+from . import _lib as L
 from .engine import FMEngine, StepEngine
 
 
@@ -169,7 +171,8 @@ class _Base(object):
                 return
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            # thread_local: NCCL's watchdog thread may query events while a data-parallel step is being captured
+            with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 self._device_step()
             self._graph = g
             # capture does not execute: fall through to the first replay
@@ -332,6 +335,8 @@ class _FNNBase(_Base):
         self.v_wt_hldr, self.c_id_hldr, self.c_wt_hldr = Placeholder("v_wt"), Placeholder("c_id"), Placeholder("c_wt")
         self.lbl_hldr = Placeholder("lbl")
         self._num_ids = np.arange(self.n_num, dtype=np.int64)[None, :]
+        self._offsets64 = np.ascontiguousarray(self.offsets, dtype=np.int64)
+        self._pack_threads = max(1, min(8, (os.cpu_count() or 2) // 2))
         self._masks = None
         if mode == "train":
             self._keep_prob = float(_reg_argv[0])
@@ -383,9 +388,28 @@ class _FNNBase(_Base):
         wts = np.concatenate([np.asarray(v_wts).reshape(n, self.n_num), np.asarray(c_wts)], axis=1)
         return ids, wts
 
+    def _pack_feed(self, v_wts, c_ids, c_wts):
+        """feed -> staging blocks in one native pass (dctr_host_pack_fields): the offset add of FNN.py:65-69, the int32
+        cast and the numeric | categorical concatenation, without numpy temporaries."""
+        h = self._stage.host
+        N, n_cat = self.N, self.X_feas - self.n_num
+        c_ids = np.ascontiguousarray(c_ids)
+        if c_ids.dtype not in (np.int32, np.int64):
+            c_ids = c_ids.astype(np.int64)
+        v_wts = np.ascontiguousarray(v_wts, dtype=np.float32)
+        c_wts = np.ascontiguousarray(c_wts, dtype=np.float32)
+        if c_ids.shape != (N, n_cat) or c_wts.shape != (N, n_cat) or v_wts.size != N * self.n_num:
+            raise ValueError("feed shapes %r %r %r do not match batch %d x (%d + %d) fields"
+                             % (v_wts.shape, c_ids.shape, c_wts.shape, N, self.n_num, n_cat))
+        L.call("dctr_host_pack_fields", c_ids.ctypes.data, c_ids.dtype.itemsize, self._offsets64.ctypes.data,
+               v_wts.ctypes.data if self.n_num else None, c_wts.ctypes.data, N, self.n_num, n_cat,
+               h["ids"].ctypes.data, h["wts"].ctypes.data, self._pack_threads)
+
     def train_step(self, feed):
-        ids, wts = self._global(feed[self.v_wt_hldr], feed[self.c_id_hldr], feed[self.c_wt_hldr])
-        return self._stage_and_step(ids, wts, np.asarray(feed[self.lbl_hldr]).reshape(self.N))
+        self._pack_feed(feed[self.v_wt_hldr], feed[self.c_id_hldr], feed[self.c_wt_hldr])
+        np.copyto(self._stage.host["y"], np.asarray(feed[self.lbl_hldr]).reshape(self.N), casting="unsafe")
+        self._pre_step()
+        return self._finish_step()
 
     def _fetch(self, kind, feed):
         if kind == "eval_preds":       # global ids [E, X_feas]; the graph subtracts offsets itself (FNN.py:65-69)

@@ -65,6 +65,13 @@ int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, const float* ta
 int dctr_arrange_fields(const int32_t* feats, const int32_t* feat_field, int N, int J, int F, int32_t pad_row,
                         int32_t* ids, float* wts, void* stream);
 
+/* HOST helper (no device work, no stream): pack one batch of the TF-form feed into the [N, F] staging blocks,
+ * F = n_num + n_cat.  ids[n, j] = j, wts[n, j] = v_wts[n, j] for the numeric fields (FNN.py:41-43);
+ * ids[n, n_num + j] = c_ids[n, j] + offsets[j] (the offset add of FNN.py:65-69), wts = c_wts (NULL -> 1).
+ * c_ids: dense [N, n_cat] int32 (id_bytes 4) or int64 (id_bytes 8); rows are split over <= threads host threads. */
+int dctr_host_pack_fields(const void* c_ids, int id_bytes, const int64_t* offsets, const float* v_wts,
+                          const float* c_wts, int64_t N, int n_num, int n_cat, int32_t* ids, float* wts, int threads);
+
 /* row gather: out[i, 0:ld) = table[ids[i], 0:ld), i < M.  The owner-side lookup of the row-sharded table (SURVEY 8(e):
  * rows live on rank row % world) and the permutation of per-slot gradient rows into all-to-all order. */
 int dctr_gather_rows(const int32_t* ids, const float* table, int64_t X, int ld, int64_t M, float* out, void* stream);

@@ -38,7 +38,7 @@ def main():
     ddist.attach(fm_dp, dist)
     fm_ref = FM(GN, [X, F, k - 1], ["uniform", -0.05, 0.05, [1, 2], None], ["sgd", 0.05, "mean"], [0.01], "train", GN)
     fm_ref.use_graph = False
-    for step in range(3):
+    for step in range(6):            # 2 eager steps, the capture, then graph replays of kernels + NCCL collectives
         feats = np.stack([rng.integers(0, X // F, GN) + f * (X // F) for f in range(F)], 1)
         feats[:, 0] = 3
         y = rng.integers(0, 2, GN)
@@ -61,7 +61,7 @@ def main():
     assert all(torch.equal(ts[0], x) for x in ts)
     if rank == 0:
         print("dp_check ok: world=%d" % world)
-    dist.destroy_process_group()
+    ddist.shutdown(dist, [dp, fm_dp])
 
 
 if __name__ == "__main__":

@@ -70,7 +70,7 @@ def main():
         np.testing.assert_allclose(pe, pr[sl], rtol=2e-5, atol=1e-6)
         if rank == 0:
             print("shard_check %s ok: world=%d loss=%.6f" % (cls_name, world, l1))
-    dist.destroy_process_group()
+    ddist.shutdown(dist)
 
 
 if __name__ == "__main__":

@@ -55,3 +55,24 @@ def test_missing_library_fails_loudly(monkeypatch, tmp_path):
         assert "no CPU fallback" in str(e)
     else:
         raise AssertionError("expected RuntimeError")
+
+
+def test_host_pack_fields(built_lib):
+    """the one HOST entry point: offset add + int32 cast + numeric | categorical concatenation (FNN.py:41-43, 65-69)"""
+    import numpy as np
+    from deepctr_b200 import _lib
+    rng = np.random.default_rng(3)
+    for N, nn, nc, dt in [(1, 0, 3, np.int64), (10001, 13, 26, np.int64), (50000, 2, 5, np.int32), (7, 3, 0, np.int64)]:
+        c = rng.integers(0, 1000, (N, nc)).astype(dt)
+        off = (np.arange(nc) * 1000 + nn).astype(np.int64)
+        v = rng.random((N, nn)).astype(np.float32)
+        cw = rng.random((N, nc)).astype(np.float32)
+        ids = np.full((N, nn + nc), -1, np.int32)
+        w = np.full((N, nn + nc), -1, np.float32)
+        for wts_given in (True, False):
+            _lib.call("dctr_host_pack_fields", c.ctypes.data if nc else None, c.dtype.itemsize, off.ctypes.data if nc else None,
+                      v.ctypes.data if nn else None, cw.ctypes.data if (wts_given and nc) else None, N, nn, nc,
+                      ids.ctypes.data, w.ctypes.data, 4)
+            assert np.array_equal(ids, np.concatenate([np.broadcast_to(np.arange(nn), (N, nn)), c.astype(np.int64) + off], 1))
+            assert np.array_equal(w, np.concatenate([v, cw if wts_given else np.ones_like(cw)], 1))
+    assert built_lib.dctr_host_pack_fields(None, 2, None, None, None, 1, 0, 1, None, None, 1) == _lib.EINVAL
