@@ -65,7 +65,7 @@ class DataParallelStep(object):
                 e.ge = torch.zeros(e.N, e.F, e.ldg, **f32)
             self.gg = torch.zeros(W * e.N, e.F, e.ldg, **f32)
         else:
-            self.gg = torch.zeros(W * e.N, e.dbuf[0].stride(0), **f32)
+            self.gg = torch.zeros(W * e.N, (e.dz0 if e.nl > 1 else e.dbuf[0]).stride(0), **f32)
 
     def _gather(self, out, t):
         self.dist.all_gather_into_tensor(out, t.contiguous(), group=self.group)
@@ -86,10 +86,10 @@ class DataParallelStep(object):
     def train_step(self, lr, decay=1.0, gscale=1.0, train_bias=True, last_decay=1.0):
         e = self.e
         cur = torch.cuda.current_stream(e.dev)
-        gids = self._gather(self.gids, e.ids)
-        gwts = None if e.wts_are_ones else self._gather(self.gwts, e.wts)
         e.side.wait_stream(cur)
-        with torch.cuda.stream(e.side):
+        with torch.cuda.stream(e.side):          # id / weight exchange and the global sort: off the forward's critical path
+            gids = self._gather(self.gids, e.ids)
+            gwts = None if e.wts_are_ones else self._gather(self.gwts, e.wts)
             self._sort_global(gids)
         e.forward(True, gscale)
         dz = e.backward()
@@ -118,10 +118,10 @@ class DataParallelStep(object):
     def train_step_fm(self, lr, lam=0.0, gscale=1.0, dense_l2=True):
         e = self.e
         cur = torch.cuda.current_stream(e.dev)
-        gids = self._gather(self.gids, e.ids)
-        gwts = None if e.wts_are_ones else self._gather(self.gwts, e.wts)
         e.side.wait_stream(cur)
-        with torch.cuda.stream(e.side):
+        with torch.cuda.stream(e.side):          # id / weight exchange and the global sort: off the forward's critical path
+            gids = self._gather(self.gids, e.ids)
+            gwts = None if e.wts_are_ones else self._gather(self.gwts, e.wts)
             self._sort_global(gids)
         e.forward(True, gscale)
         st = cur.cuda_stream

@@ -65,6 +65,7 @@ class StepEngine:
         self.ins = [torch.zeros(N, self.ldi[l], **f32) for l in range(self.nl)]
         maxw = max(self.ldi)
         self.dbuf = [torch.zeros(N, maxw, **f32) for _ in range(3)]
+        self.dz0 = torch.zeros(N, self.ldi[0], **f32)         # d loss / d z of the embedding layer: its own, narrower buffer
         self.ids = torch.zeros(N, F_, **i32)
         self.wts = torch.ones(N, F_, **f32)
         self.y = torch.zeros(N, **f32)
@@ -215,9 +216,12 @@ class StepEngine:
             nxt = (cur + 1) % 3
             if readers[nxt] is not None:
                 main.wait_event(readers[nxt])
-            L.call(self.gemm_fn, L.GEMM_NT, N, K, Hl, p(dpre), ldd, p(self.W(l)), self.ldw[l], p(self.dbuf[nxt]), ldd,
+            dout, ldo = (self.dbuf[nxt], ldd) if l > 0 else (self.dz0, self.dz0.stride(0))
+            L.call(self.gemm_fn, L.GEMM_NT, N, K, Hl, p(dpre), ldd, p(self.W(l)), self.ldw[l], p(dout), ldo,
                    L.EPI_DGRAD, L.ACT[act], None, p(self.ins[l]), self.ldi[l], mp, mld, 1, st)
             cur = nxt
+        if last > 0:
+            return self.dz0
         return self.dbuf[cur]
 
     def sort_ids(self, ids=None, M=None, rows=None, pos=None, ws=None):
