@@ -4,16 +4,19 @@
 //   C = A*B with A = A_hi + A_lo, B = B_hi + B_lo (hi = rna-tf32(x), lo = rna-tf32(x - hi)):
 //       acc += A_lo*B_hi + A_hi*B_lo + A_hi*B_hi        (fp32 accumulate in TMEM; the dropped A_lo*B_lo term is ~2^-22)
 //
-//   CTA = 10 warps, one 128 x BN output tile, BK = 32 fp32 (one 128-byte swizzle row), NS-stage mbarrier pipeline:
-//     warp 9     one lane issues the TMA loads (cp.async.bulk.tensor, SWIZZLE_128B, out-of-bounds zero fill) of the raw
-//                fp32 operand boxes: a K-contiguous operand as one [rows x 32] box (canonical K-major UMMA layout), an
-//                MN-contiguous operand as rows/32 boxes of [32 k x 32 mn] (SWIZZLE_128B_ATOM_32B, the MN-major fp32 UMMA layout) -- no
-//                transposes anywhere, the instruction descriptor carries the major-ness;
-//     warps 0-7  split every landed stage in place: raw -> hi (same bytes) and lo (second buffer, same layout), then
-//                fence.proxy.async + mbarrier arrive; after the last k-block they run the epilogue: tcgen05.ld (lane =
+//   CTA = 10 warps, one 128 x BN output tile, BK = 32 fp32 (one 128-byte row), NS-stage mbarrier pipeline:
+//     warp 9     one lane issues the TMA loads (cp.async.bulk.tensor, out-of-bounds zero fill) of the raw fp32 operand
+//                boxes.  B goes straight into its UMMA layout: K-contiguous as one [BN x 32] SWIZZLE_128B box, MN-contiguous
+//                as BN/32 boxes of [32 k x 32 n] (SWIZZLE_128B_ATOM_32B, the only MN-major fp32 UMMA layout).  A is only
+//                ever read by the converter warps, so it lands in whatever layout they read without bank conflicts;
+//     warps 0-7  split every landed stage: B raw -> hi in place and lo into a twin buffer (fence.proxy.async); A raw ->
+//                hi / lo written to TENSOR MEMORY (tcgen05.st, lane = row, column = k), so the MMAs take A from TMEM and
+//                only B crosses the shared-memory port a second time -- the port, not the tensor pipe, bounds this
+//                kernel.  After the last k-block the same warps run the epilogue: tcgen05.ld (lane =
 //                output row) -> bias / act / mask or dgrad -> 128-bit stores;
-//     warp 8     allocates TMEM; one lane issues 4 k-steps x 3 tcgen05.mma per stage; tcgen05.commit frees the stage
-//                for the TMA lane and finally signals the epilogue.
+//     warp 8     allocates TMEM; one lane issues 4 k-steps x 3 tcgen05.mma (A in TMEM, B by descriptor) per stage;
+//                tcgen05.commit frees the shared-memory stage for the TMA lane and the TMEM A slot for the converters,
+//                and finally signals the epilogue.
 #include <cuda.h>
 #include "common.cuh"
 
@@ -22,8 +25,8 @@ namespace tc {
 
 constexpr int kBM = 128;
 constexpr int kBKf = 32;                 // fp32 per k-block = 128 bytes
-constexpr int kConverters = 256;
-constexpr int kThreads = 320;
+constexpr int kConverters = 256;          // 8 warps (16 measured 4% slower: the split is not what bounds the kernel)
+constexpr int kThreads = kConverters + 64;
 constexpr int kMmaWarp = kConverters / 32, kTmaWarp = kMmaWarp + 1;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -70,6 +73,20 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// same with A read from tensor memory (lane = row, one 32-bit column per k)
+__device__ __forceinline__ void mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// 8 consecutive columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const float (&v)[8]) {
+    const uint32_t* r = reinterpret_cast<const uint32_t*>(v);
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 // arrives on the mbarrier once every tcgen05.mma issued so far by this thread has completed
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -181,8 +198,18 @@ template <int BN, int NS>
 struct TcSmem {
     static constexpr int kA = kBM * 128;           // bytes of one [128 x 32] fp32 tile
     static constexpr int kB = BN * 128;
-    static constexpr int kStage = 2 * kA + 2 * kB;  // A raw->hi | A lo | B raw->hi | B lo
+    static constexpr int kStage = kA + 2 * kB;      // A raw | B raw->hi | B lo
     static constexpr int kBytes = NS * kStage + 1024 /* alignment slack */ + 256 /* barriers */;
+};
+
+// TMEM columns: kHiAcc accumulators for hi*hi + one for the cross terms, then a ring of A slots (hi 32 | lo 32 columns)
+constexpr int kHiAcc = 2;
+template <int BN>
+struct TcTmem {
+    static constexpr int kAcc = (kHiAcc + 1) * BN;
+    static constexpr int kSlots = BN <= 64 ? 4 : 2;
+    static constexpr int kCols = 512;
+    static_assert(kAcc + kSlots * 64 <= kCols, "TMEM budget");
 };
 
 // raw fp32 -> hi in place, lo into the twin buffer (same swizzled layout): 16-byte vectors, conflict-free
@@ -202,16 +229,51 @@ __device__ __forceinline__ void split_in_place(uint8_t* hi, uint8_t* lo, int t) 
     }
 }
 
+// A tile -> tensor memory.  Thread = (row quadrant q = warp % 4, lane = row in the quadrant, k part h = warp / 4): reads its
+// kAVals raw values from shared memory, splits them, writes hi and lo to its TMEM lane.
+//   AK  (K-contiguous A, one SWIZZLE_128B box): row r at r*128 B, 16-byte chunk c at position c ^ (r % 8)
+//   !AK (MN-contiguous A, four plain [32 k x 32 m] boxes): element (k, m) of quadrant q at q*4096 + k*128 + m*4
+constexpr int kAVals = kBKf / (kConverters / 128);      // 16 with 8 converter warps
+template <bool AK>
+__device__ __forceinline__ void a_to_tmem(const uint8_t* a_raw, uint32_t slot_addr, int warp, int lane) {
+    const int q = warp & 3, h = warp >> 2;
+    float x[kAVals];
+    if (AK) {
+        const int r = q * 32 + lane;
+        const uint8_t* row = a_raw + (r >> 3) * 1024 + (r & 7) * 128;
+#pragma unroll
+        for (int c = 0; c < kAVals / 4; ++c) {
+            const float4 v = *reinterpret_cast<const float4*>(row + ((((kAVals / 4) * h + c) ^ (r & 7)) << 4));
+            x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
+        }
+    } else {
+        const uint8_t* col = a_raw + q * 4096 + lane * 4 + (kAVals * h) * 128;
+#pragma unroll
+        for (int j = 0; j < kAVals; ++j) x[j] = *reinterpret_cast<const float*>(col + j * 128);
+    }
+    const uint32_t ta = slot_addr + ((uint32_t)(q * 32) << 16) + (uint32_t)(kAVals * h);
+#pragma unroll
+    for (int g = 0; g < kAVals / 8; ++g) {
+        float hi[8], lo[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) split_tf32(x[8 * g + j], hi[j], lo[j]);
+        tmem_st8(ta + 8 * g, hi);
+        tmem_st8(ta + 32 + 8 * g, lo);
+    }
+}
+
 template <int BN, int NS, bool AK, bool BK>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB) {
     using S = TcSmem<BN, NS>;
+    using T = TcTmem<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint64_t* raw_full = reinterpret_cast<uint64_t*>(smem + NS * S::kStage);
     uint64_t* conv_full = raw_full + NS;
     uint64_t* empty = conv_full + NS;
-    uint64_t* accum_full = empty + NS;
+    uint64_t* a_empty = empty + NS;
+    uint64_t* accum_full = a_empty + T::kSlots;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_full + 1);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -223,26 +285,30 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
 
     if (tid == 0) {
         for (int s = 0; s < NS; ++s) { mbar_init(raw_full + s, 1); mbar_init(conv_full + s, kConverters); mbar_init(empty + s, 1); }
+        for (int t = 0; t < T::kSlots; ++t) mbar_init(a_empty + t, 1);
         mbar_init(accum_full, 1);
         fence_mbar_init();
     }
-    constexpr int kHiAcc = BN <= 64 ? 3 : 3;                  // hi*hi accumulators (+1 for the cross terms)
-    constexpr uint32_t kTmemCols = BN <= 64 ? 256 : 512;      // (kHiAcc + 1) * BN fp32 columns, power of two
-    if (warp == kMmaWarp) tmem_alloc(tmem_slot, kTmemCols);
+    if (warp == kMmaWarp) tmem_alloc(tmem_slot, T::kCols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_a0 = tmem_base + T::kAcc;
 
     if (warp < kMmaWarp) {
         // ===== converters =====
         for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % NS;
+            const int s = kb % NS, t = kb % T::kSlots;
             mbar_wait(raw_full + s, (kb / NS) & 1);
             uint8_t* st = smem + s * S::kStage;
-            split_in_place<S::kA>(st, st + S::kA, tid);
-            split_in_place<S::kB>(st + 2 * S::kA, st + 2 * S::kA + S::kB, tid);
+            split_in_place<S::kB>(st + S::kA, st + S::kA + S::kB, tid);
             fence_proxy_async();          // generic-proxy stores -> visible to the tensor core's async proxy
+            mbar_wait(a_empty + t, ((kb / T::kSlots) & 1) ^ 1);      // the MMAs that read this TMEM slot have completed
+            tc_fence_after();
+            a_to_tmem<AK>(st, tmem_a0 + t * 64, warp, lane);
+            tmem_st_wait();
+            tc_fence_before();
             mbar_arrive(conv_full + s);
         }
         // ===== epilogue: TMEM lane = output row =====
@@ -250,11 +316,11 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
             mbar_wait(accum_full, 0);
             tc_fence_after();
         }
-        // a warp reaches the TMEM lanes 32*(warp%4)..+31 only: warps w and w+4 share a row quadrant and split the columns
+        // a warp reaches the TMEM lanes 32*(warp%4)..+31 only: warps w, w+4, w+8, ... share a row quadrant and split the columns
         const int quad = warp & 3;
         const int m = m0 + quad * 32 + lane;
 #pragma unroll 1
-        for (int c = (warp >> 2) * 32; c < BN; c += 64) {
+        for (int c = (warp >> 2) * 32; c < BN; c += (kConverters / 128) * 32) {
             if (n0 + c >= p.N) break;                   // uniform across the warp
             float v[32];
             if (nkb > 0) {
@@ -288,7 +354,7 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
 #pragma unroll
                 for (int i = 0; i < kBM / 32; ++i) tma_load_2d(st + i * 4096, &mapA, m0 + 32 * i, k0, raw_full + s);
             }
-            uint8_t* sb = st + 2 * S::kA;
+            uint8_t* sb = st + S::kA;
             if (BK) tma_load_2d(sb, &mapB, k0, n0, raw_full + s);
             else {
 #pragma unroll
@@ -298,35 +364,37 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
     } else if (warp == kMmaWarp && lane == 0) {
         // ===== MMA issuer =====
         // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (1 << 4), A = B = TF32 (2 << 7, 2 << 10),
-        // a_major bit 15 / b_major bit 16 (0 = K-major, 1 = MN-major), N >> 3 at bit 17, M >> 4 at bit 24
-        constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((AK ? 0u : 1u) << 15) | ((BK ? 0u : 1u) << 16) |
+        // a_major bit 15 = 0 (A comes from TMEM: always K-major) / b_major bit 16 (0 = K-major, 1 = MN-major),
+        // N >> 3 at bit 17, M >> 4 at bit 24
+        constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((BK ? 0u : 1u) << 16) |
                                    ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
         for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % NS;
+            const int s = kb % NS, ts = kb % T::kSlots;
             mbar_wait(conv_full + s, (kb / NS) & 1);
             tc_fence_after();
-            const uint32_t sa = smem_u32(smem + s * S::kStage), sb = sa + 2 * S::kA;
+            const uint32_t sb = smem_u32(smem + s * S::kStage) + S::kA;
+            const uint32_t ta = tmem_a0 + ts * 64;
 #pragma unroll
-            for (int k4 = 0; k4 < kBKf / 8; ++k4) {           // UMMA_K = 8 tf32: +32 B inside a K-major row, +1024 B (8 k-rows = 2 atoms) MN-major
-                const uint64_t a_hi = AK ? make_desc(sa) + 2 * k4 : make_desc_mn(sa + k4 * 1024);
-                const uint64_t a_lo = AK ? make_desc(sa + S::kA) + 2 * k4 : make_desc_mn(sa + S::kA + k4 * 1024);
+            for (int k4 = 0; k4 < kBKf / 8; ++k4) {           // UMMA_K = 8 tf32: 8 TMEM columns of A; B +32 B inside a K-major row, +1024 B (8 k-rows = 2 atoms) MN-major
+                const uint32_t a_hi = ta + k4 * 8, a_lo = ta + 32 + k4 * 8;
                 const uint64_t b_hi = BK ? make_desc(sb) + 2 * k4 : make_desc_mn(sb + k4 * 1024);
                 const uint64_t b_lo = BK ? make_desc(sb + S::kB) + 2 * k4 : make_desc_mn(sb + S::kB + k4 * 1024);
                 // Several accumulators shorten every addition chain (the tensor core truncates when it accumulates): the
                 // hi*hi products of k-step t go to accumulator t % kHiAcc, the two small cross terms to the last one;
                 // the epilogue adds them up in fp32.
                 const int t = kb * (kBKf / 8) + k4;
-                mma_tf32(tmem_base + kHiAcc * BN, a_lo, b_hi, idesc, t != 0);
-                mma_tf32(tmem_base + kHiAcc * BN, a_hi, b_lo, idesc, 1);
-                mma_tf32(tmem_base + (t % kHiAcc) * BN, a_hi, b_hi, idesc, t >= kHiAcc);
+                mma_tf32_ts(tmem_base + kHiAcc * BN, a_lo, b_hi, idesc, t != 0);
+                mma_tf32_ts(tmem_base + kHiAcc * BN, a_hi, b_lo, idesc, 1);
+                mma_tf32_ts(tmem_base + (t % kHiAcc) * BN, a_hi, b_hi, idesc, t >= kHiAcc);
             }
-            mma_commit(empty + s);        // frees the stage when these MMAs have read it
+            mma_commit(empty + s);        // frees the shared-memory stage when these MMAs have read it ...
+            mma_commit(a_empty + ts);     // ... and the TMEM A slot
         }
         if (nkb > 0) mma_commit(accum_full);
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == kMmaWarp) tmem_dealloc(tmem_base, kTmemCols);
+    if (warp == kMmaWarp) tmem_dealloc(tmem_base, T::kCols);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -348,7 +416,7 @@ static EncodeTiledFn encode_fn() {
 //   kcontig: element (r, k) at base[r*ld + k] -> dims {K, rows}, box {32 k, box_rows}      (K-major UMMA tile)
 //   else:    element (r, k) at base[k*ld + r] -> dims {rows, K}, box {32 mn, 32 k}         (MN-major UMMA atoms)
 // Out-of-range parts of a box are zero-filled by the TMA unit, which is what pads the M / N / K edges.
-static int make_map(CUtensorMap* map, const float* base, int ld, int rows, int K, bool kcontig, int box_rows) {
+static int make_map(CUtensorMap* map, const float* base, int ld, int rows, int K, bool kcontig, int box_rows, bool plain_mn = false) {
     EncodeTiledFn fn = encode_fn();
     if (!fn) { set_error("gemm_tc: cuTensorMapEncodeTiled is not available from this driver"); return DCTR_ECUDA; }
     cuuint64_t dims[2] = {(cuuint64_t)(kcontig ? K : rows), (cuuint64_t)(kcontig ? rows : K)};
@@ -356,7 +424,8 @@ static int make_map(CUtensorMap* map, const float* base, int ld, int rows, int K
     cuuint32_t box[2] = {32u, (cuuint32_t)(kcontig ? box_rows : 32)};
     cuuint32_t estr[2] = {1u, 1u};
     CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, kcontig ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    kcontig ? CU_TENSOR_MAP_SWIZZLE_128B : (plain_mn ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B),
                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("gemm_tc: cuTensorMapEncodeTiled failed (%d) rows=%d K=%d ld=%d", (int)r, rows, K, ld); return DCTR_ECUDA; }
@@ -368,7 +437,7 @@ static int launch_tc(int layout, const TcParams& p, dim3 grid, cudaStream_t st) 
     constexpr int bytes = TcSmem<BN, NS>::kBytes;
     const bool ak = layout != DCTR_GEMM_TN, bk = layout == DCTR_GEMM_NT;
     CUtensorMap mapA, mapB;
-    int rc = make_map(&mapA, p.A, p.lda, p.M, p.K, ak, kBM);
+    int rc = make_map(&mapA, p.A, p.lda, p.M, p.K, ak, kBM, /*plain_mn=*/true);    // A is read by the converter warps only
     if (rc) return rc;
     if ((rc = make_map(&mapB, p.B, p.ldb, p.N, p.K, bk, BN))) return rc;
     cudaError_t e = cudaSuccess;
@@ -417,8 +486,8 @@ extern "C" int dctr_gemm_tc(int layout, int M, int N, int K, const float* A, int
     // narrow N tiles when a 128-wide tiling would leave most SMs idle
     if (N <= 64 || mt * ceil_div(N, 128) * splits < kNumSMs / 2) {
         dim3 grid(ceil_div(N, 64), mt, splits);
-        return tc::launch_tc<64, 4>(layout, p, grid, st);
+        return tc::launch_tc<64, 6>(layout, p, grid, st);
     }
     dim3 grid(ceil_div(N, 128), mt, splits);
-    return tc::launch_tc<128, 3>(layout, p, grid, st);
+    return tc::launch_tc<128, 4>(layout, p, grid, st);
 }
