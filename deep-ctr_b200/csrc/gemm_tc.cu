@@ -147,13 +147,13 @@ struct TcParams {
 // runtime dispatch happens once per chunk, not once per element (a per-element switch inlined 128 times made the
 // kernel 41k instructions long and the epilogue instruction-cache bound: 14 us -> measured with %globaltimer).
 template <int EPI, int ACT>
-__device__ __forceinline__ float tc_epi1(const TcParams& p, int m, int n, float acc) {
+__device__ __forceinline__ float tc_epi1(const TcParams& p, int m, int n, float acc, float auxv) {
     if (EPI == DCTR_EPI_FWD) {
         float v = act_fwd(ACT, acc + (p.bias ? __ldg(p.bias + n) : 0.f));
         if (p.mask) v *= __ldg(p.mask + (int64_t)m * p.ldmask + n);
         return v;
     } else if (EPI == DCTR_EPI_DGRAD) {
-        float mk = 1.f, t = __ldg(p.aux + (int64_t)m * p.ldaux + n);
+        float mk = 1.f, t = auxv;
         if (p.mask) {
             mk = __ldg(p.mask + (int64_t)m * p.ldmask + n);
             if (mk == 0.f) return 0.f;
@@ -163,34 +163,51 @@ __device__ __forceinline__ float tc_epi1(const TcParams& p, int m, int n, float 
     }
     return acc;
 }
-template <int EPI, int ACT>
-__device__ __forceinline__ void tc_store_chunk(const TcParams& p, float* __restrict__ dst, int m, int nbase, const float (&v)[32]) {
-    const int nlast = p.N - 1;
+// One 32 x 32 chunk: the accumulators arrive with lane = row (TMEM), global memory wants lane = column.  The chunk goes
+// through a padded [32][33] shared-memory tile (conflict-free both ways); afterwards every warp instruction loads aux /
+// mask / bias and stores C along ONE row: 128 contiguous bytes instead of 32 rows x 4 bytes (the row-per-lane form cost
+// ~13 us per tile in the dgrad epilogue, more than a K = 300 main loop).
+// the dgrad epilogue's second operand (the stored activation) for rows mbase..mbase+31 of column n: 32 independent loads,
+// issued before the accumulators are even complete so their DRAM latency hides behind the main loop's tail
+__device__ __forceinline__ void tc_prefetch_aux(const TcParams& p, int mbase, int n, float (&ax)[32]) {
+    const bool on = p.epilogue == DCTR_EPI_DGRAD && n < p.N;
+    const float* src = p.aux + (int64_t)mbase * p.ldaux + n;
 #pragma unroll
-    for (int j = 0; j < 32; j += 4) {
-        const int n = nbase + j;
-        float4 o;      // columns past N reuse the last column's bias / mask / aux (loads stay in range) and are not stored
-        o.x = tc_epi1<EPI, ACT>(p, m, min(n, nlast), v[j]); o.y = tc_epi1<EPI, ACT>(p, m, min(n + 1, nlast), v[j + 1]);
-        o.z = tc_epi1<EPI, ACT>(p, m, min(n + 2, nlast), v[j + 2]); o.w = tc_epi1<EPI, ACT>(p, m, min(n + 3, nlast), v[j + 3]);
-        if (n + 3 < p.N) *reinterpret_cast<float4*>(dst + j) = o;
-        else {
-            if (n < p.N) dst[j] = o.x;
-            if (n + 1 < p.N) dst[j + 1] = o.y;
-            if (n + 2 < p.N) dst[j + 2] = o.z;
+    for (int r = 0; r < 32; ++r) ax[r] = (on && mbase + r < p.M) ? __ldg(src + (int64_t)r * p.ldaux) : 0.f;
+}
+template <int EPI, int ACT>
+__device__ __forceinline__ void tc_store_chunk(const TcParams& p, float* __restrict__ C, float* tile, int mbase, int nbase, int lane,
+                                               const float (&v)[32], const float (&ax)[32]) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = v[j];
+    __syncwarp();
+    const int n = nbase + lane;
+    if (n < p.N) {
+        if (EPI == DCTR_EPI_DGRAD) {        // fully unrolled: ax[] must stay in registers
+#pragma unroll
+            for (int r = 0; r < 32; ++r)
+                if (mbase + r < p.M) C[(int64_t)(mbase + r) * p.ldc + n] = tc_epi1<EPI, ACT>(p, mbase + r, n, tile[r * 33 + lane], ax[r]);
+        } else {                            // 32 inlined activations would only bloat the instruction stream
+            const int rows = min(32, p.M - mbase);
+#pragma unroll 8
+            for (int r = 0; r < rows; ++r)
+                C[(int64_t)(mbase + r) * p.ldc + n] = tc_epi1<EPI, ACT>(p, mbase + r, n, tile[r * 33 + lane], 0.f);
         }
     }
+    __syncwarp();
 }
-__device__ __forceinline__ void tc_store_dispatch(const TcParams& p, float* dst, int m, int nbase, const float (&v)[32]) {
+__device__ __forceinline__ void tc_store_dispatch(const TcParams& p, float* C, float* tile, int mbase, int nbase, int lane, const float (&v)[32],
+                                                  const float (&ax)[32]) {
     switch (p.epilogue == DCTR_EPI_NONE ? 0 : p.epilogue * 4 + p.act) {
-        case DCTR_EPI_FWD * 4 + DCTR_ACT_NONE: tc_store_chunk<DCTR_EPI_FWD, DCTR_ACT_NONE>(p, dst, m, nbase, v); break;
-        case DCTR_EPI_FWD * 4 + DCTR_ACT_TANH: tc_store_chunk<DCTR_EPI_FWD, DCTR_ACT_TANH>(p, dst, m, nbase, v); break;
-        case DCTR_EPI_FWD * 4 + DCTR_ACT_RELU: tc_store_chunk<DCTR_EPI_FWD, DCTR_ACT_RELU>(p, dst, m, nbase, v); break;
-        case DCTR_EPI_FWD * 4 + DCTR_ACT_SIGMOID: tc_store_chunk<DCTR_EPI_FWD, DCTR_ACT_SIGMOID>(p, dst, m, nbase, v); break;
-        case DCTR_EPI_DGRAD * 4 + DCTR_ACT_NONE: tc_store_chunk<DCTR_EPI_DGRAD, DCTR_ACT_NONE>(p, dst, m, nbase, v); break;
-        case DCTR_EPI_DGRAD * 4 + DCTR_ACT_TANH: tc_store_chunk<DCTR_EPI_DGRAD, DCTR_ACT_TANH>(p, dst, m, nbase, v); break;
-        case DCTR_EPI_DGRAD * 4 + DCTR_ACT_RELU: tc_store_chunk<DCTR_EPI_DGRAD, DCTR_ACT_RELU>(p, dst, m, nbase, v); break;
-        case DCTR_EPI_DGRAD * 4 + DCTR_ACT_SIGMOID: tc_store_chunk<DCTR_EPI_DGRAD, DCTR_ACT_SIGMOID>(p, dst, m, nbase, v); break;
-        default: tc_store_chunk<DCTR_EPI_NONE, DCTR_ACT_NONE>(p, dst, m, nbase, v); break;
+        case DCTR_EPI_FWD * 4 + DCTR_ACT_NONE: tc_store_chunk<DCTR_EPI_FWD, DCTR_ACT_NONE>(p, C, tile, mbase, nbase, lane, v, ax); break;
+        case DCTR_EPI_FWD * 4 + DCTR_ACT_TANH: tc_store_chunk<DCTR_EPI_FWD, DCTR_ACT_TANH>(p, C, tile, mbase, nbase, lane, v, ax); break;
+        case DCTR_EPI_FWD * 4 + DCTR_ACT_RELU: tc_store_chunk<DCTR_EPI_FWD, DCTR_ACT_RELU>(p, C, tile, mbase, nbase, lane, v, ax); break;
+        case DCTR_EPI_FWD * 4 + DCTR_ACT_SIGMOID: tc_store_chunk<DCTR_EPI_FWD, DCTR_ACT_SIGMOID>(p, C, tile, mbase, nbase, lane, v, ax); break;
+        case DCTR_EPI_DGRAD * 4 + DCTR_ACT_NONE: tc_store_chunk<DCTR_EPI_DGRAD, DCTR_ACT_NONE>(p, C, tile, mbase, nbase, lane, v, ax); break;
+        case DCTR_EPI_DGRAD * 4 + DCTR_ACT_TANH: tc_store_chunk<DCTR_EPI_DGRAD, DCTR_ACT_TANH>(p, C, tile, mbase, nbase, lane, v, ax); break;
+        case DCTR_EPI_DGRAD * 4 + DCTR_ACT_RELU: tc_store_chunk<DCTR_EPI_DGRAD, DCTR_ACT_RELU>(p, C, tile, mbase, nbase, lane, v, ax); break;
+        case DCTR_EPI_DGRAD * 4 + DCTR_ACT_SIGMOID: tc_store_chunk<DCTR_EPI_DGRAD, DCTR_ACT_SIGMOID>(p, C, tile, mbase, nbase, lane, v, ax); break;
+        default: tc_store_chunk<DCTR_EPI_NONE, DCTR_ACT_NONE>(p, C, tile, mbase, nbase, lane, v, ax); break;
     }
 }
 
@@ -311,16 +328,21 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
             tc_fence_before();
             mbar_arrive(conv_full + s);
         }
-        // ===== epilogue: TMEM lane = output row =====
+        // ===== epilogue: TMEM lane = output row, global memory lane = output column =====
+        // a warp reaches the TMEM lanes 32*(warp%4)..+31 only: warps w, w+4, ... share a row quadrant and split the columns
+        const int quad = warp & 3;
+        const int mbase = m0 + quad * 32;
+        constexpr int kCStep = (kConverters / 128) * 32;
+        float ax[32];
+        tc_prefetch_aux(p, mbase, n0 + (warp >> 2) * 32 + lane, ax);
         if (nkb > 0) {
             mbar_wait(accum_full, 0);
             tc_fence_after();
         }
-        // a warp reaches the TMEM lanes 32*(warp%4)..+31 only: warps w, w+4, w+8, ... share a row quadrant and split the columns
-        const int quad = warp & 3;
-        const int m = m0 + quad * 32 + lane;
+        // every pipeline stage is drained by now (accum_full = all MMAs complete): its first bytes become the transpose tiles
+        float* tile = reinterpret_cast<float*>(smem) + warp * (32 * 33);
 #pragma unroll 1
-        for (int c = (warp >> 2) * 32; c < BN; c += (kConverters / 128) * 32) {
+        for (int c = (warp >> 2) * 32; c < BN; c += kCStep) {
             if (n0 + c >= p.N) break;                   // uniform across the warp
             float v[32];
             if (nkb > 0) {
@@ -337,7 +359,8 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = 0.f;
             }
-            if (m < p.M) tc_store_dispatch(p, C + (int64_t)m * p.ldc + n0 + c, m, n0 + c, v);
+            if (mbase < p.M) tc_store_dispatch(p, C, tile, mbase, n0 + c, lane, v, ax);
+            if (c + kCStep < BN) tc_prefetch_aux(p, mbase, n0 + c + kCStep + lane, ax);
         }
     } else if (warp == kTmaWarp && lane == 0) {
         // ===== TMA producer =====
