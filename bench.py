@@ -28,6 +28,8 @@ WORKLOADS = {
     "fnn_op_l3_ipinyou": ("tf", 16, 1_000_000, 10, [800, 400, 200], "op", 4096),
     "fnn_ip_l7_ipinyou": ("tf", 16, 1_000_000, 10, [1000, 800, 600, 400, 200, 100, 50], "ip", 65536),
     "fnn_criteo": ("tf", 39, 1_636_608, 10, [400, 400], "none", 65536),
+    # the optimizer baseline.py:93 actually runs on Criteo: adam, lr 1e-4, eps 1e-8, 'sum' (TF's dense Adam over table + MLP)
+    "fnn_criteo_adam": ("tf", 39, 1_636_608, 10, [400, 400], "none", 65536),
     # BASELINE config 5: 26 categorical fields over a 10^8-row table, rows sharded over the ranks (row % world)
     "fnn_criteo_sharded": ("tf", 26, 100_000_000, 10, [400, 400], "none", 65536),
 }
@@ -145,7 +147,7 @@ def build_model(wl, N, seed=1234, shard=None):
         cat_sizes, n_num = data.scaled_criteo_cat_sizes(X + 13) if F == 26 else data.ipinyou_field_sizes(X), 0
     offsets = data.offsets_of(cat_sizes, n_num)
     m = cls(cat_sizes, offsets, N, [X, F, rank] + hidden + ["tanh"], ["uniform", -0.01, 0.01, list(range(1, 20)), None],
-            ["sgd", 1e-3, "sum"], [1.0], "train", N, shard=shard)
+            ["adam", 1e-4, 1e-8, "sum"] if wl.endswith("_adam") else ["sgd", 1e-3, "sum"], [1.0], "train", N, shard=shard)
     for l in range(m.engine.nl):     # +-0.01 weights make every activation ~0: use fan-in scaling for a realistic step
         m.engine.W(l).uniform_(-1, 1).mul_(1.0 / np.sqrt(m.engine.widths[l]))
 
@@ -460,6 +462,8 @@ def oracle_stepper(wl, N, seed=1234):
             return net.train_step_theano(ids, y, 1e-3, 0.1, masks=masks, closed_form=True)
         return step
     net = O.OracleNet(table, 0.0, Ws, bs, F, d, cross, False, "tanh", "tanh")
+    if wl.endswith("_adam"):
+        return lambda ids, wts, y: net.train_step_tf_adam(ids, wts, y, 1e-4, 1e-8)
     return lambda ids, wts, y: net.train_step_tf(ids, wts, y, 1e-3)
 
 

@@ -278,6 +278,41 @@ __global__ void dense_sgd_kernel(float* __restrict__ p, const float* __restrict_
         p[i] = fmaf(p[i], decay, -lr * g[i]);
 }
 
+// ---- Adam, TF form (tf_util.py:18-21): dense over whatever buffer it is given ------------------------------------------
+// state = [t, lr_t, beta1^t, beta2^t]: advanced ON THE DEVICE once per step, so a captured CUDA graph replays the
+// right bias correction without a host-side scalar:  lr_t = lr * sqrt(1 - beta2^t) / (1 - beta1^t)
+__global__ void adam_tick_kernel(float* __restrict__ state, float lr, float beta1, float beta2) {
+    const float t = state[0] + 1.f;
+    const float p1 = (t == 1.f ? 1.f : state[2]) * beta1, p2 = (t == 1.f ? 1.f : state[3]) * beta2;
+    state[0] = t;
+    state[1] = lr * sqrtf(1.f - p2) / (1.f - p1);
+    state[2] = p1;
+    state[3] = p2;
+}
+
+__device__ __forceinline__ float adam1(float& p, float g, float& m, float& v, float lr_t, float b1, float b2, float eps, float l2) {
+    g = fmaf(l2, p, g);
+    m = fmaf(b1, m, (1.f - b1) * g);
+    v = fmaf(b2, v, (1.f - b2) * g * g);
+    p -= lr_t * m / (sqrtf(v) + eps);
+    return p;
+}
+
+template <bool ZERO>
+__global__ void dense_adam_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v,
+                                  int64_t n4, const float* __restrict__ state, float b1, float b2, float eps, float l2) {
+    const float lr_t = __ldg(state + 1);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        float4 pp = p[i], gg = g[i], mm = m[i], vv = v[i];
+        adam1(pp.x, gg.x, mm.x, vv.x, lr_t, b1, b2, eps, l2);
+        adam1(pp.y, gg.y, mm.y, vv.y, lr_t, b1, b2, eps, l2);
+        adam1(pp.z, gg.z, mm.z, vv.z, lr_t, b1, b2, eps, l2);
+        adam1(pp.w, gg.w, mm.w, vv.w, lr_t, b1, b2, eps, l2);
+        p[i] = pp; m[i] = mm; v[i] = vv;
+        if (ZERO) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
 // Shape of a column reduction: V = 4 when every row start is 16-byte aligned, TX = the narrowest power of two covering
 // the columns (<= 32), enough row chunks for ~4 CTAs per SM but at least 4 rows per row lane and chunk.
 constexpr int kRedHeader = 1024;                       // bytes: one ticket per column tile
@@ -399,4 +434,24 @@ extern "C" int dctr_dense_sgd(float* param, const float* grad, int64_t n, float 
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
     dense_sgd_kernel<<<blocks, 256, 0, as_stream(stream)>>>(param, grad, n, lr, decay);
     return check_launch("dense_sgd_kernel");
+}
+
+extern "C" int dctr_adam_tick(float* state, float lr, float beta1, float beta2, void* stream) {
+    DCTR_REQUIRE(state && beta1 >= 0.f && beta1 < 1.f && beta2 >= 0.f && beta2 < 1.f, "adam_tick: bad arguments");
+    adam_tick_kernel<<<1, 1, 0, as_stream(stream)>>>(state, lr, beta1, beta2);
+    return check_launch("adam_tick_kernel");
+}
+
+extern "C" int dctr_dense_adam(float* param, float* grad, float* m, float* v, int64_t n, const float* state, float beta1,
+                               float beta2, float eps, float l2, int zero_grad, void* stream) {
+    DCTR_REQUIRE(param && grad && m && v && state && n >= 0 && (n & 3) == 0, "dense_adam: null pointer or n not a multiple of 4");
+    DCTR_REQUIRE(((((uintptr_t)param) | ((uintptr_t)grad) | ((uintptr_t)m) | ((uintptr_t)v)) & 15) == 0, "dense_adam: buffers must be 16-byte aligned");
+    if (n == 0) return DCTR_OK;
+    int blocks = ceil_div(n / 4, 256);
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    float4 *p4 = reinterpret_cast<float4*>(param), *g4 = reinterpret_cast<float4*>(grad), *m4 = reinterpret_cast<float4*>(m),
+           *v4 = reinterpret_cast<float4*>(v);
+    if (zero_grad) dense_adam_kernel<true><<<blocks, 256, 0, as_stream(stream)>>>(p4, g4, m4, v4, n / 4, state, beta1, beta2, eps, l2);
+    else dense_adam_kernel<false><<<blocks, 256, 0, as_stream(stream)>>>(p4, g4, m4, v4, n / 4, state, beta1, beta2, eps, l2);
+    return check_launch("dense_adam_kernel");
 }

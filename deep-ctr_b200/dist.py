@@ -278,6 +278,8 @@ def attach_sharded(model, dist, X_global, group=None):
 def attach(model, dist, group=None):
     """Switch a model (models.FM / FNN* / theano_fnn.FNN_wnzh) to data-parallel steps.  The reference's
     batch-size-dependent constants see the GLOBAL batch: 'mean' reduce and the decay 1-2*lambda*lr/b_size."""
+    if getattr(model.engine, "adam", None) is not None:
+        raise NotImplementedError("data-parallel Adam is not built yet (SGD only)")
     dp = DataParallelStep(model.engine, dist, group)
     model.dp = dp
     # kernels AND collectives of a step replay as one CUDA graph (NCCL is capturable); DCTR_DP_GRAPH=0 issues them eagerly

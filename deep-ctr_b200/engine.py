@@ -100,6 +100,7 @@ class StepEngine:
         self.side2 = torch.cuda.Stream(device=self.dev)
         self.overlap_wgrad = True
         self._wgrad_pending = False
+        self.adam = None
         self.overlap_sort = True
         self.wts_are_ones = True
 
@@ -247,9 +248,29 @@ class StepEngine:
             g, g_ld_n, g_ld_f, w = self.ge.data_ptr(), F * self.ldg, self.ldg, None
         else:
             g, g_ld_n, g_ld_f, w = dz.data_ptr() + (4 if self.bias_first else 0), ldd, d, p(wts)
+        if self.adam is not None:
+            b1, b2, eps = self.adam
+            L.call("dctr_adam_tick", p(self.adam_state), float(lr), b1, b2, st)
+            L.call("dctr_scatter_sgd", self.scatter_mode, p(self.sorted_rows), p(self.sorted_pos), self.M, F, d,
+                   g, g_ld_n, g_ld_f, w, -1.0, 1.0, p(self.table_g), self.X, self.ld, p(self.scat_ws), self.scat_ws.numel(), st)
+            L.call("dctr_dense_adam", p(self.table), p(self.table_g), p(self.table_m), p(self.table_v), self.X * self.ld,
+                   p(self.adam_state), b1, b2, eps, 0.0, 1, st)
+            return
         L.call("dctr_scatter_sgd", self.scatter_mode, p(self.sorted_rows), p(self.sorted_pos), self.M, F, d,
                g, g_ld_n, g_ld_f, w, float(lr), float(decay), p(self.table), self.X, self.ld,
                p(self.scat_ws), self.scat_ws.numel(), st)
+
+    def enable_adam(self, eps=1e-8, beta1=0.9, beta2=0.999):
+        """Switch the step to TensorFlow's Adam over the table AND the MLP (tf_util.py:18-21).  TF densifies the table gradient
+        (FNN.py:46-49), so the slots of every row decay every step: the fold writes the summed per-row gradients into a
+        dense buffer G (dctr_scatter_sgd with table = G, lr = -1, decay = 1: G[row] = sum g) and one streaming
+        dctr_dense_adam pass over table | G | m | v applies the update and clears G (7 x 4 x X x ld bytes per step)."""
+        assert self.scatter_mode == L.SCATTER_SUM, "Adam belongs to the TF-form models (SUM scatter)"
+        f32 = dict(dtype=torch.float32, device=self.dev)
+        self.adam = (float(beta1), float(beta2), float(eps))
+        self.adam_state = torch.zeros(4, **f32)                 # [t, lr_t, beta1^t, beta2^t], advanced on the device
+        self.table_g, self.table_m, self.table_v = (torch.zeros_like(self.table) for _ in range(3))
+        self.params_m, self.params_v = torch.zeros_like(self.grads), torch.zeros_like(self.grads)
 
     def join_wgrad(self):
         """self.grads is complete on the current stream after this (weight gradients run on a side stream)."""
@@ -260,6 +281,11 @@ class StepEngine:
     def dense_update(self, lr, last_decay=1.0):
         self.join_wgrad()
         st = self._st()
+        if self.adam is not None:          # same step counter as the table (embedding_update ticked it)
+            b1, b2, eps = self.adam
+            L.call("dctr_dense_adam", L.ptr(self.params), L.ptr(self.grads), L.ptr(self.params_m), L.ptr(self.params_v),
+                   self.n_params, L.ptr(self.adam_state), b1, b2, eps, 0.0, 0, st)
+            return
         if last_decay == 1.0:
             L.call("dctr_dense_sgd", L.ptr(self.params), L.ptr(self.grads), self.n_params, float(lr), 1.0, st)
         else:   # Theano: cost += lambda1*(|w3|^2 + b3^2) touches the output unit only (FNN_wnzh.py:173)

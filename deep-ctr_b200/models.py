@@ -100,11 +100,14 @@ def init_var_map(_init_argv, variables):
     return var_map, log
 
 
-def _optimizer(_ptmzr_argv):
-    """tf_util.py:15-29.  Returns (lr, log)."""
+def _optimizer(_ptmzr_argv, allow_adam=False):
+    """tf_util.py:15-29.  Returns (lr, log); `adam` is on the fast path for the FNN family."""
     name = _ptmzr_argv[0]
+    if name == "adam" and allow_adam:
+        lr, eps = _ptmzr_argv[1:3]
+        return float(lr), "optimizer: %s, learning rate: %g, epsilon: %g" % (name, lr, eps)
     if name in ("adam", "ftrl"):
-        raise NotImplementedError("optimizer %r is not on the B200 fast path yet (SGD only; SURVEY.md 8(f) f1)" % name)
+        raise NotImplementedError("optimizer %r is not on the B200 fast path for this model yet (SURVEY.md 8(f) f1)" % name)
     lr = _ptmzr_argv[1]
     return float(lr), "optimizer: %s, learning rate: %g" % (name, lr)
 
@@ -239,6 +242,9 @@ class FM(_Base):
         eng.set_table(np.concatenate([var_map["W"], var_map["V"]], axis=1))
         eng.bias().copy_(torch.as_tensor(var_map["b"], dtype=torch.float32))
         self._setup_host(eng, batch_size, X_feas)
+        self._finish_init(_ptmzr_argv, _reg_argv, mode, eval_size)
+
+    def _finish_init(self, _ptmzr_argv, _reg_argv, mode, eval_size):
         self.sp_id_hldr, self.sp_wt_hldr, self.lbl_hldr = Placeholder("sp_id"), Placeholder("sp_wt"), Placeholder("lbl")
         if mode == "train":
             self._lambda = float(_reg_argv[0])
@@ -277,6 +283,30 @@ class FM(_Base):
         """FM.py:66-69: pickle {'W','V','b'}."""
         t = self.engine.get_table()
         var_map = {"W": t[:, :1].copy(), "V": t[:, 1:].copy(), "b": self.engine.bias().cpu().numpy()}
+        with open(model_path, "wb") as f:
+            pickle.dump(var_map, f)
+        print("model dumped at %s" % model_path)
+
+
+class LR(FM):
+    """LR(batch_size, [X_dim, X_feas], _init_argv, _ptmzr_argv, [lambda], mode, eval_size) -- LR.py:4-58: the FM path with
+    rank 0 (table rows hold the single weight `W`), same feeds; the eval weights placeholder is `eval_wt_hldr` (LR.py:44)."""
+
+    def __init__(self, batch_size, _rch_argv, _init_argv, _ptmzr_argv, _reg_argv, mode, eval_size, device="cuda"):
+        X_dim, X_feas = _rch_argv
+        self.X_dim, self.X_feas, self.rank, self.mode = X_dim, X_feas, 0, mode
+        self.log = "input dim: %d, features: %d, " % (X_dim, X_feas)
+        var_map, log = init_var_map(_init_argv, [("W", [X_dim, 1], "random"), ("b", [1], "zero")])
+        self.log += log
+        eng = FMEngine(X_dim, X_feas, 0, batch_size, device=device)
+        eng.set_table(var_map["W"])
+        eng.bias().copy_(torch.as_tensor(var_map["b"], dtype=torch.float32))
+        self._setup_host(eng, batch_size, X_feas)
+        self._finish_init(_ptmzr_argv, _reg_argv, mode, eval_size)
+
+    def dump(self, model_path):
+        """LR.py:55-58: pickle {'W','b'}."""
+        var_map = {"W": self.engine.get_table()[:, :1].copy(), "b": self.engine.bias().cpu().numpy()}
         with open(model_path, "wb") as f:
             pickle.dump(var_map, f)
         print("model dumped at %s" % model_path)
@@ -341,7 +371,11 @@ class _FNNBase(_Base):
         if mode == "train":
             self._keep_prob = float(_reg_argv[0])
             self._reduce = _ptmzr_argv[-1]
-            self.lr, log = _optimizer(_ptmzr_argv)
+            self.lr, log = _optimizer(_ptmzr_argv, allow_adam=True)
+            if _ptmzr_argv[0] == "adam":
+                if shard is not None:
+                    raise NotImplementedError("adam with a row-sharded table is not built yet")
+                eng.enable_adam(eps=float(_ptmzr_argv[2]))
             self.log += "%s, reduce by: %s, keep_prob(drop_out): %g" % (log, self._reduce, self._keep_prob)
             self.eval_size = eval_size
             self.eval_id_hldr, self.eval_wts_hldr = Placeholder("eval_id"), Placeholder("eval_wts")

@@ -176,6 +176,16 @@ int dctr_vec_sum(const float* v, int N, float scale, float* out, void* stream);
 /* ---- K7: dense SGD over a flat parameter buffer (tf_util.py:27 / FNN_wnzh.py:180-182) ---------- */
 int dctr_dense_sgd(float* param, const float* grad, int64_t n, float lr, float decay, void* stream);
 
+/* Adam in TensorFlow's form (tf_util.py:18-21 AdamOptimizer(lr, epsilon); baseline.py:93 uses it for every Criteo model).
+ * dctr_adam_tick advances state = [t, lr_t, beta1^t, beta2^t] (4 floats, zero before the first step) on the device:
+ *   lr_t = lr * sqrt(1 - beta2^t) / (1 - beta1^t)          -- once per step, graph-replay safe.
+ * dctr_dense_adam, elementwise over n floats (n % 4 == 0, 16-byte aligned buffers):
+ *   g += l2 * p;  m = beta1 m + (1-beta1) g;  v = beta2 v + (1-beta2) g^2;  p -= lr_t * m / (sqrt(v) + eps);
+ *   zero_grad != 0 clears grad afterwards (the densified table gradient is rebuilt by dctr_scatter_sgd every step). */
+int dctr_adam_tick(float* state, float lr, float beta1, float beta2, void* stream);
+int dctr_dense_adam(float* param, float* grad, float* m, float* v, int64_t n, const float* state, float beta1, float beta2,
+                    float eps, float l2, int zero_grad, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

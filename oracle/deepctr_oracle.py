@@ -209,6 +209,38 @@ class OracleNet:
             self.bs[l] -= lr * dbs[l]
         return loss, sigmoid(logit)
 
+    def train_step_tf_adam(self, ids, wts, y, lr, eps=1e-8, masks=None, reduce="sum", beta1=0.9, beta2=0.999):
+        """tf.train.AdamOptimizer(lr, epsilon=eps).minimize(loss) over ALL variables (tf_util.py:18-21; baseline.py:93 uses
+        adam for every Criteo model).  TF's form:  lr_t = lr * sqrt(1 - beta2^t) / (1 - beta1^t);  m = b1 m + (1-b1) g;
+        v = b2 v + (1-b2) g^2;  theta -= lr_t * m / (sqrt(v) + eps).  The table gradient is densified (FNN.py:46-49), so
+        the slots of EVERY row decay each step and an untouched row keeps moving while its m is non-zero."""
+        y = np.asarray(y, dtype=self.dtype)
+        logit, cache = self.forward(ids, wts, masks)
+        N = len(y)
+        scale = 1.0 if reduce == "sum" else 1.0 / N
+        loss = xent_with_logits(logit, y).sum() * scale
+        dlogit = (sigmoid(logit) - y) * scale
+        dWs, dbs, dbias, ge, _ = self.backward(cache, dlogit)
+        if not hasattr(self, "_adam"):
+            z = lambda a: [np.zeros_like(np.asarray(a, dtype=self.dtype)), np.zeros_like(np.asarray(a, dtype=self.dtype))]
+            self._adam = dict(t=0, table=z(self.table), bias=z(np.asarray(self.bias)), Ws=[z(w) for w in self.Ws], bs=[z(b) for b in self.bs])
+        st = self._adam
+        st["t"] += 1
+        lr_t = lr * np.sqrt(1.0 - beta2 ** st["t"]) / (1.0 - beta1 ** st["t"])
+
+        def upd(theta, g, mv):
+            mv[0] = beta1 * mv[0] + (1 - beta1) * g
+            mv[1] = beta2 * mv[1] + (1 - beta2) * g * g
+            return theta - lr_t * mv[0] / (np.sqrt(mv[1]) + eps)
+        G = np.zeros_like(self.table)
+        np.add.at(G, ids.reshape(-1), ge.reshape(-1, self.d))
+        self.table[...] = upd(self.table, G, st["table"])
+        self.bias = float(upd(np.asarray(self.bias, dtype=self.dtype), np.asarray(dbias, dtype=self.dtype), st["bias"]))
+        for l in range(len(self.Ws)):
+            self.Ws[l] = upd(self.Ws[l], dWs[l], st["Ws"][l])
+            self.bs[l] = upd(self.bs[l], dbs[l], st["bs"][l])
+        return loss, sigmoid(logit)
+
     # ---- Theano semantics (FNN_wnzh.py:172-182, 298-306) --------------------------------------------
     def train_step_theano(self, ids, y, lr, lambda_fm, masks=None, lambda1=0.0, faithful=False, closed_form=False):
         y = np.asarray(y, dtype=self.dtype)

@@ -36,7 +36,7 @@ def criteo_like(rng, n_num, cat_sizes):
 
 
 def make_fnn(cls_name, tmp_path, rng, N, hidden, act, n_num=3, cat_sizes=(50, 7, 200, 3, 90), rank=4, keep=1.0, lr=0.05,
-             reduce="sum", use_graph=False):
+             reduce="sum", use_graph=False, ptmzr=None):
     import deepctr_b200.models as M
     import deepctr_oracle as O
     cls = getattr(M, cls_name)
@@ -54,7 +54,7 @@ def make_fnn(cls_name, tmp_path, rng, N, hidden, act, n_num=3, cat_sizes=(50, 7,
         pickle.dump(vm, f, protocol=2)
     rch = [X_dim, X_feas, rank] + list(hidden) + [act]
     model = cls(cat_sizes, offsets, N, rch, ["uniform", -0.01, 0.01, [1, 2, 3, 4, 5, 6, 7, 8, 9, 10], path],
-                ["sgd", lr, reduce], [keep], "train", 2 * N)
+                ptmzr or ["sgd", lr, reduce], [keep], "train", 2 * N)
     model.use_graph = use_graph
     table = np.concatenate([vm["W"], vm["V"]], 1)
     net = O.OracleNet(table, vm["b"][0], [vm["h%d_w" % (i + 1)] for i in range(len(dims) - 1)],
@@ -105,6 +105,33 @@ def test_tf_family_steps(tmp_path, cls_name, hidden, act, reduce):
     close(ev, net.predict(g_ids, g_wts), 5e-5)
 
 
+@pytest.mark.parametrize("cls_name,hidden,use_graph", [("FNN", [40, 30], False), ("FNN_IP_L3", [40, 30, 20], True)])
+def test_tf_family_adam_steps(tmp_path, cls_name, hidden, use_graph):
+    """['adam', lr, eps, reduce] (tf_util.py:18-21; what baseline.py:93 runs): TF's dense Adam over table + MLP.  Rows
+    untouched by a step still move (their m decays), and the bias correction advances inside the replayed CUDA graph."""
+    rng = np.random.default_rng(202)
+    N = 64
+    model, net, (cat_sizes, offsets, n_num) = make_fnn(cls_name, tmp_path, rng, N, hidden, "tanh", use_graph=use_graph,
+                                                       ptmzr=["adam", 1e-2, 1e-8, "sum"])
+    assert "epsilon" in model.log
+    for step in range(6):
+        v_wts, c_ids, c_wts, y, g_ids, g_wts = fnn_batch(rng, N, cat_sizes, offsets, n_num)
+        if step >= 3:
+            c_ids[:, 0] = 1                     # field 0 now only touches row 1: its other rows coast on their momentum
+            g_ids[:, n_num] = 1 + offsets[0]
+        loss, preds = model.train_step({model.v_wt_hldr: v_wts, model.c_id_hldr: c_ids, model.c_wt_hldr: c_wts, model.lbl_hldr: y})
+        before = net.table.copy()
+        oloss, opreds = net.train_step_tf_adam(g_ids, g_wts, y, 1e-2, 1e-8)
+        close([loss], [oloss], 2e-5)
+        close(preds, opreds, 5e-5)
+        # Adam divides by sqrt(v) + eps: early steps move every touched weight by ~lr whatever the gradient's size, so
+        # the fp32-vs-fp64 comparison is on the weights, with an absolute floor of a few 1e-6
+        compare_state(model, net, 2e-4)
+    untouched = np.setdiff1d(np.arange(offsets[0], offsets[0] + cat_sizes[0]), [1 + offsets[0]])
+    moved = np.abs(net.table[untouched] - before[untouched]).max()
+    assert moved > 0, "dense Adam: rows without a gradient this step must still move"
+
+
 def test_tf_dropout_masks_injected(tmp_path):
     rng = np.random.default_rng(202)
     N = 64
@@ -148,6 +175,40 @@ def test_fm_steps_and_checkpoint(tmp_path):
         fm.dump(p)
         fm2 = FM(N, [X, F, rank], ["uniform", -0.05, 0.05, [1, 2], p], None, None, "test", None)
         close(fm2.test_preds.eval(feed_dict={fm2.sp_id_hldr: ids.reshape(-1), fm2.sp_wt_hldr: wts.reshape(-1)}), ev, 1e-6)
+
+
+def test_lr_steps_and_checkpoint(tmp_path):
+    """LR.py = the FM path with rank 0: logit = sum_f x_f W[id_f] + b, dense L2 on W and b (LR.py:37, 52-53)"""
+    import deepctr_oracle as O
+    from deepctr_b200.LR import LR
+    rng = np.random.default_rng(404)
+    N, X, F = 96, 500, 16
+    for lam, reduce in [(0.0, "sum"), (1e-2, "mean")]:
+        lr_m = LR(N, [X, F], ["uniform", -0.05, 0.05, [7, 8], None], ["sgd", 0.05, reduce], [lam], "train", 100)
+        lr_m.use_graph = False
+        assert lr_m.engine.get_table().shape == (X, 1)
+        olr = O.OracleFM(lr_m.engine.get_table(), 0.0)
+        for step in range(3):
+            ids = rng.integers(0, X, (N, F))
+            ids[:, 0] = 5                       # a row hit by every sample
+            wts = rng.uniform(0.5, 1.5, (N, F)).astype(np.float32)
+            y = rng.integers(0, 2, N)
+            loss, preds = lr_m.train_step({lr_m.sp_id_hldr: ids.reshape(-1), lr_m.sp_wt_hldr: wts.reshape(-1), lr_m.lbl_hldr: y})
+            oloss, opreds = olr.train_step(ids, wts, y, 0.05, lam, reduce)
+            want = opreds
+            if lam == 0.0:
+                close([loss], [oloss], 2e-5)
+            close(preds, want, 2e-5)
+            close(lr_m.engine.get_table(), olr.table, 2e-5, 2e-6)
+            close(lr_m.engine.bias().cpu(), [olr.b], 2e-5, 2e-6)
+        # the logit really is the plain weighted sum (no pairwise term at rank 0)
+        t, b = lr_m.engine.get_table().astype(np.float64), float(lr_m.engine.bias().cpu()[0])
+        ev = lr_m.eval_preds.eval(feed_dict={lr_m.eval_wt_hldr: wts.reshape(-1), lr_m.eval_id_hldr: ids.reshape(-1)})
+        close(ev, 1.0 / (1.0 + np.exp(-((t[ids, 0] * wts).sum(1) + b))), 2e-5)
+        p = str(tmp_path / "lr.pickle")
+        lr_m.dump(p)
+        lr2 = LR(N, [X, F], ["uniform", -0.05, 0.05, [1, 2], p], None, None, "test", None)
+        close(lr2.test_preds.eval(feed_dict={lr2.sp_id_hldr: ids.reshape(-1), lr2.sp_wt_hldr: wts.reshape(-1)}), ev, 1e-6)
 
 
 def make_theano(rng, N, X=640, F=16, k=11, h1=48, h2=24, dropout=1.0, lambda1=0.0, use_graph=False):
