@@ -23,6 +23,42 @@ int check_launch(const char* what);
     } while (0)
 
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// ---- programmatic dependent launch ---------------------------------------------------------------------------------
+// Every kernel of the library starts with pdl_sync(): griddepcontrol.wait blocks until the preceding kernel of the stream
+// has completed and flushed (so ordering is exactly what plain stream order gives), launch_dependents then lets the
+// NEXT kernel's CTAs be scheduled onto idle SMs while this one runs.  Launching through launch_k() with the
+// programmatic-serialization attribute hides the ~1-2 us kernel-to-kernel launch gap of a 20-launch step; a kernel
+// launched this way MUST call pdl_sync() before touching global memory.  DCTR_PDL=0 falls back to plain launches.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() { pdl_wait(); pdl_launch_dependents(); }
+int pdl_mode();          // 0 = off, 1 = every kernel, 2 (default) = every kernel but the tensor-core GEMM
+
+template <class... KArgs, class... Args>
+static inline void launch_k_mode(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);       // errors are picked up by check_launch()
+}
+template <class K, class... Args>
+static inline void launch_k(K kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    launch_k_mode(pdl_mode() != 0, kernel, grid, block, smem, st, args...);
+}
+// A CTA that owns a whole SM (192 KB of shared memory, all of TMEM): parked early behind its predecessor it would keep
+// that SM from the kernels of the other streams (weight-gradient GEMMs, the sort), which costs more than the launch gap.
+template <class K, class... Args>
+static inline void launch_k_heavy(K kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    launch_k_mode(pdl_mode() == 1, kernel, grid, block, smem, st, args...);
+}
 static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
 // ---- device helpers ----

@@ -14,6 +14,7 @@ fm_fwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts, co
               int ld, int N, int F, int d, const float* __restrict__ bias, const float* __restrict__ y,
               float gscale, float* __restrict__ logit, float* __restrict__ pred, float* __restrict__ loss_n,
               float* __restrict__ g, float* __restrict__ s, int lds, int vec) {
+    pdl_sync();
     const int q = threadIdx.x & 3;
     const float b = bias ? __ldg(bias) : 0.f;
     const int64_t groups = ((int64_t)gridDim.x * kFmThreads) >> 2;
@@ -76,7 +77,7 @@ extern "C" int dctr_fm_fwd(const int32_t* ids, const float* wts, const float* ta
     const int vec = (F & 3) == 0 && ((uintptr_t)ids & 15) == 0 && (!wts || ((uintptr_t)wts & 15) == 0);
     int blocks = ceil_div(N, kFmThreads / 4);
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    fm_fwd_kernel<<<blocks, kFmThreads, 0, as_stream(stream)>>>(ids, wts, table, ld, N, F, d, bias, y, gscale,
+    launch_k(fm_fwd_kernel, blocks, kFmThreads, 0, as_stream(stream), ids, wts, table, ld, N, F, d, bias, y, gscale,
                                                                  logit, pred, loss_n, g, s, lds, vec);
     return check_launch("fm_fwd_kernel");
 }

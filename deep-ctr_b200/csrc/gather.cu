@@ -41,6 +41,7 @@ __global__ void __launch_bounds__(kGatherWarps * 32)
 gather_concat_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
                      const float* __restrict__ table, int ld, int N, int F, int d, int bias_first,
                      const float* __restrict__ bias, int act0, float* __restrict__ out, int ldz, int warps, int vec) {
+    pdl_sync();
     extern __shared__ __align__(16) float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = lane & 3, g = lane >> 2;
@@ -152,6 +153,7 @@ __global__ void __launch_bounds__(kGatherWarps * 32)
 cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts, const float* __restrict__ table,
                  int ld, int N, int F, int d, const float* __restrict__ dz, int ldz,
                  float* __restrict__ ge, int ldg) {
+    pdl_sync();
     extern __shared__ __align__(16) float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int Fd = F * d;
@@ -214,6 +216,7 @@ cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
 __global__ void __launch_bounds__(256)
 arrange_fields_kernel(const int32_t* __restrict__ feats, const int32_t* __restrict__ feat_field, int N, int J, int F,
                       int32_t pad_row, int32_t* __restrict__ ids, float* __restrict__ wts) {
+    pdl_sync();
     const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (n >= N) return;
     int32_t* irow = ids + (int64_t)n * F;
@@ -238,6 +241,7 @@ arrange_fields_kernel(const int32_t* __restrict__ feats, const int32_t* __restri
 // permutation of gradient rows into exchange order.  One thread per 128-bit piece of a row.
 __global__ void __launch_bounds__(256)
 gather_rows_kernel(const int32_t* __restrict__ ids, const float4* __restrict__ table, int q, int64_t M, float4* __restrict__ out) {
+    pdl_sync();
     const int64_t total = M * q;
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = t / q;
@@ -285,7 +289,7 @@ extern "C" int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, cons
     do {                                                                                                     \
         if (smem > 48 * 1024)                                                                                \
             cudaFuncSetAttribute(gather_concat_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        gather_concat_kernel<C><<<grid, block, smem, st>>>(ids, wts, table, ld, N, F, d, bias_first, bias,   \
+        launch_k(gather_concat_kernel<C>, grid, block, smem, st, ids, wts, table, ld, N, F, d, bias_first, bias,   \
                                                            act0, out, ldz, warps, vec);                      \
     } while (0)
     if (cross == DCTR_CROSS_IP) LAUNCH_G(DCTR_CROSS_IP);
@@ -312,7 +316,7 @@ extern "C" int dctr_cross_bwd(const int32_t* ids, const float* wts, const float*
     do {                                                                                                     \
         if (smem > 48 * 1024)                                                                                \
             cudaFuncSetAttribute(cross_bwd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        cross_bwd_kernel<C><<<grid, block, smem, st>>>(ids, wts, table, ld, N, F, d, dz, ldz, ge, ldg);      \
+        launch_k(cross_bwd_kernel<C>, grid, block, smem, st, ids, wts, table, ld, N, F, d, dz, ldz, ge, ldg);      \
     } while (0)
     if (cross == DCTR_CROSS_IP) LAUNCH_B(DCTR_CROSS_IP);
     else if (cross == DCTR_CROSS_OP) LAUNCH_B(DCTR_CROSS_OP);
@@ -326,7 +330,7 @@ extern "C" int dctr_arrange_fields(const int32_t* feats, const int32_t* feat_fie
     DCTR_REQUIRE(N >= 0 && J > 0 && F > 0, "arrange_fields: bad shape N=%d J=%d F=%d", N, J, F);
     if (N == 0) return DCTR_OK;
     DCTR_REQUIRE(feats && feat_field && ids && wts, "arrange_fields: null pointer");
-    arrange_fields_kernel<<<ceil_div((int64_t)N * 32, 256), 256, 0, as_stream(stream)>>>(feats, feat_field, N, J, F, pad_row, ids, wts);
+    launch_k(arrange_fields_kernel, ceil_div((int64_t)N * 32, 256), 256, 0, as_stream(stream), feats, feat_field, N, J, F, pad_row, ids, wts);
     return check_launch("arrange_fields_kernel");
 }
 
@@ -336,7 +340,7 @@ extern "C" int dctr_gather_rows(const int32_t* ids, const float* table, int64_t 
     DCTR_REQUIRE(ids && table && out && ((uintptr_t)table & 15) == 0 && ((uintptr_t)out & 15) == 0, "gather_rows: null or unaligned pointer");
     int blocks = ceil_div(M * (ld / 4), 256);
     if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-    gather_rows_kernel<<<blocks, 256, 0, as_stream(stream)>>>(ids, reinterpret_cast<const float4*>(table), ld / 4, M,
+    launch_k(gather_rows_kernel, blocks, 256, 0, as_stream(stream), ids, reinterpret_cast<const float4*>(table), ld / 4, M,
                                                               reinterpret_cast<float4*>(out));
     return check_launch("gather_rows_kernel");
 }

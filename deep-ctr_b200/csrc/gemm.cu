@@ -94,6 +94,7 @@ __device__ __forceinline__ float epilogue_apply(const GemmParams& p, int m, int 
 template <int BM, int BN, bool AK, bool BKC>
 __global__ void __launch_bounds__(kGemmThreads)
 gemm_kernel(GemmParams p) {
+    pdl_sync();
     constexpr int TM = BM / 16, TN = BN / 16;
     constexpr int SA = BM + 4, SB = BN + 4;
     __shared__ __align__(16) float As[2][kBK * SA];
@@ -165,6 +166,7 @@ gemm_kernel(GemmParams p) {
 
 __global__ void splitk_reduce_kernel(const float* __restrict__ part, int splits, int M, int N, int ldc,
                                      float* __restrict__ out, int ldo) {
+    pdl_sync();
     const int64_t total = (int64_t)M * N;
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         const int m = (int)(t / N), n = (int)(t - (int64_t)m * N);
@@ -176,9 +178,9 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ part, int splits,
 
 template <int BM, int BN>
 static void launch_gemm(int layout, const GemmParams& p, dim3 grid, cudaStream_t st) {
-    if (layout == DCTR_GEMM_NN) gemm_kernel<BM, BN, true, false><<<grid, kGemmThreads, 0, st>>>(p);
-    else if (layout == DCTR_GEMM_NT) gemm_kernel<BM, BN, true, true><<<grid, kGemmThreads, 0, st>>>(p);
-    else gemm_kernel<BM, BN, false, false><<<grid, kGemmThreads, 0, st>>>(p);
+    if (layout == DCTR_GEMM_NN) launch_k(gemm_kernel<BM, BN, true, false>, grid, kGemmThreads, 0, st, p);
+    else if (layout == DCTR_GEMM_NT) launch_k(gemm_kernel<BM, BN, true, true>, grid, kGemmThreads, 0, st, p);
+    else launch_k(gemm_kernel<BM, BN, false, false>, grid, kGemmThreads, 0, st, p);
 }
 
 }  // namespace dctr
@@ -222,6 +224,6 @@ extern "C" int dctr_splitk_reduce(const float* partials, int splits, int M, int 
     if (M == 0 || N == 0) return DCTR_OK;
     int blocks = ceil_div((int64_t)M * N, 256);
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    splitk_reduce_kernel<<<blocks, 256, 0, as_stream(stream)>>>(partials, splits, M, N, ldc, out, ldo);
+    launch_k(splitk_reduce_kernel, blocks, 256, 0, as_stream(stream), partials, splits, M, N, ldc, out, ldo);
     return check_launch("splitk_reduce_kernel");
 }

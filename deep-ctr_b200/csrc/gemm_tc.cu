@@ -312,6 +312,9 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t tmem_a0 = tmem_base + T::kAcc;
+    // barriers initialised, tensor memory allocated: only now wait for the kernel that produced the operands (programmatic
+    // dependent launch: everything above overlapped its tail)
+    pdl_sync();
 
     if (warp < kMmaWarp) {
         // ===== converters =====
@@ -467,7 +470,7 @@ static int launch_tc(int layout, const TcParams& p, dim3 grid, cudaStream_t st) 
 #define DCTR_TC_LAUNCH(AKV, BKV)                                                                                      \
     do {                                                                                                              \
         e = cudaFuncSetAttribute(gemm_tc_kernel<BN, NS, AKV, BKV>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes); \
-        if (e == cudaSuccess) gemm_tc_kernel<BN, NS, AKV, BKV><<<grid, kThreads, bytes, st>>>(p, mapA, mapB);          \
+        if (e == cudaSuccess) launch_k_heavy(gemm_tc_kernel<BN, NS, AKV, BKV>, grid, kThreads, bytes, st, p, mapA, mapB);          \
     } while (0)
     if (layout == DCTR_GEMM_NN) DCTR_TC_LAUNCH(true, false);
     else if (layout == DCTR_GEMM_NT) DCTR_TC_LAUNCH(true, true);

@@ -67,6 +67,7 @@ out_xent_fwd_kernel(const float* __restrict__ a, int lda, int N, int H, const fl
                     float* __restrict__ logit, float* __restrict__ pred, float* __restrict__ loss_n,
                     float* __restrict__ dlogit, float loss_scale, float* __restrict__ loss_sum,
                     float* __restrict__ partial, unsigned* __restrict__ ticket) {
+    pdl_sync();
     __shared__ float s_loss[8];
     float my_loss = 0.f;
     const int lane = threadIdx.x & 31;
@@ -107,6 +108,7 @@ out_xent_fwd_kernel(const float* __restrict__ a, int lda, int N, int H, const fl
 __global__ void __launch_bounds__(256)
 out_bwd_kernel(const float* __restrict__ dlogit, const float* __restrict__ w, const float* __restrict__ a, int lda,
                int N, int H, int act, const float* __restrict__ mask, int ldmask, float* __restrict__ da, int ldda) {
+    pdl_sync();
     const int64_t total = (int64_t)N * H;
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         const int n = (int)(t / H), h = (int)(t - (int64_t)n * H);
@@ -162,6 +164,7 @@ template <int V>
 __global__ void __launch_bounds__(kRedThreads)
 col_wsum_kernel(const float* __restrict__ A, int lda, int N, int H, const float* __restrict__ wv, RedShape sh,
                 float* __restrict__ partial, unsigned* __restrict__ tickets, float* __restrict__ out) {
+    pdl_sync();
     __shared__ float s_acc[V * kRedThreads];
     const int TX = sh.TX, TY = kRedThreads / TX, tx = threadIdx.x % TX, ty = threadIdx.x / TX;
     const int c0 = blockIdx.x * TX * V, h0 = c0 + tx * V;
@@ -200,6 +203,7 @@ out_bwd_fused_kernel(const float* __restrict__ dlogit, const float* __restrict__
                      int N, int H, int act, const float* __restrict__ mask, int ldmask, float* __restrict__ da, int ldda,
                      RedShape sh, float* __restrict__ partial, unsigned* __restrict__ tickets,
                      float* __restrict__ gw, float* __restrict__ gb) {
+    pdl_sync();
     __shared__ float s_acc[V * kRedThreads];
     const int TX = sh.TX, TY = kRedThreads / TX, tx = threadIdx.x % TX, ty = threadIdx.x / TX;
     const int c0 = blockIdx.x * TX * V, h0 = c0 + tx * V;
@@ -261,6 +265,7 @@ out_bwd_fused_kernel(const float* __restrict__ dlogit, const float* __restrict__
 }
 
 __global__ void __launch_bounds__(1024) vec_sum_kernel(const float* __restrict__ v, int N, float scale, float* __restrict__ out) {
+    pdl_sync();
     __shared__ float sm[1024];
     float acc = 0.f;
     for (int i = threadIdx.x; i < N; i += 1024) acc += v[i];
@@ -274,6 +279,7 @@ __global__ void __launch_bounds__(1024) vec_sum_kernel(const float* __restrict__
 }
 
 __global__ void dense_sgd_kernel(float* __restrict__ p, const float* __restrict__ g, int64_t n, float lr, float decay) {
+    pdl_sync();
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
         p[i] = fmaf(p[i], decay, -lr * g[i]);
 }
@@ -282,6 +288,7 @@ __global__ void dense_sgd_kernel(float* __restrict__ p, const float* __restrict_
 // state = [t, lr_t, beta1^t, beta2^t]: advanced ON THE DEVICE once per step, so a captured CUDA graph replays the
 // right bias correction without a host-side scalar:  lr_t = lr * sqrt(1 - beta2^t) / (1 - beta1^t)
 __global__ void adam_tick_kernel(float* __restrict__ state, float lr, float beta1, float beta2) {
+    pdl_sync();
     const float t = state[0] + 1.f;
     const float p1 = (t == 1.f ? 1.f : state[2]) * beta1, p2 = (t == 1.f ? 1.f : state[3]) * beta2;
     state[0] = t;
@@ -301,6 +308,7 @@ __device__ __forceinline__ float adam1(float& p, float g, float& m, float& v, fl
 template <bool ZERO>
 __global__ void dense_adam_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v,
                                   int64_t n4, const float* __restrict__ state, float b1, float b2, float eps, float l2) {
+    pdl_sync();
     const float lr_t = __ldg(state + 1);
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
         float4 pp = p[i], gg = g[i], mm = m[i], vv = v[i];
@@ -361,7 +369,7 @@ extern "C" int dctr_out_xent_fwd(const float* a, int lda, int N, int H, const fl
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
     unsigned* ticket = static_cast<unsigned*>(workspace);
     float* partial = workspace ? reinterpret_cast<float*>(static_cast<char*>(workspace) + kRedHeader) : nullptr;
-    out_xent_fwd_kernel<<<blocks, 256, 0, as_stream(stream)>>>(a, lda, N, H, w, b, y, gscale, logit, pred, loss_n, dlogit,
+    launch_k(out_xent_fwd_kernel, blocks, 256, 0, as_stream(stream), a, lda, N, H, w, b, y, gscale, logit, pred, loss_n, dlogit,
                                                                 loss_scale, loss_sum, partial, ticket);
     return check_launch("out_xent_fwd_kernel");
 }
@@ -381,10 +389,10 @@ extern "C" int dctr_out_bwd_fused(const float* dlogit, const float* w, const flo
     float* partial = reinterpret_cast<float*>(static_cast<char*>(workspace) + kRedHeader);
     const dim3 grid(sh.col_tiles, sh.chunks);
     if (vec)
-        out_bwd_fused_kernel<4><<<grid, kRedThreads, 0, as_stream(stream)>>>(dlogit, w, a, lda, N, H, act, mask, ldmask, da, ldda,
+        launch_k(out_bwd_fused_kernel<4>, grid, kRedThreads, 0, as_stream(stream), dlogit, w, a, lda, N, H, act, mask, ldmask, da, ldda,
                                                                             sh, partial, tickets, gw, gb);
     else
-        out_bwd_fused_kernel<1><<<grid, kRedThreads, 0, as_stream(stream)>>>(dlogit, w, a, lda, N, H, act, mask, ldmask, da, ldda,
+        launch_k(out_bwd_fused_kernel<1>, grid, kRedThreads, 0, as_stream(stream), dlogit, w, a, lda, N, H, act, mask, ldmask, da, ldda,
                                                                             sh, partial, tickets, gw, gb);
     return check_launch("out_bwd_fused_kernel");
 }
@@ -395,7 +403,7 @@ extern "C" int dctr_out_bwd(const float* dlogit, const float* w, const float* a,
     if (N == 0) return DCTR_OK;
     int blocks = ceil_div((int64_t)N * H, 256);
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    out_bwd_kernel<<<blocks, 256, 0, as_stream(stream)>>>(dlogit, w, a, lda, N, H, act, mask, ldmask, da, ldda);
+    launch_k(out_bwd_kernel, blocks, 256, 0, as_stream(stream), dlogit, w, a, lda, N, H, act, mask, ldmask, da, ldda);
     return check_launch("out_bwd_kernel");
 }
 
@@ -415,15 +423,15 @@ extern "C" int dctr_col_wsum(const float* A, int lda, int N, int H, const float*
     float* partial = reinterpret_cast<float*>(static_cast<char*>(workspace) + kRedHeader);
     const dim3 grid(sh.col_tiles, sh.chunks);
     if (vec)
-        col_wsum_kernel<4><<<grid, kRedThreads, 0, as_stream(stream)>>>(A, lda, N, H, wv, sh, partial, tickets, out);
+        launch_k(col_wsum_kernel<4>, grid, kRedThreads, 0, as_stream(stream), A, lda, N, H, wv, sh, partial, tickets, out);
     else
-        col_wsum_kernel<1><<<grid, kRedThreads, 0, as_stream(stream)>>>(A, lda, N, H, wv, sh, partial, tickets, out);
+        launch_k(col_wsum_kernel<1>, grid, kRedThreads, 0, as_stream(stream), A, lda, N, H, wv, sh, partial, tickets, out);
     return check_launch("col_wsum_kernel");
 }
 
 extern "C" int dctr_vec_sum(const float* v, int N, float scale, float* out, void* stream) {
     DCTR_REQUIRE(v && out && N >= 0, "vec_sum: bad arguments");
-    vec_sum_kernel<<<1, 1024, 0, as_stream(stream)>>>(v, N, scale, out);
+    launch_k(vec_sum_kernel, 1, 1024, 0, as_stream(stream), v, N, scale, out);
     return check_launch("vec_sum_kernel");
 }
 
@@ -432,13 +440,13 @@ extern "C" int dctr_dense_sgd(float* param, const float* grad, int64_t n, float 
     if (n == 0) return DCTR_OK;
     int blocks = ceil_div(n, 256);
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    dense_sgd_kernel<<<blocks, 256, 0, as_stream(stream)>>>(param, grad, n, lr, decay);
+    launch_k(dense_sgd_kernel, blocks, 256, 0, as_stream(stream), param, grad, n, lr, decay);
     return check_launch("dense_sgd_kernel");
 }
 
 extern "C" int dctr_adam_tick(float* state, float lr, float beta1, float beta2, void* stream) {
     DCTR_REQUIRE(state && beta1 >= 0.f && beta1 < 1.f && beta2 >= 0.f && beta2 < 1.f, "adam_tick: bad arguments");
-    adam_tick_kernel<<<1, 1, 0, as_stream(stream)>>>(state, lr, beta1, beta2);
+    launch_k(adam_tick_kernel, 1, 1, 0, as_stream(stream), state, lr, beta1, beta2);
     return check_launch("adam_tick_kernel");
 }
 
@@ -451,7 +459,7 @@ extern "C" int dctr_dense_adam(float* param, float* grad, float* m, float* v, in
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
     float4 *p4 = reinterpret_cast<float4*>(param), *g4 = reinterpret_cast<float4*>(grad), *m4 = reinterpret_cast<float4*>(m),
            *v4 = reinterpret_cast<float4*>(v);
-    if (zero_grad) dense_adam_kernel<true><<<blocks, 256, 0, as_stream(stream)>>>(p4, g4, m4, v4, n / 4, state, beta1, beta2, eps, l2);
-    else dense_adam_kernel<false><<<blocks, 256, 0, as_stream(stream)>>>(p4, g4, m4, v4, n / 4, state, beta1, beta2, eps, l2);
+    if (zero_grad) launch_k(dense_adam_kernel<true>, blocks, 256, 0, as_stream(stream), p4, g4, m4, v4, n / 4, state, beta1, beta2, eps, l2);
+    else launch_k(dense_adam_kernel<false>, blocks, 256, 0, as_stream(stream), p4, g4, m4, v4, n / 4, state, beta1, beta2, eps, l2);
     return check_launch("dense_adam_kernel");
 }

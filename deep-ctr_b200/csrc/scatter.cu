@@ -103,6 +103,7 @@ __device__ __forceinline__ float4 mask_cols(float4 v, int c0, int d) {
 template <int MODE, bool ALIGNED>
 __global__ void __launch_bounds__(kFoldThreads, 2)
 fold_tile_kernel(const FoldArgs a) {
+    pdl_sync();
     __shared__ float4 sQF[kFoldThreads], sQL[kFoldThreads];
     __shared__ float sPF[kFoldThreads], sPL[kFoldThreads];
     __shared__ int sFlag[kGroups];
@@ -256,6 +257,7 @@ fold_tile_kernel(const FoldArgs a) {
 template <int MODE>
 __global__ void __launch_bounds__(kFoldThreads)
 fold_stitch_kernel(const FoldArgs a, int tiles) {
+    pdl_sync();
     const int64_t t = ((int64_t)blockIdx.x * kFoldThreads + threadIdx.x) >> 2;
     const int q = threadIdx.x & (kG - 1);
     if (t >= tiles) return;
@@ -291,6 +293,7 @@ fold_stitch_kernel(const FoldArgs a, int tiles) {
 
 __global__ void decay_sweep_kernel(float4* __restrict__ table, int64_t X, int q, float decay,
                                    const int32_t* __restrict__ rows, int64_t M) {
+    pdl_sync();
     const int64_t total = X * q;
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         const int32_t r = (int32_t)(t / q);
@@ -311,12 +314,12 @@ static int launch_fold(FoldArgs a, bool aligned, cudaStream_t st) {
     const int tiles = (int)num_tiles(a.M);
     for (int col0 = 0; col0 < a.ld; col0 += kSlab) {
         a.col0 = col0;
-        if (aligned) fold_tile_kernel<MODE, true><<<tiles, kFoldThreads, 0, st>>>(a);
-        else fold_tile_kernel<MODE, false><<<tiles, kFoldThreads, 0, st>>>(a);
+        if (aligned) launch_k(fold_tile_kernel<MODE, true>, tiles, kFoldThreads, 0, st, a);
+        else launch_k(fold_tile_kernel<MODE, false>, tiles, kFoldThreads, 0, st, a);
         int rc = check_launch("fold_tile_kernel");
         if (rc) return rc;
         if (tiles > 1) {
-            fold_stitch_kernel<MODE><<<ceil_div((int64_t)tiles * kG, kFoldThreads), kFoldThreads, 0, st>>>(a, tiles);
+            launch_k(fold_stitch_kernel<MODE>, ceil_div((int64_t)tiles * kG, kFoldThreads), kFoldThreads, 0, st, a, tiles);
             if ((rc = check_launch("fold_stitch_kernel"))) return rc;
         }
     }
@@ -394,6 +397,6 @@ extern "C" int dctr_decay_sweep(float* table, int64_t X, int ld, float decay, co
     const int64_t total = X * (ld / 4);
     int blocks = ceil_div(total, 256);
     if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-    decay_sweep_kernel<<<blocks, 256, 0, as_stream(stream)>>>(reinterpret_cast<float4*>(table), X, ld / 4, decay, sorted_rows, M);
+    launch_k(decay_sweep_kernel, blocks, 256, 0, as_stream(stream), reinterpret_cast<float4*>(table), X, ld / 4, decay, sorted_rows, M);
     return check_launch("decay_sweep_kernel");
 }

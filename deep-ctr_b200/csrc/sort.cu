@@ -22,6 +22,7 @@ enum : unsigned { kFlagAgg = 1u, kFlagPrefix = 2u };       // tile status = (cou
 // digit histograms of ALL passes in one read of the keys (they do not depend on the order of the list)
 __global__ void __launch_bounds__(kSortThreads)
 sort_hist_kernel(const int32_t* __restrict__ keys, int64_t M, int passes, unsigned* __restrict__ ghist) {
+    pdl_sync();
     __shared__ unsigned h[kMaxPasses][kRadix];
     for (int p = 0; p < passes; ++p) h[p][threadIdx.x] = 0;
     __syncthreads();
@@ -50,6 +51,7 @@ __global__ void __launch_bounds__(kSortThreads)
 sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict__ pos_in, int64_t M, int shift,
                  const unsigned* __restrict__ ghist, unsigned* __restrict__ ticket, volatile unsigned* __restrict__ status,
                  int32_t* __restrict__ keys_out, int32_t* __restrict__ pos_out) {
+    pdl_sync();
     __shared__ unsigned cnt[kSortThreads / 32][kRadix];   // per-warp digit counts -> exclusive prefix over the warps
     __shared__ unsigned gbase[kRadix];
     __shared__ unsigned lbase[kRadix];
@@ -191,7 +193,7 @@ extern "C" int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t*
     cudaStream_t st = as_stream(stream);
     const int passes = num_passes(X);
     cudaMemsetAsync(ghist, 0, (size_t)(kMaxPasses * kRadix + 16 + (size_t)passes * tiles * kRadix) * sizeof(unsigned), st);
-    sort_hist_kernel<<<tiles, kSortThreads, 0, st>>>(ids, M, passes, ghist);
+    launch_k(sort_hist_kernel, tiles, kSortThreads, 0, st, ids, M, passes, ghist);
     int rc = check_launch("sort_hist_kernel");
     if (rc) return rc;
     const int32_t* kin = ids;
@@ -200,7 +202,7 @@ extern "C" int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t*
         const bool to_out = ((passes - p) & 1) == 1;
         int32_t* kout = to_out ? sorted_rows : alt_keys;
         int32_t* pout = to_out ? sorted_pos : alt_pos;
-        sort_pass_kernel<<<tiles, kSortThreads, 0, st>>>(kin, pin, M, p * kRadixBits, ghist + p * kRadix, tickets + p,
+        launch_k(sort_pass_kernel, tiles, kSortThreads, 0, st, kin, pin, M, p * kRadixBits, ghist + p * kRadix, tickets + p,
                                                          status + (size_t)p * tiles * kRadix, kout, pout);
         if ((rc = check_launch("sort_pass_kernel"))) return rc;
         kin = kout;

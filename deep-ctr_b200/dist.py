@@ -85,6 +85,7 @@ class DataParallelStep(object):
 
     def train_step(self, lr, decay=1.0, gscale=1.0, train_bias=True, last_decay=1.0):
         e = self.e
+        L.call("dctr_set_launch_mode", 0)          # collectives sit between the kernels: plain stream order
         cur = torch.cuda.current_stream(e.dev)
         e.side.wait_stream(cur)
         with torch.cuda.stream(e.side):          # id / weight exchange and the global sort: off the forward's critical path
@@ -117,6 +118,7 @@ class DataParallelStep(object):
 
     def train_step_fm(self, lr, lam=0.0, gscale=1.0, dense_l2=True):
         e = self.e
+        L.call("dctr_set_launch_mode", 0)          # collectives sit between the kernels: plain stream order
         cur = torch.cuda.current_stream(e.dev)
         e.side.wait_stream(cur)
         with torch.cuda.stream(e.side):          # id / weight exchange and the global sort: off the forward's critical path
@@ -224,6 +226,7 @@ class ShardedStep(object):
 
     def train_step(self, lr, decay=1.0, gscale=1.0, train_bias=True, last_decay=1.0):
         e, dist = self.e, self.dist
+        L.call("dctr_set_launch_mode", 0)          # collectives sit between the kernels: plain stream order
         self.forward(True, gscale)
         sc, rc, recv_rows, back = self.last
         dz = e.backward()

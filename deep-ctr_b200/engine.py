@@ -101,6 +101,9 @@ class StepEngine:
         self.overlap_wgrad = True
         self._wgrad_pending = False
         self.adam = None
+        # programmatic dependent launch pays when the step is a chain of short kernels (measured: neutral at N = 4096 with the
+        # weight-gradient stream, -3 % at N = 65536 where parked CTAs take SMs from the concurrent streams)
+        self.launch_mode = 2 if self.N <= 8192 else 0
         self.overlap_sort = True
         self.wts_are_ones = True
 
@@ -299,6 +302,7 @@ class StepEngine:
     def train_step(self, lr, decay=1.0, gscale=1.0, train_bias=True, last_decay=1.0):
         """One full step on device buffers ids/wts/y (+ masks).  The row sort only depends on the ids, so it
         runs on a side stream concurrently with the MLP forward/backward."""
+        L.call("dctr_set_launch_mode", self.launch_mode)
         cur = torch.cuda.current_stream(self.dev)
         if self.overlap_sort:
             self.side.wait_stream(cur)
@@ -346,6 +350,7 @@ class FMEngine:
         self.scat_ws = torch.zeros(L.lib().dctr_scatter_workspace(M, self.ld), dtype=torch.uint8, device=self.dev)
         self.side = torch.cuda.Stream(device=self.dev)
         self.overlap_sort = True
+        self.launch_mode = 1 if self.N <= 16384 else 0       # FM step = 10 short kernels: -9 % with dependent launches
         self.wts_are_ones = False
 
     def bias(self, buf=None):
@@ -376,6 +381,7 @@ class FMEngine:
                L.ptr(self.sort_ws), self.sort_ws.numel(), self._st())
 
     def train_step(self, lr, lam=0.0, gscale=1.0, dense_l2=True):
+        L.call("dctr_set_launch_mode", self.launch_mode)
         cur = torch.cuda.current_stream(self.dev)
         if self.overlap_sort:
             self.side.wait_stream(cur)

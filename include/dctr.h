@@ -43,6 +43,14 @@ const char* dctr_last_error(void);
 /* number of kernels this library has launched from the calling process (bench.py's gpu_launches) */
 long long dctr_launch_count(void);
 
+/* How the calling thread's next launches are issued (captured CUDA graphs keep the mode they were captured with):
+ *   0  plain stream-ordered launches (default)
+ *   1  programmatic dependent launch for every kernel: the next kernel's CTAs are scheduled while the current one still
+ *      runs and block in griddepcontrol.wait until it has completed -- hides the launch gap of short kernels
+ *   2  as 1, except the tensor-core GEMM (a parked CTA of it holds a whole SM)
+ * Results are identical in every mode.  The DCTR_PDL environment variable, when set to 0 / 1 / 2, overrides the call. */
+int dctr_set_launch_mode(int mode);
+
 /* ---- K1: per-field embedding gather + concat (+ fused inner/outer product layer) -------------
  * replaces feats_to_layer_one_array (FNN_wnzh.py:87-96, data_fm.py:46-54), the 13 rank-1 matmuls +
  * 26 embedding_lookup_sparse + concat of FNN.forward (FNN.py:76-85), the N*P scalar matmuls of
