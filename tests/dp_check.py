@@ -48,7 +48,9 @@ def main():
         l0, p0 = ref.train(feats, y)
         np.testing.assert_allclose(l1, l0, rtol=2e-5)
         np.testing.assert_allclose(p1, p0[sl], rtol=2e-5, atol=1e-6)
-        np.testing.assert_allclose(dp.get_table(), ref.get_table(), rtol=2e-5, atol=2e-6)
+        # feature 3 is hit by every sample: its row takes GN sequential-decay updates per step, so the fp32 noise between two
+        # summation orders of the dense gradients (all-reduce vs split-K) grows with the global batch
+        np.testing.assert_allclose(dp.get_table(), ref.get_table(), rtol=2e-5, atol=max(2e-6, 5e-8 * GN))
         np.testing.assert_allclose(dp.get_weights()[0], ref.get_weights()[0], rtol=2e-5, atol=2e-6)
         f1 = fm_dp.train_step({fm_dp.sp_id_hldr: feats[sl].reshape(-1), fm_dp.sp_wt_hldr: wts[sl].reshape(-1), fm_dp.lbl_hldr: y[sl]})
         f0 = fm_ref.train_step({fm_ref.sp_id_hldr: feats.reshape(-1), fm_ref.sp_wt_hldr: wts.reshape(-1), fm_ref.lbl_hldr: y})
