@@ -193,7 +193,27 @@ def call_cost(name, a):
         return "byte", a[2] * a[3] * 4
     if name == "dctr_out_xent_fwd":
         return "byte", a[2] * a[3] * 4
+    if name == "dctr_out_bwd_fused":                # reads the last activation, writes its gradient (+ dlogit)
+        return "byte", a[4] * a[5] * 8 + a[4] * 4
+    if name == "dctr_arrange_fields":               # feats in, ids + wts out
+        return "byte", a[2] * (a[3] * 4 + a[4] * 8)
+    if name == "dctr_gather_rows":                  # id + row in, row out
+        return "byte", a[4] * (4 + 8 * a[3])
+    if name == "dctr_dense_adam":                   # p, g, m, v read; p, m, v (+ g) written
+        return "byte", a[4] * 4 * (7 + (1 if a[10] else 0))
     return "byte", 0.0
+
+
+# DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) from the committed `ncu --set full` captures
+# (profiles/r01_ncu_*.txt), keyed by C-ABI call and the workload it was captured on; null for kernels not captured.
+NCU_TRAFFIC = {
+    ("fnn_criteo", "dctr_gemm_tc[NN 65536x400x430]"): 114.06e6 + 70.96e6,      # profiles/r01_ncu_criteo_gemm_tc_kernel_v2.txt
+    ("fnn_criteo", "dctr_col_wsum"): 109.07e6 + 4.51e6,                       # profiles/r01_ncu_criteo_col_wsum_kernel.txt
+    ("emb", "gather_concat_fwd"): 257.25e6 + 698.65e6,                        # profiles/r01_ncu_emb_gather_concat_kernel.txt
+    ("emb", "fm_fwd"): 234.24e6 + 51.89e6,                                    # profiles/r01_ncu_emb_fm_fwd_kernel.txt
+    ("emb", "scatter_sgd[sum]"): 4371.56e6 + 40.12e6,                         # profiles/r01_ncu_emb_fold_tile_kernel.txt
+    ("emb", "sort_rows"): 4 * (71.26e6 + 87.29e6),                            # 4 passes x profiles/r01_ncu_emb_sort_pass_kernel.txt
+}
 
 
 def emb_roofline(N=1 << 20, F=16, rank=10, X=20_000_000, reps=5):
@@ -256,6 +276,9 @@ def emb_roofline(N=1 << 20, F=16, rank=10, X=20_000_000, reps=5):
         _, cost = call_cost(name, a)
         gbs = cost / (ms * 1e-3) / 1e9
         out["kernels"][key] = {"ms": round(ms, 4), "algorithmic_MB": round(cost / 1e6, 1), "GBs": round(gbs, 1), "frac": round(gbs / pk["hbm"], 4)}
+        tr = NCU_TRAFFIC.get(("emb", key))
+        if tr is not None and (N, F, rank, X) == (1 << 20, 16, 10, 20_000_000):       # the configuration the captures were taken on
+            out["kernels"][key]["ncu_dram_MB"] = round(tr / 1e6, 1)
     return out
 
 
@@ -401,7 +424,7 @@ def run_b200(args, rank, world):
         top = kernels[0]
         roof = {"kernel": top["kernel"], "bound": "tensor" if top["unit"] == "TFLOP/s" else "hbm", "achieved": top["achieved"],
                 "peak": pk["tensor"] if top["unit"] == "TFLOP/s" else pk["hbm"], "unit": top["unit"], "frac": top["frac"],
-                "traffic": None, "peak_source": pk["src"] + (" (bf16 sustained)" if top["unit"] == "TFLOP/s" else " (copy)"),
+                "traffic": NCU_TRAFFIC.get((wl, top["kernel"])), "peak_source": pk["src"] + (" (bf16 sustained)" if top["unit"] == "TFLOP/s" else " (copy)"),
                 "share_of_step": top["share"]}
         if top["unit"] == "TFLOP/s":
             roof["note"] = "fp32 FFMA parity path; fp32 SIMT peak is 74.4 TFLOP/s -> frac_of_fp32_peak"

@@ -285,7 +285,7 @@ GEMMS = ["dctr_gemm", "dctr_gemm_tc"]     # fp32 FFMA path and tcgen05 3xTF32 pa
 @pytest.mark.parametrize("fn", GEMMS)
 @pytest.mark.parametrize("layout", ["nn", "nt", "tn"])
 @pytest.mark.parametrize("M,N,K", [(100, 300, 177), (4096, 100, 300), (33, 7, 5), (257, 129, 1171), (64, 64, 16), (1, 1, 1),
-                                   (300, 260, 70)])
+                                   (300, 260, 70), (33000, 135, 40)])      # the last one: > 16 MB of output = the transposing epilogue
 def test_gemm_layouts(L, fn, layout, M, N, K):
     rng = np.random.default_rng(17)
     A = rng.normal(0, 1, (M, K)).astype(np.float32)
@@ -321,10 +321,10 @@ def test_gemm_layouts(L, fn, layout, M, N, K):
 @pytest.mark.parametrize("fn", GEMMS)
 @pytest.mark.parametrize("act", ["tanh", "relu", "sigmoid", "none"])
 @pytest.mark.parametrize("bcast", [False, True])
-def test_gemm_epilogues(L, fn, act, bcast):
+@pytest.mark.parametrize("M,N,K", [(130, 70, 45), (33000, 135, 45)])       # small: row-per-lane stores; > 16 MB: transposing epilogue
+def test_gemm_epilogues(L, fn, act, bcast, M, N, K):
     import deepctr_oracle as O
     rng = np.random.default_rng(19)
-    M, N, K = 130, 70, 45
     A = rng.normal(0, 0.5, (M, r4(K))).astype(np.float32); A[:, K:] = 0
     B = rng.normal(0, 0.5, (K, r4(N))).astype(np.float32); B[:, N:] = 0
     bias = rng.normal(0, 0.5, N).astype(np.float32)
