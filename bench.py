@@ -490,8 +490,20 @@ def oracle_stepper(wl, N, seed=1234):
     return lambda ids, wts, y: net.train_step_tf(ids, wts, y, 1e-3)
 
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 to its workers: give the CPU arm's BLAS every host core back."""
+    n = os.cpu_count() or 1
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=n)
+    except Exception:
+        pass
+    return n
+
+
 def cpu_baseline(wl, N, budget_s=12.0, steps=None):
     form, F, X, *_ = WORKLOADS[wl]
+    use_all_host_threads()
     step = oracle_stepper(wl, N)
     pool, _ = make_pool(form, F, X, N, 4, seed=99)
     step(*pool[0])                                  # warm-up (BLAS threads, page faults)
@@ -514,8 +526,9 @@ def run_reference(args, rank, world):
     wl = args.workload
     N = args.batch or WORKLOADS[wl][6]
     K, W = args.steps, max(1, args.warmup)
+    cores = use_all_host_threads()
     step = oracle_stepper(wl, N)
-    form, F, X, *_ = WORKLOADS[wl]
+    form, F, X, rank_k, hidden, cross, _ = WORKLOADS[wl]
     pool, _ = make_pool(form, F, X, N, 4, seed=99)
     for i in range(min(W, 3)):
         step(*pool[i % 4])
@@ -533,8 +546,10 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": "FNN train samples/s", "value": v, "unit": "samples/s", "n_gpus": world, "steps": done,
         "warmup": W, "ms_per_step": el / done * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": wl, "batch_per_gpu": N, "note": "CPU oracle port of the reference step on rank 0's host cores"},
-        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": os.cpu_count(), "kind": "port",
+        "config": {"workload": wl, "form": form, "fields": F, "rows": X, "rank": rank_k, "hidden": hidden, "cross": cross,
+                   "batch_per_gpu": N, "global_batch": N,
+                   "note": "CPU oracle port of the reference step on rank 0's host cores (the Py2 / Theano / TF original cannot run here)"},
+        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": "port",
                          "sample": "%d steps of batch %d (numpy float64 + OpenBLAS)" % (done, N)},
         "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
