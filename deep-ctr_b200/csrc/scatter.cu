@@ -41,7 +41,8 @@ struct FoldArgs {
     int F; uint64_t fmul;          // n = p / F  ==  (p * fmul) >> 40 when fmul != 0 (F < 512, p < 2^31)
     int d, ld, col0;
     float lr, decay;
-    float* table;
+    float* table;                  // rows are READ from here ...
+    float* dst;                    // ... and the folded result is written here (== table except for the gradient-only fold)
     // gradient source: dense g[n*ld_n + f*ld_f + c] (* wts[p]); FM: g[n], s[n*ld_f + c], x = wts[p]
     const float* g; const float* s; int64_t ld_n; int ld_f; const float* wts;
     // per-tile carries
@@ -198,7 +199,7 @@ fold_tile_kernel(const FoldArgs a) {
             if (tail >> j & 1) {
                 if (!open_left) {
                     if (lane_on)
-                        *reinterpret_cast<float4*>(a.table + (int64_t)r[j] * a.ld + c0) = fold_final<MODE>(old[j], P, Q, c0, a.lr, a.decay);
+                        *reinterpret_cast<float4*>(a.dst + (int64_t)r[j] * a.ld + c0) = fold_final<MODE>(old[j], P, Q, c0, a.lr, a.decay);
                 } else {
                     PF = P; QF = Q; flag |= kHasF | kFClosed;
                 }
@@ -223,7 +224,7 @@ fold_tile_kernel(const FoldArgs a) {
         }
         if (closed) {
             if (lane_on)
-                *reinterpret_cast<float4*>(a.table + (int64_t)rowL * a.ld + c0) = fold_final<MODE>(oldL, P, Q, c0, a.lr, a.decay);
+                *reinterpret_cast<float4*>(a.dst + (int64_t)rowL * a.ld + c0) = fold_final<MODE>(oldL, P, Q, c0, a.lr, a.decay);
         } else {      // the segment runs past this tile: carry-out
             reinterpret_cast<float4*>(a.out_q)[tile * kG + q] = Q;
             if (q == 0) { a.out_p[tile] = P; a.out_row[tile] = rowL; }
@@ -288,7 +289,7 @@ fold_stitch_kernel(const FoldArgs a, int tiles) {
         }
         u += 4;
     }
-    if (lane_on) *reinterpret_cast<float4*>(a.table + (int64_t)row * a.ld + c0) = fold_final<MODE>(old, P, Q, c0, a.lr, a.decay);
+    if (lane_on) *reinterpret_cast<float4*>(a.dst + (int64_t)row * a.ld + c0) = fold_final<MODE>(old, P, Q, c0, a.lr, a.decay);
 }
 
 __global__ void decay_sweep_kernel(float4* __restrict__ table, int64_t X, int q, float decay,
@@ -369,7 +370,7 @@ extern "C" int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int3
     DCTR_REQUIRE(aligned16(sorted_rows) && aligned16(sorted_pos) && aligned16(table) && aligned16(workspace),
                  "scatter_sgd: rows / pos / table / workspace must be 16-byte aligned");
     FoldArgs a{};
-    a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table;
+    a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table; a.dst = table;
     a.g = g; a.s = nullptr; a.ld_n = g_ld_n; a.ld_f = g_ld_f; a.wts = wts;
     const bool aligned = aligned16(g) && (g_ld_n & 3) == 0 && (g_ld_f & 3) == 0 && g_ld_f >= ld;
     return run_fold(mode == DCTR_SCATTER_SEQ_DECAY ? kSeq : kSum, a, aligned, workspace, workspace_bytes, as_stream(stream));
@@ -386,7 +387,24 @@ extern "C" int dctr_scatter_sgd_fm(const int32_t* sorted_rows, const int32_t* so
     DCTR_REQUIRE(aligned16(sorted_rows) && aligned16(sorted_pos) && aligned16(table) && aligned16(workspace) && aligned16(s),
                  "scatter_sgd_fm: rows / pos / table / s / workspace must be 16-byte aligned");
     FoldArgs a{};
-    a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table;
+    a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table; a.dst = table;
+    a.g = g; a.s = s; a.ld_n = 0; a.ld_f = lds; a.wts = wts;
+    return run_fold(kFm, a, true, workspace, workspace_bytes, as_stream(stream));
+}
+
+extern "C" int dctr_scatter_grad_fm(const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
+                                    const float* g, const float* s, int lds, const float* wts, const float* table, int64_t X,
+                                    int ld, float* grad_out, void* workspace, size_t workspace_bytes, void* stream) {
+    DCTR_REQUIRE(M >= 0 && M < ((int64_t)1 << 31) && F > 0 && d > 0 && d <= ld && (ld & 3) == 0 && X > 0 && lds >= ld && (lds & 3) == 0,
+                 "scatter_grad_fm: bad shape (lds must be a multiple of 4 and >= ld)");
+    if (M == 0) return DCTR_OK;
+    DCTR_REQUIRE(sorted_rows && sorted_pos && g && s && table && grad_out && workspace, "scatter_grad_fm: null pointer");
+    DCTR_REQUIRE(aligned16(sorted_rows) && aligned16(sorted_pos) && aligned16(table) && aligned16(grad_out) && aligned16(workspace) && aligned16(s),
+                 "scatter_grad_fm: rows / pos / table / grad_out / s / workspace must be 16-byte aligned");
+    FoldArgs a{};
+    // the FM fold ends in  old*decay - lr*(Q - P*old):  decay = 0, lr = -1 leaves exactly the row's gradient
+    a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = -1.f; a.decay = 0.f;
+    a.table = const_cast<float*>(table); a.dst = grad_out;
     a.g = g; a.s = s; a.ld_n = 0; a.ld_f = lds; a.wts = wts;
     return run_fold(kFm, a, true, workspace, workspace_bytes, as_stream(stream));
 }

@@ -350,6 +350,7 @@ class FMEngine:
         self.scat_ws = torch.zeros(L.lib().dctr_scatter_workspace(M, self.ld), dtype=torch.uint8, device=self.dev)
         self.side = torch.cuda.Stream(device=self.dev)
         self.overlap_sort = True
+        self.adam = None
         self.launch_mode = 1 if self.N <= 16384 else 0       # FM step = 10 short kernels: -9 % with dependent launches
         self.wts_are_ones = False
 
@@ -376,6 +377,13 @@ class FMEngine:
         if with_loss:
             L.call("dctr_vec_sum", p(self.loss_n), self.N, float(gscale), p(self.loss), self._st())
 
+    def enable_adam(self, eps=1e-8, beta1=0.9, beta2=0.999):
+        f32 = dict(dtype=torch.float32, device=self.dev)
+        self.adam = (float(beta1), float(beta2), float(eps))
+        self.adam_state = torch.zeros(4, **f32)
+        self.table_g, self.table_m, self.table_v = (torch.zeros_like(self.table) for _ in range(3))
+        self.params_m, self.params_v = torch.zeros_like(self.grads), torch.zeros_like(self.grads)
+
     def sort_ids(self):
         L.call("dctr_sort_rows", L.ptr(self.ids), self.M, self.X, L.ptr(self.sorted_rows), L.ptr(self.sorted_pos),
                L.ptr(self.sort_ws), self.sort_ws.numel(), self._st())
@@ -397,6 +405,19 @@ class FMEngine:
         if self.overlap_sort:
             cur.wait_stream(self.side)
         wts = None if self.wts_are_ones else self.wts
+        if self.adam is not None:
+            # TF Adam is dense (tf_util.py:18-21): per-row gradients into G, then one sweep over table | G | m | v with the L2
+            # term's gradient lam * theta folded in (FM.py:39, LR.py:37); the bias the same way
+            b1, b2, eps = self.adam
+            L.call("dctr_adam_tick", p(self.adam_state), float(lr), b1, b2, st)
+            L.call("dctr_scatter_grad_fm", p(self.sorted_rows), p(self.sorted_pos), self.M, self.F, self.d, p(self.g),
+                   p(self.s), self.lds, p(wts), p(self.table), self.X, self.ld, p(self.table_g),
+                   p(self.scat_ws), self.scat_ws.numel(), st)
+            L.call("dctr_dense_adam", p(self.table), p(self.table_g), p(self.table_m), p(self.table_v), self.X * self.ld,
+                   p(self.adam_state), b1, b2, eps, float(lam), 1, st)
+            L.call("dctr_dense_adam", p(self.params), p(self.grads), p(self.params_m), p(self.params_v), 4,
+                   p(self.adam_state), b1, b2, eps, float(lam), 0, st)
+            return
         L.call("dctr_scatter_sgd_fm", p(self.sorted_rows), p(self.sorted_pos), self.M, self.F, self.d, p(self.g),
                p(self.s), self.lds, p(wts), float(lr), float(decay), p(self.table), self.X, self.ld,
                p(self.scat_ws), self.scat_ws.numel(), st)

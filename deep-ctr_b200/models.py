@@ -249,7 +249,9 @@ class FM(_Base):
         if mode == "train":
             self._lambda = float(_reg_argv[0])
             self._reduce = _ptmzr_argv[-1]
-            self.lr, log = _optimizer(_ptmzr_argv)
+            self.lr, log = _optimizer(_ptmzr_argv, allow_adam=True)
+            if _ptmzr_argv[0] == "adam":
+                self.engine.enable_adam(eps=float(_ptmzr_argv[2]))
             self.log += "%s, lambda(l2): %g, reduce by: %s" % (log, self._lambda, self._reduce)
             self.eval_size = eval_size
             self.eval_id_hldr, self.eval_wts_hldr = Placeholder("eval_id"), Placeholder("eval_wts")

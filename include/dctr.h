@@ -129,6 +129,13 @@ int dctr_scatter_sgd_fm(const int32_t* sorted_rows, const int32_t* sorted_pos, i
                         const float* g, const float* s, int lds, const float* wts,
                         float lr, float decay, float* table, int64_t X, int ld,
                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* Gradient-only form of the FM fold (for optimizers that need the densified gradient, i.e. Adam): rows are read from
+ * `table`, and for every touched row   grad_out[row, c] = sum_p g x s_c - table[row, c] * sum_p g x^2   (c >= 1),
+ * grad_out[row, 0] = sum_p g x   is WRITTEN (not accumulated); untouched rows of grad_out are left alone. */
+int dctr_scatter_grad_fm(const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
+                         const float* g, const float* s, int lds, const float* wts, const float* table, int64_t X, int ld,
+                         float* grad_out, void* workspace, size_t workspace_bytes, void* stream);
 /* dense L2 sweep for FM.py:39 on the rows the batch did NOT touch: table[r,:] *= decay unless r is in
  * sorted_rows (binary search).  Pure streaming read-modify-write over X*ld floats. */
 int dctr_decay_sweep(float* table, int64_t X, int ld, float decay,

@@ -357,6 +357,39 @@ class OracleFM:
         self.b = self.b - lr * (g.sum() + lam * self.b)
         return loss, sigmoid(z)
 
+    def train_step_adam(self, ids, wts, y, lr, eps=1e-8, lam=0.0, reduce="sum", beta1=0.9, beta2=0.999):
+        """Same loss (FM.py:33-39, LR.py:30-37), minimised by tf.train.AdamOptimizer(lr, epsilon) (tf_util.py:18-21): dense
+        over W, V and b, the L2 term's gradient lam*theta included in g."""
+        x = np.asarray(wts, dtype=self.dtype)
+        y = np.asarray(y, dtype=self.dtype)
+        N, F = ids.shape
+        z, vx = self.logits(ids, x)
+        scale = 1.0 if reduce == "sum" else 1.0 / N
+        loss = xent_with_logits(z, y).sum() * scale
+        if lam:
+            loss += lam * 0.5 * ((self.table ** 2).sum() + self.b ** 2)
+        g = (sigmoid(z) - y) * scale
+        rows = self.table[ids]
+        grad = np.empty_like(rows)
+        grad[..., 0] = g[:, None] * x
+        grad[..., 1:] = g[:, None, None] * (x[..., None] * vx[:, None, :] - (x ** 2)[..., None] * rows[..., 1:])
+        dense = np.zeros_like(self.table)
+        np.add.at(dense, ids.reshape(-1), grad.reshape(N * F, -1))
+        dense += lam * self.table
+        gb = g.sum() + lam * self.b
+        if not hasattr(self, "_adam"):
+            self._adam = dict(t=0, m=np.zeros_like(self.table), v=np.zeros_like(self.table), mb=0.0, vb=0.0)
+        st = self._adam
+        st["t"] += 1
+        lr_t = lr * np.sqrt(1.0 - beta2 ** st["t"]) / (1.0 - beta1 ** st["t"])
+        st["m"] = beta1 * st["m"] + (1 - beta1) * dense
+        st["v"] = beta2 * st["v"] + (1 - beta2) * dense * dense
+        self.table -= lr_t * st["m"] / (np.sqrt(st["v"]) + eps)
+        st["mb"] = beta1 * st["mb"] + (1 - beta1) * gb
+        st["vb"] = beta2 * st["vb"] + (1 - beta2) * gb * gb
+        self.b = self.b - lr_t * st["mb"] / (np.sqrt(st["vb"]) + eps)
+        return loss, sigmoid(z)
+
 
 # --------------------------------------------------------------------------------------------------
 # initialisation (FNN_wnzh.py:15-17,106-130) -- reproducible with numpy's legacy RandomState alone

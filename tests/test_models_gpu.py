@@ -177,6 +177,35 @@ def test_fm_steps_and_checkpoint(tmp_path):
         close(fm2.test_preds.eval(feed_dict={fm2.sp_id_hldr: ids.reshape(-1), fm2.sp_wt_hldr: wts.reshape(-1)}), ev, 1e-6)
 
 
+@pytest.mark.parametrize("kind,lam,reduce,use_graph", [("fm", 0.0, "sum", False), ("fm", 1e-2, "mean", True), ("lr", 1e-2, "sum", True)])
+def test_fm_lr_adam_steps(kind, lam, reduce, use_graph):
+    """['adam', lr, eps, reduce] for FM / LR (what baseline.py runs on Criteo): dense TF Adam over W, V, b with the L2
+    gradient lam * theta inside g (FM.py:39, LR.py:37); the fold only produces the per-row gradient (dctr_scatter_grad_fm)"""
+    import deepctr_oracle as O
+    from deepctr_b200.models import FM, LR
+    rng = np.random.default_rng(505)
+    N, X, F, rank = 64, 400, 8, 6
+    init = ["uniform", -0.05, 0.05, [11, 12], None]
+    if kind == "fm":
+        m = FM(N, [X, F, rank], init, ["adam", 1e-2, 1e-8, reduce], [lam], "train", 50)
+    else:
+        m = LR(N, [X, F], init, ["adam", 1e-2, 1e-8, reduce], [lam], "train", 50)
+    m.use_graph = use_graph
+    o = O.OracleFM(m.engine.get_table(), 0.0)
+    for step in range(6):
+        ids = rng.integers(0, X // 2 if step >= 3 else X, (N, F))       # from step 3 on half of the rows only coast
+        ids[:, 0] = 7
+        wts = rng.uniform(0.5, 1.5, (N, F)).astype(np.float32)
+        y = rng.integers(0, 2, N)
+        loss, preds = m.train_step({m.sp_id_hldr: ids.reshape(-1), m.sp_wt_hldr: wts.reshape(-1), m.lbl_hldr: y})
+        oloss, opreds = o.train_step_adam(ids, wts, y, 1e-2, 1e-8, lam, reduce)
+        close(preds, opreds, 5e-5)
+        close(m.engine.get_table(), o.table, 2e-4, 2e-6)
+        close(m.engine.bias().cpu(), [o.b], 2e-4, 2e-6)
+    if lam == 0.0:
+        close([loss], [oloss], 2e-5)
+
+
 def test_lr_steps_and_checkpoint(tmp_path):
     """LR.py = the FM path with rank 0: logit = sum_f x_f W[id_f] + b, dense L2 on W and b (LR.py:37, 52-53)"""
     import deepctr_oracle as O
