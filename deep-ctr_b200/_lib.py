@@ -47,6 +47,8 @@ SIGNATURES = {
     "dctr_col_wsum": (_i, [_p, _i, _i, _i, _p, _p, _p, _z, _p]),
     "dctr_vec_sum": (_i, [_p, _i, _f, _p, _p]),
     "dctr_set_launch_mode": (_i, [_i]),
+    "dctr_eval_metrics_workspace": (_z, [_l]),
+    "dctr_eval_metrics": (_i, [_p, _p, _l, _p, _p, _z, _p]),
     "dctr_dense_sgd": (_i, [_p, _p, _l, _f, _f, _p]),
     "dctr_adam_tick": (_i, [_p, _f, _f, _f, _p]),
     "dctr_dense_adam": (_i, [_p, _p, _p, _p, _l, _p, _f, _f, _f, _f, _i, _p]),

@@ -197,11 +197,12 @@ class _Base(object):
         self._pre_step()
         return self._finish_step()
 
-    def _predict_chunks(self, ids, wts):
-        """Inference over E rows in chunks of the static batch (last chunk padded with row 0 / weight 0)."""
+    def _predict_chunks(self, ids, wts, out_dev=None):
+        """Inference over E rows in chunks of the static batch (last chunk padded with row 0 / weight 0).  With `out_dev`
+        (a float32 device tensor of E elements) the predictions stay on the device and nothing is copied back."""
         e, h = self.engine, self._stage.host
         E = ids.shape[0]
-        out = np.empty(E, dtype=np.float32)
+        out = np.empty(E, dtype=np.float32) if out_dev is None else None
         saved = self._swap_masks(None)
         for s in range(0, E, self.N):
             k = min(self.N, E - s)
@@ -212,11 +213,24 @@ class _Base(object):
                 h["wts"][k:] = 0
             self._stage.upload()
             e.forward(False)
+            if out_dev is not None:
+                out_dev[s:s + k].copy_(e.pred[:k])
+                torch.cuda.current_stream().synchronize()       # the staging buffer is reused by the next chunk
+                continue
             self._out_pinned.copy_(e.out, non_blocking=True)
             torch.cuda.current_stream().synchronize()
             out[s:s + k] = self._out_np[:k]
         self._swap_masks(saved)
-        return out
+        return out if out_dev is None else out_dev
+
+    def evaluate(self, ids, wts, labels):
+        """Predict E rows (global ids [E, F], weights [E, F]) and score them ON THE DEVICE: dict(auc, log_loss, rmse, n_pos) --
+        the eval half of the reference's loop (baseline.py:357-370 + watch_train :246-259) without the D2H of the predictions."""
+        from .metrics import device_metrics
+        ids, wts = np.asarray(ids).reshape(-1, self.F), np.asarray(wts).reshape(-1, self.F)
+        preds = torch.empty(ids.shape[0], dtype=torch.float32, device=self.engine.dev)
+        self._predict_chunks(ids, wts, out_dev=preds)
+        return device_metrics(preds, np.asarray(labels, dtype=np.float32).reshape(-1), device=self.engine.dev)
 
     def _pre_step(self):
         pass

@@ -73,6 +73,14 @@ int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, const float* ta
 int dctr_arrange_fields(const int32_t* feats, const int32_t* feat_field, int N, int J, int F, int32_t pad_row,
                         int32_t* ids, float* wts, void* stream);
 
+/* ---- eval metrics on the device (baseline.py:246-259 watch_train: roc_auc_score, mean_squared_error; log_loss) --------
+ * out (device, 4 doubles) = { ROC AUC with ties by average rank, -1 when one class is absent (the reference's ValueError
+ * branch); mean log-loss (predictions clipped to [1e-15, 1 - 1e-15]); RMSE; number of positives }.
+ * pred / y: float32 [N] on the device, labels are 0 / 1, N < 2^30.  Deterministic (integer rank sums, fixed-order doubles). */
+size_t dctr_eval_metrics_workspace(int64_t N);
+int dctr_eval_metrics(const float* pred, const float* y, int64_t N, double* out, void* workspace, size_t workspace_bytes,
+                      void* stream);
+
 /* HOST helper (no device work, no stream): pack one batch of the TF-form feed into the [N, F] staging blocks,
  * F = n_num + n_cat.  ids[n, j] = j, wts[n, j] = v_wts[n, j] for the numeric fields (FNN.py:41-43);
  * ids[n, n_num + j] = c_ids[n, j] + offsets[j] (the offset add of FNN.py:65-69), wts = c_wts (NULL -> 1).

@@ -450,6 +450,31 @@ def test_column_reductions_shapes(L, N, H, off, pad):
         assert np.all(dan[:, :off] == 7.0) and np.all(dan[:, off + H:] == 7.0)       # nothing written outside the H columns
 
 
+@pytest.mark.parametrize("N,ties,pos_rate", [(1, False, 1.0), (2, False, 0.5), (1000, False, 0.2), (5000, True, 0.05),
+                                              (70001, True, 0.5), (300, False, 0.0), (4096, True, 1.0)])
+def test_eval_metrics_vs_sklearn(L, N, ties, pos_rate):
+    """AUC (ties by average rank), log-loss and RMSE on the device equal sklearn's on the host (baseline.py:246-259)"""
+    from sklearn.metrics import log_loss, mean_squared_error, roc_auc_score
+    from deepctr_b200.metrics import device_metrics
+    rng = np.random.default_rng(N)
+    y = (rng.random(N) < pos_rate).astype(np.float32)
+    if 0.0 < pos_rate < 1.0 and N > 1:
+        y[0], y[1] = 1.0, 0.0
+    p = (1.0 / (1.0 + np.exp(-(rng.normal(0, 1.5, N) + 1.5 * y)))).astype(np.float32)
+    if ties:
+        p = np.round(p, 2).astype(np.float32)               # heavy ties, some exactly 0 or 1
+    got = [device_metrics(p, y) for _ in range(2)]
+    assert got[0] == got[1]                                    # deterministic
+    g = got[0]
+    assert g["n_pos"] == int(y.sum())
+    if y.min() == y.max():
+        assert g["auc"] == -1.0
+    else:
+        np.testing.assert_allclose(g["auc"], roc_auc_score(y, p), rtol=1e-12, atol=1e-12)
+        np.testing.assert_allclose(g["log_loss"], log_loss(y, np.clip(p.astype(np.float64), 1e-15, 1 - 1e-15), labels=[0, 1]), rtol=1e-9)
+    np.testing.assert_allclose(g["rmse"], np.sqrt(mean_squared_error(y, p.astype(np.float64))), rtol=1e-10, atol=1e-12)
+
+
 def test_empty_inputs(L):
     # N = 0 / M = 0 are accepted and launch nothing
     before = L.launch_count()

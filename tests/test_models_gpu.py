@@ -206,6 +206,25 @@ def test_fm_lr_adam_steps(kind, lam, reduce, use_graph):
         close([loss], [oloss], 2e-5)
 
 
+def test_evaluate_on_device_matches_host_metrics():
+    """model.evaluate: chunked predict + AUC / log-loss / RMSE without copying the predictions back == sklearn on the
+    host-side predictions of the same model"""
+    from sklearn.metrics import roc_auc_score
+    from deepctr_b200.models import FM
+    rng = np.random.default_rng(606)
+    N, X, F, rank = 64, 300, 8, 4
+    fm = FM(N, [X, F, rank], ["uniform", -0.5, 0.5, [3, 4], None], ["sgd", 0.05, "sum"], [0.0], "train", 100)
+    E = 3 * N + 17
+    ids = rng.integers(0, X, (E, F))
+    wts = rng.uniform(0.5, 1.5, (E, F)).astype(np.float32)
+    y = rng.integers(0, 2, E)
+    host = fm.eval_preds.eval(feed_dict={fm.eval_id_hldr: ids.reshape(-1), fm.eval_wts_hldr: wts.reshape(-1)})
+    got = fm.evaluate(ids, wts, y)
+    np.testing.assert_allclose(got["auc"], roc_auc_score(y, host), rtol=1e-12)
+    np.testing.assert_allclose(got["rmse"], np.sqrt(np.mean((host.astype(np.float64) - y) ** 2)), rtol=1e-9)
+    assert got["n_pos"] == int(y.sum())
+
+
 def test_lr_steps_and_checkpoint(tmp_path):
     """LR.py = the FM path with rank 0: logit = sum_f x_f W[id_f] + b, dense L2 on W and b (LR.py:37, 52-53)"""
     import deepctr_oracle as O
