@@ -112,8 +112,7 @@ class DataParallelStep(object):
         e.join_wgrad()
         self._reduce_dense()
         cur.wait_stream(e.side)
-        L.call("dctr_scatter_sgd", e.scatter_mode, self.g_rows.data_ptr(), self.g_pos.data_ptr(), self.GM, F, d, g, g_ld_n, g_ld_f, w,
-               float(lr), float(decay), L.ptr(e.table), e.X, e.ld, self.scat_ws.data_ptr(), self.scat_ws.numel(), st)
+        e.table_update(self.g_rows.data_ptr(), self.g_pos.data_ptr(), self.GM, F, g, g_ld_n, g_ld_f, w, lr, decay, self.scat_ws)
         e.dense_update(lr, last_decay)
 
     def train_step_fm(self, lr, lam=0.0, gscale=1.0, dense_l2=True):
@@ -131,12 +130,8 @@ class DataParallelStep(object):
         self._reduce_dense()
         gg, gs = self._gather(self.gg, e.g), self._gather(self.gs, e.s)
         cur.wait_stream(e.side)
-        decay = 1.0 - lr * lam
-        L.call("dctr_scatter_sgd_fm", self.g_rows.data_ptr(), self.g_pos.data_ptr(), self.GM, e.F, e.d, gg.data_ptr(), gs.data_ptr(),
-               e.lds, L.ptr(gwts), float(lr), float(decay), L.ptr(e.table), e.X, e.ld, self.scat_ws.data_ptr(), self.scat_ws.numel(), st)
-        if lam != 0.0 and dense_l2:
-            L.call("dctr_decay_sweep", L.ptr(e.table), e.X, e.ld, float(decay), self.g_rows.data_ptr(), self.GM, st)
-        L.call("dctr_dense_sgd", L.ptr(e.params), L.ptr(e.grads), 1, float(lr), float(decay), st)
+        e.apply_update(self.g_rows.data_ptr(), self.g_pos.data_ptr(), self.GM, gg.data_ptr(), gs.data_ptr(), L.ptr(gwts), lr, lam, dense_l2,
+                       self.scat_ws)
 
 
 # ======================================================================================================
@@ -247,6 +242,8 @@ class ShardedStep(object):
         L.call("dctr_gather_rows", L.ptr(self.perm), L.ptr(self.ge), e.M, e.ldg, e.M, L.ptr(send_g), st)
         recv_g = all_to_all_rows(dist, send_g, sc, rc, self.group)       # aligned with recv_rows
         R = recv_rows.shape[0]
+        if R == 0 and e.adam is not None:      # dense Adam moves every local row even when no gradient arrived
+            e.table_update(None, None, 0, 1, L.ptr(recv_g), e.ldg, e.ldg, None, lr, decay, e.scat_ws)
         if R > 0:
             i32 = dict(dtype=torch.int32, device=e.dev)
             rows, pos = torch.empty(R, **i32), torch.empty(R, **i32)
@@ -254,8 +251,7 @@ class ShardedStep(object):
             fws = torch.empty(L.lib().dctr_scatter_workspace(R, e.ld), dtype=torch.uint8, device=e.dev)
             L.call("dctr_sort_rows", L.ptr(recv_rows), R, e.X, L.ptr(rows), L.ptr(pos), L.ptr(sws), sws.numel(), st)
             # one "field" per received slot: position p indexes recv_g directly
-            L.call("dctr_scatter_sgd", e.scatter_mode, L.ptr(rows), L.ptr(pos), R, 1, d, L.ptr(recv_g), e.ldg, e.ldg, None,
-                   float(lr), float(decay), L.ptr(e.table), e.X, e.ld, L.ptr(fws), fws.numel(), st)
+            e.table_update(L.ptr(rows), L.ptr(pos), R, 1, L.ptr(recv_g), e.ldg, e.ldg, None, lr, decay, fws)
             self._keep = (rows, pos, sws, fws, recv_g, send_g, recv_rows, back)
         e.dense_update(lr, last_decay)
 
@@ -281,8 +277,6 @@ def attach_sharded(model, dist, X_global, group=None):
 def attach(model, dist, group=None):
     """Switch a model (models.FM / FNN* / theano_fnn.FNN_wnzh) to data-parallel steps.  The reference's
     batch-size-dependent constants see the GLOBAL batch: 'mean' reduce and the decay 1-2*lambda*lr/b_size."""
-    if getattr(model.engine, "adam", None) is not None:
-        raise NotImplementedError("data-parallel Adam is not built yet (SGD only)")
     dp = DataParallelStep(model.engine, dist, group)
     model.dp = dp
     # kernels AND collectives of a step replay as one CUDA graph (NCCL is capturable); DCTR_DP_GRAPH=0 issues them eagerly

@@ -251,17 +251,22 @@ class StepEngine:
             g, g_ld_n, g_ld_f, w = self.ge.data_ptr(), F * self.ldg, self.ldg, None
         else:
             g, g_ld_n, g_ld_f, w = dz.data_ptr() + (4 if self.bias_first else 0), ldd, d, p(wts)
+        self.table_update(p(self.sorted_rows), p(self.sorted_pos), self.M, F, g, g_ld_n, g_ld_f, w, lr, decay, self.scat_ws)
+
+    def table_update(self, rows, pos, M, F, g, g_ld_n, g_ld_f, w, lr, decay, ws):
+        """Fold the sorted (row, position) list into the table: SGD in place, or -- Adam -- into the dense gradient buffer
+        followed by the dense sweep.  Also the entry point of the multi-GPU steps (global / received lists)."""
+        st, p = self._st(), L.ptr
         if self.adam is not None:
             b1, b2, eps = self.adam
             L.call("dctr_adam_tick", p(self.adam_state), float(lr), b1, b2, st)
-            L.call("dctr_scatter_sgd", self.scatter_mode, p(self.sorted_rows), p(self.sorted_pos), self.M, F, d,
-                   g, g_ld_n, g_ld_f, w, -1.0, 1.0, p(self.table_g), self.X, self.ld, p(self.scat_ws), self.scat_ws.numel(), st)
+            L.call("dctr_scatter_sgd", self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_n, g_ld_f, w, -1.0, 1.0,
+                   p(self.table_g), self.X, self.ld, p(ws), ws.numel(), st)
             L.call("dctr_dense_adam", p(self.table), p(self.table_g), p(self.table_m), p(self.table_v), self.X * self.ld,
                    p(self.adam_state), b1, b2, eps, 0.0, 1, st)
             return
-        L.call("dctr_scatter_sgd", self.scatter_mode, p(self.sorted_rows), p(self.sorted_pos), self.M, F, d,
-               g, g_ld_n, g_ld_f, w, float(lr), float(decay), p(self.table), self.X, self.ld,
-               p(self.scat_ws), self.scat_ws.numel(), st)
+        L.call("dctr_scatter_sgd", self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_n, g_ld_f, w, float(lr), float(decay),
+               p(self.table), self.X, self.ld, p(ws), ws.numel(), st)
 
     def enable_adam(self, eps=1e-8, beta1=0.9, beta2=0.999):
         """Switch the step to TensorFlow's Adam over the table AND the MLP (tf_util.py:18-21).  TF densifies the table gradient
@@ -400,27 +405,30 @@ class FMEngine:
         self.forward(True, gscale)
         st = self._st()
         p = L.ptr
-        decay = 1.0 - lr * lam
         L.call("dctr_vec_sum", p(self.g), self.N, 1.0, p(self.grads), st)           # d loss / d b = sum_n g_n
         if self.overlap_sort:
             cur.wait_stream(self.side)
         wts = None if self.wts_are_ones else self.wts
+        self.apply_update(p(self.sorted_rows), p(self.sorted_pos), self.M, p(self.g), p(self.s), p(wts), lr, lam, dense_l2, self.scat_ws)
+
+    def apply_update(self, rows, pos, M, g, s, wts, lr, lam, dense_l2, ws):
+        """Table + bias update from a sorted (row, position) list: this rank's own, or the global one of the data-parallel step."""
+        st, p = self._st(), L.ptr
+        decay = 1.0 - lr * lam
         if self.adam is not None:
             # TF Adam is dense (tf_util.py:18-21): per-row gradients into G, then one sweep over table | G | m | v with the L2
             # term's gradient lam * theta folded in (FM.py:39, LR.py:37); the bias the same way
             b1, b2, eps = self.adam
             L.call("dctr_adam_tick", p(self.adam_state), float(lr), b1, b2, st)
-            L.call("dctr_scatter_grad_fm", p(self.sorted_rows), p(self.sorted_pos), self.M, self.F, self.d, p(self.g),
-                   p(self.s), self.lds, p(wts), p(self.table), self.X, self.ld, p(self.table_g),
-                   p(self.scat_ws), self.scat_ws.numel(), st)
+            L.call("dctr_scatter_grad_fm", rows, pos, M, self.F, self.d, g, s, self.lds, wts, p(self.table), self.X, self.ld,
+                   p(self.table_g), p(ws), ws.numel(), st)
             L.call("dctr_dense_adam", p(self.table), p(self.table_g), p(self.table_m), p(self.table_v), self.X * self.ld,
                    p(self.adam_state), b1, b2, eps, float(lam), 1, st)
             L.call("dctr_dense_adam", p(self.params), p(self.grads), p(self.params_m), p(self.params_v), 4,
                    p(self.adam_state), b1, b2, eps, float(lam), 0, st)
             return
-        L.call("dctr_scatter_sgd_fm", p(self.sorted_rows), p(self.sorted_pos), self.M, self.F, self.d, p(self.g),
-               p(self.s), self.lds, p(wts), float(lr), float(decay), p(self.table), self.X, self.ld,
-               p(self.scat_ws), self.scat_ws.numel(), st)
+        L.call("dctr_scatter_sgd_fm", rows, pos, M, self.F, self.d, g, s, self.lds, wts, float(lr), float(decay),
+               p(self.table), self.X, self.ld, p(ws), ws.numel(), st)
         if lam != 0.0 and dense_l2:   # FM.py:39: the L2 term reaches every row, touched or not
-            L.call("dctr_decay_sweep", p(self.table), self.X, self.ld, float(decay), p(self.sorted_rows), self.M, st)
+            L.call("dctr_decay_sweep", p(self.table), self.X, self.ld, float(decay), rows, M, st)
         L.call("dctr_dense_sgd", p(self.params), p(self.grads), 1, float(lr), float(decay), st)

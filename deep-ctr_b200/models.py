@@ -389,8 +389,6 @@ class _FNNBase(_Base):
             self._reduce = _ptmzr_argv[-1]
             self.lr, log = _optimizer(_ptmzr_argv, allow_adam=True)
             if _ptmzr_argv[0] == "adam":
-                if shard is not None:
-                    raise NotImplementedError("adam with a row-sharded table is not built yet")
                 eng.enable_adam(eps=float(_ptmzr_argv[2]))
             self.log += "%s, reduce by: %s, keep_prob(drop_out): %g" % (log, self._reduce, self._keep_prob)
             self.eval_size = eval_size

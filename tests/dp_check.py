@@ -56,6 +56,20 @@ def main():
         f0 = fm_ref.train_step({fm_ref.sp_id_hldr: feats.reshape(-1), fm_ref.sp_wt_hldr: wts.reshape(-1), fm_ref.lbl_hldr: y})
         np.testing.assert_allclose(f1[1], f0[1][sl], rtol=2e-5, atol=1e-6)
         np.testing.assert_allclose(fm_dp.engine.get_table(), fm_ref.engine.get_table(), rtol=2e-5, atol=2e-6)
+    # Adam (dense, TF form) under data parallelism: FM with L2, against the single-GPU Adam step on the global batch
+    ad_dp = FM(N, [X, F, k - 1], ["uniform", -0.05, 0.05, [1, 2], None], ["adam", 1e-2, 1e-8, "mean"], [0.01], "train", N)
+    ddist.attach(ad_dp, dist)
+    ad_ref = FM(GN, [X, F, k - 1], ["uniform", -0.05, 0.05, [1, 2], None], ["adam", 1e-2, 1e-8, "mean"], [0.01], "train", GN)
+    ad_ref.use_graph = False
+    for step in range(5):
+        feats = np.stack([rng.integers(0, X // F, GN) + f * (X // F) for f in range(F)], 1)
+        y = rng.integers(0, 2, GN)
+        wts = rng.uniform(0.5, 1.5, (GN, F)).astype(np.float32)
+        sl = slice(rank * N, (rank + 1) * N)
+        a1 = ad_dp.train_step({ad_dp.sp_id_hldr: feats[sl].reshape(-1), ad_dp.sp_wt_hldr: wts[sl].reshape(-1), ad_dp.lbl_hldr: y[sl]})
+        a0 = ad_ref.train_step({ad_ref.sp_id_hldr: feats.reshape(-1), ad_ref.sp_wt_hldr: wts.reshape(-1), ad_ref.lbl_hldr: y})
+        np.testing.assert_allclose(a1[1], a0[1][sl], rtol=5e-5, atol=1e-6)
+        np.testing.assert_allclose(ad_dp.engine.get_table(), ad_ref.engine.get_table(), rtol=2e-4, atol=2e-6)
     # replicas are bit-identical to each other
     t = dp.engine.table.clone()
     ts = [torch.empty_like(t) for _ in range(world)]
@@ -63,7 +77,7 @@ def main():
     assert all(torch.equal(ts[0], x) for x in ts)
     if rank == 0:
         print("dp_check ok: world=%d" % world)
-    ddist.shutdown(dist, [dp, fm_dp])
+    ddist.shutdown(dist, [dp, fm_dp, ad_dp])
 
 
 if __name__ == "__main__":

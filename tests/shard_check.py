@@ -30,7 +30,9 @@ def main():
     X_dim, F, d = n_num + int(cat_sizes.sum()), n_num + len(cat_sizes), r + 1
     N = 48
     GN = N * world
-    for cls_name, hidden in [("FNN", [24, 12]), ("FNN_IP_L3", [32, 16, 8]), ("FNN_OP_L3", [32, 16, 8])]:
+    for cls_name, hidden, ptm in [("FNN", [24, 12], ["sgd", 0.05, "sum"]), ("FNN_IP_L3", [32, 16, 8], ["sgd", 0.05, "sum"]),
+                                  ("FNN_OP_L3", [32, 16, 8], ["sgd", 0.05, "sum"]), ("FNN", [24, 12], ["adam", 1e-2, 1e-8, "sum"])]:
+        tol = 2e-5 if ptm[0] == "sgd" else 2e-4      # Adam divides by sqrt(v): summation-order noise is amplified early on
         cls = getattr(M, cls_name)
         cw = {"none": 0, "ip": F * (F - 1) // 2, "op": d * d}[cls.cross]
         dims = [F * d + cw + 1] + hidden + [1]
@@ -44,9 +46,9 @@ def main():
             pickle.dump(vm, f, protocol=2)
         rch = [X_dim, F, r] + hidden + ["tanh"]
         init = ["uniform", -0.01, 0.01, list(range(1, 12)), path]
-        sh = cls(cat_sizes, offsets, N, rch, init, ["sgd", 0.05, "sum"], [1.0], "train", N, shard=(rank, world))
+        sh = cls(cat_sizes, offsets, N, rch, init, ptm, [1.0], "train", N, shard=(rank, world))
         ddist.attach_sharded(sh, dist, X_dim)
-        ref = cls(cat_sizes, offsets, GN, rch, init, ["sgd", 0.05, "sum"], [1.0], "train", GN)
+        ref = cls(cat_sizes, offsets, GN, rch, init, ptm, [1.0], "train", GN)
         ref.use_graph = False
         for step in range(3):
             c_ids = np.stack([rng.integers(0, s, GN) for s in cat_sizes], 1)
@@ -60,8 +62,8 @@ def main():
             np.testing.assert_allclose(l1, l0, rtol=2e-5)
             np.testing.assert_allclose(p1, p0[sl], rtol=2e-5, atol=1e-6)
             mine = ref.engine.get_table()[rank::world]
-            np.testing.assert_allclose(sh.engine.get_table()[:mine.shape[0]], mine, rtol=2e-5, atol=2e-6)
-            np.testing.assert_allclose(sh.engine.get_layer(0)[0], ref.engine.get_layer(0)[0], rtol=2e-5, atol=2e-6)
+            np.testing.assert_allclose(sh.engine.get_table()[:mine.shape[0]], mine, rtol=tol, atol=2e-6)
+            np.testing.assert_allclose(sh.engine.get_layer(0)[0], ref.engine.get_layer(0)[0], rtol=tol, atol=2e-6)
         # collective inference through the sharded lookup
         ids_eval = np.concatenate([np.broadcast_to(np.arange(n_num), (GN, n_num)), c_ids + np.array(offsets)], 1)
         wts_eval = np.concatenate([v_wts, c_wts], 1)
@@ -69,7 +71,7 @@ def main():
         pr = ref.eval_preds.eval({ref.eval_id_hldr: ids_eval, ref.eval_wts_hldr: wts_eval})
         np.testing.assert_allclose(pe, pr[sl], rtol=2e-5, atol=1e-6)
         if rank == 0:
-            print("shard_check %s ok: world=%d loss=%.6f" % (cls_name, world, l1))
+            print("shard_check %s %s ok: world=%d loss=%.6f" % (cls_name, ptm[0], world, l1))
     ddist.shutdown(dist)
 
 
