@@ -181,8 +181,11 @@ def call_cost(name, a):
         return "byte", N * (F * 8 + F * 4 * d + 4 * ldz + F * 4 * d)
     if name == "dctr_sort_rows":
         M, X = a[1], a[2]
-        passes = max(1, (max(1, int(X - 1).bit_length()) + 7) // 8)
-        return "byte", passes * M * (8 + 16)       # histogram read + scatter read/write of (key, pos)
+        bits = max(1, int(X - 1).bit_length())
+        passes = (bits + 7) // 8
+        if M <= (1 << 18):
+            passes = min(passes, (bits + 9) // 10)           # short lists: 10-bit digits when they save a pass
+        return "byte", M * 4 + passes * M * 16     # one histogram read of the keys + per pass read/write of (key, pos)
     if name == "dctr_splitk_reduce":
         return "byte", (a[1] + 1) * a[2] * a[3] * 4
     if name == "dctr_dense_sgd":
@@ -193,6 +196,8 @@ def call_cost(name, a):
         return "byte", a[2] * a[3] * 4
     if name == "dctr_out_xent_fwd":
         return "byte", a[2] * a[3] * 4
+    if name == "dctr_vec_sum":
+        return "byte", a[1] * 4
     if name == "dctr_out_bwd_fused":                # reads the last activation, writes its gradient (+ dlogit)
         return "byte", a[4] * a[5] * 8 + a[4] * 4
     if name == "dctr_arrange_fields":               # feats in, ids + wts out
@@ -212,7 +217,6 @@ NCU_TRAFFIC = {
     ("emb", "gather_concat_fwd"): 257.25e6 + 698.65e6,                        # profiles/r01_ncu_emb_gather_concat_kernel.txt
     ("emb", "fm_fwd"): 234.24e6 + 51.89e6,                                    # profiles/r01_ncu_emb_fm_fwd_kernel.txt
     ("emb", "scatter_sgd[sum]"): 4371.56e6 + 40.12e6,                         # profiles/r01_ncu_emb_fold_tile_kernel.txt
-    ("emb", "sort_rows"): 4 * (71.26e6 + 87.29e6),                            # 4 passes x profiles/r01_ncu_emb_sort_pass_kernel.txt
 }
 
 

@@ -89,7 +89,7 @@ PROFILE = None   # bench.py sets this to a list; every call then appends (name, 
 
 def call(name, *args):
     """Invoke an int-returning entry point; raise RuntimeError with dctr_last_error() on failure."""
-    if PROFILE is not None:
+    if PROFILE is not None and name not in ("dctr_set_launch_mode", "dctr_host_pack_fields"):      # host-only entry points
         import torch
         st = torch.cuda.current_stream()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -11,20 +11,23 @@ namespace dctr {
 constexpr int kSortThreads = 256;
 constexpr int kSortItems = 8;                       // chunks per warp
 constexpr int kSortTile = kSortThreads * kSortItems;  // 2048 elements per CTA
-constexpr int kRadixBits = 8;
-constexpr int kRadix = 1 << kRadixBits;
-
-__device__ __forceinline__ int digit_of(int32_t key, int shift) { return (key >> shift) & (kRadix - 1); }
-
 constexpr int kMaxPasses = 4;
+constexpr int kMaxRadix = 1024;
 enum : unsigned { kFlagAgg = 1u, kFlagPrefix = 2u };       // tile status = (count << 2) | flag
 
+// Digit width RB: 8 bits (256 bins, static shared memory) or 10 bits (1024 bins, 56 KB of dynamic shared memory).  The
+// wide digit is chosen when it saves a pass: 20-bit keys sort in 2 passes instead of 3, 25..30-bit keys in 3 instead of 4.
+template <int RB>
+__device__ __forceinline__ int digit_of(int32_t key, int shift) { return (key >> shift) & ((1 << RB) - 1); }
+
 // digit histograms of ALL passes in one read of the keys (they do not depend on the order of the list)
+template <int RB>
 __global__ void __launch_bounds__(kSortThreads)
 sort_hist_kernel(const int32_t* __restrict__ keys, int64_t M, int passes, unsigned* __restrict__ ghist) {
     pdl_sync();
-    __shared__ unsigned h[kMaxPasses][kRadix];
-    for (int p = 0; p < passes; ++p) h[p][threadIdx.x] = 0;
+    constexpr int R = 1 << RB;
+    extern __shared__ unsigned h[];                  // [passes][R]
+    for (int i = threadIdx.x; i < passes * R; i += kSortThreads) h[i] = 0;
     __syncthreads();
     const int64_t base = (int64_t)blockIdx.x * kSortTile;
 #pragma unroll
@@ -32,36 +35,41 @@ sort_hist_kernel(const int32_t* __restrict__ keys, int64_t M, int passes, unsign
         const int64_t i = base + j * kSortThreads + threadIdx.x;
         if (i < M) {
             const int32_t k = keys[i];
-            for (int p = 0; p < passes; ++p) atomicAdd(&h[p][digit_of(k, p * kRadixBits)], 1u);
+            for (int p = 0; p < passes; ++p) atomicAdd(&h[p * R + digit_of<RB>(k, p * RB)], 1u);
         }
     }
     __syncthreads();
-    for (int p = 0; p < passes; ++p) {
-        const unsigned v = h[p][threadIdx.x];
-        if (v) atomicAdd(&ghist[p * kRadix + threadIdx.x], v);      // integer atomics: the totals are order-independent
+    for (int i = threadIdx.x; i < passes * R; i += kSortThreads) {
+        const unsigned v = h[i];
+        if (v) atomicAdd(&ghist[i], v);              // integer atomics: the totals are order-independent
     }
 }
 
 // One pass of the LSD sort in ONE kernel ("onesweep"): a CTA takes the next tile (ticket), ranks its 2048 keys stably,
-// publishes its per-digit counts, obtains the counts of all earlier tiles by decoupled look-back (thread d walks digit
-// d back to the nearest tile whose inclusive prefix is published), and scatters.  Tiles are handed out in ticket order,
-// so a CTA only ever waits on tiles that are already running: no deadlock, and the output does not depend on timing.
+// publishes its per-digit counts, obtains the counts of all earlier tiles by decoupled look-back (every thread walks its
+// R/256 digits back to the nearest tile whose inclusive prefix is published), and scatters.  Tiles are handed out in ticket
+// order, so a CTA only ever waits on tiles that are already running: no deadlock, and the output does not depend on timing.
 // pos_in == nullptr: payload is the element index itself (first pass)
+template <int RB>
 __global__ void __launch_bounds__(kSortThreads)
 sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict__ pos_in, int64_t M, int shift,
                  const unsigned* __restrict__ ghist, unsigned* __restrict__ ticket, volatile unsigned* __restrict__ status,
                  int32_t* __restrict__ keys_out, int32_t* __restrict__ pos_out) {
     pdl_sync();
-    __shared__ unsigned cnt[kSortThreads / 32][kRadix];   // per-warp digit counts -> exclusive prefix over the warps
-    __shared__ unsigned gbase[kRadix];
-    __shared__ unsigned lbase[kRadix];
-    __shared__ unsigned wsum[kSortThreads / 32], lsum[kSortThreads / 32];
-    __shared__ int32_t skey[kSortTile], spos[kSortTile];
+    constexpr int R = 1 << RB;
+    constexpr int DPT = R / kSortThreads;                 // digits owned by a thread: tid*DPT .. tid*DPT + DPT-1
+    constexpr int NW = kSortThreads / 32;
+    extern __shared__ unsigned sort_smem[];
+    unsigned* cnt = sort_smem;                            // [NW][R] per-warp digit counts -> exclusive prefix over the warps
+    unsigned* gbase = cnt + NW * R;                       // [R]
+    unsigned* lbase = gbase + R;                          // [R]
+    int32_t* skey = reinterpret_cast<int32_t*>(lbase + R);   // [kSortTile]
+    int32_t* spos = skey + kSortTile;                     // [kSortTile]
+    __shared__ unsigned wsum[NW], lsum[NW];
     __shared__ unsigned s_tile;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-#pragma unroll
-    for (int w = 0; w < kSortThreads / 32; ++w) cnt[w][tid] = 0;
+    for (int i = tid; i < NW * R; i += kSortThreads) cnt[i] = 0;
     __syncthreads();
     const unsigned tile = s_tile;
     const int64_t base = (int64_t)tile * kSortTile;
@@ -74,47 +82,69 @@ sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict_
         const int64_t i = base + (warp * kSortItems + j) * 32 + lane;
         const bool valid = i < M;
         key[j] = valid ? keys_in[i] : 0;
-        const int dg = digit_of(key[j], shift);
-        // lanes holding the same digit: eight ballots (one per digit bit) instead of __match_any_sync, whose cost grows
-        // with the number of distinct values in the warp
+        const int dg = digit_of<RB>(key[j], shift);
+        // lanes holding the same digit: one ballot per digit bit instead of __match_any_sync, whose cost grows with the
+        // number of distinct values in the warp
         unsigned peers = __ballot_sync(0xffffffffu, valid);
 #pragma unroll
-        for (int bit = 0; bit < kRadixBits; ++bit) {
+        for (int bit = 0; bit < RB; ++bit) {
             const unsigned m = __ballot_sync(0xffffffffu, (dg >> bit) & 1);
             peers &= ((dg >> bit) & 1) ? m : ~m;
         }
         const int leader = __ffs(peers) - 1;
         unsigned before = 0;
-        if (valid && lane == leader) { before = cnt[warp][dg]; cnt[warp][dg] = before + __popc(peers); }
+        if (valid && lane == leader) { before = cnt[warp * R + dg]; cnt[warp * R + dg] = before + __popc(peers); }
         before = __shfl_sync(0xffffffffu, before, valid ? leader : lane);
         rank[j] = before + __popc(peers & ((1u << lane) - 1u));
         __syncwarp();
     }
     __syncthreads();
 
-    // ---- thread d owns digit d: prefix over the warps, publish, look back ----
-    unsigned total = 0;
+    // ---- per owned digit: prefix over the warps, publish, look back ----
+    unsigned total[DPT], excl[DPT];
 #pragma unroll
-    for (int w = 0; w < kSortThreads / 32; ++w) { const unsigned v = cnt[w][tid]; cnt[w][tid] = total; total += v; }
-    volatile unsigned* mine = status + (int64_t)tile * kRadix + tid;
-    unsigned excl = 0;
-    if (tile == 0) {
-        *mine = (total << 2) | kFlagPrefix;
-    } else {
-        *mine = (total << 2) | kFlagAgg;
-        for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
-            unsigned v;
-            do { v = status[t * kRadix + tid]; } while ((v & 3u) == 0u);
-            excl += v >> 2;
-            if (v & kFlagPrefix) break;
-        }
-        *mine = ((excl + total) << 2) | kFlagPrefix;
+    for (int q = 0; q < DPT; ++q) {
+        const int d = tid * DPT + q;
+        unsigned t = 0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) { const unsigned v = cnt[w * R + d]; cnt[w * R + d] = t; t += v; }
+        total[q] = t;
+        excl[q] = 0;
     }
-    // ---- exclusive scans over the 256 digits: of the global totals (digit base) and of this tile's totals (local base) ----
-    unsigned lbase_d;
+    volatile unsigned* mine = status + (int64_t)tile * R + tid * DPT;
+    if (tile == 0) {
+#pragma unroll
+        for (int q = 0; q < DPT; ++q) mine[q] = (total[q] << 2) | kFlagPrefix;
+    } else {
+#pragma unroll
+        for (int q = 0; q < DPT; ++q) mine[q] = (total[q] << 2) | kFlagAgg;
+        unsigned open = (1u << DPT) - 1u;                 // digits whose walk has not met an inclusive prefix yet
+        for (int64_t t = (int64_t)tile - 1; t >= 0 && open; --t) {
+            const volatile unsigned* theirs = status + t * R + tid * DPT;
+            unsigned v[DPT];
+            bool ready;
+            do {                                           // the DPT words of one tile are read together
+                ready = true;
+#pragma unroll
+                for (int q = 0; q < DPT; ++q) { v[q] = theirs[q]; ready = ready && ((v[q] & 3u) != 0u || !((open >> q) & 1u)); }
+            } while (!ready);
+#pragma unroll
+            for (int q = 0; q < DPT; ++q) {
+                if ((open >> q) & 1u) {
+                    excl[q] += v[q] >> 2;
+                    if (v[q] & kFlagPrefix) open &= ~(1u << q);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < DPT; ++q) mine[q] = ((excl[q] + total[q]) << 2) | kFlagPrefix;
+    }
+    // ---- exclusive scans over the R digits: of the global totals (digit base) and of this tile's totals (local base) ----
     {
-        const unsigned t = ghist[tid];
-        unsigned incl = t, lincl = total;
+        unsigned gt[DPT], gsum = 0, lsum_t = 0;
+#pragma unroll
+        for (int q = 0; q < DPT; ++q) { gt[q] = ghist[tid * DPT + q]; gsum += gt[q]; lsum_t += total[q]; }
+        unsigned incl = gsum, lincl = lsum_t;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const unsigned u = __shfl_up_sync(0xffffffffu, incl, o), lu = __shfl_up_sync(0xffffffffu, lincl, o);
@@ -124,10 +154,16 @@ sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict_
         __syncthreads();
         unsigned off = 0, loff = 0;
         for (int w = 0; w < warp; ++w) { off += wsum[w]; loff += lsum[w]; }
-        lbase_d = loff + lincl - total;
-        lbase[tid] = lbase_d;
-        // destination of the tile's digit-d run, minus its offset inside the tile: dst = gbase[d] + (index in sorted tile)
-        gbase[tid] = off + incl - t + excl - lbase_d;
+        unsigned g_run = off + incl - gsum, l_run = loff + lincl - lsum_t;       // exclusive prefixes of this thread's first digit
+#pragma unroll
+        for (int q = 0; q < DPT; ++q) {
+            const int d = tid * DPT + q;
+            lbase[d] = l_run;
+            // destination of the tile's digit-d run, minus its offset inside the tile: dst = gbase[d] + (index in sorted tile)
+            gbase[d] = g_run + excl[q] - l_run;
+            g_run += gt[q];
+            l_run += total[q];
+        }
     }
     __syncthreads();
     // ---- reorder the tile in shared memory (stable), then write out runs: consecutive threads -> consecutive addresses ----
@@ -135,8 +171,8 @@ sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict_
     for (int j = 0; j < kSortItems; ++j) {
         const int64_t i = base + (warp * kSortItems + j) * 32 + lane;
         if (i < M) {
-            const int dg = digit_of(key[j], shift);
-            const unsigned lp = lbase[dg] + cnt[warp][dg] + rank[j];
+            const int dg = digit_of<RB>(key[j], shift);
+            const unsigned lp = lbase[dg] + cnt[warp * R + dg] + rank[j];
             skey[lp] = key[j];
             spos[lp] = pos_in ? pos_in[i] : (int32_t)i;
         }
@@ -148,24 +184,71 @@ sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict_
         const int t = j * kSortThreads + tid;
         if (t < nvalid) {
             const int32_t k = skey[t];
-            const unsigned dst = gbase[digit_of(k, shift)] + (unsigned)t;      // modulo 2^32: gbase may have wrapped below 0
+            const unsigned dst = gbase[digit_of<RB>(k, shift)] + (unsigned)t;      // modulo 2^32: gbase may have wrapped below 0
             keys_out[dst] = k;
             pos_out[dst] = spos[t];
         }
     }
 }
 
-static int num_passes(int64_t X) {
+static int key_bits(int64_t X) {
     int bits = 1;
     while (bits < 31 && ((int64_t)1 << bits) < X) ++bits;
-    return (bits + kRadixBits - 1) / kRadixBits;
+    return bits;
+}
+// digit width: 10 bits when that saves a pass over 8-bit digits AND the list is short.  A short list is latency-bound (a
+// pass costs ~8 us whatever it does: M = 65536, 20-bit keys: 36.8 -> 28.6 us); on a long one the wide pass loses more to
+// its 56 KB of shared memory, 10 ballots per key and 4 KB of look-back state per tile than the saved pass returns
+// (M = 16.7 M, 25-bit keys: 0.90 -> 1.19 ms), and at M = 1 M the two are equal.
+static int radix_bits(int64_t X, int64_t M) {
+    const int bits = key_bits(X);
+    return (M <= ((int64_t)1 << 18) && (bits + 9) / 10 < (bits + 7) / 8) ? 10 : 8;
+}
+static int num_passes(int64_t X, int64_t M) {
+    const int rb = radix_bits(X, M);
+    return (key_bits(X) + rb - 1) / rb;
+}
+template <int RB>
+static constexpr size_t pass_smem() { return ((size_t)(kSortThreads / 32 + 2) * (1 << RB) + 2 * kSortTile) * sizeof(unsigned); }
+
+template <int RB>
+static int run_sort(const int32_t* ids, int64_t M, int passes, int32_t* sorted_rows, int32_t* sorted_pos, int32_t* alt_keys,
+                    int32_t* alt_pos, unsigned* ghist, unsigned* tickets, unsigned* status, cudaStream_t st) {
+    constexpr int R = 1 << RB;
+    const int tiles = (int)((M + kSortTile - 1) / kSortTile);
+    static bool attr_set = false;
+    if (!attr_set) {       // 56 KB at RB = 10: above the 48 KB default
+        cudaFuncSetAttribute(sort_pass_kernel<RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pass_smem<RB>());
+        attr_set = true;
+    }
+    launch_k(sort_hist_kernel<RB>, tiles, kSortThreads, (size_t)passes * R * sizeof(unsigned), st, ids, M, passes, ghist);
+    int rc = check_launch("sort_hist_kernel");
+    if (rc) return rc;
+    const int32_t* kin = ids;
+    const int32_t* pin = nullptr;
+    for (int p = 0; p < passes; ++p) {
+        const bool to_out = ((passes - p) & 1) == 1;
+        int32_t* kout = to_out ? sorted_rows : alt_keys;
+        int32_t* pout = to_out ? sorted_pos : alt_pos;
+        launch_k(sort_pass_kernel<RB>, tiles, kSortThreads, pass_smem<RB>(), st, kin, pin, M, p * RB, ghist + p * R, tickets + p,
+                 status + (size_t)p * tiles * R, kout, pout);
+        if ((rc = check_launch("sort_pass_kernel"))) return rc;
+        kin = kout;
+        pin = pout;
+    }
+    return DCTR_OK;
 }
 
 }  // namespace dctr
 
 using namespace dctr;
 
-static size_t sort_header_words(int64_t tiles) { return (size_t)kMaxPasses * kRadix + 16 + (size_t)kMaxPasses * tiles * kRadix; }
+// ghist [kMaxPasses][kMaxRadix] | tickets [16] | status [passes][tiles][R]: 4 passes x 256 bins, or (short lists only)
+// 3 passes x 1024 bins
+static size_t sort_header_words(int64_t tiles) {
+    const size_t per_tile = tiles <= 128 ? (size_t)3 * kMaxRadix : (size_t)kMaxPasses * 256;
+    return (size_t)kMaxPasses * kMaxRadix + 16 + per_tile * tiles;
+}
 
 extern "C" size_t dctr_sort_rows_workspace(int64_t M) {
     if (M <= 0) return 16;
@@ -187,26 +270,12 @@ extern "C" int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t*
     const int64_t m4 = (M + 3) / 4 * 4;
     int32_t* alt_keys = static_cast<int32_t*>(workspace);
     int32_t* alt_pos = alt_keys + m4;
-    unsigned* ghist = reinterpret_cast<unsigned*>(alt_pos + m4);       // [passes][256] digit totals
-    unsigned* tickets = ghist + kMaxPasses * kRadix;                    // [passes] tile tickets (padded to 16 words)
-    unsigned* status = tickets + 16;                                    // [passes][tiles][256] look-back state
+    unsigned* ghist = reinterpret_cast<unsigned*>(alt_pos + m4);       // [passes][R] digit totals
+    unsigned* tickets = ghist + kMaxPasses * kMaxRadix;                 // [passes] tile tickets (padded to 16 words)
+    unsigned* status = tickets + 16;                                    // [passes][tiles][R] look-back state
     cudaStream_t st = as_stream(stream);
-    const int passes = num_passes(X);
-    cudaMemsetAsync(ghist, 0, (size_t)(kMaxPasses * kRadix + 16 + (size_t)passes * tiles * kRadix) * sizeof(unsigned), st);
-    launch_k(sort_hist_kernel, tiles, kSortThreads, 0, st, ids, M, passes, ghist);
-    int rc = check_launch("sort_hist_kernel");
-    if (rc) return rc;
-    const int32_t* kin = ids;
-    const int32_t* pin = nullptr;
-    for (int p = 0; p < passes; ++p) {
-        const bool to_out = ((passes - p) & 1) == 1;
-        int32_t* kout = to_out ? sorted_rows : alt_keys;
-        int32_t* pout = to_out ? sorted_pos : alt_pos;
-        launch_k(sort_pass_kernel, tiles, kSortThreads, 0, st, kin, pin, M, p * kRadixBits, ghist + p * kRadix, tickets + p,
-                                                         status + (size_t)p * tiles * kRadix, kout, pout);
-        if ((rc = check_launch("sort_pass_kernel"))) return rc;
-        kin = kout;
-        pin = pout;
-    }
-    return DCTR_OK;
+    const int rb = radix_bits(X, M), passes = num_passes(X, M), R = 1 << rb;
+    cudaMemsetAsync(ghist, 0, (size_t)(kMaxPasses * kMaxRadix + 16 + (size_t)passes * tiles * R) * sizeof(unsigned), st);
+    if (rb == 10) return run_sort<10>(ids, M, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
+    return run_sort<8>(ids, M, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
 }
