@@ -128,6 +128,7 @@ class DataParallelStep(object):
         st = cur.cuda_stream
         L.call("dctr_vec_sum", L.ptr(e.g), e.N, 1.0, L.ptr(e.grads), st)
         self._reduce_dense()
+        e.bias_update(lr, lam)
         gg, gs = self._gather(self.gg, e.g), self._gather(self.gs, e.s)
         cur.wait_stream(e.side)
         e.apply_update(self.g_rows.data_ptr(), self.g_pos.data_ptr(), self.GM, gg.data_ptr(), gs.data_ptr(), L.ptr(gwts), lr, lam, dense_l2,

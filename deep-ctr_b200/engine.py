@@ -406,29 +406,38 @@ class FMEngine:
         st = self._st()
         p = L.ptr
         L.call("dctr_vec_sum", p(self.g), self.N, 1.0, p(self.grads), st)           # d loss / d b = sum_n g_n
+        self.bias_update(lr, lam)          # before the join: the one-float update runs while the sort is still going
         if self.overlap_sort:
             cur.wait_stream(self.side)
         wts = None if self.wts_are_ones else self.wts
         self.apply_update(p(self.sorted_rows), p(self.sorted_pos), self.M, p(self.g), p(self.s), p(wts), lr, lam, dense_l2, self.scat_ws)
 
+    def bias_update(self, lr, lam):
+        """b from grads[0] = sum_n g_n (already all-reduced in the data-parallel step); ticks Adam's step counter."""
+        st, p = self._st(), L.ptr
+        if self.adam is not None:
+            b1, b2, eps = self.adam
+            L.call("dctr_adam_tick", p(self.adam_state), float(lr), b1, b2, st)
+            L.call("dctr_dense_adam", p(self.params), p(self.grads), p(self.params_m), p(self.params_v), 4,
+                   p(self.adam_state), b1, b2, eps, float(lam), 0, st)
+        else:
+            L.call("dctr_dense_sgd", p(self.params), p(self.grads), 1, float(lr), float(1.0 - lr * lam), st)
+
     def apply_update(self, rows, pos, M, g, s, wts, lr, lam, dense_l2, ws):
-        """Table + bias update from a sorted (row, position) list: this rank's own, or the global one of the data-parallel step."""
+        """Table update from a sorted (row, position) list: this rank's own, or the global one of the data-parallel step
+        (bias_update must have run first: it advances Adam's step)."""
         st, p = self._st(), L.ptr
         decay = 1.0 - lr * lam
         if self.adam is not None:
             # TF Adam is dense (tf_util.py:18-21): per-row gradients into G, then one sweep over table | G | m | v with the L2
             # term's gradient lam * theta folded in (FM.py:39, LR.py:37); the bias the same way
             b1, b2, eps = self.adam
-            L.call("dctr_adam_tick", p(self.adam_state), float(lr), b1, b2, st)
             L.call("dctr_scatter_grad_fm", rows, pos, M, self.F, self.d, g, s, self.lds, wts, p(self.table), self.X, self.ld,
                    p(self.table_g), p(ws), ws.numel(), st)
             L.call("dctr_dense_adam", p(self.table), p(self.table_g), p(self.table_m), p(self.table_v), self.X * self.ld,
                    p(self.adam_state), b1, b2, eps, float(lam), 1, st)
-            L.call("dctr_dense_adam", p(self.params), p(self.grads), p(self.params_m), p(self.params_v), 4,
-                   p(self.adam_state), b1, b2, eps, float(lam), 0, st)
             return
         L.call("dctr_scatter_sgd_fm", rows, pos, M, self.F, self.d, g, s, self.lds, wts, float(lr), float(decay),
                p(self.table), self.X, self.ld, p(ws), ws.numel(), st)
         if lam != 0.0 and dense_l2:   # FM.py:39: the L2 term reaches every row, touched or not
             L.call("dctr_decay_sweep", p(self.table), self.X, self.ld, float(decay), rows, M, st)
-        L.call("dctr_dense_sgd", p(self.params), p(self.grads), 1, float(lr), float(decay), st)
