@@ -214,6 +214,9 @@ def call_cost(name, a):
 NCU_TRAFFIC = {
     ("fnn_criteo", "dctr_gemm_tc[NN 65536x400x430]"): 114.06e6 + 70.96e6,      # profiles/r01_ncu_criteo_gemm_tc_kernel_v2.txt
     ("fnn_criteo", "dctr_col_wsum"): 109.07e6 + 4.51e6,                       # profiles/r01_ncu_criteo_col_wsum_kernel.txt
+    # hist + 2 wide passes at M = 65536: the lists live in L2, only cold reads reach DRAM (profiles/r01_ncu_fnn_sort_kernels_step_size.txt)
+    ("fnn_ipinyou", "dctr_sort_rows"): 285.95e3 + 321.79e3 + 577.28e3,
+    ("fm_ipinyou", "dctr_sort_rows"): 285.95e3 + 321.79e3 + 577.28e3,
     ("emb", "gather_concat_fwd"): 257.25e6 + 698.65e6,                        # profiles/r01_ncu_emb_gather_concat_kernel.txt
     ("emb", "fm_fwd"): 234.24e6 + 51.89e6,                                    # profiles/r01_ncu_emb_fm_fwd_kernel.txt
     ("emb", "scatter_sgd[sum]"): 4371.56e6 + 40.12e6,                         # profiles/r01_ncu_emb_fold_tile_kernel.txt
