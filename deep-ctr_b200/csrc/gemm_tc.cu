@@ -204,6 +204,24 @@ __device__ __forceinline__ void tc_store_rows(const TcParams& p, float* __restri
     if (m >= p.M) return;
     float* dst = C + (int64_t)m * p.ldc + nbase;
     const int nlast = p.N - 1;
+    // dgrad: this row's 32 stored activations, fetched up front as 128-bit loads where the row allows it (a scalar load
+    // per element costs 32 wavefronts per warp instruction here, lanes being rows)
+    float ax[32];
+    if (EPI == DCTR_EPI_DGRAD) {
+        const float* arow = p.aux + (int64_t)m * p.ldaux;
+        const bool vec = ((p.ldaux & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.aux) & 15) == 0);
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+            const int n = nbase + j;
+            if (vec && n + 3 <= nlast) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(arow + n));
+                ax[j] = t.x; ax[j + 1] = t.y; ax[j + 2] = t.z; ax[j + 3] = t.w;
+            } else {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) ax[j + c] = __ldg(arow + min(n + c, nlast));
+            }
+        }
+    }
 #pragma unroll
     for (int j = 0; j < 32; j += 4) {
         const int n = nbase + j;
@@ -211,8 +229,7 @@ __device__ __forceinline__ void tc_store_rows(const TcParams& p, float* __restri
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             const int nn = min(n + c, nlast);
-            const float ax = EPI == DCTR_EPI_DGRAD ? __ldg(p.aux + (int64_t)m * p.ldaux + nn) : 0.f;
-            o[c] = tc_epi1<EPI, ACT>(p, m, nn, v[j + c], ax);
+            o[c] = tc_epi1<EPI, ACT>(p, m, nn, v[j + c], EPI == DCTR_EPI_DGRAD ? ax[j + c] : 0.f);
         }
         if (n + 3 < p.N) *reinterpret_cast<float4*>(dst + j) = make_float4(o[0], o[1], o[2], o[3]);
         else {
