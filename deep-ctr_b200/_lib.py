@@ -49,6 +49,7 @@ SIGNATURES = {
     "dctr_set_launch_mode": (_i, [_i]),
     "dctr_eval_metrics_workspace": (_z, [_l]),
     "dctr_eval_metrics": (_i, [_p, _p, _l, _p, _p, _z, _p]),
+    "dctr_out_unit_train": (_i, [_p, _i, _i, _i, _p, _p, _p, _f, _i, _p, _i, _p, _p, _p, _p, _f, _p, _p, _i, _p, _p, _p, _z, _p]),
     "dctr_dense_sgd": (_i, [_p, _p, _l, _f, _f, _p]),
     "dctr_adam_tick": (_i, [_p, _f, _f, _f, _p]),
     "dctr_dense_adam": (_i, [_p, _p, _p, _p, _l, _p, _f, _f, _f, _f, _i, _p]),

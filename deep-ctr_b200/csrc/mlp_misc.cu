@@ -105,6 +105,76 @@ out_xent_fwd_kernel(const float* __restrict__ a, int lda, int N, int H, const fl
     ordered_reduce(partial, (int)gridDim.x, 1, 1, [&](int, float s) { loss_sum[0] = s * loss_scale; });
 }
 
+// Output unit of a TRAIN step in one pass over the last activation (FNN.py:54-63 + its autodiff): logit, pred, loss, dlogit,
+// d(activation), d(w_out), d(b_out).  A warp owns rows n = w, w + W, ...: the row stays in registers between the GEMV
+// and the backward; per-lane partial sums of dlogit * a over the warp's rows, then warps in order (shared memory), then
+// CTAs in order (last-ticket CTA): fixed order, no float atomics.  HV = ceil(H / 32) register columns per lane.
+template <int HV>
+__global__ void __launch_bounds__(256)
+out_unit_train_kernel(const float* __restrict__ a, int lda, int N, int H, const float* __restrict__ w, const float* __restrict__ b,
+                      const float* __restrict__ y, float gscale, int act, const float* __restrict__ mask, int ldmask,
+                      float* __restrict__ logit, float* __restrict__ pred, float* __restrict__ loss_n, float* __restrict__ dlogit,
+                      float loss_scale, float* __restrict__ loss_sum, float* __restrict__ da, int ldda,
+                      float* __restrict__ gw, float* __restrict__ gb, float* __restrict__ partial, unsigned* __restrict__ ticket) {
+    pdl_sync();
+    constexpr int WC = HV * 32 + 2;                       // gw columns | gb | loss
+    extern __shared__ float s_red[];                      // [8][WC]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t gwarp = (int64_t)blockIdx.x * 8 + warp, nwarps = (int64_t)gridDim.x * 8;
+    const float bv = b ? __ldg(b) : 0.f;
+    float wreg[HV], gacc[HV];
+#pragma unroll
+    for (int k = 0; k < HV; ++k) { const int h = lane + 32 * k; wreg[k] = h < H ? __ldg(w + h) : 0.f; gacc[k] = 0.f; }
+    float gbacc = 0.f, lacc = 0.f;
+    for (int64_t n = gwarp; n < N; n += nwarps) {
+        const float* row = a + n * lda;
+        float av[HV], acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < HV; ++k) { const int h = lane + 32 * k; av[k] = h < H ? row[h] : 0.f; acc = fmaf(av[k], wreg[k], acc); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        const float z = acc + bv, p = sigmoidf_(z), yn = y[n];
+        const float ln = xent_logits(z, yn), dl = (p - yn) * gscale;
+        if (lane == 0) {
+            if (logit) logit[n] = z;
+            if (pred) pred[n] = p;
+            if (loss_n) loss_n[n] = ln;
+            if (dlogit) dlogit[n] = dl;
+        }
+        lacc += ln;
+        gbacc += dl;
+        float* drow = da + n * ldda;
+#pragma unroll
+        for (int k = 0; k < HV; ++k) {
+            const int h = lane + 32 * k;
+            if (h < H) {
+                gacc[k] = fmaf(dl, av[k], gacc[k]);
+                const float mk = mask ? __ldg(mask + n * ldmask + h) : 1.f;
+                drow[h] = mk != 0.f ? dl * wreg[k] * mk * act_bwd_from_out(act, mask ? av[k] / mk : av[k]) : 0.f;
+            }
+        }
+    }
+    float* mine = s_red + warp * WC;
+#pragma unroll
+    for (int k = 0; k < HV; ++k) mine[lane + 32 * k] = gacc[k];
+    if (lane == 0) { mine[HV * 32] = gbacc; mine[HV * 32 + 1] = lacc; }
+    __syncthreads();
+    const int W = H + 2;
+    for (int c = threadIdx.x; c < W; c += 256) {
+        const int src = c < H ? c : HV * 32 + (c - H);
+        float s = 0.f;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) s += s_red[q * WC + src];
+        partial[(int64_t)blockIdx.x * W + c] = s;
+    }
+    if (!take_last_ticket(ticket, gridDim.x)) return;
+    ordered_reduce(partial, (int)gridDim.x, W, W, [&](int c, float s) {
+        if (c < H) gw[c] = s;
+        else if (c == H) gb[0] = s;
+        else if (loss_sum) loss_sum[0] = s * loss_scale;
+    });
+}
+
 __global__ void __launch_bounds__(256)
 out_bwd_kernel(const float* __restrict__ dlogit, const float* __restrict__ w, const float* __restrict__ a, int lda,
                int N, int H, int act, const float* __restrict__ mask, int ldmask, float* __restrict__ da, int ldda) {
@@ -462,4 +532,38 @@ extern "C" int dctr_dense_adam(float* param, float* grad, float* m, float* v, in
     if (zero_grad) launch_k(dense_adam_kernel<true>, blocks, 256, 0, as_stream(stream), p4, g4, m4, v4, n / 4, state, beta1, beta2, eps, l2);
     else launch_k(dense_adam_kernel<false>, blocks, 256, 0, as_stream(stream), p4, g4, m4, v4, n / 4, state, beta1, beta2, eps, l2);
     return check_launch("dense_adam_kernel");
+}
+
+extern "C" int dctr_out_unit_train(const float* a, int lda, int N, int H, const float* w, const float* b, const float* y,
+                                   float gscale, int act, const float* mask, int ldmask, float* logit, float* pred,
+                                   float* loss_n, float* dlogit, float loss_scale, float* loss_sum, float* da, int ldda,
+                                   float* gw, float* gb, void* workspace, size_t workspace_bytes, void* stream) {
+    DCTR_REQUIRE(a && w && y && da && gw && gb && workspace && N > 0 && H > 0 && H <= 1024 && lda >= H && ldda >= H,
+                 "out_unit_train: bad arguments (H <= 1024)");
+    if (workspace_bytes < dctr_reduce_workspace(N, H + 1)) {
+        set_error("out_unit_train: workspace %zu < %zu", workspace_bytes, dctr_reduce_workspace(N, H + 1));
+        return DCTR_EWORKSPACE;
+    }
+    int blocks = ceil_div(N, 32);                          // >= 4 rows per warp
+    if (blocks > kNumSMs * 2) blocks = kNumSMs * 2;
+    unsigned* ticket = static_cast<unsigned*>(workspace);
+    float* partial = reinterpret_cast<float*>(static_cast<char*>(workspace) + kRedHeader);
+    cudaStream_t st = as_stream(stream);
+#define DCTR_OUT_TRAIN(HVV)                                                                                                \
+    do {                                                                                                                   \
+        const size_t smem = (size_t)8 * (HVV * 32 + 2) * sizeof(float);                                                    \
+        static bool attr = false;                                                                                          \
+        if (!attr && smem > 48 * 1024) {                                                                                   \
+            cudaFuncSetAttribute(out_unit_train_kernel<HVV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);      \
+            attr = true;                                                                                                   \
+        }                                                                                                                  \
+        launch_k(out_unit_train_kernel<HVV>, blocks, 256, smem, st, a, lda, N, H, w, b, y, gscale, act, mask, ldmask, logit, \
+                 pred, loss_n, dlogit, loss_scale, loss_sum, da, ldda, gw, gb, partial, ticket);                           \
+    } while (0)
+    if (H <= 128) DCTR_OUT_TRAIN(4);
+    else if (H <= 256) DCTR_OUT_TRAIN(8);
+    else if (H <= 512) DCTR_OUT_TRAIN(16);
+    else DCTR_OUT_TRAIN(32);
+#undef DCTR_OUT_TRAIN
+    return check_launch("out_unit_train_kernel");
 }

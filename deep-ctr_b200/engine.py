@@ -94,13 +94,15 @@ class StepEngine:
             ws_elems = max(ws_elems, s * K * self.ldw[l])
         self.splitk_ws = torch.zeros(ws_elems, **f32)
         # workspace of the single-launch reductions (ticket + CTA partials): zero-filled once, left zeroed by the kernels
-        self.col_ws = torch.zeros(L.lib().dctr_reduce_workspace(N, maxw), dtype=torch.uint8, device=self.dev)
+        self.col_ws = torch.zeros(L.lib().dctr_reduce_workspace(N, maxw + 4), dtype=torch.uint8, device=self.dev)
         self.col_ws2 = torch.zeros_like(self.col_ws)           # reductions issued from the weight-gradient stream
         self.side = torch.cuda.Stream(device=self.dev)
         self.side2 = torch.cuda.Stream(device=self.dev)
         self.overlap_wgrad = True
         self._wgrad_pending = False
         self.adam = None
+        self.fuse_out_unit = True
+        self._out_unit_done = False
         # programmatic dependent launch pays when the step is a chain of short kernels (measured: neutral at N = 4096 with the
         # weight-gradient stream, -3 % at N = 65536 where parked CTAs take SMs from the concurrent streams)
         self.launch_mode = 2 if self.N <= 8192 else 0
@@ -168,6 +170,16 @@ class StepEngine:
                    p(self.W(l)), self.ldw[l], p(self.ins[l + 1]), self.ldi[l + 1], L.EPI_FWD, L.ACT[self.act],
                    p(self.b(l)), None, 0, mp, mld, 1, st)
         last = self.nl - 1
+        self._out_unit_done = False
+        if with_loss and self.widths[last] <= 1024 and self.fuse_out_unit:
+            # train step: the output unit forward AND backward in one pass over the last activation
+            mp, mld = self._mask(last)
+            L.call("dctr_out_unit_train", p(self.ins[last]), self.ldi[last], N, self.widths[last], p(self.W(last)),
+                   p(self.b(last)), p(self.y), float(gscale), L.ACT[self.act], mp, mld, p(self.logit), p(self.pred),
+                   p(self.loss_n), p(self.dlogit), float(gscale), p(self.loss), p(self.dbuf[0]), self.dbuf[0].stride(0),
+                   p(self.W(last, self.grads)), p(self.b(last, self.grads)), p(self.col_ws), self.col_ws.numel(), st)
+            self._out_unit_done = True
+            return
         # logit / pred / per-sample loss / dlogit and the reduced loss in one launch
         L.call("dctr_out_xent_fwd", p(self.ins[last]), self.ldi[last], N, self.widths[last], p(self.W(last)),
                p(self.b(last)), p(self.y) if with_loss else None, float(gscale), p(self.logit), p(self.pred),
@@ -184,10 +196,12 @@ class StepEngine:
         cur = 0
         mp, mld = self._mask(last)
         ldd = self.dbuf[0].stride(0)
-        # d(last hidden), d w_out and d b_out in one launch
-        L.call("dctr_out_bwd_fused", p(self.dlogit), p(self.W(last)), p(self.ins[last]), self.ldi[last], N, H,
-               L.ACT[self.act], mp, mld, p(self.dbuf[cur]), ldd, p(self.W(last, self.grads)), p(self.b(last, self.grads)),
-               cw, cwb, st)
+        # d(last hidden), d w_out and d b_out in one launch (unless the forward already produced them)
+        if not self._out_unit_done:
+            L.call("dctr_out_bwd_fused", p(self.dlogit), p(self.W(last)), p(self.ins[last]), self.ldi[last], N, H,
+                   L.ACT[self.act], mp, mld, p(self.dbuf[cur]), ldd, p(self.W(last, self.grads)), p(self.b(last, self.grads)),
+                   cw, cwb, st)
+        self._out_unit_done = False
         # Per layer, the weight/bias gradients (TN GEMM [+ split-K fold], column sum) only need dz_l, as does the data
         # gradient that continues the chain: they run on a second stream next to it (three rotating dz buffers, so the
         # chain is two layers ahead before it overwrites what a weight-gradient GEMM still reads).

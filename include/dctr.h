@@ -188,6 +188,15 @@ int dctr_out_bwd(const float* dlogit, const float* w, const float* a, int lda, i
 int dctr_out_bwd_fused(const float* dlogit, const float* w, const float* a, int lda, int N, int H, int act,
                        const float* mask, int ldmask, float* da, int ldda, float* gw, float* gb,
                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* The whole output unit of a TRAIN step in one pass over the last activation a [N, H] (H <= 1024): what dctr_out_xent_fwd
+ * (with y and loss_sum) followed by dctr_out_bwd_fused computes -- logit / pred / loss_n / dlogit (each may be NULL),
+ * loss_sum = loss_scale * sum loss_n (may be NULL), da, gw [H], gb [1].  workspace: dctr_reduce_workspace(N, H + 1) bytes,
+ * zero-filled once.  Fixed summation order (rows per warp, warps per CTA, CTAs by ticket). */
+int dctr_out_unit_train(const float* a, int lda, int N, int H, const float* w, const float* b, const float* y,
+                        float gscale, int act, const float* mask, int ldmask, float* logit, float* pred,
+                        float* loss_n, float* dlogit, float loss_scale, float* loss_sum, float* da, int ldda,
+                        float* gw, float* gb, void* workspace, size_t workspace_bytes, void* stream);
 /*   out[h] = sum_n (wv? wv[n]:1) * A[n,h]   single-launch fixed-order column reduction (bias / last-layer grads);
  *   workspace: dctr_col_wsum_workspace(N,H) bytes, zero-filled once */
 size_t dctr_col_wsum_workspace(int N, int H);

@@ -475,6 +475,52 @@ def test_eval_metrics_vs_sklearn(L, N, ties, pos_rate):
     np.testing.assert_allclose(g["rmse"], np.sqrt(mean_squared_error(y, p.astype(np.float64))), rtol=1e-10, atol=1e-12)
 
 
+@pytest.mark.parametrize("N,H,mask_kind", [(1, 1, None), (37, 50, "row"), (4096, 100, "row"), (5000, 129, "full"), (70000, 400, None),
+                                           (300, 1000, "full"), (2049, 1024, None)])
+def test_out_unit_train_equals_two_kernel_path(L, N, H, mask_kind):
+    """dctr_out_unit_train == dctr_out_xent_fwd + dctr_out_bwd_fused (each checked against the oracle above): same logit /
+    pred / loss / dlogit bit for bit (same GEMV order is not promised: rtol 1e-6), da, gw, gb at reduction tolerance"""
+    rng = np.random.default_rng(N * 7 + H)
+    ld = r4(H)
+    act_out = np.tanh(rng.normal(0, 1, (N, ld))).astype(np.float32)
+    mask = None
+    if mask_kind == "row":
+        mask = ((rng.random((1, ld)) < 0.6) * 2.0).astype(np.float32)
+    elif mask_kind == "full":
+        mask = ((rng.random((N, ld)) < 0.7) / 0.7).astype(np.float32)
+    stored = act_out * (mask if mask is not None else 1.0)
+    stored[:, H:] = 0
+    w = rng.normal(0, 0.3, H).astype(np.float32)
+    y = rng.integers(0, 2, N).astype(np.float32)
+    sd, wd, yd, bd = dev(stored.astype(np.float32)), dev(w), dev(y), dev(np.array([0.1], np.float32))
+    md = dev(mask) if mask is not None else None
+    ldm = 0 if mask_kind == "row" else ld
+    ws = torch.zeros(L.lib().dctr_reduce_workspace(N, H + 1), dtype=torch.uint8, device="cuda")
+    z = lambda *s: torch.zeros(*s, device="cuda")
+    ref = dict(logit=z(N), pred=z(N), loss_n=z(N), dl=z(N), loss=z(1), da=z(N, ld), gw=z(H), gb=z(1))
+    L.call("dctr_out_xent_fwd", sd.data_ptr(), ld, N, H, wd.data_ptr(), bd.data_ptr(), yd.data_ptr(), 0.5, ref["logit"].data_ptr(),
+           ref["pred"].data_ptr(), ref["loss_n"].data_ptr(), ref["dl"].data_ptr(), 0.5, ref["loss"].data_ptr(), ws.data_ptr(), ws.numel(), None)
+    L.call("dctr_out_bwd_fused", ref["dl"].data_ptr(), wd.data_ptr(), sd.data_ptr(), ld, N, H, L.ACT["tanh"], L.ptr(md), ldm,
+           ref["da"].data_ptr(), ld, ref["gw"].data_ptr(), ref["gb"].data_ptr(), ws.data_ptr(), ws.numel(), None)
+    runs = []
+    for rep in range(2):
+        got = dict(logit=z(N), pred=z(N), loss_n=z(N), dl=z(N), loss=z(1), da=z(N, ld), gw=z(H), gb=z(1))
+        L.call("dctr_out_unit_train", sd.data_ptr(), ld, N, H, wd.data_ptr(), bd.data_ptr(), yd.data_ptr(), 0.5, L.ACT["tanh"],
+               L.ptr(md), ldm, got["logit"].data_ptr(), got["pred"].data_ptr(), got["loss_n"].data_ptr(), got["dl"].data_ptr(), 0.5,
+               got["loss"].data_ptr(), got["da"].data_ptr(), ld, got["gw"].data_ptr(), got["gb"].data_ptr(), ws.data_ptr(), ws.numel(), None)
+        torch.cuda.synchronize()
+        runs.append({k: v.cpu().numpy().copy() for k, v in got.items()})
+    for k in runs[0]:
+        assert np.array_equal(runs[0][k], runs[1][k]), k            # deterministic, ticket reset
+    tol = 2e-6 * np.sqrt(N) * 4
+    for k in ("logit", "pred", "loss_n", "dl"):
+        close(runs[0][k], ref[k].cpu(), rtol=2e-6, atol=2e-6)
+    close(runs[0]["loss"], ref["loss"].cpu(), rtol=1e-5, atol=tol)
+    close(runs[0]["da"][:, :H], ref["da"].cpu().numpy()[:, :H], rtol=1e-5, atol=1e-6)
+    close(runs[0]["gw"], ref["gw"].cpu(), rtol=1e-5, atol=tol)
+    close(runs[0]["gb"], ref["gb"].cpu(), rtol=1e-5, atol=tol)
+
+
 def test_empty_inputs(L):
     # N = 0 / M = 0 are accepted and launch nothing
     before = L.launch_count()
