@@ -53,6 +53,7 @@ SIGNATURES = {
     "dctr_dense_sgd": (_i, [_p, _p, _l, _f, _f, _p]),
     "dctr_adam_tick": (_i, [_p, _f, _f, _f, _p]),
     "dctr_dense_adam": (_i, [_p, _p, _p, _p, _l, _p, _f, _f, _f, _f, _i, _p]),
+    "dctr_dense_ftrl": (_i, [_p, _p, _p, _p, _l, _f, _f, _f, _f, _f, _i, _p]),
 }
 
 _lib = None

@@ -391,6 +391,44 @@ __global__ void dense_adam_kernel(float4* __restrict__ p, float4* __restrict__ g
     }
 }
 
+// ---- FTRL-proximal, TensorFlow's ApplyFtrl form (tf_util.py:22-24 FtrlOptimizer(lr): lr_power -0.5, accumulators start at
+// 0.1, l1 = l2 = 0).  Dense like Adam: an element whose gradient is 0 keeps accum / linear and is RE-DERIVED from linear, so
+// a weight that never saw a gradient goes to 0 on the first step (linear starts at 0) -- TF's behaviour, kept.
+__device__ __forceinline__ void ftrl1(float& p, float g, float& n, float& z, float lr_inv, float lr_power, float l1, float l2,
+                                      float gl2) {
+    g = fmaf(gl2, p, g);
+    const float n_new = fmaf(g, g, n);
+    float s_new, ds;
+    if (lr_power == -0.5f) {      // sqrt(n + g^2) - sqrt(n) = g^2 / (sqrt(n + g^2) + sqrt(n)): no cancellation for small g
+        const float s_old = sqrtf(n);
+        s_new = sqrtf(n_new);
+        ds = s_new + s_old > 0.f ? g * g / (s_new + s_old) : 0.f;
+    } else {
+        s_new = powf(n_new, -lr_power);
+        ds = s_new - powf(n, -lr_power);
+    }
+    z += g - ds * lr_inv * p;
+    const float quad = fmaf(s_new, lr_inv, 2.f * l2);
+    const float sgn = z > 0.f ? 1.f : (z < 0.f ? -1.f : 0.f);
+    p = fabsf(z) > l1 ? (l1 * sgn - z) / quad : 0.f;
+    n = n_new;
+}
+
+template <bool ZERO>
+__global__ void dense_ftrl_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__ n, float4* __restrict__ z,
+                                  int64_t n4, float lr_inv, float lr_power, float l1, float l2, float gl2) {
+    pdl_sync();
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        float4 pp = p[i], gg = g[i], nn = n[i], zz = z[i];
+        ftrl1(pp.x, gg.x, nn.x, zz.x, lr_inv, lr_power, l1, l2, gl2);
+        ftrl1(pp.y, gg.y, nn.y, zz.y, lr_inv, lr_power, l1, l2, gl2);
+        ftrl1(pp.z, gg.z, nn.z, zz.z, lr_inv, lr_power, l1, l2, gl2);
+        ftrl1(pp.w, gg.w, nn.w, zz.w, lr_inv, lr_power, l1, l2, gl2);
+        p[i] = pp; n[i] = nn; z[i] = zz;
+        if (ZERO) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
 // Shape of a column reduction: V = 4 when every row start is 16-byte aligned, TX = the narrowest power of two covering
 // the columns (<= 32), enough row chunks for ~4 CTAs per SM but at least 4 rows per row lane and chunk.
 constexpr int kRedHeader = 1024;                       // bytes: one ticket per column tile
@@ -532,6 +570,22 @@ extern "C" int dctr_dense_adam(float* param, float* grad, float* m, float* v, in
     if (zero_grad) launch_k(dense_adam_kernel<true>, blocks, 256, 0, as_stream(stream), p4, g4, m4, v4, n / 4, state, beta1, beta2, eps, l2);
     else launch_k(dense_adam_kernel<false>, blocks, 256, 0, as_stream(stream), p4, g4, m4, v4, n / 4, state, beta1, beta2, eps, l2);
     return check_launch("dense_adam_kernel");
+}
+
+extern "C" int dctr_dense_ftrl(float* param, float* grad, float* accum, float* linear, int64_t n, float lr, float lr_power,
+                               float l1, float l2, float grad_l2, int zero_grad, void* stream) {
+    DCTR_REQUIRE(param && grad && accum && linear && n >= 0 && (n & 3) == 0, "dense_ftrl: null pointer or n not a multiple of 4");
+    DCTR_REQUIRE(((((uintptr_t)param) | ((uintptr_t)grad) | ((uintptr_t)accum) | ((uintptr_t)linear)) & 15) == 0,
+                 "dense_ftrl: buffers must be 16-byte aligned");
+    DCTR_REQUIRE(lr > 0.f && lr_power <= 0.f && l1 >= 0.f && l2 >= 0.f, "dense_ftrl: lr > 0, lr_power <= 0, l1 >= 0, l2 >= 0");
+    if (n == 0) return DCTR_OK;
+    int blocks = ceil_div(n / 4, 256);
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    float4 *p4 = reinterpret_cast<float4*>(param), *g4 = reinterpret_cast<float4*>(grad), *n4 = reinterpret_cast<float4*>(accum),
+           *z4 = reinterpret_cast<float4*>(linear);
+    if (zero_grad) launch_k(dense_ftrl_kernel<true>, blocks, 256, 0, as_stream(stream), p4, g4, n4, z4, n / 4, 1.f / lr, lr_power, l1, l2, grad_l2);
+    else launch_k(dense_ftrl_kernel<false>, blocks, 256, 0, as_stream(stream), p4, g4, n4, z4, n / 4, 1.f / lr, lr_power, l1, l2, grad_l2);
+    return check_launch("dense_ftrl_kernel");
 }
 
 extern "C" int dctr_out_unit_train(const float* a, int lda, int N, int H, const float* w, const float* b, const float* y,

@@ -243,7 +243,7 @@ class ShardedStep(object):
         L.call("dctr_gather_rows", L.ptr(self.perm), L.ptr(self.ge), e.M, e.ldg, e.M, L.ptr(send_g), st)
         recv_g = all_to_all_rows(dist, send_g, sc, rc, self.group)       # aligned with recv_rows
         R = recv_rows.shape[0]
-        if R == 0 and e.adam is not None:      # dense Adam moves every local row even when no gradient arrived
+        if R == 0 and e.dense_optimizer:      # dense Adam / FTRL moves every local row even when no gradient arrived
             e.table_update(None, None, 0, 1, L.ptr(recv_g), e.ldg, e.ldg, None, lr, decay, e.scat_ws)
         if R > 0:
             i32 = dict(dtype=torch.int32, device=e.dev)

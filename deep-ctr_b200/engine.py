@@ -101,6 +101,7 @@ class StepEngine:
         self.overlap_wgrad = True
         self._wgrad_pending = False
         self.adam = None
+        self.ftrl = None
         self.fuse_out_unit = True
         self._out_unit_done = False
         # programmatic dependent launch pays when the step is a chain of short kernels (measured: neutral at N = 4096 with the
@@ -279,6 +280,13 @@ class StepEngine:
             L.call("dctr_dense_adam", p(self.table), p(self.table_g), p(self.table_m), p(self.table_v), self.X * self.ld,
                    p(self.adam_state), b1, b2, eps, 0.0, 1, st)
             return
+        if self.ftrl is not None:
+            lr_power, l1, l2 = self.ftrl
+            L.call("dctr_scatter_sgd", self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_n, g_ld_f, w, -1.0, 1.0,
+                   p(self.table_g), self.X, self.ld, p(ws), ws.numel(), st)
+            L.call("dctr_dense_ftrl", p(self.table), p(self.table_g), p(self.table_n), p(self.table_z), self.X * self.ld,
+                   float(lr), lr_power, l1, l2, 0.0, 1, st)
+            return
         L.call("dctr_scatter_sgd", self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_n, g_ld_f, w, float(lr), float(decay),
                p(self.table), self.X, self.ld, p(ws), ws.numel(), st)
 
@@ -294,6 +302,21 @@ class StepEngine:
         self.table_g, self.table_m, self.table_v = (torch.zeros_like(self.table) for _ in range(3))
         self.params_m, self.params_v = torch.zeros_like(self.grads), torch.zeros_like(self.grads)
 
+    def enable_ftrl(self, init_accum=0.1, lr_power=-0.5, l1=0.0, l2=0.0):
+        """Switch the step to TensorFlow's FtrlOptimizer(lr) over the table AND the MLP (tf_util.py:22-24; TF defaults).  Dense
+        for the same reason as Adam: the fold writes per-row gradient sums into G, one streaming dctr_dense_ftrl pass over
+        table | G | accum | linear applies the update and clears G."""
+        assert self.scatter_mode == L.SCATTER_SUM, "FTRL belongs to the TF-form models (SUM scatter)"
+        self.ftrl = (float(lr_power), float(l1), float(l2))
+        self.table_g, self.table_z = torch.zeros_like(self.table), torch.zeros_like(self.table)
+        self.table_n = torch.full_like(self.table, float(init_accum))
+        self.params_n, self.params_z = torch.full_like(self.grads, float(init_accum)), torch.zeros_like(self.grads)
+
+    @property
+    def dense_optimizer(self):
+        """True when the table update is a dense sweep (Adam / FTRL): every row moves even without a gradient."""
+        return self.adam is not None or self.ftrl is not None
+
     def join_wgrad(self):
         """self.grads is complete on the current stream after this (weight gradients run on a side stream)."""
         if self._wgrad_pending:
@@ -307,6 +330,11 @@ class StepEngine:
             b1, b2, eps = self.adam
             L.call("dctr_dense_adam", L.ptr(self.params), L.ptr(self.grads), L.ptr(self.params_m), L.ptr(self.params_v),
                    self.n_params, L.ptr(self.adam_state), b1, b2, eps, 0.0, 0, st)
+            return
+        if self.ftrl is not None:
+            lr_power, l1, l2 = self.ftrl
+            L.call("dctr_dense_ftrl", L.ptr(self.params), L.ptr(self.grads), L.ptr(self.params_n), L.ptr(self.params_z),
+                   self.n_params, float(lr), lr_power, l1, l2, 0.0, 0, st)
             return
         if last_decay == 1.0:
             L.call("dctr_dense_sgd", L.ptr(self.params), L.ptr(self.grads), self.n_params, float(lr), 1.0, st)
@@ -370,6 +398,7 @@ class FMEngine:
         self.side = torch.cuda.Stream(device=self.dev)
         self.overlap_sort = True
         self.adam = None
+        self.ftrl = None
         self.launch_mode = 1 if self.N <= 16384 else 0       # FM step = 10 short kernels: -9 % with dependent launches
         self.wts_are_ones = False
 
@@ -403,6 +432,16 @@ class FMEngine:
         self.table_g, self.table_m, self.table_v = (torch.zeros_like(self.table) for _ in range(3))
         self.params_m, self.params_v = torch.zeros_like(self.grads), torch.zeros_like(self.grads)
 
+    def enable_ftrl(self, init_accum=0.1, lr_power=-0.5, l1=0.0, l2=0.0):
+        self.ftrl = (float(lr_power), float(l1), float(l2))
+        self.table_g, self.table_z = torch.zeros_like(self.table), torch.zeros_like(self.table)
+        self.table_n = torch.full_like(self.table, float(init_accum))
+        self.params_n, self.params_z = torch.full_like(self.grads, float(init_accum)), torch.zeros_like(self.grads)
+
+    @property
+    def dense_optimizer(self):
+        return self.adam is not None or self.ftrl is not None
+
     def sort_ids(self):
         L.call("dctr_sort_rows", L.ptr(self.ids), self.M, self.X, L.ptr(self.sorted_rows), L.ptr(self.sorted_pos),
                L.ptr(self.sort_ws), self.sort_ws.numel(), self._st())
@@ -434,6 +473,10 @@ class FMEngine:
             L.call("dctr_adam_tick", p(self.adam_state), float(lr), b1, b2, st)
             L.call("dctr_dense_adam", p(self.params), p(self.grads), p(self.params_m), p(self.params_v), 4,
                    p(self.adam_state), b1, b2, eps, float(lam), 0, st)
+        elif self.ftrl is not None:
+            lr_power, l1, l2 = self.ftrl
+            L.call("dctr_dense_ftrl", p(self.params), p(self.grads), p(self.params_n), p(self.params_z), 4,
+                   float(lr), lr_power, l1, l2, float(lam), 0, st)
         else:
             L.call("dctr_dense_sgd", p(self.params), p(self.grads), 1, float(lr), float(1.0 - lr * lam), st)
 
@@ -450,6 +493,13 @@ class FMEngine:
                    p(self.table_g), p(ws), ws.numel(), st)
             L.call("dctr_dense_adam", p(self.table), p(self.table_g), p(self.table_m), p(self.table_v), self.X * self.ld,
                    p(self.adam_state), b1, b2, eps, float(lam), 1, st)
+            return
+        if self.ftrl is not None:
+            lr_power, l1, l2 = self.ftrl
+            L.call("dctr_scatter_grad_fm", rows, pos, M, self.F, self.d, g, s, self.lds, wts, p(self.table), self.X, self.ld,
+                   p(self.table_g), p(ws), ws.numel(), st)
+            L.call("dctr_dense_ftrl", p(self.table), p(self.table_g), p(self.table_n), p(self.table_z), self.X * self.ld,
+                   float(lr), lr_power, l1, l2, float(lam), 1, st)
             return
         L.call("dctr_scatter_sgd_fm", rows, pos, M, self.F, self.d, g, s, self.lds, wts, float(lr), float(decay),
                p(self.table), self.X, self.ld, p(ws), ws.numel(), st)

@@ -9,7 +9,7 @@ inside (pinned staging buffers), so a call is an end-to-end step.
 Deviations, all forced by the environment or by reference defects:
   * random init uses numpy Generator(PCG64(seed)) per variable instead of TF's Philox stream (Q11);
     parity runs always inject weights through the pickle path of `_init_argv[-1]` (tf_util.py:41-49);
-  * only plain SGD ('sgd') is on the fast path; 'adam' / 'ftrl' (tf_util.py:17-25) raise NotImplementedError;
+  * 'sgd', 'adam' and 'ftrl' (tf_util.py:15-29) all run on the device; Adam and FTRL are dense sweeps, as in TF;
   * FNN_OP_L3 sizes h1_w from the forward's true width F*d + d*d + 1 (Q2).
 """
 import os
@@ -100,14 +100,16 @@ def init_var_map(_init_argv, variables):
     return var_map, log
 
 
-def _optimizer(_ptmzr_argv, allow_adam=False):
-    """tf_util.py:15-29.  Returns (lr, log); `adam` is on the fast path for the FNN family."""
+def _optimizer(_ptmzr_argv, engine):
+    """builf_optimizer, tf_util.py:15-29: 'adam' -> AdamOptimizer(lr, epsilon), 'ftrl' -> FtrlOptimizer(lr) (TF defaults),
+    anything else -> GradientDescentOptimizer(lr).  Switches the engine and returns (lr, log)."""
     name = _ptmzr_argv[0]
-    if name == "adam" and allow_adam:
+    if name == "adam":
         lr, eps = _ptmzr_argv[1:3]
+        engine.enable_adam(eps=float(eps))
         return float(lr), "optimizer: %s, learning rate: %g, epsilon: %g" % (name, lr, eps)
-    if name in ("adam", "ftrl"):
-        raise NotImplementedError("optimizer %r is not on the B200 fast path for this model yet (SURVEY.md 8(f) f1)" % name)
+    if name == "ftrl":
+        engine.enable_ftrl()
     lr = _ptmzr_argv[1]
     return float(lr), "optimizer: %s, learning rate: %g" % (name, lr)
 
@@ -263,9 +265,7 @@ class FM(_Base):
         if mode == "train":
             self._lambda = float(_reg_argv[0])
             self._reduce = _ptmzr_argv[-1]
-            self.lr, log = _optimizer(_ptmzr_argv, allow_adam=True)
-            if _ptmzr_argv[0] == "adam":
-                self.engine.enable_adam(eps=float(_ptmzr_argv[2]))
+            self.lr, log = _optimizer(_ptmzr_argv, self.engine)
             self.log += "%s, lambda(l2): %g, reduce by: %s" % (log, self._lambda, self._reduce)
             self.eval_size = eval_size
             self.eval_id_hldr, self.eval_wts_hldr = Placeholder("eval_id"), Placeholder("eval_wts")
@@ -387,9 +387,7 @@ class _FNNBase(_Base):
         if mode == "train":
             self._keep_prob = float(_reg_argv[0])
             self._reduce = _ptmzr_argv[-1]
-            self.lr, log = _optimizer(_ptmzr_argv, allow_adam=True)
-            if _ptmzr_argv[0] == "adam":
-                eng.enable_adam(eps=float(_ptmzr_argv[2]))
+            self.lr, log = _optimizer(_ptmzr_argv, eng)
             self.log += "%s, reduce by: %s, keep_prob(drop_out): %g" % (log, self._reduce, self._keep_prob)
             self.eval_size = eval_size
             self.eval_id_hldr, self.eval_wts_hldr = Placeholder("eval_id"), Placeholder("eval_wts")

@@ -218,6 +218,17 @@ int dctr_adam_tick(float* state, float lr, float beta1, float beta2, void* strea
 int dctr_dense_adam(float* param, float* grad, float* m, float* v, int64_t n, const float* state, float beta1, float beta2,
                     float eps, float l2, int zero_grad, void* stream);
 
+/* FTRL-proximal in TensorFlow's ApplyFtrl form (tf_util.py:22-24 FtrlOptimizer(lr): lr_power = -0.5, accumulators start
+ * at 0.1, l1 = l2 = 0; TensorFlow itself is not under /root/reference, the update below is its published kernel).
+ * Elementwise over n floats (n % 4 == 0, 16-byte aligned buffers), accum > 0 on entry:
+ *   g += grad_l2 * p                                   (the loss's own L2 term, FM.py:39 / LR.py:37)
+ *   n' = accum + g^2;  linear += g - (n'^(-lr_power) - accum^(-lr_power)) / lr * p
+ *   p = |linear| > l1 ? (l1 * sign(linear) - linear) / (n'^(-lr_power) / lr + 2 * l2) : 0;  accum = n'
+ * Dense, as TF applies it to these models: an element with g = 0 is re-derived from `linear` alone, so a weight that has
+ * not seen a gradient yet becomes 0 on the first step.  zero_grad != 0 clears grad afterwards. */
+int dctr_dense_ftrl(float* param, float* grad, float* accum, float* linear, int64_t n, float lr, float lr_power,
+                    float l1, float l2, float grad_l2, int zero_grad, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -241,6 +241,30 @@ class OracleNet:
             self.bs[l] = upd(self.bs[l], dbs[l], st["bs"][l])
         return loss, sigmoid(logit)
 
+    def train_step_tf_ftrl(self, ids, wts, y, lr, masks=None, reduce="sum", init_accum=0.1, lr_power=-0.5, l1=0.0, l2=0.0):
+        """tf.train.FtrlOptimizer(lr).minimize(loss) over ALL variables (tf_util.py:22-24), dense like Adam (the table
+        gradient is densified, FNN.py:46-49): see ftrl_apply."""
+        y = np.asarray(y, dtype=self.dtype)
+        logit, cache = self.forward(ids, wts, masks)
+        N = len(y)
+        scale = 1.0 if reduce == "sum" else 1.0 / N
+        loss = xent_with_logits(logit, y).sum() * scale
+        dlogit = (sigmoid(logit) - y) * scale
+        dWs, dbs, dbias, ge, _ = self.backward(cache, dlogit)
+        if not hasattr(self, "_ftrl"):
+            z = lambda a: [np.full_like(np.asarray(a, dtype=self.dtype), init_accum), np.zeros_like(np.asarray(a, dtype=self.dtype))]
+            self._ftrl = dict(table=z(self.table), bias=z(np.asarray(self.bias)), Ws=[z(w) for w in self.Ws], bs=[z(b) for b in self.bs])
+        st = self._ftrl
+        kw = dict(lr_power=lr_power, l1=l1, l2=l2)
+        G = np.zeros_like(self.table)
+        np.add.at(G, ids.reshape(-1), ge.reshape(-1, self.d))
+        self.table[...] = ftrl_apply(self.table, G, st["table"], lr, **kw)
+        self.bias = float(ftrl_apply(np.asarray(self.bias, dtype=self.dtype), np.asarray(dbias, dtype=self.dtype), st["bias"], lr, **kw))
+        for l in range(len(self.Ws)):
+            self.Ws[l] = ftrl_apply(self.Ws[l], dWs[l], st["Ws"][l], lr, **kw)
+            self.bs[l] = ftrl_apply(self.bs[l], dbs[l], st["bs"][l], lr, **kw)
+        return loss, sigmoid(logit)
+
     # ---- Theano semantics (FNN_wnzh.py:172-182, 298-306) --------------------------------------------
     def train_step_theano(self, ids, y, lr, lambda_fm, masks=None, lambda1=0.0, faithful=False, closed_form=False):
         y = np.asarray(y, dtype=self.dtype)
@@ -303,6 +327,21 @@ def seq_decay_scatter_closed_form(table, ids, ge, lr, decay):
     acc = np.add.reduceat(g[order] * wgt[:, None], starts, axis=0)
     rows = srow[starts]
     table[rows] = table[rows] * (decay ** lens)[:, None] - lr * acc
+
+
+def ftrl_apply(theta, g, slots, lr, lr_power=-0.5, l1=0.0, l2=0.0):
+    """One dense FTRL-proximal update in TensorFlow's ApplyFtrl form -- what tf.train.FtrlOptimizer(lr) (tf_util.py:22-24)
+    runs: learning_rate_power -0.5, initial_accumulator_value 0.1, l1 = l2 = 0.  TensorFlow is not under /root/reference
+    (unpinned 0.x dependency); this is its published kernel:
+        n' = n + g^2;  z += g - (n'^(-p) - n^(-p)) / lr * theta;  theta = |z| > l1 ? (l1 sign(z) - z) / (n'^(-p)/lr + 2 l2) : 0
+    slots = [n, z], updated in place; returns the new theta.  Elements with g = 0 are re-derived from z alone."""
+    n, z = slots
+    n_new = n + g * g
+    z += g - (n_new ** (-lr_power) - n ** (-lr_power)) / lr * theta
+    quad = n_new ** (-lr_power) / lr + 2.0 * l2
+    out = np.where(np.abs(z) > l1, (l1 * np.sign(z) - z) / quad, 0.0)
+    n[...] = n_new
+    return out
 
 
 # --------------------------------------------------------------------------------------------------
@@ -388,6 +427,36 @@ class OracleFM:
         st["mb"] = beta1 * st["mb"] + (1 - beta1) * gb
         st["vb"] = beta2 * st["vb"] + (1 - beta2) * gb * gb
         self.b = self.b - lr_t * st["mb"] / (np.sqrt(st["vb"]) + eps)
+        return loss, sigmoid(z)
+
+
+    def train_step_ftrl(self, ids, wts, y, lr, lam=0.0, reduce="sum", init_accum=0.1, lr_power=-0.5, l1=0.0, l2=0.0):
+        """Same loss (FM.py:33-39, LR.py:30-37), minimised by tf.train.FtrlOptimizer(lr) (tf_util.py:22-24): dense over W, V
+        and b, the L2 term's gradient lam*theta included in g (see ftrl_apply)."""
+        x = np.asarray(wts, dtype=self.dtype)
+        y = np.asarray(y, dtype=self.dtype)
+        N, F = ids.shape
+        z, vx = self.logits(ids, x)
+        scale = 1.0 if reduce == "sum" else 1.0 / N
+        loss = xent_with_logits(z, y).sum() * scale
+        if lam:
+            loss += lam * 0.5 * ((self.table ** 2).sum() + self.b ** 2)
+        g = (sigmoid(z) - y) * scale
+        rows = self.table[ids]
+        grad = np.empty_like(rows)
+        grad[..., 0] = g[:, None] * x
+        grad[..., 1:] = g[:, None, None] * (x[..., None] * vx[:, None, :] - (x ** 2)[..., None] * rows[..., 1:])
+        dense = np.zeros_like(self.table)
+        np.add.at(dense, ids.reshape(-1), grad.reshape(N * F, -1))
+        dense += lam * self.table
+        gb = np.asarray(g.sum() + lam * self.b, dtype=self.dtype)
+        if not hasattr(self, "_ftrl"):
+            self._ftrl = dict(t=[np.full_like(self.table, init_accum), np.zeros_like(self.table)],
+                              b=[np.asarray(init_accum, dtype=self.dtype).copy(), np.asarray(0.0, dtype=self.dtype).copy()])
+        st = self._ftrl
+        kw = dict(lr_power=lr_power, l1=l1, l2=l2)
+        self.table[...] = ftrl_apply(self.table, dense, st["t"], lr, **kw)
+        self.b = self.dtype(ftrl_apply(np.asarray(self.b, dtype=self.dtype), gb, st["b"], lr, **kw))
         return loss, sigmoid(z)
 
 
