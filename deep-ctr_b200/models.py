@@ -199,6 +199,25 @@ class _Base(object):
         self._pre_step()
         return self._finish_step()
 
+    def _fetch_out(self):
+        self._out_pinned.copy_(self.engine.out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(self._out_np[self.N]), self._out_np[:self.N].copy()
+
+    def train_step_device(self, ids, wts, y):
+        """One train step from DEVICE-resident blocks (ingest.DeviceText.parse_*): int32 global ids [N, F], float32 weights
+        [N, F] (None = 1), float32 labels [N].  Nothing but pred | loss crosses the bus."""
+        d = self._stage.dev
+        d["ids"].copy_(ids)
+        if wts is None:
+            d["wts"].fill_(1.0)
+        else:
+            d["wts"].copy_(wts)
+        d["y"].copy_(y)
+        self._pre_step()
+        self._run_step()
+        return self._fetch_out()
+
     def _predict_chunks(self, ids, wts, out_dev=None):
         """Inference over E rows in chunks of the static batch (last chunk padded with row 0 / weight 0).  With `out_dev`
         (a float32 device tensor of E elements) the predictions stay on the device and nothing is copied back."""

@@ -145,6 +145,16 @@ class FNN_wnzh(_Base):
         self._pre_step()
         return self._finish_step()
 
+    def train_step_device(self, feats, y):
+        """train() from DEVICE-resident blocks (ingest.DeviceText.parse_sparse with J = 16, pad_id = -1): int32 feature ids
+        [N, 16], float32 labels [N]; only the two dropout masks go up and pred | loss come back."""
+        self.feats.copy_(feats)
+        self.engine.y.copy_(y)
+        self._pre_step()
+        self._upload_masks()
+        self._run_step()
+        return self._fetch_out()
+
     def _swap_masks(self, masks):
         old = self.engine.masks
         self.engine.masks = masks if masks is not None else [None] * self.engine.nl

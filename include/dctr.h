@@ -229,6 +229,36 @@ int dctr_dense_adam(float* param, float* grad, float* m, float* v, int64_t n, co
 int dctr_dense_ftrl(float* param, float* grad, float* accum, float* linear, int64_t n, float lr, float lr_power,
                     float l1, float l2, float grad_l2, int zero_grad, void* stream);
 
+/* ---- device-side ingestion of the reference's text formats -----------------------------------------
+ * The raw file bytes are uploaded as they are; these entry points replace the Python parsers on the step's critical path:
+ * linecache.getline + replace(':',' ').split() (get_fxy, FNN_wnzh.py:224-253), load_ipinyou_data (ipinyou.py:42-65) and
+ * get_fxy (baseline.py:190-198).  text: uint8 [nbytes] on the device, 16-byte aligned.
+ *
+ * dctr_text_index_lines: line_start[i] = byte offset of the i-th NON-EMPTY line (a byte that is not '\n' and follows a '\n'
+ * or the start of the buffer), in file order; n_lines[0] (device) = how many there are in total.  line_start has room for
+ * max_lines + 1 entries: entry min(n_lines, max_lines) bounds the last line that is kept (nbytes, or the start of the first
+ * line that did not fit).  workspace: dctr_text_index_workspace(nbytes) bytes, 8-byte aligned. */
+size_t dctr_text_index_workspace(int64_t nbytes);
+int dctr_text_index_lines(const uint8_t* text, int64_t nbytes, int64_t* line_start, int64_t max_lines, int64_t* n_lines,
+                          void* workspace, size_t workspace_bytes, void* stream);
+/* `y [skip tokens] id:val id:val ...` -- train.fm.txt (skip = 0: y = int(s[0]), ids at the odd positions, values ignored;
+ * FNN_wnzh.py:248-252) and *.yzx.txt (skip = 1: fields[2:], x.split(':')[0]; ipinyou.py:50-59).  Per line i < min(n_lines,
+ * max_lines):  y[i];  feats[i, j] = id of the j-th feature, wts[i, j] = 1 (values are forced to 1, ipinyou.py:55) for
+ * j < min(nnz, J);  the remaining slots get (pad_id, 0) -- pad_id = -1 feeds dctr_arrange_fields, pad_id = X_dim - 1 is the
+ * padding of ipinyou.py:58-59;  status[i] = nnz (may exceed J: the line was truncated), -1 for a whitespace-only line,
+ * -2 for a malformed token.  n_lines is read on the device (no host sync between indexing and parsing); wts may be NULL. */
+int dctr_text_parse_sparse(const uint8_t* text, int64_t nbytes, const int64_t* line_start, const int64_t* n_lines,
+                           int64_t max_lines, int skip, int J, int32_t pad_id, int32_t* feats, float* wts, float* y,
+                           int32_t* status, void* stream);
+/* `y \t n_1 .. n_K \t c_1 .. c_C` (Criteo indexed TSV written by clean.py:148-184, read by get_fxy, baseline.py:190-198),
+ * F = n_num + n_cat.  Output is the engines' [N, F] block (what dctr_host_pack_fields builds from the TF feed):
+ *   ids[i, k] = k, wts[i, k] = (float)(n_k / max_vals[k]) (double division, as Python's);  ids[i, n_num + j] =
+ *   c_j + offsets[j], wts = 1;  y[i];  status[i] = number of tab-separated fields (1 + F when well formed), -2 if a field is
+ *   empty or not a number.  offsets: int64 [n_cat], max_vals: double [n_num], both on the device. */
+int dctr_text_parse_criteo(const uint8_t* text, int64_t nbytes, const int64_t* line_start, const int64_t* n_lines,
+                           int64_t max_lines, int n_num, int n_cat, const int64_t* offsets, const double* max_vals,
+                           int32_t* ids, float* wts, float* y, int32_t* status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -105,3 +105,134 @@ def test_fnn_ftrl_steps(tmp_path, monkeypatch, gemm):
         close([loss], [oloss], 5e-5)
         close(preds, opreds, 1e-4)
         compare_state(model, net, 2e-4)
+
+
+# ---- f2: device-side text ingestion ------------------------------------------------------------------------------------
+def _fm_text(rng, n, F, X, ragged=True, crlf=False, blank_every=0):
+    lines = []
+    for i in range(n):
+        k = int(rng.integers(1, F + 1)) if ragged else F
+        ids = rng.integers(0, X, k)
+        sep = "  " if i % 7 == 3 else " "
+        lines.append("%d%s%s" % (rng.integers(0, 2), sep, sep.join("%d:%d" % (j, 1) for j in ids)))
+        if blank_every and i % blank_every == 0:
+            lines.append("")
+    eol = "\r\n" if crlf else "\n"
+    return eol.join(lines) + (eol if n % 2 else "")          # with and without a trailing newline
+
+
+@pytest.mark.parametrize("n,F,X,crlf,blank_every", [(1, 16, 100, False, 0), (33, 16, 10 ** 6, False, 5), (1000, 16, 2 ** 31 - 1, True, 0),
+                                                    (4097, 5, 50, False, 3)])
+def test_index_and_parse_fm_lines_bit_exact(L, n, F, X, crlf, blank_every):
+    """train.fm.txt lines (FNN_wnzh.py:248-252) parsed on the device == the reference parser, bit for bit: line count,
+    ids in order, padding, labels; ragged lines, double spaces, CRLF, empty lines, missing final newline"""
+    import text_oracle as T
+    from deepctr_b200.ingest import DeviceText
+    rng = np.random.default_rng(n)
+    text = _fm_text(rng, n, F, X, crlf=crlf, blank_every=blank_every)
+    lines = T.nonblank_lines(text)
+    dt = DeviceText(text.encode())
+    assert dt.n_lines == len(lines) == n
+    starts = np.cumsum([0] + [len(s) + 1 for s in text.split("\n")])[:-1]
+    starts = [int(s) for s, ln in zip(starts, text.split("\n")) if ln != ""]
+    assert dt.line_start.cpu().numpy()[:n].tolist() == starts and int(dt.line_start[n]) == len(text)
+    feats, wts, y, status = dt.parse_sparse(F, skip=0, pad_id=-1)
+    of, ow, oy, onnz = T.sparse_block(lines, F, -1, 0)
+    assert np.array_equal(feats.cpu().numpy(), of) and np.array_equal(wts.cpu().numpy(), ow)
+    assert np.array_equal(y.cpu().numpy(), oy) and np.array_equal(status.cpu().numpy(), onnz)
+    # fewer slots than features: truncated, status still reports the full count
+    f2, _, _, s2 = dt.parse_sparse(2, skip=0, pad_id=7, with_wts=False)
+    of2, _, _, _ = T.sparse_block(lines, 2, 7, 0)
+    assert np.array_equal(f2.cpu().numpy(), of2) and np.array_equal(s2.cpu().numpy(), onnz)
+
+
+def test_parse_yzx_and_long_lines(L):
+    """*.yzx.txt (ipinyou.py:50-59): the token after y is skipped, rows are padded with (X_dim - 1, 0); lines longer than the
+    24 KB shared-memory stage take the unstaged path; a capacity smaller than the file keeps the first max_lines lines"""
+    import text_oracle as T
+    from deepctr_b200.ingest import DeviceText
+    rng = np.random.default_rng(5)
+    lines = []
+    for i in range(300):
+        k = 3000 if i in (17, 18, 250) else int(rng.integers(0, 20))        # 3000 features ~ 30 KB
+        lines.append("%d %d %s" % (rng.integers(0, 2), rng.integers(0, 300), " ".join("%d:1" % j for j in rng.integers(0, 10 ** 6, k))))
+    text = "\n".join(lines) + "\n"
+    dt = DeviceText(text.encode())
+    J, pad = 24, 10 ** 6
+    feats, wts, y, status = dt.parse_sparse(J, skip=1, pad_id=pad)
+    of, ow, oy, onnz = T.sparse_block([ln.rstrip() for ln in lines], J, pad, 1)
+    assert np.array_equal(feats.cpu().numpy(), of) and np.array_equal(wts.cpu().numpy(), ow)
+    assert np.array_equal(y.cpu().numpy(), oy) and np.array_equal(status.cpu().numpy(), onnz)
+    small = DeviceText(text.encode(), max_lines=100)
+    assert small.n_lines == 300
+    f3, _, y3, s3 = small.parse_sparse(J, skip=1, pad_id=pad)
+    assert f3.shape[0] == 100 and np.array_equal(f3.cpu().numpy(), of[:100]) and np.array_equal(y3.cpu().numpy(), oy[:100])
+
+
+def test_parse_flags_malformed_lines(L):
+    from deepctr_b200.ingest import DeviceText, check_status
+    dt = DeviceText(b"1 5:1 7:1\n   \n0 x:1\n1 99999999999:1\n0 3:1 4\n")
+    feats, wts, y, status = dt.parse_sparse(4)
+    assert status.cpu().numpy().tolist() == [2, -1, -2, -2, 2]
+    assert feats.cpu().numpy()[0].tolist() == [5, 7, -1, -1] and feats.cpu().numpy()[4].tolist() == [3, 4, -1, -1]
+    with pytest.raises(ValueError):
+        check_status(status)
+    empty = DeviceText(b"")
+    assert empty.n_lines == 0 and empty.parse_sparse(4)[0].shape[0] == 0
+    assert DeviceText(b"\n\n\n").n_lines == 0
+
+
+@pytest.mark.parametrize("n", [1, 257, 5000])
+def test_parse_criteo_tsv(L, n):
+    """Criteo indexed TSV (clean.py:148-184) -> the engines' [N, 39] block == get_fxy (baseline.py:190-198): global ids bit-exact,
+    numeric weights = float32(value / max_vals) (same double division), labels"""
+    import text_oracle as T
+    from deepctr_b200 import data as D
+    from deepctr_b200.ingest import DeviceText, check_status
+    rng = np.random.default_rng(n)
+    offsets = D.offsets_of(D.CRITEO_CAT_SIZES, first=13)
+    lines = []
+    for i in range(n):
+        num = [int(rng.integers(0, m + 1)) for m in D.CRITEO_MAX_VALS]
+        cat = [int(rng.integers(0, s)) for s in D.CRITEO_CAT_SIZES]
+        lines.append("%d\t%s\t%s" % (rng.integers(0, 2), "\t".join(map(str, num)), "\t".join(map(str, cat))))
+    text = "\n".join(lines) + "\n"
+    dt = DeviceText(text.encode())
+    ids, wts, y, status = dt.parse_criteo(offsets, D.CRITEO_MAX_VALS)
+    check_status(status, expect=40)
+    of, ox, oy = T.criteo_block(lines, offsets, D.CRITEO_MAX_VALS.tolist())
+    assert np.array_equal(ids.cpu().numpy(), of)
+    assert np.array_equal(wts.cpu().numpy(), ox)                  # integers / max: the same double division, then one cast
+    assert np.array_equal(y.cpu().numpy(), oy)
+    # short, empty-field and non-numeric lines are flagged
+    bad = DeviceText(("1\t" + "\t".join(["3"] * 10) + "\n" + lines[0].replace("\t", "\t\t", 1) + "\n" + lines[0].replace("\t", "\tz", 1) + "\n").encode())
+    s = bad.parse_criteo(offsets, D.CRITEO_MAX_VALS)[3].cpu().numpy().tolist()
+    assert s[0] == 11 and s[1] == -2 and s[2] == -2
+
+
+def test_fnn_wnzh_trains_from_device_parsed_text(tmp_path):
+    """train.fm.txt bytes -> DeviceText -> FNN_wnzh.train_step_device == train() on the host-parsed batch (same masks)"""
+    from deepctr_b200 import data as D
+    from deepctr_b200.ingest import DeviceText
+    from deepctr_b200.theano_fnn import FNN_wnzh
+    rng = np.random.default_rng(77)
+    X, F, d, N = 500, 16, 5, 64
+    sizes = np.full(F, X // F)
+    sizes[-1] += X - sizes.sum()
+    feat_field = np.repeat(np.arange(F), sizes)
+    table = rng.uniform(-0.1, 0.1, (X, d))
+    ids = D.make_field_batch(rng, 2 * N, sizes)
+    y = rng.integers(0, 2, 2 * N)
+    path = str(tmp_path / "train.fm.txt")
+    D.write_fm_samples(path, ids, y)
+    fm = dict(w_0=0.05, table=table, feat_field=feat_field)
+    a, b = FNN_wnzh(fm, batch_size=N, hidden1=24, hidden2=12), FNN_wnzh(fm, batch_size=N, hidden1=24, hidden2=12)
+    dt = DeviceText(path)
+    feats, _, yd, status = dt.parse_sparse(F, skip=0, pad_id=-1, with_wts=False)
+    assert dt.n_lines == 2 * N and (status == F).all()
+    hf, hy = D.load_fm_samples(path)
+    for s in range(0, 2 * N, N):
+        la, pa = a.train(hf[s:s + N], hy[s:s + N])
+        lb, pb = b.train_step_device(feats[s:s + N], yd[s:s + N])
+        assert la == lb and np.array_equal(pa, pb)
+    assert np.array_equal(a.get_table(), b.get_table())
