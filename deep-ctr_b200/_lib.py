@@ -54,6 +54,7 @@ SIGNATURES = {
     "dctr_adam_tick": (_i, [_p, _f, _f, _f, _p]),
     "dctr_dense_adam": (_i, [_p, _p, _p, _p, _l, _p, _f, _f, _f, _f, _i, _p]),
     "dctr_dense_ftrl": (_i, [_p, _p, _p, _p, _l, _f, _f, _f, _f, _f, _i, _p]),
+    "dctr_bag_fwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
     "dctr_text_index_workspace": (_z, [_l]),
     "dctr_text_index_lines": (_i, [_p, _l, _p, _l, _p, _p, _z, _p]),
     "dctr_text_parse_sparse": (_i, [_p, _l, _p, _p, _l, _i, _i, _i, _p, _p, _p, _p, _p]),

@@ -372,7 +372,9 @@ extern "C" int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int3
     FoldArgs a{};
     a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table; a.dst = table;
     a.g = g; a.s = nullptr; a.ld_n = g_ld_n; a.ld_f = g_ld_f; a.wts = wts;
-    const bool aligned = aligned16(g) && (g_ld_n & 3) == 0 && (g_ld_f & 3) == 0 && g_ld_f >= ld;
+    // 128-bit gradient loads need whole float4s inside the source row: per-field blocks of >= ld floats, or -- g_ld_f = 0, the
+    // embedding bag: every field of a sample shares the sample's row -- rows of >= ld floats
+    const bool aligned = aligned16(g) && (g_ld_n & 3) == 0 && (g_ld_f & 3) == 0 && (g_ld_f >= ld || (g_ld_f == 0 && g_ld_n >= ld));
     return run_fold(mode == DCTR_SCATTER_SEQ_DECAY ? kSeq : kSum, a, aligned, workspace, workspace_bytes, as_stream(stream));
 }
 

@@ -35,7 +35,7 @@ class StepEngine:
         self.scatter_mode = L.SCATTER_SEQ_DECAY if scatter_mode == "seq_decay" else L.SCATTER_SUM
         F_, d_ = self.F, self.d
         self.crossw = {"none": 0, "ip": F_ * (F_ - 1) // 2, "op": d_ * d_}[cross]
-        self.D0 = F_ * d_ + self.crossw + 1
+        self.D0 = self._input_width()
         self.widths = [self.D0] + list(hidden)          # inputs of layers 0..L-1; the last layer maps to 1
         self.nl = len(self.widths)
         assert self.nl >= 2, "need at least one hidden layer"
@@ -56,7 +56,7 @@ class StepEngine:
             self.b_off.append(off)
             off += _r4(Hout)
         self.bias_off = off
-        off += 4
+        off += self._bias_len()
         self.n_params = off
         self.params = torch.zeros(off, **f32)
         self.grads = torch.zeros(off + 4, **f32)          # + a 4-float tail: the loss rides along in the data-parallel all-reduce
@@ -110,6 +110,19 @@ class StepEngine:
         self.overlap_sort = True
         self.wts_are_ones = True
 
+    # ---- the embedding front end (overridden by BagEngine) -------------------------------------------
+    def _input_width(self):
+        return self.F * self.d + self.crossw + 1          # [e_0 .. e_{F-1} | cross | bias]
+
+    def _bias_len(self):
+        return 4                                          # w_0 / fm b: one float, padded
+
+    def _embed_forward(self, ids, wts, table, X, st):
+        p = L.ptr
+        L.call("dctr_gather_concat_fwd", p(ids), p(wts), p(table), X, self.ld, self.N, self.F, self.d,
+               L.CROSS[self.cross], int(self.bias_first), p(self.bias()), L.ACT[self.act0],
+               p(self.ins[0]), self.ldi[0], st)
+
     # ---- parameter views -------------------------------------------------------------------------
     def W(self, l, buf=None):
         buf = self.params if buf is None else buf
@@ -160,9 +173,7 @@ class StepEngine:
         N, F, d, p = self.N, self.F, self.d, L.ptr
         wts = None if self.wts_are_ones else self.wts
         ids, table, X = (self.ids, self.table, self.X) if lookup is None else lookup
-        L.call("dctr_gather_concat_fwd", p(ids), p(wts), p(table), X, self.ld, N, F, d,
-               L.CROSS[self.cross], int(self.bias_first), p(self.bias()), L.ACT[self.act0],
-               p(self.ins[0]), self.ldi[0], st)
+        self._embed_forward(ids, wts, table, X, st)
         if self.masks[0] is not None:
             self.ins[0].mul_(self.masks[0])     # input dropout (tf.nn.dropout on act(z1), FNN.py:87): torch elementwise
         for l in range(self.nl - 1):
@@ -323,7 +334,9 @@ class StepEngine:
             torch.cuda.current_stream(self.dev).wait_stream(self.side2)
             self._wgrad_pending = False
 
-    def dense_update(self, lr, last_decay=1.0):
+    def dense_update(self, lr, last_decay=1.0, mlp_decay=1.0):
+        """last_decay: L2 on the output unit only (FNN_wnzh.py:173); mlp_decay: L2 on every MLP weight and bias but not on the
+        embedding-side bias (SNN_DAE.py:151-153)."""
         self.join_wgrad()
         st = self._st()
         if self.adam is not None:          # same step counter as the table (embedding_update ticked it)
@@ -336,7 +349,12 @@ class StepEngine:
             L.call("dctr_dense_ftrl", L.ptr(self.params), L.ptr(self.grads), L.ptr(self.params_n), L.ptr(self.params_z),
                    self.n_params, float(lr), lr_power, l1, l2, 0.0, 0, st)
             return
-        if last_decay == 1.0:
+        if mlp_decay != 1.0:
+            hi = self.bias_off
+            pp, gg = self.params.data_ptr(), self.grads.data_ptr()
+            L.call("dctr_dense_sgd", pp, gg, hi, float(lr), float(mlp_decay), st)
+            L.call("dctr_dense_sgd", pp + 4 * hi, gg + 4 * hi, self.n_params - hi, float(lr), 1.0, st)
+        elif last_decay == 1.0:
             L.call("dctr_dense_sgd", L.ptr(self.params), L.ptr(self.grads), self.n_params, float(lr), 1.0, st)
         else:   # Theano: cost += lambda1*(|w3|^2 + b3^2) touches the output unit only (FNN_wnzh.py:173)
             lo = self.w_off[self.nl - 1]
@@ -346,7 +364,7 @@ class StepEngine:
             L.call("dctr_dense_sgd", pp + 4 * lo, gg + 4 * lo, hi - lo, float(lr), float(last_decay), st)
             L.call("dctr_dense_sgd", pp + 4 * hi, gg + 4 * hi, self.n_params - hi, float(lr), 1.0, st)
 
-    def train_step(self, lr, decay=1.0, gscale=1.0, train_bias=True, last_decay=1.0):
+    def train_step(self, lr, decay=1.0, gscale=1.0, train_bias=True, last_decay=1.0, mlp_decay=1.0):
         """One full step on device buffers ids/wts/y (+ masks).  The row sort only depends on the ids, so it
         runs on a side stream concurrently with the MLP forward/backward."""
         L.call("dctr_set_launch_mode", self.launch_mode)
@@ -362,7 +380,41 @@ class StepEngine:
         if self.overlap_sort:
             cur.wait_stream(self.side)
         self.embedding_update(dz, lr, decay, train_bias)
-        self.dense_update(lr, last_decay)
+        self.dense_update(lr, last_decay, mlp_decay)
+
+
+class BagEngine(StepEngine):
+    """Embedding-BAG front end: ins[0] = sigmoid(sum_f table[ids[n,f]] + b0) with H0-wide rows instead of the
+    per-field concat -- the first layer of the SNN models (get_fi_h1_y, SNN_DAE.py:234-260).  Everything behind it is the
+    StepEngine: the first dgrad GEMM's epilogue applies sigmoid' and leaves gx*x*(1-x) in dz0, the sorted fold adds that
+    sample row into every row the sample touched (g_ld_f = 0) and its column sums are b0's gradient (SNN_DAE.py:282-288)."""
+
+    def __init__(self, X, F, H0, hidden, batch_size, act="tanh", device="cuda", gemm=None):
+        StepEngine.__init__(self, X, F, H0 - 1, hidden, batch_size, cross="none", bias_first=False, act0="sigmoid", act=act,
+                            scatter_mode="sum", device=device, gemm=gemm)
+
+    def _input_width(self):
+        return self.d                                     # d = H0: the bag output IS the MLP input
+
+    def _bias_len(self):
+        return _r4(self.d)                                # bb0 [H0]
+
+    def bias(self, buf=None):
+        buf = self.params if buf is None else buf
+        return buf[self.bias_off:self.bias_off + self.d]
+
+    def _embed_forward(self, ids, wts, table, X, st):
+        p = L.ptr
+        L.call("dctr_bag_fwd", p(ids), p(wts), p(table), X, self.ld, self.N, self.F, self.d, p(self.bias()),
+               L.ACT[self.act0], p(self.ins[0]), self.ldi[0], st)
+
+    def embedding_update(self, dz, lr, decay=1.0, train_bias=True):
+        st, p = self._st(), L.ptr
+        ldd = dz.stride(0)
+        if train_bias:          # bb0 -= lr * sum_t gx_t x_t (1 - x_t)   (SNN_DAE.py:284)
+            L.call("dctr_col_wsum", p(dz), ldd, self.N, self.d, None, p(self.bias(self.grads)), p(self.col_ws), self.col_ws.numel(), st)
+        wts = None if self.wts_are_ones else self.wts
+        self.table_update(p(self.sorted_rows), p(self.sorted_pos), self.M, self.F, p(dz), ldd, 0, p(wts), lr, decay, self.scat_ws)
 
 
 class FMEngine:

@@ -229,6 +229,16 @@ int dctr_dense_adam(float* param, float* grad, float* m, float* v, int64_t n, co
 int dctr_dense_ftrl(float* param, float* grad, float* accum, float* linear, int64_t n, float lr, float lr_power,
                     float l1, float l2, float grad_l2, int zero_grad, void* stream);
 
+/* ---- embedding bag: the first layer of the SNN models (get_fi_h1_y, SNN_DAE.py:234-260, SNN_RBM.py:238-262)
+ *   out[n, c] = act( b0[c] + sum_f wts[n,f] * table[ids[n,f], c] ),  c < H;  columns H..ldo-1 are written as 0
+ * table: float32 [X, ld] (ld % 4 == 0, ld >= H; the reference's ww0 is 133465 x 200), b0: [H] or NULL, act: DCTR_ACT_*
+ * (the reference applies the sigmoid).  Ragged samples pad their slots with any valid row and weight 0.
+ * Its backward is the existing path: d/d(pre-activation) comes out of the first dgrad GEMM's epilogue, b0's gradient is
+ * dctr_col_wsum of it, and the touched-row update `ww0[feat] -= lr * gx*x*(1-x)` (SNN_DAE.py:282-288) is dctr_scatter_sgd in
+ * SUM mode with g_ld_f = 0: every feature of a sample receives that sample's gradient row. */
+int dctr_bag_fwd(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld, int N, int F, int H,
+                 const float* b0, int act, float* out, int ldo, void* stream);
+
 /* ---- device-side ingestion of the reference's text formats -----------------------------------------
  * The raw file bytes are uploaded as they are; these entry points replace the Python parsers on the step's critical path:
  * linecache.getline + replace(':',' ').split() (get_fxy, FNN_wnzh.py:224-253), load_ipinyou_data (ipinyou.py:42-65) and

@@ -461,6 +461,81 @@ class OracleFM:
 
 
 # --------------------------------------------------------------------------------------------------
+# SNN fine-tuning step (SNN_DAE.py:103-160, 234-288; SNN_RBM.py is the same graph) -- SURVEY 8(f) f4
+# --------------------------------------------------------------------------------------------------
+class OracleSNN:
+    """x_dense = sigmoid(sum_{feat in sample} ww0[feat] + bb0) on the host (get_fi_h1_y, SNN_DAE.py:234-260), then the
+    Theano graph z1 = x.w1 + b1, h1 = act(z1), d1 = h1*r1, d2 = tanh(d1.w2 + b2)*r2, p_drop = sigmoid(d2.w3 + b3),
+    cost = xent.sum() + lambda1*(|w1|^2 + |w2|^2 + |w3|^2 + |b1|^2 + |b2|^2 + b3^2) (:113-153), SGD on w1..b3 (:157-163) and
+    the host loop  bb0 -= lr*gx_t*x_t*(1-x_t);  ww0[feat] -= lr*gx_t*x_t*(1-x_t)  per sample and feature (:282-288)."""
+
+    def __init__(self, ww0, bb0, Ws, bs, act="tanh", dtype=np.float64):
+        self.dtype = dtype
+        self.ww0, self.bb0 = np.array(ww0, dtype=dtype), np.array(bb0, dtype=dtype)
+        self.Ws = [np.array(w, dtype=dtype).reshape(w.shape[0], -1) for w in map(np.asarray, Ws)]
+        self.bs = [np.array(b, dtype=dtype).reshape(-1) for b in bs]
+        self.act = act
+
+    def dense(self, feats):
+        """feats: list of feature-id lists (ragged) or an [N, J] array padded with -1."""
+        x = np.zeros((len(feats), self.ww0.shape[1]), dtype=self.dtype)
+        for t, ft in enumerate(feats):
+            for feat in ft:
+                if feat >= 0:
+                    x[t] += self.ww0[feat]                        # :248
+        return sigmoid(x + self.bb0)                              # :250-253
+
+    def _mlp(self, x, r1, r2):
+        h1 = activate(self.act, x @ self.Ws[0] + self.bs[0])
+        d1 = h1 * r1
+        d2 = np.tanh(d1 @ self.Ws[1] + self.bs[1]) * r2           # :137 -- tanh whatever acti_type says
+        logit = (d2 @ self.Ws[2] + self.bs[2]).reshape(-1)
+        return h1, d1, d2, logit
+
+    def predict(self, feats):
+        x = self.dense(feats)
+        h1 = activate(self.act, x @ self.Ws[0] + self.bs[0])
+        h2 = activate(self.act, h1 @ self.Ws[1] + self.bs[1])     # :127-133
+        return sigmoid((h2 @ self.Ws[2] + self.bs[2]).reshape(-1))
+
+    def loss_and_grads(self, x, y, r1, r2, lambda1=0.0):
+        h1, d1, d2, logit = self._mlp(x, r1, r2)
+        loss = xent_with_logits(logit, y).sum() + lambda1 * (sum((w ** 2).sum() for w in self.Ws) + sum((b ** 2).sum() for b in self.bs))
+        dl = (sigmoid(logit) - y).reshape(-1, 1)
+        gW3, gb3 = d2.T @ dl, dl.sum(0)
+        dd2 = dl @ self.Ws[2].T
+        dz2 = dd2 * r2 * (1 - np.where(r2 != 0, d2 / np.where(r2 != 0, r2, 1), 0.0) ** 2)
+        gW2, gb2 = d1.T @ dz2, dz2.sum(0)
+        dz1 = (dz2 @ self.Ws[1].T) * r1 * activate_grad_from_out(self.act, h1)
+        gW1, gb1 = x.T @ dz1, dz1.sum(0)
+        gx = dz1 @ self.Ws[0].T
+        gWs = [gW1 + 2 * lambda1 * self.Ws[0], gW2 + 2 * lambda1 * self.Ws[1], gW3 + 2 * lambda1 * self.Ws[2]]
+        gbs = [gb1 + 2 * lambda1 * self.bs[0], gb2 + 2 * lambda1 * self.bs[1], gb3 + 2 * lambda1 * self.bs[2]]
+        return loss, sigmoid(logit), gx, gWs, gbs
+
+    def train_step(self, feats, y, lr, r1=1.0, r2=1.0, lambda1=0.0, faithful=False):
+        y = np.asarray(y, dtype=self.dtype)
+        x = self.dense(feats)
+        loss, p, gx, gWs, gbs = self.loss_and_grads(x, y, np.asarray(r1, dtype=self.dtype), np.asarray(r2, dtype=self.dtype), lambda1)
+        gs = gx * x * (1 - x)
+        if faithful:                                              # the literal loop of SNN_DAE.py:282-288
+            for t in range(len(feats)):
+                self.bb0 = self.bb0 - lr * gs[t]
+                for feat in feats[t]:
+                    if feat >= 0:
+                        self.ww0[feat] = self.ww0[feat] - lr * gs[t]
+        else:
+            self.bb0 = self.bb0 - lr * gs.sum(0)
+            for t, ft in enumerate(feats):
+                ft = np.asarray([f for f in ft if f >= 0], dtype=np.int64)
+                np.add.at(self.ww0, ft, -lr * gs[t])
+        for l in range(3):
+            self.Ws[l] = self.Ws[l] - lr * gWs[l]
+            self.bs[l] = self.bs[l] - lr * gbs[l]
+        return loss, p
+
+
+# --------------------------------------------------------------------------------------------------
 # initialisation (FNN_wnzh.py:15-17,106-130) -- reproducible with numpy's legacy RandomState alone
 # --------------------------------------------------------------------------------------------------
 def theano_fnn_init(xdim, hidden1, hidden2, acti_type="tanh", seed=1234):

@@ -236,3 +236,73 @@ def test_fnn_wnzh_trains_from_device_parsed_text(tmp_path):
         lb, pb = b.train_step_device(feats[s:s + N], yd[s:s + N])
         assert la == lb and np.array_equal(pa, pb)
     assert np.array_equal(a.get_table(), b.get_table())
+
+
+# ---- f4: SNN first layer as an embedding bag ----------------------------------------------------------------------------
+@pytest.mark.parametrize("N,F,H,X,act,with_w", [(1, 1, 1, 3, "none", False), (37, 16, 200, 5000, "sigmoid", True), (64, 7, 130, 90, "tanh", True),
+                                                (1000, 16, 200, 133465, "sigmoid", False), (9, 20, 300, 50, "sigmoid", True)])
+def test_bag_fwd(L, N, F, H, X, act, with_w):
+    """dctr_bag_fwd: out = act(b0 + sum_f w * table[id]) -- x_dense of get_fi_h1_y (SNN_DAE.py:234-260); pad columns are 0"""
+    import deepctr_oracle as O
+    rng = np.random.default_rng(N + H)
+    ld, ldo = (H + 3) // 4 * 4, (H + 3) // 4 * 4 + 4
+    table = np.zeros((X, ld), np.float32)
+    table[:, :H] = rng.normal(0, 0.3, (X, H))
+    ids = rng.integers(0, X, (N, F)).astype(np.int32)
+    ids[:, -1] = ids[:, 0]                                   # a feature twice in one sample counts twice
+    wts = (rng.random((N, F)) < 0.8).astype(np.float32) if with_w else None
+    b0 = rng.normal(0, 0.1, H).astype(np.float32)
+    t_ids, t_tab, t_b0 = torch.tensor(ids).cuda(), torch.tensor(table).cuda(), torch.tensor(b0).cuda()
+    t_w = torch.tensor(wts).cuda() if with_w else None
+    out = torch.full((N, ldo), 7.0, device="cuda")
+    L.call("dctr_bag_fwd", t_ids.data_ptr(), L.ptr(t_w), t_tab.data_ptr(), X, ld, N, F, H, t_b0.data_ptr(), L.ACT[act],
+           out.data_ptr(), ldo, None)
+    rows = table[ids, :H].astype(np.float64)
+    pre = (rows * (wts[..., None] if with_w else 1.0)).sum(1) + b0
+    ref = O.activate(act, pre) if act != "none" else pre
+    o = out.cpu().numpy()
+    close(o[:, :H], ref, 1e-5, 2e-6)
+    assert (o[:, H:] == 0).all()
+
+
+@pytest.mark.parametrize("gemm,use_graph,lambda1", [("simt", False, 0.0), ("tc", True, 0.01)])
+def test_snn_train_steps(monkeypatch, gemm, use_graph, lambda1):
+    """SNN fine-tuning steps (SNN_DAE.py:276-288) against OracleSNN: ragged samples, a feature that every sample has (a
+    512-long duplicate segment), a feature twice inside one sample, injected dropout masks, then predict()"""
+    monkeypatch.setenv("DCTR_GEMM", gemm)
+    import deepctr_oracle as O
+    from deepctr_b200.snn import SNN
+    rng = np.random.default_rng(808)
+    X, J, H0, H1, H2, N = 3000, 12, 200, 48, 20, 128
+    ww0, bb0 = rng.normal(0, 0.2, (X, H0)), rng.normal(0, 0.1, H0)
+    Ws = [rng.normal(0, 1, (H0, H1)) / np.sqrt(H0), rng.normal(0, 1, (H1, H2)) / np.sqrt(H1)]
+    bs = [rng.normal(0, 0.1, H1), rng.normal(0, 0.1, H2)]
+    f32 = lambda a: np.asarray(a, np.float32)
+    m = SNN(x_dim=X, max_feats=J, batch_size=N, lr=0.05, dropout=0.5, hidden0=H0, hidden1=H1, hidden2=H2, lambda1=lambda1,
+            weights=(f32(ww0), f32(bb0), f32(Ws[0]), f32(bs[0]), f32(Ws[1]), f32(bs[1])))
+    m.use_graph = use_graph
+    m.engine.set_layer(2, rng.uniform(-0.3, 0.3, (H2, 1)), np.array([0.05]))          # w3 = 0 would leave gx = 0
+    w3, b3 = m.engine.get_layer(2)
+    o = O.OracleSNN(f32(ww0), f32(bb0), [f32(Ws[0]), f32(Ws[1]), w3], [f32(bs[0]), f32(bs[1]), b3])
+    for step in range(4):
+        feats = np.full((N, J), -1, dtype=np.int64)
+        for t in range(N):
+            k = int(rng.integers(1, J))
+            feats[t, :k] = rng.integers(0, X, k)
+        feats[:, 0] = 11
+        feats[5, 1] = feats[5, 2] = 77
+        y = rng.integers(0, 2, N)
+        r1, r2 = (rng.random((1, H1)) < 0.5).astype(np.float32), (rng.random((1, H2)) < 0.5).astype(np.float32)
+        m.set_masks(r1, r2)
+        loss, p = m.train(feats, y)
+        oloss, op = o.train_step([list(r) for r in feats], y, 0.05, r1.astype(np.float64), r2.astype(np.float64), lambda1)
+        if lambda1 == 0.0:
+            close([loss], [oloss], 2e-5)
+        close(p, op, 5e-5)
+        tw0, tb0, w1, b1, w2, b2, w3n, b3n = m.get_weights()
+        close(tw0, o.ww0, 5e-5, 5e-6)
+        close(tb0, o.bb0, 5e-5, 5e-6)
+        close(w1, o.Ws[0], 5e-5, 5e-6)
+        close(w2, o.Ws[1], 5e-5, 5e-6)
+        close(w3n, o.Ws[2].reshape(-1), 5e-5, 5e-6)
+    close(m.predict(feats[:100]), o.predict([list(r) for r in feats[:100]]), 5e-5)
