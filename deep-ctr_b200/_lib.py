@@ -5,7 +5,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdctr.so")
+LIB_PATH = os.environ.get("DCTR_LIB") or os.path.join(_HERE, "libdctr.so")      # DCTR_LIB: an experimental build of the same ABI
 CSRC = os.path.join(_HERE, "csrc")
 
 OK, EINVAL, EWORKSPACE, ECUDA = 0, -1, -2, -3
@@ -14,7 +14,6 @@ CROSS = {"none": 0, None: 0, "ip": 1, "op": 2}
 SCATTER_SUM, SCATTER_SEQ_DECAY = 0, 1
 GEMM_NN, GEMM_NT, GEMM_TN = 0, 1, 2
 EPI_NONE, EPI_FWD, EPI_DGRAD = 0, 1, 2
-FOLD_CHUNK, FOLD_TILE = 8, 512
 
 _p, _i, _l, _f, _z = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float, ctypes.c_size_t
 

@@ -5,13 +5,14 @@
 // the list splits into segments (Zipf heads and the Criteo numeric rows that every sample touches cost the
 // same per element as singletons):
 //
-//   level 0  a 4-lane group owns DCTR_FOLD_CHUNK = 8 consecutive sorted elements; lane q owns one float4 of the
-//            row.  All 8 gradient gathers (random 44-48 B reads) and the old rows of the segments that END in
-//            the chunk are issued up front (16 independent 128-bit loads per lane), then the chunk is folded
-//            serially in list order.  A segment that starts and ends inside the chunk is written straight to
+//   level 0  a 4-lane group owns DCTR_FOLD_CHUNK = 4 consecutive sorted elements; lane q owns one float4 of the
+//            row.  All gradient gathers (random 44-48 B reads) and the old rows of the segments that END in
+//            the chunk are issued up front (8 independent 128-bit loads per lane), then the chunk is folded
+//            serially in list order.  (Chunks of 8 need 105-116 registers = 2 CTAs per SM; chunks of 4 fit 64 registers =
+//            4 CTAs per SM and measure 10-15 % faster on lists far larger than L2, equal at step sizes.)  A segment that starts and ends inside the chunk is written straight to
 //            the table (one read-modify-write per touched row).
 //   level 1  pieces that cross chunk borders are parked in shared memory as partials (P, Q) and composed in
-//            group order by the group that holds the segment head (CTA tile = 64 groups = 512 elements).
+//            group order by the group that holds the segment head (CTA tile = 64 groups = 256 elements).
 //   level 2  pieces that cross tile borders leave the CTA as one carry-in and one carry-out partial per tile;
 //            fold_stitch_kernel walks them in tile order and writes the row.
 //
@@ -28,9 +29,9 @@ constexpr int kC = DCTR_FOLD_CHUNK;            // sorted elements per group
 constexpr int kG = 4;                          // lanes per group
 constexpr int kFoldThreads = 256;
 constexpr int kGroups = kFoldThreads / kG;     // 64 groups per CTA
-constexpr int kTile = kGroups * kC;            // 512 sorted elements per CTA
+constexpr int kTile = kGroups * kC;            // 256 sorted elements per CTA
 constexpr int kSlab = 4 * kG;                  // 16 table columns per launch
-static_assert(kTile == DCTR_FOLD_TILE, "dctr.h out of sync");
+static_assert(kTile == DCTR_FOLD_TILE && (kC == 4 || kC == 8), "dctr.h out of sync");
 
 enum { kSum = 0, kSeq = 1, kFm = 2 };
 enum { kHasF = 1, kFClosed = 2, kHasL = 4 };
@@ -102,7 +103,7 @@ __device__ __forceinline__ float4 mask_cols(float4 v, int c0, int d) {
 }
 
 template <int MODE, bool ALIGNED>
-__global__ void __launch_bounds__(kFoldThreads, 2)
+__global__ void __launch_bounds__(kFoldThreads, kC == 8 ? 2 : 4)
 fold_tile_kernel(const FoldArgs a) {
     pdl_sync();
     __shared__ float4 sQF[kFoldThreads], sQL[kFoldThreads];
@@ -117,10 +118,12 @@ fold_tile_kernel(const FoldArgs a) {
     // ---- the chunk's (row, position) pairs and its two neighbours ----
     int r[kC], p[kC];
     if (k0 + kC <= a.M) {
-        const int4 r0 = __ldg(reinterpret_cast<const int4*>(a.rows + k0)), r1 = __ldg(reinterpret_cast<const int4*>(a.rows + k0) + 1);
-        const int4 p0 = __ldg(reinterpret_cast<const int4*>(a.pos + k0)), p1 = __ldg(reinterpret_cast<const int4*>(a.pos + k0) + 1);
-        r[0] = r0.x; r[1] = r0.y; r[2] = r0.z; r[3] = r0.w; r[4] = r1.x; r[5] = r1.y; r[6] = r1.z; r[7] = r1.w;
-        p[0] = p0.x; p[1] = p0.y; p[2] = p0.z; p[3] = p0.w; p[4] = p1.x; p[5] = p1.y; p[6] = p1.z; p[7] = p1.w;
+#pragma unroll
+        for (int h = 0; h < kC / 4; ++h) {
+            const int4 rr = __ldg(reinterpret_cast<const int4*>(a.rows + k0) + h), pp = __ldg(reinterpret_cast<const int4*>(a.pos + k0) + h);
+            r[4 * h] = rr.x; r[4 * h + 1] = rr.y; r[4 * h + 2] = rr.z; r[4 * h + 3] = rr.w;
+            p[4 * h] = pp.x; p[4 * h + 1] = pp.y; p[4 * h + 2] = pp.z; p[4 * h + 3] = pp.w;
+        }
     } else {
 #pragma unroll
         for (int j = 0; j < kC; ++j) {

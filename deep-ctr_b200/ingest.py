@@ -32,7 +32,7 @@ class DeviceText(object):
         self.nbytes = int(data.size)
         cap = (self.nbytes + 15) // 16 * 16 + 16
         pinned = torch.zeros(cap, dtype=torch.uint8).pin_memory()
-        pinned[:self.nbytes] = torch.from_numpy(data)
+        np.copyto(pinned.numpy()[:self.nbytes], data)         # straight into the pinned block (bytes objects are read-only views)
         self.text = torch.empty(cap, dtype=torch.uint8, device=self.dev)        # torch allocations are >= 256-byte aligned
         self.text.copy_(pinned, non_blocking=True)
         self._pinned = pinned

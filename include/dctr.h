@@ -123,8 +123,10 @@ int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t* sorted_row
  * cross chunk / tile borders are composed in list order (fixed association => bit-reproducible).
  * rows / pos / table / workspace must be 16-byte aligned.
  * workspace: dctr_scatter_workspace(M, ld) bytes (one carry-in and one carry-out partial per tile). */
-#define DCTR_FOLD_CHUNK 8    /* sorted elements folded serially by one 4-lane group */
-#define DCTR_FOLD_TILE 512   /* sorted elements per CTA */
+#ifndef DCTR_FOLD_CHUNK
+#define DCTR_FOLD_CHUNK 4    /* sorted elements folded serially by one 4-lane group (4 or 8; 4: <= 64 registers, 4 CTAs per SM) */
+#endif
+#define DCTR_FOLD_TILE (64 * DCTR_FOLD_CHUNK)   /* sorted elements per CTA (64 groups) */
 size_t dctr_scatter_workspace(int64_t M, int ld);
 int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
                      const float* g, int64_t g_ld_n, int g_ld_f, const float* wts,
