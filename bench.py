@@ -173,8 +173,8 @@ def call_cost(name, a):
     if name == "dctr_fm_fwd":
         N, F, d = a[5], a[6], a[7]
         return "byte", N * (F * 8 + 4 + F * 4 * d + 4 + 4 * d)
-    if name in ("dctr_scatter_sgd", "dctr_scatter_sgd_fm"):
-        M, d = (a[3], a[5]) if name == "dctr_scatter_sgd" else (a[2], a[4])
+    if name in ("dctr_scatter_sgd", "dctr_scatter_sgd_masked", "dctr_scatter_sgd_fm"):
+        M, d = (a[2], a[4]) if name == "dctr_scatter_sgd_fm" else (a[3], a[5])
         return "byte", M * (4 + 4 * d + 2 * 4 * d)
     if name == "dctr_cross_bwd":
         N, F, d, ldz = a[5], a[6], a[7], a[10]
@@ -251,6 +251,7 @@ def emb_roofline(N=1 << 20, F=16, rank=10, X=20_000_000, reps=5):
     ldz = (D0 + 3) // 4 * 4
     z = torch.empty(N, ldz, device=dev)
     dz = torch.empty(N, ldz, device=dev).uniform_(-1, 1)
+    ge = torch.empty(N, F, ld, device=dev).uniform_(-1, 1)
     y = (torch.rand(N, device=dev) < 0.05).float()
     bias = torch.zeros(1, device=dev)
     M = N * F
@@ -266,6 +267,12 @@ def emb_roofline(N=1 << 20, F=16, rank=10, X=20_000_000, reps=5):
         "sort_rows": ("dctr_sort_rows", (p(ids), M, X, p(rows), p(pos), p(sws), sws.numel(), None)),
         "scatter_sgd[seq_decay]": ("dctr_scatter_sgd", (1, p(rows), p(pos), M, F, d, p(dz) + 4, ldz, d, p(wts), 1e-3, 0.9999, p(table), X, ld, p(fws), fws.numel(), None)),
         "scatter_sgd[sum]": ("dctr_scatter_sgd", (0, p(rows), p(pos), M, F, d, p(dz) + 4, ldz, d, p(wts), 1e-3, 1.0, p(table), X, ld, p(fws), fws.numel(), None)),
+        # 0 / 1 weights with the 0s on one pad row (FNN_wnzh, SNN): no per-slot weight gather
+        "scatter_sgd_masked[seq_decay]": ("dctr_scatter_sgd_masked", (1, p(rows), p(pos), M, F, d, p(dz) + 4, ldz, d, X - 1, 1e-3, 0.9999, p(table), X, ld, p(fws), fws.numel(), None)),
+        "scatter_sgd_masked[sum]": ("dctr_scatter_sgd_masked", (0, p(rows), p(pos), M, F, d, p(dz) + 4, ldz, d, X - 1, 1e-3, 1.0, p(table), X, ld, p(fws), fws.numel(), None)),
+        # the same fold fed from a per-slot gradient buffer [N, F, ld] (what the IP / OP models and the multi-GPU steps hand it):
+        # 16-byte aligned 48-byte rows, 128-bit loads, weights already applied
+        "scatter_sgd[sum, slot buffer]": ("dctr_scatter_sgd", (0, p(rows), p(pos), M, F, d, p(ge), F * ld, ld, None, 1e-3, 1.0, p(table), X, ld, p(fws), fws.numel(), None)),
         "scatter_sgd_fm": ("dctr_scatter_sgd_fm", (p(rows), p(pos), M, F, d, p(g), p(s), ld, p(wts), 1e-3, 1.0, p(table), X, ld, p(fws), fws.numel(), None)),
     }
     pk = peaks()

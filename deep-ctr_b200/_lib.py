@@ -32,6 +32,7 @@ SIGNATURES = {
     "dctr_sort_rows": (_i, [_p, _l, _l, _p, _p, _p, _z, _p]),
     "dctr_scatter_workspace": (_z, [_l, _i]),
     "dctr_scatter_sgd": (_i, [_i, _p, _p, _l, _i, _i, _p, _l, _i, _p, _f, _f, _p, _l, _i, _p, _z, _p]),
+    "dctr_scatter_sgd_masked": (_i, [_i, _p, _p, _l, _i, _i, _p, _l, _i, _i, _f, _f, _p, _l, _i, _p, _z, _p]),
     "dctr_scatter_sgd_fm": (_i, [_p, _p, _l, _i, _i, _p, _p, _i, _p, _f, _f, _p, _l, _i, _p, _z, _p]),
     "dctr_scatter_grad_fm": (_i, [_p, _p, _l, _i, _i, _p, _p, _i, _p, _p, _l, _i, _p, _p, _z, _p]),
     "dctr_decay_sweep": (_i, [_p, _l, _i, _f, _p, _l, _p]),

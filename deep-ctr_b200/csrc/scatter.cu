@@ -41,6 +41,7 @@ struct FoldArgs {
     const int32_t* rows; const int32_t* pos; int64_t M;
     int F; uint64_t fmul;          // n = p / F  ==  (p * fmul) >> 40 when fmul != 0 (F < 512, p < 2^31)
     int d, ld, col0;
+    int skip_row;                  // segments of this row are folded but never written (-1: none) -- the pad row of absent fields
     float lr, decay;
     float* table;                  // rows are READ from here ...
     float* dst;                    // ... and the folded result is written here (== table except for the gradient-only fold)
@@ -201,7 +202,7 @@ fold_tile_kernel(const FoldArgs a) {
             fold_elem<MODE>(P, Q, e[j], v[j], a.lr, a.decay);
             if (tail >> j & 1) {
                 if (!open_left) {
-                    if (lane_on)
+                    if (lane_on && r[j] != a.skip_row)
                         *reinterpret_cast<float4*>(a.dst + (int64_t)r[j] * a.ld + c0) = fold_final<MODE>(old[j], P, Q, c0, a.lr, a.decay);
                 } else {
                     PF = P; QF = Q; flag |= kHasF | kFClosed;
@@ -226,7 +227,7 @@ fold_tile_kernel(const FoldArgs a) {
             if (fh & kFClosed) { closed = true; break; }
         }
         if (closed) {
-            if (lane_on)
+            if (lane_on && rowL != a.skip_row)
                 *reinterpret_cast<float4*>(a.dst + (int64_t)rowL * a.ld + c0) = fold_final<MODE>(oldL, P, Q, c0, a.lr, a.decay);
         } else {      // the segment runs past this tile: carry-out
             reinterpret_cast<float4*>(a.out_q)[tile * kG + q] = Q;
@@ -292,7 +293,8 @@ fold_stitch_kernel(const FoldArgs a, int tiles) {
         }
         u += 4;
     }
-    if (lane_on) *reinterpret_cast<float4*>(a.dst + (int64_t)row * a.ld + c0) = fold_final<MODE>(old, P, Q, c0, a.lr, a.decay);
+    if (lane_on && row != a.skip_row)
+        *reinterpret_cast<float4*>(a.dst + (int64_t)row * a.ld + c0) = fold_final<MODE>(old, P, Q, c0, a.lr, a.decay);
 }
 
 __global__ void decay_sweep_kernel(float4* __restrict__ table, int64_t X, int q, float decay,
@@ -362,10 +364,10 @@ extern "C" size_t dctr_scatter_workspace(int64_t M, int ld) {
 
 static bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 
-extern "C" int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F,
-                                int d, const float* g, int64_t g_ld_n, int g_ld_f, const float* wts, float lr,
-                                float decay, float* table, int64_t X, int ld, void* workspace,
-                                size_t workspace_bytes, void* stream) {
+static int scatter_sgd_impl(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F,
+                            int d, const float* g, int64_t g_ld_n, int g_ld_f, const float* wts, int32_t skip_row, float lr,
+                            float decay, float* table, int64_t X, int ld, void* workspace,
+                            size_t workspace_bytes, void* stream) {
     DCTR_REQUIRE(mode == DCTR_SCATTER_SUM || mode == DCTR_SCATTER_SEQ_DECAY, "scatter_sgd: bad mode %d", mode);
     DCTR_REQUIRE(M >= 0 && M < ((int64_t)1 << 31) && F > 0 && d > 0 && d <= ld && (ld & 3) == 0 && X > 0, "scatter_sgd: bad shape");
     if (M == 0) return DCTR_OK;
@@ -373,12 +375,29 @@ extern "C" int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int3
     DCTR_REQUIRE(aligned16(sorted_rows) && aligned16(sorted_pos) && aligned16(table) && aligned16(workspace),
                  "scatter_sgd: rows / pos / table / workspace must be 16-byte aligned");
     FoldArgs a{};
+    a.skip_row = -1;
     a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table; a.dst = table;
-    a.g = g; a.s = nullptr; a.ld_n = g_ld_n; a.ld_f = g_ld_f; a.wts = wts;
+    a.g = g; a.s = nullptr; a.ld_n = g_ld_n; a.ld_f = g_ld_f; a.wts = wts; a.skip_row = skip_row;
     // 128-bit gradient loads need whole float4s inside the source row: per-field blocks of >= ld floats, or -- g_ld_f = 0, the
     // embedding bag: every field of a sample shares the sample's row -- rows of >= ld floats
     const bool aligned = aligned16(g) && (g_ld_n & 3) == 0 && (g_ld_f & 3) == 0 && (g_ld_f >= ld || (g_ld_f == 0 && g_ld_n >= ld));
     return run_fold(mode == DCTR_SCATTER_SEQ_DECAY ? kSeq : kSum, a, aligned, workspace, workspace_bytes, as_stream(stream));
+}
+
+extern "C" int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F,
+                                int d, const float* g, int64_t g_ld_n, int g_ld_f, const float* wts, float lr,
+                                float decay, float* table, int64_t X, int ld, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+    return scatter_sgd_impl(mode, sorted_rows, sorted_pos, M, F, d, g, g_ld_n, g_ld_f, wts, -1, lr, decay, table, X, ld, workspace,
+                            workspace_bytes, stream);
+}
+
+extern "C" int dctr_scatter_sgd_masked(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F,
+                                       int d, const float* g, int64_t g_ld_n, int g_ld_f, int32_t skip_row, float lr,
+                                       float decay, float* table, int64_t X, int ld, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+    return scatter_sgd_impl(mode, sorted_rows, sorted_pos, M, F, d, g, g_ld_n, g_ld_f, nullptr, skip_row, lr, decay, table, X, ld,
+                            workspace, workspace_bytes, stream);
 }
 
 extern "C" int dctr_scatter_sgd_fm(const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
@@ -392,6 +411,7 @@ extern "C" int dctr_scatter_sgd_fm(const int32_t* sorted_rows, const int32_t* so
     DCTR_REQUIRE(aligned16(sorted_rows) && aligned16(sorted_pos) && aligned16(table) && aligned16(workspace) && aligned16(s),
                  "scatter_sgd_fm: rows / pos / table / s / workspace must be 16-byte aligned");
     FoldArgs a{};
+    a.skip_row = -1;
     a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table; a.dst = table;
     a.g = g; a.s = s; a.ld_n = 0; a.ld_f = lds; a.wts = wts;
     return run_fold(kFm, a, true, workspace, workspace_bytes, as_stream(stream));
@@ -407,6 +427,7 @@ extern "C" int dctr_scatter_grad_fm(const int32_t* sorted_rows, const int32_t* s
     DCTR_REQUIRE(aligned16(sorted_rows) && aligned16(sorted_pos) && aligned16(table) && aligned16(grad_out) && aligned16(workspace) && aligned16(s),
                  "scatter_grad_fm: rows / pos / table / grad_out / s / workspace must be 16-byte aligned");
     FoldArgs a{};
+    a.skip_row = -1;
     // the FM fold ends in  old*decay - lr*(Q - P*old):  decay = 0, lr = -1 leaves exactly the row's gradient
     a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = -1.f; a.decay = 0.f;
     a.table = const_cast<float*>(table); a.dst = grad_out;

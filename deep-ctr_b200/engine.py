@@ -109,6 +109,7 @@ class StepEngine:
         self.launch_mode = 2 if self.N <= 8192 else 0
         self.overlap_sort = True
         self.wts_are_ones = True
+        self.skip_row = None        # set when the weights are 0 / 1 and 0 only marks this (all-zero pad) row: no weight gather in the fold
 
     # ---- the embedding front end (overridden by BagEngine) -------------------------------------------
     def _input_width(self):
@@ -297,6 +298,10 @@ class StepEngine:
                    p(self.table_g), self.X, self.ld, p(ws), ws.numel(), st)
             L.call("dctr_dense_ftrl", p(self.table), p(self.table_g), p(self.table_n), p(self.table_z), self.X * self.ld,
                    float(lr), lr_power, l1, l2, 0.0, 1, st)
+            return
+        if self.skip_row is not None:
+            L.call("dctr_scatter_sgd_masked", self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_n, g_ld_f, int(self.skip_row),
+                   float(lr), float(decay), p(self.table), self.X, self.ld, p(ws), ws.numel(), st)
             return
         L.call("dctr_scatter_sgd", self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_n, g_ld_f, w, float(lr), float(decay),
                p(self.table), self.X, self.ld, p(ws), ws.numel(), st)

@@ -45,6 +45,7 @@ class SNN(_Base):
         eng.set_layer(1, ww2, bb2)
         eng.set_layer(2, np.zeros((hidden2, 1)), np.zeros(1))
         eng.wts_are_ones = False
+        eng.skip_row = X            # 0 / 1 weights, 0 only on the pad row: no weight gather in the fold
         self.pad_row = X
         self.mask_streams = MaskStreams(hidden1, hidden2, dropout) if dropout < 1.0 else None
         extra = []

@@ -70,6 +70,7 @@ class FNN_wnzh(_Base):
         for l in range(3):
             eng.set_layer(l, Ws[l], bs[l])
         eng.wts_are_ones = False
+        eng.skip_row = X            # weights are 1 except on the pad row: the fold drops that row instead of gathering weights
         self.pad_row = X
         N = batch_size
         extra = [("feats", np.int32, (N, n_fields))]

@@ -132,6 +132,14 @@ int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int32_t* sorted
                      const float* g, int64_t g_ld_n, int g_ld_f, const float* wts,
                      float lr, float decay, float* table, int64_t X, int ld,
                      void* workspace, size_t workspace_bytes, void* stream);
+/* The same fold for 0 / 1 weights where 0 only occurs on ONE row -- the all-zero pad row that stands in for a field a sample
+ * does not have (feats_to_layer_one_array leaves x = 0 there, FNN_wnzh.py:91-95): every slot has weight 1 and the segment of
+ * `skip_row` is never written, so the per-slot weight gather (a random 4-byte read per slot: 20 % of the fold's time on
+ * lists larger than L2) disappears.  skip_row = -1 skips nothing. */
+int dctr_scatter_sgd_masked(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
+                            const float* g, int64_t g_ld_n, int g_ld_f, int32_t skip_row,
+                            float lr, float decay, float* table, int64_t X, int ld,
+                            void* workspace, size_t workspace_bytes, void* stream);
 /* FM source (FM.py:55-64 differentiated):
  *   grad(p,0) = g[n]*x_p ; grad(p,c>=1) = g[n]*( x_p*s[n,c] - x_p^2*row_old[c] ) ; row = row*decay - lr*sum grad
  *   (decay = 1 - lr*lambda realises the L2 term of FM.py:39 on the touched rows). */

@@ -306,3 +306,35 @@ def test_snn_train_steps(monkeypatch, gemm, use_graph, lambda1):
         close(w2, o.Ws[1], 5e-5, 5e-6)
         close(w3n, o.Ws[2].reshape(-1), 5e-5, 5e-6)
     close(m.predict(feats[:100]), o.predict([list(r) for r in feats[:100]]), 5e-5)
+
+
+# ---- the fold without its weight gather (0 / 1 weights, the 0s on one pad row) -----------------------------------------
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("N,F,d,X", [(300, 16, 11, 400), (5000, 16, 11, 3000), (64, 5, 200, 40)])
+def test_scatter_masked_equals_weighted(L, mode, N, F, d, X):
+    """dctr_scatter_sgd_masked(skip_row = pad) == dctr_scatter_sgd with weights 1 / 0-on-the-pad-row, bit for bit (the pad
+    row is all zero, as in FNN_wnzh / SNN), including a pad segment that spans many tiles"""
+    rng = np.random.default_rng(N + d + mode)
+    ld = (d + 3) // 4 * 4
+    pad = X - 1
+    ids = rng.integers(0, X - 1, (N, F)).astype(np.int32)
+    ids[rng.random((N, F)) < 0.3] = pad
+    ids[:, 0] = 3                                             # a hot row as well
+    wts = (ids != pad).astype(np.float32)
+    table = np.zeros((X, ld), np.float32)
+    table[:pad, :d] = rng.normal(0, 0.1, (pad, d))
+    g = rng.normal(0, 1, (N, F * d + 4)).astype(np.float32)
+    M = N * F
+    t_ids, t_w, t_g = torch.tensor(ids).cuda(), torch.tensor(wts).cuda(), torch.tensor(g).cuda()
+    rows, pos = torch.empty(M, dtype=torch.int32, device="cuda"), torch.empty(M, dtype=torch.int32, device="cuda")
+    sws = torch.zeros(L.lib().dctr_sort_rows_workspace(M), dtype=torch.uint8, device="cuda")
+    fws = torch.zeros(L.lib().dctr_scatter_workspace(M, ld), dtype=torch.uint8, device="cuda")
+    L.call("dctr_sort_rows", t_ids.data_ptr(), M, X, rows.data_ptr(), pos.data_ptr(), sws.data_ptr(), sws.numel(), None)
+    ta, tb = torch.tensor(table).cuda(), torch.tensor(table).cuda()
+    L.call("dctr_scatter_sgd", mode, rows.data_ptr(), pos.data_ptr(), M, F, d, t_g.data_ptr() + 4, g.shape[1], d, t_w.data_ptr(),
+           0.05, 0.999, ta.data_ptr(), X, ld, fws.data_ptr(), fws.numel(), None)
+    L.call("dctr_scatter_sgd_masked", mode, rows.data_ptr(), pos.data_ptr(), M, F, d, t_g.data_ptr() + 4, g.shape[1], d, pad,
+           0.05, 0.999, tb.data_ptr(), X, ld, fws.data_ptr(), fws.numel(), None)
+    torch.cuda.synchronize()
+    assert torch.equal(ta, tb) and not torch.equal(ta, torch.tensor(table).cuda())
+    assert bool((tb[pad] == 0).all())
