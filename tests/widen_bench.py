@@ -21,8 +21,13 @@ except Exception:
 _flush = None
 
 
+ONCE = bool(os.environ.get("WIDEN_ONCE"))     # one launch of every kernel, no end-to-end loop: the run ncu attaches to
+
+
 def timed(fn, reps=5, warm=3):
     global _flush
+    if ONCE:
+        reps, warm = 1, 0
     if _flush is None:
         _flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
     for _ in range(warm):
@@ -96,6 +101,8 @@ def main():
     ms = timed(lambda: L.call("dctr_dense_ftrl", p.data_ptr(), gg.data_ptr(), nn.data_ptr(), zz.data_ptr(), n4, 0.01, -0.5, 0.0, 0.0, 0.0, 1, None))
     line(out, "dense_ftrl_kernel 19.6 M floats", ms, n4 * 4 * 8, note="4 reads + 4 writes per element")
     del p, gg, nn, zz
+    if ONCE:
+        return
     # ---- SNN fine-tuning step, reference shape (x_dim 133465, 200-300-100-1, batch 1000), graph replay, host feeds
     from deepctr_b200.snn import SNN
     import time
