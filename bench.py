@@ -219,7 +219,7 @@ NCU_TRAFFIC = {
     ("fm_ipinyou", "dctr_sort_rows"): 285.95e3 + 321.79e3 + 577.28e3,
     ("emb", "gather_concat_fwd"): 257.25e6 + 698.65e6,                        # profiles/r01_ncu_emb_gather_concat_kernel.txt
     ("emb", "fm_fwd"): 234.24e6 + 51.89e6,                                    # profiles/r01_ncu_emb_fm_fwd_kernel.txt
-    ("emb", "scatter_sgd[sum]"): 4371.56e6 + 40.12e6,                         # profiles/r01_ncu_emb_fold_tile_kernel.txt
+    ("emb", "scatter_sgd[sum]"): 4375.48e6 + 42.46e6,                         # profiles/r01_ncu_emb_fold_tile_kernel_chunk4.txt
 }
 
 

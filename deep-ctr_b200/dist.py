@@ -90,7 +90,8 @@ class DataParallelStep(object):
         e.side.wait_stream(cur)
         with torch.cuda.stream(e.side):          # id / weight exchange and the global sort: off the forward's critical path
             gids = self._gather(self.gids, e.ids)
-            gwts = None if e.wts_are_ones else self._gather(self.gwts, e.wts)
+            # weights reach the fold only when they are not 0 / 1-with-the-0s-on-the-pad-row (engine.skip_row: masked fold)
+            gwts = None if (e.wts_are_ones or e.skip_row is not None) else self._gather(self.gwts, e.wts)
             self._sort_global(gids)
         e.forward(True, gscale)
         dz = e.backward()
