@@ -1,0 +1,63 @@
+"""CPU tests of host-side logic that needs no device: optimizer dispatch (builf_optimizer, tf_util.py:15-29), the SNN slot
+packing (get_fi_h1_y's feature lists, SNN_DAE.py:241-249) and the parser status check."""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+
+class _FakeEngine:
+    def __init__(self):
+        self.calls = []
+
+    def enable_adam(self, eps):
+        self.calls.append(("adam", eps))
+
+    def enable_ftrl(self):
+        self.calls.append(("ftrl",))
+
+
+def test_optimizer_dispatch_follows_builf_optimizer():
+    from deepctr_b200.models import _optimizer
+    e = _FakeEngine()
+    lr, log = _optimizer(["adam", 1e-4, 1e-8, "sum"], e)
+    assert lr == 1e-4 and e.calls == [("adam", 1e-8)] and "epsilon" in log
+    e = _FakeEngine()
+    lr, log = _optimizer(["ftrl", 0.01, "mean"], e)
+    assert lr == 0.01 and e.calls == [("ftrl",)] and "ftrl" in log
+    e = _FakeEngine()
+    lr, log = _optimizer(["sgd", 1e-3, "sum"], e)             # anything else is plain gradient descent (tf_util.py:26-28)
+    assert lr == 1e-3 and e.calls == []
+    lr, _ = _optimizer(["whatever", 0.5, "sum"], e)
+    assert lr == 0.5 and e.calls == []
+
+
+def test_snn_slot_packing():
+    from deepctr_b200.snn import SNN, init_weight
+
+    class Fake:
+        F, pad_row = 5, 99
+    ids, wts = SNN.slots(Fake(), np.array([[3, -1, 7], [1, 2, -1]]))
+    assert ids.tolist() == [[3, 99, 7, 99, 99], [1, 2, 99, 99, 99]] and wts.tolist() == [[1, 0, 1, 0, 0], [1, 1, 0, 0, 0]]
+    ids, wts = SNN.slots(Fake(), [[3, 7], [1, 2, 4, 5, 6], []])
+    assert ids.tolist() == [[3, 7, 99, 99, 99], [1, 2, 4, 5, 6], [99] * 5] and wts.sum(1).tolist() == [2, 5, 0]
+    with pytest.raises(ValueError):
+        SNN.slots(Fake(), [[1, 2, 3, 4, 5, 6]])
+    with pytest.raises(ValueError):
+        SNN.slots(Fake(), np.zeros((2, 6), dtype=np.int64))
+    # dl_utils.init_weight (dl_utils.py:44-56): x4 for sigmoid, zero bias, bound sqrt(6 / (fan_in + fan_out))
+    w, b = init_weight(np.random.RandomState(1), 30, 20, "sigmoid")
+    w2, _ = init_weight(np.random.RandomState(1), 30, 20, "tanh")
+    assert np.allclose(w, 4 * w2) and (b == 0).all() and np.abs(w2).max() <= np.sqrt(6.0 / 50)
+
+
+def test_parser_status_check():
+    from deepctr_b200.ingest import check_status
+    ok = torch.tensor([16, 16, 3], dtype=torch.int32)
+    assert check_status(ok).tolist() == [16, 16, 3]
+    with pytest.raises(ValueError):
+        check_status(torch.tensor([16, -2], dtype=torch.int32))
+    with pytest.raises(ValueError):
+        check_status(torch.tensor([40, 39], dtype=torch.int32), expect=40)
+    with pytest.raises(ValueError):
+        check_status(torch.tensor([16, 17], dtype=torch.int32), max_nnz=16)
