@@ -88,6 +88,26 @@ class DeviceText(object):
         return ids[:k], (None if wts is None else wts[:k]), y[:k], status[:k]
 
 
+def chunk_shuffle_perm(n, size=100000, rng=None):
+    """Line order of the reference's `collect` (ipinyou.py:11-20; `size` = 10 000 / 100 000 lines): the file is read in chunks of
+    `size` lines and every chunk is shuffled with `np.random.shuffle`.  Returns perm (int64 [n]) with shuffled[k] = lines[perm[k]];
+    with the same RandomState it is the reference's order exactly (shuffle draws depend on the chunk length only)."""
+    rng = np.random if rng is None else rng
+    perm = np.arange(n, dtype=np.int64)
+    for s in range(0, n, size):
+        rng.shuffle(perm[s:s + size])
+    return perm
+
+
+def take_lines(perm, *tensors):
+    """Apply a line permutation to parsed device blocks (ids, wts, y, ...): a device-side row gather, None passes through."""
+    idx = torch.as_tensor(perm, dtype=torch.int64)
+    out = []
+    for t in tensors:
+        out.append(None if t is None else t.index_select(0, idx.to(t.device)))
+    return out
+
+
 def check_status(status, expect=None, max_nnz=None):
     """Raise on lines the parser flagged (the reference's int() / IndexError would have raised on the same lines).
     expect: exact status every line must have (Criteo: 1 + F); max_nnz: sparse lines longer than this were truncated."""

@@ -61,3 +61,32 @@ def test_parser_status_check():
         check_status(torch.tensor([40, 39], dtype=torch.int32), expect=40)
     with pytest.raises(ValueError):
         check_status(torch.tensor([16, 17], dtype=torch.int32), max_nnz=16)
+
+
+def test_chunk_shuffle_reproduces_collect():
+    """ingest.chunk_shuffle_perm == the order `collect` (ipinyou.py:11-20) hands out: chunks of `size` lines, each shuffled in
+    place with np.random.shuffle -- same RandomState, same order, including the short last chunk"""
+    from deepctr_b200.ingest import chunk_shuffle_perm, take_lines
+    lines = ["line %d" % i for i in range(1037)]
+
+    def collect(it, size, rng):                    # the reference function, RNG made explicit
+        buf = []
+        for _ in range(size):
+            try:
+                buf.append(next(it))
+            except StopIteration:
+                break
+        rng.shuffle(buf)
+        return buf
+    rng = np.random.RandomState(99)
+    it, ref = iter(lines), []
+    while True:
+        buf = collect(it, 250, rng)
+        if not buf:
+            break
+        ref.extend(buf)
+    perm = chunk_shuffle_perm(len(lines), 250, np.random.RandomState(99))
+    assert [lines[i] for i in perm] == ref and sorted(perm.tolist()) == list(range(1037))
+    t = torch.arange(1037 * 3).view(1037, 3)
+    a, b = take_lines(perm, t, None)
+    assert b is None and a[:, 0].tolist() == (perm * 3).tolist()
