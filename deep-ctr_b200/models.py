@@ -244,14 +244,14 @@ class _Base(object):
         self._swap_masks(saved)
         return out if out_dev is None else out_dev
 
-    def evaluate(self, ids, wts, labels):
+    def evaluate(self, ids, wts, labels, nds_rate=None):
         """Predict E rows (global ids [E, F], weights [E, F]) and score them ON THE DEVICE: dict(auc, log_loss, rmse, n_pos) --
         the eval half of the reference's loop (baseline.py:357-370 + watch_train :246-259) without the D2H of the predictions."""
         from .metrics import device_metrics
         ids, wts = np.asarray(ids).reshape(-1, self.F), np.asarray(wts).reshape(-1, self.F)
         preds = torch.empty(ids.shape[0], dtype=torch.float32, device=self.engine.dev)
         self._predict_chunks(ids, wts, out_dev=preds)
-        return device_metrics(preds, np.asarray(labels, dtype=np.float32).reshape(-1), device=self.engine.dev)
+        return device_metrics(preds, np.asarray(labels, dtype=np.float32).reshape(-1), device=self.engine.dev, nds_rate=nds_rate)
 
     def _pre_step(self):
         pass

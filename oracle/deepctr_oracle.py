@@ -536,6 +536,35 @@ class OracleSNN:
 
 
 # --------------------------------------------------------------------------------------------------
+# evaluation-side host logic of the driver (baseline.py:262-281, 369-370)
+# --------------------------------------------------------------------------------------------------
+def early_stop_literal(step, errs, metric, least_step, skip_window, smooth_window, stop_window):
+    """early_stop, baseline.py:262-281, statement by statement (prints dropped)."""
+    if step > least_step:
+        skip_metric = list(errs)[::skip_window]
+        smooth_metric = np.array(skip_metric[smooth_window - 1:], dtype=np.float64)
+        for i in range(smooth_window - 1):
+            smooth_metric += skip_metric[i:(i - smooth_window + 1)]
+        smooth_metric /= smooth_window
+        if len(smooth_metric) < stop_window:
+            return False
+        smooth_error = smooth_metric[stop_window - 1:] - smooth_metric[:1 - stop_window]
+        if metric == "rmse" and smooth_error[-1] > 0:
+            return True
+        elif metric == "auc" and smooth_error[-1] < 0:
+            return True
+        return False
+    return False
+
+
+def recalibrate_literal(eval_preds, nds_rate):
+    """baseline.py:369-370: eval_preds /= eval_preds + (1 - eval_preds) / nds_rate."""
+    eval_preds = np.array(eval_preds, dtype=np.float64)
+    eval_preds /= eval_preds + (1 - eval_preds) / nds_rate
+    return eval_preds
+
+
+# --------------------------------------------------------------------------------------------------
 # initialisation (FNN_wnzh.py:15-17,106-130) -- reproducible with numpy's legacy RandomState alone
 # --------------------------------------------------------------------------------------------------
 def theano_fnn_init(xdim, hidden1, hidden2, acti_type="tanh", seed=1234):

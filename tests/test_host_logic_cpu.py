@@ -90,3 +90,28 @@ def test_chunk_shuffle_reproduces_collect():
     t = torch.arange(1037 * 3).view(1037, 3)
     a, b = take_lines(perm, t, None)
     assert b is None and a[:, 0].tolist() == (perm * 3).tolist()
+
+
+def test_early_stop_and_recalibration_equal_the_driver_logic():
+    """metrics.early_stop / recalibrate against the statement-by-statement restatement of baseline.py:262-281, 369-370"""
+    import deepctr_oracle as O
+    from deepctr_b200.metrics import early_stop, recalibrate
+    rng = np.random.default_rng(3)
+    hits = 0
+    for trial in range(300):
+        n = int(rng.integers(0, 60))
+        errs = (0.7 + 0.05 * rng.standard_normal(n) + 0.002 * np.arange(n) * rng.choice([-1, 1])).tolist()
+        skip, smooth, stop = int(rng.integers(1, 4)), int(rng.integers(1, 12)), int(rng.integers(2, 12))
+        for metric in ("auc", "rmse"):
+            for step, least in ((100, 10), (5, 10)):
+                a = early_stop(step, errs, metric, least, skip, smooth, stop)
+                b = O.early_stop_literal(step, errs, metric, least, skip, smooth, stop)
+                assert a == b, (trial, n, skip, smooth, stop, metric)
+                hits += a
+    assert hits > 50
+    # baseline.py's own windows (skip 1, smooth 10, stop 10) on a record that turns down
+    rec = [0.70 + 0.001 * i for i in range(30)] + [0.73 - 0.002 * i for i in range(12)]
+    assert not early_stop(1000, rec[:30]) and early_stop(1000, rec)
+    p = rng.random(1000)
+    np.testing.assert_allclose(recalibrate(p, 0.025), O.recalibrate_literal(p, 0.025), rtol=1e-15)
+    np.testing.assert_allclose(recalibrate(torch.tensor(p), 0.025).numpy(), O.recalibrate_literal(p, 0.025), rtol=1e-12)
