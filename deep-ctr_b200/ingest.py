@@ -99,6 +99,33 @@ def chunk_shuffle_perm(n, size=100000, rng=None):
     return perm
 
 
+class LineCursor(object):
+    """Which lines the reference's readers hand to each batch, as index arrays into the parsed device blocks.
+      wrap=True   get_batch_xy (baseline.py:225-243): read `size` lines; at end of file reopen it and top the batch up from the
+                  first line, the next batch continuing from there -- the file is a ring;
+      wrap=False  FNN_wnzh.py:292-297 / ipinyou.py:166-172: consecutive full batches, the ragged tail of an epoch is dropped
+                  and the next epoch starts at line 0 (next() returns None once at the end of an epoch)."""
+
+    def __init__(self, n_lines, wrap=True):
+        self.n, self.wrap, self.pos = int(n_lines), bool(wrap), 0
+
+    def next(self, size):
+        if self.n <= 0 or size <= 0:
+            return None
+        if self.wrap:
+            left = self.n - self.pos                       # lines before the end of the file
+            take = min(size, left + self.n)                # one reopen per batch: a file shorter than the top-up gives a short batch
+            idx = (self.pos + np.arange(take, dtype=np.int64)) % self.n
+            self.pos = int((self.pos + take) % self.n)
+            return idx
+        if self.pos + size > self.n:
+            self.pos = 0
+            return None
+        idx = np.arange(self.pos, self.pos + size, dtype=np.int64)
+        self.pos += size
+        return idx
+
+
 def take_lines(perm, *tensors):
     """Apply a line permutation to parsed device blocks (ids, wts, y, ...): a device-side row gather, None passes through."""
     idx = torch.as_tensor(perm, dtype=torch.int64)

@@ -115,3 +115,38 @@ def test_early_stop_and_recalibration_equal_the_driver_logic():
     p = rng.random(1000)
     np.testing.assert_allclose(recalibrate(p, 0.025), O.recalibrate_literal(p, 0.025), rtol=1e-15)
     np.testing.assert_allclose(recalibrate(torch.tensor(p), 0.025).numpy(), O.recalibrate_literal(p, 0.025), rtol=1e-12)
+
+
+def test_line_cursor_follows_the_reference_readers():
+    """ingest.LineCursor(wrap=True) == get_batch_xy / get_batch_sparse_tensor (baseline.py:201-243) simulated on an in-memory
+    'file' (end of file -> reopen and top up); wrap=False == consecutive full batches with the ragged tail dropped"""
+    from deepctr_b200.ingest import LineCursor
+
+    class Reader:                                  # the two reference functions with the file replaced by a list of line numbers
+        def __init__(self, n):
+            self.n, self.it = n, None
+
+        def sparse(self, size):
+            if self.it is None:
+                self.it = iter(range(self.n))
+            got = []
+            for _ in range(size):
+                try:
+                    got.append(next(self.it))
+                except StopIteration:
+                    self.it = None
+                    break
+            return got
+
+        def batch(self, size):
+            got = self.sparse(size)
+            if len(got) == size:
+                return got
+            return got + self.sparse(size - len(got))
+    for n, size in [(10, 3), (10, 5), (10, 10), (7, 4), (3, 8), (100, 33)]:
+        ref, cur = Reader(n), LineCursor(n, wrap=True)
+        for _ in range(25):
+            assert cur.next(size).tolist() == ref.batch(size), (n, size)
+    cur = LineCursor(10, wrap=False)
+    seen = [cur.next(4) for _ in range(7)]
+    assert [None if s is None else s.tolist() for s in seen] == [[0, 1, 2, 3], [4, 5, 6, 7], None, [0, 1, 2, 3], [4, 5, 6, 7], None, [0, 1, 2, 3]]
