@@ -7,7 +7,10 @@ import this file; the product package (deep-ctr_b200/) never does.
 PARITY UNPINNED: the reference (Python 2 + Theano / TensorFlow 0.x) cannot run in this image and ships no
 tests, golden vectors or fixtures.  This restatement is therefore pinned only by
 (a) line-by-line citation of the reference, (b) central finite differences of every hand-derived backward
-(tests/test_oracle.py) and (c) algebraic identities (FM pairwise identity, OP prefix form, IP index formula).
+(tests/test_oracle.py), (c) algebraic identities (FM pairwise identity, OP prefix form, IP index formula; FTRL = AdaGrad) and
+(d) an independent derivation of every gradient: the forward of each model family rewritten in torch (float64, CPU) and
+differentiated by autograd agrees with the hand-derived backward to 1e-9 (test_network_backward_equals_autograd,
+test_fm_gradient_equals_autograd).
 
 Reference citations are file:line under /root/reference/python.
 """
