@@ -440,7 +440,12 @@ def run_b200(args, rank, world):
                 "peak": pk["tensor"] if top["unit"] == "TFLOP/s" else pk["hbm"], "unit": top["unit"], "frac": top["frac"],
                 "traffic": NCU_TRAFFIC.get((wl, top["kernel"])), "peak_source": pk["src"] + (" (bf16 sustained)" if top["unit"] == "TFLOP/s" else " (copy)"),
                 "share_of_step": top["share"]}
-        if top["unit"] == "TFLOP/s":
+        if top["unit"] == "TFLOP/s" and top["kernel"].startswith("dctr_gemm_tc"):
+            # achieved counts fp32-equivalent flops (2 M N K); the kernel issues three tf32 MMAs per k-step (error compensation)
+            roof["note"] = ("3xTF32 on tcgen05: fp32-equivalent FLOP/s; its ceiling is cuBLAS TF32 / 3 = 243 TFLOP/s (DESIGN 3.4) "
+                            "-> frac_of_3xtf32_ceiling; a GEMM of this size is launch- and latency-bound")
+            roof["frac_of_3xtf32_ceiling"] = round(top["achieved"] / 243.0, 4)
+        elif top["unit"] == "TFLOP/s":
             roof["note"] = "fp32 FFMA parity path; fp32 SIMT peak is 74.4 TFLOP/s -> frac_of_fp32_peak"
             roof["frac_of_fp32_peak"] = round(top["achieved"] / 74.4, 4)
 
