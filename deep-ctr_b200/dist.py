@@ -261,6 +261,9 @@ class ShardedStep(object):
 def attach_sharded(model, dist, X_global, group=None):
     """Switch a TF-form model built with `shard=(rank, world)` (its engine table holds the local rows only) to the
     row-sharded step.  'mean' reduce sees the GLOBAL batch; forward / predict become collective calls."""
+    from .engine import BagEngine
+    if isinstance(model.engine, BagEngine):
+        raise NotImplementedError("the SNN embedding-bag step has no row-sharded form yet")
     sh = ShardedStep(model.engine, dist, X_global, group)
     model.sharded = sh
     model.use_graph = False           # the split sizes of the all-to-alls are read on the host every step
@@ -279,6 +282,10 @@ def attach_sharded(model, dist, X_global, group=None):
 def attach(model, dist, group=None):
     """Switch a model (models.FM / FNN* / theano_fnn.FNN_wnzh) to data-parallel steps.  The reference's
     batch-size-dependent constants see the GLOBAL batch: 'mean' reduce and the decay 1-2*lambda*lr/b_size."""
+    from .engine import BagEngine
+    if isinstance(model.engine, BagEngine):
+        raise NotImplementedError("the SNN embedding-bag step has no data-parallel form yet (its bias is a vector and every field of a "
+                                  "sample shares one gradient row); run it on one GPU")
     dp = DataParallelStep(model.engine, dist, group)
     model.dp = dp
     # kernels AND collectives of a step replay as one CUDA graph (NCCL is capturable); DCTR_DP_GRAPH=0 issues them eagerly
