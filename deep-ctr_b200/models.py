@@ -188,6 +188,7 @@ class _Base(object):
         self._stage.upload()
         self._run_step()
         self._out_pinned.copy_(self.engine.out, non_blocking=True)
+        self._post_launch()            # host work that can overlap the step running on the device
         torch.cuda.current_stream().synchronize()
         return float(self._out_np[self.N]), self._out_np[:self.N].copy()
 
@@ -216,6 +217,7 @@ class _Base(object):
         d["y"].copy_(y)
         self._pre_step()
         self._run_step()
+        self._post_launch()
         return self._fetch_out()
 
     def _predict_chunks(self, ids, wts, out_dev=None):
@@ -254,6 +256,9 @@ class _Base(object):
         return device_metrics(preds, np.asarray(labels, dtype=np.float32).reshape(-1), device=self.engine.dev, nds_rate=nds_rate)
 
     def _pre_step(self):
+        pass
+
+    def _post_launch(self):
         pass
 
     def _swap_masks(self, masks):

@@ -83,11 +83,15 @@ class SNN(_Base):
     def _pre_step(self):
         if self.mask_streams is None:
             return
-        r1, r2 = self._next_masks if self._next_masks is not None else self.mask_streams.draw()
+        r1, r2 = self._next_masks if self._next_masks is not None else self.mask_streams.take()
         self._next_masks = None
         h = self._stage.host
         h["mask1"][:, :r1.shape[1]] = r1
         h["mask2"][:, :r2.shape[1]] = r2
+
+    def _post_launch(self):
+        if self.mask_streams is not None:
+            self.mask_streams.prefetch()
 
     def _device_step(self):
         # cost adds lambda1 * (|w1|^2 + |w2|^2 + |w3|^2 + |b|^2) (SNN_DAE.py:151-153): decay on the MLP, not on ww0 / bb0

@@ -150,3 +150,83 @@ def test_line_cursor_follows_the_reference_readers():
     cur = LineCursor(10, wrap=False)
     seen = [cur.next(4) for _ in range(7)]
     assert [None if s is None else s.tolist() for s in seen] == [[0, 1, 2, 3], [4, 5, 6, 7], None, [0, 1, 2, 3], [4, 5, 6, 7], None, [0, 1, 2, 3]]
+
+
+def test_mask_prefetch_keeps_the_stream_and_the_step_plumbing_runs():
+    """MaskStreams.take() hands out exactly the pairs draw() would have, however prefetch() calls are interleaved; and the
+    host side of a step (_finish_step: upload, launch, post-launch prefetch, fetch) runs end to end on fakes"""
+    from unittest import mock
+    from deepctr_b200.theano_fnn import FNN_wnzh, MaskStreams
+    a, b = MaskStreams(30, 10, 0.5), MaskStreams(30, 10, 0.5)
+    rng = np.random.default_rng(0)
+    for step in range(40):
+        if rng.random() < 0.6:
+            b.prefetch()
+        if rng.random() < 0.3:
+            b.prefetch()                          # a second call before the pair is taken draws nothing
+        ra, rb = a.draw(), b.take()
+        assert np.array_equal(ra[0], rb[0]) and np.array_equal(ra[1], rb[1])
+
+    class Stage:
+        def __init__(self):
+            self.host = {"mask1": np.zeros((1, 32), np.float32), "mask2": np.zeros((1, 12), np.float32)}
+            self.uploads = 0
+
+        def upload(self):
+            self.uploads += 1
+
+    class Eng:
+        out = torch.arange(12, dtype=torch.float32)
+
+    m = FNN_wnzh.__new__(FNN_wnzh)               # host plumbing only: no engine, no device
+    m.N, m._stage, m.engine, m.mask_streams, m._next_masks = 8, Stage(), Eng(), MaskStreams(30, 10, 0.5), None
+    m._out_pinned = torch.zeros(12)
+    m._out_np = m._out_pinned.numpy()
+    m._run_step = lambda: None
+    ref = MaskStreams(30, 10, 0.5)
+    with mock.patch("torch.cuda.current_stream") as cs:
+        for step in range(3):
+            m._pre_step()
+            want = ref.draw()
+            assert np.array_equal(m._stage.host["mask1"][0, :30], want[0][0]) and np.array_equal(m._stage.host["mask2"][0, :10], want[1][0])
+            loss, pred = m._finish_step()
+            assert loss == 8.0 and pred.tolist() == list(range(8)) and m.mask_streams._ahead is not None
+        assert cs.return_value.synchronize.call_count == 3 and m._stage.uploads == 3
+    m.set_masks(np.ones(30), np.zeros(10))        # an injected pair does not consume the stream
+    m._pre_step()
+    assert m._stage.host["mask1"][0, :30].all() and not m._stage.host["mask2"][0, :10].any()
+    m._pre_step()
+    want = ref.draw()
+    assert np.array_equal(m._stage.host["mask1"][0, :30], want[0][0])
+
+
+def test_device_fed_step_plumbing_runs_on_fakes():
+    """FNN_wnzh.train_step_device and the SNN mask hooks, host side only (CPU tensors stand in for the device blocks)"""
+    from unittest import mock
+    from deepctr_b200.snn import SNN
+    from deepctr_b200.theano_fnn import FNN_wnzh, MaskStreams
+
+    class Stage:
+        def __init__(self):
+            self.host = {"mask1": np.zeros((1, 32), np.float32), "mask2": np.zeros((1, 12), np.float32)}
+            self.dev = {k: torch.zeros(v.shape) for k, v in self.host.items()}
+
+    class Eng:
+        out = torch.arange(12, dtype=torch.float32)
+        y = torch.zeros(8)
+
+    for cls in (FNN_wnzh, SNN):
+        m = cls.__new__(cls)
+        m.N, m._stage, m.engine, m.mask_streams, m._next_masks = 8, Stage(), Eng(), MaskStreams(30, 10, 0.5), None
+        m._out_pinned = torch.zeros(12)
+        m._out_np = m._out_pinned.numpy()
+        m._run_step = lambda: None
+        m._pre_step()
+        m._post_launch()
+        assert m.mask_streams._ahead is not None
+        if cls is FNN_wnzh:
+            m.feats = torch.zeros(8, 16, dtype=torch.int32)
+            with mock.patch("torch.cuda.current_stream"):
+                loss, pred = m.train_step_device(torch.ones(8, 16, dtype=torch.int32), torch.ones(8))
+            assert loss == 8.0 and bool((m.feats == 1).all()) and bool((m.engine.y == 1).all())
+            assert np.array_equal(m._stage.dev["mask1"].numpy(), m._stage.host["mask1"])
