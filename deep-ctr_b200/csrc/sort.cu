@@ -4,6 +4,7 @@
 // __match_any_sync on top of per-warp running digit counters, across tiles from the look-back running in tile
 // order, so equal rows keep their (sample, field) order: that is what lets SEQ_DECAY reproduce the sample-major
 // loop of FNN_wnzh.py:300-306 and makes SUM bit-reproducible.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace dctr {
@@ -200,7 +201,17 @@ static int key_bits(int64_t X) {
 // pass costs ~8 us whatever it does: M = 65536, 20-bit keys: 36.8 -> 28.6 us); on a long one the wide pass loses more to
 // its 56 KB of shared memory, 10 ballots per key and 4 KB of look-back state per tile than the saved pass returns
 // (M = 16.7 M, 25-bit keys: 0.90 -> 1.19 ms), and at M = 1 M the two are equal.
+// DCTR_SORT_BITS = 8 / 9 / 10 forces the digit width (experiments: 9-bit digits sort 25-27-bit row ids in 3 passes instead of 4)
+static int forced_bits() {
+    static const int v = [] {
+        const char* e = getenv("DCTR_SORT_BITS");
+        const int b = e ? atoi(e) : 0;
+        return (b == 8 || b == 9 || b == 10) ? b : 0;
+    }();
+    return v;
+}
 static int radix_bits(int64_t X, int64_t M) {
+    if (forced_bits()) return forced_bits();
     const int bits = key_bits(X);
     return (M <= ((int64_t)1 << 18) && (bits + 9) / 10 < (bits + 7) / 8) ? 10 : 8;
 }
@@ -246,7 +257,8 @@ using namespace dctr;
 // ghist [kMaxPasses][kMaxRadix] | tickets [16] | status [passes][tiles][R]: 4 passes x 256 bins, or (short lists only)
 // 3 passes x 1024 bins
 static size_t sort_header_words(int64_t tiles) {
-    const size_t per_tile = tiles <= 128 ? (size_t)3 * kMaxRadix : (size_t)kMaxPasses * 256;
+    const size_t per_tile = forced_bits() ? (size_t)kMaxPasses << forced_bits()
+                                          : (tiles <= 128 ? (size_t)3 * kMaxRadix : (size_t)kMaxPasses * 256);
     return (size_t)kMaxPasses * kMaxRadix + 16 + per_tile * tiles;
 }
 
@@ -277,5 +289,6 @@ extern "C" int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t*
     const int rb = radix_bits(X, M), passes = num_passes(X, M), R = 1 << rb;
     cudaMemsetAsync(ghist, 0, (size_t)(kMaxPasses * kMaxRadix + 16 + (size_t)passes * tiles * R) * sizeof(unsigned), st);
     if (rb == 10) return run_sort<10>(ids, M, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
+    if (rb == 9) return run_sort<9>(ids, M, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
     return run_sort<8>(ids, M, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
 }
