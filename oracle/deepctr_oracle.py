@@ -298,6 +298,37 @@ class OracleNet:
         return loss, p
 
 
+    def train_step_theano_feats(self, feats, feat_field, y, lr, lambda_fm, masks=None, lambda1=0.0):
+        """The loop body FNN_wnzh.py:296-306 on per-sample FEATURE LISTS (ragged, as get_fxy returns them, :248-253), literal:
+        x is built by feats_to_layer_one_array (:87-96: slot = field of the feature, a later feature of the same field
+        overwrites the slot, a field without a feature stays 0), then EVERY feature of the sample -- the overwritten one
+        too -- is updated from the gradient of the slot of its field (:300-306).  self.table must end with one all-zero row
+        (the slot of an absent field); it is never updated."""
+        y = np.asarray(y, dtype=self.dtype)
+        N, F, d = len(feats), self.F, self.d
+        pad = self.table.shape[0] - 1
+        ids = np.full((N, F), pad, dtype=np.int64)
+        for t, ft in enumerate(feats):
+            for feat in ft:
+                ids[t, feat_field[feat]] = feat
+        logit, cache = self.forward(ids, None, masks)
+        p = sigmoid(logit)
+        loss = xent_with_logits(logit, y).sum() + lambda1 * ((self.Ws[-1] ** 2).sum() + (self.bs[-1] ** 2).sum())
+        dWs, dbs, _, _, gz = self.backward(cache, p - y)
+        dWs[-1] = dWs[-1] + 2 * lambda1 * self.Ws[-1]
+        dbs[-1] = dbs[-1] + 2 * lambda1 * self.bs[-1]
+        b_size = N
+        for t in range(b_size):
+            for feat in feats[t]:
+                o = 1 + feat_field[feat] * d
+                for l in range(d):
+                    self.table[feat, l] = self.table[feat, l] * (1 - 2. * lambda_fm * lr / b_size) - lr * gz[t, o + l]
+        for l in range(len(self.Ws)):
+            self.Ws[l] -= lr * dWs[l]
+            self.bs[l] -= lr * dbs[l]
+        return loss, p, dict(x=cache["z"], gx=gz, ids=ids)
+
+
 def seq_decay_scatter(table, ids, ge, lr, decay):
     """Vectorised equivalent of FNN_wnzh.py:300-306: per row, occurrences in (sample, field) order,
     w <- w*decay - lr*g.  Rounds of 'k-th occurrence of each row' keep the per-row order exact."""
