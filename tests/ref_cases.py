@@ -47,7 +47,9 @@ def tf_case(name, seed=7):
     if name in ("FM", "LR"):
         c.update(X_dim=40, X_feas=5, lam=0.01, rank=3 if name == "FM" else 0)
     else:
-        c.update(cat_sizes=np.array([9, 4, 17]), n_hidden={"FNN": 2, "FNN_IP_L3": 3, "FNN_OP_L3": 3, "FNN_IP_L5": 5, "FNN_IP_L7": 7}[name])
+        # ... and 26 categorical ones: the placeholders are declared [batch, 13] / [batch, 26] (FNN.py:41-43)
+        c.update(cat_sizes=np.array([9, 4, 17, 3, 5, 2, 6, 4, 3, 8, 2, 5, 3, 4, 7, 2, 3, 5, 4, 2, 6, 3, 4, 2, 5, 3]), N=4, E=3,
+                 n_hidden={"FNN": 2, "FNN_IP_L3": 3, "FNN_OP_L3": 3, "FNN_IP_L5": 5, "FNN_IP_L7": 7}[name])
         c["hidden"] = [10, 8, 7, 6, 5, 4, 3][:c["n_hidden"]]
         c["cross"] = "ip" if "IP" in name else ("op" if "OP" in name else "none")
     c["rng"] = rng

@@ -117,3 +117,178 @@ def test_fnn_wnzh_vectorised_scatter_equals_script(wnzh_run):
                 want[feat, l] = want[feat, l] * (1 - 2. * g["lambda_fm"] * g["lr"] / 100) - g["lr"] * gx[t, g["feat_layer_one_index"](feat, l)]
     close(table, want, 1e-12, 1e-15)
     close(table2, want, 1e-10, 1e-14)
+
+
+# ======================================================================================================================
+# TF generation: FM / LR / FNN / FNN_IP_L3 / L5 / L7 / FNN_OP_L3 graph builders on the tensorflow shim
+# ======================================================================================================================
+@pytest.fixture(scope="module")
+def tfm():
+    return ref_run.tf_modules()
+
+
+def _binary_masks(rng, keep, shapes):
+    return [np.floor(keep + rng.random(s)) for s in shapes]
+
+
+PTMZR = {"sgd": lambda r: ["sgd", 0.05, r], "adam": lambda r: ["adam", 0.01, 1e-8, r], "ftrl": lambda r: ["ftrl", 0.05, r]}
+
+
+@pytest.mark.parametrize("ptmzr", ["sgd", "adam", "ftrl"])
+@pytest.mark.parametrize("name", ["FM", "LR"])
+@pytest.mark.parametrize("reduce", ["sum", "mean"])
+def test_fm_lr_steps_equal_oracle(tfm, tmp_path, name, ptmzr, reduce):
+    tf = tfm["tf"]
+    c = C.tf_case(name)
+    rng, N, E, X, F, r, lam = c["rng"], c["N"], c["E"], c["X_dim"], c["X_feas"], c["rank"], c["lam"]
+    vm = {"W": rng.uniform(-0.3, 0.3, (X, 1)).astype(np.float32), "b": np.array([0.05], np.float32)}
+    if name == "FM":
+        vm["V"] = rng.uniform(-0.3, 0.3, (X, r)).astype(np.float32)
+    path = C.dump_pickle(vm, str(tmp_path / "init.pickle"))
+    pt = PTMZR[ptmzr](reduce)
+    rch = [X, F, r] if name == "FM" else [X, F]
+    model = getattr(tfm[name], name)(N, rch, ["uniform", -1, 1, [1, 2], path], pt, [lam], "train", E)
+    table = np.concatenate([vm["W"], vm["V"]], 1) if name == "FM" else vm["W"]
+    ofm = O.OracleFM(table, vm["b"][0])
+    with tf.Session(graph=model.graph) as sess:
+        tf.initialize_all_variables().run()
+        for step in range(3):
+            ids = rng.integers(0, X, (N, F))
+            ids[1] = ids[0]
+            ids[:, -1] = X - 1                                    # the padded slot of ipinyou.py:58-59: id = X_dim - 1, weight 0
+            wts = rng.uniform(0.5, 1.5, (N, F)).astype(np.float32)
+            wts[:, -1] = 0
+            y = rng.integers(0, 2, N)
+            _, l, p = sess.run([model.ptmzr, model.loss, model.train_preds],
+                               feed_dict={model.sp_id_hldr: ids.flatten(), model.sp_wt_hldr: wts.flatten(), model.lbl_hldr: y})
+            if ptmzr == "sgd":
+                ol, op = ofm.train_step(ids, wts, y, pt[1], lam, reduce)
+            elif ptmzr == "adam":
+                ol, op = ofm.train_step_adam(ids, wts, y, pt[1], pt[2], lam, reduce)
+            else:
+                ol, op = ofm.train_step_ftrl(ids, wts, y, pt[1], lam, reduce)
+            close(l, ol, 1e-10)
+            close(p, op, 1e-10)
+        eids, ewts = rng.integers(0, X, (E, F)), rng.uniform(0.5, 1.5, (E, F)).astype(np.float32)
+        wt_h = model.eval_wts_hldr if name == "FM" else model.eval_wt_hldr          # FM.py:45 vs LR.py:44
+        ep = model.eval_preds.eval(feed_dict={model.eval_id_hldr: eids.flatten(), wt_h: ewts.flatten()})
+        close(ep, ofm.predict(eids, ewts), 1e-10)
+        model.dump(str(tmp_path / "out.pickle"))
+        with pytest.raises(IndexError):                           # TF: InvalidArgument for an id outside the table
+            bad = eids.copy()
+            bad[0, 0] = X
+            model.eval_preds.eval(feed_dict={model.eval_id_hldr: bad.flatten(), wt_h: ewts.flatten()})
+    with open(str(tmp_path / "out.pickle"), "rb") as f:
+        out = pickle.load(f)
+    got = np.concatenate([out["W"], out["V"]], 1) if name == "FM" else out["W"]
+    close(got, ofm.table, 1e-9)
+    close(out["b"], [ofm.b], 1e-9)
+
+
+def run_fnn_case(tfm, tmp_path, name, ptmzr="sgd", keep=1.0, reduce="sum", act="tanh", record=None):
+    """3 optimiser steps + eval + dump of one FNN-family class of the reference against the oracle; `record` (a dict)
+    receives every input and output (tests/golden/make_golden_ref.py)."""
+    tf = tfm["tf"]
+    c = C.tf_case(name)
+    c["act"] = act
+    rng, N, E = c["rng"], c["N"], c["E"]
+    cat_sizes, offsets, X_dim, X_feas, d, cw = C.fnn_geometry(c)
+    vm, dims = C.fnn_var_map(c)
+    path = C.dump_pickle(vm, str(tmp_path / "init.pickle"))
+    pt = PTMZR[ptmzr](reduce)
+    rch = [X_dim, X_feas, c["rank"]] + c["hidden"] + [act]
+    cls = getattr(tfm[name], name)
+    model = cls(cat_sizes, offsets, N, rch, ["uniform", -1, 1, list(range(1, 20)), path], pt, [keep], "train", E)
+    nl = len(dims) - 1
+    net = O.OracleNet(np.concatenate([vm["W"], vm["V"]], 1), vm["b"][0], [vm["h%d_w" % (i + 1)] for i in range(nl)],
+                      [vm["h%d_b" % (i + 1)] for i in range(nl)], X_feas, d, c["cross"], False, act, act)
+    mrng = np.random.default_rng(99)
+    shapes = [(N, w) for w in dims[:-1]]
+    rec = record if record is not None else {}
+    rec.update(init=vm, cat_sizes=cat_sizes, offsets=np.asarray(offsets), rch=rch, ptmzr=pt, keep=keep, steps=[])
+    with tf.Session(graph=model.graph) as sess:
+        tf.initialize_all_variables().run()
+        for step in range(c["steps"]):
+            v_wts, c_ids, c_wts, y = C.fnn_batch(c, N)
+            binm = _binary_masks(mrng, keep, shapes) if keep < 1 else None
+            tf.DROPOUT_HOOK = (lambda shape, kp, k: binm[k]) if keep < 1 else None
+            _, l, p = sess.run([model.ptmzr, model.loss, model.train_preds],
+                               feed_dict={model.v_wt_hldr: v_wts, model.c_id_hldr: c_ids, model.c_wt_hldr: c_wts, model.lbl_hldr: y})
+            tf.DROPOUT_HOOK = None
+            g_ids = np.concatenate([np.broadcast_to(np.arange(13), (N, 13)), c_ids + np.asarray(offsets)], 1)
+            g_wts = np.concatenate([v_wts, c_wts], 1)
+            masks = [m / keep for m in binm] if keep < 1 else None
+            if ptmzr == "sgd":
+                ol, op = net.train_step_tf(g_ids, g_wts, y, pt[1], masks, reduce)
+            elif ptmzr == "adam":
+                ol, op = net.train_step_tf_adam(g_ids, g_wts, y, pt[1], pt[2], masks, reduce)
+            else:
+                ol, op = net.train_step_tf_ftrl(g_ids, g_wts, y, pt[1], masks, reduce)
+            close(l, ol, 1e-9)
+            close(p, op, 1e-9)
+            rec["steps"].append(dict(v_wts=v_wts, c_ids=c_ids, c_wts=c_wts, y=y, masks=masks, loss=float(l), preds=np.asarray(p)))
+        # eval graph: GLOBAL ids [E, X_feas], offsets subtracted in-graph (FNN.py:65-69), no dropout
+        v_wts, c_ids, c_wts, _ = C.fnn_batch(c, E)
+        g_ids = np.concatenate([np.broadcast_to(np.arange(13), (E, 13)), c_ids + np.asarray(offsets)], 1)
+        g_wts = np.concatenate([v_wts, c_wts], 1)
+        ep = model.eval_preds.eval(feed_dict={model.eval_id_hldr: g_ids, model.eval_wts_hldr: g_wts})
+        close(ep, net.predict(g_ids, g_wts), 1e-9)
+        rec.update(eval_ids=g_ids, eval_wts=g_wts, eval_preds=np.asarray(ep))
+        model.dump(str(tmp_path / "out.pickle"))
+    with open(str(tmp_path / "out.pickle"), "rb") as f:
+        out = pickle.load(f)
+    rec["final"] = out
+    close(np.concatenate([out["W"], out["V"]], 1), net.table, 1e-8, 1e-12)
+    close(out["b"], [net.bias], 1e-8, 1e-12)
+    for i in range(nl):
+        close(out["h%d_w" % (i + 1)], net.Ws[i], 1e-8, 1e-12)
+        close(out["h%d_b" % (i + 1)], net.bs[i], 1e-8, 1e-12)
+    if c["cross"] != "op":
+        assert model.log.startswith("input dim: %d, features: %d, rank: %d, embedding: %d" % (X_dim, X_feas, c["rank"], dims[0]))
+    return rec
+
+
+@pytest.mark.parametrize("name", ["FNN", "FNN_IP_L3", "FNN_IP_L5", "FNN_IP_L7"])
+@pytest.mark.parametrize("ptmzr,keep,reduce,act", [("sgd", 1.0, "sum", "tanh"), ("sgd", 0.5, "mean", "relu"), ("adam", 0.5, "sum", "sigmoid"),
+                                                    ("ftrl", 1.0, "sum", "tanh")])
+def test_fnn_family_steps_equal_oracle(tfm, tmp_path, name, ptmzr, keep, reduce, act):
+    """the reference's own graph-building code (pair order, concat order, bias column last, activation applied to the
+    layer INPUT incl. z1 (Q7), dropout on every layer input) against the oracle, 3 optimiser steps + eval + dump."""
+    run_fnn_case(tfm, tmp_path, name, ptmzr, keep, reduce, act)
+
+
+def test_fnn_op_l3_declared_width_defect(tfm, tmp_path):
+    """FNN_OP_L3.py:18,24 declares h1_w with P = F(F-1)/2 cross columns while forward() produces d*d (:93-100).  The
+    placeholders fix F = 39 (P = 741, never a square), so with the DECLARED shape the reference's own matmul fails on
+    every configuration ..."""
+    tf = tfm["tf"]
+    c = C.tf_case("FNN_OP_L3")
+    cat_sizes, offsets, X_dim, X_feas, d, cw = C.fnn_geometry(c)
+    P = X_feas * (X_feas - 1) // 2
+    assert d * d != P
+    vm, dims = C.fnn_var_map(c, declared_width=X_feas * d + P + 1)
+    path = C.dump_pickle(vm, str(tmp_path / "init.pickle"))
+    model = tfm["FNN_OP_L3"].FNN_OP_L3(cat_sizes, offsets, c["N"], [X_dim, X_feas, c["rank"]] + c["hidden"] + ["tanh"],
+                                      ["uniform", -1, 1, list(range(1, 20)), path], ["sgd", 0.05, "sum"], [1.0], "train", c["E"])
+    assert ("embedding: %d" % (X_feas * d + P + 1)) in model.log
+    v_wts, c_ids, c_wts, y = C.fnn_batch(c, c["N"])
+    with tf.Session(graph=model.graph) as sess:
+        tf.initialize_all_variables().run()
+        with pytest.raises(ValueError, match="matmul"):
+            sess.run([model.ptmzr, model.loss], feed_dict={model.v_wt_hldr: v_wts, model.c_id_hldr: c_ids, model.c_wt_hldr: c_wts,
+                                                           model.lbl_hldr: y})
+
+
+@pytest.mark.parametrize("ptmzr,keep", [("sgd", 1.0), ("adam", 0.5)])
+def test_fnn_op_l3_true_width_equals_oracle(tfm, tmp_path, ptmzr, keep):
+    """... but init_var_map takes a checkpointed h1_w as it is (tf_util.py:43-45), so a pickle whose h1_w has the
+    forward's TRUE width F*d + d*d + 1 makes the reference's own OP graph run: that is the build's sizing (Q2), and there
+    the reference equals the oracle (outer products summed over pairs i<j, flattened row-major)."""
+    run_fnn_case(tfm, tmp_path, "FNN_OP_L3", ptmzr, keep, "sum", "tanh")
+
+
+def test_build_inds(tfm):
+    """tf_util.py:7-12: COO indices, sample-major -- the flat [N*F] order of sp_id_hldr."""
+    inds = tfm["tf_util"].build_inds(3, 4)
+    assert inds.shape == (12, 2)
+    assert (inds[:, 0] * 4 + inds[:, 1] == np.arange(12)).all()
