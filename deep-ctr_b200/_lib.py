@@ -24,12 +24,15 @@ SIGNATURES = {
     "dctr_launch_count": (ctypes.c_longlong, []),
     "dctr_gather_concat_fwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
     "dctr_arrange_fields": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
+    "dctr_arrange_update_list": (_i, [_p, _p, _i, _i, _i, _l, _i, _p, _p, _p, _p, _p]),
+    "dctr_set_id_status": (_i, [_p]),
     "dctr_gather_rows": (_i, [_p, _p, _l, _i, _l, _p, _p]),
     "dctr_host_pack_fields": (_i, [_p, _i, _p, _p, _p, _l, _i, _i, _p, _p, _i]),
     "dctr_cross_bwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
     "dctr_fm_fwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _p, _p, _f, _p, _p, _p, _p, _p, _i, _p]),
     "dctr_sort_rows_workspace": (_z, [_l]),
     "dctr_sort_rows": (_i, [_p, _l, _l, _p, _p, _p, _z, _p]),
+    "dctr_sort_pairs": (_i, [_p, _p, _l, _l, _p, _p, _p, _z, _p]),
     "dctr_scatter_workspace": (_z, [_l, _i]),
     "dctr_scatter_sgd": (_i, [_i, _p, _p, _l, _i, _i, _p, _l, _i, _p, _f, _f, _p, _l, _i, _p, _z, _p]),
     "dctr_scatter_sgd_masked": (_i, [_i, _p, _p, _l, _i, _i, _p, _l, _i, _i, _f, _f, _p, _l, _i, _p, _z, _p]),
@@ -85,7 +88,7 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(h, name)
             fn.restype, fn.argtypes = res, args
-        if h.dctr_version() != 1:
+        if h.dctr_version() != 2:
             raise RuntimeError("libdctr.so version mismatch")
         _lib = h
     return _lib
@@ -96,7 +99,7 @@ PROFILE = None   # bench.py sets this to a list; every call then appends (name, 
 
 def call(name, *args):
     """Invoke an int-returning entry point; raise RuntimeError with dctr_last_error() on failure."""
-    if PROFILE is not None and name not in ("dctr_set_launch_mode", "dctr_host_pack_fields"):      # host-only entry points
+    if PROFILE is not None and name not in ("dctr_set_launch_mode", "dctr_host_pack_fields", "dctr_set_id_status"):      # host-only entry points
         import torch
         st = torch.cuda.current_stream()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

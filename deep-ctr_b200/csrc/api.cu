@@ -24,6 +24,9 @@ int pdl_mode() {
     return env >= 0 ? env : g_pdl;
 }
 
+static thread_local int32_t* g_id_status = nullptr;
+int32_t* id_status() { return g_id_status; }
+
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 // Called right after a <<<>>> launch: picks up launch-configuration errors without synchronising.
@@ -47,6 +50,7 @@ int dctr_set_launch_mode(int mode) {
     dctr::g_pdl = mode;
     return DCTR_OK;
 }
+int dctr_set_id_status(int32_t* status) { dctr::g_id_status = status; return DCTR_OK; }
 const char* dctr_last_error(void) { return dctr::g_err; }
 long long dctr_launch_count(void) { return dctr::g_launches.load(); }
 }

@@ -12,7 +12,8 @@ constexpr int kBagWarps = 8;
 
 __global__ void __launch_bounds__(kBagWarps * 32)
 bag_fwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts, const float* __restrict__ table, int ld,
-               int N, int F, int H, const float* __restrict__ b0, int act, float* __restrict__ out, int ldo, bool vec) {
+               int N, int F, int H, const float* __restrict__ b0, int act, float* __restrict__ out, int ldo, bool vec,
+               int X, int32_t* __restrict__ status) {
     pdl_sync();
     const int lane = threadIdx.x & 31;
     const int n = blockIdx.x * kBagWarps + (threadIdx.x >> 5);
@@ -30,7 +31,7 @@ bag_fwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts, c
         for (int f0 = 0; f0 < F; f0 += 8) {
             int id[8];
             float w[8];
-            load_fields8(ids, wts, pbase, f0, F, vec, id, w);
+            load_fields8(ids, wts, pbase, f0, F, vec, id, w, X, status);
             float4 r[8];
 #pragma unroll
             for (int k = 7; k >= 0; --k) r[k] = ldg_f4_issue(table + (int64_t)id[k] * ld + c, on && f0 + k < F);
@@ -61,6 +62,6 @@ extern "C" int dctr_bag_fwd(const int32_t* ids, const float* wts, const float* t
     DCTR_REQUIRE((((uintptr_t)table | (uintptr_t)out) & 15) == 0, "bag_fwd: table / out must be 16-byte aligned");
     const bool vec = (F & 3) == 0 && ((uintptr_t)ids & 15) == 0 && (!wts || ((uintptr_t)wts & 15) == 0);
     launch_k(bag_fwd_kernel, ceil_div(N, kBagWarps), kBagWarps * 32, 0, as_stream(stream), ids, wts, table, ld, N, F, H, b0, act,
-             out, ldo, vec);
+             out, ldo, vec, (int)X, id_status());
     return check_launch("bag_fwd_kernel");
 }

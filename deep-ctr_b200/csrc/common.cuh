@@ -34,6 +34,7 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_sync() { pdl_wait(); pdl_launch_dependents(); }
 int pdl_mode();          // 0 = off, 1 = every kernel, 2 (default) = every kernel but the tensor-core GEMM
+int32_t* id_status();    // device words {count of out-of-range ids, one offending id} of the calling thread, or nullptr (api.cu)
 
 template <class... KArgs, class... Args>
 static inline void launch_k_mode(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
@@ -101,10 +102,21 @@ __device__ __forceinline__ float4 ldg_f4_issue(const float* p) {
     return v;
 }
 
+// Row ids come from data files: an id outside [0, X) (a forgotten -1 pad, a test-set feature above the training maximum) is
+// counted in the caller's status words (dctr_set_id_status) and READ as row 0, so it can never address memory outside the
+// table -- TensorFlow raises InvalidArgument for these; the host side raises after the step.
+__device__ __forceinline__ int checked_id(int id, int X, int32_t* __restrict__ status) {
+    if ((unsigned)id >= (unsigned)X) {
+        if (status) { atomicAdd(status, 1); status[1] = id; }
+        return 0;
+    }
+    return id;
+}
+
 // ids / weights of 8 consecutive fields [f0, f0+8) of one sample (row-major [N, F] arrays, pbase = n*F); slots past F
 // get id 0 / weight 0.  `vec`: F % 4 == 0 and 16-byte aligned arrays, so the 8 values are two 128-bit loads.
 __device__ __forceinline__ void load_fields8(const int32_t* __restrict__ ids, const float* __restrict__ wts, int64_t pbase,
-                                             int f0, int F, bool vec, int (&id)[8], float (&w)[8]) {
+                                             int f0, int F, bool vec, int (&id)[8], float (&w)[8], int X, int32_t* __restrict__ status) {
     if (vec && f0 + 8 <= F) {
         const int4 a = __ldg(reinterpret_cast<const int4*>(ids + pbase + f0)), b = __ldg(reinterpret_cast<const int4*>(ids + pbase + f0) + 1);
         id[0] = a.x; id[1] = a.y; id[2] = a.z; id[3] = a.w; id[4] = b.x; id[5] = b.y; id[6] = b.z; id[7] = b.w;
@@ -123,6 +135,8 @@ __device__ __forceinline__ void load_fields8(const int32_t* __restrict__ ids, co
             w[k] = ok ? (wts ? __ldg(wts + pbase + f0 + k) : 1.f) : 0.f;
         }
     }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) id[k] = checked_id(id[k], X, status);
 }
 
 __device__ __forceinline__ float4 ld_f4_issue(const float* p, bool pred) {      // plain (coherent) load, predicated

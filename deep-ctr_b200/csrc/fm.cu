@@ -13,7 +13,7 @@ __global__ void __launch_bounds__(kFmThreads)
 fm_fwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts, const float* __restrict__ table,
               int ld, int N, int F, int d, const float* __restrict__ bias, const float* __restrict__ y,
               float gscale, float* __restrict__ logit, float* __restrict__ pred, float* __restrict__ loss_n,
-              float* __restrict__ g, float* __restrict__ s, int lds, int vec) {
+              float* __restrict__ g, float* __restrict__ s, int lds, int vec, int X, int32_t* __restrict__ status) {
     pdl_sync();
     const int q = threadIdx.x & 3;
     const float b = bias ? __ldg(bias) : 0.f;
@@ -29,7 +29,7 @@ fm_fwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts, co
                 const int64_t pbase = n * F;
                 for (int f0 = 0; f0 < F; f0 += 8) {
                     int id[8]; float w[8]; float4 v[8];
-                    load_fields8(ids, wts, pbase, f0, F, vec, id, w);
+                    load_fields8(ids, wts, pbase, f0, F, vec, id, w, X, status);
 #pragma unroll
                     for (int k = 0; k < 8; ++k) v[k] = ldg_f4_issue(table + (int64_t)id[k] * ld + c0);
 #pragma unroll
@@ -69,7 +69,7 @@ extern "C" int dctr_fm_fwd(const int32_t* ids, const float* wts, const float* ta
                            int N, int F, int d, const float* bias, const float* y, float gscale,
                            float* logit, float* pred, float* loss_n, float* g, float* s, int lds, void* stream) {
     DCTR_REQUIRE(ids && table, "fm_fwd: null pointer");
-    DCTR_REQUIRE(N >= 0 && F > 0 && d > 0 && d <= ld && (ld & 3) == 0 && X > 0, "fm_fwd: bad shape N=%d F=%d d=%d ld=%d", N, F, d, ld);
+    DCTR_REQUIRE(N >= 0 && F > 0 && d > 0 && d <= ld && (ld & 3) == 0 && X > 0 && X < ((int64_t)1 << 31), "fm_fwd: bad shape N=%d F=%d d=%d ld=%d", N, F, d, ld);
     DCTR_REQUIRE(!s || lds >= d, "fm_fwd: lds=%d < d=%d", lds, d);
     if (N == 0) return DCTR_OK;
     DCTR_REQUIRE(((uintptr_t)table & 15) == 0 && (!s || (((uintptr_t)s & 15) == 0 && (lds & 3) == 0 && lds >= ld)),
@@ -78,6 +78,6 @@ extern "C" int dctr_fm_fwd(const int32_t* ids, const float* wts, const float* ta
     int blocks = ceil_div(N, kFmThreads / 4);
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
     launch_k(fm_fwd_kernel, blocks, kFmThreads, 0, as_stream(stream), ids, wts, table, ld, N, F, d, bias, y, gscale,
-                                                                 logit, pred, loss_n, g, s, lds, vec);
+                                                                 logit, pred, loss_n, g, s, lds, vec, (int)X, id_status());
     return check_launch("fm_fwd_kernel");
 }

@@ -13,14 +13,14 @@ constexpr int kGatherWarps = 8;
 // stage e[f][0:ld) = w_f * table[id_f][0:ld) for one sample into this warp's smem block
 __device__ __forceinline__ void stage_field_block(const int32_t* __restrict__ ids, const float* __restrict__ wts,
                                                   const float* __restrict__ table, int ld, int F, int64_t n,
-                                                  int lane, float* e) {
+                                                  int lane, float* e, int X, int32_t* __restrict__ status) {
     const int Q = ld >> 2;
     const int T = F * Q;
     for (int t = lane; t < T; t += 32) {
         const int f = t / Q;
         const int q = t - f * Q;
         const int64_t p = n * F + f;
-        const int64_t id = ids[p];
+        const int64_t id = checked_id(ids[p], X, status);
         const float w = wts ? wts[p] : 1.f;
         float4 v = ldg_f4(table + id * ld + q * 4);
         v.x *= w; v.y *= w; v.z *= w; v.w *= w;
@@ -40,7 +40,8 @@ template <int CROSS>
 __global__ void __launch_bounds__(kGatherWarps * 32)
 gather_concat_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
                      const float* __restrict__ table, int ld, int N, int F, int d, int bias_first,
-                     const float* __restrict__ bias, int act0, float* __restrict__ out, int ldz, int warps, int vec) {
+                     const float* __restrict__ bias, int act0, float* __restrict__ out, int ldz, int warps, int vec,
+                     int X, int32_t* __restrict__ status) {
     pdl_sync();
     extern __shared__ __align__(16) float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -73,7 +74,7 @@ gather_concat_kernel(const int32_t* __restrict__ ids, const float* __restrict__ 
                 const int c0 = qq * 4;
                 for (int f0 = 0; f0 < F; f0 += 8) {
                     int id[8]; float w[8]; float4 v[8];
-                    load_fields8(ids, wts, pbase, f0, F, vec, id, w);
+                    load_fields8(ids, wts, pbase, f0, F, vec, id, w, X, status);
 #pragma unroll
                     for (int k = 0; k < 8; ++k) v[k] = ldg_f4_issue(table + (int64_t)id[k] * ld + c0);
 #pragma unroll
@@ -152,7 +153,7 @@ template <int CROSS>
 __global__ void __launch_bounds__(kGatherWarps * 32)
 cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts, const float* __restrict__ table,
                  int ld, int N, int F, int d, const float* __restrict__ dz, int ldz,
-                 float* __restrict__ ge, int ldg) {
+                 float* __restrict__ ge, int ldg, int X, int32_t* __restrict__ status) {
     pdl_sync();
     extern __shared__ __align__(16) float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -169,7 +170,7 @@ cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
         const float* dzr = dz + n * (int64_t)ldz;
         if (CROSS != DCTR_CROSS_NONE) {
             for (int t = lane; t < crossw; t += 32) dc[t] = dzr[Fd + t];
-            stage_field_block(ids, wts, table, ld, F, n, lane, e);   // ends with __syncwarp
+            stage_field_block(ids, wts, table, ld, F, n, lane, e, X, status);   // ends with __syncwarp
         }
         if (CROSS == DCTR_CROSS_OP) {
             for (int c = lane; c < d; c += 32) {
@@ -213,9 +214,13 @@ cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
 // K0: slot of a feature = its field (feats_to_layer_one_array, FNN_wnzh.py:91-95).  One warp per sample: lanes fill the
 // row with (pad_row, 0), then lane j places feature j; when several features of one sample share a field the highest j
 // wins (__match_any_sync picks it), which is the reference loop's "later feature overwrites".
+// upd_rows / upd_pos (optional, [N, J]): the UPDATE list of the sample -- the reference's scatter loops over every feature
+// of the sample, the overwritten ones included, and gives each the gradient of its field's slot (FNN_wnzh.py:300-306):
+// entry j = (feature id, n * F + field); absent / unknown features become (pad_row, n * F), which the fold skips.
 __global__ void __launch_bounds__(256)
 arrange_fields_kernel(const int32_t* __restrict__ feats, const int32_t* __restrict__ feat_field, int N, int J, int F,
-                      int32_t pad_row, int32_t* __restrict__ ids, float* __restrict__ wts) {
+                      int32_t X, int32_t pad_row, int32_t* __restrict__ ids, float* __restrict__ wts,
+                      int32_t* __restrict__ upd_rows, int32_t* __restrict__ upd_pos, int32_t* __restrict__ status) {
     pdl_sync();
     const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (n >= N) return;
@@ -229,24 +234,34 @@ arrange_fields_kernel(const int32_t* __restrict__ feats, const int32_t* __restri
         const int32_t feat = j < J ? frow[j] : -1;
         int slot = -1 - lane;                     // invalid lanes: private keys
         if (feat >= 0) {
-            const int s = __ldg(feat_field + feat);
-            if (s >= 0 && s < F) slot = s;
+            if (feat < X) {
+                const int s = __ldg(feat_field + feat);
+                if (s >= 0 && s < F) slot = s;
+            } else if (status) {                  // a feature id the FM model does not have (KeyError in the reference)
+                atomicAdd(status, 1);
+                status[1] = feat;
+            }
         }
         const unsigned peers = __match_any_sync(0xffffffffu, slot);
         if (slot >= 0 && (31 - __clz(peers)) == lane) { irow[slot] = feat; wrow[slot] = 1.f; }
+        if (upd_rows && j < J) {
+            upd_rows[(int64_t)n * J + j] = slot >= 0 ? feat : pad_row;
+            upd_pos[(int64_t)n * J + j] = n * F + (slot >= 0 ? slot : 0);
+        }
     }
 }
 
 // Row gather out[i, :] = table[ids[i], :] -- the owner-side lookup of the row-sharded table and the
 // permutation of gradient rows into exchange order.  One thread per 128-bit piece of a row.
 __global__ void __launch_bounds__(256)
-gather_rows_kernel(const int32_t* __restrict__ ids, const float4* __restrict__ table, int q, int64_t M, float4* __restrict__ out) {
+gather_rows_kernel(const int32_t* __restrict__ ids, const float4* __restrict__ table, int q, int64_t M, float4* __restrict__ out,
+                   int X, int32_t* __restrict__ status) {
     pdl_sync();
     const int64_t total = M * q;
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = t / q;
         const int c = (int)(t - i * q);
-        out[t] = __ldg(table + (int64_t)__ldg(ids + i) * q + c);
+        out[t] = __ldg(table + (int64_t)checked_id(__ldg(ids + i), X, c == 0 ? status : nullptr) * q + c);
     }
 }
 
@@ -268,7 +283,7 @@ extern "C" int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, cons
     DCTR_REQUIRE(cross >= 0 && cross <= 2 && !(cross && bias_first), "gather_concat_fwd: bad cross/bias_first");
     const int crossw = cross == DCTR_CROSS_IP ? F * (F - 1) / 2 : (cross == DCTR_CROSS_OP ? d * d : 0);
     DCTR_REQUIRE(ldz >= F * d + crossw + 1, "gather_concat_fwd: ldz=%d < D0=%d", ldz, F * d + crossw + 1);
-    DCTR_REQUIRE(X > 0 && X * (int64_t)ld < ((int64_t)1 << 40), "gather_concat_fwd: bad X");
+    DCTR_REQUIRE(X > 0 && X < ((int64_t)1 << 31) && X * (int64_t)ld < ((int64_t)1 << 40), "gather_concat_fwd: bad X");
     if (N == 0) return DCTR_OK;
     DCTR_REQUIRE((ldz & 3) == 0 && ((uintptr_t)out & 15) == 0 && ((uintptr_t)table & 15) == 0,
                  "gather_concat_fwd: out / table must be 16-byte aligned and ldz a multiple of 4");
@@ -290,7 +305,7 @@ extern "C" int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, cons
         if (smem > 48 * 1024)                                                                                \
             cudaFuncSetAttribute(gather_concat_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         launch_k(gather_concat_kernel<C>, grid, block, smem, st, ids, wts, table, ld, N, F, d, bias_first, bias,   \
-                                                           act0, out, ldz, warps, vec);                      \
+                                                           act0, out, ldz, warps, vec, (int)X, id_status()); \
     } while (0)
     if (cross == DCTR_CROSS_IP) LAUNCH_G(DCTR_CROSS_IP);
     else if (cross == DCTR_CROSS_OP) LAUNCH_G(DCTR_CROSS_OP);
@@ -316,7 +331,7 @@ extern "C" int dctr_cross_bwd(const int32_t* ids, const float* wts, const float*
     do {                                                                                                     \
         if (smem > 48 * 1024)                                                                                \
             cudaFuncSetAttribute(cross_bwd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        launch_k(cross_bwd_kernel<C>, grid, block, smem, st, ids, wts, table, ld, N, F, d, dz, ldz, ge, ldg);      \
+        launch_k(cross_bwd_kernel<C>, grid, block, smem, st, ids, wts, table, ld, N, F, d, dz, ldz, ge, ldg, (int)X, id_status()); \
     } while (0)
     if (cross == DCTR_CROSS_IP) LAUNCH_B(DCTR_CROSS_IP);
     else if (cross == DCTR_CROSS_OP) LAUNCH_B(DCTR_CROSS_OP);
@@ -327,10 +342,18 @@ extern "C" int dctr_cross_bwd(const int32_t* ids, const float* wts, const float*
 
 extern "C" int dctr_arrange_fields(const int32_t* feats, const int32_t* feat_field, int N, int J, int F, int32_t pad_row,
                                    int32_t* ids, float* wts, void* stream) {
-    DCTR_REQUIRE(N >= 0 && J > 0 && F > 0, "arrange_fields: bad shape N=%d J=%d F=%d", N, J, F);
+    return dctr_arrange_update_list(feats, feat_field, N, J, F, (int64_t)1 << 30, pad_row, ids, wts, nullptr, nullptr, stream);
+}
+
+extern "C" int dctr_arrange_update_list(const int32_t* feats, const int32_t* feat_field, int N, int J, int F, int64_t X,
+                                        int32_t pad_row, int32_t* ids, float* wts, int32_t* upd_rows, int32_t* upd_pos,
+                                        void* stream) {
+    DCTR_REQUIRE(N >= 0 && J > 0 && F > 0 && X > 0 && X <= ((int64_t)1 << 30) && (int64_t)N * F < ((int64_t)1 << 31),
+                 "arrange_fields: bad shape N=%d J=%d F=%d", N, J, F);
     if (N == 0) return DCTR_OK;
-    DCTR_REQUIRE(feats && feat_field && ids && wts, "arrange_fields: null pointer");
-    launch_k(arrange_fields_kernel, ceil_div((int64_t)N * 32, 256), 256, 0, as_stream(stream), feats, feat_field, N, J, F, pad_row, ids, wts);
+    DCTR_REQUIRE(feats && feat_field && ids && wts && (!upd_rows == !upd_pos), "arrange_fields: null pointer");
+    launch_k(arrange_fields_kernel, ceil_div((int64_t)N * 32, 256), 256, 0, as_stream(stream), feats, feat_field, N, J, F, (int32_t)X,
+             pad_row, ids, wts, upd_rows, upd_pos, id_status());
     return check_launch("arrange_fields_kernel");
 }
 
@@ -341,6 +364,6 @@ extern "C" int dctr_gather_rows(const int32_t* ids, const float* table, int64_t 
     int blocks = ceil_div(M * (ld / 4), 256);
     if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
     launch_k(gather_rows_kernel, blocks, 256, 0, as_stream(stream), ids, reinterpret_cast<const float4*>(table), ld / 4, M,
-                                                              reinterpret_cast<float4*>(out));
+                                                              reinterpret_cast<float4*>(out), (int)X, id_status());
     return check_launch("gather_rows_kernel");
 }

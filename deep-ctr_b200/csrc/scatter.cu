@@ -41,6 +41,7 @@ struct FoldArgs {
     const int32_t* rows; const int32_t* pos; int64_t M;
     int F; uint64_t fmul;          // n = p / F  ==  (p * fmul) >> 40 when fmul != 0 (F < 512, p < 2^31)
     int d, ld, col0;
+    int X;                         // rows >= X (the sort's sentinel for out-of-range ids) are folded but never read or written
     int skip_row;                  // segments of this row are folded but never written (-1: none) -- the pad row of absent fields
     float lr, decay;
     float* table;                  // rows are READ from here ...
@@ -133,8 +134,12 @@ fold_tile_kernel(const FoldArgs a) {
             p[j] = ok ? __ldg(a.pos + k0 + j) : 0;
         }
     }
-    const int prev = (k0 > 0 && k0 <= a.M) ? __ldg(a.rows + k0 - 1) : -1;
-    const int next = (k0 + kC < a.M) ? __ldg(a.rows + k0 + kC) : -1;
+#pragma unroll
+    for (int j = 0; j < kC; ++j) if (r[j] >= a.X) r[j] = -1;       // sentinel tail of the sorted list == past the end
+    int prev = (k0 > 0 && k0 <= a.M) ? __ldg(a.rows + k0 - 1) : -1;
+    int next = (k0 + kC < a.M) ? __ldg(a.rows + k0 + kC) : -1;
+    if (prev >= a.X) prev = -1;
+    if (next >= a.X) next = -1;
     unsigned head = 0, tail = 0, valid = 0;
 #pragma unroll
     for (int j = 0; j < kC; ++j) {
@@ -393,14 +398,14 @@ static int scatter_sgd_impl(int mode, const int32_t* sorted_rows, const int32_t*
                             float decay, float* table, int64_t X, int ld, void* workspace,
                             size_t workspace_bytes, void* stream) {
     DCTR_REQUIRE(mode == DCTR_SCATTER_SUM || mode == DCTR_SCATTER_SEQ_DECAY, "scatter_sgd: bad mode %d", mode);
-    DCTR_REQUIRE(M >= 0 && M < ((int64_t)1 << 31) && F > 0 && d > 0 && d <= ld && (ld & 3) == 0 && X > 0, "scatter_sgd: bad shape");
+    DCTR_REQUIRE(M >= 0 && M < ((int64_t)1 << 31) && F > 0 && d > 0 && d <= ld && (ld & 3) == 0 && X > 0 && X < ((int64_t)1 << 31), "scatter_sgd: bad shape");
     if (M == 0) return DCTR_OK;
     DCTR_REQUIRE(sorted_rows && sorted_pos && g && table && workspace, "scatter_sgd: null pointer");
     DCTR_REQUIRE(aligned16(sorted_rows) && aligned16(sorted_pos) && aligned16(table) && aligned16(workspace),
                  "scatter_sgd: rows / pos / table / workspace must be 16-byte aligned");
     FoldArgs a{};
     a.skip_row = -1;
-    a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table; a.dst = table;
+    a.X = (int)X; a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table; a.dst = table;
     a.g = g; a.s = nullptr; a.ld_n = g_ld_n; a.ld_f = g_ld_f; a.wts = wts; a.skip_row = skip_row;
     // 128-bit gradient loads need whole float4s inside the source row: per-field blocks of >= ld floats, or -- g_ld_f = 0, the
     // embedding bag: every field of a sample shares the sample's row -- rows of >= ld floats
@@ -436,7 +441,7 @@ extern "C" int dctr_scatter_sgd_fm(const int32_t* sorted_rows, const int32_t* so
                  "scatter_sgd_fm: rows / pos / table / s / workspace must be 16-byte aligned");
     FoldArgs a{};
     a.skip_row = -1;
-    a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table; a.dst = table;
+    a.X = (int)X; a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table; a.dst = table;
     a.g = g; a.s = s; a.ld_n = 0; a.ld_f = lds; a.wts = wts;
     return run_fold(kFm, a, true, workspace, workspace_bytes, as_stream(stream));
 }
@@ -453,7 +458,7 @@ extern "C" int dctr_scatter_grad_fm(const int32_t* sorted_rows, const int32_t* s
     FoldArgs a{};
     a.skip_row = -1;
     // the FM fold ends in  old*decay - lr*(Q - P*old):  decay = 0, lr = -1 leaves exactly the row's gradient
-    a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = -1.f; a.decay = 0.f;
+    a.X = (int)X; a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = -1.f; a.decay = 0.f;
     a.table = const_cast<float*>(table); a.dst = grad_out;
     a.g = g; a.s = s; a.ld_n = 0; a.ld_f = lds; a.wts = wts;
     return run_fold(kFm, a, true, workspace, workspace_bytes, as_stream(stream));

@@ -20,11 +20,15 @@ enum : unsigned { kFlagAgg = 1u, kFlagPrefix = 2u };       // tile status = (cou
 // wide digit is chosen when it saves a pass: 20-bit keys sort in 2 passes instead of 3, 25..30-bit keys in 3 instead of 4.
 template <int RB>
 __device__ __forceinline__ int digit_of(int32_t key, int shift) { return (key >> shift) & ((1 << RB) - 1); }
+// keys outside [0, X) (malformed input) become the sentinel X: they sort behind every table row and the fold never touches
+// them; the key width is that of X + 1, so the sentinel is representable
+__device__ __forceinline__ int32_t sane_key(int32_t k, int32_t X) { return (unsigned)k < (unsigned)X ? k : X; }
 
 // digit histograms of ALL passes in one read of the keys (they do not depend on the order of the list)
 template <int RB>
 __global__ void __launch_bounds__(kSortThreads)
-sort_hist_kernel(const int32_t* __restrict__ keys, int64_t M, int passes, unsigned* __restrict__ ghist) {
+sort_hist_kernel(const int32_t* __restrict__ keys, int64_t M, int passes, unsigned* __restrict__ ghist, int32_t X,
+                 int32_t* __restrict__ id_stat) {
     pdl_sync();
     constexpr int R = 1 << RB;
     extern __shared__ unsigned h[];                  // [passes][R]
@@ -35,7 +39,8 @@ sort_hist_kernel(const int32_t* __restrict__ keys, int64_t M, int passes, unsign
     for (int j = 0; j < kSortItems; ++j) {
         const int64_t i = base + j * kSortThreads + threadIdx.x;
         if (i < M) {
-            const int32_t k = keys[i];
+            const int32_t raw = keys[i], k = sane_key(raw, X);
+            if (k != raw && id_stat) { atomicAdd(id_stat, 1); id_stat[1] = raw; }
             for (int p = 0; p < passes; ++p) atomicAdd(&h[p * R + digit_of<RB>(k, p * RB)], 1u);
         }
     }
@@ -55,7 +60,7 @@ template <int RB>
 __global__ void __launch_bounds__(kSortThreads)
 sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict__ pos_in, int64_t M, int shift,
                  const unsigned* __restrict__ ghist, unsigned* __restrict__ ticket, volatile unsigned* __restrict__ status,
-                 int32_t* __restrict__ keys_out, int32_t* __restrict__ pos_out) {
+                 int32_t* __restrict__ keys_out, int32_t* __restrict__ pos_out, int32_t X, int first) {
     pdl_sync();
     constexpr int R = 1 << RB;
     constexpr int DPT = R / kSortThreads;                 // digits owned by a thread: tid*DPT .. tid*DPT + DPT-1
@@ -82,7 +87,7 @@ sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict_
     for (int j = 0; j < kSortItems; ++j) {
         const int64_t i = base + (warp * kSortItems + j) * 32 + lane;
         const bool valid = i < M;
-        key[j] = valid ? keys_in[i] : 0;
+        key[j] = valid ? (first ? sane_key(keys_in[i], X) : keys_in[i]) : 0;
         const int dg = digit_of<RB>(key[j], shift);
         // lanes holding the same digit: one ballot per digit bit instead of __match_any_sync, whose cost grows with the
         // number of distinct values in the warp
@@ -175,7 +180,7 @@ sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict_
             const int dg = digit_of<RB>(key[j], shift);
             const unsigned lp = lbase[dg] + cnt[warp * R + dg] + rank[j];
             skey[lp] = key[j];
-            spos[lp] = pos_in ? pos_in[i] : (int32_t)i;
+            spos[lp] = pos_in ? pos_in[i] : (int32_t)i;          // first pass: the caller's payload, or the element index
         }
     }
     __syncthreads();
@@ -212,19 +217,19 @@ static int forced_bits() {
 }
 static int radix_bits(int64_t X, int64_t M) {
     if (forced_bits()) return forced_bits();
-    const int bits = key_bits(X);
+    const int bits = key_bits(X + 1);
     return (M <= ((int64_t)1 << 18) && (bits + 9) / 10 < (bits + 7) / 8) ? 10 : 8;
 }
 static int num_passes(int64_t X, int64_t M) {
     const int rb = radix_bits(X, M);
-    return (key_bits(X) + rb - 1) / rb;
+    return (key_bits(X + 1) + rb - 1) / rb;
 }
 template <int RB>
 static constexpr size_t pass_smem() { return ((size_t)(kSortThreads / 32 + 2) * (1 << RB) + 2 * kSortTile) * sizeof(unsigned); }
 
 template <int RB>
-static int run_sort(const int32_t* ids, int64_t M, int passes, int32_t* sorted_rows, int32_t* sorted_pos, int32_t* alt_keys,
-                    int32_t* alt_pos, unsigned* ghist, unsigned* tickets, unsigned* status, cudaStream_t st) {
+static int run_sort(const int32_t* ids, const int32_t* payload, int64_t M, int32_t X, int passes, int32_t* sorted_rows, int32_t* sorted_pos,
+                    int32_t* alt_keys, int32_t* alt_pos, unsigned* ghist, unsigned* tickets, unsigned* status, cudaStream_t st) {
     constexpr int R = 1 << RB;
     const int tiles = (int)((M + kSortTile - 1) / kSortTile);
     static bool attr_set = false;
@@ -232,17 +237,17 @@ static int run_sort(const int32_t* ids, int64_t M, int passes, int32_t* sorted_r
         cudaFuncSetAttribute(sort_pass_kernel<RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pass_smem<RB>());
         attr_set = true;
     }
-    launch_k(sort_hist_kernel<RB>, tiles, kSortThreads, (size_t)passes * R * sizeof(unsigned), st, ids, M, passes, ghist);
+    launch_k(sort_hist_kernel<RB>, tiles, kSortThreads, (size_t)passes * R * sizeof(unsigned), st, ids, M, passes, ghist, X, id_status());
     int rc = check_launch("sort_hist_kernel");
     if (rc) return rc;
     const int32_t* kin = ids;
-    const int32_t* pin = nullptr;
+    const int32_t* pin = payload;
     for (int p = 0; p < passes; ++p) {
         const bool to_out = ((passes - p) & 1) == 1;
         int32_t* kout = to_out ? sorted_rows : alt_keys;
         int32_t* pout = to_out ? sorted_pos : alt_pos;
         launch_k(sort_pass_kernel<RB>, tiles, kSortThreads, pass_smem<RB>(), st, kin, pin, M, p * RB, ghist + p * R, tickets + p,
-                 status + (size_t)p * tiles * R, kout, pout);
+                 status + (size_t)p * tiles * R, kout, pout, X, (int)(p == 0));
         if ((rc = check_launch("sort_pass_kernel"))) return rc;
         kin = kout;
         pin = pout;
@@ -271,7 +276,12 @@ extern "C" size_t dctr_sort_rows_workspace(int64_t M) {
 
 extern "C" int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t* sorted_rows, int32_t* sorted_pos,
                               void* workspace, size_t workspace_bytes, void* stream) {
-    DCTR_REQUIRE(M >= 0 && M < ((int64_t)1 << 30) && X > 0 && X <= ((int64_t)1 << 31), "sort_rows: bad M/X");
+    return dctr_sort_pairs(ids, nullptr, M, X, sorted_rows, sorted_pos, workspace, workspace_bytes, stream);
+}
+
+extern "C" int dctr_sort_pairs(const int32_t* ids, const int32_t* payload, int64_t M, int64_t X, int32_t* sorted_rows,
+                               int32_t* sorted_pos, void* workspace, size_t workspace_bytes, void* stream) {
+    DCTR_REQUIRE(M >= 0 && M < ((int64_t)1 << 30) && X > 0 && X < ((int64_t)1 << 31) - 1, "sort_rows: bad M/X");
     if (M == 0) return DCTR_OK;
     DCTR_REQUIRE(ids && sorted_rows && sorted_pos && workspace, "sort_rows: null pointer");
     if (workspace_bytes < dctr_sort_rows_workspace(M)) {
@@ -288,7 +298,7 @@ extern "C" int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t*
     cudaStream_t st = as_stream(stream);
     const int rb = radix_bits(X, M), passes = num_passes(X, M), R = 1 << rb;
     cudaMemsetAsync(ghist, 0, (size_t)(kMaxPasses * kMaxRadix + 16 + (size_t)passes * tiles * R) * sizeof(unsigned), st);
-    if (rb == 10) return run_sort<10>(ids, M, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
-    if (rb == 9) return run_sort<9>(ids, M, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
-    return run_sort<8>(ids, M, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
+    if (rb == 10) return run_sort<10>(ids, payload, M, (int32_t)X, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
+    if (rb == 9) return run_sort<9>(ids, payload, M, (int32_t)X, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
+    return run_sort<8>(ids, payload, M, (int32_t)X, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
 }

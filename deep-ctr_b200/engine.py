@@ -32,6 +32,7 @@ class StepEngine:
         self.X, self.F, self.d, self.N = int(X), int(F), int(rank) + 1, int(batch_size)
         self.ld = ld or _r4(self.d)
         self.cross, self.bias_first, self.act0, self.act = cross, bool(bias_first), act0, act
+        self.acts = None          # optional per-layer override: acts[l] = activation that produced ins[l], l >= 1 (FNN_wnzh.py:163)
         self.scatter_mode = L.SCATTER_SEQ_DECAY if scatter_mode == "seq_decay" else L.SCATTER_SUM
         F_, d_ = self.F, self.d
         self.crossw = {"none": 0, "ip": F_ * (F_ - 1) // 2, "op": d_ * d_}[cross]
@@ -109,6 +110,7 @@ class StepEngine:
         self.launch_mode = 2 if self.N <= 8192 else 0
         self.overlap_sort = True
         self.wts_are_ones = True
+        self.upd_rows = self.upd_pos = None     # use_update_list()
         self.skip_row = None        # set when the weights are 0 / 1 and 0 only marks this (all-zero pad) row: no weight gather in the fold
 
     # ---- the embedding front end (overridden by BagEngine) -------------------------------------------
@@ -157,6 +159,26 @@ class StepEngine:
     def get_table(self):
         return self.table[:, :self.d].cpu().numpy()
 
+    def act_of(self, l):
+        """activation that produced ins[l]: act0 for the embedding layer, otherwise the hidden activation (or its override)"""
+        if l == 0:
+            return self.act0
+        return self.acts[l] if self.acts is not None else self.act
+
+    def use_update_list(self, J):
+        """Sparse update over an explicit (row, slot) list of J entries per sample instead of the [N, F] id block: the Theano
+        script updates EVERY feature of a sample, also one whose slot a later feature of the same field took
+        (FNN_wnzh.py:300-306).  dctr_arrange_update_list fills upd_rows / upd_pos, dctr_sort_pairs orders them."""
+        i32 = dict(dtype=torch.int32, device=self.dev)
+        self.J = int(J)
+        self.M = self.N * self.J
+        self.upd_rows = torch.zeros(self.M, **i32)
+        self.upd_pos = torch.zeros(self.M, **i32)
+        self.sorted_rows = torch.zeros(self.M, **i32)
+        self.sorted_pos = torch.zeros(self.M, **i32)
+        self.sort_ws = torch.zeros(L.lib().dctr_sort_rows_workspace(self.M), dtype=torch.uint8, device=self.dev)
+        self.scat_ws = torch.zeros(L.lib().dctr_scatter_workspace(self.M, self.ld), dtype=torch.uint8, device=self.dev)
+
     # ---- kernels ---------------------------------------------------------------------------------
     def _st(self):
         return torch.cuda.current_stream(self.dev).cuda_stream
@@ -180,7 +202,7 @@ class StepEngine:
         for l in range(self.nl - 1):
             mp, mld = self._mask(l + 1)
             L.call(self.gemm_fn, L.GEMM_NN, N, self.widths[l + 1], self.widths[l], p(self.ins[l]), self.ldi[l],
-                   p(self.W(l)), self.ldw[l], p(self.ins[l + 1]), self.ldi[l + 1], L.EPI_FWD, L.ACT[self.act],
+                   p(self.W(l)), self.ldw[l], p(self.ins[l + 1]), self.ldi[l + 1], L.EPI_FWD, L.ACT[self.act_of(l + 1)],
                    p(self.b(l)), None, 0, mp, mld, 1, st)
         last = self.nl - 1
         self._out_unit_done = False
@@ -188,7 +210,7 @@ class StepEngine:
             # train step: the output unit forward AND backward in one pass over the last activation
             mp, mld = self._mask(last)
             L.call("dctr_out_unit_train", p(self.ins[last]), self.ldi[last], N, self.widths[last], p(self.W(last)),
-                   p(self.b(last)), p(self.y), float(gscale), L.ACT[self.act], mp, mld, p(self.logit), p(self.pred),
+                   p(self.b(last)), p(self.y), float(gscale), L.ACT[self.act_of(last)], mp, mld, p(self.logit), p(self.pred),
                    p(self.loss_n), p(self.dlogit), float(gscale), p(self.loss), p(self.dbuf[0]), self.dbuf[0].stride(0),
                    p(self.W(last, self.grads)), p(self.b(last, self.grads)), p(self.col_ws), self.col_ws.numel(), st)
             self._out_unit_done = True
@@ -212,7 +234,7 @@ class StepEngine:
         # d(last hidden), d w_out and d b_out in one launch (unless the forward already produced them)
         if not self._out_unit_done:
             L.call("dctr_out_bwd_fused", p(self.dlogit), p(self.W(last)), p(self.ins[last]), self.ldi[last], N, H,
-                   L.ACT[self.act], mp, mld, p(self.dbuf[cur]), ldd, p(self.W(last, self.grads)), p(self.b(last, self.grads)),
+                   L.ACT[self.act_of(last)], mp, mld, p(self.dbuf[cur]), ldd, p(self.W(last, self.grads)), p(self.b(last, self.grads)),
                    cw, cwb, st)
         self._out_unit_done = False
         # Per layer, the weight/bias gradients (TN GEMM [+ split-K fold], column sum) only need dz_l, as does the data
@@ -243,7 +265,7 @@ class StepEngine:
                     readers[cur] = self.side2.record_event()
                     self._wgrad_pending = True
             mp, mld = self._mask(l)
-            act = self.act if l > 0 else self.act0
+            act = self.act_of(l)
             nxt = (cur + 1) % 3
             if readers[nxt] is not None:
                 main.wait_event(readers[nxt])
@@ -256,10 +278,12 @@ class StepEngine:
         return self.dbuf[cur]
 
     def sort_ids(self, ids=None, M=None, rows=None, pos=None, ws=None):
-        ids = self.ids if ids is None else ids
+        payload = None
+        if ids is None:
+            ids, payload = (self.ids, None) if self.upd_rows is None else (self.upd_rows, self.upd_pos)
         M = self.M if M is None else M
         ws = self.sort_ws if ws is None else ws
-        L.call("dctr_sort_rows", L.ptr(ids), M, self.X, L.ptr(self.sorted_rows if rows is None else rows),
+        L.call("dctr_sort_pairs", L.ptr(ids), L.ptr(payload), M, self.X, L.ptr(self.sorted_rows if rows is None else rows),
                L.ptr(self.sorted_pos if pos is None else pos), L.ptr(ws), ws.numel(), self._st())
 
     def embedding_update(self, dz, lr, decay=1.0, train_bias=True):

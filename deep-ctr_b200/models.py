@@ -152,10 +152,13 @@ class _Base(object):
         if with_ids:
             engine.ids, engine.wts = self._stage.dev["ids"], self._stage.dev["wts"]
         engine.y = self._stage.dev["y"]
+        # pred [N] | loss | - | id status {count, one offending id} (int32 words written by the kernels, dctr_set_id_status)
         engine.out = torch.zeros(N + 4, dtype=torch.float32, device=engine.dev)
         engine.pred, engine.loss = engine.out[:N], engine.out[N:N + 1]
+        self._status_ptr = engine.out.data_ptr() + 4 * (N + 2)
         self._out_pinned = torch.zeros(N + 4, dtype=torch.float32).pin_memory()
         self._out_np = self._out_pinned.numpy()
+        self._out_i32 = self._out_np.view(np.int32)
         self._graph = None
         self._warm = 0
         self.h2d_bytes = self._stage.nbytes
@@ -164,8 +167,22 @@ class _Base(object):
     def session(self):
         return Session(self)
 
+    def _bind_status(self):
+        """the kernels launched next from this thread report out-of-range ids into this model's output block"""
+        L.call("dctr_set_id_status", self._status_ptr)
+
+    def _check_ids(self):
+        """after the D2H of the output block: raise for ids outside the table -- TF's InvalidArgument (FM.py:57), the Theano
+        script's KeyError (FNN_wnzh.py:95).  The offending ids were read as row 0 and never written."""
+        bad = int(self._out_i32[self.N + 2])
+        if bad:
+            one = int(self._out_i32[self.N + 3])
+            self.engine.out[self.N + 2:].zero_()
+            raise IndexError("%d feature id(s) outside the embedding table in this batch (e.g. %d): ids must lie in [0, X_dim)" % (bad, one))
+
     # -- subclasses: _device_step() issues the kernels of one train step on the current stream
     def _run_step(self):
+        self._bind_status()
         if not self.use_graph:
             self._device_step()
             return
@@ -190,6 +207,7 @@ class _Base(object):
         self._out_pinned.copy_(self.engine.out, non_blocking=True)
         self._post_launch()            # host work that can overlap the step running on the device
         torch.cuda.current_stream().synchronize()
+        self._check_ids()
         return float(self._out_np[self.N]), self._out_np[:self.N].copy()
 
     def _stage_and_step(self, ids, wts, y):
@@ -203,6 +221,7 @@ class _Base(object):
     def _fetch_out(self):
         self._out_pinned.copy_(self.engine.out, non_blocking=True)
         torch.cuda.current_stream().synchronize()
+        self._check_ids()
         return float(self._out_np[self.N]), self._out_np[:self.N].copy()
 
     def train_step_device(self, ids, wts, y):
@@ -227,6 +246,7 @@ class _Base(object):
         E = ids.shape[0]
         out = np.empty(E, dtype=np.float32) if out_dev is None else None
         saved = self._swap_masks(None)
+        self._bind_status()
         for s in range(0, E, self.N):
             k = min(self.N, E - s)
             h["ids"][:k] = ids[s:s + k]
@@ -238,11 +258,11 @@ class _Base(object):
             e.forward(False)
             if out_dev is not None:
                 out_dev[s:s + k].copy_(e.pred[:k])
-                torch.cuda.current_stream().synchronize()       # the staging buffer is reused by the next chunk
-                continue
             self._out_pinned.copy_(e.out, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-            out[s:s + k] = self._out_np[:k]
+            torch.cuda.current_stream().synchronize()           # the staging buffer is reused by the next chunk
+            self._check_ids()
+            if out_dev is None:
+                out[s:s + k] = self._out_np[:k]
         self._swap_masks(saved)
         return out if out_dev is None else out_dev
 

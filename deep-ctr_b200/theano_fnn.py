@@ -63,10 +63,11 @@ class MaskStreams(object):
 
 class FNN_wnzh(_Base):
     def __init__(self, fm_model, batch_size=100, lr=0.001, dropout=0.5, hidden1=300, hidden2=100, lambda1=0.0,
-                 lambda_fm=0.1, acti_type="tanh", n_fields=16, device="cuda", weights=None):
+                 lambda_fm=0.1, acti_type="tanh", n_fields=16, device="cuda", weights=None, max_feats=None):
         """fm_model: dict(w_0=float, table=[X, k+1] float array indexed by feature id, feat_field=[X] int)
         as loaded by data.load_fm_model (FNN_wnzh.py:62-84).  Hyper-parameters default to the advertiser-2997
-        branch (:43-49), the only one that defines them all."""
+        branch (:43-49), the only one that defines them all.  max_feats: longest feature list of a sample (default
+        n_fields; larger when lines carry several features of one field)."""
         table = np.asarray(fm_model["table"], dtype=np.float32)
         X, d = table.shape
         self.k = d
@@ -85,8 +86,14 @@ class FNN_wnzh(_Base):
         eng.wts_are_ones = False
         eng.skip_row = X            # weights are 1 except on the pad row: the fold drops that row instead of gathering weights
         self.pad_row = X
+        # the dropout branch computes hidden layer 2 with tanh whatever acti_type says (d2 = T.tanh(...), FNN_wnzh.py:163); only
+        # the prediction branch uses acti_type there (:157-162)
+        self._acts_train, self._acts_eval = [None, act, "tanh"], [None, act, act]
+        eng.acts = self._acts_train
         N = batch_size
-        extra = [("feats", np.int32, (N, n_fields))]
+        self.J = int(max_feats or n_fields)
+        eng.use_update_list(self.J)         # every feature of a sample is updated, overwritten ones too (FNN_wnzh.py:300-306)
+        extra = [("feats", np.int32, (N, self.J))]
         self.mask_streams = MaskStreams(hidden1, hidden2, dropout) if dropout < 1.0 else None
         if self.mask_streams is not None:
             extra += [("mask1", np.float32, (1, eng.ldi[1])), ("mask2", np.float32, (1, eng.ldi[2]))]
@@ -139,8 +146,10 @@ class FNN_wnzh(_Base):
                 st.dev[k].copy_(torch.from_numpy(st.host[k]), non_blocking=True)
 
     def _arrange_on_device(self):
-        L.call("dctr_arrange_fields", L.ptr(self.feats), L.ptr(self.feat_field_dev), self.N, self.F, self.F, self.pad_row,
-               L.ptr(self.engine.ids), L.ptr(self.engine.wts), torch.cuda.current_stream(self.engine.dev).cuda_stream)
+        e = self.engine
+        L.call("dctr_arrange_update_list", L.ptr(self.feats), L.ptr(self.feat_field_dev), self.N, self.J, self.F, self.pad_row,
+               self.pad_row, L.ptr(e.ids), L.ptr(e.wts), L.ptr(e.upd_rows), L.ptr(e.upd_pos),
+               torch.cuda.current_stream(e.dev).cuda_stream)
 
     def _device_step(self):
         decay = 1.0 - 2.0 * self.lambda_fm * self.lr / getattr(self, "global_N", self.N)   # FNN_wnzh.py:305 (b_size)
@@ -151,8 +160,10 @@ class FNN_wnzh(_Base):
         h = self._stage.host["feats"]
         feats = np.asarray(feats)
         k, j = feats.shape
+        if j > self.J:
+            raise ValueError("a sample has %d features, the model was built with max_feats=%d" % (j, self.J))
         h[:k, :j] = feats
-        if j < self.F:
+        if j < self.J:
             h[:k, j:] = -1
         if k < self.N:
             h[k:] = -1
@@ -185,18 +196,40 @@ class FNN_wnzh(_Base):
         feats = np.asarray(feats)
         E = feats.shape[0]
         out = np.empty(E, dtype=np.float32)
-        saved = self._swap_masks(None)
-        for s in range(0, E, self.N):
-            k = min(self.N, E - s)
-            self._stage_feats(feats[s:s + k])
-            self._stage.upload()
-            self._arrange_on_device()
-            self.engine.forward(False)
-            self._out_pinned.copy_(self.engine.out, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-            out[s:s + k] = self._out_np[:k]
-        self._swap_masks(saved)
+        self._predict_into(feats, out, None)
         return out
+
+    def _predict_into(self, feats, out_np, out_dev):
+        E = feats.shape[0]
+        saved = self._swap_masks(None)
+        self.engine.acts = self._acts_eval
+        self._bind_status()
+        try:
+            for s in range(0, E, self.N):
+                k = min(self.N, E - s)
+                self._stage_feats(feats[s:s + k])
+                self._stage.upload()
+                self._arrange_on_device()
+                self.engine.forward(False)
+                if out_dev is not None:
+                    out_dev[s:s + k].copy_(self.engine.pred[:k])
+                self._out_pinned.copy_(self.engine.out, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+                self._check_ids()
+                if out_np is not None:
+                    out_np[s:s + k] = self._out_np[:k]
+        finally:
+            self.engine.acts = self._acts_train
+            self._swap_masks(saved)
+
+    def evaluate(self, feats, labels, nds_rate=None):
+        """Predict E samples (feature lists [E, <= max_feats], -1 = absent) and score them ON THE DEVICE: dict(auc, log_loss,
+        rmse, n_pos) -- print_err / get_err_bat of the script (FNN_wnzh.py:187-221) without the D2H of the predictions."""
+        from .metrics import device_metrics
+        feats = np.asarray(feats)
+        preds = torch.empty(feats.shape[0], dtype=torch.float32, device=self.engine.dev)
+        self._predict_into(feats, None, preds)
+        return device_metrics(preds, np.asarray(labels, dtype=np.float32).reshape(-1), device=self.engine.dev, nds_rate=nds_rate)
 
     def get_weights(self):
         """(w1, w2, w3, b1, b2, b3) like the tail of train()'s outputs -- POST-update here."""

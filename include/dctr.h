@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define DCTR_VERSION 1
+#define DCTR_VERSION 2
 
 enum { DCTR_OK = 0, DCTR_EINVAL = -1, DCTR_EWORKSPACE = -2, DCTR_ECUDA = -3 };
 enum { DCTR_ACT_NONE = 0, DCTR_ACT_TANH = 1, DCTR_ACT_RELU = 2, DCTR_ACT_SIGMOID = 3 };
@@ -51,6 +51,14 @@ long long dctr_launch_count(void);
  * Results are identical in every mode.  The DCTR_PDL environment variable, when set to 0 / 1 / 2, overrides the call. */
 int dctr_set_launch_mode(int mode);
 
+/* Row ids come from data files.  Every kernel that takes ids compares them with X: an id outside [0, X) is READ as row 0 by
+ * the forward kernels, sorted behind the table by dctr_sort_*, never written by the folds, and counted in the two device
+ * words registered here for the calling thread: status[0] += 1 per offending id, status[1] = one offending value (captured
+ * CUDA graphs keep the pointer they were captured with; NULL = do not report).  TensorFlow raises InvalidArgument and the
+ * Theano script KeyError for such ids (FM.py:57 embedding_lookup_sparse, FNN_wnzh.py:95); the host side of the build
+ * raises after the step when status[0] != 0. */
+int dctr_set_id_status(int32_t* status);
+
 /* ---- K1: per-field embedding gather + concat (+ fused inner/outer product layer) -------------
  * replaces feats_to_layer_one_array (FNN_wnzh.py:87-96, data_fm.py:46-54), the 13 rank-1 matmuls +
  * 26 embedding_lookup_sparse + concat of FNN.forward (FNN.py:76-85), the N*P scalar matmuls of
@@ -72,6 +80,14 @@ int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, const float* ta
  * feature of the same field overwrites an earlier one, as in the reference loop. */
 int dctr_arrange_fields(const int32_t* feats, const int32_t* feat_field, int N, int J, int F, int32_t pad_row,
                         int32_t* ids, float* wts, void* stream);
+/* The same, plus the sample's UPDATE list: the reference's scatter loops over EVERY feature of the sample (`for feat in ft`,
+ * FNN_wnzh.py:300-306), so a feature whose slot was overwritten by a later feature of the same field, or that occurs twice,
+ * is still updated -- from the gradient of its field's slot.  upd_rows / upd_pos: int32 [N, J]; entry j = (feature id,
+ * n * F + field(feature)); absent (negative) and unknown features become (pad_row, n * F) -- sort them with dctr_sort_pairs
+ * (payload = upd_pos) and fold with dctr_scatter_sgd_masked(skip_row = pad_row).  X = number of entries of feat_field: a feature
+ * id >= X is reported through dctr_set_id_status (the reference raises KeyError there) and treated as absent. */
+int dctr_arrange_update_list(const int32_t* feats, const int32_t* feat_field, int N, int J, int F, int64_t X, int32_t pad_row,
+                             int32_t* ids, float* wts, int32_t* upd_rows, int32_t* upd_pos, void* stream);
 
 /* ---- eval metrics on the device (baseline.py:246-259 watch_train: roc_auc_score, mean_squared_error; log_loss) --------
  * out (device, 4 doubles) = { ROC AUC with ties by average rank, -1 when one class is absent (the reference's ValueError
@@ -114,6 +130,11 @@ int dctr_fm_fwd(const int32_t* ids, const float* wts, const float* table, int64_
 size_t dctr_sort_rows_workspace(int64_t M);
 int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t* sorted_rows, int32_t* sorted_pos,
                    void* workspace, size_t workspace_bytes, void* stream);
+/* The same with an explicit payload per key (NULL = the element index): sorted_pos receives payload[i] of the i-th smallest
+ * key, ties in input order.  Keys outside [0, X) are reported through dctr_set_id_status, sort behind every valid row and are
+ * never folded. */
+int dctr_sort_pairs(const int32_t* ids, const int32_t* payload, int64_t M, int64_t X, int32_t* sorted_rows,
+                    int32_t* sorted_pos, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- K6b: segmented fold + SGD into the touched rows only -------------------------------------
  * dense source (FNN*, Theano FNN):  grad(p=n*F+f, c) = (wts? wts[p] : 1) * g[n*g_ld_n + f*g_ld_f + c]

@@ -26,7 +26,7 @@ def test_header_symbols_exported(built_lib):
 
 def test_version_and_error_slot(built_lib):
     from deepctr_b200 import _lib
-    assert built_lib.dctr_version() == 1
+    assert built_lib.dctr_version() == 2
     # bad arguments are rejected before any CUDA call: ld not a multiple of 4
     rc = built_lib.dctr_gather_concat_fwd(1, None, 1, 10, 3, 1, 2, 3, 0, 0, None, 0, 1, 16, None)
     assert rc == _lib.EINVAL

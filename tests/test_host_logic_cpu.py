@@ -176,12 +176,13 @@ def test_mask_prefetch_keeps_the_stream_and_the_step_plumbing_runs():
             self.uploads += 1
 
     class Eng:
-        out = torch.arange(12, dtype=torch.float32)
+        out = torch.cat([torch.arange(10, dtype=torch.float32), torch.zeros(2)])      # pred[8] | loss | - | id status words (0 = clean)
 
     m = FNN_wnzh.__new__(FNN_wnzh)               # host plumbing only: no engine, no device
     m.N, m._stage, m.engine, m.mask_streams, m._next_masks = 8, Stage(), Eng(), MaskStreams(30, 10, 0.5), None
     m._out_pinned = torch.zeros(12)
     m._out_np = m._out_pinned.numpy()
+    m._out_i32 = m._out_np.view(np.int32)
     m._run_step = lambda: None
     ref = MaskStreams(30, 10, 0.5)
     with mock.patch("torch.cuda.current_stream") as cs:
@@ -212,7 +213,7 @@ def test_device_fed_step_plumbing_runs_on_fakes():
             self.dev = {k: torch.zeros(v.shape) for k, v in self.host.items()}
 
     class Eng:
-        out = torch.arange(12, dtype=torch.float32)
+        out = torch.cat([torch.arange(10, dtype=torch.float32), torch.zeros(2)])      # pred[8] | loss | - | id status words (0 = clean)
         y = torch.zeros(8)
 
     for cls in (FNN_wnzh, SNN):
@@ -220,6 +221,7 @@ def test_device_fed_step_plumbing_runs_on_fakes():
         m.N, m._stage, m.engine, m.mask_streams, m._next_masks = 8, Stage(), Eng(), MaskStreams(30, 10, 0.5), None
         m._out_pinned = torch.zeros(12)
         m._out_np = m._out_pinned.numpy()
+        m._out_i32 = m._out_np.view(np.int32)
         m._run_step = lambda: None
         m._pre_step()
         m._post_launch()
