@@ -179,8 +179,8 @@ def call_cost(name, a):
     if name == "dctr_cross_bwd":
         N, F, d, ldz = a[5], a[6], a[7], a[10]
         return "byte", N * (F * 8 + F * 4 * d + 4 * ldz + F * 4 * d)
-    if name == "dctr_sort_rows":
-        M, X = a[1], a[2]
+    if name in ("dctr_sort_rows", "dctr_sort_pairs"):
+        M, X = (a[1], a[2]) if name == "dctr_sort_rows" else (a[2], a[3])
         bits = max(1, int(X - 1).bit_length())
         passes = (bits + 7) // 8
         if M <= (1 << 18):
@@ -202,6 +202,10 @@ def call_cost(name, a):
         return "byte", a[4] * a[5] * 8 + a[4] * 4
     if name == "dctr_arrange_fields":               # feats in, ids + wts out
         return "byte", a[2] * (a[3] * 4 + a[4] * 8)
+    if name == "dctr_arrange_update_list":          # feats in, ids + wts + update list out
+        return "byte", a[2] * (a[3] * 12 + a[4] * 8)
+    if name == "dctr_out_unit_train":               # the last activation in, its gradient out, pred / loss / dlogit
+        return "byte", a[2] * a[3] * 8 + a[2] * 16
     if name == "dctr_gather_rows":                  # id + row in, row out
         return "byte", a[4] * (4 + 8 * a[3])
     if name == "dctr_dense_adam":                   # p, g, m, v read; p, m, v (+ g) written
@@ -223,7 +227,7 @@ NCU_TRAFFIC = {
 }
 
 
-def emb_roofline(N=1 << 20, F=16, rank=10, X=20_000_000, reps=5):
+def emb_roofline(N=1 << 20, F=16, rank=10, X=20_000_000, reps=5, zipf=1.1):
     """The HBM-bound kernels alone at a size where they ARE bandwidth-bound (table 0.96 GB >> 126 MB L2,
     N = 2^20 samples per launch): achieved algorithmic GB/s vs the measured copy peak."""
     import torch
@@ -242,7 +246,7 @@ def emb_roofline(N=1 << 20, F=16, rank=10, X=20_000_000, reps=5):
     ld = (d + 3) // 4 * 4
     rng = np.random.default_rng(7)
     sizes = data.ipinyou_field_sizes(X)
-    ids_h = data.make_field_batch(rng, N, sizes, 1.1).astype(np.int32)
+    ids_h = data.make_field_batch(rng, N, sizes, zipf).astype(np.int32)        # zipf = 0: uniform within each field
     dev = "cuda"
     ids = torch.as_tensor(ids_h).to(dev)
     wts = torch.ones(N, F, device=dev)
@@ -276,7 +280,8 @@ def emb_roofline(N=1 << 20, F=16, rank=10, X=20_000_000, reps=5):
         "scatter_sgd_fm": ("dctr_scatter_sgd_fm", (p(rows), p(pos), M, F, d, p(g), p(s), ld, p(wts), 1e-3, 1.0, p(table), X, ld, p(fws), fws.numel(), None)),
     }
     pk = peaks()
-    out = {"N": N, "F": F, "d": d, "rows": X, "table_GB": round(X * ld * 4 / 1e9, 2), "peak_GBs": pk["hbm"], "kernels": {}}
+    out = {"N": N, "F": F, "d": d, "rows": X, "ids": "zipf(%g) within each field" % zipf if zipf else "uniform within each field",
+           "unique_rows": int(len(np.unique(ids_h))), "table_GB": round(X * ld * 4 / 1e9, 2), "peak_GBs": pk["hbm"], "kernels": {}}
     for key, (name, a) in calls.items():
         L.call(name, *a)
         torch.cuda.synchronize()
@@ -291,7 +296,7 @@ def emb_roofline(N=1 << 20, F=16, rank=10, X=20_000_000, reps=5):
         gbs = cost / (ms * 1e-3) / 1e9
         out["kernels"][key] = {"ms": round(ms, 4), "algorithmic_MB": round(cost / 1e6, 1), "GBs": round(gbs, 1), "frac": round(gbs / pk["hbm"], 4)}
         tr = NCU_TRAFFIC.get(("emb", key))
-        if tr is not None and (N, F, rank, X) == (1 << 20, 16, 10, 20_000_000):       # the configuration the captures were taken on
+        if tr is not None and (N, F, rank, X, zipf) == (1 << 20, 16, 10, 20_000_000, 1.1):       # the configuration the captures were taken on
             out["kernels"][key]["ncu_dram_MB"] = round(tr / 1e6, 1)
     return out
 
@@ -586,10 +591,11 @@ def main():
     ap.add_argument("--emb-only", action="store_true", help="only run the embedding-kernel roofline sweep")
     ap.add_argument("--emb-n", type=int, default=1 << 20)
     ap.add_argument("--emb-reps", type=int, default=5)
+    ap.add_argument("--emb-zipf", type=float, default=1.1, help="Zipf exponent of the ids inside each field; 0 = uniform")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     if args.emb_only:
-        print(json.dumps({"emb_roofline": emb_roofline(N=args.emb_n, reps=args.emb_reps)}))
+        print(json.dumps({"emb_roofline": emb_roofline(N=args.emb_n, reps=args.emb_reps, zipf=args.emb_zipf)}))
     elif args.impl == "reference":
         run_reference(args, rank, world)
     else:
