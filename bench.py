@@ -202,6 +202,10 @@ def call_cost(name, a):
         return "byte", a[4] * a[5] * 8 + a[4] * 4
     if name == "dctr_arrange_fields":               # feats in, ids + wts out
         return "byte", a[2] * (a[3] * 4 + a[4] * 8)
+    if name == "dctr_mlp2_train":                   # fp32 FFMA: forward + data gradients of both hidden layers
+        return "flop", 4.0 * a[0] * (a[1] * a[2] + a[2] * a[3] + a[3])
+    if name == "dctr_mlp2_wgrad":
+        return "flop", 2.0 * a[0] * (a[1] * a[2] + a[2] * a[3])
     if name == "dctr_arrange_update_list":          # feats in, ids + wts + update list out
         return "byte", a[2] * (a[3] * 12 + a[4] * 8)
     if name == "dctr_out_unit_train":               # the last activation in, its gradient out, pred / loss / dlogit
@@ -450,6 +454,10 @@ def run_b200(args, rank, world):
             roof["note"] = ("3xTF32 on tcgen05: fp32-equivalent FLOP/s; its ceiling is cuBLAS TF32 / 3 = 243 TFLOP/s (DESIGN 3.4) "
                             "-> frac_of_3xtf32_ceiling; a GEMM of this size is launch- and latency-bound")
             roof["frac_of_3xtf32_ceiling"] = round(top["achieved"] / 243.0, 4)
+        elif top["unit"] == "TFLOP/s" and top["kernel"].startswith("dctr_mlp2"):
+            roof["note"] = ("fused fp32 FFMA kernel (csrc/mlp2.cu); the layers of this net are too small for tensor-core tiles, so the "
+                            "bound that applies is the fp32 SIMT peak, 148 SMs x 128 lanes x 2 x 1.965 GHz = 74.4 TFLOP/s -> frac_of_fp32_peak")
+            roof["frac_of_fp32_peak"] = round(top["achieved"] / 74.4, 4)
         elif top["unit"] == "TFLOP/s":
             roof["note"] = "fp32 FFMA parity path; fp32 SIMT peak is 74.4 TFLOP/s -> frac_of_fp32_peak"
             roof["frac_of_fp32_peak"] = round(top["achieved"] / 74.4, 4)

@@ -15,7 +15,7 @@ SCATTER_SUM, SCATTER_SEQ_DECAY = 0, 1
 GEMM_NN, GEMM_NT, GEMM_TN = 0, 1, 2
 EPI_NONE, EPI_FWD, EPI_DGRAD = 0, 1, 2
 
-_p, _i, _l, _f, _z = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float, ctypes.c_size_t
+_p, _i, _l, _f, _z, _d = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float, ctypes.c_size_t, ctypes.c_double
 
 # name -> (restype, argtypes); must list every symbol include/dctr.h declares (tests/test_abi.py checks)
 SIGNATURES = {
@@ -34,9 +34,9 @@ SIGNATURES = {
     "dctr_sort_rows": (_i, [_p, _l, _l, _p, _p, _p, _z, _p]),
     "dctr_sort_pairs": (_i, [_p, _p, _l, _l, _p, _p, _p, _z, _p]),
     "dctr_scatter_workspace": (_z, [_l, _i]),
-    "dctr_scatter_sgd": (_i, [_i, _p, _p, _l, _i, _i, _p, _l, _i, _p, _f, _f, _p, _l, _i, _p, _z, _p]),
-    "dctr_scatter_sgd_masked": (_i, [_i, _p, _p, _l, _i, _i, _p, _l, _i, _i, _f, _f, _p, _l, _i, _p, _z, _p]),
-    "dctr_scatter_sgd_fm": (_i, [_p, _p, _l, _i, _i, _p, _p, _i, _p, _f, _f, _p, _l, _i, _p, _z, _p]),
+    "dctr_scatter_sgd": (_i, [_i, _p, _p, _l, _i, _i, _p, _l, _i, _p, _f, _d, _p, _l, _i, _p, _z, _p]),
+    "dctr_scatter_sgd_masked": (_i, [_i, _p, _p, _l, _i, _i, _p, _l, _i, _i, _f, _d, _p, _l, _i, _p, _z, _p]),
+    "dctr_scatter_sgd_fm": (_i, [_p, _p, _l, _i, _i, _p, _p, _i, _p, _f, _d, _p, _l, _i, _p, _z, _p]),
     "dctr_scatter_grad_fm": (_i, [_p, _p, _l, _i, _i, _p, _p, _i, _p, _p, _l, _i, _p, _p, _z, _p]),
     "dctr_decay_sweep": (_i, [_p, _l, _i, _f, _p, _l, _p]),
     "dctr_gemm": (_i, [_i, _i, _i, _i, _p, _i, _p, _i, _p, _i, _i, _i, _p, _p, _i, _p, _i, _i, _p]),
@@ -53,6 +53,13 @@ SIGNATURES = {
     "dctr_eval_metrics_workspace": (_z, [_l]),
     "dctr_eval_metrics": (_i, [_p, _p, _l, _p, _p, _z, _p]),
     "dctr_out_unit_train": (_i, [_p, _i, _i, _i, _p, _p, _p, _f, _i, _p, _i, _p, _p, _p, _p, _f, _p, _p, _i, _p, _p, _p, _z, _p]),
+    "dctr_l2_loss_add": (_i, [_p, _l, _p, _i, _f, _p, _p, _z, _p]),
+    "dctr_mlp2_transpose": (_i, [_i, _i, _i, _p, _i, _p, _i, _p, _i, _p, _i, _p]),
+    "dctr_mlp2_supported": (_i, [_i, _i, _i]),
+    "dctr_mlp2_workspace": (_z, [_i, _i, _i, _i]),
+    "dctr_mlp2_train": (_i, [_i, _i, _i, _i, _p, _i, _p, _i, _i, _p, _i, _p, _i, _p, _i, _p, _i, _p, _i, _p, _i, _p, _p, _p, _p, _p, _f, _f,
+                             _p, _i, _p, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _i, _f, _f, _p, _z, _p]),
+    "dctr_mlp2_wgrad": (_i, [_i, _i, _i, _i, _p, _i, _p, _i, _p, _p, _i, _p, _i, _p, _p, _i, _p, _p, _p, _p, _p, _i, _f, _f, _p, _z, _p]),
     "dctr_dense_sgd": (_i, [_p, _p, _l, _f, _f, _p]),
     "dctr_adam_tick": (_i, [_p, _f, _f, _f, _p]),
     "dctr_dense_adam": (_i, [_p, _p, _p, _p, _l, _p, _f, _f, _f, _f, _i, _p]),

@@ -537,6 +537,47 @@ extern "C" int dctr_col_wsum(const float* A, int lda, int N, int H, const float*
     return check_launch("col_wsum_kernel");
 }
 
+// lam * l2_loss(table) + lam * l2_loss(b) of FM.py:39 / LR.py:37 (tf.nn.l2_loss = sum(t^2) / 2) ADDED to out[0]: the loss the
+// reference fetches includes the regulariser.  CTA partials in double, folded in CTA order by the last CTA.
+namespace dctr {
+__global__ void __launch_bounds__(256)
+sumsq_kernel(const float4* __restrict__ v, int64_t n4, const float* __restrict__ extra, int n_extra, float scale,
+             float* __restrict__ out, double* __restrict__ partial, unsigned* __restrict__ ticket) {
+    pdl_sync();
+    __shared__ double sh[256];
+    double s = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (int64_t)gridDim.x * 256) {
+        const float4 t = __ldg(v + i);
+        s += (double)t.x * t.x + (double)t.y * t.y + (double)t.z * t.z + (double)t.w * t.w;
+    }
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
+    if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
+    if (!take_last_ticket(ticket, gridDim.x)) return;
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (unsigned k = 0; k < gridDim.x; ++k) t += __ldcg(partial + k);
+        for (int k = 0; k < n_extra; ++k) t += (double)extra[k] * extra[k];
+        out[0] += (float)(0.5 * scale * t);
+    }
+}
+}  // namespace dctr
+
+extern "C" int dctr_l2_loss_add(const float* v, int64_t n, const float* extra, int n_extra, float scale, float* out,
+                                void* workspace, size_t workspace_bytes, void* stream) {
+    DCTR_REQUIRE(v && out && workspace && n >= 0 && (n & 3) == 0 && ((uintptr_t)v & 15) == 0 && n_extra >= 0 && (n_extra == 0 || extra),
+                 "l2_loss_add: bad arguments (n must be a multiple of 4, v 16-byte aligned)");
+    DCTR_REQUIRE(workspace_bytes >= dctr_reduce_workspace(1, 1), "l2_loss_add: workspace smaller than dctr_reduce_workspace(1, 1)");
+    int blocks = dctr::ceil_div(n / 4, 256 * 8);
+    if (blocks > dctr::kNumSMs * 4) blocks = dctr::kNumSMs * 4;
+    if (blocks < 1) blocks = 1;
+    char* ws = static_cast<char*>(workspace);
+    dctr::launch_k(dctr::sumsq_kernel, blocks, 256, 0, dctr::as_stream(stream), reinterpret_cast<const float4*>(v), n / 4, extra, n_extra, scale,
+                   out, reinterpret_cast<double*>(ws + dctr::kRedHeader), reinterpret_cast<unsigned*>(ws));
+    return dctr::check_launch("sumsq_kernel");
+}
+
 extern "C" int dctr_vec_sum(const float* v, int N, float scale, float* out, void* stream) {
     DCTR_REQUIRE(v && out && N >= 0, "vec_sum: bad arguments");
     launch_k(vec_sum_kernel, 1, 1024, 0, as_stream(stream), v, N, scale, out);

@@ -44,6 +44,10 @@ struct FoldArgs {
     int X;                         // rows >= X (the sort's sentinel for out-of-range ids) are folded but never read or written
     int skip_row;                  // segments of this row are folded but never written (-1: none) -- the pad row of absent fields
     float lr, decay;
+    // decay as 1 - eps_d with eps_d and log(decay) rounded from DOUBLE: the Theano decay 1 - 2*lambda*lr/N (FNN_wnzh.py:305) is
+    // 1 - 4.9e-8 at the headline configuration, which float32 can only represent as 1 - 5.96e-8 -- applied once per occurrence
+    // that is a 2e-3 relative error on a row 70 000 samples hit (tests/test_baseline_sizes_gpu.py)
+    float eps_d, log_decay;
     float* table;                  // rows are READ from here ...
     float* dst;                    // ... and the folded result is written here (== table except for the gradient-only fold)
     // gradient source: dense g[n*ld_n + f*ld_f + c] (* wts[p]); FM: g[n], s[n*ld_f + c], x = wts[p]
@@ -52,14 +56,19 @@ struct FoldArgs {
     float* in_q; float* out_q; float* in_p; float* out_p; int32_t* in_flag; int32_t* out_row;
 };
 
-template <int MODE> __device__ __forceinline__ float p_identity() { return MODE == kSeq ? 1.f : 0.f; }
+// P of a partial: SUM unused, FM sum of g x^2, SEQ the NUMBER of occurrences m folded so far (the map is w -> decay^m w + Q;
+// decay^m = exp(m log decay) is formed where it is applied, a running float product of decays would lose the increment)
+template <int MODE> __device__ __forceinline__ float p_identity() { return 0.f; }
+__device__ __forceinline__ float seq_pow(float m, float log_decay) { return log_decay == 0.f ? 1.f : expf(m * log_decay); }
+// x * decay as x - eps_d * x: one rounding of the exact product
+__device__ __forceinline__ float mul_decay(float x, float eps_d) { return fmaf(-eps_d, x, x); }
 
 template <int MODE>
-__device__ __forceinline__ void fold_elem(float& P, float4& Q, const float4& e, float v, float lr, float decay) {
+__device__ __forceinline__ void fold_elem(float& P, float4& Q, const float4& e, float v, float lr, float eps_d) {
     if (MODE == kSeq) {
-        P *= decay;
-        Q.x = fmaf(Q.x, decay, -lr * e.x); Q.y = fmaf(Q.y, decay, -lr * e.y);
-        Q.z = fmaf(Q.z, decay, -lr * e.z); Q.w = fmaf(Q.w, decay, -lr * e.w);
+        P += 1.f;
+        Q.x = fmaf(-lr, e.x, mul_decay(Q.x, eps_d)); Q.y = fmaf(-lr, e.y, mul_decay(Q.y, eps_d));
+        Q.z = fmaf(-lr, e.z, mul_decay(Q.z, eps_d)); Q.w = fmaf(-lr, e.w, mul_decay(Q.w, eps_d));
     } else {
         if (MODE == kFm) P += v;
         Q.x += e.x; Q.y += e.y; Q.z += e.z; Q.w += e.w;
@@ -67,29 +76,31 @@ __device__ __forceinline__ void fold_elem(float& P, float4& Q, const float4& e, 
 }
 // (P, Q) followed in list order by (P2, Q2)
 template <int MODE>
-__device__ __forceinline__ void fold_combine(float& P, float4& Q, float P2, const float4& Q2) {
+__device__ __forceinline__ void fold_combine(float& P, float4& Q, float P2, const float4& Q2, float log_decay) {
     if (MODE == kSeq) {
-        Q.x = fmaf(Q.x, P2, Q2.x); Q.y = fmaf(Q.y, P2, Q2.y); Q.z = fmaf(Q.z, P2, Q2.z); Q.w = fmaf(Q.w, P2, Q2.w);
-        P *= P2;
+        const float f = seq_pow(P2, log_decay);
+        Q.x = fmaf(Q.x, f, Q2.x); Q.y = fmaf(Q.y, f, Q2.y); Q.z = fmaf(Q.z, f, Q2.z); Q.w = fmaf(Q.w, f, Q2.w);
+        P += P2;
     } else {
         if (MODE == kFm) P += P2;
         Q.x += Q2.x; Q.y += Q2.y; Q.z += Q2.z; Q.w += Q2.w;
     }
 }
 template <int MODE>
-__device__ __forceinline__ float4 fold_final(const float4& old, float P, const float4& Q, int c0, float lr, float decay) {
+__device__ __forceinline__ float4 fold_final(const float4& old, float P, const float4& Q, int c0, float lr, float eps_d, float log_decay) {
     float4 r;
     if (MODE == kSeq) {
-        r.x = fmaf(P, old.x, Q.x); r.y = fmaf(P, old.y, Q.y); r.z = fmaf(P, old.z, Q.z); r.w = fmaf(P, old.w, Q.w);
+        const float f = seq_pow(P, log_decay);
+        r.x = fmaf(f, old.x, Q.x); r.y = fmaf(f, old.y, Q.y); r.z = fmaf(f, old.z, Q.z); r.w = fmaf(f, old.w, Q.w);
     } else if (MODE == kFm) {
         const float gx = c0 == 0 ? Q.x : fmaf(-P, old.x, Q.x);     // component 0 is the linear weight: grad = gn*x
-        r.x = fmaf(old.x, decay, -lr * gx);
-        r.y = fmaf(old.y, decay, -lr * fmaf(-P, old.y, Q.y));
-        r.z = fmaf(old.z, decay, -lr * fmaf(-P, old.z, Q.z));
-        r.w = fmaf(old.w, decay, -lr * fmaf(-P, old.w, Q.w));
+        r.x = fmaf(-lr, gx, mul_decay(old.x, eps_d));
+        r.y = fmaf(-lr, fmaf(-P, old.y, Q.y), mul_decay(old.y, eps_d));
+        r.z = fmaf(-lr, fmaf(-P, old.z, Q.z), mul_decay(old.z, eps_d));
+        r.w = fmaf(-lr, fmaf(-P, old.w, Q.w), mul_decay(old.w, eps_d));
     } else {
-        r.x = fmaf(old.x, decay, -lr * Q.x); r.y = fmaf(old.y, decay, -lr * Q.y);
-        r.z = fmaf(old.z, decay, -lr * Q.z); r.w = fmaf(old.w, decay, -lr * Q.w);
+        r.x = fmaf(-lr, Q.x, mul_decay(old.x, eps_d)); r.y = fmaf(-lr, Q.y, mul_decay(old.y, eps_d));
+        r.z = fmaf(-lr, Q.z, mul_decay(old.z, eps_d)); r.w = fmaf(-lr, Q.w, mul_decay(old.w, eps_d));
     }
     return r;
 }
@@ -204,11 +215,11 @@ fold_tile_kernel(const FoldArgs a) {
     for (int j = 0; j < kC; ++j) {
         if (valid >> j & 1) {
             if (head >> j & 1) { P = p_identity<MODE>(); Q = make_float4(0.f, 0.f, 0.f, 0.f); open_left = false; }
-            fold_elem<MODE>(P, Q, e[j], v[j], a.lr, a.decay);
+            fold_elem<MODE>(P, Q, e[j], v[j], a.lr, a.eps_d);
             if (tail >> j & 1) {
                 if (!open_left) {
                     if (lane_on && r[j] != a.skip_row)
-                        *reinterpret_cast<float4*>(a.dst + (int64_t)r[j] * a.ld + c0) = fold_final<MODE>(old[j], P, Q, c0, a.lr, a.decay);
+                        *reinterpret_cast<float4*>(a.dst + (int64_t)r[j] * a.ld + c0) = fold_final<MODE>(old[j], P, Q, c0, a.lr, a.eps_d, a.log_decay);
                 } else {
                     PF = P; QF = Q; flag |= kHasF | kFClosed;
                 }
@@ -228,12 +239,12 @@ fold_tile_kernel(const FoldArgs a) {
         bool closed = false;
         for (int h = grp + 1; h < kGroups; ++h) {
             const int fh = sFlag[h];
-            fold_combine<MODE>(P, Q, sPF[h * kG + q], sQF[h * kG + q]);
+            fold_combine<MODE>(P, Q, sPF[h * kG + q], sQF[h * kG + q], a.log_decay);
             if (fh & kFClosed) { closed = true; break; }
         }
         if (closed) {
             if (lane_on && rowL != a.skip_row)
-                *reinterpret_cast<float4*>(a.dst + (int64_t)rowL * a.ld + c0) = fold_final<MODE>(oldL, P, Q, c0, a.lr, a.decay);
+                *reinterpret_cast<float4*>(a.dst + (int64_t)rowL * a.ld + c0) = fold_final<MODE>(oldL, P, Q, c0, a.lr, a.eps_d, a.log_decay);
         } else {      // the segment runs past this tile: carry-out
             reinterpret_cast<float4*>(a.out_q)[tile * kG + q] = Q;
             if (q == 0) { a.out_p[tile] = P; a.out_row[tile] = rowL; }
@@ -247,7 +258,7 @@ fold_tile_kernel(const FoldArgs a) {
             for (int h = 1; h < kGroups && !closed; ++h) {
                 const int fh = sFlag[h];
                 if (!(fh & kHasF)) break;     // only past the end of the list
-                fold_combine<MODE>(P, Q, sPF[h * kG + q], sQF[h * kG + q]);
+                fold_combine<MODE>(P, Q, sPF[h * kG + q], sQF[h * kG + q], a.log_decay);
                 closed = fh & kFClosed;
             }
             reinterpret_cast<float4*>(a.in_q)[tile * kG + q] = Q;
@@ -302,7 +313,7 @@ fold_stitch_kernel(const FoldArgs a, int tiles) {
 #pragma unroll
         for (int j = 0; j < kSt; ++j) {
             if (!gclosed && u + kSt * i0 + j < tiles) {
-                fold_combine<MODE>(gP, gQ, pp[j], qq[j]);
+                fold_combine<MODE>(gP, gQ, pp[j], qq[j], a.log_decay);
                 gclosed = fl[j] & kInClosed;
             }
         }
@@ -316,14 +327,14 @@ fold_stitch_kernel(const FoldArgs a, int tiles) {
             q2.x = __shfl_sync(0xffffffffu, gQ.x, src); q2.y = __shfl_sync(0xffffffffu, gQ.y, src);
             q2.z = __shfl_sync(0xffffffffu, gQ.z, src); q2.w = __shfl_sync(0xffffffffu, gQ.w, src);
             if (!closed) {
-                fold_combine<MODE>(P, Q, p2, q2);
+                fold_combine<MODE>(P, Q, p2, q2, a.log_decay);
                 closed = c != 0;
             }
         }
         u += 8 * kSt;
     }
     if (i0 == 0 && lane_on && row != a.skip_row)
-        *reinterpret_cast<float4*>(a.dst + (int64_t)row * a.ld + c0) = fold_final<MODE>(old, P, Q, c0, a.lr, a.decay);
+        *reinterpret_cast<float4*>(a.dst + (int64_t)row * a.ld + c0) = fold_final<MODE>(old, P, Q, c0, a.lr, a.eps_d, a.log_decay);
 }
 
 __global__ void decay_sweep_kernel(float4* __restrict__ table, int64_t X, int q, float decay,
@@ -392,10 +403,16 @@ extern "C" size_t dctr_scatter_workspace(int64_t M, int ld) {
 }
 
 static bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
+#include <cmath>
+static void set_decay(dctr::FoldArgs& a, double decay) {
+    a.decay = (float)decay;
+    a.eps_d = (float)(1.0 - decay);
+    a.log_decay = decay > 0.0 ? (float)std::log(decay) : 0.f;
+}
 
 static int scatter_sgd_impl(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F,
                             int d, const float* g, int64_t g_ld_n, int g_ld_f, const float* wts, int32_t skip_row, float lr,
-                            float decay, float* table, int64_t X, int ld, void* workspace,
+                            double decay, float* table, int64_t X, int ld, void* workspace,
                             size_t workspace_bytes, void* stream) {
     DCTR_REQUIRE(mode == DCTR_SCATTER_SUM || mode == DCTR_SCATTER_SEQ_DECAY, "scatter_sgd: bad mode %d", mode);
     DCTR_REQUIRE(M >= 0 && M < ((int64_t)1 << 31) && F > 0 && d > 0 && d <= ld && (ld & 3) == 0 && X > 0 && X < ((int64_t)1 << 31), "scatter_sgd: bad shape");
@@ -405,7 +422,7 @@ static int scatter_sgd_impl(int mode, const int32_t* sorted_rows, const int32_t*
                  "scatter_sgd: rows / pos / table / workspace must be 16-byte aligned");
     FoldArgs a{};
     a.skip_row = -1;
-    a.X = (int)X; a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table; a.dst = table;
+    a.X = (int)X; a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; set_decay(a, decay); a.table = table; a.dst = table;
     a.g = g; a.s = nullptr; a.ld_n = g_ld_n; a.ld_f = g_ld_f; a.wts = wts; a.skip_row = skip_row;
     // 128-bit gradient loads need whole float4s inside the source row: per-field blocks of >= ld floats, or -- g_ld_f = 0, the
     // embedding bag: every field of a sample shares the sample's row -- rows of >= ld floats
@@ -415,7 +432,7 @@ static int scatter_sgd_impl(int mode, const int32_t* sorted_rows, const int32_t*
 
 extern "C" int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F,
                                 int d, const float* g, int64_t g_ld_n, int g_ld_f, const float* wts, float lr,
-                                float decay, float* table, int64_t X, int ld, void* workspace,
+                                double decay, float* table, int64_t X, int ld, void* workspace,
                                 size_t workspace_bytes, void* stream) {
     return scatter_sgd_impl(mode, sorted_rows, sorted_pos, M, F, d, g, g_ld_n, g_ld_f, wts, -1, lr, decay, table, X, ld, workspace,
                             workspace_bytes, stream);
@@ -423,14 +440,14 @@ extern "C" int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int3
 
 extern "C" int dctr_scatter_sgd_masked(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F,
                                        int d, const float* g, int64_t g_ld_n, int g_ld_f, int32_t skip_row, float lr,
-                                       float decay, float* table, int64_t X, int ld, void* workspace,
+                                       double decay, float* table, int64_t X, int ld, void* workspace,
                                        size_t workspace_bytes, void* stream) {
     return scatter_sgd_impl(mode, sorted_rows, sorted_pos, M, F, d, g, g_ld_n, g_ld_f, nullptr, skip_row, lr, decay, table, X, ld,
                             workspace, workspace_bytes, stream);
 }
 
 extern "C" int dctr_scatter_sgd_fm(const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
-                                   const float* g, const float* s, int lds, const float* wts, float lr, float decay,
+                                   const float* g, const float* s, int lds, const float* wts, float lr, double decay,
                                    float* table, int64_t X, int ld, void* workspace, size_t workspace_bytes,
                                    void* stream) {
     DCTR_REQUIRE(M >= 0 && M < ((int64_t)1 << 31) && F > 0 && d > 0 && d <= ld && (ld & 3) == 0 && X > 0 && lds >= ld && (lds & 3) == 0,
@@ -441,7 +458,7 @@ extern "C" int dctr_scatter_sgd_fm(const int32_t* sorted_rows, const int32_t* so
                  "scatter_sgd_fm: rows / pos / table / s / workspace must be 16-byte aligned");
     FoldArgs a{};
     a.skip_row = -1;
-    a.X = (int)X; a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; a.decay = decay; a.table = table; a.dst = table;
+    a.X = (int)X; a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = lr; set_decay(a, decay); a.table = table; a.dst = table;
     a.g = g; a.s = s; a.ld_n = 0; a.ld_f = lds; a.wts = wts;
     return run_fold(kFm, a, true, workspace, workspace_bytes, as_stream(stream));
 }
@@ -458,7 +475,7 @@ extern "C" int dctr_scatter_grad_fm(const int32_t* sorted_rows, const int32_t* s
     FoldArgs a{};
     a.skip_row = -1;
     // the FM fold ends in  old*decay - lr*(Q - P*old):  decay = 0, lr = -1 leaves exactly the row's gradient
-    a.X = (int)X; a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = -1.f; a.decay = 0.f;
+    a.X = (int)X; a.rows = sorted_rows; a.pos = sorted_pos; a.M = M; a.F = F; a.d = d; a.ld = ld; a.lr = -1.f; set_decay(a, 0.0);
     a.table = const_cast<float*>(table); a.dst = grad_out;
     a.g = g; a.s = s; a.ld_n = 0; a.ld_f = lds; a.wts = wts;
     return run_fold(kFm, a, true, workspace, workspace_bytes, as_stream(stream));

@@ -10,7 +10,10 @@
 namespace dctr {
 
 constexpr int kSortThreads = 256;
-constexpr int kSortItems = 8;                       // chunks per warp
+#ifndef DCTR_SORT_ITEMS
+#define DCTR_SORT_ITEMS 8
+#endif
+constexpr int kSortItems = DCTR_SORT_ITEMS;        // 32-key rows per warp (experiment knob: -DDCTR_SORT_ITEMS=16)
 constexpr int kSortTile = kSortThreads * kSortItems;  // 2048 elements per CTA
 constexpr int kMaxPasses = 4;
 constexpr int kMaxRadix = 1024;

@@ -111,6 +111,21 @@ class StepEngine:
         self.overlap_sort = True
         self.wts_are_ones = True
         self.upd_rows = self.upd_pos = None     # use_update_list()
+        # Small two-hidden-layer nets at small batches: the whole MLP forward + backward as ONE kernel per 32-sample tile and
+        # the weight gradients (+ SGD) as one split-K kernel (csrc/mlp2.cu) instead of ~14 per-layer launches.
+        # DCTR_MLP2 = auto (batches <= 16384) | on | off
+        mode = os.environ.get("DCTR_MLP2", "auto")
+        ok = self.nl == 3 and bool(L.lib().dctr_mlp2_supported(self.widths[0], self.widths[1], self.widths[2]))
+        self.fused_mlp2 = ok and (mode == "on" or (mode == "auto" and self.N <= 16384))
+        self._mlp2_sgd = False                  # this step's fused kernels apply plain SGD to the MLP themselves
+        self._mlp2_cfg = None                   # (lr, decay_hidden, decay_out, train_bias) when they do
+        self._mlp2_tr_event = None
+        if self.fused_mlp2:
+            self.mlp2_ws = torch.zeros(L.lib().dctr_mlp2_workspace(N, self.widths[0], self.widths[1], self.widths[2]), dtype=torch.uint8, device=self.dev)
+            # transposed copies of the two hidden-layer weights, rebuilt on the second stream at the start of every step: the
+            # backward GEMMs then stream row-major [k][column] slabs like the forward ones
+            self.W1t = torch.zeros(self.widths[1], self.ldi[0], **f32)
+            self.W2t = torch.zeros(self.widths[2], self.ldi[1], **f32)
         self.skip_row = None        # set when the weights are 0 / 1 and 0 only marks this (all-zero pad) row: no weight gather in the fold
 
     # ---- the embedding front end (overridden by BagEngine) -------------------------------------------
@@ -197,6 +212,9 @@ class StepEngine:
         wts = None if self.wts_are_ones else self.wts
         ids, table, X = (self.ids, self.table, self.X) if lookup is None else lookup
         self._embed_forward(ids, wts, table, X, st)
+        if with_loss and self.fused_mlp2:
+            self._mlp2_forward_backward(gscale)
+            return
         if self.masks[0] is not None:
             self.ins[0].mul_(self.masks[0])     # input dropout (tf.nn.dropout on act(z1), FNN.py:87): torch elementwise
         for l in range(self.nl - 1):
@@ -221,8 +239,63 @@ class StepEngine:
                p(self.loss_n), p(self.dlogit), float(gscale), p(self.loss) if with_loss else None,
                p(self.col_ws), self.col_ws.numel(), st)
 
+    def _mlp2_forward_backward(self, gscale):
+        """csrc/mlp2.cu, kernel 1: x -> a1 -> a2 -> output unit -> dz2 -> dz1 -> dz0 for every 32-sample tile; with plain SGD
+        the kernel's last CTA also updates the output unit."""
+        p = L.ptr
+        D0, H1, H2 = self.widths
+        m0, ldm0 = self._mask(0)
+        m1, ldm1 = self._mask(1)
+        m2, ldm2 = self._mask(2)
+        sgd = self._mlp2_cfg is not None
+        lr, _, dout = self._mlp2_cfg[:3] if sgd else (0.0, 1.0, 1.0)
+        self._mlp2_sgd = sgd
+        main = torch.cuda.current_stream(self.dev)
+        if self._mlp2_tr_event is not None:             # the transposes were issued on the second stream (train_step)
+            main.wait_event(self._mlp2_tr_event)
+            self._mlp2_tr_event = None
+        else:
+            self._mlp2_transpose()
+        L.call("dctr_mlp2_train", self.N, D0, H1, H2, p(self.ins[0]), self.ldi[0], m0, ldm0, L.ACT[self.act_of(0)],
+               p(self.W(0)), self.ldw[0], p(self.b(0)), L.ACT[self.act_of(1)], m1, ldm1,
+               p(self.W(1)), self.ldw[1], p(self.b(1)), L.ACT[self.act_of(2)], m2, ldm2,
+               p(self.W1t), p(self.W2t), p(self.W(2)), p(self.b(2)), p(self.y), float(gscale), float(gscale),
+               p(self.ins[1]), self.ldi[1], p(self.dbuf[0]), p(self.dbuf[1]), self.dbuf[0].stride(0), p(self.dz0),
+               p(self.logit), p(self.pred), p(self.loss_n), p(self.dlogit), p(self.loss),
+               p(self.W(2, self.grads)), p(self.b(2, self.grads)), int(sgd), float(lr), float(dout),
+               p(self.mlp2_ws), self.mlp2_ws.numel(), self._st())
+
+    def _mlp2_transpose(self):
+        p = L.ptr
+        D0, H1, H2 = self.widths
+        L.call("dctr_mlp2_transpose", D0, H1, H2, p(self.W(0)), self.ldw[0], p(self.W(1)), self.ldw[1], p(self.W1t), self.ldi[0],
+               p(self.W2t), self.ldi[1], self._st())
+
+    def _mlp2_wgrad(self):
+        """kernel 2: both weight gradients and bias gradients as one split-K launch (gradients into self.grads, or SGD in
+        place); runs on the second stream next to the sparse update, which only needs dz0."""
+        p = L.ptr
+        D0, H1, H2 = self.widths
+        sgd = self._mlp2_sgd
+        lr, dhid, _ = self._mlp2_cfg[:3] if sgd else (0.0, 1.0, 1.0)
+        ov = self.overlap_wgrad
+        main = torch.cuda.current_stream(self.dev)
+        if ov:
+            self.side2.wait_stream(main)
+        with torch.cuda.stream(self.side2 if ov else main):
+            L.call("dctr_mlp2_wgrad", self.N, D0, H1, H2, p(self.ins[0]), self.ldi[0], p(self.ins[1]), self.ldi[1],
+                   p(self.dbuf[0]), p(self.dbuf[1]), self.dbuf[0].stride(0), p(self.W(0)), self.ldw[0], p(self.b(0)),
+                   p(self.W(1)), self.ldw[1], p(self.b(1)), p(self.W(0, self.grads)), p(self.b(0, self.grads)),
+                   p(self.W(1, self.grads)), p(self.b(1, self.grads)), int(sgd), float(lr), float(dhid),
+                   p(self.mlp2_ws), self.mlp2_ws.numel(), self._st())
+        if ov:
+            self._wgrad_pending = True
+
     def backward(self):
         """Fills self.grads (dense) and leaves d loss / d z in self.dbuf[k]; returns that buffer."""
+        if self.fused_mlp2:
+            self._mlp2_wgrad()
+            return self.dz0
         st = self._st()
         N, p = self.N, L.ptr
         last = self.nl - 1
@@ -368,6 +441,13 @@ class StepEngine:
         embedding-side bias (SNN_DAE.py:151-153)."""
         self.join_wgrad()
         st = self._st()
+        if self._mlp2_sgd:                 # the fused kernels updated the MLP; what is left is the embedding-side bias
+            self._mlp2_sgd = False
+            if self._mlp2_cfg[3]:
+                hi = self.bias_off
+                L.call("dctr_dense_sgd", self.params.data_ptr() + 4 * hi, self.grads.data_ptr() + 4 * hi, self.n_params - hi,
+                       float(lr), 1.0, st)
+            return
         if self.adam is not None:          # same step counter as the table (embedding_update ticked it)
             b1, b2, eps = self.adam
             L.call("dctr_dense_adam", L.ptr(self.params), L.ptr(self.grads), L.ptr(self.params_m), L.ptr(self.params_v),
@@ -404,12 +484,22 @@ class StepEngine:
                 self.sort_ids()
         else:                                    # per-kernel timing (bench.py): everything on one stream
             self.sort_ids()
+        # plain SGD on one GPU: the fused MLP kernels apply the update themselves (the multi-GPU steps call forward / backward
+        # directly and all-reduce self.grads first, Adam / FTRL need the gradients)
+        plain = self.fused_mlp2 and not self.dense_optimizer
+        if self.fused_mlp2 and self.overlap_wgrad:     # W^T for the backward GEMMs: off the critical path, next to the gather
+            self.side2.wait_stream(cur)
+            with torch.cuda.stream(self.side2):
+                self._mlp2_transpose()
+                self._mlp2_tr_event = self.side2.record_event()
+        self._mlp2_cfg = (float(lr), float(mlp_decay), float(last_decay if mlp_decay == 1.0 else mlp_decay), bool(train_bias)) if plain else None
         self.forward(True, gscale)
         dz = self.backward()
         if self.overlap_sort:
             cur.wait_stream(self.side)
         self.embedding_update(dz, lr, decay, train_bias)
         self.dense_update(lr, last_decay, mlp_decay)
+        self._mlp2_cfg = None
 
 
 class BagEngine(StepEngine):
@@ -480,6 +570,7 @@ class FMEngine:
         self.overlap_sort = True
         self.adam = None
         self.ftrl = None
+        self.l2_ws = torch.zeros(L.lib().dctr_reduce_workspace(1, 1), dtype=torch.uint8, device=self.dev)
         self.launch_mode = 1 if self.N <= 16384 else 0       # FM step = 10 short kernels: -9 % with dependent launches
         self.wts_are_ones = False
 
@@ -497,7 +588,7 @@ class FMEngine:
     def _st(self):
         return torch.cuda.current_stream(self.dev).cuda_stream
 
-    def forward(self, with_loss, gscale=1.0):
+    def forward(self, with_loss, gscale=1.0, lam=0.0):
         p = L.ptr
         wts = None if self.wts_are_ones else self.wts
         L.call("dctr_fm_fwd", p(self.ids), p(wts), p(self.table), self.X, self.ld, self.N, self.F, self.d,
@@ -505,6 +596,9 @@ class FMEngine:
                p(self.loss_n), p(self.g), p(self.s) if with_loss else None, self.lds, self._st())
         if with_loss:
             L.call("dctr_vec_sum", p(self.loss_n), self.N, float(gscale), p(self.loss), self._st())
+            if lam != 0.0:      # the loss the reference fetches carries lam * (l2_loss(W) + l2_loss(V) + l2_loss(b)) (FM.py:39, LR.py:37)
+                L.call("dctr_l2_loss_add", p(self.table), self.X * self.ld, p(self.bias()), 1, float(lam), p(self.loss),
+                       p(self.l2_ws), self.l2_ws.numel(), self._st())
 
     def enable_adam(self, eps=1e-8, beta1=0.9, beta2=0.999):
         f32 = dict(dtype=torch.float32, device=self.dev)
@@ -536,7 +630,7 @@ class FMEngine:
                 self.sort_ids()
         else:                                    # per-kernel timing (bench.py): everything on one stream
             self.sort_ids()
-        self.forward(True, gscale)
+        self.forward(True, gscale, lam)
         st = self._st()
         p = L.ptr
         L.call("dctr_vec_sum", p(self.g), self.N, 1.0, p(self.grads), st)           # d loss / d b = sum_n g_n

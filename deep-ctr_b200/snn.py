@@ -45,6 +45,10 @@ class SNN(_Base):
         eng.set_layer(1, ww2, bb2)
         eng.set_layer(2, np.zeros((hidden2, 1)), np.zeros(1))
         eng.wts_are_ones = False
+        # the dropout branch computes hidden layer 2 with tanh whatever acti_type says (SNN_DAE.py:136-137); the prediction
+        # branch uses acti_type (:127-133)
+        self._acts_train, self._acts_eval = [None, act, "tanh"], [None, act, act]
+        eng.acts = self._acts_train
         eng.skip_row = X            # 0 / 1 weights, 0 only on the pad row: no weight gather in the fold
         self.pad_row = X
         self.mask_streams = MaskStreams(hidden1, hidden2, dropout) if dropout < 1.0 else None
@@ -103,8 +107,10 @@ class SNN(_Base):
         return self._stage_and_step(ids, wts, y)
 
     def _swap_masks(self, masks):
+        """masks = None: the prediction branch (no dropout, acti_type on both hidden layers); otherwise back to training"""
         old = self.engine.masks
         self.engine.masks = masks if masks is not None else [None] * self.engine.nl
+        self.engine.acts = self._acts_eval if masks is None else self._acts_train
         return old
 
     def predict(self, feats):

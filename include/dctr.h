@@ -143,6 +143,8 @@ int dctr_sort_pairs(const int32_t* ids, const int32_t* payload, int64_t M, int64
  * The fold is flat over the sorted list: 4-lane groups fold DCTR_FOLD_CHUNK consecutive elements, pieces that
  * cross chunk / tile borders are composed in list order (fixed association => bit-reproducible).
  * rows / pos / table / workspace must be 16-byte aligned.
+ * decay is a DOUBLE: the Theano factor 1 - 2*lambda_fm*lr/N (FNN_wnzh.py:305) is 1 - 4.9e-8 at the headline configuration, below
+ * float32's resolution at 1.0; the kernels apply it as x - (1-decay)*x and decay^m as exp(m*log(decay)).
  * workspace: dctr_scatter_workspace(M, ld) bytes (one carry-in and one carry-out partial per tile). */
 #ifndef DCTR_FOLD_CHUNK
 #define DCTR_FOLD_CHUNK 4    /* sorted elements folded serially by one 4-lane group (4 or 8; 4: <= 64 registers, 4 CTAs per SM) */
@@ -151,7 +153,7 @@ int dctr_sort_pairs(const int32_t* ids, const int32_t* payload, int64_t M, int64
 size_t dctr_scatter_workspace(int64_t M, int ld);
 int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
                      const float* g, int64_t g_ld_n, int g_ld_f, const float* wts,
-                     float lr, float decay, float* table, int64_t X, int ld,
+                     float lr, double decay, float* table, int64_t X, int ld,
                      void* workspace, size_t workspace_bytes, void* stream);
 /* The same fold for 0 / 1 weights where 0 only occurs on ONE row -- the all-zero pad row that stands in for a field a sample
  * does not have (feats_to_layer_one_array leaves x = 0 there, FNN_wnzh.py:91-95): every slot has weight 1 and the segment of
@@ -159,14 +161,14 @@ int dctr_scatter_sgd(int mode, const int32_t* sorted_rows, const int32_t* sorted
  * lists larger than L2) disappears.  skip_row = -1 skips nothing. */
 int dctr_scatter_sgd_masked(int mode, const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
                             const float* g, int64_t g_ld_n, int g_ld_f, int32_t skip_row,
-                            float lr, float decay, float* table, int64_t X, int ld,
+                            float lr, double decay, float* table, int64_t X, int ld,
                             void* workspace, size_t workspace_bytes, void* stream);
 /* FM source (FM.py:55-64 differentiated):
  *   grad(p,0) = g[n]*x_p ; grad(p,c>=1) = g[n]*( x_p*s[n,c] - x_p^2*row_old[c] ) ; row = row*decay - lr*sum grad
  *   (decay = 1 - lr*lambda realises the L2 term of FM.py:39 on the touched rows). */
 int dctr_scatter_sgd_fm(const int32_t* sorted_rows, const int32_t* sorted_pos, int64_t M, int F, int d,
                         const float* g, const float* s, int lds, const float* wts,
-                        float lr, float decay, float* table, int64_t X, int ld,
+                        float lr, double decay, float* table, int64_t X, int ld,
                         void* workspace, size_t workspace_bytes, void* stream);
 
 /* Gradient-only form of the FM fold (for optimizers that need the densified gradient, i.e. Adam): rows are read from
@@ -236,6 +238,12 @@ int dctr_col_wsum(const float* A, int lda, int N, int H, const float* wv, float*
 /*   out[0] = sum_n v[n]  (fixed order, one CTA) -- loss = reduce_sum(log_loss) (FM.py:36) */
 int dctr_vec_sum(const float* v, int N, float scale, float* out, void* stream);
 
+/*   out[0] += scale * ( sum(v[0:n)^2) + sum(extra[0:n_extra)^2) ) / 2 -- the regulariser lam * (l2_loss(W) + l2_loss(V) + l2_loss(b)) that
+ *   FM.py:39 / LR.py:37 add to the loss the caller fetches (tf.nn.l2_loss = sum(t^2) / 2).  n % 4 == 0, v 16-byte aligned; partial
+ *   sums in double, fixed order.  workspace: dctr_reduce_workspace(1, 1) bytes, zero-filled once. */
+int dctr_l2_loss_add(const float* v, int64_t n, const float* extra, int n_extra, float scale, float* out,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- K7: dense SGD over a flat parameter buffer (tf_util.py:27 / FNN_wnzh.py:180-182) ---------- */
 int dctr_dense_sgd(float* param, const float* grad, int64_t n, float lr, float decay, void* stream);
 
@@ -259,6 +267,36 @@ int dctr_dense_adam(float* param, float* grad, float* m, float* v, int64_t n, co
  * not seen a gradient yet becomes 0 on the first step.  zero_grad != 0 clears grad afterwards. */
 int dctr_dense_ftrl(float* param, float* grad, float* accum, float* linear, int64_t n, float lr, float lr_power,
                     float l1, float l2, float grad_l2, int zero_grad, void* stream);
+
+/* ---- fused train step of a two-hidden-layer MLP at small batches (csrc/mlp2.cu) -------------------------------------------
+ * replaces the whole Theano graph of FNN_wnzh.py:147-182 (and FNN.py:86-94 at small widths) -- forward, loss, T.grad, the SGD
+ * updates -- with two launches instead of ~14 per-layer ones.  fp32 FFMA (the layers are far too small for tensor-core tiles).
+ *   x [N, ld0] = act0(z) of the embedding layer (dctr_gather_concat_fwd); m0 / m1 / m2: dropout masks on x / a1 / a2
+ *   ([N, ld] with ldm = row stride, or one broadcast row with ldm = 0, or NULL); W1 [D0, ldw1], W2 [H1, ldw2], w3 [H2].
+ * dctr_mlp2_train: a1 = m1*act1(x W1 + b1), a2 = m2*act2(a1 W2 + b2), logit = a2 w3 + b3, pred, loss_n, dlogit = (pred-y)*gscale,
+ *   loss_sum = loss_scale * sum loss_n, then dz2, dz1 [N, ldd] (gradients w.r.t. the pre-activations) and dz0 [N, ld0] (the
+ *   gradient w.r.t. z: Theano's gx, what the sparse update folds).  x is overwritten by x*m0 when m0 != NULL; a1 is stored.
+ *   W1t [H1, ld0] / W2t [H2, ld1] are the TRANSPOSED weights (dctr_mlp2_transpose) the backward GEMMs stream.
+ *   sgd != 0: the kernel's last CTA applies w3 = w3*decay_out - lr*gw3 (b3 likewise); else gw3 [H2], gb3 [1] are written.
+ * dctr_mlp2_wgrad: gW1 = x^T dz1, gb1 = colsum dz1, gW2 = a1^T dz2, gb2 = colsum dz2 in one split-K launch (fixed order);
+ *   sgd != 0: W = W*decay - lr*gW in place (biases likewise), else the gradients are stored (same leading dimensions as W).
+ * workspace: dctr_mlp2_workspace bytes, zero-filled once, shared by the three entry points.  Supported: dctr_mlp2_supported. */
+int dctr_mlp2_supported(int D0, int H1, int H2);
+size_t dctr_mlp2_workspace(int N, int D0, int H1, int H2);
+int dctr_mlp2_transpose(int D0, int H1, int H2, const float* W1, int ldw1, const float* W2, int ldw2, float* W1t, int ld0,
+                        float* W2t, int ld1, void* stream);
+int dctr_mlp2_train(int N, int D0, int H1, int H2, float* x, int ld0, const float* m0, int ldm0, int act0,
+                    const float* W1, int ldw1, const float* b1, int act1, const float* m1, int ldm1,
+                    const float* W2, int ldw2, const float* b2, int act2, const float* m2, int ldm2,
+                    const float* W1t, const float* W2t, float* w3, float* b3, const float* y, float gscale, float loss_scale,
+                    float* a1, int ld1, float* dz1, float* dz2, int ldd, float* dz0,
+                    float* logit, float* pred, float* loss_n, float* dlogit, float* loss_sum,
+                    float* gw3, float* gb3, int sgd, float lr, float decay_out,
+                    void* workspace, size_t workspace_bytes, void* stream);
+int dctr_mlp2_wgrad(int N, int D0, int H1, int H2, const float* x, int ld0, const float* a1, int ld1,
+                    const float* dz1, const float* dz2, int ldd, float* W1, int ldw1, float* b1, float* W2, int ldw2,
+                    float* b2, float* gW1, float* gb1, float* gW2, float* gb2, int sgd, float lr, float decay,
+                    void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- embedding bag: the first layer of the SNN models (get_fi_h1_y, SNN_DAE.py:234-260, SNN_RBM.py:238-262)
  *   out[n, c] = act( b0[c] + sum_f wts[n,f] * table[ids[n,f], c] ),  c < H;  columns H..ldo-1 are written as 0

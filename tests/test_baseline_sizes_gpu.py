@@ -173,13 +173,19 @@ def test_fnn_criteo_step_at_baseline_size():
                       [vm["h%d_b" % (i + 1)] for i in range(nl)], 39, 11, "none", False, "tanh", "tanh")
     for step, (ids, wts, y) in enumerate(pool):
         loss, p = train(ids, wts, y)
+        # magnitude of the terms each row's gradient sum is made of: the error of a 65 536-term fp32 sum (rows 0..12 are hit by
+        # every sample) scales with sum |g|, not with the much smaller |sum g| the terms cancel to
+        logit, cache = net.forward(ids, wts.astype(np.float64))
+        ge = net.backward(cache, O.sigmoid(logit) - y)[3]
+        mag = np.zeros((net.table.shape[0], 1))
+        np.add.at(mag, ids.reshape(-1), np.abs(ge).reshape(-1, 11).max(1, keepdims=True))
         ol, op = net.train_step_tf(ids, wts.astype(np.float64), y, 1e-3)
         vm = m.var_map()
         e_p, e_l = relerr(p, op, 1e-3), abs(loss - ol) / abs(ol)
         touched = np.unique(ids)
-        e_t = relerr(np.concatenate([vm["W"], vm["V"]], 1)[touched], net.table[touched], 1e-3)
+        got_t = np.concatenate([vm["W"], vm["V"]], 1)[touched].astype(np.float64)
+        e_t = float(np.max(np.abs(got_t - net.table[touched]) / (np.abs(net.table[touched]) + 1e-3 * mag[touched] + 1e-3)))
         # a weight gradient here is a sum over 65 536 samples: compare against the scale of the layer
         e_w = max(float(np.max(np.abs(vm["h%d_w" % (i + 1)] - net.Ws[i])) / np.max(np.abs(net.Ws[i]))) for i in range(nl))
         print("fnn_criteo step %d: loss %.2e preds %.2e touched rows %.2e weights %.2e (of max|W|)" % (step, e_l, e_p, e_t, e_w))
-        assert max(e_p, e_l, e_w) <= (step + 1) * RTOL
-        assert e_t <= 3 * (step + 1) * RTOL            # rows 0..12 fold 65 536 fp32 gradients each
+        assert max(e_p, e_l, e_w, e_t) <= (step + 1) * RTOL

@@ -18,10 +18,12 @@ def _need_cuda():
         pytest.skip("no CUDA device")
 
 
-@pytest.fixture(autouse=True, params=["simt", "tc"])
+@pytest.fixture(autouse=True, params=["simt", "tc", "mlp2"])
 def gemm_path(request, monkeypatch):
-    """Every model-level parity test runs on both MLP GEMM paths (fp32 FFMA and tcgen05 3xTF32)."""
-    monkeypatch.setenv("DCTR_GEMM", request.param)
+    """Every model-level parity test runs on the per-layer GEMM paths (fp32 FFMA, tcgen05 3xTF32) and with the fused
+    two-hidden-layer kernels of csrc/mlp2.cu (which only apply to models with two hidden layers)."""
+    monkeypatch.setenv("DCTR_GEMM", "simt" if request.param == "mlp2" else request.param)
+    monkeypatch.setenv("DCTR_MLP2", "on" if request.param == "mlp2" else "off")
     return request.param
 
 

@@ -26,9 +26,10 @@ def gold():
         return pickle.load(f)
 
 
-@pytest.fixture(params=["simt", "tc"])
+@pytest.fixture(params=["simt", "tc", "mlp2"])
 def gemm_path(request, monkeypatch):
-    monkeypatch.setenv("DCTR_GEMM", request.param)
+    monkeypatch.setenv("DCTR_GEMM", "simt" if request.param == "mlp2" else request.param)
+    monkeypatch.setenv("DCTR_MLP2", "on" if request.param == "mlp2" else "off")
     return request.param
 
 
