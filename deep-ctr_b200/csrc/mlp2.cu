@@ -13,9 +13,10 @@
 //                         k-rows (each slab is read from L2 once per CTA).  The backward GEMMs read TRANSPOSED copies of the
 //                         weights (mlp2_transpose_kernel, a side-stream launch per step) so every phase is the same row-major
 //                         [k][column] stream.  Leaves x (masked), a1, dz1, dz2 in global memory for the weight gradients.
-//   mlp2_wgrad_kernel     gW1 = x^T dz1, gW2 = a1^T dz2 and both bias gradients as ONE split-K launch over 128x64 output tiles,
-//                         8x8 outputs per thread; the CTA that completes a tile adds the partial slabs in split order (fixed
-//                         order, no float atomics) and either stores the gradient or applies plain SGD in place.
+//   mlp2_wgrad_kernel     gW1 = x^T dz1, gW2 = a1^T dz2 and both bias gradients as ONE launch of 8-CTA clusters, one 64x64 output tile per
+//                         cluster; the 8 CTAs split the batch, park their partial tiles in shared memory and add them in rank
+//                         order through distributed shared memory (fixed order, no float atomics, no global round trip), then
+//                         store the gradient or apply plain SGD in place.
 //
 // What bounds the first kernel: shared-memory -> register bandwidth (128 B/clk/SM).  A thread tile of R samples x C columns
 // needs (R + C) / (R C) operand floats per FFMA; with 32 samples x 300 columns per 256 threads R = 4, C = 12 is what fits:
@@ -101,7 +102,9 @@ __device__ __forceinline__ void slab_mainloop(const Slab& s, float* ring, const 
         __syncthreads();                                   // slab c has landed for everyone; slab c-1 is no longer read
         slab_issue(s, c + kM2Stages - 1, ring + ((c + kM2Stages - 1) % kM2Stages) * kM2StageFloats);
         const float* st = ring + (c % kM2Stages) * kM2StageFloats + lane;
-#pragma unroll
+        // unrolled by 2 only: the fully unrolled body (8 k x 61 instructions = 7.8 KB) did not fit the instruction cache and the
+        // kernel spent 2.9 cycles per issued instruction waiting for fetches (profiles/r02_ncu_mlp2_v2.txt)
+#pragma unroll 2
         for (int k = 0; k < kM2KC; ++k) {
             const float4 a = *reinterpret_cast<const float4*>(arow + (c * kM2KC + k) * kM2LdT);      // the warp's 4 samples: broadcast
             const float* b = st + k * s.ldb;
@@ -157,8 +160,11 @@ __device__ __forceinline__ void tile_to_global(const float* __restrict__ tt, int
     }
 }
 
-// derivative of `act` at a masked activation value v = m * act(z): m * act'(act(z)), 0 where the unit was dropped
-__device__ __forceinline__ float dact_masked(int act, float v, float m) { return m != 0.f ? m * act_bwd_from_out(act, v / m) : 0.f; }
+// derivative of `act` at a masked activation value v = m * act(z): m * act'(act(z)), 0 where the unit was dropped.
+// Both helpers are deliberately NOT inlined: the epilogues call them for 48 register values at 12 call sites, and the inlined
+// tanhf / expf expansions made the kernel 670 KB of code (instruction-fetch bound, profiles/r02_ncu_mlp2_v2.txt).
+__device__ __noinline__ float dact_masked(int act, float v, float m) { return m != 0.f ? m * act_bwd_from_out(act, v / m) : 0.f; }
+__device__ __noinline__ float m2_act(int act, float x) { return act_fwd(act, x); }
 
 __global__ void __launch_bounds__(kM2Threads, 1)
 mlp2_train_kernel(const Mlp2Args a) {
@@ -206,14 +212,14 @@ mlp2_train_kernel(const Mlp2Args a) {
     auto mask_of = [&](const float* m, int ldm, int u, int c) { return m ? __ldg(m + (ldm ? grow[u] : 0) * ldm + c) : 1.f; };
 
     // ---- layer 1: a1 = m1 * act1(x W1 + b1) ----
-    gemm_phase(s1, ring, xt, a1t, a.H1, [&](int u, int c, float v) { return act_fwd(a.act1, v + __ldg(a.b1 + c)) * mask_of(a.m1, a.ldm1, u, c); });
+    gemm_phase(s1, ring, xt, a1t, a.H1, [&](int u, int c, float v) { return m2_act(a.act1, v + __ldg(a.b1 + c)) * mask_of(a.m1, a.ldm1, u, c); });
     Slab s2 = make_slab(a.W2, a.ldw2, a.H1);
     slab_prologue(s2, ring);
     __syncthreads();
     tile_to_global(a1t, a.H1, a.a1 + (size_t)r0 * a.ld1, a.ld1, a.ld1 >> 2, rows);
 
     // ---- layer 2: a2 = m2 * act2(a1 W2 + b2) ----
-    gemm_phase(s2, ring, a1t, a2t, a.H2, [&](int u, int c, float v) { return act_fwd(a.act2, v + __ldg(a.b2 + c)) * mask_of(a.m2, a.ldm2, u, c); });
+    gemm_phase(s2, ring, a1t, a2t, a.H2, [&](int u, int c, float v) { return m2_act(a.act2, v + __ldg(a.b2 + c)) * mask_of(a.m2, a.ldm2, u, c); });
     Slab s3 = make_slab(a.W2t, a.ld1, a.H2);         // dz2 * W2^T comes next: B = W2^T [H2, ld1]
     slab_prologue(s3, ring);
     __syncthreads();
@@ -328,14 +334,15 @@ mlp2_transpose_kernel(const float* __restrict__ W1, int ldw1, int D0, int H1, fl
 }
 
 // ---- weight gradients of both layers (+ bias gradients) as one launch of 8-CTA clusters ------------------------------------------
-// Work item = (layer, 128x64 output tile) per CLUSTER; the 8 CTAs of the cluster split the batch (k) dimension.  A[k][i] = layer
-// input (x or a1, [N, lda]), B[k][j] = dz of the layer.  CTA: 128 threads, thread (ty, tx) owns outputs i0 + 8 ty .. +7 (ty < 16) and
-// columns j0 + 4 tx .. +3 and j0 + 32 + 4 tx .. +3 (tx < 8): per k four 128-bit operand reads for 64 FFMA; k in slabs of 16 samples
+// Work item = (layer, 64x64 output tile) per CLUSTER (25 tiles x 8 CTAs for 177-300-100: several CTAs per SM, a 128x64 tile with
+// one 4-warp CTA per SM left every scheduler with a single warp, 47 % issue activity); the 8 CTAs of the cluster split the batch (k) dimension.  A[k][i] = layer
+// input (x or a1, [N, lda]), B[k][j] = dz of the layer.  CTA: 128 threads, thread (ty, tx) owns outputs i0 + 4 ty .. +3 (ty < 16) and
+// columns j0 + 4 tx .. +3 and j0 + 32 + 4 tx .. +3 (tx < 8): per k three 128-bit operand reads for 32 FFMA; k in slabs of 16 samples
 // through a 3-stage cp.async ring.  The split-K reduction never touches global memory: every CTA parks its partial tile in its own
-// shared memory, and after a cluster barrier CTA r adds rows 16 r .. 16 r + 15 of the 8 partials in rank order through distributed
+// shared memory, and after a cluster barrier CTA r adds rows 8 r .. 8 r + 7 of the 8 partials in rank order through distributed
 // shared memory (fixed order: deterministic, no float atomics) and stores the gradient or applies plain SGD in place.  Rank 0 also
 // folds the bias gradient (column sums of dz) of the tiles with i0 == 0.
-constexpr int kWgTI = 128, kWgTJ = 64, kWgK = 16, kWgThreads = 128, kWgStages = 3, kWgSplit = 8;
+constexpr int kWgTI = 64, kWgTJ = 64, kWgK = 16, kWgThreads = 128, kWgStages = 3, kWgSplit = 8;
 constexpr int kWgRing = kWgStages * kWgK * (kWgTI + kWgTJ);       // floats: 9216
 constexpr int kWgPart = kWgTI * kWgTJ + kWgTJ;                    // floats: the partial tile + its bias row
 constexpr int kWgSmem = (kWgRing > kWgPart ? kWgRing : kWgPart) * 4;
@@ -347,7 +354,7 @@ struct WgArgs {
     int sgd; float lr;
 };
 
-__global__ void __launch_bounds__(kWgThreads, 4)
+__global__ void __launch_bounds__(kWgThreads, 5)
 mlp2_wgrad_kernel(const WgArgs a) {
     pdl_sync();
     extern __shared__ __align__(16) float wsm[];
@@ -363,21 +370,21 @@ mlp2_wgrad_kernel(const WgArgs a) {
     const int i0 = ti_ * kWgTI, j0 = tj_ * kWgTJ;
     const int k_lo = (int)split * a.rows_per_split, k_hi = min(L.K, k_lo + a.rows_per_split);
     const int tid = threadIdx.x, ty = tid >> 3, tx = tid & 7;
-    float acc[8][8];
+    float acc[4][8];
 #pragma unroll
-    for (int u = 0; u < 8; ++u)
+    for (int u = 0; u < 4; ++u)
 #pragma unroll
         for (int v = 0; v < 8; ++v) acc[u][v] = 0.f;
     float bsum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     const bool do_bias = (i0 == 0) && ty == 0;
     const int nslabs = k_hi > k_lo ? (k_hi - k_lo + kWgK - 1) / kWgK : 0;
-    // slab: 16 rows x 128 floats of A (512 float4) and 16 x 64 of B (256 float4): 4 + 2 pieces per thread, zero outside the matrix
+    // slab: 16 rows x 64 floats of A and of B (256 float4 each): 2 + 2 pieces per thread, zero outside the matrix
     auto load = [&](int s, int buf) {
         if (s < nslabs) {
             const int kb = k_lo + s * kWgK;
 #pragma unroll
-            for (int h = 0; h < 4; ++h) {
-                const int idx = tid + kWgThreads * h, r = idx >> 5, q = (idx & 31) * 4;
+            for (int h = 0; h < 2; ++h) {
+                const int idx = tid + kWgThreads * h, r = idx >> 4, q = (idx & 15) * 4;
                 float* d = &As[buf][r][q];
                 if (kb + r < k_hi && i0 + q + 3 < L.lda) cp_async16(d, L.A + (size_t)(kb + r) * L.lda + i0 + q);
                 else *reinterpret_cast<float4*>(d) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -399,13 +406,13 @@ mlp2_wgrad_kernel(const WgArgs a) {
         __syncthreads();
         load(s + 2, (s + 2) % kWgStages);
         const int buf = s % kWgStages;
-#pragma unroll
+#pragma unroll 4
         for (int k = 0; k < kWgK; ++k) {
-            const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][8 * ty]), a1 = *reinterpret_cast<const float4*>(&As[buf][k][8 * ty + 4]);
+            const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][4 * ty]);
             const float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][k][4 * tx]), b1 = *reinterpret_cast<const float4*>(&Bs[buf][k][32 + 4 * tx]);
-            const float aa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w}, bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            const float aa[4] = {a0.x, a0.y, a0.z, a0.w}, bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-            for (int u = 0; u < 8; ++u)
+            for (int u = 0; u < 4; ++u)
 #pragma unroll
                 for (int v = 0; v < 8; ++v) acc[u][v] = fmaf(aa[u], bb[v], acc[u][v]);
             if (do_bias) {
@@ -416,10 +423,10 @@ mlp2_wgrad_kernel(const WgArgs a) {
     }
     cp_async_wait<0>();
     __syncthreads();                 // the operand ring is dead: the partial tile takes its place
-    float* part = wsm;               // [128][64] | bias [64]
+    float* part = wsm;               // [64][64] | bias [64]
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
-        float* pr = part + (8 * ty + u) * kWgTJ;
+    for (int u = 0; u < 4; ++u) {
+        float* pr = part + (4 * ty + u) * kWgTJ;
         *reinterpret_cast<float4*>(pr + 4 * tx) = make_float4(acc[u][0], acc[u][1], acc[u][2], acc[u][3]);
         *reinterpret_cast<float4*>(pr + 32 + 4 * tx) = make_float4(acc[u][4], acc[u][5], acc[u][6], acc[u][7]);
     }
@@ -430,9 +437,9 @@ mlp2_wgrad_kernel(const WgArgs a) {
     }
     // cluster barrier (release / acquire): every partial tile is visible to the whole cluster
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-    // ---- CTA r: rows 16 r .. 16 r + 15 of the tile (256 float4, two per thread) over the partials of ranks 0 .. 7, in rank order ----
+    // ---- CTA r: rows 8 r .. 8 r + 7 of the tile (128 float4, one per thread) over the partials of ranks 0 .. 7, in rank order ----
     const unsigned my = (unsigned)__cvta_generic_to_shared(part);
-    const int rpc = kWgTI / kWgSplit;            // 16 rows per CTA
+    const int rpc = kWgTI / kWgSplit;            // 8 rows per CTA
     for (int e = tid; e < (rpc + (split == 0 ? 1 : 0)) * (kWgTJ / 4); e += kWgThreads) {
         const int rr = e / (kWgTJ / 4), q = (e - rr * (kWgTJ / 4)) * 4;
         const bool bias_row = rr == rpc;

@@ -10,11 +10,8 @@
 namespace dctr {
 
 constexpr int kSortThreads = 256;
-#ifndef DCTR_SORT_ITEMS
-#define DCTR_SORT_ITEMS 8
-#endif
-constexpr int kSortItems = DCTR_SORT_ITEMS;        // 32-key rows per warp (experiment knob: -DDCTR_SORT_ITEMS=16)
-constexpr int kSortTile = kSortThreads * kSortItems;  // 2048 elements per CTA
+constexpr int kSortItems = 8;                       // 32-key rows per warp: 2048 keys per CTA (16 rows = 4096 keys on long lists)
+constexpr int kSortTile = kSortThreads * kSortItems;  // histogram tile
 constexpr int kMaxPasses = 4;
 constexpr int kMaxRadix = 1024;
 enum : unsigned { kFlagAgg = 1u, kFlagPrefix = 2u };       // tile status = (count << 2) | flag
@@ -59,7 +56,7 @@ sort_hist_kernel(const int32_t* __restrict__ keys, int64_t M, int passes, unsign
 // R/256 digits back to the nearest tile whose inclusive prefix is published), and scatters.  Tiles are handed out in ticket
 // order, so a CTA only ever waits on tiles that are already running: no deadlock, and the output does not depend on timing.
 // pos_in == nullptr: payload is the element index itself (first pass)
-template <int RB>
+template <int RB, int ITEMS>
 __global__ void __launch_bounds__(kSortThreads)
 sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict__ pos_in, int64_t M, int shift,
                  const unsigned* __restrict__ ghist, unsigned* __restrict__ ticket, volatile unsigned* __restrict__ status,
@@ -72,8 +69,9 @@ sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict_
     unsigned* cnt = sort_smem;                            // [NW][R] per-warp digit counts -> exclusive prefix over the warps
     unsigned* gbase = cnt + NW * R;                       // [R]
     unsigned* lbase = gbase + R;                          // [R]
-    int32_t* skey = reinterpret_cast<int32_t*>(lbase + R);   // [kSortTile]
-    int32_t* spos = skey + kSortTile;                     // [kSortTile]
+    constexpr int TILE = kSortThreads * ITEMS;
+    int32_t* skey = reinterpret_cast<int32_t*>(lbase + R);   // [TILE]
+    int32_t* spos = skey + TILE;                          // [TILE]
     __shared__ unsigned wsum[NW], lsum[NW];
     __shared__ unsigned s_tile;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -81,16 +79,25 @@ sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict_
     for (int i = tid; i < NW * R; i += kSortThreads) cnt[i] = 0;
     __syncthreads();
     const unsigned tile = s_tile;
-    const int64_t base = (int64_t)tile * kSortTile;
+    const int64_t base = (int64_t)tile * TILE;
 
-    // ---- stable ranks inside the tile: warp w owns rows w*8 .. w*8+7 of 32 consecutive keys ----
-    int32_t key[kSortItems];
-    unsigned rank[kSortItems];
+    // ---- stable ranks inside the tile: warp w owns rows w*ITEMS .. w*ITEMS+ITEMS-1 of 32 consecutive keys ----
+    // keys AND payloads are fetched up front (the payload is only needed by the reorder step, but loading it there exposed a
+    // full memory latency per tile)
+    int32_t key[ITEMS], pay[ITEMS];
+    unsigned rank[ITEMS];
 #pragma unroll
-    for (int j = 0; j < kSortItems; ++j) {
-        const int64_t i = base + (warp * kSortItems + j) * 32 + lane;
+    for (int j = 0; j < ITEMS; ++j) {
+        const int64_t i = base + (warp * ITEMS + j) * 32 + lane;
         const bool valid = i < M;
-        key[j] = valid ? (first ? sane_key(keys_in[i], X) : keys_in[i]) : 0;
+        key[j] = valid ? keys_in[i] : 0;
+        pay[j] = valid ? (pos_in ? pos_in[i] : (int32_t)i) : 0;
+    }
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const int64_t i = base + (warp * ITEMS + j) * 32 + lane;
+        const bool valid = i < M;
+        if (first) key[j] = sane_key(key[j], X);
         const int dg = digit_of<RB>(key[j], shift);
         // lanes holding the same digit: one ballot per digit bit instead of __match_any_sync, whose cost grows with the
         // number of distinct values in the warp
@@ -177,19 +184,19 @@ sort_pass_kernel(const int32_t* __restrict__ keys_in, const int32_t* __restrict_
     __syncthreads();
     // ---- reorder the tile in shared memory (stable), then write out runs: consecutive threads -> consecutive addresses ----
 #pragma unroll
-    for (int j = 0; j < kSortItems; ++j) {
-        const int64_t i = base + (warp * kSortItems + j) * 32 + lane;
+    for (int j = 0; j < ITEMS; ++j) {
+        const int64_t i = base + (warp * ITEMS + j) * 32 + lane;
         if (i < M) {
             const int dg = digit_of<RB>(key[j], shift);
             const unsigned lp = lbase[dg] + cnt[warp * R + dg] + rank[j];
             skey[lp] = key[j];
-            spos[lp] = pos_in ? pos_in[i] : (int32_t)i;          // first pass: the caller's payload, or the element index
+            spos[lp] = pay[j];            // first pass: the caller's payload, or the element index
         }
     }
     __syncthreads();
-    const int nvalid = (int)min((int64_t)kSortTile, M - base);
+    const int nvalid = (int)min((int64_t)TILE, M - base);
 #pragma unroll
-    for (int j = 0; j < kSortItems; ++j) {
+    for (int j = 0; j < ITEMS; ++j) {
         const int t = j * kSortThreads + tid;
         if (t < nvalid) {
             const int32_t k = skey[t];
@@ -219,28 +226,39 @@ static int forced_bits() {
     return v;
 }
 static int radix_bits(int64_t X, int64_t M) {
-    if (forced_bits()) return forced_bits();
+    if (forced_bits() && (forced_bits() < 10 || M <= ((int64_t)1 << 18))) return forced_bits();
     const int bits = key_bits(X + 1);
-    return (M <= ((int64_t)1 << 18) && (bits + 9) / 10 < (bits + 7) / 8) ? 10 : 8;
+    if (M <= ((int64_t)1 << 18) && (bits + 9) / 10 < (bits + 7) / 8) return 10;
+    // long lists: 9-bit digits when they save a pass (25..27-bit row ids sort in 3 passes instead of 4: 1.00 -> 0.86 ms at
+    // 16.7 M keys, profiles/r02_sort_experiments.txt); 512 bins still fit the per-warp counters in shared memory
+    return (bits + 8) / 9 < (bits + 7) / 8 ? 9 : 8;
 }
 static int num_passes(int64_t X, int64_t M) {
     const int rb = radix_bits(X, M);
     return (key_bits(X + 1) + rb - 1) / rb;
 }
-template <int RB>
-static constexpr size_t pass_smem() { return ((size_t)(kSortThreads / 32 + 2) * (1 << RB) + 2 * kSortTile) * sizeof(unsigned); }
+template <int RB, int ITEMS>
+static constexpr size_t pass_smem() { return ((size_t)(kSortThreads / 32 + 2) * (1 << RB) + 2 * kSortThreads * ITEMS) * sizeof(unsigned); }
 
-template <int RB>
+// keys per CTA of the pass kernel: 4096 on long lists (fewer tiles: half the look-back and scan work per key), 2048 otherwise
+static int pass_items(int64_t M) {
+    static const int forced = [] { const char* e = getenv("DCTR_SORT_ITEMS"); const int v = e ? atoi(e) : 0; return (v == 8 || v == 16) ? v : 0; }();
+    if (forced) return forced;
+    return M > ((int64_t)1 << 20) ? 16 : 8;
+}
+
+template <int RB, int ITEMS>
 static int run_sort(const int32_t* ids, const int32_t* payload, int64_t M, int32_t X, int passes, int32_t* sorted_rows, int32_t* sorted_pos,
                     int32_t* alt_keys, int32_t* alt_pos, unsigned* ghist, unsigned* tickets, unsigned* status, cudaStream_t st) {
     constexpr int R = 1 << RB;
-    const int tiles = (int)((M + kSortTile - 1) / kSortTile);
+    const int htiles = (int)((M + kSortTile - 1) / kSortTile);
+    const int tiles = (int)((M + kSortThreads * ITEMS - 1) / (kSortThreads * ITEMS));
     static bool attr_set = false;
-    if (!attr_set) {       // 56 KB at RB = 10: above the 48 KB default
-        cudaFuncSetAttribute(sort_pass_kernel<RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pass_smem<RB>());
+    if (!attr_set) {       // above the 48 KB default for wide digits / large tiles
+        cudaFuncSetAttribute(sort_pass_kernel<RB, ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pass_smem<RB, ITEMS>());
         attr_set = true;
     }
-    launch_k(sort_hist_kernel<RB>, tiles, kSortThreads, (size_t)passes * R * sizeof(unsigned), st, ids, M, passes, ghist, X, id_status());
+    launch_k(sort_hist_kernel<RB>, htiles, kSortThreads, (size_t)passes * R * sizeof(unsigned), st, ids, M, passes, ghist, X, id_status());
     int rc = check_launch("sort_hist_kernel");
     if (rc) return rc;
     const int32_t* kin = ids;
@@ -249,7 +267,7 @@ static int run_sort(const int32_t* ids, const int32_t* payload, int64_t M, int32
         const bool to_out = ((passes - p) & 1) == 1;
         int32_t* kout = to_out ? sorted_rows : alt_keys;
         int32_t* pout = to_out ? sorted_pos : alt_pos;
-        launch_k(sort_pass_kernel<RB>, tiles, kSortThreads, pass_smem<RB>(), st, kin, pin, M, p * RB, ghist + p * R, tickets + p,
+        launch_k(sort_pass_kernel<RB, ITEMS>, tiles, kSortThreads, pass_smem<RB, ITEMS>(), st, kin, pin, M, p * RB, ghist + p * R, tickets + p,
                  status + (size_t)p * tiles * R, kout, pout, X, (int)(p == 0));
         if ((rc = check_launch("sort_pass_kernel"))) return rc;
         kin = kout;
@@ -264,17 +282,17 @@ using namespace dctr;
 
 // ghist [kMaxPasses][kMaxRadix] | tickets [16] | status [passes][tiles][R]: 4 passes x 256 bins, or (short lists only)
 // 3 passes x 1024 bins
-static size_t sort_header_words(int64_t tiles) {
-    const size_t per_tile = forced_bits() ? (size_t)kMaxPasses << forced_bits()
-                                          : (tiles <= 128 ? (size_t)3 * kMaxRadix : (size_t)kMaxPasses * 256);
-    return (size_t)kMaxPasses * kMaxRadix + 16 + per_tile * tiles;
+static int64_t pass_tiles(int64_t M) { const int64_t t = (int64_t)kSortThreads * pass_items(M); return (M + t - 1) / t; }
+static size_t sort_header_words(int64_t M) {
+    // look-back words per tile: up to 3 passes x 1024 bins on short lists, 4 passes x 512 bins otherwise
+    const size_t per_tile = M <= ((int64_t)1 << 18) ? (size_t)3 * kMaxRadix : (size_t)kMaxPasses * 512;
+    return (size_t)kMaxPasses * kMaxRadix + 16 + per_tile * (size_t)pass_tiles(M);
 }
 
 extern "C" size_t dctr_sort_rows_workspace(int64_t M) {
     if (M <= 0) return 16;
-    const int64_t tiles = (M + kSortTile - 1) / kSortTile;
     const int64_t m4 = (M + 3) / 4 * 4;
-    return (size_t)(2 * m4) * sizeof(int32_t) + sort_header_words(tiles) * sizeof(unsigned);
+    return (size_t)(2 * m4) * sizeof(int32_t) + sort_header_words(M) * sizeof(unsigned);
 }
 
 extern "C" int dctr_sort_rows(const int32_t* ids, int64_t M, int64_t X, int32_t* sorted_rows, int32_t* sorted_pos,
@@ -291,7 +309,7 @@ extern "C" int dctr_sort_pairs(const int32_t* ids, const int32_t* payload, int64
         set_error("sort_rows: workspace %zu < %zu bytes", workspace_bytes, dctr_sort_rows_workspace(M));
         return DCTR_EWORKSPACE;
     }
-    const int tiles = (int)((M + kSortTile - 1) / kSortTile);
+    const int64_t tiles = pass_tiles(M);
     const int64_t m4 = (M + 3) / 4 * 4;
     int32_t* alt_keys = static_cast<int32_t*>(workspace);
     int32_t* alt_pos = alt_keys + m4;
@@ -301,7 +319,10 @@ extern "C" int dctr_sort_pairs(const int32_t* ids, const int32_t* payload, int64
     cudaStream_t st = as_stream(stream);
     const int rb = radix_bits(X, M), passes = num_passes(X, M), R = 1 << rb;
     cudaMemsetAsync(ghist, 0, (size_t)(kMaxPasses * kMaxRadix + 16 + (size_t)passes * tiles * R) * sizeof(unsigned), st);
-    if (rb == 10) return run_sort<10>(ids, payload, M, (int32_t)X, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
-    if (rb == 9) return run_sort<9>(ids, payload, M, (int32_t)X, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
-    return run_sort<8>(ids, payload, M, (int32_t)X, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st);
+#define DCTR_RUN_SORT(RB_, IT_) run_sort<RB_, IT_>(ids, payload, M, (int32_t)X, passes, sorted_rows, sorted_pos, alt_keys, alt_pos, ghist, tickets, status, st)
+    const bool big = pass_items(M) == 16;
+    if (rb == 10) return DCTR_RUN_SORT(10, 8);
+    if (rb == 9) return big ? DCTR_RUN_SORT(9, 16) : DCTR_RUN_SORT(9, 8);
+    return big ? DCTR_RUN_SORT(8, 16) : DCTR_RUN_SORT(8, 8);
+#undef DCTR_RUN_SORT
 }

@@ -18,6 +18,9 @@ import os
 import torch
 
 from . import _lib as L
+from . import ops as _ops      # noqa: F401  (registers torch.ops.deepctr)
+
+O = torch.ops.deepctr
 
 
 def all_gather_cat(dist, t, group=None):
@@ -73,8 +76,7 @@ class DataParallelStep(object):
 
     def _sort_global(self, gids):
         e = self.e
-        L.call("dctr_sort_rows", gids.data_ptr(), self.GM, e.X, self.g_rows.data_ptr(), self.g_pos.data_ptr(),
-               self.sort_ws.data_ptr(), self.sort_ws.numel(), torch.cuda.current_stream(e.dev).cuda_stream)
+        O.sort_pairs(gids, None, self.GM, e.X, self.g_rows, self.g_pos, self.sort_ws)
 
     def _reduce_dense(self):
         """ONE all-reduce for the dense gradients and the loss (the loss rides in the tail of the gradient buffer)."""
@@ -95,25 +97,20 @@ class DataParallelStep(object):
             self._sort_global(gids)
         e.forward(True, gscale)
         dz = e.backward()
-        st = cur.cuda_stream
         N, F, d = e.N, e.F, e.d
-        ldd = dz.stride(0)
         if train_bias:
             col = 0 if e.bias_first else F * d + e.crossw
-            L.call("dctr_col_wsum", dz.data_ptr() + 4 * col, ldd, N, 1, None, L.ptr(e.bias(e.grads)), L.ptr(e.col_ws), e.col_ws.numel(), st)
+            O.col_wsum(dz[:, col:col + 1], 1, None, e.bias(e.grads), e.col_ws)
         if e.cross != "none":
             wts = None if e.wts_are_ones else e.wts
-            L.call("dctr_cross_bwd", L.ptr(e.ids), L.ptr(wts), L.ptr(e.table), e.X, e.ld, N, F, d, L.CROSS[e.cross],
-                   L.ptr(dz), ldd, L.ptr(e.ge), e.ldg, st)
-            gg = self._gather(self.gg, e.ge)
-            g, g_ld_n, g_ld_f, w = gg.data_ptr(), F * e.ldg, e.ldg, None
+            O.cross_bwd(e.ids.view(N, F), None if wts is None else wts.view(N, F), e.table, d, L.CROSS[e.cross], dz, e.ge)
+            g, g_ld_f, w = self._gather(self.gg, e.ge), e.ldg, None
         else:
-            gg = self._gather(self.gg, dz)
-            g, g_ld_n, g_ld_f, w = gg.data_ptr() + (4 if e.bias_first else 0), ldd, d, L.ptr(gwts)
+            g, g_ld_f, w = self._gather(self.gg, dz)[:, (1 if e.bias_first else 0):], d, gwts
         e.join_wgrad()
         self._reduce_dense()
         cur.wait_stream(e.side)
-        e.table_update(self.g_rows.data_ptr(), self.g_pos.data_ptr(), self.GM, F, g, g_ld_n, g_ld_f, w, lr, decay, self.scat_ws)
+        e.table_update(self.g_rows, self.g_pos, self.GM, F, g, g_ld_f, w, lr, decay, self.scat_ws)
         e.dense_update(lr, last_decay)
 
     def train_step_fm(self, lr, lam=0.0, gscale=1.0, dense_l2=True):
@@ -125,15 +122,13 @@ class DataParallelStep(object):
             gids = self._gather(self.gids, e.ids)
             gwts = None if e.wts_are_ones else self._gather(self.gwts, e.wts)
             self._sort_global(gids)
-        e.forward(True, gscale)
-        st = cur.cuda_stream
-        L.call("dctr_vec_sum", L.ptr(e.g), e.N, 1.0, L.ptr(e.grads), st)
+        e.forward(True, gscale, lam)
+        O.vec_sum(e.g, e.N, 1.0, e.grads)
         self._reduce_dense()
         e.bias_update(lr, lam)
         gg, gs = self._gather(self.gg, e.g), self._gather(self.gs, e.s)
         cur.wait_stream(e.side)
-        e.apply_update(self.g_rows.data_ptr(), self.g_pos.data_ptr(), self.GM, gg.data_ptr(), gs.data_ptr(), L.ptr(gwts), lr, lam, dense_l2,
-                       self.scat_ws)
+        e.apply_update(self.g_rows, self.g_pos, self.GM, gg, gs, gwts, lr, lam, dense_l2, self.scat_ws)
 
 
 # ======================================================================================================
@@ -197,8 +192,7 @@ class ShardedStep(object):
 
     def _stable_argsort(self, owner):
         e = self.e
-        L.call("dctr_sort_rows", L.ptr(owner.contiguous()), e.M, self.world, L.ptr(self.owner_sorted), L.ptr(self.perm),
-               L.ptr(self.plan_ws), self.plan_ws.numel(), self._st())
+        O.sort_pairs(owner.contiguous(), None, e.M, self.world, self.owner_sorted, self.perm, self.plan_ws)
         return self.perm
 
     def lookup(self):
@@ -210,7 +204,8 @@ class ShardedStep(object):
         recv_rows = all_to_all_rows(dist, send_rows.to(torch.int32), sc, rc, self.group)
         R = recv_rows.shape[0]
         rows = torch.empty(max(R, 1), e.ld, dtype=torch.float32, device=e.dev)
-        L.call("dctr_gather_rows", L.ptr(recv_rows), L.ptr(e.table), e.X, e.ld, R, L.ptr(rows), self._st())
+        if R:
+            O.gather_rows(recv_rows, e.table, rows)
         back = all_to_all_rows(dist, rows[:R], rc, sc, self.group)        # [M, ld], in perm order
         self.inv.view(-1)[perm.long()] = self.arange                      # slot -> its row in `back`
         self.last = (sc, rc, recv_rows, back)
@@ -227,33 +222,30 @@ class ShardedStep(object):
         self.forward(True, gscale)
         sc, rc, recv_rows, back = self.last
         dz = e.backward()
-        st = self._st()
         N, F, d = e.N, e.F, e.d
-        ldd = dz.stride(0)
         if train_bias:
-            L.call("dctr_col_wsum", dz.data_ptr() + 4 * (F * d + e.crossw), ldd, N, 1, None, L.ptr(e.bias(e.grads)),
-                   L.ptr(e.col_ws), e.col_ws.numel(), st)
+            col = F * d + e.crossw
+            O.col_wsum(dz[:, col:col + 1], 1, None, e.bias(e.grads), e.col_ws)
         e.join_wgrad()
         allreduce_dense(dist, e.grads, self.group)
         allreduce_dense(dist, e.loss, self.group)
         # per-slot embedding gradient (weights applied), against the exchanged pre-update rows
         wts = None if e.wts_are_ones else e.wts
-        L.call("dctr_cross_bwd", L.ptr(self.inv), L.ptr(wts), L.ptr(back), max(back.shape[0], 1), e.ld, N, F, d,
-               L.CROSS[e.cross], L.ptr(dz), ldd, L.ptr(self.ge), e.ldg, st)
+        O.cross_bwd(self.inv.view(N, F), None if wts is None else wts.view(N, F), back, d, L.CROSS[e.cross], dz, self.ge)
         send_g = torch.empty(e.M, e.ldg, dtype=torch.float32, device=e.dev)
-        L.call("dctr_gather_rows", L.ptr(self.perm), L.ptr(self.ge), e.M, e.ldg, e.M, L.ptr(send_g), st)
+        O.gather_rows(self.perm, self.ge.view(e.M, e.ldg), send_g)
         recv_g = all_to_all_rows(dist, send_g, sc, rc, self.group)       # aligned with recv_rows
         R = recv_rows.shape[0]
         if R == 0 and e.dense_optimizer:      # dense Adam / FTRL moves every local row even when no gradient arrived
-            e.table_update(None, None, 0, 1, L.ptr(recv_g), e.ldg, e.ldg, None, lr, decay, e.scat_ws)
+            e.table_update(None, None, 0, 1, recv_g, e.ldg, None, lr, decay, e.scat_ws)
         if R > 0:
             i32 = dict(dtype=torch.int32, device=e.dev)
             rows, pos = torch.empty(R, **i32), torch.empty(R, **i32)
             sws = torch.empty(L.lib().dctr_sort_rows_workspace(R), dtype=torch.uint8, device=e.dev)
             fws = torch.empty(L.lib().dctr_scatter_workspace(R, e.ld), dtype=torch.uint8, device=e.dev)
-            L.call("dctr_sort_rows", L.ptr(recv_rows), R, e.X, L.ptr(rows), L.ptr(pos), L.ptr(sws), sws.numel(), st)
+            O.sort_pairs(recv_rows, None, R, e.X, rows, pos, sws)
             # one "field" per received slot: position p indexes recv_g directly
-            e.table_update(L.ptr(rows), L.ptr(pos), R, 1, L.ptr(recv_g), e.ldg, e.ldg, None, lr, decay, fws)
+            e.table_update(rows, pos, R, 1, recv_g, e.ldg, None, lr, decay, fws)
             self._keep = (rows, pos, sws, fws, recv_g, send_g, recv_rows, back)
         e.dense_update(lr, last_decay)
 

@@ -13,6 +13,9 @@ import os
 import torch
 
 from . import _lib as L
+from . import ops as _ops          # registers torch.ops.deepctr.* (the C-ABI of libdctr.so as PyTorch custom ops)
+
+O = torch.ops.deepctr
 
 
 def _r4(n):
@@ -111,12 +114,13 @@ class StepEngine:
         self.overlap_sort = True
         self.wts_are_ones = True
         self.upd_rows = self.upd_pos = None     # use_update_list()
-        # Small two-hidden-layer nets at small batches: the whole MLP forward + backward as ONE kernel per 32-sample tile and
-        # the weight gradients (+ SGD) as one split-K kernel (csrc/mlp2.cu) instead of ~14 per-layer launches.
-        # DCTR_MLP2 = auto (batches <= 16384) | on | off
-        mode = os.environ.get("DCTR_MLP2", "auto")
+        # Small two-hidden-layer nets: the whole MLP forward + backward as ONE fp32 FFMA kernel per 32-sample tile and the weight
+        # gradients (+ SGD) as one cluster kernel (csrc/mlp2.cu) instead of ~14 per-layer launches.  Opt-in (DCTR_MLP2=on):
+        # measured at N = 4096, 177-300-100-1 it LOSES to the per-layer tcgen05 chain (0.264 vs 0.158 ms per step,
+        # profiles/r02_bench_fnn_ipinyou_mlp2_v3.json) -- fp32 SIMT cannot match the tensor cores even at these sizes.
+        mode = os.environ.get("DCTR_MLP2", "off")
         ok = self.nl == 3 and bool(L.lib().dctr_mlp2_supported(self.widths[0], self.widths[1], self.widths[2]))
-        self.fused_mlp2 = ok and (mode == "on" or (mode == "auto" and self.N <= 16384))
+        self.fused_mlp2 = ok and mode == "on"
         self._mlp2_sgd = False                  # this step's fused kernels apply plain SGD to the MLP themselves
         self._mlp2_cfg = None                   # (lr, decay_hidden, decay_out, train_bias) when they do
         self._mlp2_tr_event = None
@@ -135,11 +139,9 @@ class StepEngine:
     def _bias_len(self):
         return 4                                          # w_0 / fm b: one float, padded
 
-    def _embed_forward(self, ids, wts, table, X, st):
-        p = L.ptr
-        L.call("dctr_gather_concat_fwd", p(ids), p(wts), p(table), X, self.ld, self.N, self.F, self.d,
-               L.CROSS[self.cross], int(self.bias_first), p(self.bias()), L.ACT[self.act0],
-               p(self.ins[0]), self.ldi[0], st)
+    def _embed_forward(self, ids, wts, table, X):
+        O.gather_concat_fwd(ids.view(self.N, self.F), None if wts is None else wts.view(self.N, self.F), table[:X], self.d,
+                            L.CROSS[self.cross], self.bias_first, self.bias(), L.ACT[self.act0], self.ins[0])
 
     # ---- parameter views -------------------------------------------------------------------------
     def W(self, l, buf=None):
@@ -198,55 +200,41 @@ class StepEngine:
     def _st(self):
         return torch.cuda.current_stream(self.dev).cuda_stream
 
-    def _mask(self, l):
-        m = self.masks[l]
-        if m is None:
-            return None, 0
-        return m.data_ptr(), (0 if m.shape[0] == 1 else m.stride(0))
+    def _gemm(self, *a):
+        (O.gemm_tc if self.gemm_fn == "dctr_gemm_tc" else O.gemm)(*a)
 
     def forward(self, with_loss, gscale=1.0, lookup=None):
         """lookup = (ids, rows, n_rows): gather from an already exchanged row buffer instead of the local table
         (row-sharded mode, dist.ShardedStep)."""
-        st = self._st()
-        N, F, d, p = self.N, self.F, self.d, L.ptr
+        N = self.N
         wts = None if self.wts_are_ones else self.wts
         ids, table, X = (self.ids, self.table, self.X) if lookup is None else lookup
-        self._embed_forward(ids, wts, table, X, st)
+        self._embed_forward(ids, wts, table, X)
         if with_loss and self.fused_mlp2:
             self._mlp2_forward_backward(gscale)
             return
         if self.masks[0] is not None:
             self.ins[0].mul_(self.masks[0])     # input dropout (tf.nn.dropout on act(z1), FNN.py:87): torch elementwise
         for l in range(self.nl - 1):
-            mp, mld = self._mask(l + 1)
-            L.call(self.gemm_fn, L.GEMM_NN, N, self.widths[l + 1], self.widths[l], p(self.ins[l]), self.ldi[l],
-                   p(self.W(l)), self.ldw[l], p(self.ins[l + 1]), self.ldi[l + 1], L.EPI_FWD, L.ACT[self.act_of(l + 1)],
-                   p(self.b(l)), None, 0, mp, mld, 1, st)
+            self._gemm(L.GEMM_NN, N, self.widths[l + 1], self.widths[l], self.ins[l], self.W(l), self.ins[l + 1], L.EPI_FWD,
+                       L.ACT[self.act_of(l + 1)], self.b(l), None, self.masks[l + 1], 1)
         last = self.nl - 1
         self._out_unit_done = False
         if with_loss and self.widths[last] <= 1024 and self.fuse_out_unit:
             # train step: the output unit forward AND backward in one pass over the last activation
-            mp, mld = self._mask(last)
-            L.call("dctr_out_unit_train", p(self.ins[last]), self.ldi[last], N, self.widths[last], p(self.W(last)),
-                   p(self.b(last)), p(self.y), float(gscale), L.ACT[self.act_of(last)], mp, mld, p(self.logit), p(self.pred),
-                   p(self.loss_n), p(self.dlogit), float(gscale), p(self.loss), p(self.dbuf[0]), self.dbuf[0].stride(0),
-                   p(self.W(last, self.grads)), p(self.b(last, self.grads)), p(self.col_ws), self.col_ws.numel(), st)
+            O.out_unit_train(self.ins[last], self.widths[last], self.W(last), self.b(last), self.y, float(gscale),
+                             L.ACT[self.act_of(last)], self.masks[last], self.logit, self.pred, self.loss_n, self.dlogit,
+                             float(gscale), self.loss, self.dbuf[0], self.W(last, self.grads), self.b(last, self.grads), self.col_ws)
             self._out_unit_done = True
             return
         # logit / pred / per-sample loss / dlogit and the reduced loss in one launch
-        L.call("dctr_out_xent_fwd", p(self.ins[last]), self.ldi[last], N, self.widths[last], p(self.W(last)),
-               p(self.b(last)), p(self.y) if with_loss else None, float(gscale), p(self.logit), p(self.pred),
-               p(self.loss_n), p(self.dlogit), float(gscale), p(self.loss) if with_loss else None,
-               p(self.col_ws), self.col_ws.numel(), st)
+        O.out_xent_fwd(self.ins[last], self.widths[last], self.W(last), self.b(last), self.y if with_loss else None, float(gscale),
+                       self.logit, self.pred, self.loss_n, self.dlogit, float(gscale), self.loss if with_loss else None, self.col_ws)
 
     def _mlp2_forward_backward(self, gscale):
         """csrc/mlp2.cu, kernel 1: x -> a1 -> a2 -> output unit -> dz2 -> dz1 -> dz0 for every 32-sample tile; with plain SGD
         the kernel's last CTA also updates the output unit."""
-        p = L.ptr
         D0, H1, H2 = self.widths
-        m0, ldm0 = self._mask(0)
-        m1, ldm1 = self._mask(1)
-        m2, ldm2 = self._mask(2)
         sgd = self._mlp2_cfg is not None
         lr, _, dout = self._mlp2_cfg[:3] if sgd else (0.0, 1.0, 1.0)
         self._mlp2_sgd = sgd
@@ -256,25 +244,19 @@ class StepEngine:
             self._mlp2_tr_event = None
         else:
             self._mlp2_transpose()
-        L.call("dctr_mlp2_train", self.N, D0, H1, H2, p(self.ins[0]), self.ldi[0], m0, ldm0, L.ACT[self.act_of(0)],
-               p(self.W(0)), self.ldw[0], p(self.b(0)), L.ACT[self.act_of(1)], m1, ldm1,
-               p(self.W(1)), self.ldw[1], p(self.b(1)), L.ACT[self.act_of(2)], m2, ldm2,
-               p(self.W1t), p(self.W2t), p(self.W(2)), p(self.b(2)), p(self.y), float(gscale), float(gscale),
-               p(self.ins[1]), self.ldi[1], p(self.dbuf[0]), p(self.dbuf[1]), self.dbuf[0].stride(0), p(self.dz0),
-               p(self.logit), p(self.pred), p(self.loss_n), p(self.dlogit), p(self.loss),
-               p(self.W(2, self.grads)), p(self.b(2, self.grads)), int(sgd), float(lr), float(dout),
-               p(self.mlp2_ws), self.mlp2_ws.numel(), self._st())
+        O.mlp2_train(D0, H1, H2, self.ins[0], self.masks[0], L.ACT[self.act_of(0)], self.W(0), self.b(0), L.ACT[self.act_of(1)],
+                     self.masks[1], self.W(1), self.b(1), L.ACT[self.act_of(2)], self.masks[2], self.W1t, self.W2t, self.W(2).view(-1),
+                     self.b(2), self.y, float(gscale), float(gscale), self.ins[1], self.dbuf[0], self.dbuf[1], self.dz0, self.logit,
+                     self.pred, self.loss_n, self.dlogit, self.loss, self.W(2, self.grads).view(-1), self.b(2, self.grads), sgd,
+                     float(lr), float(dout), self.mlp2_ws)
 
     def _mlp2_transpose(self):
-        p = L.ptr
         D0, H1, H2 = self.widths
-        L.call("dctr_mlp2_transpose", D0, H1, H2, p(self.W(0)), self.ldw[0], p(self.W(1)), self.ldw[1], p(self.W1t), self.ldi[0],
-               p(self.W2t), self.ldi[1], self._st())
+        O.mlp2_transpose(D0, H1, H2, self.W(0), self.W(1), self.W1t, self.W2t)
 
     def _mlp2_wgrad(self):
-        """kernel 2: both weight gradients and bias gradients as one split-K launch (gradients into self.grads, or SGD in
-        place); runs on the second stream next to the sparse update, which only needs dz0."""
-        p = L.ptr
+        """kernel 2: both weight gradients and bias gradients as one launch of 8-CTA clusters (gradients into self.grads, or
+        SGD in place); runs on the second stream next to the sparse update, which only needs dz0."""
         D0, H1, H2 = self.widths
         sgd = self._mlp2_sgd
         lr, dhid, _ = self._mlp2_cfg[:3] if sgd else (0.0, 1.0, 1.0)
@@ -283,11 +265,9 @@ class StepEngine:
         if ov:
             self.side2.wait_stream(main)
         with torch.cuda.stream(self.side2 if ov else main):
-            L.call("dctr_mlp2_wgrad", self.N, D0, H1, H2, p(self.ins[0]), self.ldi[0], p(self.ins[1]), self.ldi[1],
-                   p(self.dbuf[0]), p(self.dbuf[1]), self.dbuf[0].stride(0), p(self.W(0)), self.ldw[0], p(self.b(0)),
-                   p(self.W(1)), self.ldw[1], p(self.b(1)), p(self.W(0, self.grads)), p(self.b(0, self.grads)),
-                   p(self.W(1, self.grads)), p(self.b(1, self.grads)), int(sgd), float(lr), float(dhid),
-                   p(self.mlp2_ws), self.mlp2_ws.numel(), self._st())
+            O.mlp2_wgrad(D0, H1, H2, self.ins[0], self.ins[1], self.dbuf[0], self.dbuf[1], self.W(0), self.b(0), self.W(1), self.b(1),
+                         self.W(0, self.grads), self.b(0, self.grads), self.W(1, self.grads), self.b(1, self.grads), sgd, float(lr),
+                         float(dhid), self.mlp2_ws)
         if ov:
             self._wgrad_pending = True
 
@@ -296,19 +276,14 @@ class StepEngine:
         if self.fused_mlp2:
             self._mlp2_wgrad()
             return self.dz0
-        st = self._st()
-        N, p = self.N, L.ptr
+        N = self.N
         last = self.nl - 1
         H = self.widths[last]
-        cw, cwb = p(self.col_ws), self.col_ws.numel()
         cur = 0
-        mp, mld = self._mask(last)
-        ldd = self.dbuf[0].stride(0)
         # d(last hidden), d w_out and d b_out in one launch (unless the forward already produced them)
         if not self._out_unit_done:
-            L.call("dctr_out_bwd_fused", p(self.dlogit), p(self.W(last)), p(self.ins[last]), self.ldi[last], N, H,
-                   L.ACT[self.act_of(last)], mp, mld, p(self.dbuf[cur]), ldd, p(self.W(last, self.grads)), p(self.b(last, self.grads)),
-                   cw, cwb, st)
+            O.out_bwd_fused(self.dlogit, self.W(last), self.ins[last], H, L.ACT[self.act_of(last)], self.masks[last], self.dbuf[cur],
+                            self.W(last, self.grads), self.b(last, self.grads), self.col_ws)
         self._out_unit_done = False
         # Per layer, the weight/bias gradients (TN GEMM [+ split-K fold], column sum) only need dz_l, as does the data
         # gradient that continues the chain: they run on a second stream next to it (three rotating dz buffers, so the
@@ -324,27 +299,23 @@ class StepEngine:
             if ov:
                 self.side2.wait_stream(main)
             with torch.cuda.stream(self.side2 if ov else main):
-                st2 = self._st()
-                cw2, cwb2 = (p(self.col_ws2), self.col_ws2.numel()) if ov else (cw, cwb)
+                cws = self.col_ws2 if ov else self.col_ws
                 if s > 1:
-                    L.call(self.gemm_fn, L.GEMM_TN, K, Hl, N, p(self.ins[l]), self.ldi[l], p(dpre), ldd, p(self.splitk_ws),
-                           self.ldw[l], L.EPI_NONE, 0, None, None, 0, None, 0, s, st2)
-                    L.call("dctr_splitk_reduce", p(self.splitk_ws), s, K, Hl, self.ldw[l], p(gW), self.ldw[l], st2)
+                    slabs = self.splitk_ws[:s * K * self.ldw[l]].view(s, K, self.ldw[l])
+                    self._gemm(L.GEMM_TN, K, Hl, N, self.ins[l], dpre, slabs, L.EPI_NONE, 0, None, None, None, s)
+                    O.splitk_reduce(slabs, s, K, Hl, self.ldw[l], gW)
                 else:
-                    L.call(self.gemm_fn, L.GEMM_TN, K, Hl, N, p(self.ins[l]), self.ldi[l], p(dpre), ldd, p(gW),
-                           self.ldw[l], L.EPI_NONE, 0, None, None, 0, None, 0, 1, st2)
-                L.call("dctr_col_wsum", p(dpre), ldd, N, Hl, None, p(self.b(l, self.grads)), cw2, cwb2, st2)
+                    self._gemm(L.GEMM_TN, K, Hl, N, self.ins[l], dpre, gW, L.EPI_NONE, 0, None, None, None, 1)
+                O.col_wsum(dpre, Hl, None, self.b(l, self.grads), cws)
                 if ov:
                     readers[cur] = self.side2.record_event()
                     self._wgrad_pending = True
-            mp, mld = self._mask(l)
-            act = self.act_of(l)
             nxt = (cur + 1) % 3
             if readers[nxt] is not None:
                 main.wait_event(readers[nxt])
-            dout, ldo = (self.dbuf[nxt], ldd) if l > 0 else (self.dz0, self.dz0.stride(0))
-            L.call(self.gemm_fn, L.GEMM_NT, N, K, Hl, p(dpre), ldd, p(self.W(l)), self.ldw[l], p(dout), ldo,
-                   L.EPI_DGRAD, L.ACT[act], None, p(self.ins[l]), self.ldi[l], mp, mld, 1, st)
+            dout = self.dbuf[nxt] if l > 0 else self.dz0
+            self._gemm(L.GEMM_NT, N, K, Hl, dpre, self.W(l), dout, L.EPI_DGRAD, L.ACT[self.act_of(l)], None, self.ins[l],
+                       self.masks[l], 1)
             cur = nxt
         if last > 0:
             return self.dz0
@@ -355,53 +326,45 @@ class StepEngine:
         if ids is None:
             ids, payload = (self.ids, None) if self.upd_rows is None else (self.upd_rows, self.upd_pos)
         M = self.M if M is None else M
-        ws = self.sort_ws if ws is None else ws
-        L.call("dctr_sort_pairs", L.ptr(ids), L.ptr(payload), M, self.X, L.ptr(self.sorted_rows if rows is None else rows),
-               L.ptr(self.sorted_pos if pos is None else pos), L.ptr(ws), ws.numel(), self._st())
+        O.sort_pairs(ids, payload, M, self.X, self.sorted_rows if rows is None else rows, self.sorted_pos if pos is None else pos,
+                     self.sort_ws if ws is None else ws)
 
     def embedding_update(self, dz, lr, decay=1.0, train_bias=True):
         """dz: [N, ldd] gradient w.r.t. z.  Requires sort_ids() to have run on this stream (or joined)."""
-        st = self._st()
-        N, F, d, p = self.N, self.F, self.d, L.ptr
-        ldd = dz.stride(0)
+        F, d = self.F, self.d
         wts = None if self.wts_are_ones else self.wts
         if train_bias:
             col = 0 if self.bias_first else F * d + self.crossw
-            L.call("dctr_col_wsum", dz.data_ptr() + 4 * col, ldd, N, 1, None, p(self.bias(self.grads)),
-                   p(self.col_ws), self.col_ws.numel(), st)
+            O.col_wsum(dz[:, col:col + 1], 1, None, self.bias(self.grads), self.col_ws)
         if self.cross != "none":
-            L.call("dctr_cross_bwd", p(self.ids), p(wts), p(self.table), self.X, self.ld, N, F, d, L.CROSS[self.cross],
-                   p(dz), ldd, p(self.ge), self.ldg, st)
-            g, g_ld_n, g_ld_f, w = self.ge.data_ptr(), F * self.ldg, self.ldg, None
+            O.cross_bwd(self.ids.view(self.N, F), None if wts is None else wts.view(self.N, F), self.table, d, L.CROSS[self.cross], dz, self.ge)
+            g, g_ld_f, w = self.ge, self.ldg, None
         else:
-            g, g_ld_n, g_ld_f, w = dz.data_ptr() + (4 if self.bias_first else 0), ldd, d, p(wts)
-        self.table_update(p(self.sorted_rows), p(self.sorted_pos), self.M, F, g, g_ld_n, g_ld_f, w, lr, decay, self.scat_ws)
+            g, g_ld_f, w = dz[:, (1 if self.bias_first else 0):], d, wts
+        self.table_update(self.sorted_rows, self.sorted_pos, self.M, F, g, g_ld_f, w, lr, decay, self.scat_ws)
 
-    def table_update(self, rows, pos, M, F, g, g_ld_n, g_ld_f, w, lr, decay, ws):
-        """Fold the sorted (row, position) list into the table: SGD in place, or -- Adam -- into the dense gradient buffer
-        followed by the dense sweep.  Also the entry point of the multi-GPU steps (global / received lists)."""
-        st, p = self._st(), L.ptr
-        if self.adam is not None:
-            b1, b2, eps = self.adam
-            L.call("dctr_adam_tick", p(self.adam_state), float(lr), b1, b2, st)
-            L.call("dctr_scatter_sgd", self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_n, g_ld_f, w, -1.0, 1.0,
-                   p(self.table_g), self.X, self.ld, p(ws), ws.numel(), st)
-            L.call("dctr_dense_adam", p(self.table), p(self.table_g), p(self.table_m), p(self.table_v), self.X * self.ld,
-                   p(self.adam_state), b1, b2, eps, 0.0, 1, st)
-            return
-        if self.ftrl is not None:
-            lr_power, l1, l2 = self.ftrl
-            L.call("dctr_scatter_sgd", self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_n, g_ld_f, w, -1.0, 1.0,
-                   p(self.table_g), self.X, self.ld, p(ws), ws.numel(), st)
-            L.call("dctr_dense_ftrl", p(self.table), p(self.table_g), p(self.table_n), p(self.table_z), self.X * self.ld,
-                   float(lr), lr_power, l1, l2, 0.0, 1, st)
+    def table_update(self, rows, pos, M, F, g, g_ld_f, w, lr, decay, ws):
+        """Fold the sorted (row, position) list into the table: SGD in place, or -- Adam / FTRL -- into the dense gradient
+        buffer followed by the dense sweep.  g: [N, >= F * g_ld_f] gradient rows (field f at column f * g_ld_f) or a per-slot
+        buffer [N, F, ldg].  Also the entry point of the multi-GPU steps (global / received lists)."""
+        if M == 0:
+            rows = pos = self.sorted_rows            # never read
+        if self.dense_optimizer:
+            if self.adam is not None:
+                O.adam_tick(self.adam_state, float(lr), self.adam[0], self.adam[1])
+            O.scatter_sgd(self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_f, w, -1, -1.0, 1.0, self.table_g, ws)
+            if self.adam is not None:
+                b1, b2, eps = self.adam
+                O.dense_adam(self.table, self.table_g, self.table_m, self.table_v, self.X * self.ld, self.adam_state, b1, b2, eps, 0.0, True)
+            else:
+                lr_power, l1, l2 = self.ftrl
+                O.dense_ftrl(self.table, self.table_g, self.table_n, self.table_z, self.X * self.ld, float(lr), lr_power, l1, l2, 0.0, True)
             return
         if self.skip_row is not None:
-            L.call("dctr_scatter_sgd_masked", self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_n, g_ld_f, int(self.skip_row),
-                   float(lr), float(decay), p(self.table), self.X, self.ld, p(ws), ws.numel(), st)
+            O.scatter_sgd(self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_f, None, int(self.skip_row), float(lr), float(decay),
+                          self.table, ws)
             return
-        L.call("dctr_scatter_sgd", self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_n, g_ld_f, w, float(lr), float(decay),
-               p(self.table), self.X, self.ld, p(ws), ws.numel(), st)
+        O.scatter_sgd(self.scatter_mode, rows, pos, M, F, self.d, g, g_ld_f, w, -1, float(lr), float(decay), self.table, ws)
 
     def enable_adam(self, eps=1e-8, beta1=0.9, beta2=0.999):
         """Switch the step to TensorFlow's Adam over the table AND the MLP (tf_util.py:18-21).  TF densifies the table gradient
@@ -440,38 +403,33 @@ class StepEngine:
         """last_decay: L2 on the output unit only (FNN_wnzh.py:173); mlp_decay: L2 on every MLP weight and bias but not on the
         embedding-side bias (SNN_DAE.py:151-153)."""
         self.join_wgrad()
-        st = self._st()
+        P, G, n = self.params, self.grads, self.n_params
+
+        def sgd(lo, hi, decay):
+            O.dense_sgd(P[lo:hi], G[lo:hi], hi - lo, float(lr), float(decay))
         if self._mlp2_sgd:                 # the fused kernels updated the MLP; what is left is the embedding-side bias
             self._mlp2_sgd = False
             if self._mlp2_cfg[3]:
-                hi = self.bias_off
-                L.call("dctr_dense_sgd", self.params.data_ptr() + 4 * hi, self.grads.data_ptr() + 4 * hi, self.n_params - hi,
-                       float(lr), 1.0, st)
+                sgd(self.bias_off, n, 1.0)
             return
         if self.adam is not None:          # same step counter as the table (embedding_update ticked it)
             b1, b2, eps = self.adam
-            L.call("dctr_dense_adam", L.ptr(self.params), L.ptr(self.grads), L.ptr(self.params_m), L.ptr(self.params_v),
-                   self.n_params, L.ptr(self.adam_state), b1, b2, eps, 0.0, 0, st)
+            O.dense_adam(P, G, self.params_m, self.params_v, n, self.adam_state, b1, b2, eps, 0.0, False)
             return
         if self.ftrl is not None:
             lr_power, l1, l2 = self.ftrl
-            L.call("dctr_dense_ftrl", L.ptr(self.params), L.ptr(self.grads), L.ptr(self.params_n), L.ptr(self.params_z),
-                   self.n_params, float(lr), lr_power, l1, l2, 0.0, 0, st)
+            O.dense_ftrl(P, G, self.params_n, self.params_z, n, float(lr), lr_power, l1, l2, 0.0, False)
             return
         if mlp_decay != 1.0:
-            hi = self.bias_off
-            pp, gg = self.params.data_ptr(), self.grads.data_ptr()
-            L.call("dctr_dense_sgd", pp, gg, hi, float(lr), float(mlp_decay), st)
-            L.call("dctr_dense_sgd", pp + 4 * hi, gg + 4 * hi, self.n_params - hi, float(lr), 1.0, st)
+            sgd(0, self.bias_off, mlp_decay)
+            sgd(self.bias_off, n, 1.0)
         elif last_decay == 1.0:
-            L.call("dctr_dense_sgd", L.ptr(self.params), L.ptr(self.grads), self.n_params, float(lr), 1.0, st)
+            sgd(0, n, 1.0)
         else:   # Theano: cost += lambda1*(|w3|^2 + b3^2) touches the output unit only (FNN_wnzh.py:173)
-            lo = self.w_off[self.nl - 1]
-            hi = self.bias_off
-            pp, gg = self.params.data_ptr(), self.grads.data_ptr()
-            L.call("dctr_dense_sgd", pp, gg, lo, float(lr), 1.0, st)
-            L.call("dctr_dense_sgd", pp + 4 * lo, gg + 4 * lo, hi - lo, float(lr), float(last_decay), st)
-            L.call("dctr_dense_sgd", pp + 4 * hi, gg + 4 * hi, self.n_params - hi, float(lr), 1.0, st)
+            lo, hi = self.w_off[self.nl - 1], self.bias_off
+            sgd(0, lo, 1.0)
+            sgd(lo, hi, last_decay)
+            sgd(hi, n, 1.0)
 
     def train_step(self, lr, decay=1.0, gscale=1.0, train_bias=True, last_decay=1.0, mlp_decay=1.0):
         """One full step on device buffers ids/wts/y (+ masks).  The row sort only depends on the ids, so it
@@ -522,18 +480,15 @@ class BagEngine(StepEngine):
         buf = self.params if buf is None else buf
         return buf[self.bias_off:self.bias_off + self.d]
 
-    def _embed_forward(self, ids, wts, table, X, st):
-        p = L.ptr
-        L.call("dctr_bag_fwd", p(ids), p(wts), p(table), X, self.ld, self.N, self.F, self.d, p(self.bias()),
-               L.ACT[self.act0], p(self.ins[0]), self.ldi[0], st)
+    def _embed_forward(self, ids, wts, table, X):
+        O.bag_fwd(ids.view(self.N, self.F), None if wts is None else wts.view(self.N, self.F), table[:X], self.d, self.bias(),
+                  L.ACT[self.act0], self.ins[0])
 
     def embedding_update(self, dz, lr, decay=1.0, train_bias=True):
-        st, p = self._st(), L.ptr
-        ldd = dz.stride(0)
         if train_bias:          # bb0 -= lr * sum_t gx_t x_t (1 - x_t)   (SNN_DAE.py:284)
-            L.call("dctr_col_wsum", p(dz), ldd, self.N, self.d, None, p(self.bias(self.grads)), p(self.col_ws), self.col_ws.numel(), st)
+            O.col_wsum(dz, self.d, None, self.bias(self.grads), self.col_ws)
         wts = None if self.wts_are_ones else self.wts
-        self.table_update(p(self.sorted_rows), p(self.sorted_pos), self.M, self.F, p(dz), ldd, 0, p(wts), lr, decay, self.scat_ws)
+        self.table_update(self.sorted_rows, self.sorted_pos, self.M, self.F, dz, 0, wts, lr, decay, self.scat_ws)
 
 
 class FMEngine:
@@ -589,16 +544,13 @@ class FMEngine:
         return torch.cuda.current_stream(self.dev).cuda_stream
 
     def forward(self, with_loss, gscale=1.0, lam=0.0):
-        p = L.ptr
-        wts = None if self.wts_are_ones else self.wts
-        L.call("dctr_fm_fwd", p(self.ids), p(wts), p(self.table), self.X, self.ld, self.N, self.F, self.d,
-               p(self.bias()), p(self.y) if with_loss else None, float(gscale), p(self.logit), p(self.pred),
-               p(self.loss_n), p(self.g), p(self.s) if with_loss else None, self.lds, self._st())
+        wts = None if self.wts_are_ones else self.wts.view(self.N, self.F)
+        O.fm_fwd(self.ids.view(self.N, self.F), wts, self.table, self.d, self.bias(), self.y if with_loss else None, float(gscale),
+                 self.logit, self.pred, self.loss_n, self.g, self.s if with_loss else None)
         if with_loss:
-            L.call("dctr_vec_sum", p(self.loss_n), self.N, float(gscale), p(self.loss), self._st())
+            O.vec_sum(self.loss_n, self.N, float(gscale), self.loss)
             if lam != 0.0:      # the loss the reference fetches carries lam * (l2_loss(W) + l2_loss(V) + l2_loss(b)) (FM.py:39, LR.py:37)
-                L.call("dctr_l2_loss_add", p(self.table), self.X * self.ld, p(self.bias()), 1, float(lam), p(self.loss),
-                       p(self.l2_ws), self.l2_ws.numel(), self._st())
+                O.l2_loss_add(self.table.view(-1), self.bias(), float(lam), self.loss, self.l2_ws)
 
     def enable_adam(self, eps=1e-8, beta1=0.9, beta2=0.999):
         f32 = dict(dtype=torch.float32, device=self.dev)
@@ -618,8 +570,7 @@ class FMEngine:
         return self.adam is not None or self.ftrl is not None
 
     def sort_ids(self):
-        L.call("dctr_sort_rows", L.ptr(self.ids), self.M, self.X, L.ptr(self.sorted_rows), L.ptr(self.sorted_pos),
-               L.ptr(self.sort_ws), self.sort_ws.numel(), self._st())
+        O.sort_pairs(self.ids, None, self.M, self.X, self.sorted_rows, self.sorted_pos, self.sort_ws)
 
     def train_step(self, lr, lam=0.0, gscale=1.0, dense_l2=True):
         L.call("dctr_set_launch_mode", self.launch_mode)
@@ -631,52 +582,42 @@ class FMEngine:
         else:                                    # per-kernel timing (bench.py): everything on one stream
             self.sort_ids()
         self.forward(True, gscale, lam)
-        st = self._st()
-        p = L.ptr
-        L.call("dctr_vec_sum", p(self.g), self.N, 1.0, p(self.grads), st)           # d loss / d b = sum_n g_n
+        O.vec_sum(self.g, self.N, 1.0, self.grads)           # d loss / d b = sum_n g_n
         self.bias_update(lr, lam)          # before the join: the one-float update runs while the sort is still going
         if self.overlap_sort:
             cur.wait_stream(self.side)
         wts = None if self.wts_are_ones else self.wts
-        self.apply_update(p(self.sorted_rows), p(self.sorted_pos), self.M, p(self.g), p(self.s), p(wts), lr, lam, dense_l2, self.scat_ws)
+        self.apply_update(self.sorted_rows, self.sorted_pos, self.M, self.g, self.s, wts, lr, lam, dense_l2, self.scat_ws)
 
     def bias_update(self, lr, lam):
         """b from grads[0] = sum_n g_n (already all-reduced in the data-parallel step); ticks Adam's step counter."""
-        st, p = self._st(), L.ptr
+        P, G = self.params[:4], self.grads[:4]
         if self.adam is not None:
             b1, b2, eps = self.adam
-            L.call("dctr_adam_tick", p(self.adam_state), float(lr), b1, b2, st)
-            L.call("dctr_dense_adam", p(self.params), p(self.grads), p(self.params_m), p(self.params_v), 4,
-                   p(self.adam_state), b1, b2, eps, float(lam), 0, st)
+            O.adam_tick(self.adam_state, float(lr), b1, b2)
+            O.dense_adam(P, G, self.params_m[:4], self.params_v[:4], 4, self.adam_state, b1, b2, eps, float(lam), False)
         elif self.ftrl is not None:
             lr_power, l1, l2 = self.ftrl
-            L.call("dctr_dense_ftrl", p(self.params), p(self.grads), p(self.params_n), p(self.params_z), 4,
-                   float(lr), lr_power, l1, l2, float(lam), 0, st)
+            O.dense_ftrl(P, G, self.params_n[:4], self.params_z[:4], 4, float(lr), lr_power, l1, l2, float(lam), False)
         else:
-            L.call("dctr_dense_sgd", p(self.params), p(self.grads), 1, float(lr), float(1.0 - lr * lam), st)
+            O.dense_sgd(P, G, 1, float(lr), float(1.0 - lr * lam))
 
     def apply_update(self, rows, pos, M, g, s, wts, lr, lam, dense_l2, ws):
         """Table update from a sorted (row, position) list: this rank's own, or the global one of the data-parallel step
-        (bias_update must have run first: it advances Adam's step)."""
-        st, p = self._st(), L.ptr
+        (bias_update must have run first: it advances Adam's step).  rows / pos / g / s / wts / ws are device tensors."""
         decay = 1.0 - lr * lam
-        if self.adam is not None:
-            # TF Adam is dense (tf_util.py:18-21): per-row gradients into G, then one sweep over table | G | m | v with the L2
-            # term's gradient lam * theta folded in (FM.py:39, LR.py:37); the bias the same way
-            b1, b2, eps = self.adam
-            L.call("dctr_scatter_grad_fm", rows, pos, M, self.F, self.d, g, s, self.lds, wts, p(self.table), self.X, self.ld,
-                   p(self.table_g), p(ws), ws.numel(), st)
-            L.call("dctr_dense_adam", p(self.table), p(self.table_g), p(self.table_m), p(self.table_v), self.X * self.ld,
-                   p(self.adam_state), b1, b2, eps, float(lam), 1, st)
+        F, d, n = self.F, self.d, self.X * self.ld
+        if self.dense_optimizer:
+            # TF Adam / FTRL are dense (tf_util.py:18-24): per-row gradients into G, then one sweep over table | G | slots with the
+            # L2 term's gradient lam * theta folded in (FM.py:39, LR.py:37); the bias the same way
+            O.scatter_grad_fm(rows, pos, M, F, d, g, s, wts, self.table, self.table_g, ws)
+            if self.adam is not None:
+                b1, b2, eps = self.adam
+                O.dense_adam(self.table, self.table_g, self.table_m, self.table_v, n, self.adam_state, b1, b2, eps, float(lam), True)
+            else:
+                lr_power, l1, l2 = self.ftrl
+                O.dense_ftrl(self.table, self.table_g, self.table_n, self.table_z, n, float(lr), lr_power, l1, l2, float(lam), True)
             return
-        if self.ftrl is not None:
-            lr_power, l1, l2 = self.ftrl
-            L.call("dctr_scatter_grad_fm", rows, pos, M, self.F, self.d, g, s, self.lds, wts, p(self.table), self.X, self.ld,
-                   p(self.table_g), p(ws), ws.numel(), st)
-            L.call("dctr_dense_ftrl", p(self.table), p(self.table_g), p(self.table_n), p(self.table_z), self.X * self.ld,
-                   float(lr), lr_power, l1, l2, float(lam), 1, st)
-            return
-        L.call("dctr_scatter_sgd_fm", rows, pos, M, self.F, self.d, g, s, self.lds, wts, float(lr), float(decay),
-               p(self.table), self.X, self.ld, p(ws), ws.numel(), st)
+        O.scatter_sgd_fm(rows, pos, M, F, d, g, s, wts, float(lr), float(decay), self.table, ws)
         if lam != 0.0 and dense_l2:   # FM.py:39: the L2 term reaches every row, touched or not
-            L.call("dctr_decay_sweep", p(self.table), self.X, self.ld, float(decay), rows, M, st)
+            O.decay_sweep(self.table, float(decay), rows, M)

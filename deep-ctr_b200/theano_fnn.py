@@ -147,9 +147,8 @@ class FNN_wnzh(_Base):
 
     def _arrange_on_device(self):
         e = self.engine
-        L.call("dctr_arrange_update_list", L.ptr(self.feats), L.ptr(self.feat_field_dev), self.N, self.J, self.F, self.pad_row,
-               self.pad_row, L.ptr(e.ids), L.ptr(e.wts), L.ptr(e.upd_rows), L.ptr(e.upd_pos),
-               torch.cuda.current_stream(e.dev).cuda_stream)
+        torch.ops.deepctr.arrange_update_list(self.feats, self.feat_field_dev, self.F, self.pad_row, self.pad_row, e.ids, e.wts,
+                                              e.upd_rows.view(self.N, self.J), e.upd_pos.view(self.N, self.J))
 
     def _device_step(self):
         decay = 1.0 - 2.0 * self.lambda_fm * self.lr / getattr(self, "global_N", self.N)   # FNN_wnzh.py:305 (b_size)

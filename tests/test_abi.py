@@ -76,3 +76,29 @@ def test_host_pack_fields(built_lib):
             assert np.array_equal(ids, np.concatenate([np.broadcast_to(np.arange(nn), (N, nn)), c.astype(np.int64) + off], 1))
             assert np.array_equal(w, np.concatenate([v, cw if wts_given else np.ones_like(cw)], 1))
     assert built_lib.dctr_host_pack_fields(None, 2, None, None, None, 1, 0, 1, None, None, 1) == _lib.EINVAL
+
+
+def test_every_device_entry_point_is_a_torch_op(built_lib):
+    """north_star: "a thin C-ABI exposed as PyTorch custom ops" -- one torch.ops.deepctr.<name> per device entry point of
+    include/dctr.h (host helpers, size queries and per-thread settings have no tensors to dispatch on), each declared with a
+    schema that marks what it writes, CUDA-only."""
+    import torch
+    from deepctr_b200 import ops
+    host_side = {"dctr_version", "dctr_last_error", "dctr_launch_count", "dctr_set_launch_mode", "dctr_set_id_status",
+                 "dctr_host_pack_fields", "dctr_mlp2_supported"}
+    merged = {"dctr_sort_rows": "sort_pairs", "dctr_arrange_fields": "arrange_update_list", "dctr_scatter_sgd_masked": "scatter_sgd",
+              "dctr_out_bwd": "out_bwd_fused"}      # entry points that are special cases of another one's op
+    for sym in declared_symbols():
+        if sym in host_side or sym.endswith("_workspace"):
+            continue
+        name = merged.get(sym, sym[len("dctr_"):])
+        assert name in ops.OPS, "no torch op for %s" % sym
+        schema = str(getattr(torch.ops.deepctr, name).default._schema)
+        assert "!" in schema, "%s declares no mutated argument: %s" % (name, schema)
+    # no CPU fallback: the dispatcher has no CPU kernel to run
+    try:
+        torch.ops.deepctr.vec_sum(torch.zeros(4), 4, 1.0, torch.zeros(1))
+    except NotImplementedError:
+        pass
+    else:
+        raise AssertionError("a CPU tensor must not dispatch")
