@@ -240,11 +240,12 @@ static int num_passes(int64_t X, int64_t M) {
 template <int RB, int ITEMS>
 static constexpr size_t pass_smem() { return ((size_t)(kSortThreads / 32 + 2) * (1 << RB) + 2 * kSortThreads * ITEMS) * sizeof(unsigned); }
 
-// keys per CTA of the pass kernel: 4096 on long lists (fewer tiles: half the look-back and scan work per key), 2048 otherwise
+// keys per CTA of the pass kernel (DCTR_SORT_ITEMS = 8 | 16 rows of 32 keys per warp: experiment knob)
 static int pass_items(int64_t M) {
     static const int forced = [] { const char* e = getenv("DCTR_SORT_ITEMS"); const int v = e ? atoi(e) : 0; return (v == 8 || v == 16) ? v : 0; }();
     if (forced) return forced;
-    return M > ((int64_t)1 << 20) ? 16 : 8;
+    (void)M;
+    return 8;          // 4096-key tiles (128-146 registers, 1-2 CTAs per SM) measured slower: 0.957 vs 0.767 ms at 16.7 M keys
 }
 
 template <int RB, int ITEMS>
