@@ -307,17 +307,43 @@ def emb_roofline(N=1 << 20, F=16, rank=10, X=20_000_000, reps=5, zipf=1.1):
 
 def run_b200(args, rank, world):
     import torch
-    import deepctr_b200
-    from deepctr_b200 import _lib
+    import deepctr_b200  # noqa: F401
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dist = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    wl = args.workload
+    out = measure_workload(args.workload, args.batch, args.steps, max(3, args.warmup), rank, world, dist, local, not args.no_profile)
+    if rank == 0 and world == 1 and not args.no_profile:
+        torch.cuda.empty_cache()
+        out["emb_roofline"] = emb_roofline()
+        out["emb_roofline_uniform_ids"] = emb_roofline(zipf=0.0)
+    # the other configurations BASELINE.json names, at the same number of GPUs, in the same driver run: config 5 (Criteo-shaped,
+    # 10^8-row table row-sharded over the ranks: the curve the north star's 0.8 scaling target is stated on) and config 4
+    # (FNN_IP_L7 at batch 65 536 per GPU, data parallel)
+    if args.workload == "fnn_ipinyou" and not args.batch and not args.no_secondary:
+        out["secondary"] = {}
+        for wl2 in ("fnn_criteo_sharded", "fnn_ip_l7_ipinyou"):
+            r2 = measure_workload(wl2, 0, min(args.steps, 20), 3, rank, world, dist, local, False)
+            out["secondary"][wl2] = {k: r2[k] for k in ("value", "unit", "ms_per_step", "n_gpus", "config", "e2e", "launches_per_step", "clocks")}
+    if rank == 0 and world == 1 and not args.no_cpu:
+        out["cpu_baseline"] = cpu_baseline(args.workload, args.batch or WORKLOADS[args.workload][6], budget_s=12.0)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if dist:
+        from deepctr_b200 import dist as ddist
+        ddist.shutdown(dist, [])
+
+
+def measure_workload(wl, batch, steps, warmup, rank, world, dist, local, profile):
+    """One workload at `world` GPUs: device-timed steps (value), the end-to-end loop through the model class (e2e), the
+    per-kernel pass (profile).  Returns the JSON line as a dict."""
+    import torch
+    from deepctr_b200 import _lib
+    import gc
     form, F, X, rank_k, hidden, cross, N = WORKLOADS[wl]
-    N = args.batch or N
+    N = batch or N
     sharded = wl.endswith("_sharded")
     model, train = build_model(wl, N, shard=(rank, world) if sharded else None)
     if world > 1:
@@ -330,7 +356,7 @@ def run_b200(args, rank, world):
     pool, _ = make_pool(form, F, X, N, 8, seed=1234 + rank)
     dpool = [(torch.as_tensor(i.astype(np.int32)).cuda(), torch.as_tensor(w).cuda(), torch.as_tensor(y).cuda()) for i, w, y in pool]
     flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device="cuda")     # > 126 MB L2
-    K, W = args.steps, max(3, args.warmup)
+    K, W = steps, warmup
 
     def device_step(i):
         ids, wts, y = dpool[i % len(dpool)]
@@ -412,7 +438,7 @@ def run_b200(args, rank, world):
 
     # ---- per-kernel timing (CUDA events on the launching stream; eager; launches queued behind a sleep) ----
     kernels, roof = [], None
-    if not args.no_profile:
+    if profile:
         was_graph = model.use_graph
         model.use_graph = False
         eng.overlap_wgrad = False
@@ -478,23 +504,19 @@ def run_b200(args, rank, world):
     if roof:
         out["roofline"] = roof
         out["kernels"] = kernels
-    if rank == 0 and world == 1 and not args.no_profile:
-        del flush, dpool
-        torch.cuda.empty_cache()
-        out["emb_roofline"] = emb_roofline()
-    if rank == 0 and world == 1 and not args.no_cpu:
-        out["cpu_baseline"] = cpu_baseline(wl, N, budget_s=12.0)
-    if rank == 0:
-        print(json.dumps(out), flush=True)
-    if dist:
-        from deepctr_b200 import dist as ddist
-        ddist.shutdown(dist, [model])
+    # release the model (and its captured graph) before the next workload is built
+    model._graph = None
+    del flush, dpool, model, eng, train
+    gc.collect()
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    return out
 
 
 # ---------------------------------------------------------------------------------------------------
 # CPU arm: the oracle restatement of the reference step (numpy float64 + OpenBLAS, all host cores)
 # ---------------------------------------------------------------------------------------------------
-def oracle_stepper(wl, N, seed=1234):
+def oracle_stepper(wl, N, seed=1234, dtype=np.float64):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import deepctr_oracle as O
     form, F, X, rank, hidden, cross, _ = WORKLOADS[wl]
@@ -502,21 +524,21 @@ def oracle_stepper(wl, N, seed=1234):
     d = rank + 1
     table = rng.uniform(-0.01, 0.01, (X, d))
     if form == "fm":
-        fm = O.OracleFM(table, 0.0)
+        fm = O.OracleFM(table, 0.0, dtype=dtype)
         return lambda ids, wts, y: fm.train_step(ids, wts, y, 1e-3, 0.0, dense_l2=False)
     cw = {"none": 0, "ip": F * (F - 1) // 2, "op": d * d}[cross]
     dims = [F * d + cw + 1] + hidden + [1]
     Ws = [rng.uniform(-1, 1, (dims[i], dims[i + 1])) / np.sqrt(dims[i]) for i in range(len(dims) - 1)]
     bs = [np.zeros(dims[i + 1]) for i in range(len(dims) - 1)]
     if form == "theano":
-        net = O.OracleNet(table, 0.0, Ws, bs, F, d, "none", True, "none", "tanh")
+        net = O.OracleNet(table, 0.0, Ws, bs, F, d, "none", True, "none", "tanh", dtype=dtype)
         mrng = np.random.RandomState(234)
 
         def step(ids, wts, y):
-            masks = [None, mrng.binomial(1, 0.5, (1, hidden[0])).astype(np.float64), mrng.binomial(1, 0.5, (1, hidden[1])).astype(np.float64)]
+            masks = [None, mrng.binomial(1, 0.5, (1, hidden[0])).astype(dtype), mrng.binomial(1, 0.5, (1, hidden[1])).astype(dtype)]
             return net.train_step_theano(ids, y, 1e-3, 0.1, masks=masks, closed_form=True)
         return step
-    net = O.OracleNet(table, 0.0, Ws, bs, F, d, cross, False, "tanh", "tanh")
+    net = O.OracleNet(table, 0.0, Ws, bs, F, d, cross, False, "tanh", "tanh", dtype=dtype)
     if wl.endswith("_adam"):
         return lambda ids, wts, y: net.train_step_tf_adam(ids, wts, y, 1e-4, 1e-8)
     return lambda ids, wts, y: net.train_step_tf(ids, wts, y, 1e-3)
@@ -533,6 +555,44 @@ def use_all_host_threads():
     return n
 
 
+def faithful_baseline(wl, n1=512, budget_s=4.0):
+    """B1 of SURVEY 8(d): what the reference COSTS -- its own structure on a reduced batch: the per-sample, per-feature gather of
+    feats_to_layer_one_array (FNN_wnzh.py:87-96), BLAS for the Theano graph, and the interpreted triple update loop (:298-306)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import deepctr_oracle as O
+    form, F, X, rank, hidden, cross, _ = WORKLOADS[wl]
+    if form != "theano":
+        return None
+    from deepctr_b200 import data
+    rng = np.random.default_rng(5)
+    d = rank + 1
+    sizes = data.ipinyou_field_sizes(X)
+    feat_field = np.repeat(np.arange(F), sizes)
+    table = np.concatenate([rng.uniform(-0.01, 0.01, (X, d)), np.zeros((1, d))], 0)
+    dims = [F * d + 1] + hidden + [1]
+    Ws = [rng.uniform(-1, 1, (dims[i], dims[i + 1])) / np.sqrt(dims[i]) for i in range(3)]
+    net = O.OracleNet(table, 0.0, Ws, [np.zeros(dims[i + 1]) for i in range(3)], F, d, "none", True, "none", "tanh")
+    n, t0 = 0, time.perf_counter()
+    while True:
+        ids = data.make_field_batch(rng, n1, sizes, 1.1)
+        y = (rng.random(n1) < 0.05).astype(np.float64)
+        feats = [list(r) for r in ids]
+        x = np.zeros((n1, dims[0]))
+        for t, ft in enumerate(feats):                       # feats_to_layer_one_array, one sample at a time
+            x[t, 0] = 0.0
+            for feat in ft:
+                o = 1 + feat_field[feat] * d
+                x[t, o:o + d] = net.table[feat]
+        masks = [None, rng.binomial(1, 0.5, (1, hidden[0])).astype(np.float64), rng.binomial(1, 0.5, (1, hidden[1])).astype(np.float64)]
+        net.train_step_theano_feats(feats, feat_field, y, 1e-3, 0.1, masks)       # BLAS graph + the literal triple loop
+        n += 1
+        el = time.perf_counter() - t0
+        if el > budget_s:
+            break
+    return {"value": n * n1 / el, "unit": "samples/s", "kind": "port", "cores": 1,
+            "sample": "%d steps of batch %d: per-sample gather loop + BLAS graph + interpreted triple update loop (the reference's own structure)" % (n, n1)}
+
+
 def cpu_baseline(wl, N, budget_s=12.0, steps=None):
     form, F, X, *_ = WORKLOADS[wl]
     use_all_host_threads()
@@ -546,9 +606,23 @@ def cpu_baseline(wl, N, budget_s=12.0, steps=None):
         el = time.perf_counter() - t0
         if (steps and n >= steps) or (not steps and el > budget_s):
             break
-    return {"value": n * N / el, "unit": "samples/s", "cores": os.cpu_count(), "kind": "port",
-            "sample": "%d steps of batch %d of workload %s (vectorised numpy float64 restatement, OpenBLAS threads = all cores)" % (n, N, wl),
-            "ms_per_step": el / n * 1e3}
+    out = {"value": n * N / el, "unit": "samples/s", "cores": os.cpu_count(), "kind": "port",
+           "sample": "%d steps of batch %d of workload %s (B2: vectorised numpy float64 restatement, OpenBLAS threads = all cores; "
+                     "the Theano path of the reference is float64, its TF path float32)" % (n, N, wl),
+           "ms_per_step": el / n * 1e3}
+    if not steps:
+        # the same port in float32 (what the TF generation of the reference computes in) and the faithful loop structure (B1)
+        step32 = oracle_stepper(wl, N, dtype=np.float32)
+        step32(*pool[0])
+        k, t0 = 0, time.perf_counter()
+        while time.perf_counter() - t0 < budget_s / 3:
+            step32(*pool[k % len(pool)])
+            k += 1
+        out["float32"] = {"value": k * N / (time.perf_counter() - t0), "unit": "samples/s", "steps": k}
+        b1 = faithful_baseline(wl)
+        if b1:
+            out["faithful_B1"] = b1
+    return out
 
 
 def run_reference(args, rank, world):
@@ -596,6 +670,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the secondary block (BASELINE configs 4 and 5 at the same GPU count)")
     ap.add_argument("--emb-only", action="store_true", help="only run the embedding-kernel roofline sweep")
     ap.add_argument("--emb-n", type=int, default=1 << 20)
     ap.add_argument("--emb-reps", type=int, default=5)

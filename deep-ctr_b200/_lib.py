@@ -53,6 +53,7 @@ SIGNATURES = {
     "dctr_eval_metrics_workspace": (_z, [_l]),
     "dctr_eval_metrics": (_i, [_p, _p, _l, _p, _p, _z, _p]),
     "dctr_out_unit_train": (_i, [_p, _i, _i, _i, _p, _p, _p, _f, _i, _p, _i, _p, _p, _p, _p, _f, _p, _p, _i, _p, _p, _p, _z, _p]),
+    "dctr_dropout_masks": (_i, [_p, _l, _f, ctypes.c_uint, _p, _p, _l, _p]),
     "dctr_l2_loss_add": (_i, [_p, _l, _p, _i, _f, _p, _p, _z, _p]),
     "dctr_mlp2_transpose": (_i, [_i, _i, _i, _p, _i, _p, _i, _p, _i, _p, _i, _p]),
     "dctr_mlp2_supported": (_i, [_i, _i, _i]),
@@ -74,13 +75,20 @@ SIGNATURES = {
 _lib = None
 
 
-def build(force=False):
-    """Compile libdctr.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+def build(force=False, verbose=True):
+    """Compile libdctr.so in-tree for sm_100a (nvcc cross-compiles without a GPU).  Prints which sources were compiled and which
+    objects were reused (the prebuilt objects travel with the snapshot to the GPU box)."""
     if force:
         subprocess.run(["make", "-C", CSRC, "clean"], check=True, capture_output=True)
     r = subprocess.run(["make", "-C", CSRC, "-j8"], capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("building libdctr.so failed:\n" + r.stdout[-4000:] + r.stderr[-4000:])
+    if verbose:
+        compiled = sorted(set(ln.split(" -c ")[1].split()[0] for ln in r.stdout.splitlines() if " -c " in ln))
+        srcs = sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
+        linked = any(" -shared " in ln for ln in r.stdout.splitlines())
+        print("deepctr_b200.build: %d of %d CUDA sources compiled for sm_100a (%s), %d objects reused, libdctr.so %s"
+              % (len(compiled), len(srcs), ", ".join(compiled) or "none", len(srcs) - len(compiled), "linked" if linked else "up to date"))
     return LIB_PATH
 
 

@@ -578,6 +578,60 @@ extern "C" int dctr_l2_loss_add(const float* v, int64_t n, const float* extra, i
     return dctr::check_launch("sumsq_kernel");
 }
 
+// tf.nn.dropout masks for every layer input of a step in ONE launch (FNN.py:87-89: keep_prob + U[0,1) floored, scaled by
+// 1 / keep_prob), drawn on the device with Philox-4x32-10 keyed by (seed, step counter): the step replays as a CUDA graph, so
+// the counter lives in device memory and is advanced by the kernel's last CTA.  TF leaves these masks unseeded; parity runs
+// inject masks instead.  apply != NULL: the first `apply_n` mask elements are also multiplied into `apply` in place (the
+// dropout on act(z1), the first layer's input).
+namespace dctr {
+__device__ __forceinline__ uint4 philox4x32(uint4 ctr, uint2 key) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const unsigned hi0 = __umulhi(0xD2511F53u, ctr.x), lo0 = 0xD2511F53u * ctr.x;
+        const unsigned hi1 = __umulhi(0xCD9E8D57u, ctr.z), lo1 = 0xCD9E8D57u * ctr.z;
+        ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+        key.x += 0x9E3779B9u; key.y += 0xBB67AE85u;
+    }
+    return ctr;
+}
+__global__ void __launch_bounds__(256)
+dropout_masks_kernel(float4* __restrict__ masks, int64_t n4, float keep, unsigned seed, unsigned* __restrict__ state,
+                     float4* __restrict__ apply, int64_t apply_n4) {
+    pdl_sync();
+    const unsigned step = state[0];
+    const float inv = 1.f / keep;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (int64_t)gridDim.x * 256) {
+        const uint4 r = philox4x32(make_uint4((unsigned)i, (unsigned)(i >> 32), step, 0u), make_uint2(seed, 0x5EEDu));
+        // 24-bit uniforms in [0, 1): kept iff u < keep  (== floor(keep + u') >= 1 for u' = 1 - u)
+        float4 m;
+        m.x = (r.x >> 8) * (1.f / 16777216.f) < keep ? inv : 0.f;
+        m.y = (r.y >> 8) * (1.f / 16777216.f) < keep ? inv : 0.f;
+        m.z = (r.z >> 8) * (1.f / 16777216.f) < keep ? inv : 0.f;
+        m.w = (r.w >> 8) * (1.f / 16777216.f) < keep ? inv : 0.f;
+        masks[i] = m;
+        if (i < apply_n4) {
+            float4 v = apply[i];
+            v.x *= m.x; v.y *= m.y; v.z *= m.z; v.w *= m.w;
+            apply[i] = v;
+        }
+    }
+    if (take_last_ticket(state + 1, gridDim.x) && threadIdx.x == 0) state[0] = step + 1;      // every CTA has read the counter
+}
+}  // namespace dctr
+
+extern "C" int dctr_dropout_masks(float* masks, int64_t n, float keep, unsigned seed, unsigned* state, float* apply, int64_t apply_n,
+                                  void* stream) {
+    DCTR_REQUIRE(masks && state && n >= 0 && (n & 3) == 0 && ((uintptr_t)masks & 15) == 0 && keep > 0.f && keep <= 1.f,
+                 "dropout_masks: bad arguments (n a multiple of 4, masks 16-byte aligned, 0 < keep <= 1)");
+    DCTR_REQUIRE(!apply || ((apply_n & 3) == 0 && apply_n <= n && ((uintptr_t)apply & 15) == 0), "dropout_masks: bad apply block");
+    if (n == 0) return DCTR_OK;
+    int blocks = dctr::ceil_div(n / 4, 256 * 4);
+    if (blocks > dctr::kNumSMs * 8) blocks = dctr::kNumSMs * 8;
+    dctr::launch_k(dctr::dropout_masks_kernel, blocks, 256, 0, dctr::as_stream(stream), reinterpret_cast<float4*>(masks), n / 4, keep, seed, state,
+                   reinterpret_cast<float4*>(apply), apply ? apply_n / 4 : (int64_t)0);
+    return dctr::check_launch("dropout_masks_kernel");
+}
+
 extern "C" int dctr_vec_sum(const float* v, int N, float scale, float* out, void* stream) {
     DCTR_REQUIRE(v && out && N >= 0, "vec_sum: bad arguments");
     launch_k(vec_sum_kernel, 1, 1024, 0, as_stream(stream), v, N, scale, out);

@@ -114,6 +114,7 @@ class StepEngine:
         self.overlap_sort = True
         self.wts_are_ones = True
         self.upd_rows = self.upd_pos = None     # use_update_list()
+        self.dropout = None                     # (flat mask buffer, keep_prob, seed, device state): masks drawn inside the step
         # Small two-hidden-layer nets: the whole MLP forward + backward as ONE fp32 FFMA kernel per 32-sample tile and the weight
         # gradients (+ SGD) as one cluster kernel (csrc/mlp2.cu) instead of ~14 per-layer launches.  Opt-in (DCTR_MLP2=on):
         # measured at N = 4096, 177-300-100-1 it LOSES to the per-layer tcgen05 chain (0.264 vs 0.158 ms per step,
@@ -211,10 +212,16 @@ class StepEngine:
         ids, table, X = (self.ids, self.table, self.X) if lookup is None else lookup
         self._embed_forward(ids, wts, table, X)
         if with_loss and self.fused_mlp2:
+            if self.dropout is not None:
+                flat, keep, seed, state = self.dropout
+                O.dropout_masks(flat, keep, seed, state, None)      # the fused kernel applies the first mask itself
             self._mlp2_forward_backward(gscale)
             return
-        if self.masks[0] is not None:
-            self.ins[0].mul_(self.masks[0])     # input dropout (tf.nn.dropout on act(z1), FNN.py:87): torch elementwise
+        if with_loss and self.dropout is not None:
+            flat, keep, seed, state = self.dropout      # this step's tf.nn.dropout masks, the first one applied to act(z1) (FNN.py:87)
+            O.dropout_masks(flat, keep, seed, state, self.ins[0])
+        elif self.masks[0] is not None:
+            self.ins[0].mul_(self.masks[0])     # injected masks (parity runs): plain elementwise product
         for l in range(self.nl - 1):
             self._gemm(L.GEMM_NN, N, self.widths[l + 1], self.widths[l], self.ins[l], self.W(l), self.ins[l + 1], L.EPI_FWD,
                        L.ACT[self.act_of(l + 1)], self.b(l), None, self.masks[l + 1], 1)

@@ -438,11 +438,17 @@ class _FNNBase(_Base):
             self.ptmzr, self.loss, self.train_preds = Fetch(self, "ptmzr"), Fetch(self, "loss"), Fetch(self, "train_preds")
             self.eval_preds = Fetch(self, "eval_preds")
             if self._keep_prob < 1.0:
-                # tf.nn.dropout on every layer input incl. act(z1) (FNN.py:87-89): Bernoulli(keep)/keep
-                self._masks = [torch.ones(batch_size, eng.ldi[l], device=eng.dev) for l in range(eng.nl)]
+                # tf.nn.dropout on every layer input incl. act(z1) (FNN.py:87-89): Bernoulli(keep) / keep.  All masks of a step
+                # live in one buffer (layer 0 first) and are drawn by ONE kernel inside the captured step (dctr_dropout_masks,
+                # Philox keyed by a device-side step counter), which also applies the first layer's mask to act(z1).
+                sizes = [batch_size * eng.ldi[l] for l in range(eng.nl)]
+                flat = torch.ones(sum(sizes), device=eng.dev)
+                self._masks, o = [], 0
+                for l, n in enumerate(sizes):
+                    self._masks.append(flat[o:o + n].view(batch_size, eng.ldi[l]))
+                    o += n
                 eng.masks = list(self._masks)
-                self._gen = torch.Generator(device=eng.dev)
-                self._gen.manual_seed(0x5EED)
+                eng.dropout = (flat, self._keep_prob, 0x5EED, torch.zeros(2, dtype=torch.int32, device=eng.dev))
         else:
             self.test_preds = Fetch(self, "test_preds")
 
@@ -451,6 +457,7 @@ class _FNNBase(_Base):
         eng = self.engine
         self._masks = None
         eng.masks = [None] * eng.nl
+        eng.dropout = None
         for l, m in enumerate(masks):
             if m is not None:
                 t = torch.zeros(self.N, eng.ldi[l], device=eng.dev)
@@ -462,11 +469,6 @@ class _FNNBase(_Base):
         old = self.engine.masks
         self.engine.masks = masks if masks is not None else [None] * self.engine.nl
         return old
-
-    def _pre_step(self):
-        if self._masks is not None:
-            for m in self._masks:
-                m.copy_((torch.rand(m.shape, device=m.device, generator=self._gen) < self._keep_prob).float() / self._keep_prob)
 
     def _device_step(self):
         gs = 1.0 if self._reduce == "sum" else 1.0 / getattr(self, "global_N", self.N)

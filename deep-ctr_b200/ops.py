@@ -250,6 +250,12 @@ def dense_ftrl(param, grad, accum, linear, n, lr, lr_power, l1, l2, grad_l2, zer
            _ptr(linear, _F32, "linear", 16), n, lr, lr_power, l1, l2, grad_l2, int(zero_grad), _st(param))
 
 
+@_op("dropout_masks", "(Tensor(a!) masks, float keep, int seed, Tensor(b!) state, Tensor(c!)? apply) -> ()")
+def dropout_masks(masks, keep, seed, state, apply):
+    L.call("dctr_dropout_masks", _ptr(masks, _F32, "masks", 16), masks.numel(), keep, seed, _ptr(state, _I32, "state"),
+           _ptr(apply, _F32, "apply", 16), 0 if apply is None else apply.numel(), _st(masks))
+
+
 # ---- fused two-hidden-layer step (csrc/mlp2.cu) ------------------------------------------------------------------------------------
 @_op("mlp2_transpose", "(int D0, int H1, int H2, Tensor W1, Tensor W2, Tensor(a!) W1t, Tensor(b!) W2t) -> ()")
 def mlp2_transpose(D0, H1, H2, W1, W2, W1t, W2t):

@@ -244,6 +244,13 @@ int dctr_vec_sum(const float* v, int N, float scale, float* out, void* stream);
 int dctr_l2_loss_add(const float* v, int64_t n, const float* extra, int n_extra, float scale, float* out,
                      void* workspace, size_t workspace_bytes, void* stream);
 
+/* tf.nn.dropout masks (FNN.py:87-89) for all layer inputs of a step in one launch: masks[i] = Bernoulli(keep) / keep from
+ * Philox-4x32-10 keyed by (seed, state[0]); state = {step counter, ticket} (2 words, zero before the first step), advanced on
+ * the device so that a captured CUDA graph draws fresh masks on every replay.  apply != NULL: apply[0:apply_n) *= masks[0:apply_n)
+ * (the first layer's input).  n, apply_n multiples of 4; 16-byte aligned buffers. */
+int dctr_dropout_masks(float* masks, int64_t n, float keep, unsigned seed, unsigned* state, float* apply, int64_t apply_n,
+                       void* stream);
+
 /* ---- K7: dense SGD over a flat parameter buffer (tf_util.py:27 / FNN_wnzh.py:180-182) ---------- */
 int dctr_dense_sgd(float* param, const float* grad, int64_t n, float lr, float decay, void* stream);
 

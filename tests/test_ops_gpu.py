@@ -78,3 +78,67 @@ def test_ops_equal_raw_abi_and_validate():
         O.gather_concat_fwd(ids, wts, table, d, 0, False, bias, 1, c)
     s.synchronize()
     assert torch.equal(c, a)
+
+
+def test_dropout_masks_kernel_and_graph_replay():
+    """dctr_dropout_masks: values in {0, 1/keep}, keep fraction, fresh masks on every launch AND every graph replay (the step
+    counter lives on the device), reproducible for the same (seed, step), first block applied in place."""
+    O = torch.ops.deepctr
+    n, keep = 1 << 20, 0.5
+    m = torch.zeros(n, device="cuda")
+    st = torch.zeros(2, dtype=torch.int32, device="cuda")
+    x = torch.ones(4096, device="cuda")
+    O.dropout_masks(m, keep, 7, st, x)
+    torch.cuda.synchronize()
+    first = m.clone()
+    assert set(torch.unique(m).tolist()) == {0.0, 2.0}
+    assert abs(float((m > 0).float().mean()) - keep) < 3e-3
+    assert torch.equal(x, m[:4096]) and int(st[0]) == 1 and int(st[1]) == 0
+    O.dropout_masks(m, keep, 7, st, None)
+    assert not torch.equal(m, first) and int(st[0]) == 2
+    st.zero_()
+    O.dropout_masks(m, keep, 7, st, None)
+    assert torch.equal(m, first)                      # same (seed, step) -> same masks
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(g):
+            O.dropout_masks(m, 0.8, 7, st, None)
+    seen = []
+    for _ in range(3):
+        g.replay()
+        torch.cuda.synchronize()
+        seen.append(m.clone())
+    assert not torch.equal(seen[0], seen[1]) and not torch.equal(seen[1], seen[2])
+    assert abs(float((seen[2] > 0).float().mean()) - 0.8) < 3e-3 and abs(float(seen[2].max()) - 1.25) < 1e-6
+
+
+def test_tf_dropout_runs_inside_the_captured_step(tmp_path):
+    """FNN with keep_prob 0.5 (baseline.py:164): the masks are drawn by the library inside the CUDA graph -- no eager torch op per
+    step -- and differ from step to step; predictions use no dropout."""
+    import deepctr_b200.models as M
+    from deepctr_b200 import _lib as L
+    rng = np.random.default_rng(0)
+    cat_sizes = np.array([50, 7, 200])
+    offsets = [2 + int(cat_sizes[:i].sum()) for i in range(3)]
+    N = 256
+    m = M.FNN(cat_sizes, offsets, N, [2 + int(cat_sizes.sum()), 5, 4, 32, 16, "tanh"], ["uniform", -0.1, 0.1, list(range(1, 12)), None],
+              ["sgd", 0.01, "sum"], [0.5], "train", N)
+    assert m.engine.dropout is not None
+    feed = {m.v_wt_hldr: rng.random((N, 2)).astype(np.float32), m.c_id_hldr: np.stack([rng.integers(0, s, N) for s in cat_sizes], 1),
+            m.c_wt_hldr: np.ones((N, 3), np.float32), m.lbl_hldr: rng.integers(0, 2, N)}
+    masks, launches = [], []
+    for step in range(5):
+        l0 = L.launch_count()
+        loss, p = m.train_step(feed)
+        launches.append(L.launch_count() - l0)
+        assert np.isfinite(loss)
+        masks.append(m.engine.masks[1].clone())
+    assert m._graph is not None and launches[-1] == 0          # replayed: nothing is launched from the host, masks included
+    assert not torch.equal(masks[3], masks[4])
+    assert abs(float((masks[4] > 0).float().mean()) - 0.5) < 0.05
+    p1 = m.eval_preds.eval({m.eval_id_hldr: np.concatenate([np.broadcast_to(np.arange(2), (N, 2)), feed[m.c_id_hldr] + np.asarray(offsets)], 1),
+                            m.eval_wts_hldr: np.concatenate([feed[m.v_wt_hldr], feed[m.c_wt_hldr]], 1)})
+    p2 = m.eval_preds.eval({m.eval_id_hldr: np.concatenate([np.broadcast_to(np.arange(2), (N, 2)), feed[m.c_id_hldr] + np.asarray(offsets)], 1),
+                            m.eval_wts_hldr: np.concatenate([feed[m.v_wt_hldr], feed[m.c_wt_hldr]], 1)})
+    assert np.array_equal(p1, p2)
