@@ -122,7 +122,7 @@ class DataParallelStep(object):
             gids = self._gather(self.gids, e.ids)
             gwts = None if e.wts_are_ones else self._gather(self.gwts, e.wts)
             self._sort_global(gids)
-        e.forward(True, gscale, lam)
+        e.forward(True, gscale, lam if self.rank == 0 else 0.0)      # the loss is summed over the ranks: the L2 term enters once
         O.vec_sum(e.g, e.N, 1.0, e.grads)
         self._reduce_dense()
         e.bias_update(lr, lam)

@@ -11,7 +11,8 @@ import torch
 import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT)
+sys.path[:0] = [ROOT, os.path.join(ROOT, "oracle")]
+import deepctr_oracle as O  # noqa: E402  (the checker: every rank also runs the float64 oracle on the GLOBAL batch)
 
 
 def main():
@@ -38,6 +39,8 @@ def main():
     ddist.attach(fm_dp, dist)
     fm_ref = FM(GN, [X, F, k - 1], ["uniform", -0.05, 0.05, [1, 2], None], ["sgd", 0.05, "mean"], [0.01], "train", GN)
     fm_ref.use_graph = False
+    onet = O.OracleNet(np.concatenate([table, np.zeros((1, k))], 0), -0.3, Ws, bs, F, k, "none", True, "none", "tanh")
+    ofm = O.OracleFM(fm_ref.engine.get_table().astype(np.float64), 0.0)
     for step in range(6):            # 2 eager steps, the capture, then graph replays of kernels + NCCL collectives
         feats = np.stack([rng.integers(0, X // F, GN) + f * (X // F) for f in range(F)], 1)
         feats[:, 0] = 3
@@ -52,10 +55,21 @@ def main():
         # summation orders of the dense gradients (all-reduce vs split-K) grows with the global batch
         np.testing.assert_allclose(dp.get_table(), ref.get_table(), rtol=2e-5, atol=max(2e-6, 5e-8 * GN))
         np.testing.assert_allclose(dp.get_weights()[0], ref.get_weights()[0], rtol=2e-5, atol=2e-6)
+        # ... and the ORACLE on the global batch: 1e-5 relative per step (north_star), absolute floor for the hot row as above
+        ol, op = onet.train_step_theano(feats, y, 0.01, 0.1)
+        tol = 1e-5 * (step + 1)
+        np.testing.assert_allclose(l1, ol, rtol=tol)
+        np.testing.assert_allclose(p1, op[sl], rtol=tol, atol=1e-6)
+        np.testing.assert_allclose(dp.get_table(), onet.table[:-1], rtol=tol, atol=max(2e-6, 5e-8 * GN))
+        np.testing.assert_allclose(dp.get_weights()[0], onet.Ws[0], rtol=tol, atol=2e-6)
         f1 = fm_dp.train_step({fm_dp.sp_id_hldr: feats[sl].reshape(-1), fm_dp.sp_wt_hldr: wts[sl].reshape(-1), fm_dp.lbl_hldr: y[sl]})
         f0 = fm_ref.train_step({fm_ref.sp_id_hldr: feats.reshape(-1), fm_ref.sp_wt_hldr: wts.reshape(-1), fm_ref.lbl_hldr: y})
         np.testing.assert_allclose(f1[1], f0[1][sl], rtol=2e-5, atol=1e-6)
         np.testing.assert_allclose(fm_dp.engine.get_table(), fm_ref.engine.get_table(), rtol=2e-5, atol=2e-6)
+        fl, fp = ofm.train_step(feats, wts, y, 0.05, 0.01, "mean")
+        np.testing.assert_allclose(f1[0], fl, rtol=tol)
+        np.testing.assert_allclose(f1[1], fp[sl], rtol=tol, atol=1e-6)
+        np.testing.assert_allclose(fm_dp.engine.get_table(), ofm.table, rtol=tol, atol=2e-6)
     # Adam (dense, TF form) under data parallelism: FM with L2, against the single-GPU Adam step on the global batch
     ad_dp = FM(N, [X, F, k - 1], ["uniform", -0.05, 0.05, [1, 2], None], ["adam", 1e-2, 1e-8, "mean"], [0.01], "train", N)
     ddist.attach(ad_dp, dist)

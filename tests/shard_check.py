@@ -14,7 +14,8 @@ import torch
 import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT)
+sys.path[:0] = [ROOT, os.path.join(ROOT, "oracle")]
+import deepctr_oracle as O  # noqa: E402  (the checker: every rank also runs the float64 oracle on the GLOBAL batch)
 
 
 def main():
@@ -50,6 +51,9 @@ def main():
         ddist.attach_sharded(sh, dist, X_dim)
         ref = cls(cat_sizes, offsets, GN, rch, init, ptm, [1.0], "train", GN)
         ref.use_graph = False
+        nl = len(dims) - 1
+        onet = O.OracleNet(np.concatenate([vm["W"], vm["V"]], 1), vm["b"][0], [vm["h%d_w" % (i + 1)] for i in range(nl)],
+                           [vm["h%d_b" % (i + 1)] for i in range(nl)], F, d, cls.cross, False, "tanh", "tanh")
         for step in range(3):
             c_ids = np.stack([rng.integers(0, s, GN) for s in cat_sizes], 1)
             c_ids[GN // 2] = c_ids[0]
@@ -64,6 +68,13 @@ def main():
             mine = ref.engine.get_table()[rank::world]
             np.testing.assert_allclose(sh.engine.get_table()[:mine.shape[0]], mine, rtol=tol, atol=2e-6)
             np.testing.assert_allclose(sh.engine.get_layer(0)[0], ref.engine.get_layer(0)[0], rtol=tol, atol=2e-6)
+            if ptm[0] == "sgd":       # ... and the ORACLE on the global batch, 1e-5 relative per step (north_star)
+                g_ids = np.concatenate([np.broadcast_to(np.arange(n_num), (GN, n_num)), c_ids + np.array(offsets)], 1)
+                ol, op = onet.train_step_tf(g_ids, np.concatenate([v_wts, c_wts], 1), y, 0.05)
+                t2 = 1e-5 * (step + 1)
+                np.testing.assert_allclose(l1, ol, rtol=t2)
+                np.testing.assert_allclose(p1, op[sl], rtol=t2, atol=1e-6)
+                np.testing.assert_allclose(sh.engine.get_table()[:mine.shape[0]], onet.table[rank::world], rtol=t2, atol=2e-6)
         # collective inference through the sharded lookup
         ids_eval = np.concatenate([np.broadcast_to(np.arange(n_num), (GN, n_num)), c_ids + np.array(offsets)], 1)
         wts_eval = np.concatenate([v_wts, c_wts], 1)
