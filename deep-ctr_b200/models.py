@@ -512,8 +512,28 @@ class _FNNBase(_Base):
             raise ValueError("fetch %r needs Session.run with model.ptmzr" % kind)
         return self._predict_chunks(ids, wts)
 
-    def var_map(self):
+    def _global_table(self):
+        """[X_dim, d] table in global row order.  Row-sharded mode (shard = (rank, world)): the engine holds the rows g with
+        g % world == rank as local rows g // world; the shards are all-gathered (a collective: every rank must call) and
+        interleaved back, so the checkpoint is the reference's [X_dim, ...] format whatever the sharding."""
         t = self.engine.get_table()
+        if self.shard is None:
+            return t
+        rank, world = self.shard
+        sh = getattr(self, "sharded", None)
+        if sh is None or world == 1:
+            return t[:self.X_dim]
+        loc = self.engine.table[:, :self.engine.d].contiguous()
+        parts = [torch.empty_like(loc) for _ in range(world)]
+        sh.dist.all_gather(parts, loc, group=sh.group)
+        full = np.empty((self.X_dim, self.engine.d), dtype=np.float32)
+        for r, part in enumerate(parts):
+            rows = full[r::world]
+            rows[...] = part[:rows.shape[0]].cpu().numpy()
+        return full
+
+    def var_map(self):
+        t = self._global_table()
         vm = {"W": t[:, :1].copy(), "V": t[:, 1:].copy(), "b": self.engine.bias().cpu().numpy()}
         for i in range(self.engine.nl):
             w, b = self.engine.get_layer(i)
@@ -521,9 +541,12 @@ class _FNNBase(_Base):
         return vm
 
     def dump(self, model_path):
-        """FNN.py:96-101: pickle {'W','V','b','h{i}_w','h{i}_b'}."""
+        """FNN.py:96-101: pickle {'W','V','b','h{i}_w','h{i}_b'}.  Row-sharded: a collective call, rank 0 writes the file."""
+        vm = self.var_map()
+        if self.shard is not None and self.shard[0] != 0:
+            return
         with open(model_path, "wb") as f:
-            pickle.dump(self.var_map(), f)
+            pickle.dump(vm, f)
         print("model dumped at %s" % model_path)
 
 

@@ -230,6 +230,50 @@ class FNN_wnzh(_Base):
         self._predict_into(feats, None, preds)
         return device_metrics(preds, np.asarray(labels, dtype=np.float32).reshape(-1), device=self.engine.dev, nds_rate=nds_rate)
 
+    def set_weights(self, w):
+        """(w1, w2, w3, b1, b2, b3) as get_weights() returns them -- w1.set_value(best_w1) ... of get_pred (FNN_wnzh.py:257-263)."""
+        w1, w2, w3, b1, b2, b3 = w
+        e = self.engine
+        e.set_layer(0, w1, b1)
+        e.set_layer(1, w2, b2)
+        e.set_layer(2, np.asarray(w3).reshape(-1, 1), [b3])
+
+    def fit(self, train_feats, train_y, test_feats, test_y, epochs=100, masks=None, log=None):
+        """The epoch loop of the script (FNN_wnzh.py:286-343): per epoch n_batch = train_size // batch_size consecutive batches
+        (the ragged tail is never trained on), then AUC / RMSE of the whole train and test files (print_err / get_err_bat,
+        :187-221 -- scored on the device), then the patience rule: a new best test AUC snapshots the weights and earns credit
+        (times_reduce up to 3), anything else costs one, below zero stops.  The snapshot is what the LAST train() call of the
+        epoch returned, i.e. the weights BEFORE that step (:179-182, 330-335) -- kept.
+        masks: optional iterator of (r1, r2) pairs injected per step (parity runs).  Returns dict(history, min_err,
+        min_err_epoch, best) with best = the snapshot get_pred would load."""
+        train_feats, test_feats = np.asarray(train_feats), np.asarray(test_feats)
+        train_y, test_y = np.asarray(train_y), np.asarray(test_y)
+        N = self.N
+        n_batch = len(train_y) // N
+        best, min_err, min_err_epoch, times_reduce, history = self.get_weights(), 0, 0, 0, []
+        last = best
+        for i in range(epochs):
+            for j in range(n_batch):
+                if j == n_batch - 1:
+                    last = self.get_weights()
+                if masks is not None:
+                    self.set_masks(*next(masks))
+                self.train(train_feats[j * N:(j + 1) * N], train_y[j * N:(j + 1) * N])
+            tr = self.evaluate(train_feats, train_y)
+            te = self.evaluate(test_feats, test_y)
+            history.append(dict(epoch=i, train_auc=tr["auc"], train_rmse=tr["rmse"], test_auc=te["auc"], test_rmse=te["rmse"]))
+            if log is not None:
+                log("Test Err:%d\t%s\t%s" % (i, te["auc"], te["rmse"]))
+            if te["auc"] > min_err:
+                best, min_err, min_err_epoch = last, te["auc"], i
+                if times_reduce < 3:
+                    times_reduce += 1
+            else:
+                times_reduce -= 1
+            if times_reduce < 0:
+                break
+        return dict(history=history, min_err=min_err, min_err_epoch=min_err_epoch, best=best)
+
     def get_weights(self):
         """(w1, w2, w3, b1, b2, b3) like the tail of train()'s outputs -- POST-update here."""
         e = self.engine

@@ -4,13 +4,18 @@ A numpy (float64 by default) restatement of the reference algorithm for the path
 north_star.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg may
 import this file; the product package (deep-ctr_b200/) never does.
 
-PARITY UNPINNED: the reference (Python 2 + Theano / TensorFlow 0.x) cannot run in this image and ships no
-tests, golden vectors or fixtures.  This restatement is therefore pinned only by
-(a) line-by-line citation of the reference, (b) central finite differences of every hand-derived backward
-(tests/test_oracle.py), (c) algebraic identities (FM pairwise identity, OP prefix form, IP index formula; FTRL = AdaGrad) and
-(d) an independent derivation of every gradient: the forward of each model family rewritten in torch (float64, CPU) and
-differentiated by autograd agrees with the hand-derived backward to 1e-9 (test_network_backward_equals_autograd,
-test_fm_gradient_equals_autograd).
+PARITY PINNED against the reference itself (round 2): the reference's own Python -- /root/reference/python/*.py after the
+mechanical Py2->3 fixes of oracle/build_ref.py -- is executed on two small engine shims (oracle/shims/theano, oracle/shims/
+tensorflow: lazy graphs evaluated by torch, autograd for T.grad / minimize), and tests/test_oracle_vs_ref.py asserts this
+restatement equal to it: every train() / predict() call of the whole FNN_wnzh.py script (23 epochs, duplicate / missing /
+repeated features included, 1e-8), 3 optimiser steps + eval + dump of FM, LR, FNN, FNN_IP_L3/L5/L7, FNN_OP_L3 under sgd / adam /
+ftrl with logged dropout masks (1e-9), build_inds, get_fxy, get_batch_xy, early_stop, watch_train, the whole baseline.train()
+loop, collect / stat / load_ipinyou_data.  What the shims stand in for is the ENGINES (Theano, TensorFlow 0.x: absent from
+/root/reference, unpinned versions): their op semantics are restated from the published behaviour (oracle/shims/*/__init__.py
+list every point).  Golden vectors generated from those runs: tests/golden/ref_golden.pkl (tests/golden/make_golden_ref.py).
+Independently of the reference, this file is also pinned by central finite differences of every hand-derived backward,
+algebraic identities (FM pairwise identity, OP prefix form, IP index formula; FTRL = AdaGrad) and torch-autograd re-derivations
+(tests/test_oracle.py).
 
 Reference citations are file:line under /root/reference/python.
 """

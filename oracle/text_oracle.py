@@ -1,9 +1,9 @@
 """CPU restatement of the reference's TEXT PARSERS -- test infrastructure only (checker of the device-side ingestion,
 deep-ctr_b200/csrc/text.cu); nothing in the product path imports it.
 
-Parity: UNPINNED like the rest of oracle/ -- the reference ships no data files or parser tests; each function
-follows the cited lines literally (Python 2 -> 3 is the only change) and is exercised on files written in the formats those
-parsers imply.
+Parity: pinned against the reference's own parsers executed here (oracle/_ref): get_fxy / get_batch_xy of baseline.py and
+collect / stat / load_ipinyou_data of ipinyou.py in tests/test_oracle_vs_ref.py, the FNN_wnzh.py line parser through the whole
+script run.  The reference ships no data files: the files are written in the formats those parsers imply.
 """
 import numpy as np
 

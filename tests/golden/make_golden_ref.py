@@ -46,6 +46,9 @@ def wnzh():
             if k in (3, 5):                                # weights as train() returned them = after 3 / 5 updates
                 st.update(w1=c["outputs"][1].astype(np.float32), w2=c["outputs"][2].astype(np.float32))
             rec["steps"].append(st)
+    rec["min_err"], rec["min_err_epoch"] = float(g["min_err"]), int(g["min_err_epoch"])
+    with open(os.path.join(wd, "python", "mlp3fm_test_2997.p"), "rb") as f:        # get_pred(test_file, best_w1, ...), FNN_wnzh.py:346-347
+        rec["best_test_pred"] = np.asarray(pickle.load(f), dtype=np.float32)
     preds = [c["outputs"][0] for c in calls if c["fn"] == "function2"]
     rec["epochs"] = [dict(train_p=preds[2 * e].astype(np.float32), test_p=preds[2 * e + 1].astype(np.float32)) for e in range(len(preds) // 2 - 1)]
     return rec

@@ -75,6 +75,17 @@ def main():
                 np.testing.assert_allclose(l1, ol, rtol=t2)
                 np.testing.assert_allclose(p1, op[sl], rtol=t2, atol=1e-6)
                 np.testing.assert_allclose(sh.engine.get_table()[:mine.shape[0]], onet.table[rank::world], rtol=t2, atol=2e-6)
+        # checkpoint of the sharded model = the reference's [X_dim, ...] format: gathered, written by rank 0, reloadable unsharded
+        ck = os.path.join(tempfile.gettempdir(), "shard_check_dump_%s.pickle" % cls_name)
+        sh.dump(ck)
+        dist.barrier()
+        with open(ck, "rb") as f:
+            got = pickle.load(f)
+        np.testing.assert_array_equal(np.concatenate([got["W"], got["V"]], 1), np.concatenate([sh.var_map()["W"], sh.var_map()["V"]], 1))
+        np.testing.assert_allclose(np.concatenate([got["W"], got["V"]], 1), ref.engine.get_table(), rtol=tol, atol=2e-6)
+        assert got["W"].shape == (X_dim, 1) and got["h1_w"].shape == (dims[0], dims[1])
+        re = cls(cat_sizes, offsets, GN, rch, ["uniform", -0.01, 0.01, list(range(1, 12)), ck], ptm, [1.0], "train", GN)
+        np.testing.assert_array_equal(re.engine.get_table(), np.concatenate([got["W"], got["V"]], 1))
         # collective inference through the sharded lookup
         ids_eval = np.concatenate([np.broadcast_to(np.arange(n_num), (GN, n_num)), c_ids + np.array(offsets)], 1)
         wts_eval = np.concatenate([v_wts, c_wts], 1)

@@ -171,3 +171,24 @@ def test_out_of_range_id_raises(gold, tmp_path):
     assert np.isfinite(m.engine.get_table()).all() and m.engine.get_table().shape == before.shape
     l, p = m.train_step({m.sp_id_hldr: st["ids"].flatten(), m.sp_wt_hldr: st["wts"].flatten(), m.lbl_hldr: st["y"]})   # status was reset
     assert np.isfinite(l)
+
+
+def test_fnn_wnzh_epoch_protocol(gold):
+    """FNN_wnzh.fit = the script's epoch loop with its patience rule and best-weight snapshot (FNN_wnzh.py:286-343): fed the
+    dropout draws the reference run logged, it stops after the same epoch, reports the same best epoch and test AUC, and
+    get_pred's predictions with the snapshot (best MLP weights on the FINAL table, :257-263, 346-347) agree."""
+    from deepctr_b200.theano_fnn import FNN_wnzh
+    g = gold["wnzh"]
+    h = g["hyper"]
+    N = h["batch_size"]
+    J = max(len(ft) for _, ft in g["train"] + g["test"])
+    m = FNN_wnzh(dict(w_0=g["w_0"], table=g["table"], feat_field=g["feat_field"]), batch_size=N, lr=h["lr"], dropout=h["dropout"],
+                 hidden1=h["hidden1"], hidden2=h["hidden2"], lambda1=h["lambda1"], lambda_fm=h["lambda_fm"], acti_type=h["acti_type"],
+                 max_feats=J)
+    train_f, train_y = _pad([ft for _, ft in g["train"]], J), np.array([y for y, _ in g["train"]])
+    test_f, test_y = _pad([ft for _, ft in g["test"]], J), np.array([y for y, _ in g["test"]])
+    res = m.fit(train_f, train_y, test_f, test_y, epochs=100, masks=iter((s["r1"], s["r2"]) for s in g["steps"]))
+    assert len(res["history"]) == len(g["epochs"]) and res["min_err_epoch"] == g["min_err_epoch"]
+    assert abs(res["min_err"] - g["min_err"]) < 5e-4
+    m.set_weights(res["best"])
+    close(m.predict(test_f), g["best_test_pred"], len(g["steps"]) * RTOL, 2e-6)
