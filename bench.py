@@ -330,7 +330,7 @@ def run_b200(args, rank, world):
     if rank == 0 and world == 1 and not args.no_cpu:
         out["cpu_baseline"] = cpu_baseline(args.workload, args.batch or WORKLOADS[args.workload][6], budget_s=12.0)
     if rank == 0:
-        print(json.dumps(out), flush=True)
+        print_json(out)
     if dist:
         from deepctr_b200 import dist as ddist
         ddist.shutdown(dist, [])
@@ -648,7 +648,7 @@ def run_reference(args, rank, world):
             break
     el = time.perf_counter() - t0
     v = done * N / el
-    print(json.dumps({
+    print_json({
         "impl": "reference", "metric": "FNN train samples/s", "value": v, "unit": "samples/s", "n_gpus": world, "steps": done,
         "warmup": W, "ms_per_step": el / done * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
@@ -657,7 +657,10 @@ def run_reference(args, rank, world):
                    "note": "CPU oracle port of the reference step on rank 0's host cores (the Py2 / Theano / TF original cannot run here)"},
         "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": "port",
                          "sample": "%d steps of batch %d (numpy float64 + OpenBLAS)" % (done, N)},
-        "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+
+
+print_json = None
 
 
 def main():
@@ -677,8 +680,14 @@ def main():
     ap.add_argument("--emb-zipf", type=float, default=1.1, help="Zipf exponent of the ids inside each field; 0 = uniform")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    # stdout carries ONE JSON line: anything libraries print there (NCCL's version banner, build messages) goes to stderr
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    global print_json
+    print_json = lambda obj: (real_stdout.write(json.dumps(obj) + "\n"), real_stdout.flush())
     if args.emb_only:
-        print(json.dumps({"emb_roofline": emb_roofline(N=args.emb_n, reps=args.emb_reps, zipf=args.emb_zipf)}))
+        print_json({"emb_roofline": emb_roofline(N=args.emb_n, reps=args.emb_reps, zipf=args.emb_zipf)})
     elif args.impl == "reference":
         run_reference(args, rank, world)
     else:

@@ -110,6 +110,7 @@ def lib():
 
 
 PROFILE = None   # bench.py sets this to a list; every call then appends (name, args, start_event, end_event)
+NVTX = os.environ.get("DCTR_NVTX", "0") == "1"      # one NVTX range per C-ABI call (K0..K7 show up by name in nsys / ncu --nvtx)
 
 
 def call(name, *args):
@@ -122,6 +123,13 @@ def call(name, *args):
         rc = getattr(lib(), name)(*args)
         e1.record(st)
         PROFILE.append((name, args, e0, e1))
+    elif NVTX:
+        import torch
+        torch.cuda.nvtx.range_push(name)
+        try:
+            rc = getattr(lib(), name)(*args)
+        finally:
+            torch.cuda.nvtx.range_pop()
     else:
         rc = getattr(lib(), name)(*args)
     if rc != 0:

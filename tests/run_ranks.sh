@@ -5,10 +5,11 @@
 secs=$1; n=$2; port=$3; log=$4; shift 4
 setsid python -m torch.distributed.run --nproc-per-node "$n" --master-addr 127.0.0.1 --master-port "$port" "$@" > "$log" 2>&1 < /dev/null &
 pid=$!
-( sleep "$secs"; echo "run_ranks: limit of ${secs}s hit, killing group $pid" >> "$log"; kill -KILL -- "-$pid" 2>/dev/null ) &
+# the watcher must not inherit the caller's stdout / stderr: its `sleep` outlives this script and would keep a pipe open
+( sleep "$secs"; echo "run_ranks: limit of ${secs}s hit, killing group $pid" >> "$log"; kill -KILL -- "-$pid" 2>/dev/null ) > /dev/null 2>&1 < /dev/null &
 watcher=$!
 wait "$pid"; rc=$?
-kill "$watcher" 2>/dev/null
+pkill -P "$watcher" 2>/dev/null; kill "$watcher" 2>/dev/null
 echo "run_ranks: rc=$rc ($*)"
 tail -n 4 "$log" | cut -c1-400
 exit $rc
