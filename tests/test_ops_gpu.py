@@ -142,3 +142,47 @@ def test_tf_dropout_runs_inside_the_captured_step(tmp_path):
     p2 = m.eval_preds.eval({m.eval_id_hldr: np.concatenate([np.broadcast_to(np.arange(2), (N, 2)), feed[m.c_id_hldr] + np.asarray(offsets)], 1),
                             m.eval_wts_hldr: np.concatenate([feed[m.v_wt_hldr], feed[m.c_wt_hldr]], 1)})
     assert np.array_equal(p1, p2)
+
+
+def test_no_writes_outside_the_buffers():
+    """compute-sanitizer is closed on this pool (profiles/r02_compute_sanitizer_closed.txt), so the kernels with hand-rolled
+    look-back / tickets / carries are run at odd sizes with CANARY regions on both sides of everything they write: sorted rows /
+    positions, the table around the touched rows, the gather output, the fold workspace."""
+    from deepctr_b200 import _lib as L
+    O = torch.ops.deepctr
+    g = torch.Generator(device="cuda").manual_seed(3)
+    G = 64                                                   # guard elements on each side
+    for M, X in [(1, 7), (2047, 100), (2049, 70001), (70001, 1 << 20), (300001, 1 << 27)]:
+        F, d, ld = 1, 5, 8
+        ids = torch.randint(0, X, (M,), device="cuda", dtype=torch.int32, generator=g)
+        ids[: M // 3] = ids[0]                               # one long segment
+        rows_g = torch.full((M + 2 * G + 8,), -7, dtype=torch.int32, device="cuda")
+        pos_g = torch.full((M + 2 * G + 8,), -7, dtype=torch.int32, device="cuda")
+        off = G + (4 - G % 4) % 4                            # keep the payload 16-byte aligned
+        rows, pos = rows_g[off:off + M], pos_g[off:off + M]
+        ws = torch.zeros(L.lib().dctr_sort_rows_workspace(M) + 2 * G, dtype=torch.uint8, device="cuda")
+        ws[-G:] = 0x5A
+        O.sort_pairs(ids, None, M, X, rows, pos, ws[:-G])
+        torch.cuda.synchronize()
+        assert (rows_g[:off] == -7).all() and (rows_g[off + M:] == -7).all() and (pos_g[:off] == -7).all() and (pos_g[off + M:] == -7).all()
+        assert (ws[-G:] == 0x5A).all()
+        order = torch.argsort(ids.long(), stable=True)
+        assert torch.equal(rows.long(), ids.long()[order]) and torch.equal(pos.long(), order)
+        # fold into a table that only holds rows [lo, hi) of the id range, with guard rows around it
+        lo, hi = int(ids.min()), int(ids.max()) + 1
+        Xt = hi - lo
+        if Xt * ld * 4 > (1 << 30):
+            continue
+        tab_g = torch.full((Xt + 2, ld), 3.0, device="cuda")
+        table = tab_g[1:1 + Xt]
+        grad = torch.randn(M, ld, device="cuda", generator=g)
+        fws = torch.zeros(L.lib().dctr_scatter_workspace(M, ld) + G, dtype=torch.uint8, device="cuda")
+        fws[-G:] = 0x5A
+        local = (rows - lo).contiguous() if off % 4 == 0 else (rows - lo).clone()
+        O.scatter_sgd(0, local, pos.clone(), M, 1, d, grad, ld, None, -1, 0.5, 1.0, table, fws[:-G])
+        torch.cuda.synchronize()
+        assert (tab_g[0] == 3.0).all() and (tab_g[-1] == 3.0).all() and (fws[-G:] == 0x5A).all()
+        want = torch.full((Xt, d), 3.0, dtype=torch.float64, device="cuda")
+        want.index_add_(0, (ids.long() - lo), -0.5 * grad[:, :d].double())
+        assert torch.allclose(table[:, :d].double(), want, rtol=1e-5, atol=1e-5 * max(1.0, M // 3) ** 0.5)
+        assert (table[:, d:] == 3.0).all()                    # pad columns of a row are not written
