@@ -48,6 +48,8 @@ SIGNATURES = {
     "dctr_out_bwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
     "dctr_col_wsum_workspace": (_z, [_i, _i]),
     "dctr_col_wsum": (_i, [_p, _i, _i, _i, _p, _p, _p, _z, _p]),
+    "dctr_col_wsum_static_max_h": (_i, []),
+    "dctr_col_wsum_static": (_i, [_p, _i, _i, _i, _p, _p, _p]),
     "dctr_vec_sum": (_i, [_p, _i, _f, _p, _p]),
     "dctr_set_launch_mode": (_i, [_i]),
     "dctr_eval_metrics_workspace": (_z, [_l]),

@@ -537,6 +537,61 @@ extern "C" int dctr_col_wsum(const float* A, int lda, int N, int H, const float*
     return check_launch("col_wsum_kernel");
 }
 
+// ---- dctr_col_wsum without a caller-provided workspace (no counterpart in the reference; added
+// for callers that cannot allocate: code under graph capture, serving loops, harnesses that forbid cudaMalloc).
+// The scratch (tickets + chunk partials of dctr_col_wsum) lives in a file-scope device array that every GPU loading the
+// library holds until exit: kStaticMaxH columns -> kRedHeader + 1184 x (kStaticMaxH + 1) x 4 bytes = 4.63 MiB.
+// In host code the array's NAME is only a host-side stand-in: its device address comes from cudaGetSymbolAddress, asked once
+// per device with that device current.  Every call shares the array and the array keeps the previous call's contents, so the
+// ticket header is cleared on the caller's stream before each launch; two calls that overlap on the GPU (different streams
+// without an ordering between them) race on it.
+namespace dctr {
+constexpr int kStaticMaxH = 1024;
+constexpr size_t kStaticRows = (size_t)(kRedMaxChunks > kNumSMs * 8 ? kRedMaxChunks : kNumSMs * 8);
+constexpr size_t kStaticScratchBytes = kRedHeader + kStaticRows * (size_t)(kStaticMaxH + 1) * sizeof(float);
+static __device__ __align__(256) unsigned char g_col_wsum_scratch[kStaticScratchBytes];
+constexpr int kStaticMaxDevices = 64;
+static void* g_col_wsum_scratch_addr[kStaticMaxDevices];      // device address per device ordinal (0 = not asked yet)
+}  // namespace dctr
+
+extern "C" int dctr_col_wsum_static_max_h(void) { return kStaticMaxH; }
+
+extern "C" int dctr_col_wsum_static(const float* A, int lda, int N, int H, const float* wv, float* out, void* stream) {
+    DCTR_REQUIRE(A && out && N > 0 && H > 0, "col_wsum_static: bad arguments");
+    if (H > kStaticMaxH) {
+        set_error("col_wsum_static: H=%d exceeds the built-in scratch (at most %d columns, %zu bytes): use dctr_col_wsum with a workspace",
+                  H, kStaticMaxH, (size_t)kStaticScratchBytes);
+        return DCTR_EINVAL;
+    }
+    if (dctr_reduce_workspace(N, H) > kStaticScratchBytes) {
+        set_error("col_wsum_static: N=%d H=%d needs %zu bytes of scratch, the built-in array holds %zu", N, H, dctr_reduce_workspace(N, H),
+                  (size_t)kStaticScratchBytes);
+        return DCTR_EINVAL;
+    }
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kStaticMaxDevices) {
+        set_error("col_wsum_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+        return DCTR_ECUDA;
+    }
+    void* scratch = __atomic_load_n(&g_col_wsum_scratch_addr[dev], __ATOMIC_ACQUIRE);
+    if (!scratch) {                     // set-up, once per device, with that device current (two racing threads get the same answer)
+        e = cudaGetSymbolAddress(&scratch, g_col_wsum_scratch);
+        if (e != cudaSuccess || !scratch) {
+            set_error("col_wsum_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return DCTR_ECUDA;
+        }
+        __atomic_store_n(&g_col_wsum_scratch_addr[dev], scratch, __ATOMIC_RELEASE);
+    }
+    // the tickets must start at zero; a previous call that failed half-way (or a racing one) may have left them otherwise
+    e = cudaMemsetAsync(scratch, 0, kRedHeader, as_stream(stream));
+    if (e != cudaSuccess) {
+        set_error("col_wsum_static: cudaMemsetAsync: %s", cudaGetErrorString(e));
+        return DCTR_ECUDA;
+    }
+    return dctr_col_wsum(A, lda, N, H, wv, out, scratch, kStaticScratchBytes, stream);
+}
+
 // lam * l2_loss(table) + lam * l2_loss(b) of FM.py:39 / LR.py:37 (tf.nn.l2_loss = sum(t^2) / 2) ADDED to out[0]: the loss the
 // reference fetches includes the regulariser.  CTA partials in double, folded in CTA order by the last CTA.
 namespace dctr {

@@ -214,6 +214,12 @@ def col_wsum(A, H, wv, out, workspace):
            _ptr(workspace, _U8, "workspace"), workspace.numel(), _st(A))
 
 
+@_op("col_wsum_static", "(Tensor A, int H, Tensor? wv, Tensor(a!) out) -> ()")
+def col_wsum_static(A, H, wv, out):
+    """dctr_col_wsum on the library's built-in scratch (H <= 1024): nothing is allocated, calls on one device must not overlap."""
+    L.call("dctr_col_wsum_static", _ptr(A, _F32, "A"), A.stride(0), A.shape[0], H, _ptr(wv, _F32, "wv"), _ptr(out, _F32, "out"), _st(A))
+
+
 @_op("vec_sum", "(Tensor v, int N, float scale, Tensor(a!) out) -> ()")
 def vec_sum(v, N, scale, out):
     L.call("dctr_vec_sum", _ptr(v, _F32, "v"), N, scale, _ptr(out, _F32, "out"), _st(v))

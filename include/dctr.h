@@ -235,6 +235,15 @@ int dctr_out_unit_train(const float* a, int lda, int N, int H, const float* w, c
 size_t dctr_col_wsum_workspace(int N, int H);
 int dctr_col_wsum(const float* A, int lda, int N, int H, const float* wv, float* out,
                   void* workspace, size_t workspace_bytes, void* stream);
+/*   dctr_col_wsum for callers that cannot allocate (code under CUDA graph capture, serving loops, harnesses that forbid
+ *   cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same result as dctr_col_wsum,
+ *   bit for bit; the scratch is a device array built into the library (4.63 MiB per GPU that loads it, held until exit), so
+ *   H <= dctr_col_wsum_static_max_h() = 1024 -- wider matrices are rejected with DCTR_EINVAL and a message.  The call itself
+ *   allocates nothing (no cudaMalloc / cudaFree / allocating library routine).  Every call shares that array: calls are
+ *   ordered by their stream; calls that overlap on the GPU (streams without an ordering between them, several host threads on
+ *   one device) race on it.  The ticket words are cleared on `stream` before each launch. */
+int dctr_col_wsum_static_max_h(void);
+int dctr_col_wsum_static(const float* A, int lda, int N, int H, const float* wv, float* out, void* stream);
 /*   out[0] = sum_n v[n]  (fixed order, one CTA) -- loss = reduce_sum(log_loss) (FM.py:36) */
 int dctr_vec_sum(const float* v, int N, float scale, float* out, void* stream);
 
