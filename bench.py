@@ -315,7 +315,7 @@ def run_b200(args, rank, world):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     out = measure_workload(args.workload, args.batch, args.steps, max(3, args.warmup), rank, world, dist, local, not args.no_profile)
-    if rank == 0 and world == 1 and not args.no_profile:
+    if rank == 0 and world == 1 and not args.no_profile and not args.no_emb:
         torch.cuda.empty_cache()
         out["emb_roofline"] = emb_roofline()
         out["emb_roofline_uniform_ids"] = emb_roofline(zipf=0.0)
@@ -672,6 +672,7 @@ def main():
     ap.add_argument("--workload", default="fnn_ipinyou", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--no-emb", action="store_true", help="skip the embedding-kernel bandwidth sweeps")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the secondary block (BASELINE configs 4 and 5 at the same GPU count)")
     ap.add_argument("--emb-only", action="store_true", help="only run the embedding-kernel roofline sweep")

@@ -62,6 +62,12 @@ SIGNATURES = {
     "dctr_mlp2_workspace": (_z, [_i, _i, _i, _i]),
     "dctr_mlp2_train": (_i, [_i, _i, _i, _i, _p, _i, _p, _i, _i, _p, _i, _p, _i, _p, _i, _p, _i, _p, _i, _p, _i, _p, _p, _p, _p, _p, _f, _f,
                              _p, _i, _p, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _i, _f, _f, _p, _z, _p]),
+    "dctr_mlp2tc_supported": (_i, [_i, _i, _i]),
+    "dctr_mlp2tc_workspace": (_z, [_i, _i]),
+    "dctr_mlp2tc_packed_bytes": (_z, [_i, _i, _i]),
+    "dctr_mlp2tc_pack": (_i, [_i, _i, _i, _p, _i, _p, _i, _p, _z, _p]),
+    "dctr_mlp2tc_train": (_i, [_i, _i, _i, _i, _p, _i, _p, _i, _i, _p, _p, _i, _p, _i, _p, _i, _p, _i, _p, _p, _p, _f, _f,
+                               _p, _i, _p, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _i, _f, _f, _p, _z, _p]),
     "dctr_mlp2_wgrad": (_i, [_i, _i, _i, _i, _p, _i, _p, _i, _p, _p, _i, _p, _i, _p, _p, _i, _p, _p, _p, _p, _p, _i, _f, _f, _p, _z, _p]),
     "dctr_dense_sgd": (_i, [_p, _p, _l, _f, _f, _p]),
     "dctr_adam_tick": (_i, [_p, _f, _f, _f, _p]),

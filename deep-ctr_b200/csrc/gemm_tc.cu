@@ -17,8 +17,7 @@
 //     warp 8     allocates TMEM; one lane issues 4 k-steps x 3 tcgen05.mma (A in TMEM, B by descriptor) per stage;
 //                tcgen05.commit frees the shared-memory stage for the TMA lane and the TMEM A slot for the converters,
 //                and finally signals the epilogue.
-#include <cuda.h>
-#include "common.cuh"
+#include "tc_common.cuh"
 
 namespace dctr {
 namespace tc {
@@ -29,106 +28,6 @@ constexpr int kConverters = 256;          // 8 warps (16 measured 4% slower: the
 constexpr int kThreads = kConverters + 64;
 constexpr int kMmaWarp = kConverters / 32, kTmaWarp = kMmaWarp + 1;
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-// 2-D tiled TMA load global -> shared, completion counted in bytes on the mbarrier
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
-}
-// D[tmem] (+)= A[smem desc] * B[smem desc], fp32 operands read as tf32
-__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-// same with A read from tensor memory (lane = row, one 32-bit column per k)
-__device__ __forceinline__ void mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-// 8 consecutive columns of this thread's TMEM lane
-__device__ __forceinline__ void tmem_st8(uint32_t taddr, const float (&v)[8]) {
-    const uint32_t* r = reinterpret_cast<const uint32_t*>(v);
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
-                 ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
-}
-__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-// arrives on the mbarrier once every tcgen05.mma issued so far by this thread has completed
-__device__ __forceinline__ void mma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
-    uint32_t* r = reinterpret_cast<uint32_t*>(v);
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr)
-        : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// K-major SWIZZLE_128B shared-memory descriptor (cute::UMMA::SmemDescriptor): start address >> 4 in bits [0,14),
-// stride byte offset (8 rows x 128 B = 1024 B) >> 4 in bits [32,46), version 1 in bits [46,48), layout type 2
-// (SWIZZLE_128B) in bits [61,64); the tile base is 1024-byte aligned so base_offset = 0.
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
-    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
-}
-// MN-major fp32 operands have exactly one legal layout, SWIZZLE_128B_BASE32B (layout type 1; TMA's
-// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B): atoms of [4 k x 32 mn] (512 B, 32-byte chunks XOR k%4).  The next 4 k-rows follow
-// at +512 B (stride byte offset), the next 32 mn at +4096 B (leading byte offset = one [32 k x 32 mn] TMA box).
-__device__ __forceinline__ uint64_t make_desc_mn(uint32_t saddr) {
-    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(4096 >> 4) << 16) | ((uint64_t)(512 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)1 << 61);
-}
-// byte offset of element (row, k) of a [rows x 32 fp32] tile in that layout (16-byte chunk index XOR row%8)
-__device__ __forceinline__ uint32_t swz(int row, int k) {
-    return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((((k >> 2) ^ (row & 7)) << 4)) + (k & 3) * 4);
-}
-// round-to-nearest (ties away, like cvt.rna.tf32.f32) by integer arithmetic on the bit pattern: the conversion unit
-// runs cvt at 1/8 rate and was the bottleneck of the split (measured with %globaltimer: ~1 us per k-block)
-__device__ __forceinline__ float rna_tf32(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u); }
-__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
-    hi = rna_tf32(x);
-    lo = rna_tf32(x - hi);
-}
 
 
 struct TcParams {
@@ -341,7 +240,7 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
     using S = TcSmem<BN, NS>;
     using T = TcTmem<BN>;
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);     // pointer arithmetic keeps the shared address space (LDS / STS, not generic LD / ST)
     uint64_t* raw_full = reinterpret_cast<uint64_t*>(smem + NS * S::kStage);
     uint64_t* conv_full = raw_full + NS;
     uint64_t* empty = conv_full + NS;
@@ -483,40 +382,6 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
     if (warp == kMmaWarp) tmem_dealloc(tmem_base, T::kCols);
 }
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_fn() {
-    static EncodeTiledFn fn = nullptr;
-    if (!fn) {
-        void* ptr = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(ptr);
-    }
-    return fn;
-}
-
-// Tensor map of one GEMM operand, an fp32 matrix with `rows` logical MN rows and `K` logical k columns.
-//   kcontig: element (r, k) at base[r*ld + k] -> dims {K, rows}, box {32 k, box_rows}      (K-major UMMA tile)
-//   else:    element (r, k) at base[k*ld + r] -> dims {rows, K}, box {32 mn, 32 k}         (MN-major UMMA atoms)
-// Out-of-range parts of a box are zero-filled by the TMA unit, which is what pads the M / N / K edges.
-static int make_map(CUtensorMap* map, const float* base, int ld, int rows, int K, bool kcontig, int box_rows, bool plain_mn = false) {
-    EncodeTiledFn fn = encode_fn();
-    if (!fn) { set_error("gemm_tc: cuTensorMapEncodeTiled is not available from this driver"); return DCTR_ECUDA; }
-    cuuint64_t dims[2] = {(cuuint64_t)(kcontig ? K : rows), (cuuint64_t)(kcontig ? rows : K)};
-    cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
-    cuuint32_t box[2] = {32u, (cuuint32_t)(kcontig ? box_rows : 32)};
-    cuuint32_t estr[2] = {1u, 1u};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE,
-                    kcontig ? CU_TENSOR_MAP_SWIZZLE_128B : (plain_mn ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B),
-                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) { set_error("gemm_tc: cuTensorMapEncodeTiled failed (%d) rows=%d K=%d ld=%d", (int)r, rows, K, ld); return DCTR_ECUDA; }
-    return DCTR_OK;
-}
 
 template <int BN, int NS>
 static int launch_tc(int layout, const TcParams& p, dim3 grid, cudaStream_t st) {

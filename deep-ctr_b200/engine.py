@@ -119,18 +119,34 @@ class StepEngine:
         # gradients (+ SGD) as one cluster kernel (csrc/mlp2.cu) instead of ~14 per-layer launches.  Opt-in (DCTR_MLP2=on):
         # measured at N = 4096, 177-300-100-1 it LOSES to the per-layer tcgen05 chain (0.264 vs 0.158 ms per step,
         # profiles/r02_bench_fnn_ipinyou_mlp2_v3.json) -- fp32 SIMT cannot match the tensor cores even at these sizes.
+        # DCTR_MLP2=tc: the same fusion on the tensor cores (csrc/mlp2tc.cu: forward + data gradients of a 128-sample tile chained
+        # through tcgen05 with the activations handed from epilogue to A tile in shared memory); weight gradients by
+        # DCTR_MLP2_WGRAD = gemm (split-K TN GEMMs, one side stream per layer) | cluster (the FFMA cluster kernel of mlp2.cu).
         mode = os.environ.get("DCTR_MLP2", "off")
         ok = self.nl == 3 and bool(L.lib().dctr_mlp2_supported(self.widths[0], self.widths[1], self.widths[2]))
-        self.fused_mlp2 = ok and mode == "on"
+        ok_tc = self.nl == 3 and bool(L.lib().dctr_mlp2tc_supported(self.widths[0], self.widths[1], self.widths[2]))
+        self.mlp2_tc = ok_tc and mode == "tc"
+        self.mlp2_wgrad_gemm = self.mlp2_tc and os.environ.get("DCTR_MLP2_WGRAD", "gemm") == "gemm"
+        self.fused_mlp2 = (ok and mode == "on") or (self.mlp2_tc and (ok or self.mlp2_wgrad_gemm))
+        if self.mlp2_tc and not self.fused_mlp2:
+            self.mlp2_tc = False
         self._mlp2_sgd = False                  # this step's fused kernels apply plain SGD to the MLP themselves
         self._mlp2_cfg = None                   # (lr, decay_hidden, decay_out, train_bias) when they do
         self._mlp2_tr_event = None
-        if self.fused_mlp2:
+        if self.fused_mlp2 and not self.mlp2_wgrad_gemm:
             self.mlp2_ws = torch.zeros(L.lib().dctr_mlp2_workspace(N, self.widths[0], self.widths[1], self.widths[2]), dtype=torch.uint8, device=self.dev)
             # transposed copies of the two hidden-layer weights, rebuilt on the second stream at the start of every step: the
             # backward GEMMs then stream row-major [k][column] slabs like the forward ones
             self.W1t = torch.zeros(self.widths[1], self.ldi[0], **f32)
             self.W2t = torch.zeros(self.widths[2], self.ldi[1], **f32)
+        if self.mlp2_tc:
+            self.mlp2tc_ws = torch.zeros(L.lib().dctr_mlp2tc_workspace(N, self.widths[2]), dtype=torch.uint8, device=self.dev)
+            # the hidden-layer weights as tf32 hi / lo tiles in the kernel's shared-memory layout and consumption order, rebuilt on
+            # the second stream at the start of every step
+            self.W12_packed = torch.zeros(L.lib().dctr_mlp2tc_packed_bytes(*self.widths), dtype=torch.uint8, device=self.dev)
+            self.side3 = torch.cuda.Stream(device=self.dev)
+            self.col_ws3 = torch.zeros_like(self.col_ws)
+            self.splitk_ws3 = torch.zeros_like(self.splitk_ws)
         self.skip_row = None        # set when the weights are 0 / 1 and 0 only marks this (all-zero pad) row: no weight gather in the fold
 
     # ---- the embedding front end (overridden by BagEngine) -------------------------------------------
@@ -251,6 +267,13 @@ class StepEngine:
             self._mlp2_tr_event = None
         else:
             self._mlp2_transpose()
+        if self.mlp2_tc:
+            O.mlp2tc_train(D0, H1, H2, self.ins[0], self.masks[0], L.ACT[self.act_of(0)], self.W12_packed, self.b(0), L.ACT[self.act_of(1)],
+                           self.masks[1], self.b(1), L.ACT[self.act_of(2)], self.masks[2], self.W(2).view(-1),
+                           self.b(2), self.y, float(gscale), float(gscale), self.ins[1], self.dbuf[0], self.dbuf[1], self.dz0, self.logit,
+                           self.pred, self.loss_n, self.dlogit, self.loss, self.W(2, self.grads).view(-1), self.b(2, self.grads), sgd,
+                           float(lr), float(dout), self.mlp2tc_ws)
+            return
         O.mlp2_train(D0, H1, H2, self.ins[0], self.masks[0], L.ACT[self.act_of(0)], self.W(0), self.b(0), L.ACT[self.act_of(1)],
                      self.masks[1], self.W(1), self.b(1), L.ACT[self.act_of(2)], self.masks[2], self.W1t, self.W2t, self.W(2).view(-1),
                      self.b(2), self.y, float(gscale), float(gscale), self.ins[1], self.dbuf[0], self.dbuf[1], self.dz0, self.logit,
@@ -259,6 +282,9 @@ class StepEngine:
 
     def _mlp2_transpose(self):
         D0, H1, H2 = self.widths
+        if self.mlp2_tc:
+            O.mlp2tc_pack(D0, H1, H2, self.W(0), self.W(1), self.W12_packed)
+            return
         O.mlp2_transpose(D0, H1, H2, self.W(0), self.W(1), self.W1t, self.W2t)
 
     def _mlp2_wgrad(self):
@@ -269,6 +295,25 @@ class StepEngine:
         lr, dhid, _ = self._mlp2_cfg[:3] if sgd else (0.0, 1.0, 1.0)
         ov = self.overlap_wgrad
         main = torch.cuda.current_stream(self.dev)
+        if self.mlp2_wgrad_gemm:
+            # dz1 = dbuf[0] pairs with ins[0], dz2 = dbuf[1] with ins[1]: split-K TN GEMM, fold, bias column sums -- the two layers are
+            # independent of each other, so each gets its own side stream (both start when the fused kernel ends)
+            for l, side, cws, sws in ((0, self.side2, self.col_ws2, self.splitk_ws), (1, self.side3, self.col_ws3, self.splitk_ws3)):
+                if ov:
+                    side.wait_stream(main)
+                with torch.cuda.stream(side if ov else main):
+                    K, Hl, s_ = self.widths[l], self.widths[l + 1], self.splits[l]
+                    dpre, gW = self.dbuf[l], self.W(l, self.grads)
+                    if s_ > 1:
+                        slabs = sws[:s_ * K * self.ldw[l]].view(s_, K, self.ldw[l])
+                        self._gemm(L.GEMM_TN, K, Hl, self.N, self.ins[l], dpre, slabs, L.EPI_NONE, 0, None, None, None, s_)
+                        O.splitk_reduce(slabs, s_, K, Hl, self.ldw[l], gW)
+                    else:
+                        self._gemm(L.GEMM_TN, K, Hl, self.N, self.ins[l], dpre, gW, L.EPI_NONE, 0, None, None, None, 1)
+                    O.col_wsum(dpre, Hl, None, self.b(l, self.grads), cws if ov else self.col_ws)
+            if ov:
+                self._wgrad_pending = True
+            return
         if ov:
             self.side2.wait_stream(main)
         with torch.cuda.stream(self.side2 if ov else main):
@@ -404,6 +449,8 @@ class StepEngine:
         """self.grads is complete on the current stream after this (weight gradients run on a side stream)."""
         if self._wgrad_pending:
             torch.cuda.current_stream(self.dev).wait_stream(self.side2)
+            if self.mlp2_wgrad_gemm:
+                torch.cuda.current_stream(self.dev).wait_stream(self.side3)
             self._wgrad_pending = False
 
     def dense_update(self, lr, last_decay=1.0, mlp_decay=1.0):
@@ -451,7 +498,7 @@ class StepEngine:
             self.sort_ids()
         # plain SGD on one GPU: the fused MLP kernels apply the update themselves (the multi-GPU steps call forward / backward
         # directly and all-reduce self.grads first, Adam / FTRL need the gradients)
-        plain = self.fused_mlp2 and not self.dense_optimizer
+        plain = self.fused_mlp2 and not self.dense_optimizer and not self.mlp2_wgrad_gemm
         if self.fused_mlp2 and self.overlap_wgrad:     # W^T for the backward GEMMs: off the critical path, next to the gather
             self.side2.wait_stream(cur)
             with torch.cuda.stream(self.side2):

@@ -296,6 +296,33 @@ def mlp2_wgrad(D0, H1, H2, x, a1, dz1, dz2, W1, b1, W2, b2, gW1, gb1, gW2, gb2, 
            _ptr(gb2, _F32, "gb2"), int(sgd), lr, decay, _ptr(workspace, _U8, "workspace", 16), workspace.numel(), _st(x))
 
 
+# ---- the fused two-hidden-layer step on the tensor cores (csrc/mlp2tc.cu) ------------------------------------------------------------
+@_op("mlp2tc_pack", "(int D0, int H1, int H2, Tensor W1, Tensor W2, Tensor(a!) packed) -> ()")
+def mlp2tc_pack(D0, H1, H2, W1, W2, packed):
+    L.call("dctr_mlp2tc_pack", D0, H1, H2, _ptr(W1, _F32, "W1"), W1.stride(0), _ptr(W2, _F32, "W2"), W2.stride(0),
+           _ptr(packed, _U8, "packed", 128), packed.numel(), _st(W1))
+
+
+@_op("mlp2tc_train", "(int D0, int H1, int H2, Tensor(a!) x, Tensor? m0, int act0, Tensor packed, Tensor b1, int act1, Tensor? m1, "
+     "Tensor b2, int act2, Tensor? m2, Tensor(b!) w3, Tensor(c!) b3, Tensor y, float gscale, float loss_scale, "
+     "Tensor(d!) a1, Tensor(e!) dz1, Tensor(f!) dz2, Tensor(g!) dz0, Tensor(h!) logit, Tensor(i!) pred, Tensor(j!) loss_n, Tensor(k!) dlogit, "
+     "Tensor(l!) loss_sum, Tensor(m!) gw3, Tensor(n!) gb3, bool sgd, float lr, float decay_out, Tensor(o!) workspace) -> ()")
+def mlp2tc_train(D0, H1, H2, x, m0, act0, packed, b1, act1, m1, b2, act2, m2, w3, b3, y, gscale, loss_scale, a1, dz1, dz2, dz0,
+                 logit, pred, loss_n, dlogit, loss_sum, gw3, gb3, sgd, lr, decay_out, workspace):
+    if dz1.stride(0) != dz2.stride(0):
+        raise ValueError("mlp2tc_train: dz1 and dz2 must share their leading dimension")
+    if packed.numel() < L.lib().dctr_mlp2tc_packed_bytes(D0, H1, H2):
+        raise ValueError("mlp2tc_train: packed weight buffer is smaller than dctr_mlp2tc_packed_bytes")
+    L.call("dctr_mlp2tc_train", x.shape[0], D0, H1, H2, _ptr(x, _F32, "x", 16), x.stride(0), _ptr(m0, _F32, "m0", 16), _ld(m0, "m0"), act0,
+           _ptr(packed, _U8, "packed", 128), _ptr(b1, _F32, "b1"), act1, _ptr(m1, _F32, "m1", 16), _ld(m1, "m1"),
+           _ptr(b2, _F32, "b2"), act2, _ptr(m2, _F32, "m2", 16), _ld(m2, "m2"),
+           _ptr(w3, _F32, "w3"), _ptr(b3, _F32, "b3"), _ptr(y, _F32, "y"), gscale, loss_scale,
+           _ptr(a1, _F32, "a1", 16), a1.stride(0), _ptr(dz1, _F32, "dz1", 16), _ptr(dz2, _F32, "dz2", 16), dz1.stride(0), _ptr(dz0, _F32, "dz0", 16),
+           _ptr(logit, _F32, "logit"), _ptr(pred, _F32, "pred"), _ptr(loss_n, _F32, "loss_n"), _ptr(dlogit, _F32, "dlogit"),
+           _ptr(loss_sum, _F32, "loss_sum"), _ptr(gw3, _F32, "gw3"), _ptr(gb3, _F32, "gb3"), int(sgd), lr, decay_out,
+           _ptr(workspace, _U8, "workspace", 16), workspace.numel(), _st(x))
+
+
 # ---- eval metrics and device-side text ingestion -----------------------------------------------------------------------------------
 @_op("eval_metrics", "(Tensor pred, Tensor y, Tensor(a!) out, Tensor(b!) workspace) -> ()")
 def eval_metrics(pred, y, out, workspace):

@@ -314,6 +314,29 @@ int dctr_mlp2_wgrad(int N, int D0, int H1, int H2, const float* x, int ld0, cons
                     float* b2, float* gW1, float* gb1, float* gW2, float* gb2, int sgd, float lr, float decay,
                     void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- the same fused step on the tensor cores (csrc/mlp2tc.cu): one CTA per 128 samples chains x -> a1 -> a2 -> output unit ->
+ * dz2 -> dz1 -> dz0 through tcgen05 (3xTF32, accumulators in tensor memory, activations handed from an epilogue to the next
+ * phase's A tiles in shared memory).  Same contract and outputs as dctr_mlp2_train, except that the hidden-layer weights are
+ * read from `packed`: dctr_mlp2tc_pack of W1 [D0, ldw1] and W2 [H1, ldw2] (split into tf32 hi / lo and laid out as the swizzled
+ * shared-memory tiles of the four GEMM phases in consumption order; dctr_mlp2tc_packed_bytes bytes, 128-byte aligned; to be
+ * redone whenever W1 / W2 change) -- every weight tile is one contiguous bulk copy, no transposed copies, no tensor maps.
+ * tanh / sigmoid are evaluated through ex2.approx / rcp.approx (absolute error < 3e-7).  The weight gradients are the caller's
+ * (dctr_mlp2_wgrad or the TN GEMMs).  Limits: dctr_mlp2tc_supported (D0 <= 192, H1 <= 320, H2 <= 128).
+ * workspace: dctr_mlp2tc_workspace bytes, zero-filled once.  DCTR_M2TC_TIMING=1 prints a %globaltimer timeline of CTA 0. */
+int dctr_mlp2tc_supported(int D0, int H1, int H2);
+size_t dctr_mlp2tc_workspace(int N, int H2);
+size_t dctr_mlp2tc_packed_bytes(int D0, int H1, int H2);
+int dctr_mlp2tc_pack(int D0, int H1, int H2, const float* W1, int ldw1, const float* W2, int ldw2, void* packed,
+                     size_t packed_bytes, void* stream);
+int dctr_mlp2tc_train(int N, int D0, int H1, int H2, float* x, int ld0, const float* m0, int ldm0, int act0,
+                      const void* packed, const float* b1, int act1, const float* m1, int ldm1,
+                      const float* b2, int act2, const float* m2, int ldm2,
+                      float* w3, float* b3, const float* y, float gscale, float loss_scale,
+                      float* a1, int ld1, float* dz1, float* dz2, int ldd, float* dz0,
+                      float* logit, float* pred, float* loss_n, float* dlogit, float* loss_sum,
+                      float* gw3, float* gb3, int sgd, float lr, float decay_out,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- embedding bag: the first layer of the SNN models (get_fi_h1_y, SNN_DAE.py:234-260, SNN_RBM.py:238-262)
  *   out[n, c] = act( b0[c] + sum_f wts[n,f] * table[ids[n,f], c] ),  c < H;  columns H..ldo-1 are written as 0
  * table: float32 [X, ld] (ld % 4 == 0, ld >= H; the reference's ww0 is 133465 x 200), b0: [H] or NULL, act: DCTR_ACT_*

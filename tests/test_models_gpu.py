@@ -18,12 +18,12 @@ def _need_cuda():
         pytest.skip("no CUDA device")
 
 
-@pytest.fixture(autouse=True, params=["simt", "tc", "mlp2"])
+@pytest.fixture(autouse=True, params=["simt", "tc", "mlp2", "mlp2tc"])
 def gemm_path(request, monkeypatch):
     """Every model-level parity test runs on the per-layer GEMM paths (fp32 FFMA, tcgen05 3xTF32) and with the fused
     two-hidden-layer kernels of csrc/mlp2.cu (which only apply to models with two hidden layers)."""
-    monkeypatch.setenv("DCTR_GEMM", "simt" if request.param == "mlp2" else request.param)
-    monkeypatch.setenv("DCTR_MLP2", "on" if request.param == "mlp2" else "off")
+    monkeypatch.setenv("DCTR_GEMM", {"mlp2": "simt", "mlp2tc": "tc"}.get(request.param, request.param))
+    monkeypatch.setenv("DCTR_MLP2", {"mlp2": "on", "mlp2tc": "tc"}.get(request.param, "off"))
     return request.param
 
 

@@ -26,10 +26,10 @@ def gold():
         return pickle.load(f)
 
 
-@pytest.fixture(params=["simt", "tc", "mlp2"])
+@pytest.fixture(params=["simt", "tc", "mlp2", "mlp2tc"])
 def gemm_path(request, monkeypatch):
-    monkeypatch.setenv("DCTR_GEMM", "simt" if request.param == "mlp2" else request.param)
-    monkeypatch.setenv("DCTR_MLP2", "on" if request.param == "mlp2" else "off")
+    monkeypatch.setenv("DCTR_GEMM", {"mlp2": "simt", "mlp2tc": "tc"}.get(request.param, request.param))
+    monkeypatch.setenv("DCTR_MLP2", {"mlp2": "on", "mlp2tc": "tc"}.get(request.param, "off"))
     return request.param
 
 
