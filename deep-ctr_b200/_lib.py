@@ -41,6 +41,7 @@ SIGNATURES = {
     "dctr_decay_sweep": (_i, [_p, _l, _i, _f, _p, _l, _p]),
     "dctr_gemm": (_i, [_i, _i, _i, _i, _p, _i, _p, _i, _p, _i, _i, _i, _p, _p, _i, _p, _i, _i, _p]),
     "dctr_splitk_reduce": (_i, [_p, _i, _i, _i, _i, _p, _i, _p]),
+    "dctr_splitk_reduce_sgd": (_i, [_p, _i, _i, _i, _i, _p, _i, _f, _f, _p]),
     "dctr_gemm_tc": (_i, [_i, _i, _i, _i, _p, _i, _p, _i, _p, _i, _i, _i, _p, _p, _i, _p, _i, _i, _p]),
     "dctr_reduce_workspace": (_z, [_i, _i]),
     "dctr_out_xent_fwd": (_i, [_p, _i, _i, _i, _p, _p, _p, _f, _p, _p, _p, _p, _f, _p, _p, _z, _p]),
@@ -48,6 +49,7 @@ SIGNATURES = {
     "dctr_out_bwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
     "dctr_col_wsum_workspace": (_z, [_i, _i]),
     "dctr_col_wsum": (_i, [_p, _i, _i, _i, _p, _p, _p, _z, _p]),
+    "dctr_col_wsum_sgd": (_i, [_p, _i, _i, _i, _p, _p, _f, _f, _p, _z, _p]),
     "dctr_col_wsum_static_max_h": (_i, []),
     "dctr_col_wsum_static": (_i, [_p, _i, _i, _i, _p, _p, _p]),
     "dctr_vec_sum": (_i, [_p, _i, _f, _p, _p]),

@@ -164,15 +164,18 @@ gemm_kernel(GemmParams p) {
     }
 }
 
+// SGD: out is the weight matrix itself, out = out * decay - lr * (sum of the slabs) -- the gradient never goes to memory
+template <bool SGD>
 __global__ void splitk_reduce_kernel(const float* __restrict__ part, int splits, int M, int N, int ldc,
-                                     float* __restrict__ out, int ldo) {
+                                     float* __restrict__ out, int ldo, float lr, float decay) {
     pdl_sync();
     const int64_t total = (int64_t)M * N;
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         const int m = (int)(t / N), n = (int)(t - (int64_t)m * N);
         float acc = 0.f;
         for (int z = 0; z < splits; ++z) acc += part[((int64_t)z * M + m) * ldc + n];
-        out[(int64_t)m * ldo + n] = acc;
+        float* o = out + (int64_t)m * ldo + n;
+        *o = SGD ? fmaf(*o, decay, -lr * acc) : acc;
     }
 }
 
@@ -224,6 +227,16 @@ extern "C" int dctr_splitk_reduce(const float* partials, int splits, int M, int 
     if (M == 0 || N == 0) return DCTR_OK;
     int blocks = ceil_div((int64_t)M * N, 256);
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    launch_k(splitk_reduce_kernel, blocks, 256, 0, as_stream(stream), partials, splits, M, N, ldc, out, ldo);
+    launch_k(splitk_reduce_kernel<false>, blocks, 256, 0, as_stream(stream), partials, splits, M, N, ldc, out, ldo, 0.f, 1.f);
+    return check_launch("splitk_reduce_kernel");
+}
+
+extern "C" int dctr_splitk_reduce_sgd(const float* partials, int splits, int M, int N, int ldc, float* W, int ldw, float lr,
+                                      float decay, void* stream) {
+    DCTR_REQUIRE(partials && W && splits >= 1 && M >= 0 && N >= 0, "splitk_reduce_sgd: bad arguments");
+    if (M == 0 || N == 0) return DCTR_OK;
+    int blocks = ceil_div((int64_t)M * N, 256);
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    launch_k(splitk_reduce_kernel<true>, blocks, 256, 0, as_stream(stream), partials, splits, M, N, ldc, W, ldw, lr, decay);
     return check_launch("splitk_reduce_kernel");
 }

@@ -36,7 +36,17 @@ namespace dctr {
 namespace m2tc {
 using namespace tc;
 
-constexpr int kRows = 128;
+constexpr int kRows = 128;                 // rows of an MMA tile (UMMA M)
+// Samples per CTA.  The epilogues, not the MMAs, bound this kernel (~30 instructions per activation element against ~45 ns per
+// MMA), and 4096 / 128 = 32 CTAs leave 116 SMs idle: a CTA therefore takes only 16 * 4 = 64 samples -- rows 0-15 of each
+// 32-lane TMEM quadrant, so that every worker warp (which can only reach the TMEM lanes of quadrant warp % 4) keeps a
+// share -- and issues the same M = 128 MMAs over half-empty tiles (rows 16-31 of a quadrant stay zero).
+#ifndef DCTR_M2TC_QROWS
+#define DCTR_M2TC_QROWS 16
+#endif
+constexpr int kQRows = DCTR_M2TC_QROWS;     // valid rows per quadrant: 16 or 32
+constexpr int kTileRows = 4 * kQRows;
+static_assert(kQRows == 8 || kQRows == 16 || kQRows == 32, "rows per quadrant");
 constexpr int kWorkers = 384;             // 12 warps = 3 groups of 4 row quadrants: three worker warps per scheduler hide each other's latencies
 constexpr int kGroups = kWorkers / 128;   // == kASlots: inside a phase a group always fills the same slot, so a writer is never more than
                                            // one mbarrier phase ahead of the MMAs (a parity wait cannot tell phases two apart)
@@ -80,7 +90,6 @@ struct Args {
     int sgd_out; float lr, decay_out;
     float* partial; unsigned* ticket;       // [tiles][H2 + 2] CTA partials of (d w3 | d b3 | loss), ticket word
     const uint8_t* packed;                  // weight tiles in consumption order (mlp2tc_pack_kernel)
-    int dbg;                                // diagnostic knobs for the F1 epilogue (DCTR_M2TC_DBG): 1 no global store, 2 no activation, 4 no slot write
     unsigned long long* timing;             // diagnostic (DCTR_M2TC_TIMING=1): %globaltimer stamps of CTA 0, else NULL
     Phase ph[4];
 };
@@ -134,6 +143,7 @@ __device__ __forceinline__ uint32_t off_rm(int quad, int t, int lane) {
     return (uint32_t)((R >> 3) * 1024 + (R & 7) * 128 + ((j ^ (R & 7)) << 4));
 }
 __device__ __forceinline__ void park_rows(uint8_t* tile, int quad, int lane, const float (&v)[32]) {
+    if (lane >= kQRows) return;                // rows past the quadrant's share stay zero
 #pragma unroll
     for (int i = 0; i < 8; ++i)
         *reinterpret_cast<float4*>(tile + off_lane(quad, lane, i)) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
@@ -194,7 +204,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // global rows row0 + rm_row(t), columns col .. col+3 -> plane (same swizzled positions this thread reads back); zero fill outside
 __device__ __forceinline__ void rm_fetch(uint8_t* plane, const float* base, int ld, int64_t row0, int col, int N, int lim, int quad, int lane) {
 #pragma unroll 4
-    for (int t = 0; t < 8; ++t) {
+    for (int t = 0; t < kQRows / 4; ++t) {
         const int64_t grow = row0 + rm_row(t, lane);
         const bool ok = grow < N && col < lim;
         cp_async16(plane + off_rm(quad, t, lane), ok ? base + grow * ld + col : base, ok);
@@ -213,7 +223,7 @@ __device__ __forceinline__ void sts128(uint32_t addr, float4 v) {
 __device__ __noinline__ void rm_backward(uint32_t tile, int quad, int lane, int64_t row0, int col, int N, int act, const float* m, int ldm,
                                          uint32_t srow, int mlim, int H, float* out, int ldo, int olim, int to_slot) {
 #pragma unroll 2
-    for (int t = 0; t < 8; ++t) {
+    for (int t = 0; t < kQRows / 4; ++t) {
         const uint32_t off = off_rm(quad, t, lane);
         const int64_t grow = row0 + rm_row(t, lane);
         const bool ok = grow < N;
@@ -257,6 +267,10 @@ mlp2tc_train_kernel(const Args a) {
         fence_mbar_init();
     }
     if (warp == kMmaWarp) tmem_alloc(tmem_slot, 512);
+    if (kQRows < 32) {                          // the unused rows of every A tile are zeros for the whole kernel
+        for (int i = tid; i < kASlots * kASlot / 16; i += kThreads) reinterpret_cast<float4*>(aring)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        fence_proxy_async();
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -266,10 +280,10 @@ mlp2tc_train_kernel(const Args a) {
     if (warp < kMmaWarp) {
         // =================================================== workers ===================================================
         const int quad = warp & 3, grp = warp >> 2, j4 = (lane & 7) * 4;
-        const int64_t row0 = (int64_t)blockIdx.x * kRows + quad * 32;       // first row of this warp's quadrant
+        const int64_t row0 = (int64_t)blockIdx.x * kTileRows + quad * kQRows;     // first sample of this warp's quadrant
         const int r = quad * 32 + lane;                                     // row layout: this lane's row of the tile
-        const int64_t row = (int64_t)blockIdx.x * kRows + r;
-        const bool row_ok = row < a.N;
+        const int64_t row = row0 + lane;
+        const bool row_ok = lane < kQRows && row < a.N;
         const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
         float* sdot = scratch;                  // [3][128] partial logits of the warp groups (+ 128 unused)
         float* colpart = scratch + 512;         // [4][128] per-quadrant column sums of dlogit * a2
@@ -311,7 +325,7 @@ mlp2tc_train_kernel(const Args a) {
             rm_fetch(sl, a.x, a.ld0, row0, col, a.N, a.ld0, quad, lane);
             cp_async_wait_all();
 #pragma unroll 2
-            for (int t = 0; t < 8; ++t) {
+            for (int t = 0; t < kQRows / 4; ++t) {
                 const uint32_t off = off_rm(quad, t, lane);
                 const int64_t grow = row0 + rm_row(t, lane);
                 const bool ok = grow < a.N;
@@ -334,32 +348,23 @@ mlp2tc_train_kernel(const Args a) {
         for (int c = grp; c < nc1; c += kGroups) {
             const int g = gbase + c, slot = g % kASlots, col = 32 * c + j4;
             uint8_t* sl = aring + slot * kASlot;
-            const bool st2 = stamp && c == 4;
-            if (st2) a.timing[16] = global_ns();
             tmem_ld32(tlane + a.ph[0].acc_col + 32 * c, v);
-            if (st2) a.timing[17] = global_ns() + (__float_as_uint(v[0]) & 1u);
             mbar_wait(a_empty + slot, ((g / kASlots) & 1) ^ 1);
-            if (st2) a.timing[18] = global_ns();
             park_rows(sl, quad, lane, v);
             __syncwarp();
-            if (st2) a.timing[19] = global_ns();
             const float4 bias = *reinterpret_cast<const float4*>(sb1 + col);
 #pragma unroll 2
-            for (int t = 0; t < 8; ++t) {
+            for (int t = 0; t < kQRows / 4; ++t) {
                 const uint32_t off = off_rm(quad, t, lane);
                 const int64_t grow = row0 + rm_row(t, lane);
                 const bool ok = grow < a.N;
-                float4 u = add4(*reinterpret_cast<const float4*>(sl + off), bias);
-                if (!(a.dbg & 2)) u = act4(a.act1, u);
+                float4 u = act4(a.act1, add4(*reinterpret_cast<const float4*>(sl + off), bias));
                 if (a.m1) u = mul4(u, mask4(a.m1, a.ldm1, sm1, grow, col, ok && col < lim1));
                 u = clip4(u, col, a.H1, ok);
-                if (ok && col < a.ld1 && !(a.dbg & 1)) *reinterpret_cast<float4*>(a.a1 + grow * a.ld1 + col) = u;
-                if (!(a.dbg & 4)) put_split(sl, off, u);
-                if (st2 && t == 1) a.timing[20] = global_ns();
+                if (ok && col < a.ld1) *reinterpret_cast<float4*>(a.a1 + grow * a.ld1 + col) = u;
+                put_split(sl, off, u);
             }
-            if (st2) a.timing[21] = global_ns();
             publish(a_full + slot);
-            if (st2) a.timing[22] = global_ns();
         }
         gbase += nc1;
         M2TC_STAMP(3);
@@ -424,7 +429,7 @@ mlp2tc_train_kernel(const Args a) {
             const float4 bias = *reinterpret_cast<const float4*>(sb2 + col), wq = *reinterpret_cast<const float4*>(sw3 + col);
             float4 cs = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 2
-            for (int t = 0; t < 8; ++t) {
+            for (int t = 0; t < kQRows / 4; ++t) {
                 const uint32_t off = off_rm(quad, t, lane);
                 const int R = rm_row(t, lane);
                 const int64_t grow = row0 + R;
@@ -658,7 +663,7 @@ extern "C" int dctr_mlp2tc_supported(int D0, int H1, int H2) {
 
 extern "C" size_t dctr_mlp2tc_workspace(int N, int H2) {
     if (N < 0) N = 0;
-    const size_t tiles = (size_t)(N + m2tc::kRows - 1) / m2tc::kRows;
+    const size_t tiles = (size_t)(N + m2tc::kTileRows - 1) / m2tc::kTileRows;
     return 256 + tiles * (size_t)(H2 + 2) * sizeof(float);
 }
 
@@ -741,8 +746,6 @@ extern "C" int dctr_mlp2tc_train(int N, int D0, int H1, int H2, float* x, int ld
     DCTR_REQUIRE(a.ph[1].acc_col + a.ph[1].nh * a.ph[1].hw <= 512 && a.ph[3].acc_col + a.ph[3].nh * a.ph[3].hw <= 512 && a.ph[1].nh == 1,
                  "mlp2tc_train: accumulators do not fit tensor memory");
     a.packed = static_cast<const uint8_t*>(packed);
-    static const int dbg = getenv("DCTR_M2TC_DBG") ? atoi(getenv("DCTR_M2TC_DBG")) : 0;
-    a.dbg = dbg;
     static unsigned long long* timing = nullptr;
     static const bool want_timing = getenv("DCTR_M2TC_TIMING") != nullptr;
     if (want_timing && !timing) cudaMalloc(&timing, 32 * sizeof(unsigned long long));      // diagnostic runs only
@@ -750,7 +753,9 @@ extern "C" int dctr_mlp2tc_train(int N, int D0, int H1, int H2, float* x, int ld
     if (a.timing) { cudaMemsetAsync(timing + 14, 0xFF, 8, as_stream(stream)); cudaMemsetAsync(timing + 15, 0, 8, as_stream(stream)); }
     cudaError_t e = cudaFuncSetAttribute(mlp2tc_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
     if (e != cudaSuccess) { set_error("mlp2tc_train: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return DCTR_ECUDA; }
-    launch_k_heavy(mlp2tc_train_kernel, dim3((N + kRows - 1) / kRows), kThreads, kSmem, as_stream(stream), a);
+    // programmatic dependent launch: barrier set-up, the TMEM allocation and the zero fill of the A ring overlap the tail of the
+    // kernel before (64 CTAs leave the other SMs to the concurrent streams, unlike the per-layer GEMM's full waves)
+    launch_k(mlp2tc_train_kernel, dim3((N + kTileRows - 1) / kTileRows), kThreads, kSmem, as_stream(stream), a);
     const int rc = check_launch("mlp2tc_train_kernel");
     if (want_timing && timing && rc == DCTR_OK && cudaStreamSynchronize(as_stream(stream)) == cudaSuccess) {
         // workers (thread 0 of CTA 0): start | x chunks written | z1 complete | a1 chunks written | z2 complete | dz2 chunks written |
@@ -759,9 +764,7 @@ extern "C" int dctr_mlp2tc_train(int N, int D0, int H1, int H2, float* x, int ld
         cudaMemcpy(t, timing, sizeof(t), cudaMemcpyDeviceToHost);
         fprintf(stderr, "mlp2tc timing (ns, CTA 0):");
         for (int i = 0; i < 14; ++i) fprintf(stderr, " %lld", (long long)(t[i] - t[0]));
-        fprintf(stderr, " | first CTA start %lld, last CTA end %lld | F1 chunk 4:", (long long)(t[14] - t[0]), (long long)(t[15] - t[0]));
-        for (int i = 16; i < 23; ++i) fprintf(stderr, " %lld", (long long)(t[i] - t[0]));
-        fprintf(stderr, "\n");
+        fprintf(stderr, " | first CTA start %lld, last CTA end %lld\n", (long long)(t[14] - t[0]), (long long)(t[15] - t[0]));
     }
     return rc;
 }

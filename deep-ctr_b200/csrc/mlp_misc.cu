@@ -233,7 +233,7 @@ __device__ __forceinline__ void fold_row_lanes(float (&acc)[V], int TX, float* s
 template <int V>
 __global__ void __launch_bounds__(kRedThreads)
 col_wsum_kernel(const float* __restrict__ A, int lda, int N, int H, const float* __restrict__ wv, RedShape sh,
-                float* __restrict__ partial, unsigned* __restrict__ tickets, float* __restrict__ out) {
+                float* __restrict__ partial, unsigned* __restrict__ tickets, float* __restrict__ out, int sgd, float lr, float decay) {
     pdl_sync();
     __shared__ float s_acc[V * kRedThreads];
     const int TX = sh.TX, TY = kRedThreads / TX, tx = threadIdx.x % TX, ty = threadIdx.x / TX;
@@ -262,7 +262,9 @@ col_wsum_kernel(const float* __restrict__ A, int lda, int N, int H, const float*
             if (h0 + c < H) partial[(int64_t)blockIdx.y * H + h0 + c] = acc[c];
     }
     if (!take_last_ticket(tickets + blockIdx.x, gridDim.y)) return;
-    ordered_reduce(partial + c0, (int)gridDim.y, H, min(TX * V, H - c0), [&](int h, float s) { out[c0 + h] = s; });
+    // sgd: out is the parameter vector itself (a bias): out = out * decay - lr * (column sum)
+    ordered_reduce(partial + c0, (int)gridDim.y, H, min(TX * V, H - c0),
+                   [&](int h, float s) { out[c0 + h] = sgd ? fmaf(out[c0 + h], decay, -lr * s) : s; });
 }
 
 // backward of the output unit in one launch (FNN.py:54-63 / FNN_wnzh.py:169-174 differentiated):
@@ -517,8 +519,8 @@ extern "C" int dctr_out_bwd(const float* dlogit, const float* w, const float* a,
 
 extern "C" size_t dctr_col_wsum_workspace(int N, int H) { return dctr_reduce_workspace(N, H); }
 
-extern "C" int dctr_col_wsum(const float* A, int lda, int N, int H, const float* wv, float* out, void* workspace,
-                             size_t workspace_bytes, void* stream) {
+static int col_wsum_impl(const float* A, int lda, int N, int H, const float* wv, float* out, int sgd, float lr, float decay,
+                         void* workspace, size_t workspace_bytes, void* stream) {
     DCTR_REQUIRE(A && out && workspace && N > 0 && H > 0, "col_wsum: bad arguments");
     if (workspace_bytes < dctr_reduce_workspace(N, H)) {
         set_error("col_wsum: workspace %zu < %zu", workspace_bytes, dctr_reduce_workspace(N, H));
@@ -531,10 +533,20 @@ extern "C" int dctr_col_wsum(const float* A, int lda, int N, int H, const float*
     float* partial = reinterpret_cast<float*>(static_cast<char*>(workspace) + kRedHeader);
     const dim3 grid(sh.col_tiles, sh.chunks);
     if (vec)
-        launch_k(col_wsum_kernel<4>, grid, kRedThreads, 0, as_stream(stream), A, lda, N, H, wv, sh, partial, tickets, out);
+        launch_k(col_wsum_kernel<4>, grid, kRedThreads, 0, as_stream(stream), A, lda, N, H, wv, sh, partial, tickets, out, sgd, lr, decay);
     else
-        launch_k(col_wsum_kernel<1>, grid, kRedThreads, 0, as_stream(stream), A, lda, N, H, wv, sh, partial, tickets, out);
+        launch_k(col_wsum_kernel<1>, grid, kRedThreads, 0, as_stream(stream), A, lda, N, H, wv, sh, partial, tickets, out, sgd, lr, decay);
     return check_launch("col_wsum_kernel");
+}
+
+extern "C" int dctr_col_wsum(const float* A, int lda, int N, int H, const float* wv, float* out, void* workspace,
+                             size_t workspace_bytes, void* stream) {
+    return col_wsum_impl(A, lda, N, H, wv, out, 0, 0.f, 1.f, workspace, workspace_bytes, stream);
+}
+
+extern "C" int dctr_col_wsum_sgd(const float* A, int lda, int N, int H, const float* wv, float* param, float lr, float decay,
+                                 void* workspace, size_t workspace_bytes, void* stream) {
+    return col_wsum_impl(A, lda, N, H, wv, param, 1, lr, decay, workspace, workspace_bytes, stream);
 }
 
 // ---- dctr_col_wsum without a caller-provided workspace (no counterpart in the reference; added

@@ -131,6 +131,7 @@ class StepEngine:
         if self.mlp2_tc and not self.fused_mlp2:
             self.mlp2_tc = False
         self._mlp2_sgd = False                  # this step's fused kernels apply plain SGD to the MLP themselves
+        self._bias_sgd_done = False
         self._mlp2_cfg = None                   # (lr, decay_hidden, decay_out, train_bias) when they do
         self._mlp2_tr_event = None
         if self.fused_mlp2 and not self.mlp2_wgrad_gemm:
@@ -145,6 +146,7 @@ class StepEngine:
             # the second stream at the start of every step
             self.W12_packed = torch.zeros(L.lib().dctr_mlp2tc_packed_bytes(*self.widths), dtype=torch.uint8, device=self.dev)
             self.side3 = torch.cuda.Stream(device=self.dev)
+            self.side4 = torch.cuda.Stream(device=self.dev)
             self.col_ws3 = torch.zeros_like(self.col_ws)
             self.splitk_ws3 = torch.zeros_like(self.splitk_ws)
         self.skip_row = None        # set when the weights are 0 / 1 and 0 only marks this (all-zero pad) row: no weight gather in the fold
@@ -296,21 +298,37 @@ class StepEngine:
         ov = self.overlap_wgrad
         main = torch.cuda.current_stream(self.dev)
         if self.mlp2_wgrad_gemm:
-            # dz1 = dbuf[0] pairs with ins[0], dz2 = dbuf[1] with ins[1]: split-K TN GEMM, fold, bias column sums -- the two layers are
-            # independent of each other, so each gets its own side stream (both start when the fused kernel ends)
-            for l, side, cws, sws in ((0, self.side2, self.col_ws2, self.splitk_ws), (1, self.side3, self.col_ws3, self.splitk_ws3)):
+            # dz1 = dbuf[0] pairs with ins[0], dz2 = dbuf[1] with ins[1].  Per layer: split-K TN GEMM -> fold of the slabs, and the
+            # bias column sums; the layers are independent of each other and the bias sums of the GEMMs, so there are three side
+            # streams (all start when the fused kernel ends).  Plain SGD on one GPU: the fold and the column sums apply the update
+            # themselves (W = W * decay - lr * gW), the gradients never go to memory and there is no dense sweep afterwards.
+            def on(side):
                 if ov:
                     side.wait_stream(main)
-                with torch.cuda.stream(side if ov else main):
+                return torch.cuda.stream(side if ov else main)
+            for l, side, sws in ((0, self.side2, self.splitk_ws), (1, self.side3, self.splitk_ws3)):
+                with on(side):
                     K, Hl, s_ = self.widths[l], self.widths[l + 1], self.splits[l]
                     dpre, gW = self.dbuf[l], self.W(l, self.grads)
                     if s_ > 1:
                         slabs = sws[:s_ * K * self.ldw[l]].view(s_, K, self.ldw[l])
                         self._gemm(L.GEMM_TN, K, Hl, self.N, self.ins[l], dpre, slabs, L.EPI_NONE, 0, None, None, None, s_)
-                        O.splitk_reduce(slabs, s_, K, Hl, self.ldw[l], gW)
+                        if sgd:
+                            O.splitk_reduce_sgd(slabs, s_, K, Hl, self.ldw[l], self.W(l), float(lr), float(dhid))
+                        else:
+                            O.splitk_reduce(slabs, s_, K, Hl, self.ldw[l], gW)
                     else:
                         self._gemm(L.GEMM_TN, K, Hl, self.N, self.ins[l], dpre, gW, L.EPI_NONE, 0, None, None, None, 1)
-                    O.col_wsum(dpre, Hl, None, self.b(l, self.grads), cws if ov else self.col_ws)
+                        if sgd:
+                            lo = self.w_off[l]
+                            O.dense_sgd(self.params[lo:lo + K * self.ldw[l]], self.grads[lo:lo + K * self.ldw[l]], K * self.ldw[l], float(lr), float(dhid))
+            with on(self.side4):
+                for l, cws in ((0, self.col_ws2), (1, self.col_ws3)):
+                    cw = cws if ov else self.col_ws
+                    if sgd:
+                        O.col_wsum_sgd(self.dbuf[l], self.widths[l + 1], None, self.b(l), float(lr), float(dhid), cw)
+                    else:
+                        O.col_wsum(self.dbuf[l], self.widths[l + 1], None, self.b(l, self.grads), cw)
             if ov:
                 self._wgrad_pending = True
             return
@@ -387,7 +405,11 @@ class StepEngine:
         wts = None if self.wts_are_ones else self.wts
         if train_bias:
             col = 0 if self.bias_first else F * d + self.crossw
-            O.col_wsum(dz[:, col:col + 1], 1, None, self.bias(self.grads), self.col_ws)
+            if self._mlp2_sgd:          # plain SGD with the fused MLP kernels: the bias takes its step right here
+                O.col_wsum_sgd(dz[:, col:col + 1], 1, None, self.bias(), float(lr), 1.0, self.col_ws)
+                self._bias_sgd_done = True
+            else:
+                O.col_wsum(dz[:, col:col + 1], 1, None, self.bias(self.grads), self.col_ws)
         if self.cross != "none":
             O.cross_bwd(self.ids.view(self.N, F), None if wts is None else wts.view(self.N, F), self.table, d, L.CROSS[self.cross], dz, self.ge)
             g, g_ld_f, w = self.ge, self.ldg, None
@@ -451,6 +473,7 @@ class StepEngine:
             torch.cuda.current_stream(self.dev).wait_stream(self.side2)
             if self.mlp2_wgrad_gemm:
                 torch.cuda.current_stream(self.dev).wait_stream(self.side3)
+                torch.cuda.current_stream(self.dev).wait_stream(self.side4)
             self._wgrad_pending = False
 
     def dense_update(self, lr, last_decay=1.0, mlp_decay=1.0):
@@ -463,8 +486,9 @@ class StepEngine:
             O.dense_sgd(P[lo:hi], G[lo:hi], hi - lo, float(lr), float(decay))
         if self._mlp2_sgd:                 # the fused kernels updated the MLP; what is left is the embedding-side bias
             self._mlp2_sgd = False
-            if self._mlp2_cfg[3]:
+            if self._mlp2_cfg[3] and not self._bias_sgd_done:
                 sgd(self.bias_off, n, 1.0)
+            self._bias_sgd_done = False
             return
         if self.adam is not None:          # same step counter as the table (embedding_update ticked it)
             b1, b2, eps = self.adam
@@ -498,7 +522,7 @@ class StepEngine:
             self.sort_ids()
         # plain SGD on one GPU: the fused MLP kernels apply the update themselves (the multi-GPU steps call forward / backward
         # directly and all-reduce self.grads first, Adam / FTRL need the gradients)
-        plain = self.fused_mlp2 and not self.dense_optimizer and not self.mlp2_wgrad_gemm
+        plain = self.fused_mlp2 and not self.dense_optimizer
         if self.fused_mlp2 and self.overlap_wgrad:     # W^T for the backward GEMMs: off the critical path, next to the gather
             self.side2.wait_stream(cur)
             with torch.cuda.stream(self.side2):

@@ -182,6 +182,11 @@ def splitk_reduce(partials, splits, M, N, ldc, out):
     L.call("dctr_splitk_reduce", _ptr(partials, _F32, "partials"), splits, M, N, ldc, _ptr(out, _F32, "out"), out.stride(0), _st(out))
 
 
+@_op("splitk_reduce_sgd", "(Tensor partials, int splits, int M, int N, int ldc, Tensor(a!) W, float lr, float decay) -> ()")
+def splitk_reduce_sgd(partials, splits, M, N, ldc, W, lr, decay):
+    L.call("dctr_splitk_reduce_sgd", _ptr(partials, _F32, "partials"), splits, M, N, ldc, _ptr(W, _F32, "W"), W.stride(0), lr, decay, _st(W))
+
+
 @_op("out_xent_fwd", "(Tensor a, int H, Tensor w, Tensor b, Tensor? y, float gscale, Tensor(a!) logit, Tensor(b!) pred, Tensor(c!) loss_n, "
      "Tensor(d!) dlogit, float loss_scale, Tensor(e!)? loss_sum, Tensor(f!) workspace) -> ()")
 def out_xent_fwd(a, H, w, b, y, gscale, logit, pred, loss_n, dlogit, loss_scale, loss_sum, workspace):
@@ -211,6 +216,12 @@ def out_unit_train(a, H, w, b, y, gscale, act, mask, logit, pred, loss_n, dlogit
 @_op("col_wsum", "(Tensor A, int H, Tensor? wv, Tensor(a!) out, Tensor(b!) workspace) -> ()")
 def col_wsum(A, H, wv, out, workspace):
     L.call("dctr_col_wsum", _ptr(A, _F32, "A"), A.stride(0), A.shape[0], H, _ptr(wv, _F32, "wv"), _ptr(out, _F32, "out"),
+           _ptr(workspace, _U8, "workspace"), workspace.numel(), _st(A))
+
+
+@_op("col_wsum_sgd", "(Tensor A, int H, Tensor? wv, Tensor(a!) param, float lr, float decay, Tensor(b!) workspace) -> ()")
+def col_wsum_sgd(A, H, wv, param, lr, decay, workspace):
+    L.call("dctr_col_wsum_sgd", _ptr(A, _F32, "A"), A.stride(0), A.shape[0], H, _ptr(wv, _F32, "wv"), _ptr(param, _F32, "param"), lr, decay,
            _ptr(workspace, _U8, "workspace"), workspace.numel(), _st(A))
 
 

@@ -197,6 +197,10 @@ int dctr_gemm(int layout, int M, int N, int K, const float* A, int lda, const fl
               float* C, int ldc, int epilogue, int act, const float* bias,
               const float* aux, int ldaux, const float* mask, int ldmask, int splits, void* stream);
 int dctr_splitk_reduce(const float* partials, int splits, int M, int N, int ldc, float* out, int ldo, void* stream);
+/* the same fold with the SGD step applied: W = W * decay - lr * (sum of the slabs); the weight gradient never goes to memory
+ * (plain SGD of FNN_wnzh.py:176-183 / GradientDescentOptimizer on one GPU) */
+int dctr_splitk_reduce_sgd(const float* partials, int splits, int M, int N, int ldc, float* W, int ldw, float lr, float decay,
+                           void* stream);
 /* 3xTF32 error-compensated tensor-core variant (tcgen05.mma kind::tf32, TMEM accumulators, operands split into
  * tf32 hi + lo parts on their way into shared memory: acc += A_lo*B_hi + A_hi*B_lo + A_hi*B_hi).  Same contract,
  * layouts, epilogues and split-K slab convention as dctr_gemm; results agree with it to ~1e-6 relative. */
@@ -235,6 +239,9 @@ int dctr_out_unit_train(const float* a, int lda, int N, int H, const float* w, c
 size_t dctr_col_wsum_workspace(int N, int H);
 int dctr_col_wsum(const float* A, int lda, int N, int H, const float* wv, float* out,
                   void* workspace, size_t workspace_bytes, void* stream);
+/*   the same with the SGD step of a bias applied: param[h] = param[h] * decay - lr * sum_n (wv? wv[n]:1) * A[n,h] */
+int dctr_col_wsum_sgd(const float* A, int lda, int N, int H, const float* wv, float* param, float lr, float decay,
+                      void* workspace, size_t workspace_bytes, void* stream);
 /*   dctr_col_wsum for callers that cannot allocate (code under CUDA graph capture, serving loops, harnesses that forbid
  *   cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same result as dctr_col_wsum,
  *   bit for bit; the scratch is a device array built into the library (4.63 MiB per GPU that loads it, held until exit), so

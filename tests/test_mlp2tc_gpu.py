@@ -158,3 +158,35 @@ def test_mlp2tc_is_deterministic():
         outs.append((a1, dz1, dz2, dz0, sc[1], loss, gw3, gb3))
     for u, v in zip(*outs):
         assert torch.equal(u, v)
+
+
+def test_sgd_fused_reductions():
+    """dctr_splitk_reduce_sgd / dctr_col_wsum_sgd: the fold of the split-K slabs and the bias column sums with the SGD step applied
+    in place -- equal to the gradient-producing entry point followed by dctr_dense_sgd, bit for bit."""
+    import deepctr_b200.ops  # noqa: F401
+    from deepctr_b200 import _lib as L
+    O = torch.ops.deepctr
+    g = torch.Generator(device="cuda").manual_seed(9)
+    f32 = dict(dtype=torch.float32, device="cuda")
+    for splits, M, N in ((8, 177, 300), (3, 5, 7), (1, 64, 64)):
+        ld = r4(N)
+        slabs = torch.randn(splits, M, ld, generator=g, **f32)
+        W = torch.randn(M, ld, generator=g, **f32)
+        gW, W2 = torch.zeros(M, ld, **f32), W.clone()
+        O.splitk_reduce(slabs, splits, M, N, ld, gW)
+        O.dense_sgd(W2.view(-1), gW.view(-1), M * ld, 0.05, 0.999)
+        W1 = W.clone()
+        O.splitk_reduce_sgd(slabs, splits, M, N, ld, W1, 0.05, 0.999)
+        torch.cuda.synchronize()
+        assert torch.equal(W1[:, :N], W2[:, :N]) and torch.equal(W1[:, N:], W[:, N:])
+    for N, H in ((4096, 300), (100, 7), (65536, 100)):
+        A = torch.randn(N, r4(H) + 4, generator=g, **f32)
+        b = torch.randn(H, generator=g, **f32)
+        ws = torch.zeros(L.lib().dctr_col_wsum_workspace(N, H), dtype=torch.uint8, device="cuda")
+        gb, b2 = torch.zeros(H, **f32), b.clone()
+        O.col_wsum(A, H, None, gb, ws)
+        O.dense_sgd(b2, gb, H, 0.05, 0.999)
+        b1 = b.clone()
+        O.col_wsum_sgd(A, H, None, b1, 0.05, 0.999, ws)
+        torch.cuda.synchronize()
+        assert torch.equal(b1, b2)

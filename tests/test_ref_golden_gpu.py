@@ -68,7 +68,10 @@ def test_fnn_wnzh_whole_script(gold, gemm_path):
             m.train(train_f[j * N:(j + 1) * N], train_y[j * N:(j + 1) * N])
             if "gx" in st:
                 gx = m.engine.dz0[:, :st["gx"].shape[1]].cpu().numpy()
-                close(gx, st["gx"], (k + 1) * RTOL, 1e-7)
+                # the fused tcgen05 kernel keeps ONE accumulator per output (tensor memory is full) and evaluates tanh through
+                # ex2 / rcp: its elements carry an absolute error of a few 1e-6 of the LARGEST gradient of the batch
+                atol = 1e-7 if gemm_path != "mlp2tc" else 4e-6 * float(np.abs(st["gx"]).max())
+                close(gx, st["gx"], (k + 1) * RTOL, atol)
             k += 1
         for feats, yy, want in ((train_f, train_y, erec["train_p"]), (test_f, test_y, erec["test_p"])):
             p = m.predict(feats)
