@@ -122,10 +122,12 @@ class StepEngine:
         # DCTR_MLP2=tc: the same fusion on the tensor cores (csrc/mlp2tc.cu: forward + data gradients of a 128-sample tile chained
         # through tcgen05 with the activations handed from epilogue to A tile in shared memory); weight gradients by
         # DCTR_MLP2_WGRAD = gemm (split-K TN GEMMs, one side stream per layer) | cluster (the FFMA cluster kernel of mlp2.cu).
-        mode = os.environ.get("DCTR_MLP2", "off")
+        # Default (DCTR_MLP2=auto): the tcgen05 fusion wherever it applies and the engine is on the tensor-core path -- measured at
+        # N = 4096, 177-300-100-1: 0.128 ms per step against 0.153 for the per-layer chain (profiles/r02_bench_fnn_ipinyou_mlp2tc.json).
+        mode = os.environ.get("DCTR_MLP2", "auto")
         ok = self.nl == 3 and bool(L.lib().dctr_mlp2_supported(self.widths[0], self.widths[1], self.widths[2]))
         ok_tc = self.nl == 3 and bool(L.lib().dctr_mlp2tc_supported(self.widths[0], self.widths[1], self.widths[2]))
-        self.mlp2_tc = ok_tc and mode == "tc"
+        self.mlp2_tc = ok_tc and (mode == "tc" or (mode == "auto" and self.gemm_fn == "dctr_gemm_tc"))
         self.mlp2_wgrad_gemm = self.mlp2_tc and os.environ.get("DCTR_MLP2_WGRAD", "gemm") == "gemm"
         self.fused_mlp2 = (ok and mode == "on") or (self.mlp2_tc and (ok or self.mlp2_wgrad_gemm))
         if self.mlp2_tc and not self.fused_mlp2:
