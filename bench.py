@@ -202,6 +202,14 @@ def call_cost(name, a):
         return "byte", a[4] * a[5] * 8 + a[4] * 4
     if name == "dctr_arrange_fields":               # feats in, ids + wts out
         return "byte", a[2] * (a[3] * 4 + a[4] * 8)
+    if name == "dctr_mlp2tc_train":                 # 3xTF32 on tcgen05: forward + data gradients of both hidden layers (fp32-equivalent flops)
+        return "flop", 4.0 * a[0] * (a[1] * a[2] + a[2] * a[3] + a[3])
+    if name == "dctr_mlp2tc_pack":                  # W1, W2 read; each written twice (both orientations) as hi + lo planes
+        return "byte", (a[0] * a[1] + a[1] * a[2]) * 4 * 5
+    if name == "dctr_splitk_reduce_sgd":            # slabs + W read, W written
+        return "byte", (a[1] + 2) * a[2] * a[3] * 4
+    if name == "dctr_col_wsum_sgd":
+        return "byte", a[2] * a[3] * 4
     if name == "dctr_mlp2_train":                   # fp32 FFMA: forward + data gradients of both hidden layers
         return "flop", 4.0 * a[0] * (a[1] * a[2] + a[2] * a[3] + a[3])
     if name == "dctr_mlp2_wgrad":
@@ -479,6 +487,13 @@ def measure_workload(wl, batch, steps, warmup, rank, world, dist, local, profile
             # achieved counts fp32-equivalent flops (2 M N K); the kernel issues three tf32 MMAs per k-step (error compensation)
             roof["note"] = ("3xTF32 on tcgen05: fp32-equivalent FLOP/s; its ceiling is cuBLAS TF32 / 3 = 243 TFLOP/s (DESIGN 3.4) "
                             "-> frac_of_3xtf32_ceiling; a GEMM of this size is launch- and latency-bound")
+            roof["frac_of_3xtf32_ceiling"] = round(top["achieved"] / 243.0, 4)
+        elif top["unit"] == "TFLOP/s" and top["kernel"].startswith("dctr_mlp2tc"):
+            # 64 CTAs of 64 samples issue M = 128 MMAs over half-empty tiles on 64 of the 148 SMs: the ceiling that applies to THIS launch
+            # is 243 TFLOP/s x 64 / 148 x 1 / 2 = 52.5 TFLOP/s fp32-equivalent; the epilogues (activation, tf32 split, the transposition
+            # through shared memory: ~25 instructions per element) bound it, not the MMAs
+            roof["note"] = ("forward + data gradients of both hidden layers chained through tcgen05 in one kernel (csrc/mlp2tc.cu), 3xTF32: "
+                            "fp32-equivalent FLOP/s; ceiling of 3xTF32 = 243 TFLOP/s -> frac_of_3xtf32_ceiling; epilogue-bound (DESIGN 3.5)")
             roof["frac_of_3xtf32_ceiling"] = round(top["achieved"] / 243.0, 4)
         elif top["unit"] == "TFLOP/s" and top["kernel"].startswith("dctr_mlp2"):
             roof["note"] = ("fused fp32 FFMA kernel (csrc/mlp2.cu); the layers of this net are too small for tensor-core tiles, so the "
