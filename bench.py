@@ -417,6 +417,15 @@ def measure_workload(wl, batch, steps, warmup, rank, world, dist, local, profile
     torch.cuda.synchronize()
     warm_ms = e0.elapsed_time(e1)
     clocks = sampler.summary()
+    shard_phases = None
+    if getattr(model, "sharded", None) is not None and os.environ.get("DCTR_SHARD_PROFILE"):
+        was_graph, g = model.use_graph, model._graph        # eager steps with CUDA events between the phases of the exchange
+        model.use_graph = False
+        model.sharded.summary()
+        for i in range(5):
+            device_step(W + i)
+        shard_phases = dict(model.sharded.summary(), capacity=model.sharded.C, slots=eng.M)
+        model.use_graph, model._graph = was_graph, g
     if dist:
         t = torch.tensor([total_ms, warm_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -511,6 +520,7 @@ def measure_workload(wl, batch, steps, warmup, rank, world, dist, local, profile
                    "batch_per_gpu": N, "global_batch": N * world, "l2": "flushed (512 MB write) before every timed step",
                    "parallelism": ("rowshard%d" if sharded else "dp%d") % world if world > 1 else "single", "cuda_graph": bool(model.use_graph)},
         "warm_l2": {"ms_per_step": warm_ms / K, "value": N * world * K / (warm_ms * 1e-3)},
+        **({"shard_phases_ms": shard_phases} if shard_phases else {}),
         "e2e": {"value": N * world * K / e2e_s, "unit": "samples/s", "h2d_bytes_per_step": model.h2d_bytes,
                 "d2h_bytes_per_step": model.d2h_bytes, "ms_per_step": e2e_s / K * 1e3},
         "gpu_launches": int(per_step_launches * K), "launches_per_step": int(per_step_launches),

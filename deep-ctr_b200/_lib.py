@@ -27,8 +27,10 @@ SIGNATURES = {
     "dctr_arrange_update_list": (_i, [_p, _p, _i, _i, _i, _l, _i, _p, _p, _p, _p, _p]),
     "dctr_set_id_status": (_i, [_p]),
     "dctr_gather_rows": (_i, [_p, _p, _l, _i, _l, _p, _p]),
+    "dctr_shard_pack": (_i, [_p, _p, _p, _l, _i, _l, _p, _p, _p, _p, _p]),
     "dctr_host_pack_fields": (_i, [_p, _i, _p, _p, _p, _l, _i, _i, _p, _p, _i]),
     "dctr_cross_bwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
+    "dctr_cross_bwd_to": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _i, _p, _i, _p, _i, _p, _p]),
     "dctr_fm_fwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _p, _p, _f, _p, _p, _p, _p, _p, _i, _p]),
     "dctr_sort_rows_workspace": (_z, [_l]),
     "dctr_sort_rows": (_i, [_p, _l, _l, _p, _p, _p, _z, _p]),

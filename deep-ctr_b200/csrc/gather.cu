@@ -153,7 +153,8 @@ template <int CROSS>
 __global__ void __launch_bounds__(kGatherWarps * 32)
 cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts, const float* __restrict__ table,
                  int ld, int N, int F, int d, const float* __restrict__ dz, int ldz,
-                 float* __restrict__ ge, int ldg, int X, int32_t* __restrict__ status) {
+                 float* __restrict__ ge, int ldg, int X, int32_t* __restrict__ status, const int32_t* __restrict__ dest) {
+    // dest != NULL: slot (n, f) writes row dest[n * F + f] of ge instead of row n * F + f (the bucket order of the row-sharded exchange)
     pdl_sync();
     extern __shared__ __align__(16) float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -198,13 +199,13 @@ cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
                 }
             }
             const float w = wts ? wts[n * F + f] : 1.f;
-            ge[(n * F + f) * (int64_t)ldg + c] = w * acc;
+            ge[(dest ? (int64_t)dest[n * F + f] : n * F + f) * (int64_t)ldg + c] = w * acc;
         }
         if (ldg > d) {
             const int padw = ldg - d;
             for (int t = lane; t < F * padw; t += 32) {
                 const int f = t / padw;
-                ge[(n * F + f) * (int64_t)ldg + d + (t - f * padw)] = 0.f;
+                ge[(dest ? (int64_t)dest[n * F + f] : n * F + f) * (int64_t)ldg + d + (t - f * padw)] = 0.f;
             }
         }
         __syncwarp();
@@ -314,9 +315,9 @@ extern "C" int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, cons
     return check_launch("gather_concat_kernel");
 }
 
-extern "C" int dctr_cross_bwd(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
-                              int N, int F, int d, int cross, const float* dz, int ldz,
-                              float* ge, int ldg, void* stream) {
+static int cross_bwd_impl(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
+                          int N, int F, int d, int cross, const float* dz, int ldz,
+                          float* ge, int ldg, const int32_t* dest, void* stream) {
     DCTR_REQUIRE(ids && table && dz && ge, "cross_bwd: null pointer");
     DCTR_REQUIRE(N >= 0 && F > 0 && F < 256 && d > 0 && d <= ld && (ld & 3) == 0 && ldg >= d, "cross_bwd: bad shape");
     DCTR_REQUIRE(cross >= 0 && cross <= 2 && X > 0, "cross_bwd: bad cross");
@@ -331,13 +332,26 @@ extern "C" int dctr_cross_bwd(const int32_t* ids, const float* wts, const float*
     do {                                                                                                     \
         if (smem > 48 * 1024)                                                                                \
             cudaFuncSetAttribute(cross_bwd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        launch_k(cross_bwd_kernel<C>, grid, block, smem, st, ids, wts, table, ld, N, F, d, dz, ldz, ge, ldg, (int)X, id_status()); \
+        launch_k(cross_bwd_kernel<C>, grid, block, smem, st, ids, wts, table, ld, N, F, d, dz, ldz, ge, ldg, (int)X, id_status(), dest); \
     } while (0)
     if (cross == DCTR_CROSS_IP) LAUNCH_B(DCTR_CROSS_IP);
     else if (cross == DCTR_CROSS_OP) LAUNCH_B(DCTR_CROSS_OP);
     else LAUNCH_B(DCTR_CROSS_NONE);
 #undef LAUNCH_B
     return check_launch("cross_bwd_kernel");
+}
+
+extern "C" int dctr_cross_bwd(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
+                              int N, int F, int d, int cross, const float* dz, int ldz,
+                              float* ge, int ldg, void* stream) {
+    return cross_bwd_impl(ids, wts, table, X, ld, N, F, d, cross, dz, ldz, ge, ldg, nullptr, stream);
+}
+
+extern "C" int dctr_cross_bwd_to(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
+                                 int N, int F, int d, int cross, const float* dz, int ldz,
+                                 float* ge, int ldg, const int32_t* dest, void* stream) {
+    DCTR_REQUIRE(dest, "cross_bwd_to: null destination index");
+    return cross_bwd_impl(ids, wts, table, X, ld, N, F, d, cross, dz, ldz, ge, ldg, dest, stream);
 }
 
 extern "C" int dctr_arrange_fields(const int32_t* feats, const int32_t* feat_field, int N, int J, int F, int32_t pad_row,
@@ -355,6 +369,57 @@ extern "C" int dctr_arrange_update_list(const int32_t* feats, const int32_t* fea
     launch_k(arrange_fields_kernel, ceil_div((int64_t)N * 32, 256), 256, 0, as_stream(stream), feats, feat_field, N, J, F, (int32_t)X,
              pad_row, ids, wts, upd_rows, upd_pos, id_status());
     return check_launch("arrange_fields_kernel");
+}
+
+// ---- fixed-capacity exchange plan of the row-sharded table ---------------------------------------------------------------------------
+// The slots of a batch, already ordered by owner rank (perm / owner_sorted from the stable sort on the owner key), go into `world`
+// buckets of C entries each: slot perm[i] of owner o is entry i - first(o).  Entries past a bucket's fill keep the sentinel -1
+// (send_ids) / 0 (src_of_dest); a bucket that would overflow drops the slot and counts it in status[0] (status[1] = the largest
+// fill seen) -- the caller sizes C from a calibration step and treats status[0] != 0 as an error.
+namespace dctr {
+__global__ void __launch_bounds__(256)
+shard_pack_kernel(const int32_t* __restrict__ ids, const int32_t* __restrict__ perm, const int32_t* __restrict__ owner_sorted, int64_t M,
+                  int world, int64_t C, int32_t* __restrict__ send_ids, int32_t* __restrict__ src_of_dest, int32_t* __restrict__ inv,
+                  int32_t* __restrict__ status) {
+    pdl_sync();
+    __shared__ int64_t s_first[65];
+    if ((int)threadIdx.x <= world) {            // first position of every owner in the sorted list (lower bound), [world] = M
+        const int o = threadIdx.x;
+        int64_t lo = 0, hi = M;
+        while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (owner_sorted[mid] < o) lo = mid + 1; else hi = mid; }
+        s_first[o] = lo;
+    }
+    __syncthreads();
+    if (blockIdx.x == 0 && (int)threadIdx.x < world) atomicMax(status + 1, (int)(s_first[threadIdx.x + 1] - s_first[threadIdx.x]));
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (int64_t)gridDim.x * blockDim.x) {
+        const int o = owner_sorted[i], slot = perm[i];
+        const int64_t k = i - s_first[o];
+        if (k < C) {
+            const int64_t dest = (int64_t)o * C + k;
+            send_ids[dest] = ids[slot] / world;
+            src_of_dest[dest] = slot;
+            inv[slot] = (int32_t)dest;
+        } else {
+            inv[slot] = (int32_t)((int64_t)o * C);      // a valid position; the step is reported as failed
+            atomicAdd(status, 1);
+        }
+    }
+}
+}  // namespace dctr
+
+extern "C" int dctr_shard_pack(const int32_t* ids, const int32_t* perm, const int32_t* owner_sorted, int64_t M, int world, int64_t C,
+                               int32_t* send_ids, int32_t* src_of_dest, int32_t* inv, int32_t* status, void* stream) {
+    DCTR_REQUIRE(M >= 0 && world >= 1 && world <= 64 && C >= 1 && (int64_t)world * C < ((int64_t)1 << 31), "shard_pack: bad shape");
+    DCTR_REQUIRE(send_ids && src_of_dest && status && (M == 0 || (ids && perm && owner_sorted && inv)), "shard_pack: null pointer");
+    cudaStream_t st = as_stream(stream);
+    cudaError_t e = cudaMemsetAsync(send_ids, 0xFF, (size_t)world * C * sizeof(int32_t), st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(src_of_dest, 0, (size_t)world * C * sizeof(int32_t), st);
+    if (e != cudaSuccess) { set_error("shard_pack: cudaMemsetAsync: %s", cudaGetErrorString(e)); return DCTR_ECUDA; }
+    if (M == 0) return DCTR_OK;
+    int blocks = ceil_div(M, 256);
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    launch_k(shard_pack_kernel, blocks, 256, 0, st, ids, perm, owner_sorted, M, world, C, send_ids, src_of_dest, inv, status);
+    return check_launch("shard_pack_kernel");
 }
 
 extern "C" int dctr_gather_rows(const int32_t* ids, const float* table, int64_t X, int ld, int64_t M, float* out, void* stream) {

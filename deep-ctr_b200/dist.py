@@ -186,6 +186,64 @@ class ShardedStep(object):
         self.plan_ws = torch.zeros(L.lib().dctr_sort_rows_workspace(e.M), dtype=torch.uint8, device=e.dev)
         self.ge = e.ge if e.ge is not None else torch.zeros(e.N, e.F, e.ldg, dtype=torch.float32, device=e.dev)
         self.last = None
+        # Fixed-capacity exchanges (DCTR_SHARD_FIXED=0 keeps the variable-split path): the first step runs with the split sizes read
+        # on the host and measures the fullest (source, owner) bucket over all ranks; from the second step on every bucket has C =
+        # slack x that entries, the three all-to-alls have equal splits, every buffer is static and the step replays as a CUDA graph.
+        self.fixed = os.environ.get("DCTR_SHARD_FIXED", "1") != "0"
+        self.slack = float(os.environ.get("DCTR_SHARD_SLACK", "1.15"))
+        self.C = None
+        self.overflow = torch.zeros(2, **i32)       # [slots that did not fit a bucket since the last check, fullest bucket seen]
+        self._prof = [] if os.environ.get("DCTR_SHARD_PROFILE") else None
+        self._train = False
+
+    def _mark(self, name):
+        """DCTR_SHARD_PROFILE=1 (eager steps only): CUDA events between the phases of a step; summary() prints the averages"""
+        if self._prof is None or torch.cuda.is_current_stream_capturing():
+            return
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        self._prof.append((name, ev))
+
+    def summary(self):
+        if not self._prof:
+            return {}
+        torch.cuda.synchronize()
+        acc, cnt = {}, {}
+        for (n0, e0), (n1, e1) in zip(self._prof[:-1], self._prof[1:]):
+            if n1 == "start":
+                continue
+            acc[n1] = acc.get(n1, 0.0) + e0.elapsed_time(e1)
+            cnt[n1] = cnt.get(n1, 0) + 1
+        self._prof = []
+        return {k: round(acc[k] / cnt[k], 4) for k in acc}
+
+    def set_capacity(self, C):
+        """allocate the static exchange buffers for buckets of C slots per (source, owner) pair"""
+        e = self.e
+        C = (int(C) + 255) // 256 * 256
+        RC = self.world * C
+        i32 = dict(dtype=torch.int32, device=e.dev)
+        f32 = dict(dtype=torch.float32, device=e.dev)
+        self.C, self.RC = C, RC
+        self.send_ids, self.recv_ids, self.src_of_dest = torch.zeros(RC, **i32), torch.zeros(RC, **i32), torch.zeros(RC, **i32)
+        self.gather_ids = torch.zeros(RC, **i32)
+        self.rows_buf, self.back = torch.zeros(RC, e.ld, **f32), torch.zeros(RC, e.ld, **f32)
+        self.send_g, self.recv_g = torch.zeros(RC, e.ldg, **f32), torch.zeros(RC, e.ldg, **f32)
+        self.srows, self.spos = torch.zeros(RC, **i32), torch.zeros(RC, **i32)
+        self.sws = torch.zeros(L.lib().dctr_sort_rows_workspace(RC), dtype=torch.uint8, device=e.dev)
+        self.fws = torch.zeros(L.lib().dctr_scatter_workspace(RC, e.ld), dtype=torch.uint8, device=e.dev)
+
+    def check_overflow(self):
+        """host side, after a step: a bucket that overflowed dropped slots -- the step is invalid"""
+        if self.C is None:
+            return
+        lost = int(self.overflow[0].item())
+        if lost:
+            self.overflow.zero_()
+            C = self.C
+            self.C = None                          # the next step re-measures
+            raise RuntimeError("row-sharded exchange: %d slot(s) did not fit the buckets of %d entries per rank pair (the id distribution "
+                               "changed since the calibration step); this step's update is incomplete -- raise DCTR_SHARD_SLACK" % (lost, C))
 
     def _st(self):
         return torch.cuda.current_stream(self.e.dev).cuda_stream
@@ -198,6 +256,8 @@ class ShardedStep(object):
     def lookup(self):
         """steps 1-2: returns (inv ids [N,F], exchanged rows [M, ld]) and remembers the plan for the backward."""
         e, dist = self.e, self.dist
+        if self.C is not None:
+            return self._lookup_fixed()
         perm, counts, send_rows = plan_exchange(e.ids.view(-1), self.world, self._stable_argsort)
         recv_counts = exchange_counts(dist, counts, self.group)
         sc, rc = counts.tolist(), recv_counts.tolist()                    # host sync: the split sizes
@@ -209,17 +269,52 @@ class ShardedStep(object):
         back = all_to_all_rows(dist, rows[:R], rc, sc, self.group)        # [M, ld], in perm order
         self.inv.view(-1)[perm.long()] = self.arange                      # slot -> its row in `back`
         self.last = (sc, rc, recv_rows, back)
+        if self.fixed:                                                    # calibration: the fullest bucket over all ranks and pairs
+            mx = torch.maximum(counts.max(), recv_counts.max()).reshape(1)
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=self.group)
+            self._want_C = int(mx.item() * self.slack) + 64
         return self.inv, back
 
-    def forward(self, with_loss, gscale=1.0):
+    def _lookup_fixed(self):
+        """steps 1-2 with equal-sized buckets: no host read, static buffers"""
+        e, dist = self.e, self.dist
+        ids = e.ids.view(-1)
+        self._mark("start")
+        owner = torch.remainder(ids, self.world).to(torch.int32)
+        O.sort_pairs(owner, None, e.M, self.world, self.owner_sorted, self.perm, self.plan_ws)
+        self._mark("owner sort")
+        O.shard_pack(ids, self.perm, self.owner_sorted, self.world, self.C, self.send_ids, self.src_of_dest, self.inv.view(-1), self.overflow)
+        self._mark("pack")
+        dist.all_to_all_single(self.recv_ids, self.send_ids, group=self.group)
+        self._mark("a2a ids")
+        if self._train:      # the owner-side sort of the received rows only needs the ids: on the side stream, under the forward / backward
+            main = torch.cuda.current_stream(e.dev)
+            e.side.wait_stream(main)
+            with torch.cuda.stream(e.side):
+                # the unused entries (-1) become the sort's sentinel: behind every table row, never read or written by the fold
+                L.call("dctr_set_id_status", None)
+                O.sort_pairs(self.recv_ids, None, self.RC, e.X, self.srows, self.spos, self.sws)
+                L.call("dctr_set_id_status", self.status_ptr)
+        torch.clamp(self.recv_ids, min=0, out=self.gather_ids)            # unused entries (-1) read row 0; nobody looks at them
+        O.gather_rows(self.gather_ids, e.table, self.rows_buf)
+        self._mark("owner gather")
+        dist.all_to_all_single(self.back, self.rows_buf, group=self.group)
+        self._mark("a2a rows")
+        self.last = None
+        return self.inv, self.back
+
+    def forward(self, with_loss, gscale=1.0, train=False):
         """collective inference / forward: every rank must call it together (the lookups are all-to-alls)."""
+        self._train = train
         inv, back = self.lookup()
         self.e.forward(with_loss, gscale, lookup=(inv, back, max(back.shape[0], 1)))
 
     def train_step(self, lr, decay=1.0, gscale=1.0, train_bias=True, last_decay=1.0):
         e, dist = self.e, self.dist
         L.call("dctr_set_launch_mode", 0)          # collectives sit between the kernels: plain stream order
-        self.forward(True, gscale)
+        self.forward(True, gscale, train=True)
+        if self.last is None:
+            return self._train_tail_fixed(lr, decay, train_bias, last_decay)
         sc, rc, recv_rows, back = self.last
         dz = e.backward()
         N, F, d = e.N, e.F, e.d
@@ -248,6 +343,35 @@ class ShardedStep(object):
             e.table_update(rows, pos, R, 1, recv_g, e.ldg, None, lr, decay, fws)
             self._keep = (rows, pos, sws, fws, recv_g, send_g, recv_rows, back)
         e.dense_update(lr, last_decay)
+        if self.fixed and self.C is None:
+            self.set_capacity(self._want_C)           # from the next step on: fixed-capacity exchanges
+
+    def _train_tail_fixed(self, lr, decay, train_bias, last_decay):
+        e, dist = self.e, self.dist
+        self._mark("forward")
+        dz = e.backward()                     # data gradients on this stream, weight gradients on the engine's second stream
+        N, F, d = e.N, e.F, e.d
+        if train_bias:
+            col = F * d + e.crossw
+            O.col_wsum(dz[:, col:col + 1], 1, None, e.bias(e.grads), e.col_ws)
+        self._mark("backward")
+        # the embedding side first: it only needs dz, and the weight-gradient GEMMs run next to it
+        wts = None if e.wts_are_ones else e.wts
+        # per-slot gradients written straight into the owner buckets (unused entries keep stale rows: the owner drops them)
+        O.cross_bwd_to(self.inv.view(N, F), None if wts is None else wts.view(N, F), self.back, d, L.CROSS[e.cross], dz, self.inv.view(-1),
+                       self.send_g)
+        self._mark("slot grads")
+        dist.all_to_all_single(self.recv_g, self.send_g, group=self.group)             # aligned with recv_ids
+        self._mark("a2a grads")
+        torch.cuda.current_stream(e.dev).wait_stream(e.side)                           # the sorted (row, position) list of the received slots
+        e.table_update(self.srows, self.spos, self.RC, 1, self.recv_g, e.ldg, None, lr, decay, self.fws)
+        self._mark("fold")
+        e.join_wgrad()
+        allreduce_dense(dist, e.grads, self.group)
+        allreduce_dense(dist, e.loss, self.group)
+        self._mark("allreduce dense")
+        e.dense_update(lr, last_decay)
+        self._mark("dense update")
 
 
 def attach_sharded(model, dist, X_global, group=None):
@@ -258,7 +382,17 @@ def attach_sharded(model, dist, X_global, group=None):
         raise NotImplementedError("the SNN embedding-bag step has no row-sharded form yet")
     sh = ShardedStep(model.engine, dist, X_global, group)
     model.sharded = sh
-    model.use_graph = False           # the split sizes of the all-to-alls are read on the host every step
+    sh.status_ptr = model._status_ptr
+    # variable-split exchanges read their split sizes on the host every step; with fixed-capacity buckets (the default) the first
+    # step calibrates and the later ones replay as a CUDA graph, collectives included (DCTR_SHARD_GRAPH=0: eager)
+    model.use_graph = sh.fixed and os.environ.get("DCTR_SHARD_GRAPH", "1") != "0"
+    model._graph, model._warm = None, 0
+    check_ids = model._check_ids
+
+    def check_ids_and_buckets():
+        check_ids()
+        sh.check_overflow()
+    model._check_ids = check_ids_and_buckets
     model.global_N = model.N * sh.world
     model.engine.train_step = sh.train_step
     eng_forward = model.engine.forward

@@ -81,11 +81,30 @@ def gather_rows(ids, table, out):
            _ptr(out, _F32, "out", 16), _st(ids))
 
 
+@_op("shard_pack", "(Tensor ids, Tensor perm, Tensor owner_sorted, int world, int C, Tensor(a!) send_ids, Tensor(b!) src_of_dest, "
+     "Tensor(c!) inv, Tensor(d!) status) -> ()")
+def shard_pack(ids, perm, owner_sorted, world, C, send_ids, src_of_dest, inv, status):
+    if send_ids.numel() < world * C or src_of_dest.numel() < world * C or inv.numel() < ids.numel() or status.numel() < 2:
+        raise ValueError("shard_pack: send_ids / src_of_dest need world * C entries, inv one per slot, status two words")
+    L.call("dctr_shard_pack", _ptr(ids, _I32, "ids"), _ptr(perm, _I32, "perm"), _ptr(owner_sorted, _I32, "owner_sorted"), ids.numel(), world, C,
+           _ptr(send_ids, _I32, "send_ids"), _ptr(src_of_dest, _I32, "src_of_dest"), _ptr(inv, _I32, "inv"), _ptr(status, _I32, "status"), _st(ids))
+
+
 @_op("cross_bwd", "(Tensor ids, Tensor? wts, Tensor table, int d, int cross, Tensor dz, Tensor(a!) ge) -> ()")
 def cross_bwd(ids, wts, table, d, cross, dz, ge):
     N, F = ids.shape
     L.call("dctr_cross_bwd", _ptr(ids, _I32, "ids"), _ptr(wts, _F32, "wts"), _ptr(table, _F32, "table", 16), table.shape[0], table.stride(0),
            N, F, d, cross, _ptr(dz, _F32, "dz"), dz.stride(0), _ptr(ge, _F32, "ge"), ge.stride(1), _st(ids))
+
+
+@_op("cross_bwd_to", "(Tensor ids, Tensor? wts, Tensor table, int d, int cross, Tensor dz, Tensor dest, Tensor(a!) ge) -> ()")
+def cross_bwd_to(ids, wts, table, d, cross, dz, dest, ge):
+    """ge: [rows, ldg]; slot (n, f) is written to row dest[n * F + f]"""
+    N, F = ids.shape
+    if dest.numel() < N * F or ge.dim() != 2:
+        raise ValueError("cross_bwd_to: dest needs one entry per slot and ge must be [rows, ldg]")
+    L.call("dctr_cross_bwd_to", _ptr(ids, _I32, "ids"), _ptr(wts, _F32, "wts"), _ptr(table, _F32, "table", 16), table.shape[0], table.stride(0),
+           N, F, d, cross, _ptr(dz, _F32, "dz"), dz.stride(0), _ptr(ge, _F32, "ge"), ge.stride(0), _ptr(dest, _I32, "dest"), _st(ids))
 
 
 @_op("bag_fwd", "(Tensor ids, Tensor? wts, Tensor table, int H, Tensor? b0, int act, Tensor(a!) out) -> ()")

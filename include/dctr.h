@@ -107,6 +107,13 @@ int dctr_host_pack_fields(const void* c_ids, int id_bytes, const int64_t* offset
 /* row gather: out[i, 0:ld) = table[ids[i], 0:ld), i < M.  The owner-side lookup of the row-sharded table (SURVEY 8(e):
  * rows live on rank row % world) and the permutation of per-slot gradient rows into all-to-all order. */
 int dctr_gather_rows(const int32_t* ids, const float* table, int64_t X, int ld, int64_t M, float* out, void* stream);
+/* fixed-capacity exchange plan of the row-sharded table: the M slots of a batch, ordered by owner rank (perm /
+ * owner_sorted: the stable sort of the slots on the key ids % world), are laid out as `world` buckets of C entries:
+ *   send_ids[o*C + k] = ids[slot] / world (the owner-local row), src_of_dest[o*C + k] = slot, inv[slot] = o*C + k;
+ * unused entries are -1 / 0.  Equal-sized buckets make the three all-to-alls of a step static (no split sizes read on the host,
+ * CUDA-graph capturable).  status[0] += slots that did not fit (the step is then invalid), status[1] = max(status[1], largest fill). */
+int dctr_shard_pack(const int32_t* ids, const int32_t* perm, const int32_t* owner_sorted, int64_t M, int world, int64_t C,
+                    int32_t* send_ids, int32_t* src_of_dest, int32_t* inv, int32_t* status, void* stream);
 
 /* backward of the cross layer into a per-(sample,field) embedding-gradient buffer
  *   ge[n,f,c] = wts[n,f] * ( dz[n, f*d+c] + d(cross)/d(e_f[c]) ),  ge: float32 [N, F, ldg], ldg%4==0
@@ -115,6 +122,11 @@ int dctr_gather_rows(const int32_t* ids, const float* table, int64_t X, int ld, 
 int dctr_cross_bwd(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
                    int N, int F, int d, int cross, const float* dz, int ldz,
                    float* ge, int ldg, void* stream);
+/* the same, written in a caller-given row order: slot (n, f) goes to row dest[n*F + f] of ge -- the row-sharded step writes the
+ * per-slot gradients straight into the owner buckets of its all-to-all (dest = the inv of dctr_shard_pack) */
+int dctr_cross_bwd_to(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
+                      int N, int F, int d, int cross, const float* dz, int ldz,
+                      float* ge, int ldg, const int32_t* dest, void* stream);
 
 /* ---- K1fm: fused gather + FM forward + sigmoid cross-entropy (FM.py:55-64, 33-38) -------------
  *   s[n,c] = sum_f x_f*row_f[c];  logit = s[n,0] + b + 0.5*sum_{c>=1}( s[n,c]^2 - sum_f x_f^2 row_f[c]^2 )

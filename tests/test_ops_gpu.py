@@ -186,3 +186,36 @@ def test_no_writes_outside_the_buffers():
         want.index_add_(0, (ids.long() - lo), -0.5 * grad[:, :d].double())
         assert torch.allclose(table[:, :d].double(), want, rtol=1e-5, atol=1e-5 * max(1.0, M // 3) ** 0.5)
         assert (table[:, d:] == 3.0).all()                    # pad columns of a row are not written
+
+
+def test_shard_pack_buckets():
+    """dctr_shard_pack: slots ordered by owner go into equal-sized buckets; inv / src_of_dest are inverse to each other, unused
+    entries keep -1 / 0, an overflowing bucket is counted and its slots still point at a valid entry."""
+    import deepctr_b200.ops  # noqa: F401
+    O = torch.ops.deepctr
+    from deepctr_b200 import _lib as L
+    g = torch.Generator(device="cuda").manual_seed(21)
+    for world, M, C in ((2, 1000, 600), (3, 4097, 1500), (8, 50000, 7000), (4, 777, 100)):
+        ids = torch.randint(0, 100000, (M,), device="cuda", dtype=torch.int32, generator=g)
+        ids[: M // 5] = ids[0]                                 # a hot row: one owner gets a fuller bucket
+        owner = torch.remainder(ids, world).to(torch.int32)
+        owner_sorted, perm = torch.empty_like(ids), torch.empty_like(ids)
+        ws = torch.zeros(L.lib().dctr_sort_rows_workspace(M), dtype=torch.uint8, device="cuda")
+        O.sort_pairs(owner, None, M, world, owner_sorted, perm, ws)
+        send_ids = torch.full((world * C,), 7, dtype=torch.int32, device="cuda")
+        src = torch.full((world * C,), 7, dtype=torch.int32, device="cuda")
+        inv = torch.full((M,), -5, dtype=torch.int32, device="cuda")
+        status = torch.zeros(2, dtype=torch.int32, device="cuda")
+        O.shard_pack(ids, perm, owner_sorted, world, C, send_ids, src, inv, status)
+        torch.cuda.synchronize()
+        counts = torch.bincount(owner.long(), minlength=world)
+        lost = int((counts - C).clamp_min(0).sum())
+        assert int(status[0]) == lost and int(status[1]) == int(counts.max())
+        assert (inv >= 0).all() and (inv < world * C).all()
+        for o in range(world):
+            n = min(int(counts[o]), C)
+            slots = torch.nonzero(owner == o).flatten()[:n]                       # stable: original slot order inside a bucket
+            assert torch.equal(src[o * C:o * C + n].long(), slots)
+            assert torch.equal(send_ids[o * C:o * C + n], torch.div(ids[slots], world, rounding_mode="floor"))
+            assert torch.equal(inv[slots].long(), torch.arange(o * C, o * C + n, device="cuda"))
+            assert (send_ids[o * C + n:(o + 1) * C] == -1).all() and (src[o * C + n:(o + 1) * C] == 0).all()
