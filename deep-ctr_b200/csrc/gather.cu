@@ -4,6 +4,7 @@
 // Rows are fetched with 128-bit loads (row stride ld is a multiple of 4 floats, so a row is ld/4 LDG.128), scaled
 // by the field weight and staged in shared memory; the concat / IP / OP outputs are produced from the staged
 // block and written with warp-coalesced 128-bit stores.  HBM-bound: no tensor cores here by design.
+#include <string.h>
 #include "common.cuh"
 
 namespace dctr {
@@ -149,12 +150,28 @@ gather_concat_kernel(const int32_t* __restrict__ ids, const float* __restrict__ 
     }
 }
 
+// first element of the output row of slot `slot` (see cross_bwd_kernel); ldg is applied by the caller through the row pointer
+struct OutRow {
+    float* p;
+    __device__ __forceinline__ float& operator[](int64_t i) const { return p[i]; }
+};
+__device__ __forceinline__ OutRow out_row_impl(float* ge, int ldg, const int32_t* dest, float* const* peers, int64_t C, int rank, int64_t slot) {
+    if (!dest) return OutRow{ge + slot * ldg};
+    const int64_t dd = dest[slot];
+    if (!peers) return OutRow{ge + dd * ldg};
+    const int64_t o = dd / C;
+    return OutRow{peers[o] + ((int64_t)rank * C + (dd - o * C)) * ldg};
+}
+#define out_row(ge, dest, peers, C, rank, slot) out_row_impl(ge, ldg, dest, peers, C, rank, slot)
+
 template <int CROSS>
 __global__ void __launch_bounds__(kGatherWarps * 32)
 cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts, const float* __restrict__ table,
                  int ld, int N, int F, int d, const float* __restrict__ dz, int ldz,
-                 float* __restrict__ ge, int ldg, int X, int32_t* __restrict__ status, const int32_t* __restrict__ dest) {
-    // dest != NULL: slot (n, f) writes row dest[n * F + f] of ge instead of row n * F + f (the bucket order of the row-sharded exchange)
+                 float* __restrict__ ge, int ldg, int X, int32_t* __restrict__ status, const int32_t* __restrict__ dest,
+                 float* const* __restrict__ peers, int64_t C, int rank) {
+    // dest != NULL: slot (n, f) writes row dest[n * F + f] of ge instead of row n * F + f (the bucket order of the row-sharded exchange);
+    // peers != NULL: bucket o = dest / C lives on rank o -- the row goes to peers[o] at row rank * C + dest % C (a store over NVLink)
     pdl_sync();
     extern __shared__ __align__(16) float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -167,6 +184,8 @@ cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
     float* dc = e + F * ld * (CROSS == DCTR_CROSS_OP ? 2 : 1);      // dL/dcross
     float* tot = dc + crossw;                                       // OP only: sum_f e_f
 
+    // CROSS_NONE leaves the warp's shared-memory block unused: with a destination index it stages the sample's F rows there
+    const bool vec_rows = dest != nullptr && ldg <= ld && (ldg & 3) == 0;
     for (int64_t n = (int64_t)blockIdx.x * kGatherWarps + warp; n < N; n += (int64_t)gridDim.x * kGatherWarps) {
         const float* dzr = dz + n * (int64_t)ldz;
         if (CROSS != DCTR_CROSS_NONE) {
@@ -199,13 +218,24 @@ cross_bwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wts,
                 }
             }
             const float w = wts ? wts[n * F + f] : 1.f;
-            ge[(dest ? (int64_t)dest[n * F + f] : n * F + f) * (int64_t)ldg + c] = w * acc;
+            if (CROSS == DCTR_CROSS_NONE && vec_rows) e[f * ldg + c] = w * acc;       // staged: the rows leave as 128-bit stores below
+            else out_row(ge, dest, peers, C, rank, n * F + f)[(int64_t)0 * ldg + c] = w * acc;
         }
-        if (ldg > d) {
+        if (CROSS == DCTR_CROSS_NONE && vec_rows) {
+            // rows written in a caller-given order (bucket order, possibly into peer memory over NVLink): whole rows as 16-byte
+            // stores instead of one 4-byte store per lane and element
+            for (int t = lane; t < F * (ldg - d); t += 32) { const int f = t / (ldg - d); e[f * ldg + d + (t - f * (ldg - d))] = 0.f; }
+            __syncwarp();
+            const int q = ldg >> 2;
+            for (int t = lane; t < F * q; t += 32) {
+                const int f = t / q, j = t - f * q;
+                reinterpret_cast<float4*>(out_row(ge, dest, peers, C, rank, n * F + f).p)[j] = reinterpret_cast<const float4*>(e + f * ldg)[j];
+            }
+        } else if (ldg > d) {
             const int padw = ldg - d;
             for (int t = lane; t < F * padw; t += 32) {
                 const int f = t / padw;
-                ge[(dest ? (int64_t)dest[n * F + f] : n * F + f) * (int64_t)ldg + d + (t - f * padw)] = 0.f;
+                out_row(ge, dest, peers, C, rank, n * F + f)[d + (t - f * padw)] = 0.f;
             }
         }
         __syncwarp();
@@ -317,7 +347,7 @@ extern "C" int dctr_gather_concat_fwd(const int32_t* ids, const float* wts, cons
 
 static int cross_bwd_impl(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
                           int N, int F, int d, int cross, const float* dz, int ldz,
-                          float* ge, int ldg, const int32_t* dest, void* stream) {
+                          float* ge, int ldg, const int32_t* dest, float* const* peers, int64_t C, int rank, void* stream) {
     DCTR_REQUIRE(ids && table && dz && ge, "cross_bwd: null pointer");
     DCTR_REQUIRE(N >= 0 && F > 0 && F < 256 && d > 0 && d <= ld && (ld & 3) == 0 && ldg >= d, "cross_bwd: bad shape");
     DCTR_REQUIRE(cross >= 0 && cross <= 2 && X > 0, "cross_bwd: bad cross");
@@ -328,11 +358,11 @@ static int cross_bwd_impl(const int32_t* ids, const float* wts, const float* tab
     DCTR_REQUIRE(smem <= 200 * 1024, "cross_bwd: field block too large for shared memory");
     dim3 grid(gather_grid(N)), block(kGatherWarps * 32);
     cudaStream_t st = as_stream(stream);
-#define LAUNCH_B(C)                                                                                          \
+#define LAUNCH_B(CR)                                                                                          \
     do {                                                                                                     \
         if (smem > 48 * 1024)                                                                                \
-            cudaFuncSetAttribute(cross_bwd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        launch_k(cross_bwd_kernel<C>, grid, block, smem, st, ids, wts, table, ld, N, F, d, dz, ldz, ge, ldg, (int)X, id_status(), dest); \
+            cudaFuncSetAttribute(cross_bwd_kernel<CR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        launch_k(cross_bwd_kernel<CR>, grid, block, smem, st, ids, wts, table, ld, N, F, d, dz, ldz, ge, ldg, (int)X, id_status(), dest, peers, C, rank); \
     } while (0)
     if (cross == DCTR_CROSS_IP) LAUNCH_B(DCTR_CROSS_IP);
     else if (cross == DCTR_CROSS_OP) LAUNCH_B(DCTR_CROSS_OP);
@@ -344,14 +374,21 @@ static int cross_bwd_impl(const int32_t* ids, const float* wts, const float* tab
 extern "C" int dctr_cross_bwd(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
                               int N, int F, int d, int cross, const float* dz, int ldz,
                               float* ge, int ldg, void* stream) {
-    return cross_bwd_impl(ids, wts, table, X, ld, N, F, d, cross, dz, ldz, ge, ldg, nullptr, stream);
+    return cross_bwd_impl(ids, wts, table, X, ld, N, F, d, cross, dz, ldz, ge, ldg, nullptr, nullptr, 1, 0, stream);
 }
 
 extern "C" int dctr_cross_bwd_to(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
                                  int N, int F, int d, int cross, const float* dz, int ldz,
                                  float* ge, int ldg, const int32_t* dest, void* stream) {
     DCTR_REQUIRE(dest, "cross_bwd_to: null destination index");
-    return cross_bwd_impl(ids, wts, table, X, ld, N, F, d, cross, dz, ldz, ge, ldg, dest, stream);
+    return cross_bwd_impl(ids, wts, table, X, ld, N, F, d, cross, dz, ldz, ge, ldg, dest, nullptr, 1, 0, stream);
+}
+
+extern "C" int dctr_cross_bwd_push(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
+                                   int N, int F, int d, int cross, const float* dz, int ldz, int ldg, const int32_t* dest,
+                                   float* const* peers, int64_t C, int rank, void* stream) {
+    DCTR_REQUIRE(dest && peers && C >= 1 && rank >= 0, "cross_bwd_push: null destination index / peer table");
+    return cross_bwd_impl(ids, wts, table, X, ld, N, F, d, cross, dz, ldz, const_cast<float*>(dz), ldg, dest, peers, C, rank, stream);
 }
 
 extern "C" int dctr_arrange_fields(const int32_t* feats, const int32_t* feat_field, int N, int J, int F, int32_t pad_row,
@@ -420,6 +457,67 @@ extern "C" int dctr_shard_pack(const int32_t* ids, const int32_t* perm, const in
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
     launch_k(shard_pack_kernel, blocks, 256, 0, st, ids, perm, owner_sorted, M, world, C, send_ids, src_of_dest, inv, status);
     return check_launch("shard_pack_kernel");
+}
+
+// ---- owner-side lookup that delivers over peer memory: entry k of bucket s (the ids rank s asked this rank for) goes to row
+// rank * C + k of rank s's row buffer (peers[s]); unused entries (-1) are not transmitted.  One kernel instead of gather + all-to-all.
+namespace dctr {
+__global__ void __launch_bounds__(256)
+gather_rows_push_kernel(const int32_t* __restrict__ ids, const float4* __restrict__ table, int q, int64_t C, int world, int rank,
+                        float* const* __restrict__ peers, int X) {
+    pdl_sync();
+    const int64_t total = (int64_t)world * C * q;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = t / q;
+        const int c = (int)(t - i * q);
+        const int id = __ldg(ids + i);
+        if ((unsigned)id >= (unsigned)X) continue;
+        const int64_t s = i / C, k = i - s * C;
+        reinterpret_cast<float4*>(peers[s])[((int64_t)rank * C + k) * q + c] = __ldg(table + (int64_t)id * q + c);
+    }
+}
+}  // namespace dctr
+
+extern "C" int dctr_gather_rows_push(const int32_t* ids, const float* table, int64_t X, int ld, int64_t C, int world, int rank,
+                                     float* const* peers, void* stream) {
+    DCTR_REQUIRE(C >= 1 && world >= 1 && rank >= 0 && rank < world && X > 0 && ld > 0 && (ld & 3) == 0, "gather_rows_push: bad shape");
+    DCTR_REQUIRE(ids && table && peers && ((uintptr_t)table & 15) == 0, "gather_rows_push: null or unaligned pointer");
+    int blocks = ceil_div((int64_t)world * C * (ld / 4), 256);
+    if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+    launch_k(gather_rows_push_kernel, blocks, 256, 0, as_stream(stream), ids, reinterpret_cast<const float4*>(table), ld / 4, C, world, rank,
+             peers, (int)X);
+    return check_launch("gather_rows_push_kernel");
+}
+
+// ---- device buffers other processes of the node can map (CUDA IPC): the exchange buffers of the row-sharded step ------------------
+extern "C" int dctr_ipc_alloc(size_t bytes, void** ptr, unsigned char* handle64) {
+    DCTR_REQUIRE(ptr && handle64 && bytes > 0, "ipc_alloc: bad arguments");
+    cudaError_t e = cudaMalloc(ptr, bytes);
+    if (e == cudaSuccess) e = cudaMemset(*ptr, 0, bytes);
+    cudaIpcMemHandle_t h;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, *ptr);
+    if (e != cudaSuccess) { set_error("ipc_alloc: %s", cudaGetErrorString(e)); return DCTR_ECUDA; }
+    static_assert(sizeof(h) == 64, "CUDA IPC handle size");
+    memcpy(handle64, &h, 64);
+    return DCTR_OK;
+}
+extern "C" int dctr_ipc_open(const unsigned char* handle64, void** ptr) {
+    DCTR_REQUIRE(ptr && handle64, "ipc_open: bad arguments");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    cudaError_t e = cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { set_error("ipc_open: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); return DCTR_ECUDA; }
+    return DCTR_OK;
+}
+extern "C" int dctr_ipc_close(void* ptr) {
+    cudaError_t e = cudaIpcCloseMemHandle(ptr);
+    if (e != cudaSuccess) { set_error("ipc_close: %s", cudaGetErrorString(e)); return DCTR_ECUDA; }
+    return DCTR_OK;
+}
+extern "C" int dctr_ipc_free(void* ptr) {
+    cudaError_t e = cudaFree(ptr);
+    if (e != cudaSuccess) { set_error("ipc_free: %s", cudaGetErrorString(e)); return DCTR_ECUDA; }
+    return DCTR_OK;
 }
 
 extern "C" int dctr_gather_rows(const int32_t* ids, const float* table, int64_t X, int ld, int64_t M, float* out, void* stream) {

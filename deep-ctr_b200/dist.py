@@ -227,11 +227,65 @@ class ShardedStep(object):
         self.C, self.RC = C, RC
         self.send_ids, self.recv_ids, self.src_of_dest = torch.zeros(RC, **i32), torch.zeros(RC, **i32), torch.zeros(RC, **i32)
         self.gather_ids = torch.zeros(RC, **i32)
-        self.rows_buf, self.back = torch.zeros(RC, e.ld, **f32), torch.zeros(RC, e.ld, **f32)
-        self.send_g, self.recv_g = torch.zeros(RC, e.ldg, **f32), torch.zeros(RC, e.ldg, **f32)
+        self.p2p = self._setup_p2p(RC) if os.environ.get("DCTR_SHARD_P2P", "1") != "0" and self.world > 1 else False
+        if not self.p2p:
+            self.rows_buf, self.back = torch.zeros(RC, e.ld, **f32), torch.zeros(RC, e.ld, **f32)
+            self.send_g, self.recv_g = torch.zeros(RC, e.ldg, **f32), torch.zeros(RC, e.ldg, **f32)
         self.srows, self.spos = torch.zeros(RC, **i32), torch.zeros(RC, **i32)
         self.sws = torch.zeros(L.lib().dctr_sort_rows_workspace(RC), dtype=torch.uint8, device=e.dev)
         self.fws = torch.zeros(L.lib().dctr_scatter_workspace(RC, e.ld), dtype=torch.uint8, device=e.dev)
+
+    def _setup_p2p(self, RC):
+        """The two row-sized exchanges as kernels that store into peer memory: `back` (rows the owners deliver) and `recv_g` (per-slot
+        gradients the requesters deliver) live in cudaMalloc'ed buffers every rank of the node maps through CUDA IPC.  Returns False
+        (and the step keeps the NCCL all-to-alls) if any rank fails to allocate or map."""
+        import ctypes
+        import sys
+        e, dist = self.e, self.dist
+        mine, ok = [], True
+        try:
+            for cols in (e.ld, e.ldg):
+                ptr, h = ctypes.c_void_p(), (ctypes.c_ubyte * 64)()
+                L.call("dctr_ipc_alloc", RC * cols * 4, ctypes.byref(ptr), h)
+                mine.append((ptr.value, bytes(h)))
+        except Exception as ex:                                      # noqa: BLE001
+            ok, err = False, str(ex)
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, (ok, [h for _, h in mine]), group=self.group)
+        peers = [[0] * self.world for _ in range(2)]
+        if all(o for o, _ in everyone):
+            try:
+                for r, (_, handles) in enumerate(everyone):
+                    for b in range(2):
+                        if r == self.rank:
+                            peers[b][r] = mine[b][0]
+                        else:
+                            ptr = ctypes.c_void_p()
+                            L.call("dctr_ipc_open", (ctypes.c_ubyte * 64).from_buffer_copy(handles[b]), ctypes.byref(ptr))
+                            peers[b][r] = ptr.value
+            except Exception as ex:                                  # noqa: BLE001
+                ok, err = False, str(ex)
+        else:
+            ok, err = False, "a rank could not allocate"
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=e.dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if not int(flag.item()):
+            if self.rank == 0:
+                print("deepctr_b200.dist: peer-memory exchange unavailable (%s); using NCCL all-to-alls" % (err if not ok else "another rank failed"),
+                      file=sys.stderr)
+            for ptr, _ in mine:
+                L.call("dctr_ipc_free", ptr)
+            return False
+
+        class _Dev(object):                                          # torch view of memory this module owns (never freed before exit)
+            def __init__(self, ptr, shape):
+                self.__cuda_array_interface__ = {"shape": shape, "typestr": "<f4", "data": (ptr, False), "version": 3, "strides": None}
+        self.back = torch.as_tensor(_Dev(mine[0][0], (RC, e.ld)), device=e.dev)
+        self.recv_g = torch.as_tensor(_Dev(mine[1][0], (RC, e.ldg)), device=e.dev)
+        self.back_peers = torch.tensor(peers[0], dtype=torch.int64, device=e.dev)
+        self.recvg_peers = torch.tensor(peers[1], dtype=torch.int64, device=e.dev)
+        self.bar = torch.zeros(1, dtype=torch.float32, device=e.dev)
+        return True
 
     def check_overflow(self):
         """host side, after a step: a bucket that overflowed dropped slots -- the step is invalid"""
@@ -295,11 +349,19 @@ class ShardedStep(object):
                 L.call("dctr_set_id_status", None)
                 O.sort_pairs(self.recv_ids, None, self.RC, e.X, self.srows, self.spos, self.sws)
                 L.call("dctr_set_id_status", self.status_ptr)
-        torch.clamp(self.recv_ids, min=0, out=self.gather_ids)            # unused entries (-1) read row 0; nobody looks at them
-        O.gather_rows(self.gather_ids, e.table, self.rows_buf)
-        self._mark("owner gather")
-        dist.all_to_all_single(self.back, self.rows_buf, group=self.group)
-        self._mark("a2a rows")
+        if self.p2p:
+            # lookup + delivery in one kernel: every requested row is stored into the requester's buffer over NVLink (unused entries
+            # are not transmitted); the small all-reduce is the barrier after which every rank's `back` is complete
+            O.gather_rows_push(self.recv_ids, e.table, self.C, self.world, self.rank, self.back_peers, self.back)
+            self._mark("owner gather")
+            dist.all_reduce(self.bar, group=self.group)
+            self._mark("a2a rows")
+        else:
+            torch.clamp(self.recv_ids, min=0, out=self.gather_ids)            # unused entries (-1) read row 0; nobody looks at them
+            O.gather_rows(self.gather_ids, e.table, self.rows_buf)
+            self._mark("owner gather")
+            dist.all_to_all_single(self.back, self.rows_buf, group=self.group)
+            self._mark("a2a rows")
         self.last = None
         return self.inv, self.back
 
@@ -358,10 +420,16 @@ class ShardedStep(object):
         # the embedding side first: it only needs dz, and the weight-gradient GEMMs run next to it
         wts = None if e.wts_are_ones else e.wts
         # per-slot gradients written straight into the owner buckets (unused entries keep stale rows: the owner drops them)
-        O.cross_bwd_to(self.inv.view(N, F), None if wts is None else wts.view(N, F), self.back, d, L.CROSS[e.cross], dz, self.inv.view(-1),
-                       self.send_g)
-        self._mark("slot grads")
-        dist.all_to_all_single(self.recv_g, self.send_g, group=self.group)             # aligned with recv_ids
+        if self.p2p:      # ... of the OWNER's gradient buffer, over NVLink; the all-reduce is the barrier before the owners fold
+            O.cross_bwd_push(self.inv.view(N, F), None if wts is None else wts.view(N, F), self.back, d, L.CROSS[e.cross], dz,
+                             self.inv.view(-1), e.ldg, self.C, self.rank, self.recvg_peers, self.recv_g)
+            self._mark("slot grads")
+            dist.all_reduce(self.bar, group=self.group)
+        else:
+            O.cross_bwd_to(self.inv.view(N, F), None if wts is None else wts.view(N, F), self.back, d, L.CROSS[e.cross], dz, self.inv.view(-1),
+                           self.send_g)
+            self._mark("slot grads")
+            dist.all_to_all_single(self.recv_g, self.send_g, group=self.group)             # aligned with recv_ids
         self._mark("a2a grads")
         torch.cuda.current_stream(e.dev).wait_stream(e.side)                           # the sorted (row, position) list of the received slots
         e.table_update(self.srows, self.spos, self.RC, 1, self.recv_g, e.ldg, None, lr, decay, self.fws)

@@ -107,6 +107,25 @@ def cross_bwd_to(ids, wts, table, d, cross, dz, dest, ge):
            N, F, d, cross, _ptr(dz, _F32, "dz"), dz.stride(0), _ptr(ge, _F32, "ge"), ge.stride(0), _ptr(dest, _I32, "dest"), _st(ids))
 
 
+@_op("gather_rows_push", "(Tensor ids, Tensor table, int C, int world, int rank, Tensor peers, Tensor(a!) own) -> ()")
+def gather_rows_push(ids, table, C, world, rank, peers, own):
+    """peers: int64 [world] device tensor of row-buffer base pointers (peers[rank] == own.data_ptr()); `own` only declares the write"""
+    if ids.numel() < world * C or peers.numel() < world or peers.dtype != _I64:
+        raise ValueError("gather_rows_push: ids needs world * C entries, peers one int64 pointer per rank")
+    L.call("dctr_gather_rows_push", _ptr(ids, _I32, "ids"), _ptr(table, _F32, "table", 16), table.shape[0], table.stride(0), C, world, rank,
+           _ptr(peers, _I64, "peers", 8), _st(ids))
+
+
+@_op("cross_bwd_push", "(Tensor ids, Tensor? wts, Tensor table, int d, int cross, Tensor dz, Tensor dest, int ldg, int C, int rank, "
+     "Tensor peers, Tensor(a!) own) -> ()")
+def cross_bwd_push(ids, wts, table, d, cross, dz, dest, ldg, C, rank, peers, own):
+    N, F = ids.shape
+    if dest.numel() < N * F or peers.dtype != _I64:
+        raise ValueError("cross_bwd_push: dest needs one entry per slot, peers one int64 pointer per rank")
+    L.call("dctr_cross_bwd_push", _ptr(ids, _I32, "ids"), _ptr(wts, _F32, "wts"), _ptr(table, _F32, "table", 16), table.shape[0], table.stride(0),
+           N, F, d, cross, _ptr(dz, _F32, "dz"), dz.stride(0), ldg, _ptr(dest, _I32, "dest"), _ptr(peers, _I64, "peers", 8), C, rank, _st(ids))
+
+
 @_op("bag_fwd", "(Tensor ids, Tensor? wts, Tensor table, int H, Tensor? b0, int act, Tensor(a!) out) -> ()")
 def bag_fwd(ids, wts, table, H, b0, act, out):
     N, F = ids.shape

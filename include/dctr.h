@@ -128,6 +128,26 @@ int dctr_cross_bwd_to(const int32_t* ids, const float* wts, const float* table, 
                       int N, int F, int d, int cross, const float* dz, int ldz,
                       float* ge, int ldg, const int32_t* dest, void* stream);
 
+/* ---- the row-sharded exchanges as kernels that store into PEER memory (NVLink / NVSwitch), SURVEY 8(e) -------------------------
+ * Exchange buffers other ranks of the node can map: dctr_ipc_alloc (cudaMalloc + cudaIpcGetMemHandle, zero-filled; handle64 = the
+ * 64-byte CUDA IPC handle to pass to the other processes), dctr_ipc_open (cudaIpcOpenMemHandle with lazy peer access) on the
+ * receiving side, dctr_ipc_close / dctr_ipc_free at teardown.  peers = DEVICE array of `world` base pointers (own buffer included).
+ * dctr_gather_rows_push: the owner-side lookup + delivery in one kernel: entry k of bucket s of ids [world * C] (the owner-local
+ *   rows rank s asked for; -1 = unused, not transmitted) is stored to row rank * C + k of rank s's row buffer peers[s] ([world*C, ld]).
+ * dctr_cross_bwd_push: dctr_cross_bwd_to whose destination bucket o = dest / C lives on rank o: the per-slot gradient row goes to
+ *   row rank * C + dest % C of peers[o] ([world*C, ldg]).
+ * Ordering is the caller's: a collective (any NCCL call all ranks take part in) between the last reader of a buffer and the next
+ * remote writer, and one after the pushing kernel before the owner reads. */
+int dctr_ipc_alloc(size_t bytes, void** ptr, unsigned char* handle64);
+int dctr_ipc_open(const unsigned char* handle64, void** ptr);
+int dctr_ipc_close(void* ptr);
+int dctr_ipc_free(void* ptr);
+int dctr_gather_rows_push(const int32_t* ids, const float* table, int64_t X, int ld, int64_t C, int world, int rank,
+                          float* const* peers, void* stream);
+int dctr_cross_bwd_push(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
+                        int N, int F, int d, int cross, const float* dz, int ldz, int ldg, const int32_t* dest,
+                        float* const* peers, int64_t C, int rank, void* stream);
+
 /* ---- K1fm: fused gather + FM forward + sigmoid cross-entropy (FM.py:55-64, 33-38) -------------
  *   s[n,c] = sum_f x_f*row_f[c];  logit = s[n,0] + b + 0.5*sum_{c>=1}( s[n,c]^2 - sum_f x_f^2 row_f[c]^2 )
  *   pred = sigmoid(logit); loss_n = max(z,0) - z*y + log1p(exp(-|z|)); g[n] = (pred - y)*gscale

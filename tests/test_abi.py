@@ -85,7 +85,8 @@ def test_every_device_entry_point_is_a_torch_op(built_lib):
     import torch
     from deepctr_b200 import ops
     host_side = {"dctr_version", "dctr_last_error", "dctr_launch_count", "dctr_set_launch_mode", "dctr_set_id_status",
-                 "dctr_host_pack_fields", "dctr_mlp2_supported", "dctr_mlp2tc_supported", "dctr_col_wsum_static_max_h"}
+                 "dctr_host_pack_fields", "dctr_mlp2_supported", "dctr_mlp2tc_supported", "dctr_col_wsum_static_max_h",
+                 "dctr_ipc_alloc", "dctr_ipc_open", "dctr_ipc_close", "dctr_ipc_free"}
     merged = {"dctr_sort_rows": "sort_pairs", "dctr_arrange_fields": "arrange_update_list", "dctr_scatter_sgd_masked": "scatter_sgd",
               "dctr_out_bwd": "out_bwd_fused"}      # entry points that are special cases of another one's op
     for sym in declared_symbols():
