@@ -228,6 +228,7 @@ def call_cost(name, a):
 # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) from the committed `ncu --set full` captures
 # (profiles/r01_ncu_*.txt), keyed by C-ABI call and the workload it was captured on; null for kernels not captured.
 NCU_TRAFFIC = {
+    ("fnn_ipinyou", "dctr_mlp2tc_train"): 4.677e6 + 768.0,                     # profiles/r02_ncu_mlp2tc_final.txt (weights + x in, L2-resident outputs)
     ("fnn_criteo", "dctr_gemm_tc[NN 65536x400x430]"): 114.06e6 + 70.96e6,      # profiles/r01_ncu_criteo_gemm_tc_kernel_v2.txt
     ("fnn_criteo", "dctr_col_wsum"): 109.07e6 + 4.51e6,                       # profiles/r01_ncu_criteo_col_wsum_kernel.txt
     # hist + 2 wide passes at M = 65536: the lists live in L2, only cold reads reach DRAM (profiles/r01_ncu_fnn_sort_kernels_step_size.txt)

@@ -131,16 +131,30 @@ __device__ __forceinline__ float4 clip4(float4 v, int col, int H, bool ok) {
 }
 
 // ---- the two views of a warp's [32 rows x 32 columns] chunk inside a K-major SWIZZLE_128B tile -------------------------------------
+// Two accumulators per sample out of the idle half of the tile (kQRows == 16).  The tensor core TRUNCATES when it adds an MMA's
+// products to the accumulator -- a bias that grows with the number of inexact additions (one accumulator, K = 300: ~3e-6 relative,
+// and it compounds over the four chained GEMMs).  Tensor memory has no room for a second accumulator, but rows 16-31 of every
+// quadrant are idle: the 16-byte column j of sample row r is stored in row r + 16 * ((j >> 1) & 1), i.e. the k-steps (8 columns)
+// of a chunk alternate between the sample's two rows and every other position of both rows stays zero.  Adding an exact zero is
+// exact, so each row sees half of the inexact additions; the epilogue adds TMEM lanes r and r + 16 (one shuffle per value).
+__device__ __forceinline__ int split_row(int j) { return kQRows == 16 ? 16 * ((j >> 1) & 1) : 0; }
 // row-per-lane (TMEM order): lane = row, 16-byte column i
 __device__ __forceinline__ uint32_t off_lane(int quad, int lane, int i) {
-    const int R = quad * 32 + lane;
+    const int R = quad * 32 + lane + split_row(i);
     return (uint32_t)((R >> 3) * 1024 + (R & 7) * 128 + ((i ^ (R & 7)) << 4));
 }
 // row-major (global-memory order): step t < 8, lane -> row 4 t + (lane >> 3), 16-byte column lane & 7
 __device__ __forceinline__ int rm_row(int t, int lane) { return 4 * t + (lane >> 3); }
 __device__ __forceinline__ uint32_t off_rm(int quad, int t, int lane) {
-    const int R = quad * 32 + rm_row(t, lane), j = lane & 7;
+    const int j = lane & 7, R = quad * 32 + rm_row(t, lane) + split_row(j);
     return (uint32_t)((R >> 3) * 1024 + (R & 7) * 128 + ((j ^ (R & 7)) << 4));
+}
+// the two partial accumulators of a sample live in TMEM lanes r and r + 16: after this, lanes < 16 (and their mirrors) hold the sum
+template <int NV>
+__device__ __forceinline__ void join_split(float (&v)[NV]) {
+    if (kQRows != 16) return;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) v[j] += __shfl_xor_sync(0xffffffffu, v[j], 16);
 }
 __device__ __forceinline__ void park_rows(uint8_t* tile, int quad, int lane, const float (&v)[32]) {
     if (lane >= kQRows) return;                // rows past the quadrant's share stay zero
@@ -349,6 +363,7 @@ mlp2tc_train_kernel(const Args a) {
             const int g = gbase + c, slot = g % kASlots, col = 32 * c + j4;
             uint8_t* sl = aring + slot * kASlot;
             tmem_ld32(tlane + a.ph[0].acc_col + 32 * c, v);
+            join_split(v);
             mbar_wait(a_empty + slot, ((g / kASlots) & 1) ^ 1);
             park_rows(sl, quad, lane, v);
             __syncwarp();
@@ -381,6 +396,7 @@ mlp2tc_train_kernel(const Args a) {
                     const int c0 = 32 * c + 8 * q;
                     float z8[8];
                     tmem_ld8(tlane + a.ph[1].acc_col + c0, z8);
+                    join_split(z8);
                     float4 u0 = act4(a.act2, add4(make_float4(z8[0], z8[1], z8[2], z8[3]), *reinterpret_cast<const float4*>(sb2 + c0)));
                     float4 u1 = act4(a.act2, add4(make_float4(z8[4], z8[5], z8[6], z8[7]), *reinterpret_cast<const float4*>(sb2 + c0 + 4)));
                     if (a.m2) {
@@ -423,6 +439,7 @@ mlp2tc_train_kernel(const Args a) {
             const int g = gbase + c, slot = g % kASlots, col = 32 * c + j4;
             uint8_t* sl = aring + slot * kASlot;
             tmem_ld32(tlane + a.ph[1].acc_col + 32 * c, v);
+            join_split(v);
             mbar_wait(a_empty + slot, ((g / kASlots) & 1) ^ 1);
             park_rows(sl, quad, lane, v);
             __syncwarp();
@@ -473,6 +490,7 @@ mlp2tc_train_kernel(const Args a) {
             mbar_wait(a_empty + slot, ((g / kASlots) & 1) ^ 1);
             rm_fetch(sl + kATile, a.a1, a.ld1, row0, col, a.N, a.ld1, quad, lane);      // this thread's own stores of the F1 epilogue (same mapping)
             tmem_ld32(tlane + a.ph[2].acc_col + 32 * c, v);
+            join_split(v);
             park_rows(sl, quad, lane, v);
             cp_async_wait_all();
             __syncwarp();
@@ -491,6 +509,7 @@ mlp2tc_train_kernel(const Args a) {
             const int col = 32 * c + j4;
             rm_fetch(stg + kATile, a.x, a.ld0, row0, col, a.N, a.ld0, quad, lane);      // masked in place by this thread in the first loop
             tmem_ld32(tlane + a.ph[3].acc_col + 32 * c, v);
+            join_split(v);
             park_rows(stg, quad, lane, v);
             cp_async_wait_all();
             __syncwarp();
