@@ -324,30 +324,39 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
             if (mbase < p.M) tc_store_dispatch(p, C, tile, mbase, n0 + c, lane, v, ax);
             if (c + kCStep < BN) tc_prefetch_aux(p, mbase, n0 + c + kCStep + lane, ax);
         }
-    } else if (warp == kTmaWarp && lane == 0) {
-        // ===== TMA producer =====
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapB)) : "memory");
+    } else if (warp == kTmaWarp) {
+        // ===== TMA producer ===== (all lanes run the loop, one elected lane issues -- see the MMA issuer below)
+        if (elect_one()) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapB)) : "memory");
+        }
+        __syncwarp();
         for (int kb = 0; kb < nkb; ++kb) {
             const int s = kb % NS;
-            mbar_wait(empty + s, ((kb / NS) & 1) ^ 1);
+            mbar_wait<64>(empty + s, ((kb / NS) & 1) ^ 1);
             uint8_t* st = smem + s * S::kStage;
             const int k0 = kbeg + kb * kBKf;
-            mbar_expect_tx(raw_full + s, S::kA + S::kB);
-            if (AK) tma_load_2d(st, &mapA, k0, m0, raw_full + s);
-            else {
+            if (elect_one()) {
+                mbar_expect_tx(raw_full + s, S::kA + S::kB);
+                if (AK) tma_load_2d(st, &mapA, k0, m0, raw_full + s);
+                else {
 #pragma unroll
-                for (int i = 0; i < kBM / 32; ++i) tma_load_2d(st + i * 4096, &mapA, m0 + 32 * i, k0, raw_full + s);
-            }
-            uint8_t* sb = st + S::kA;
-            if (BK) tma_load_2d(sb, &mapB, k0, n0, raw_full + s);
-            else {
+                    for (int i = 0; i < kBM / 32; ++i) tma_load_2d(st + i * 4096, &mapA, m0 + 32 * i, k0, raw_full + s);
+                }
+                uint8_t* sb = st + S::kA;
+                if (BK) tma_load_2d(sb, &mapB, k0, n0, raw_full + s);
+                else {
 #pragma unroll
-                for (int i = 0; i < BN / 32; ++i) tma_load_2d(sb + i * 4096, &mapB, n0 + 32 * i, k0, raw_full + s);
+                    for (int i = 0; i < BN / 32; ++i) tma_load_2d(sb + i * 4096, &mapB, n0 + 32 * i, k0, raw_full + s);
+                }
             }
+            __syncwarp();
         }
-    } else if (warp == kMmaWarp && lane == 0) {
+    } else if (warp == kMmaWarp) {
         // ===== MMA issuer =====
+        // All 32 lanes run the loop and the waits, one elected lane issues: inside `if (lane == 0)` ptxas cannot prove the
+        // descriptors warp-uniform and wraps EVERY tcgen05.mma in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop (~70 ns per MMA,
+        // measured in mlp2tc.cu -- more than the 34 ns a 128 x 128 x 8 tf32 MMA takes).
         // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (1 << 4), A = B = TF32 (2 << 7, 2 << 10),
         // a_major bit 15 = 0 (A comes from TMEM: always K-major) / b_major bit 16 (0 = K-major, 1 = MN-major),
         // N >> 3 at bit 17, M >> 4 at bit 24
@@ -355,27 +364,32 @@ gemm_tc_kernel(const TcParams p, const __grid_constant__ CUtensorMap mapA, const
                                    ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
         for (int kb = 0; kb < nkb; ++kb) {
             const int s = kb % NS, ts = kb % T::kSlots;
-            mbar_wait(conv_full + s, (kb / NS) & 1);
+            mbar_wait<32>(conv_full + s, (kb / NS) & 1);
             tc_fence_after();
             const uint32_t sb = smem_u32(smem + s * S::kStage) + S::kA;
             const uint32_t ta = tmem_a0 + ts * 64;
+            const uint64_t b_hi0 = BK ? make_desc(sb) : make_desc_mn(sb), b_lo0 = BK ? make_desc(sb + S::kB) : make_desc_mn(sb + S::kB);
+            constexpr uint64_t bstep = BK ? 2 : (1024 >> 4);     // B: +32 B inside a K-major row, +1024 B (8 k-rows = 2 atoms) MN-major
+            if (elect_one()) {
 #pragma unroll
-            for (int k4 = 0; k4 < kBKf / 8; ++k4) {           // UMMA_K = 8 tf32: 8 TMEM columns of A; B +32 B inside a K-major row, +1024 B (8 k-rows = 2 atoms) MN-major
-                const uint32_t a_hi = ta + k4 * 8, a_lo = ta + 32 + k4 * 8;
-                const uint64_t b_hi = BK ? make_desc(sb) + 2 * k4 : make_desc_mn(sb + k4 * 1024);
-                const uint64_t b_lo = BK ? make_desc(sb + S::kB) + 2 * k4 : make_desc_mn(sb + S::kB + k4 * 1024);
-                // Several accumulators shorten every addition chain (the tensor core truncates when it accumulates): the
-                // hi*hi products of k-step t go to accumulator t % kHiAcc, the two small cross terms to the last one;
-                // the epilogue adds them up in fp32.
-                const int t = kb * (kBKf / 8) + k4;
-                mma_tf32_ts(tmem_base + kHiAcc * BN, a_lo, b_hi, idesc, t != 0);
-                mma_tf32_ts(tmem_base + kHiAcc * BN, a_hi, b_lo, idesc, 1);
-                mma_tf32_ts(tmem_base + (t % kHiAcc) * BN, a_hi, b_hi, idesc, t >= kHiAcc);
+                for (int k4 = 0; k4 < kBKf / 8; ++k4) {           // UMMA_K = 8 tf32: 8 TMEM columns of A
+                    const uint32_t a_hi = ta + k4 * 8, a_lo = ta + 32 + k4 * 8;
+                    const uint64_t b_hi = b_hi0 + bstep * k4, b_lo = b_lo0 + bstep * k4;
+                    // Several accumulators shorten every addition chain (the tensor core truncates when it accumulates): the
+                    // hi*hi products of k-step t go to accumulator t % kHiAcc, the two small cross terms to the last one;
+                    // the epilogue adds them up in fp32.
+                    const int t = kb * (kBKf / 8) + k4;
+                    mma_tf32_ts(tmem_base + kHiAcc * BN, a_lo, b_hi, idesc, t != 0);
+                    mma_tf32_ts(tmem_base + kHiAcc * BN, a_hi, b_lo, idesc, 1);
+                    mma_tf32_ts(tmem_base + (t % kHiAcc) * BN, a_hi, b_hi, idesc, t >= kHiAcc);
+                }
+                mma_commit(empty + s);        // frees the shared-memory stage when these MMAs have read it ...
+                mma_commit(a_empty + ts);     // ... and the TMEM A slot
             }
-            mma_commit(empty + s);        // frees the shared-memory stage when these MMAs have read it ...
-            mma_commit(a_empty + ts);     // ... and the TMEM A slot
+            __syncwarp();
         }
-        if (nkb > 0) mma_commit(accum_full);
+        if (nkb > 0 && elect_one()) mma_commit(accum_full);
+        __syncwarp();
     }
     tc_fence_before();
     __syncthreads();
