@@ -489,6 +489,46 @@ extern "C" int dctr_gather_rows_push(const int32_t* ids, const float* table, int
     return check_launch("gather_rows_push_kernel");
 }
 
+// ---- per-slot gradients of a model WITHOUT a cross layer, delivered in BUCKET order: entry i of the owner buckets (slot
+// src_of_dest[i], valid where send_ids[i] >= 0) is wts * dz[n, f*d .. f*d+d) and goes to row rank * C + i % C of rank i / C's gradient
+// buffer.  Walking the destination order makes every remote store stream contiguous rows (the sample-order kernel, dctr_cross_bwd_push,
+// scatters 48-byte rows over the owners: 360 GB/s at 8 GPUs); the scattered side is the local, cheap one.
+namespace dctr {
+__global__ void __launch_bounds__(256)
+slot_grads_push_kernel(const int32_t* __restrict__ send_ids, const int32_t* __restrict__ src_of_dest, const float* __restrict__ wts,
+                       const float* __restrict__ dz, int64_t ldz, int F, int d, int q4, int64_t C, int world, int rank,
+                       float* const* __restrict__ peers) {
+    pdl_sync();
+    const int64_t total = (int64_t)world * C * q4;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = t / q4;
+        const int c = 4 * (int)(t - i * q4);
+        if (__ldg(send_ids + i) < 0) continue;
+        const int slot = __ldg(src_of_dest + i);
+        const int n = slot / F, f = slot - n * F;
+        const float w = wts ? __ldg(wts + slot) : 1.f;
+        const float* src = dz + (int64_t)n * ldz + (int64_t)f * d + c;
+        float4 v;
+        v.x = c < d ? w * __ldg(src) : 0.f;
+        v.y = c + 1 < d ? w * __ldg(src + 1) : 0.f;
+        v.z = c + 2 < d ? w * __ldg(src + 2) : 0.f;
+        v.w = c + 3 < d ? w * __ldg(src + 3) : 0.f;
+        const int64_t o = i / C, k = i - o * C;
+        reinterpret_cast<float4*>(peers[o])[((int64_t)rank * C + k) * q4 + (c >> 2)] = v;
+    }
+}
+}  // namespace dctr
+
+extern "C" int dctr_slot_grads_push(const int32_t* send_ids, const int32_t* src_of_dest, const float* wts, const float* dz, int64_t ldz,
+                                    int F, int d, int ldg, int64_t C, int world, int rank, float* const* peers, void* stream) {
+    DCTR_REQUIRE(send_ids && src_of_dest && dz && peers, "slot_grads_push: null pointer");
+    DCTR_REQUIRE(F > 0 && d > 0 && ldg >= d && (ldg & 3) == 0 && C >= 1 && world >= 1 && rank >= 0 && rank < world, "slot_grads_push: bad shape");
+    int blocks = ceil_div((int64_t)world * C * (ldg / 4), 256);
+    if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+    launch_k(slot_grads_push_kernel, blocks, 256, 0, as_stream(stream), send_ids, src_of_dest, wts, dz, ldz, F, d, ldg / 4, C, world, rank, peers);
+    return check_launch("slot_grads_push_kernel");
+}
+
 // ---- device buffers other processes of the node can map (CUDA IPC): the exchange buffers of the row-sharded step ------------------
 extern "C" int dctr_ipc_alloc(size_t bytes, void** ptr, unsigned char* handle64) {
     DCTR_REQUIRE(ptr && handle64 && bytes > 0, "ipc_alloc: bad arguments");

@@ -195,6 +195,8 @@ class ShardedStep(object):
         self.overflow = torch.zeros(2, **i32)       # [slots that did not fit a bucket since the last check, fullest bucket seen]
         self._prof = [] if os.environ.get("DCTR_SHARD_PROFILE") else None
         self._train = False
+        self._ar_pending = False
+        self.ar_stream = torch.cuda.Stream(device=e.dev)
 
     def _mark(self, name):
         """DCTR_SHARD_PROFILE=1 (eager steps only): CUDA events between the phases of a step; summary() prints the averages"""
@@ -421,10 +423,23 @@ class ShardedStep(object):
         wts = None if e.wts_are_ones else e.wts
         # per-slot gradients written straight into the owner buckets (unused entries keep stale rows: the owner drops them)
         if self.p2p:      # ... of the OWNER's gradient buffer, over NVLink; the all-reduce is the barrier before the owners fold
-            O.cross_bwd_push(self.inv.view(N, F), None if wts is None else wts.view(N, F), self.back, d, L.CROSS[e.cross], dz,
-                             self.inv.view(-1), e.ldg, self.C, self.rank, self.recvg_peers, self.recv_g)
+            if e.cross == "none":     # no cross term: walk the buckets, every remote store streams contiguous rows
+                O.slot_grads_push(self.send_ids, self.src_of_dest, None if wts is None else wts.view(-1), dz, F, d, e.ldg, self.C, self.world,
+                                  self.rank, self.recvg_peers, self.recv_g)
+            else:
+                O.cross_bwd_push(self.inv.view(N, F), None if wts is None else wts.view(N, F), self.back, d, L.CROSS[e.cross], dz,
+                                 self.inv.view(-1), e.ldg, self.C, self.rank, self.recvg_peers, self.recv_g)
             self._mark("slot grads")
             dist.all_reduce(self.bar, group=self.group)
+            # the dense gradients' all-reduce only needs the weight gradients: issued AFTER the barrier (collectives keep their issue
+            # order) on its own stream, it runs next to the owners' fold instead of behind it
+            main = torch.cuda.current_stream(e.dev)
+            self.ar_stream.wait_stream(main)
+            with torch.cuda.stream(self.ar_stream):
+                e.join_wgrad()
+                allreduce_dense(dist, e.grads, self.group)
+                allreduce_dense(dist, e.loss, self.group)
+            self._ar_pending = True
         else:
             O.cross_bwd_to(self.inv.view(N, F), None if wts is None else wts.view(N, F), self.back, d, L.CROSS[e.cross], dz, self.inv.view(-1),
                            self.send_g)
@@ -434,9 +449,13 @@ class ShardedStep(object):
         torch.cuda.current_stream(e.dev).wait_stream(e.side)                           # the sorted (row, position) list of the received slots
         e.table_update(self.srows, self.spos, self.RC, 1, self.recv_g, e.ldg, None, lr, decay, self.fws)
         self._mark("fold")
-        e.join_wgrad()
-        allreduce_dense(dist, e.grads, self.group)
-        allreduce_dense(dist, e.loss, self.group)
+        if self._ar_pending:
+            torch.cuda.current_stream(e.dev).wait_stream(self.ar_stream)
+            self._ar_pending = False
+        else:
+            e.join_wgrad()
+            allreduce_dense(dist, e.grads, self.group)
+            allreduce_dense(dist, e.loss, self.group)
         self._mark("allreduce dense")
         e.dense_update(lr, last_decay)
         self._mark("dense update")

@@ -116,6 +116,15 @@ def gather_rows_push(ids, table, C, world, rank, peers, own):
            _ptr(peers, _I64, "peers", 8), _st(ids))
 
 
+@_op("slot_grads_push", "(Tensor send_ids, Tensor src_of_dest, Tensor? wts, Tensor dz, int F, int d, int ldg, int C, int world, int rank, "
+     "Tensor peers, Tensor(a!) own) -> ()")
+def slot_grads_push(send_ids, src_of_dest, wts, dz, F, d, ldg, C, world, rank, peers, own):
+    if send_ids.numel() < world * C or src_of_dest.numel() < world * C or peers.dtype != _I64 or peers.numel() < world:
+        raise ValueError("slot_grads_push: send_ids / src_of_dest need world * C entries, peers one int64 pointer per rank")
+    L.call("dctr_slot_grads_push", _ptr(send_ids, _I32, "send_ids"), _ptr(src_of_dest, _I32, "src_of_dest"), _ptr(wts, _F32, "wts"),
+           _ptr(dz, _F32, "dz"), dz.stride(0), F, d, ldg, C, world, rank, _ptr(peers, _I64, "peers", 8), _st(dz))
+
+
 @_op("cross_bwd_push", "(Tensor ids, Tensor? wts, Tensor table, int d, int cross, Tensor dz, Tensor dest, int ldg, int C, int rank, "
      "Tensor peers, Tensor(a!) own) -> ()")
 def cross_bwd_push(ids, wts, table, d, cross, dz, dest, ldg, C, rank, peers, own):

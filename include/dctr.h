@@ -144,6 +144,11 @@ int dctr_ipc_close(void* ptr);
 int dctr_ipc_free(void* ptr);
 int dctr_gather_rows_push(const int32_t* ids, const float* table, int64_t X, int ld, int64_t C, int world, int rank,
                           float* const* peers, void* stream);
+/* models without a cross layer (TF layout, embedding block first): the same delivery walked in BUCKET order, so that every remote
+ * store streams contiguous rows: entry i (slot src_of_dest[i], valid where send_ids[i] >= 0; both from dctr_shard_pack) =
+ * wts[slot] * dz[n, f*d .. f*d+d) -> row rank * C + i % C of peers[i / C] ([world*C, ldg]) */
+int dctr_slot_grads_push(const int32_t* send_ids, const int32_t* src_of_dest, const float* wts, const float* dz, int64_t ldz,
+                         int F, int d, int ldg, int64_t C, int world, int rank, float* const* peers, void* stream);
 int dctr_cross_bwd_push(const int32_t* ids, const float* wts, const float* table, int64_t X, int ld,
                         int N, int F, int d, int cross, const float* dz, int ldz, int ldg, const int32_t* dest,
                         float* const* peers, int64_t C, int rank, void* stream);

@@ -219,3 +219,42 @@ def test_shard_pack_buckets():
             assert torch.equal(send_ids[o * C:o * C + n], torch.div(ids[slots], world, rounding_mode="floor"))
             assert torch.equal(inv[slots].long(), torch.arange(o * C, o * C + n, device="cuda"))
             assert (send_ids[o * C + n:(o + 1) * C] == -1).all() and (src[o * C + n:(o + 1) * C] == 0).all()
+
+
+@pytest.mark.gpu
+def test_slot_grads_push_matches_the_sample_order_delivery():
+    """dctr_slot_grads_push (bucket order) writes exactly what the per-slot gradient of a model without a cross layer is:
+    wts * dz[n, f*d .. f*d+d) at row rank * C + k of the owner's buffer; padded columns zero, unused rows untouched."""
+    import deepctr_b200.ops  # noqa: F401
+    O = torch.ops.deepctr
+    from deepctr_b200 import _lib as L
+    g = torch.Generator(device="cuda").manual_seed(5)
+    for world, rank, N, F, d, weighted in ((2, 1, 300, 7, 11, True), (4, 0, 1025, 39, 10, False), (3, 2, 64, 5, 4, True)):
+        M, ldg = N * F, (d + 3) // 4 * 4
+        C = int(M / world * 1.3) + 8
+        ids = torch.randint(0, 5000, (M,), device="cuda", dtype=torch.int32, generator=g)
+        owner = torch.remainder(ids, world).to(torch.int32)
+        owner_sorted, perm = torch.empty_like(ids), torch.empty_like(ids)
+        ws = torch.zeros(L.lib().dctr_sort_rows_workspace(M), dtype=torch.uint8, device="cuda")
+        O.sort_pairs(owner, None, M, world, owner_sorted, perm, ws)
+        send_ids = torch.empty(world * C, dtype=torch.int32, device="cuda")
+        src = torch.empty(world * C, dtype=torch.int32, device="cuda")
+        inv = torch.empty(M, dtype=torch.int32, device="cuda")
+        status = torch.zeros(2, dtype=torch.int32, device="cuda")
+        O.shard_pack(ids, perm, owner_sorted, world, C, send_ids, src, inv, status)
+        assert int(status[0]) == 0
+        dz = torch.randn(N, F * d + 3, device="cuda", generator=g)[:, : F * d + 1]          # a strided view, bias column last
+        wts = torch.rand(M, device="cuda", generator=g) if weighted else None
+        bufs = [torch.full((world * C, ldg), 9.0, device="cuda") for _ in range(world)]
+        peers = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device="cuda")
+        O.slot_grads_push(send_ids, src, wts, dz, F, d, ldg, C, world, rank, peers, bufs[rank])
+        torch.cuda.synchronize()
+        rows = dz[:, : F * d].reshape(M, d) * (wts[:, None] if weighted else 1.0)
+        for o in range(world):
+            want = torch.full((world * C, ldg), 9.0, device="cuda")
+            valid = torch.nonzero(send_ids[o * C:(o + 1) * C] >= 0).flatten()
+            blk = torch.zeros(valid.numel(), ldg, device="cuda")
+            blk[:, :d] = rows[src[o * C + valid].long()]
+            want[rank * C + valid] = blk
+            assert torch.equal(bufs[o], want), (world, rank, o)
+
