@@ -35,6 +35,7 @@ SIGNATURES = {
     "dctr_slot_grads_push": (_i, [_p, _p, _p, _p, _l, _i, _i, _i, _l, _i, _i, _p, _p]),
     "dctr_cross_bwd_push": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _i, _p, _i, _i, _p, _p, _l, _i, _p]),
     "dctr_shard_pack": (_i, [_p, _p, _p, _l, _i, _l, _p, _p, _p, _p, _p]),
+    "dctr_shard_pack_push": (_i, [_p, _p, _p, _l, _i, _l, _p, _p, _p, _p, _i, _p, _p]),
     "dctr_host_pack_fields": (_i, [_p, _i, _p, _p, _p, _l, _i, _i, _p, _p, _i]),
     "dctr_cross_bwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _i, _p, _i, _p, _i, _p]),
     "dctr_cross_bwd_to": (_i, [_p, _p, _p, _l, _i, _i, _i, _i, _i, _p, _i, _p, _i, _p, _p]),

@@ -417,7 +417,7 @@ namespace dctr {
 __global__ void __launch_bounds__(256)
 shard_pack_kernel(const int32_t* __restrict__ ids, const int32_t* __restrict__ perm, const int32_t* __restrict__ owner_sorted, int64_t M,
                   int world, int64_t C, int32_t* __restrict__ send_ids, int32_t* __restrict__ src_of_dest, int32_t* __restrict__ inv,
-                  int32_t* __restrict__ status) {
+                  int32_t* __restrict__ status, int rank, int32_t* const* __restrict__ peers) {
     pdl_sync();
     __shared__ int64_t s_first[65];
     if ((int)threadIdx.x <= world) {            // first position of every owner in the sorted list (lower bound), [world] = M
@@ -441,22 +441,43 @@ shard_pack_kernel(const int32_t* __restrict__ ids, const int32_t* __restrict__ p
             atomicAdd(status, 1);
         }
     }
+    if (!peers) return;
+    // delivery of the id buckets over peer memory: bucket o -- its unused tail (-1) included -- is block `rank` of rank o's
+    // request list, walked in destination order so that the remote stores are contiguous
+    const int64_t total = (int64_t)world * C;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int o = (int)(t / C);
+        const int64_t k = t - (int64_t)o * C, i = s_first[o] + k;
+        peers[o][(int64_t)rank * C + k] = i < s_first[o + 1] ? ids[perm[i]] / world : -1;
+    }
 }
 }  // namespace dctr
 
-extern "C" int dctr_shard_pack(const int32_t* ids, const int32_t* perm, const int32_t* owner_sorted, int64_t M, int world, int64_t C,
-                               int32_t* send_ids, int32_t* src_of_dest, int32_t* inv, int32_t* status, void* stream) {
+static int shard_pack_impl(const int32_t* ids, const int32_t* perm, const int32_t* owner_sorted, int64_t M, int world, int64_t C,
+                           int32_t* send_ids, int32_t* src_of_dest, int32_t* inv, int32_t* status, int rank, int32_t* const* peers, void* stream) {
     DCTR_REQUIRE(M >= 0 && world >= 1 && world <= 64 && C >= 1 && (int64_t)world * C < ((int64_t)1 << 31), "shard_pack: bad shape");
     DCTR_REQUIRE(send_ids && src_of_dest && status && (M == 0 || (ids && perm && owner_sorted && inv)), "shard_pack: null pointer");
     cudaStream_t st = as_stream(stream);
     cudaError_t e = cudaMemsetAsync(send_ids, 0xFF, (size_t)world * C * sizeof(int32_t), st);
     if (e == cudaSuccess) e = cudaMemsetAsync(src_of_dest, 0, (size_t)world * C * sizeof(int32_t), st);
     if (e != cudaSuccess) { set_error("shard_pack: cudaMemsetAsync: %s", cudaGetErrorString(e)); return DCTR_ECUDA; }
-    if (M == 0) return DCTR_OK;
-    int blocks = ceil_div(M, 256);
+    if (M == 0 && !peers) return DCTR_OK;
+    int blocks = ceil_div(M > (int64_t)world * C ? M : (int64_t)world * C, 256);
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    launch_k(shard_pack_kernel, blocks, 256, 0, st, ids, perm, owner_sorted, M, world, C, send_ids, src_of_dest, inv, status);
+    launch_k(shard_pack_kernel, blocks, 256, 0, st, ids, perm, owner_sorted, M, world, C, send_ids, src_of_dest, inv, status, rank, peers);
     return check_launch("shard_pack_kernel");
+}
+
+extern "C" int dctr_shard_pack(const int32_t* ids, const int32_t* perm, const int32_t* owner_sorted, int64_t M, int world, int64_t C,
+                               int32_t* send_ids, int32_t* src_of_dest, int32_t* inv, int32_t* status, void* stream) {
+    return shard_pack_impl(ids, perm, owner_sorted, M, world, C, send_ids, src_of_dest, inv, status, 0, nullptr, stream);
+}
+
+extern "C" int dctr_shard_pack_push(const int32_t* ids, const int32_t* perm, const int32_t* owner_sorted, int64_t M, int world, int64_t C,
+                                    int32_t* send_ids, int32_t* src_of_dest, int32_t* inv, int32_t* status, int rank, int32_t* const* peers,
+                                    void* stream) {
+    DCTR_REQUIRE(peers && rank >= 0 && rank < world, "shard_pack_push: null peer table / bad rank");
+    return shard_pack_impl(ids, perm, owner_sorted, M, world, C, send_ids, src_of_dest, inv, status, rank, peers, stream);
 }
 
 // ---- owner-side lookup that delivers over peer memory: entry k of bucket s (the ids rank s asked this rank for) goes to row

@@ -61,6 +61,7 @@ class DataParallelStep(object):
         self.gids = torch.zeros(W * e.N, e.F, **i32)
         self.gwts = torch.zeros(W * e.N, e.F, **f32)
         self.loss_slot = e.grads[e.n_params:e.n_params + 1]
+        self.ar_stream = torch.cuda.Stream(device=e.dev)
         if self.is_fm:
             self.gg, self.gs = torch.zeros(W * e.N, **f32), torch.zeros(W * e.N, e.lds, **f32)
         elif e.cross != "none":
@@ -107,10 +108,15 @@ class DataParallelStep(object):
             g, g_ld_f, w = self._gather(self.gg, e.ge), e.ldg, None
         else:
             g, g_ld_f, w = self._gather(self.gg, dz)[:, (1 if e.bias_first else 0):], d, gwts
-        e.join_wgrad()
-        self._reduce_dense()
+        # the dense all-reduce (issued after the gradient all-gather: collectives keep their issue order) runs on its own stream next
+        # to the fold, which only needs the gathered slot gradients and the sorted global list
+        self.ar_stream.wait_stream(cur)
+        with torch.cuda.stream(self.ar_stream):
+            e.join_wgrad()
+            self._reduce_dense()
         cur.wait_stream(e.side)
         e.table_update(self.g_rows, self.g_pos, self.GM, F, g, g_ld_f, w, lr, decay, self.scat_ws)
+        cur.wait_stream(self.ar_stream)
         e.dense_update(lr, last_decay)
 
     def train_step_fm(self, lr, lam=0.0, gscale=1.0, dense_l2=True):
@@ -246,7 +252,7 @@ class ShardedStep(object):
         e, dist = self.e, self.dist
         mine, ok = [], True
         try:
-            for cols in (e.ld, e.ldg):
+            for cols in (e.ld, e.ldg, 1):
                 ptr, h = ctypes.c_void_p(), (ctypes.c_ubyte * 64)()
                 L.call("dctr_ipc_alloc", RC * cols * 4, ctypes.byref(ptr), h)
                 mine.append((ptr.value, bytes(h)))
@@ -254,11 +260,11 @@ class ShardedStep(object):
             ok, err = False, str(ex)
         everyone = [None] * self.world
         dist.all_gather_object(everyone, (ok, [h for _, h in mine]), group=self.group)
-        peers = [[0] * self.world for _ in range(2)]
+        peers = [[0] * self.world for _ in range(3)]
         if all(o for o, _ in everyone):
             try:
                 for r, (_, handles) in enumerate(everyone):
-                    for b in range(2):
+                    for b in range(3):
                         if r == self.rank:
                             peers[b][r] = mine[b][0]
                         else:
@@ -280,12 +286,18 @@ class ShardedStep(object):
             return False
 
         class _Dev(object):                                          # torch view of memory this module owns (never freed before exit)
-            def __init__(self, ptr, shape):
-                self.__cuda_array_interface__ = {"shape": shape, "typestr": "<f4", "data": (ptr, False), "version": 3, "strides": None}
+            def __init__(self, ptr, shape, typestr="<f4"):
+                self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 3, "strides": None}
         self.back = torch.as_tensor(_Dev(mine[0][0], (RC, e.ld)), device=e.dev)
         self.recv_g = torch.as_tensor(_Dev(mine[1][0], (RC, e.ldg)), device=e.dev)
         self.back_peers = torch.tensor(peers[0], dtype=torch.int64, device=e.dev)
         self.recvg_peers = torch.tensor(peers[1], dtype=torch.int64, device=e.dev)
+        # the id buckets travel the same way (dctr_shard_pack_push) unless DCTR_SHARD_P2P_IDS=0 keeps the id all-to-all
+        self.p2p_ids = os.environ.get("DCTR_SHARD_P2P_IDS", "1") != "0"
+        if self.p2p_ids:
+            # (not initialised here: a peer may already be storing its first buckets; every entry is written by its source each step)
+            self.recv_ids = torch.as_tensor(_Dev(mine[2][0], (RC,), "<i4"), device=e.dev)
+            self.ids_peers = torch.tensor(peers[2], dtype=torch.int64, device=e.dev)
         self.bar = torch.zeros(1, dtype=torch.float32, device=e.dev)
         return True
 
@@ -339,9 +351,15 @@ class ShardedStep(object):
         owner = torch.remainder(ids, self.world).to(torch.int32)
         O.sort_pairs(owner, None, e.M, self.world, self.owner_sorted, self.perm, self.plan_ws)
         self._mark("owner sort")
-        O.shard_pack(ids, self.perm, self.owner_sorted, self.world, self.C, self.send_ids, self.src_of_dest, self.inv.view(-1), self.overflow)
-        self._mark("pack")
-        dist.all_to_all_single(self.recv_ids, self.send_ids, group=self.group)
+        if self.p2p and self.p2p_ids:      # the id buckets are stored into the owners' request lists; the all-reduce is the barrier
+            O.shard_pack_push(ids, self.perm, self.owner_sorted, self.world, self.C, self.send_ids, self.src_of_dest, self.inv.view(-1),
+                              self.overflow, self.rank, self.ids_peers, self.recv_ids)
+            self._mark("pack")
+            dist.all_reduce(self.bar, group=self.group)
+        else:
+            O.shard_pack(ids, self.perm, self.owner_sorted, self.world, self.C, self.send_ids, self.src_of_dest, self.inv.view(-1), self.overflow)
+            self._mark("pack")
+            dist.all_to_all_single(self.recv_ids, self.send_ids, group=self.group)
         self._mark("a2a ids")
         if self._train:      # the owner-side sort of the received rows only needs the ids: on the side stream, under the forward / backward
             main = torch.cuda.current_stream(e.dev)
@@ -430,6 +448,8 @@ class ShardedStep(object):
                 O.cross_bwd_push(self.inv.view(N, F), None if wts is None else wts.view(N, F), self.back, d, L.CROSS[e.cross], dz,
                                  self.inv.view(-1), e.ldg, self.C, self.rank, self.recvg_peers, self.recv_g)
             self._mark("slot grads")
+            # the owner-side sort joins BEFORE the barrier: a peer that has passed it may start its next step and overwrite recv_ids
+            torch.cuda.current_stream(e.dev).wait_stream(e.side)
             dist.all_reduce(self.bar, group=self.group)
             # the dense gradients' all-reduce only needs the weight gradients: issued AFTER the barrier (collectives keep their issue
             # order) on its own stream, it runs next to the owners' fold instead of behind it

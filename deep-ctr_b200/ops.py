@@ -90,6 +90,18 @@ def shard_pack(ids, perm, owner_sorted, world, C, send_ids, src_of_dest, inv, st
            _ptr(send_ids, _I32, "send_ids"), _ptr(src_of_dest, _I32, "src_of_dest"), _ptr(inv, _I32, "inv"), _ptr(status, _I32, "status"), _st(ids))
 
 
+@_op("shard_pack_push", "(Tensor ids, Tensor perm, Tensor owner_sorted, int world, int C, Tensor(a!) send_ids, Tensor(b!) src_of_dest, "
+     "Tensor(c!) inv, Tensor(d!) status, int rank, Tensor peers, Tensor(e!) own) -> ()")
+def shard_pack_push(ids, perm, owner_sorted, world, C, send_ids, src_of_dest, inv, status, rank, peers, own):
+    if send_ids.numel() < world * C or src_of_dest.numel() < world * C or inv.numel() < ids.numel() or status.numel() < 2:
+        raise ValueError("shard_pack_push: send_ids / src_of_dest need world * C entries, inv one per slot, status two words")
+    if peers.dtype != _I64 or peers.numel() < world or own.numel() < world * C:
+        raise ValueError("shard_pack_push: peers = one int64 pointer per rank, each to world * C int32 entries")
+    L.call("dctr_shard_pack_push", _ptr(ids, _I32, "ids"), _ptr(perm, _I32, "perm"), _ptr(owner_sorted, _I32, "owner_sorted"), ids.numel(), world, C,
+           _ptr(send_ids, _I32, "send_ids"), _ptr(src_of_dest, _I32, "src_of_dest"), _ptr(inv, _I32, "inv"), _ptr(status, _I32, "status"),
+           rank, _ptr(peers, _I64, "peers", 8), _st(ids))
+
+
 @_op("cross_bwd", "(Tensor ids, Tensor? wts, Tensor table, int d, int cross, Tensor dz, Tensor(a!) ge) -> ()")
 def cross_bwd(ids, wts, table, d, cross, dz, ge):
     N, F = ids.shape

@@ -114,6 +114,12 @@ int dctr_gather_rows(const int32_t* ids, const float* table, int64_t X, int ld, 
  * CUDA-graph capturable).  status[0] += slots that did not fit (the step is then invalid), status[1] = max(status[1], largest fill). */
 int dctr_shard_pack(const int32_t* ids, const int32_t* perm, const int32_t* owner_sorted, int64_t M, int world, int64_t C,
                     int32_t* send_ids, int32_t* src_of_dest, int32_t* inv, int32_t* status, void* stream);
+/* ... and the delivery of the id buckets in the same launch: bucket o, its unused tail included, is also stored as block `rank` of
+ * peers[o] ([world*C] int32, memory of rank o mapped with dctr_ipc_open; peers[rank] = the local list).  Replaces the id all-to-all;
+ * the caller orders it against the readers with a barrier. */
+int dctr_shard_pack_push(const int32_t* ids, const int32_t* perm, const int32_t* owner_sorted, int64_t M, int world, int64_t C,
+                         int32_t* send_ids, int32_t* src_of_dest, int32_t* inv, int32_t* status, int rank, int32_t* const* peers,
+                         void* stream);
 
 /* backward of the cross layer into a per-(sample,field) embedding-gradient buffer
  *   ge[n,f,c] = wts[n,f] * ( dz[n, f*d+c] + d(cross)/d(e_f[c]) ),  ge: float32 [N, F, ldg], ldg%4==0

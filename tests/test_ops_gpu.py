@@ -219,6 +219,19 @@ def test_shard_pack_buckets():
             assert torch.equal(send_ids[o * C:o * C + n], torch.div(ids[slots], world, rounding_mode="floor"))
             assert torch.equal(inv[slots].long(), torch.arange(o * C, o * C + n, device="cuda"))
             assert (send_ids[o * C + n:(o + 1) * C] == -1).all() and (src[o * C + n:(o + 1) * C] == 0).all()
+        # the same plan with the id buckets delivered into (here: local stand-ins for) the owners' request lists
+        rank = world - 1
+        lists = [torch.full((world * C,), 3, dtype=torch.int32, device="cuda") for _ in range(world)]
+        peers = torch.tensor([t.data_ptr() for t in lists], dtype=torch.int64, device="cuda")
+        s2, r2, i2 = torch.full_like(send_ids, 7), torch.full_like(src, 7), torch.full_like(inv, -5)
+        status.zero_()
+        O.shard_pack_push(ids, perm, owner_sorted, world, C, s2, r2, i2, status, rank, peers, lists[rank])
+        torch.cuda.synchronize()
+        assert torch.equal(s2, send_ids) and torch.equal(r2, src) and torch.equal(i2, inv) and int(status[0]) == lost
+        for o in range(world):
+            assert torch.equal(lists[o][rank * C:(rank + 1) * C], send_ids[o * C:(o + 1) * C])
+            rest = torch.cat([lists[o][:rank * C], lists[o][(rank + 1) * C:]])
+            assert (rest == 3).all()
 
 
 @pytest.mark.gpu
