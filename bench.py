@@ -628,6 +628,56 @@ def faithful_baseline(wl, n1=512, budget_s=4.0):
             "sample": "%d steps of batch %d: per-sample gather loop + BLAS graph + interpreted triple update loop (the reference's own structure)" % (n, n1)}
 
 
+def reference_script_baseline(budget_s=8.0, n_train=2000, n_test=500):
+    """B0: the reference's OWN script timed on the host -- python/FNN_wnzh.py as converted by oracle/build_ref.py (mechanical Py2->3
+    only), executed top to bottom on the Theano stand-in of oracle/shims (torch CPU float64 for the compiled graph), with its
+    hard-coded advertiser-2997 hyper-parameters (batch 100, FNN_wnzh.py:18,43-49) on the S1 demo set of SURVEY 8(d) written in its
+    text formats.  One loop iteration = get_batch_data (linecache + split + dict gather, :224-253), train() (:177-182) and the
+    interpreted triple update loop (:298-306); timed from the exit of one train() call to the exit of the next inside an epoch, so
+    the per-epoch evaluation passes are not counted.  Returns None when oracle/_ref is not there."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import tempfile
+    import ref_run
+    if not ref_run.available():
+        return None
+    from deepctr_b200 import data
+    rng = np.random.default_rng(1234)
+    F, d, X = 16, 11, 2048
+    sizes = data.ipinyou_field_sizes(X)
+    feat_field = np.repeat(np.arange(F), sizes)
+    table = rng.uniform(-0.05, 0.05, (X, d))
+    wd = tempfile.mkdtemp(prefix="dctr_ref_script_")
+    os.makedirs(os.path.join(wd, "data"))
+    data.write_fm_model(os.path.join(wd, "data", "fm.model.txt"), 0.1, table, feat_field)
+    for name, n in (("train", n_train), ("test", n_test)):
+        ids = data.make_field_batch(rng, n, sizes)
+        y = data.planted_labels(rng, ids, table * 20, pos_rate=0.2)
+        with open(os.path.join(wd, "data", "%s.fm.txt" % name), "w") as f:
+            for t in range(n):
+                f.write("%d %s\n" % (y[t], " ".join("%d:1" % i for i in ids[t])))
+    try:
+        _, calls = ref_run.run_fnn_wnzh(wd, budget_s=budget_s)
+    finally:
+        import shutil
+        shutil.rmtree(wd, ignore_errors=True)
+    el, n, graph = 0.0, 0, 0.0
+    for a, b in zip(calls[:-1], calls[1:]):
+        if a["fn"] == "function1" and b["fn"] == "function1":      # consecutive train() calls of one epoch
+            el += b["t1"] - a["t1"]
+            graph += b["t1"] - b["t0"]                             # the compiled-graph call alone (the stand-in's share of the iteration)
+            n += 1
+    if not n:
+        return None
+    N = calls[0]["inputs"][0].shape[0]
+    return {"value": n * N / el, "unit": "samples/s", "kind": "reference", "cores": 1, "ms_per_step": el / n * 1e3,
+            # the stand-in evaluates the graph symbolically (slower than compiled Theano): the same iterations with the train() call
+            # itself taken out = an upper bound on what the script can reach with a free graph engine
+            "train_call_ms": graph / n * 1e3, "value_without_train_call": n * N / (el - graph),
+            "sample": "%d loop iterations of python/FNN_wnzh.py itself (oracle/_ref: Py2->3 conversion only; Theano stand-in on torch CPU "
+                      "float64), batch %d as the script hard-codes, S1 demo set (16 fields, %d features): batch read + dict gather + "
+                      "train() + the interpreted triple update loop" % (n, N, X)}
+
+
 def cpu_baseline(wl, N, budget_s=12.0, steps=None):
     form, F, X, *_ = WORKLOADS[wl]
     use_all_host_threads()
@@ -657,11 +707,17 @@ def cpu_baseline(wl, N, budget_s=12.0, steps=None):
         b1 = faithful_baseline(wl)
         if b1:
             out["faithful_B1"] = b1
+        b0 = reference_script_baseline(budget_s=budget_s / 2) if form == "theano" else None
+        if b0:
+            out["reference_script_B0"] = b0
     return out
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU path (oracle port; the Py2/Theano/TF original cannot run here)."""
+    """--impl reference: the reference's CPU path on rank 0's host cores.  The headline value is the vectorised float64 port of the
+    step (oracle/deepctr_oracle.py, pinned against the reference's own code by tests/test_oracle_vs_ref.py) on THIS arm's config with
+    every host core -- the strongest CPU baseline; the reference's own script (oracle/_ref on the Theano stand-in, its hard-coded
+    batch of 100) is timed beside it as cpu_baseline.reference_script_B0 and is 30-40x slower than the port."""
     if rank != 0:
         return
     wl = args.workload
@@ -683,15 +739,19 @@ def run_reference(args, rank, world):
             break
     el = time.perf_counter() - t0
     v = done * N / el
+    b0 = reference_script_baseline(budget_s=8.0) if form == "theano" else None
     print_json({
         "impl": "reference", "metric": "FNN train samples/s", "value": v, "unit": "samples/s", "n_gpus": world, "steps": done,
         "warmup": W, "ms_per_step": el / done * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": wl, "form": form, "fields": F, "rows": X, "rank": rank_k, "hidden": hidden, "cross": cross,
                    "batch_per_gpu": N, "global_batch": N,
-                   "note": "CPU oracle port of the reference step on rank 0's host cores (the Py2 / Theano / TF original cannot run here)"},
+                   "note": "vectorised CPU port of the reference step on rank 0's host cores at this config (the stronger baseline); the "
+                           "reference's own Py2 / Theano script, converted and run on a Theano stand-in at its hard-coded batch of 100, is "
+                           "cpu_baseline.reference_script_B0"},
         "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": "port",
-                         "sample": "%d steps of batch %d (numpy float64 + OpenBLAS)" % (done, N)},
+                         "sample": "%d steps of batch %d (numpy float64 + OpenBLAS)" % (done, N),
+                         **({"reference_script_B0": b0} if b0 else {})},
         "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
 
 

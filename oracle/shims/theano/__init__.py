@@ -11,8 +11,13 @@ Semantics kept from Theano:
   * every RandomStreams op owns a numpy RandomState seeded from RandomState(seed).randint(2 ** 30) in creation order and
     draws once per function call when it is part of that function's graph (recollection of
     theano.tensor.shared_randomstreams; the draws are logged so a comparison never depends on this rule).
-Every function call is appended to CALL_LOG: dict(fn=name, inputs=[...], random={op name: draw}, outputs=[...]).
+Every function call is appended to CALL_LOG: dict(fn=name, inputs=[...], random={op name: draw}, outputs=[...], t0=, t1=) with
+t0 / t1 = time.perf_counter() at entry / exit of the call (bench.py times the script's own loop from them).  DEADLINE (a
+perf_counter value, default None) bounds a run: the first function call after it raises BudgetExceeded, which the runner
+(oracle/ref_run.py) catches -- the reference script has no way to stop its 100-epoch loop early.
 """
+import time
+
 import numpy as np
 import torch
 
@@ -25,6 +30,11 @@ class _Config(object):
 
 config = _Config()
 CALL_LOG = []
+DEADLINE = None
+
+
+class BudgetExceeded(Exception):
+    pass
 
 
 class SharedVariable(Sym):
@@ -87,6 +97,9 @@ class Function(object):
     def __call__(self, *args):
         if len(args) != len(self.inputs):
             raise TypeError("%s takes %d inputs" % (self.name, len(self.inputs)))
+        t0 = time.perf_counter()
+        if DEADLINE is not None and t0 > DEADLINE:
+            raise BudgetExceeded(self.name)
         env = Env()
         ins = []
         for s, a in zip(self.inputs, args):
@@ -113,7 +126,7 @@ class Function(object):
         for s, v in new:
             s.value = v.detach().clone().to(DTYPE)
         res = [o.numpy() if o.ndim else np.float64(o.item()) for o in outs]
-        CALL_LOG.append(dict(fn=self.name, inputs=ins, random=draws, outputs=[np.array(r) for r in res]))
+        CALL_LOG.append(dict(fn=self.name, inputs=ins, random=draws, outputs=[np.array(r) for r in res], t0=t0, t1=time.perf_counter()))
         return res[0] if self.single else res
 
 
