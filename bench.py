@@ -236,7 +236,10 @@ NCU_TRAFFIC = {
     ("fm_ipinyou", "dctr_sort_rows"): 285.95e3 + 321.79e3 + 577.28e3,
     ("emb", "gather_concat_fwd"): 257.25e6 + 698.65e6,                        # profiles/r01_ncu_emb_gather_concat_kernel.txt
     ("emb", "fm_fwd"): 234.24e6 + 51.89e6,                                    # profiles/r01_ncu_emb_fm_fwd_kernel.txt
-    ("emb", "scatter_sgd[sum]"): 4375.48e6 + 42.46e6,                         # profiles/r01_ncu_emb_fold_tile_kernel_chunk4.txt
+    # profiles/r02_ncu_emb_fold_tile_kernel_final.txt: re-captured on the final fold of round 2 (update list, double-precision decay): the
+    # same 4.37 GB the round-1 kernel moved (r01_ncu_emb_fold_tile_kernel_chunk4.txt); without the per-slot weight gather 2.76 GB
+    ("emb", "scatter_sgd[sum]"): 4374.34e6 + 42.05e6,
+    ("emb", "scatter_sgd_masked[seq_decay]"): 2756.41e6 + 42.46e6,
 }
 
 
