@@ -632,6 +632,14 @@ def faithful_baseline(wl, n1=512, budget_s=4.0):
 
 
 def reference_script_baseline(budget_s=8.0, n_train=2000, n_test=500):
+    """reference_script_run() guarded: this leg is extra evidence and must never cost the bench its JSON line."""
+    try:
+        return reference_script_run(budget_s, n_train, n_test)
+    except Exception as ex:                                         # noqa: BLE001
+        return {"unavailable": "%s: %s" % (type(ex).__name__, str(ex)[:200]), "kind": "reference"}
+
+
+def reference_script_run(budget_s=8.0, n_train=2000, n_test=500):
     """B0: the reference's OWN script timed on the host -- python/FNN_wnzh.py as converted by oracle/build_ref.py (mechanical Py2->3
     only), executed top to bottom on the Theano stand-in of oracle/shims (torch CPU float64 for the compiled graph), with its
     hard-coded advertiser-2997 hyper-parameters (batch 100, FNN_wnzh.py:18,43-49) on the S1 demo set of SURVEY 8(d) written in its

@@ -55,8 +55,8 @@ def _fresh(*names):
 
 def run_fnn_wnzh(workdir, argv=(), quiet=True, budget_s=None):
     """workdir/data/{fm.model.txt, train.fm.txt, test.fm.txt} must exist.  Returns (globals, calls).
-    budget_s: stop the script at its first train() / predict() call after that many seconds (the shim raises BudgetExceeded, caught
-    here); the globals are then only {'__stdout__', '__stopped__'} and `calls` holds what ran -- bench.py's bounded timing sample."""
+    budget_s: stop the script at its first train() / predict() call more than that many seconds after its first one (the shim raises
+    BudgetExceeded, caught here); the globals are then only {'__stdout__', '__stopped__'} and `calls` holds what ran -- bench.py's bounded timing sample."""
     assert available(), "oracle/_ref is not built (needs /root/reference)"
     py = os.path.join(workdir, "python")
     os.makedirs(py, exist_ok=True)
@@ -69,16 +69,15 @@ def run_fnn_wnzh(workdir, argv=(), quiet=True, budget_s=None):
     try:
         with _paths(py):
             import theano
-            import time
             del theano.CALL_LOG[:]
-            theano.DEADLINE = None if budget_s is None else time.perf_counter() + budget_s
+            theano.BUDGET_S, theano._FIRST_CALL[0] = budget_s, None
             with contextlib.redirect_stdout(buf if quiet else sys.stdout):
                 try:
                     g = runpy.run_path(os.path.join(REF, "FNN_wnzh.py"), run_name="__main__")
                 except theano.BudgetExceeded:
                     g = {"__stopped__": True}
                 finally:
-                    theano.DEADLINE = None
+                    theano.BUDGET_S = None
             calls = list(theano.CALL_LOG)
     finally:
         sys.argv = old_argv
