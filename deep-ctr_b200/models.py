@@ -125,16 +125,31 @@ class _Staging(object):
             offs[name] = (total, nbytes, dtype, tuple(shape))
             total += (nbytes + 15) // 16 * 16
         self.nbytes = total
+        self._offs = offs
         self.pinned = torch.zeros(total, dtype=torch.uint8).pin_memory()
         self.device = torch.zeros(total, dtype=torch.uint8, device=device)
         tdt = {np.int32: torch.int32, np.float32: torch.float32}
-        self.host, self.dev = {}, {}
+        self.host, self.dev = self._host_views(self.pinned), {}
         for name, (o, nb, dtype, shape) in offs.items():
-            self.host[name] = self.pinned[o:o + nb].numpy().view(dtype).reshape(shape)
             self.dev[name] = self.device[o:o + nb].view(tdt[dtype]).view(*shape)
+
+    def _host_views(self, pinned):
+        return {name: pinned[o:o + nb].numpy().view(dtype).reshape(shape) for name, (o, nb, dtype, shape) in self._offs.items()}
 
     def upload(self):
         self.device.copy_(self.pinned, non_blocking=True)
+
+    def enable_pipeline(self):
+        """two-deep pipelining (_Base._train_async): a second pinned block, so the host can stage step t+1 while the upload of step t
+        may still be in flight, and a device-side landing buffer the copy stream fills while the running step reads `device`."""
+        if not hasattr(self, "landing"):
+            second = torch.zeros(self.nbytes, dtype=torch.uint8).pin_memory()
+            self._blocks = [(self.pinned, self.host), (second, self._host_views(second))]
+            self.landing = torch.zeros_like(self.device)
+
+    def select(self, k):
+        """`pinned` / `host[...]` now name block k (every staging helper looks them up at call time)"""
+        self.pinned, self.host = self._blocks[k]
 
 
 class _Base(object):
@@ -210,13 +225,72 @@ class _Base(object):
         self._check_ids()
         return float(self._out_np[self.N]), self._out_np[:self.N].copy()
 
-    def _stage_and_step(self, ids, wts, y):
+    def _stage_ids(self, ids, wts, y):
         h = self._stage.host
         np.copyto(h["ids"], ids, casting="unsafe")
         np.copyto(h["wts"], wts, casting="unsafe")
         np.copyto(h["y"], y, casting="unsafe")
+
+    def _stage_and_step(self, ids, wts, y):
+        self._stage_ids(ids, wts, y)
         self._pre_step()
         return self._finish_step()
+
+    # ---- two-deep pipelined training: an ADDITION next to the synchronous calls (the reference's loop is synchronous, baseline.py:351,
+    # FNN_wnzh.py:296-298).  Call t stages batch t into pinned block t % 2, queues its upload on a copy stream into a landing buffer,
+    # queues [landing -> input block, the step, pred | loss -> pinned out block t % 2] on the compute stream and returns the result of
+    # step t - 1: the host packs batch t + 1 and the bus carries it while the device runs step t.  Same kernels, same order, same
+    # results as the synchronous call; flush_async() returns the last step's result.
+    def _pipe_setup(self):
+        self._stage.enable_pipeline()
+        second = torch.zeros(self.N + 4, dtype=torch.float32).pin_memory()
+        dev = self.engine.dev
+        self._pipe = dict(k=0, pending=None, copy_stream=torch.cuda.Stream(device=dev), landing_free=None,
+                          outs=[(self._out_pinned, self._out_np, self._out_i32), (second, second.numpy(), second.numpy().view(np.int32))],
+                          h2d=[torch.cuda.Event(), torch.cuda.Event()], out=[torch.cuda.Event(), torch.cuda.Event()])
+        return self._pipe
+
+    def _pipe_result(self, k):
+        p = self._pipe
+        p["out"][k].synchronize()
+        self._out_pinned, self._out_np, self._out_i32 = p["outs"][k]
+        self._check_ids()
+        return float(self._out_np[self.N]), self._out_np[:self.N].copy()
+
+    def _train_async(self, stage_fn):
+        p = getattr(self, "_pipe", None) or self._pipe_setup()
+        st, k = self._stage, p["k"]
+        # pinned block k was uploaded two calls ago; that step's result has been read since, so the upload is complete
+        st.select(k)
+        stage_fn()
+        self._pre_step()
+        main, cs = torch.cuda.current_stream(self.engine.dev), p["copy_stream"]
+        if p["landing_free"] is not None:
+            cs.wait_event(p["landing_free"])                 # the previous step has taken its inputs out of the landing buffer
+        with torch.cuda.stream(cs):
+            st.landing.copy_(st.pinned, non_blocking=True)
+            p["h2d"][k].record(cs)
+        main.wait_event(p["h2d"][k])
+        st.device.copy_(st.landing, non_blocking=True)
+        p["landing_free"] = torch.cuda.Event()
+        p["landing_free"].record(main)
+        # a later step is launched before an earlier one's id status has been looked at: every pipelined step starts from clean status
+        # words, so the count that travels back with its result is its own
+        self.engine.out[self.N + 2:].zero_()
+        self._run_step()
+        p["outs"][k][0].copy_(self.engine.out, non_blocking=True)
+        p["out"][k].record(main)
+        self._post_launch()
+        prev, p["pending"], p["k"] = p["pending"], k, k ^ 1
+        return None if prev is None else self._pipe_result(prev)
+
+    def flush_async(self):
+        """(loss, preds) of the last pipelined step, or None when nothing is pending."""
+        p = getattr(self, "_pipe", None)
+        if not p or p["pending"] is None:
+            return None
+        prev, p["pending"] = p["pending"], None
+        return self._pipe_result(prev)
 
     def _fetch_out(self):
         self._out_pinned.copy_(self.engine.out, non_blocking=True)
@@ -328,6 +402,13 @@ class FM(_Base):
         wts = np.asarray(feed[self.sp_wt_hldr]).reshape(self.N, self.F)
         y = np.asarray(feed[self.lbl_hldr]).reshape(self.N)
         return self._stage_and_step(ids, wts, y)
+
+    def train_step_async(self, feed):
+        """train_step, two-deep pipelined: returns (loss, preds) of the PREVIOUS call (None on the first); flush_async() ends the run."""
+        ids = np.asarray(feed[self.sp_id_hldr]).reshape(self.N, self.F)
+        wts = np.asarray(feed[self.sp_wt_hldr]).reshape(self.N, self.F)
+        y = np.asarray(feed[self.lbl_hldr]).reshape(self.N)
+        return self._train_async(lambda: self._stage_ids(ids, wts, y))
 
     def _fetch(self, kind, feed):
         if kind == "eval_preds":
@@ -497,11 +578,19 @@ class _FNNBase(_Base):
                v_wts.ctypes.data if self.n_num else None, c_wts.ctypes.data, N, self.n_num, n_cat,
                h["ids"].ctypes.data, h["wts"].ctypes.data, self._pack_threads)
 
-    def train_step(self, feed):
+    def _stage_feed(self, feed):
         self._pack_feed(feed[self.v_wt_hldr], feed[self.c_id_hldr], feed[self.c_wt_hldr])
         np.copyto(self._stage.host["y"], np.asarray(feed[self.lbl_hldr]).reshape(self.N), casting="unsafe")
+
+    def train_step(self, feed):
+        self._stage_feed(feed)
         self._pre_step()
         return self._finish_step()
+
+    def train_step_async(self, feed):
+        """train_step, two-deep pipelined: the pack and the upload of this batch run under the previous step.  Returns (loss, preds)
+        of the PREVIOUS call (None on the first); flush_async() returns the last one."""
+        return self._train_async(lambda: self._stage_feed(feed))
 
     def _fetch(self, kind, feed):
         if kind == "eval_preds":       # global ids [E, X_feas]; the graph subtracts offsets itself (FNN.py:65-69)

@@ -174,6 +174,15 @@ class FNN_wnzh(_Base):
         self._pre_step()
         return self._finish_step()
 
+    def _stage_batch(self, feats, y):
+        self._stage_feats(feats)
+        np.copyto(self._stage.host["y"], np.asarray(y).reshape(self.N), casting="unsafe")
+
+    def train_async(self, feats, y):
+        """train(), two-deep pipelined (models._Base._train_async): returns (loss, p_drop) of the PREVIOUS call (None on the first);
+        flush_async() returns the last one.  The mask stream is consumed in call order, as train() does."""
+        return self._train_async(lambda: self._stage_batch(feats, y))
+
     def train_step_device(self, feats, y):
         """train() from DEVICE-resident blocks (ingest.DeviceText.parse_sparse with J = 16, pad_id = -1): int32 feature ids
         [N, 16], float32 labels [N]; only the two dropout masks go up and pred | loss come back."""
