@@ -338,7 +338,7 @@ def run_b200(args, rank, world):
         out["secondary"] = {}
         for wl2 in ("fnn_criteo_sharded", "fnn_ip_l7_ipinyou"):
             r2 = measure_workload(wl2, 0, min(args.steps, 20), 3, rank, world, dist, local, False)
-            out["secondary"][wl2] = {k: r2[k] for k in ("value", "unit", "ms_per_step", "n_gpus", "config", "e2e", "launches_per_step", "clocks")}
+            out["secondary"][wl2] = {k: r2[k] for k in ("value", "unit", "ms_per_step", "n_gpus", "config", "e2e", "e2e_pipelined", "launches_per_step", "clocks")}
     if rank == 0 and world == 1 and not args.no_cpu:
         out["cpu_baseline"] = cpu_baseline(args.workload, args.batch or WORKLOADS[args.workload][6], budget_s=12.0)
     if rank == 0:
