@@ -759,7 +759,7 @@ def run_reference(args, rank, world):
     """--impl reference: the reference's CPU path on rank 0's host cores.  The headline value is the vectorised float64 port of the
     step (oracle/deepctr_oracle.py, pinned against the reference's own code by tests/test_oracle_vs_ref.py) on THIS arm's config with
     every host core -- the strongest CPU baseline; the reference's own script (oracle/_ref on the Theano stand-in, its hard-coded
-    batch of 100) is timed beside it as cpu_baseline.reference_script_B0 and is 30-40x slower than the port."""
+    batch of 100) is timed beside it as cpu_baseline.reference_script_B0 and is ~10x slower than the port."""
     if rank != 0:
         return
     wl = args.workload
