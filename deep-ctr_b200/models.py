@@ -258,6 +258,9 @@ class _Base(object):
         return float(self._out_np[self.N]), self._out_np[:self.N].copy()
 
     def _train_async(self, stage_fn):
+        if getattr(self, "dp", None) is not None or getattr(self, "sharded", None) is not None:
+            raise NotImplementedError("the pipelined call has only been run on single-GPU models; data-parallel and row-sharded models "
+                                      "(dist.attach / attach_sharded) take the synchronous call")
         p = getattr(self, "_pipe", None) or self._pipe_setup()
         st, k = self._stage, p["k"]
         # pinned block k was uploaded two calls ago; that step's result has been read since, so the upload is complete

@@ -232,3 +232,80 @@ def test_device_fed_step_plumbing_runs_on_fakes():
                 loss, pred = m.train_step_device(torch.ones(8, 16, dtype=torch.int32), torch.ones(8))
             assert loss == 8.0 and bool((m.feats == 1).all()) and bool((m.engine.y == 1).all())
             assert np.array_equal(m._stage.dev["mask1"].numpy(), m._stage.host["mask1"])
+
+
+def test_pipelined_call_returns_each_result_one_call_late_on_fakes():
+    """models._Base._train_async, host side only: CPU tensors stand in for the pinned and device blocks (pin_memory patched out, CUDA
+    streams / events mocked).  Call t stages into pinned block t % 2, the step sees batch t in its device block, the result of step
+    t comes back from call t + 1, flush_async() returns the last one, and models attached to a process group are refused."""
+    from unittest import mock
+    from deepctr_b200.models import _Staging
+    from deepctr_b200.theano_fnn import FNN_wnzh
+    N, J = 8, 16
+    with mock.patch.object(torch.Tensor, "pin_memory", lambda self: self), mock.patch("torch.cuda.Stream"), mock.patch("torch.cuda.Event"), \
+            mock.patch("torch.cuda.stream"), mock.patch("torch.cuda.current_stream"):
+        m = FNN_wnzh.__new__(FNN_wnzh)
+        m.N, m.J, m.mask_streams, m._next_masks = N, J, None, None
+        m._stage = _Staging([("feats", np.int32, (N, J)), ("y", np.float32, (N,))], "cpu")
+
+        class Eng:
+            dev = "cpu"
+            out = torch.zeros(N + 4)
+        m.engine = Eng()
+        m._out_pinned = torch.zeros(N + 4)
+        m._out_np = m._out_pinned.numpy()
+        m._out_i32 = m._out_np.view(np.int32)
+        seen = []
+
+        def run_step():                      # "the step": pred = 2 y, loss = sum of the feature ids, read from the DEVICE block
+            y, feats = m._stage.dev["y"], m._stage.dev["feats"]
+            seen.append(int(feats[0, 0]))
+            m.engine.out[:N] = 2 * y
+            m.engine.out[N] = float(feats.sum())
+        m._run_step = run_step
+        batches = [(np.full((N, J), t + 1, np.int64), np.arange(N, dtype=np.float64) + 10 * t) for t in range(5)]
+        got = [m.train_async(*b) for b in batches]
+        blocks = m._stage._blocks
+        assert got[0] is None and seen == [1, 2, 3, 4, 5]
+        assert blocks[0][1]["feats"][0, 0] == 5 and blocks[1][1]["feats"][0, 0] == 4          # block t % 2 holds batch t
+        got = got[1:] + [m.flush_async()]
+        assert m.flush_async() is None
+        for t, (loss, pred) in enumerate(got):
+            assert loss == (t + 1) * N * J and np.array_equal(pred, 2 * batches[t][1].astype(np.float32))
+        # a bad id is reported by the call that collects that step: the status words travel in the step's own out block
+        def bad_step():
+            m.engine.out[:N + 1] = 0
+            m.engine.out[N + 2:] = torch.tensor([2, 77], dtype=torch.int32).view(torch.float32)
+        m._run_step = bad_step
+        assert m.train_async(*batches[0]) is None
+        m._run_step = run_step
+        with pytest.raises(IndexError, match="77"):
+            m.train_async(*batches[1])
+        assert m.flush_async()[0] == 2 * N * J
+        m.dp = object()
+        with pytest.raises(NotImplementedError):
+            m.train_async(*batches[0])
+
+
+def test_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` (no GPU involved): ONE JSON line on stdout with the arm's metric / unit / config, `impl`,
+    a cpu_baseline describing the run and an e2e block without copies; the reference's own script rides in cpu_baseline when
+    oracle/_ref is there."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1"],
+                       capture_output=True, text=True, timeout=300, cwd=root)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "FNN train samples/s" and d["unit"] == "samples/s" and d["higher_is_better"] is True
+    assert d["config"]["workload"] == "fnn_ipinyou" and d["config"]["batch_per_gpu"] == 4096 and d["steps"] == 2
+    assert d["value"] > 0 and d["cpu_baseline"]["value"] == d["value"] and d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"] == {"value": d["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    b0 = d["cpu_baseline"].get("reference_script_B0")
+    if b0 is not None and "unavailable" not in b0:
+        assert b0["kind"] == "reference" and 0 < b0["value"] < d["value"]
