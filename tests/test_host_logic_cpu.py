@@ -309,3 +309,25 @@ def test_reference_arm_prints_the_contract_line():
     b0 = d["cpu_baseline"].get("reference_script_B0")
     if b0 is not None and "unavailable" not in b0:
         assert b0["kind"] == "reference" and 0 < b0["value"] < d["value"]
+
+
+def test_bench_algorithmic_costs_are_the_survey_figures():
+    """bench.call_cost = SURVEY.md 8(d)'s algorithmic bytes / flops per sample (iPinYou shape: F = 16, d = 11): gather-concat 1 540 B,
+    scatter-SGD 2 176 B, FM forward 840 B + the s row, Theano-FNN MLP forward + data gradients; the roofline fractions are these
+    figures over measured time, so they are pinned here."""
+    import bench
+    N, F, d = 4096, 16, 11
+    gather = (0, 0, 0, 10 ** 6, 12, N, F, d, 0, 1, 0, 0, 0, 180, None)
+    assert bench.call_cost("dctr_gather_concat_fwd", gather) == ("byte", N * 1540)
+    ip = gather[:8] + (1,) + gather[9:]
+    assert bench.call_cost("dctr_gather_concat_fwd", ip) == ("byte", N * (1540 + 4 * 120))            # + 4 P for the inner products
+    scatter = (0, 0, 0, N * F, F, d)
+    assert bench.call_cost("dctr_scatter_sgd", scatter) == ("byte", N * 2176)
+    assert bench.call_cost("dctr_scatter_sgd_masked", scatter) == ("byte", N * 2176)
+    assert bench.call_cost("dctr_fm_fwd", gather) == ("byte", N * (840 + 4 * d))
+    unit, flops = bench.call_cost("dctr_mlp2tc_train", (N, 177, 300, 100))
+    assert unit == "flop" and flops == 4.0 * N * (177 * 300 + 300 * 100 + 100)                        # 2 of the 3 GEMM families of a step
+    assert bench.call_cost("dctr_gemm_tc", (2, 177, 300, N)) == ("flop", 2.0 * 177 * 300 * N)
+    # the sort's figure: one histogram read of the keys + (key, position) read and written per pass; 20-bit ids sort in 2 passes of 10 bits
+    assert bench.call_cost("dctr_sort_rows", (0, N * F, 10 ** 6)) == ("byte", N * F * (4 + 2 * 16))
+    assert bench.call_cost("dctr_sort_rows", (0, 1 << 24, 2 * 10 ** 7)) == ("byte", (1 << 24) * (4 + 4 * 16))
