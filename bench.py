@@ -585,8 +585,15 @@ def measure_workload(wl, batch, steps, warmup, rank, world, dist, local, profile
 # ---------------------------------------------------------------------------------------------------
 # CPU arm: the oracle restatement of the reference step (numpy float64 + OpenBLAS, all host cores)
 # ---------------------------------------------------------------------------------------------------
+def _oracle_on_path():
+    """oracle/ is test infrastructure: only the CPU legs of this file (cpu_baseline, --impl reference) put it on the path"""
+    p = os.path.join(ROOT, "oracle")
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
 def oracle_stepper(wl, N, seed=1234, dtype=np.float64):
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    _oracle_on_path()
     import deepctr_oracle as O
     form, F, X, rank, hidden, cross, _ = WORKLOADS[wl]
     rng = np.random.default_rng(seed)
@@ -627,7 +634,7 @@ def use_all_host_threads():
 def faithful_baseline(wl, n1=512, budget_s=4.0):
     """B1 of SURVEY 8(d): what the reference COSTS -- its own structure on a reduced batch: the per-sample, per-feature gather of
     feats_to_layer_one_array (FNN_wnzh.py:87-96), BLAS for the Theano graph, and the interpreted triple update loop (:298-306)."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    _oracle_on_path()
     import deepctr_oracle as O
     form, F, X, rank, hidden, cross, _ = WORKLOADS[wl]
     if form != "theano":
@@ -677,7 +684,7 @@ def reference_script_run(budget_s=8.0, n_train=2000, n_test=500):
     text formats.  One loop iteration = get_batch_data (linecache + split + dict gather, :224-253), train() (:177-182) and the
     interpreted triple update loop (:298-306); timed from the exit of one train() call to the exit of the next inside an epoch, so
     the per-epoch evaluation passes are not counted.  Returns None when oracle/_ref is not there."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    _oracle_on_path()
     import tempfile
     import ref_run
     if not ref_run.available():
