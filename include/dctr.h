@@ -104,7 +104,10 @@ int dctr_eval_metrics(const float* pred, const float* y, int64_t N, double* out,
 int dctr_host_pack_fields(const void* c_ids, int id_bytes, const int64_t* offsets, const float* v_wts,
                           const float* c_wts, int64_t N, int n_num, int n_cat, int32_t* ids, float* wts, int threads);
 
-/* row gather: out[i, 0:ld) = table[ids[i], 0:ld), i < M.  The owner-side lookup of the row-sharded table (SURVEY 8(e):
+/* ---- row-sharded embedding table (BASELINE config 5).  NO COUNTERPART IN THE REFERENCE, which is single-process (SURVEY section 2:
+ * "Parallelism strategies / communication backend in the reference: none"); the entry points from here to dctr_cross_bwd_push --
+ * except dctr_cross_bwd, the autodiff of FNN_IP_L3.py:91-97 / FNN_OP_L3.py:93-100 -- implement SURVEY 8(e), third row. ----
+ * row gather: out[i, 0:ld) = table[ids[i], 0:ld), i < M.  The owner-side lookup of the row-sharded table (SURVEY 8(e):
  * rows live on rank row % world) and the permutation of per-slot gradient rows into all-to-all order. */
 int dctr_gather_rows(const int32_t* ids, const float* table, int64_t X, int ld, int64_t M, float* out, void* stream);
 /* fixed-capacity exchange plan of the row-sharded table: the M slots of a batch, ordered by owner rank (perm /
@@ -121,7 +124,8 @@ int dctr_shard_pack_push(const int32_t* ids, const int32_t* perm, const int32_t*
                          int32_t* send_ids, int32_t* src_of_dest, int32_t* inv, int32_t* status, int rank, int32_t* const* peers,
                          void* stream);
 
-/* backward of the cross layer into a per-(sample,field) embedding-gradient buffer
+/* backward of the cross layer (the autodiff of FNN_IP_L3.py:91-97 / FNN_OP_L3.py:93-100 and of the gather FNN.py:76-85) into a
+ * per-(sample,field) embedding-gradient buffer
  *   ge[n,f,c] = wts[n,f] * ( dz[n, f*d+c] + d(cross)/d(e_f[c]) ),  ge: float32 [N, F, ldg], ldg%4==0
  * dz is dL/dz (the activation derivative already applied), TF layout (bias last).
  * cross = NONE just copies/scales the embedding block.  Reads the PRE-update table. */
