@@ -10,7 +10,8 @@ tensorflow: lazy graphs evaluated by torch, autograd for T.grad / minimize), and
 restatement equal to it: every train() / predict() call of the whole FNN_wnzh.py script (23 epochs, duplicate / missing /
 repeated features included, 1e-8), 3 optimiser steps + eval + dump of FM, LR, FNN, FNN_IP_L3/L5/L7, FNN_OP_L3 under sgd / adam /
 ftrl with logged dropout masks (1e-9), build_inds, get_fxy, get_batch_xy, early_stop, watch_train, the whole baseline.train()
-loop, collect / stat / load_ipinyou_data.  What the shims stand in for is the ENGINES (Theano, TensorFlow 0.x: absent from
+loop, collect / stat / load_ipinyou_data, and every train() / predict() call of the whole SNN_DAE.py script against OracleSNN
+(1e-9).  What the shims stand in for is the ENGINES (Theano, TensorFlow 0.x: absent from
 /root/reference, unpinned versions): their op semantics are restated from the published behaviour (oracle/shims/*/__init__.py
 list every point).  Golden vectors generated from those runs: tests/golden/ref_golden.pkl (tests/golden/make_golden_ref.py).
 Independently of the reference, this file is also pinned by central finite differences of every hand-derived backward,

@@ -4,6 +4,7 @@ TEST INFRASTRUCTURE, NOT PRODUCT CODE.  Only tests/ and tests/golden/make_golden
   run_fnn_wnzh(workdir)        executes the converted FNN_wnzh.py top to bottom (runpy) in <workdir>/python with the data
                                files it opens under <workdir>/data; returns its final globals and the log of every
                                train() / predict() call the script made (inputs, dropout draws, outputs).
+  run_snn_dae(workdir, w)      the same for the converted SNN_DAE.py, started from the weight pickle it loads.
   tf_modules()                 imports tf_util / FM / LR / FNN / FNN_IP_L3 / L5 / L7 / FNN_OP_L3 on the tensorflow shim.
   load_baseline(workdir, ...)  imports baseline.py (its module body opens ../log/<tag>) so that get_fxy, get_batch_xy,
                                early_stop, watch_train and train() can be called with overridden module globals.
@@ -74,6 +75,41 @@ def run_fnn_wnzh(workdir, argv=(), quiet=True, budget_s=None):
             with contextlib.redirect_stdout(buf if quiet else sys.stdout):
                 try:
                     g = runpy.run_path(os.path.join(REF, "FNN_wnzh.py"), run_name="__main__")
+                except theano.BudgetExceeded:
+                    g = {"__stopped__": True}
+                finally:
+                    theano.BUDGET_S = None
+            calls = list(theano.CALL_LOG)
+    finally:
+        sys.argv = old_argv
+    g["__stdout__"] = buf.getvalue()
+    return g, calls
+
+
+def run_snn_dae(workdir, weights, quiet=True, budget_s=None):
+    """Executes the converted SNN_DAE.py top to bottom.  workdir/data/{train,test}.fm.txt must exist (batch_size is 1000 and
+    x_dim 133465 in the script, SNN_DAE.py:19,41); `weights` = (ww0, bb0, ww1, bb1, ww2, bb2) is written to the pickle the script
+    loads instead of pre-training (dropda_2997_.p, :83-86).  Returns (globals, calls) like run_fnn_wnzh."""
+    import pickle
+    assert available(), "oracle/_ref is not built (needs /root/reference)"
+    py = os.path.join(workdir, "python")
+    os.makedirs(py, exist_ok=True)
+    os.makedirs(os.path.join(workdir, "log"), exist_ok=True)
+    with open(os.path.join(py, "dropda_2997_.p"), "wb") as f:
+        pickle.dump(tuple(weights), f)
+    _fresh("theano", "theano.tensor", "theano.tensor.shared_randomstreams", "dl_utils", "data_fm", "sampling_based_denosing_autoencoder")
+    linecache.clearcache()
+    old_argv = sys.argv
+    sys.argv = ["SNN_DAE.py"]
+    buf = io.StringIO()
+    try:
+        with _paths(py):
+            import theano
+            del theano.CALL_LOG[:]
+            theano.BUDGET_S, theano._FIRST_CALL[0] = budget_s, None
+            with contextlib.redirect_stdout(buf if quiet else sys.stdout):
+                try:
+                    g = runpy.run_path(os.path.join(REF, "SNN_DAE.py"), run_name="__main__")
                 except theano.BudgetExceeded:
                     g = {"__stopped__": True}
                 finally:

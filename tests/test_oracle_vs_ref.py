@@ -474,3 +474,64 @@ def test_bench_times_the_reference_script_itself():
     assert b0["value"] > 0 and b0["value_without_train_call"] > b0["value"] and 0 < b0["train_call_ms"] < b0["ms_per_step"]
     import sys
     assert sys.modules["theano"].BUDGET_S is None
+
+
+def test_snn_dae_script_equals_oracle(tmp_path):
+    """the reference's own SNN_DAE.py (converted, run top to bottom from the weight pickle it loads, SNN_DAE.py:83-86)
+    against OracleSNN, call by call: the dense inputs x = sigmoid(sum ww0[feat] + bb0) of every train() call (get_fi_h1_y :234-260 --
+    they carry the ww0 / bb0 updates of all earlier steps, :282-288), gx and the weights train() returns (:113-163, dropout draws
+    taken from the call log), and the per-epoch predict() passes over the train and test files (:164-196)."""
+    rng = np.random.default_rng(3)
+    X_DIM, H0, H1, H2, N = 133465, 200, 300, 100, 1000          # x_dim, hidden0/1/2 of advertiser 2997 and batch_size (:19,41-45)
+    lr, lambda1 = 0.0005, 0.0                                     # :46-49
+    wd = str(tmp_path)
+    os.makedirs(os.path.join(wd, "data"))
+    n_ids = 4000
+
+    def write(name, n):
+        feats = np.stack([rng.integers(0, n_ids // 16, n) + f * (n_ids // 16) for f in range(16)], 1)
+        feats[5] = feats[4]                                        # a repeated sample: its rows are updated twice, in order
+        y = rng.integers(0, 2, n)
+        with open(os.path.join(wd, "data", name), "w") as f:
+            for t in range(n):
+                f.write("%d %s\n" % (y[t], " ".join("%d:1" % i for i in feats[t])))
+        return feats, y
+    (tr_f, tr_y), (te_f, te_y) = write("train.fm.txt", 2 * N), write("test.fm.txt", 300)
+    ww0, bb0 = rng.uniform(-0.05, 0.05, (X_DIM, H0)), rng.uniform(-0.1, 0.1, H0)
+    ww1, bb1 = rng.uniform(-0.1, 0.1, (H0, H1)), rng.uniform(-0.1, 0.1, H1)
+    ww2, bb2 = rng.uniform(-0.1, 0.1, (H1, H2)), rng.uniform(-0.1, 0.1, H2)
+    _, calls = ref_run.run_snn_dae(wd, (ww0, bb0, ww1, bb1, ww2, bb2), budget_s=4.0)
+    net = O.OracleSNN(ww0, bb0, [ww1, ww2, np.zeros((H2, 1))], [bb1, bb2, np.zeros(1)], act="tanh")      # ww3 = 0, bb3 = 0 (:93-94)
+    steps = epochs = 0
+    k = 0
+    close = lambda a, b, tol=1e-9: np.testing.assert_allclose(np.asarray(a, np.float64), np.asarray(b, np.float64), rtol=tol, atol=1e-12)
+    while k < len(calls):
+        c = calls[k]
+        if c["fn"] == "function1":                                # train(x, y) of batch j = steps % 2
+            j = steps % 2
+            feats, y = tr_f[j * N:(j + 1) * N], tr_y[j * N:(j + 1) * N]
+            x = net.dense(feats)
+            close(c["inputs"][0], x)                              # the bag forward on the CURRENT ww0 / bb0
+            close(c["inputs"][1], y)
+            r1, r2 = c["random"]["binomial0"], c["random"]["binomial1"]
+            assert r1.shape == (1, H1) and r2.shape == (1, H2)
+            _, _, gx, _, _ = net.loss_and_grads(x, y.astype(np.float64), r1, r2, lambda1)
+            out = c["outputs"]
+            close(out[0], gx, 1e-8)
+            close(out[1], net.Ws[0]); close(out[2], net.Ws[1]); close(out[3], net.Ws[2].reshape(-1))      # pre-update values
+            close(out[4], net.bs[0]); close(out[5], net.bs[1]); close(out[6], net.bs[2][0])
+            net.train_step(feats, y, lr, r1, r2, lambda1, faithful=True)
+            steps += 1
+            k += 1
+        else:                                                     # the epoch's two predict() passes: train file, then test file
+            close(c["outputs"][0], net.predict(tr_f), 1e-8)
+            close(calls[k + 1]["outputs"][0], net.predict(te_f), 1e-8) if k + 1 < len(calls) else None
+            epochs += 1
+            k += 2
+    assert steps >= 4 and epochs >= 2, (steps, epochs)
+    # the vectorised update of the oracle (what the GPU tests compare the CUDA bag step with) equals the literal loop
+    a = O.OracleSNN(ww0[:n_ids], bb0, [ww1, ww2, rng.uniform(-0.1, 0.1, (H2, 1))], [bb1, bb2, np.zeros(1)])
+    b = O.OracleSNN(ww0[:n_ids], bb0, a.Ws, a.bs)
+    a.train_step(tr_f[:64], tr_y[:64], 0.05, faithful=True)
+    b.train_step(tr_f[:64], tr_y[:64], 0.05, faithful=False)
+    close(a.ww0, b.ww0, 1e-9); close(a.bb0, b.bb0, 1e-9)
