@@ -9,8 +9,8 @@ T.grad / minimize).  What runs is therefore the reference's own statements: feat
 feats_to_layer_one_array / get_fxy / the triple update loop (FNN_wnzh.py:87-96, 248-253, 298-306), build_inds and
 init_var_map (tf_util.py:7-12, 41-82), the forward() graph builders of FM / LR / FNN / FNN_IP_L3/L5/L7 / FNN_OP_L3,
 get_fxy / get_batch_xy / early_stop / watch_train (baseline.py:190-281), collect / stat / load_ipinyou_data
-(ipinyou.py:11-65), and the SNN fine-tuning script SNN_DAE.py (get_fi_h1_y :234-260, its graph :113-163, the ww0 / bb0
-update loop :282-288).
+(ipinyou.py:11-65), and the SNN fine-tuning scripts SNN_DAE.py / SNN_RBM.py (get_fi_h1_y SNN_DAE.py:234-260, the graph :113-163,
+the ww0 / bb0 update loop :282-288).
 
 Fixes applied (every one is asserted to match, so a changed reference fails loudly):
   * `print x, y` statements -> print(x, y)            (token-level, any file)
@@ -34,8 +34,8 @@ OUT = os.path.join(HERE, "_ref", "python")
 FILES = ["FNN_wnzh.py", "dl_utils.py", "data_fm.py", "tf_util.py", "FM.py", "LR.py", "FNN.py", "FNN_IP_L3.py", "FNN_IP_L5.py",
          "FNN_IP_L7.py", "FNN_OP_L3.py", "baseline.py", "ipinyou.py",
          # the SNN fine-tuning script (embedding-bag first layer); its pre-training module is only imported
-         # (get_da_weights is not called when the weight pickle of SNN_DAE.py:84-86 exists)
-         "SNN_DAE.py", "sampling_based_denosing_autoencoder.py"]
+         # (get_da_weights / get_rbm_weights are not called when the weight pickle of SNN_DAE.py:84-86 / SNN_RBM.py:84-86 exists)
+         "SNN_DAE.py", "sampling_based_denosing_autoencoder.py", "SNN_RBM.py", "sampling_based_gaussian_binary_rbm_sparse.py"]
 
 # (file, old, new, why) -- `old` must occur exactly `count` times (default 1)
 PATCHES = [
@@ -54,6 +54,8 @@ PATCHES = [
     ("data_fm.py", None, None, None),
     ("SNN_DAE.py", "n_batch=train_size/batch_size", "n_batch=train_size//batch_size", "Py2 floor division; the value bounds range()"),
     ("SNN_DAE.py", "start_t = time.clock()", "start_t = time.perf_counter()", "time.clock() is gone in Python 3.8+ (an unused timer)"),
+    ("SNN_RBM.py", "n_batch = train_size / batch_size", "n_batch = train_size // batch_size", "Py2 floor division; the value bounds range()"),
+    ("SNN_RBM.py", "start_t = time.clock()", "start_t = time.perf_counter()", "time.clock() is gone in Python 3.8+ (an unused timer)"),
 ]
 
 

@@ -86,21 +86,23 @@ def run_fnn_wnzh(workdir, argv=(), quiet=True, budget_s=None):
     return g, calls
 
 
-def run_snn_dae(workdir, weights, quiet=True, budget_s=None):
-    """Executes the converted SNN_DAE.py top to bottom.  workdir/data/{train,test}.fm.txt must exist (batch_size is 1000 and
-    x_dim 133465 in the script, SNN_DAE.py:19,41); `weights` = (ww0, bb0, ww1, bb1, ww2, bb2) is written to the pickle the script
-    loads instead of pre-training (dropda_2997_.p, :83-86).  Returns (globals, calls) like run_fnn_wnzh."""
+def run_snn_dae(workdir, weights, quiet=True, budget_s=None, script="SNN_DAE.py"):
+    """Executes the converted SNN_DAE.py (or script="SNN_RBM.py") top to bottom.  workdir/data/{train,test}.fm.txt must exist
+    (batch_size is 1000 and x_dim 133465 in the scripts, SNN_DAE.py:19,41); `weights` = (ww0, bb0, ww1, bb1, ww2, bb2) is written to
+    the pickle the script loads instead of pre-training (dropda_2997_.p, SNN_DAE.py:83-86; rbm_2997_.p, SNN_RBM.py:84-86).  Returns
+    (globals, calls) like run_fnn_wnzh."""
     import pickle
     assert available(), "oracle/_ref is not built (needs /root/reference)"
     py = os.path.join(workdir, "python")
     os.makedirs(py, exist_ok=True)
     os.makedirs(os.path.join(workdir, "log"), exist_ok=True)
-    with open(os.path.join(py, "dropda_2997_.p"), "wb") as f:
+    with open(os.path.join(py, {"SNN_DAE.py": "dropda_2997_.p", "SNN_RBM.py": "rbm_2997_.p"}[script]), "wb") as f:
         pickle.dump(tuple(weights), f)
-    _fresh("theano", "theano.tensor", "theano.tensor.shared_randomstreams", "dl_utils", "data_fm", "sampling_based_denosing_autoencoder")
+    _fresh("theano", "theano.tensor", "theano.tensor.shared_randomstreams", "theano.sparse", "dl_utils", "data_fm",
+           "sampling_based_denosing_autoencoder", "sampling_based_gaussian_binary_rbm_sparse")
     linecache.clearcache()
     old_argv = sys.argv
-    sys.argv = ["SNN_DAE.py"]
+    sys.argv = [script]
     buf = io.StringIO()
     try:
         with _paths(py):
@@ -109,7 +111,7 @@ def run_snn_dae(workdir, weights, quiet=True, budget_s=None):
             theano.BUDGET_S, theano._FIRST_CALL[0] = budget_s, None
             with contextlib.redirect_stdout(buf if quiet else sys.stdout):
                 try:
-                    g = runpy.run_path(os.path.join(REF, "SNN_DAE.py"), run_name="__main__")
+                    g = runpy.run_path(os.path.join(REF, script), run_name="__main__")
                 except theano.BudgetExceeded:
                     g = {"__stopped__": True}
                 finally:

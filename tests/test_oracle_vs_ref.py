@@ -476,14 +476,16 @@ def test_bench_times_the_reference_script_itself():
     assert sys.modules["theano"].BUDGET_S is None
 
 
-def test_snn_dae_script_equals_oracle(tmp_path):
-    """the reference's own SNN_DAE.py (converted, run top to bottom from the weight pickle it loads, SNN_DAE.py:83-86)
+@pytest.mark.parametrize("script,lr", [("SNN_DAE.py", 0.0005), ("SNN_RBM.py", 0.001)])
+def test_snn_dae_script_equals_oracle(tmp_path, script, lr):
+    """the reference's own SNN_DAE.py / SNN_RBM.py (the same graph and loop; lr 0.0005 / 0.001, dropout 0.99 / 0.98 for
+    advertiser 2997, SNN_DAE.py:41-49, SNN_RBM.py:52-58) (converted, run top to bottom from the weight pickle it loads, SNN_DAE.py:83-86)
     against OracleSNN, call by call: the dense inputs x = sigmoid(sum ww0[feat] + bb0) of every train() call (get_fi_h1_y :234-260 --
     they carry the ww0 / bb0 updates of all earlier steps, :282-288), gx and the weights train() returns (:113-163, dropout draws
     taken from the call log), and the per-epoch predict() passes over the train and test files (:164-196)."""
     rng = np.random.default_rng(3)
     X_DIM, H0, H1, H2, N = 133465, 200, 300, 100, 1000          # x_dim, hidden0/1/2 of advertiser 2997 and batch_size (:19,41-45)
-    lr, lambda1 = 0.0005, 0.0                                     # :46-49
+    lambda1 = 0.0                                                 # :46-49
     wd = str(tmp_path)
     os.makedirs(os.path.join(wd, "data"))
     n_ids = 4000
@@ -500,7 +502,7 @@ def test_snn_dae_script_equals_oracle(tmp_path):
     ww0, bb0 = rng.uniform(-0.05, 0.05, (X_DIM, H0)), rng.uniform(-0.1, 0.1, H0)
     ww1, bb1 = rng.uniform(-0.1, 0.1, (H0, H1)), rng.uniform(-0.1, 0.1, H1)
     ww2, bb2 = rng.uniform(-0.1, 0.1, (H1, H2)), rng.uniform(-0.1, 0.1, H2)
-    _, calls = ref_run.run_snn_dae(wd, (ww0, bb0, ww1, bb1, ww2, bb2), budget_s=4.0)
+    _, calls = ref_run.run_snn_dae(wd, (ww0, bb0, ww1, bb1, ww2, bb2), budget_s=4.0, script=script)
     net = O.OracleSNN(ww0, bb0, [ww1, ww2, np.zeros((H2, 1))], [bb1, bb2, np.zeros(1)], act="tanh")      # ww3 = 0, bb3 = 0 (:93-94)
     steps = epochs = 0
     k = 0
