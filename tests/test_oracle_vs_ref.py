@@ -537,3 +537,37 @@ def test_snn_dae_script_equals_oracle(tmp_path, script, lr):
     a.train_step(tr_f[:64], tr_y[:64], 0.05, faithful=True)
     b.train_step(tr_f[:64], tr_y[:64], 0.05, faithful=False)
     close(a.ww0, b.ww0, 1e-9); close(a.bb0, b.bb0, 1e-9)
+
+
+def test_data_fm_class_equals_the_loaders(tmp_path):
+    """data_fm.DataFM (data_fm.py:14-84, the class form of FNN_wnzh.py:62-96, 224-253), run as it is: the parsed model (w_0, k,
+    xdim, feat_weights, feat_field), feat_layer_one_index, and get_batch_data -- feature lists, labels and the host-gathered dense
+    x of every line, duplicate-field and missing-field lines included -- equal data.load_fm_model / load_fm_samples and the
+    oracle's gather of the same ids."""
+    import importlib
+    import sys
+    from deepctr_b200 import data as D
+    case = C.write_s1_demo(str(tmp_path), dup_field=True)
+    model_path = os.path.join(str(tmp_path), "data", "fm.model.txt")
+    train_path = os.path.join(str(tmp_path), "data", "train.fm.txt")
+    sys.modules.pop("data_fm", None)
+    with ref_run._paths():
+        dfm = importlib.import_module("data_fm").DataFM(model_path)
+        f_ref, x_ref, y_ref = dfm.get_batch_data(train_path, 1, 60)          # lines 1..60 (linecache is 1-based)
+        idx = [dfm.feat_layer_one_index(feat, l) for feat in (0, 5, case["X"] - 1) for l in (0, 3, dfm.k - 1)]
+    m = D.load_fm_model(model_path)
+    assert dfm.w_0 == m["w_0"] and dfm.k == m["k"] == case["d"] and dfm.xdim == 1 + 16 * m["k"]
+    assert np.array_equal(np.array([dfm.feat_weights[f] for f in range(case["X"])]), m["table"])
+    assert np.array_equal(np.array([dfm.feat_field[f] for f in range(case["X"])]), m["feat_field"])
+    assert idx == [1 + m["feat_field"][feat] * m["k"] + l for feat in (0, 5, case["X"] - 1) for l in (0, 3, m["k"] - 1)]
+    feats, y = D.load_fm_samples(train_path)
+    assert np.array_equal(y_ref, y[:60]) and [list(r[r >= 0]) for r in feats[:60]] == [list(r) for r in f_ref]
+    # the dense rows: slot of a feature = its field, a later feature of the same field overwrites, a missing field stays 0
+    x = np.zeros((60, dfm.xdim))
+    x[:, 0] = m["w_0"]
+    for t in range(60):
+        for feat in feats[t][feats[t] >= 0]:
+            o = 1 + m["feat_field"][feat] * m["k"]
+            x[t, o:o + m["k"]] = m["table"][feat]
+    assert np.array_equal(x_ref, x)
+    assert any(len(r) == 17 for r in f_ref) and any(len(r) == 15 for r in f_ref)      # the adversarial lines are inside the sample
