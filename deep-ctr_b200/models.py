@@ -225,6 +225,12 @@ class _Base(object):
         self._check_ids()
         return float(self._out_np[self.N]), self._out_np[:self.N].copy()
 
+    def _no_step_in_flight(self):
+        """the synchronous calls reuse the staging blocks at once: a pipelined step that has not been collected would lose its inputs"""
+        p = getattr(self, "_pipe", None)
+        if p is not None and p["pending"] is not None:
+            raise RuntimeError("a pipelined step is still in flight: collect it with flush_async() before a synchronous call")
+
     def _stage_ids(self, ids, wts, y):
         h = self._stage.host
         np.copyto(h["ids"], ids, casting="unsafe")
@@ -232,6 +238,7 @@ class _Base(object):
         np.copyto(h["y"], y, casting="unsafe")
 
     def _stage_and_step(self, ids, wts, y):
+        self._no_step_in_flight()
         self._stage_ids(ids, wts, y)
         self._pre_step()
         return self._finish_step()
@@ -319,6 +326,7 @@ class _Base(object):
     def _predict_chunks(self, ids, wts, out_dev=None):
         """Inference over E rows in chunks of the static batch (last chunk padded with row 0 / weight 0).  With `out_dev`
         (a float32 device tensor of E elements) the predictions stay on the device and nothing is copied back."""
+        self._no_step_in_flight()
         e, h = self.engine, self._stage.host
         E = ids.shape[0]
         out = np.empty(E, dtype=np.float32) if out_dev is None else None
@@ -586,6 +594,7 @@ class _FNNBase(_Base):
         np.copyto(self._stage.host["y"], np.asarray(feed[self.lbl_hldr]).reshape(self.N), casting="unsafe")
 
     def train_step(self, feed):
+        self._no_step_in_flight()
         self._stage_feed(feed)
         self._pre_step()
         return self._finish_step()

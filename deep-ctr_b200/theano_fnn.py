@@ -169,6 +169,7 @@ class FNN_wnzh(_Base):
 
     def train(self, feats, y):
         """One step of the loop body FNN_wnzh.py:296-306.  feats: [N, <=16] feature ids (-1 = absent)."""
+        self._no_step_in_flight()
         self._stage_feats(feats)
         np.copyto(self._stage.host["y"], np.asarray(y).reshape(self.N), casting="unsafe")
         self._pre_step()
@@ -209,6 +210,7 @@ class FNN_wnzh(_Base):
 
     def _predict_into(self, feats, out_np, out_dev):
         E = feats.shape[0]
+        self._no_step_in_flight()
         saved = self._swap_masks(None)
         self.engine.acts = self._acts_eval
         self._bind_status()

@@ -282,6 +282,14 @@ def test_pipelined_call_returns_each_result_one_call_late_on_fakes():
         with pytest.raises(IndexError, match="77"):
             m.train_async(*batches[1])
         assert m.flush_async()[0] == 2 * N * J
+        # a synchronous call while a pipelined step is in flight would overwrite that step's staging block: refused until it is collected
+        assert m.train_async(*batches[2]) is None
+        with pytest.raises(RuntimeError, match="flush_async"):
+            m.train(*batches[3])
+        with pytest.raises(RuntimeError, match="flush_async"):
+            m.predict(batches[3][0])
+        assert m.flush_async()[0] == 3 * N * J
+        m._no_step_in_flight()
         m.dp = object()
         with pytest.raises(NotImplementedError):
             m.train_async(*batches[0])
